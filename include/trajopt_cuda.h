@@ -1,0 +1,264 @@
+/* trajopt_cuda.h — C ABI of libtrajopt_cuda.so (B200 / sm_100a collision-term evaluation).
+ *
+ * This is the drop-in boundary for ONE hot path of trajopt 0.35: the per-SQP-iteration evaluation of
+ * collision terms and their gradients over every (trajectory, timestep/sub-state, link pair).
+ * The reference has no FFI on this path; its seams are C++ virtual interfaces.  Each entry point below
+ * names the reference interface it stands behind (paths relative to the trajopt source tree):
+ *
+ *   tc_scene_create     evaluator constructors                      trajopt/src/collision_terms.cpp:600-644,737-808,978-1051
+ *                                                                   trajopt_ifopt/src/constraints/collision/discrete_collision_evaluators.cpp:38-87
+ *                                                                   trajopt_ifopt/src/constraints/collision/continuous_collision_evaluators.cpp:41-95,266-315
+ *   tc_eval             CalcCollisions / calcCollisions / calcCollisionData (geometry pass) and
+ *                       GetGradient / getGradient (linearisation)   trajopt/src/collision_terms.cpp:195-332,653-688,817-898,1060-1161
+ *                                                                   trajopt_common/src/collision_utils.cpp:116-221
+ *                                                                   trajopt_ifopt/.../discrete_collision_evaluators.cpp:89-202
+ *                                                                   trajopt_ifopt/.../continuous_collision_evaluators.cpp:97-248,317-458
+ *   tc_result_contacts  tesseract::collision::ContactResultMap as flattened by
+ *                       flattenWrapperResults                       trajopt/src/collision_terms.cpp:436-461
+ *   tc_result_gradients trajopt_common::GradientResults             trajopt_common/include/trajopt_common/collision_types.h:187-235
+ *   tc_result_rows      DiscreteCollisionConstraintD / ContinuousCollisionConstraintD ::getValues/getJacobian
+ *                                                                   trajopt_ifopt/.../discrete_collision_constraint.cpp:177-283
+ *                                                                   trajopt_ifopt/.../continuous_collision_constraint.cpp:276-417
+ *                       and CollisionsToDistanceExpressions (legacy AffExpr rows)
+ *                                                                   trajopt/src/collision_terms.cpp:341-386,463-554
+ *   tc_result_sets      GradientResultsSet grouping, top-max_num_cnt order, weighted-average rows
+ *                       of the fixed-size constraints               trajopt_ifopt/.../discrete_collision_evaluators.cpp:101-148
+ *                                                                   trajopt_ifopt/.../continuous_collision_evaluators.cpp:113-162
+ *                                                                   trajopt_ifopt/.../weighted_average_methods.cpp:31-107
+ *                                                                   trajopt_ifopt/.../discrete_collision_constraint.cpp:68-141
+ *                                                                   trajopt_ifopt/.../continuous_collision_constraint.cpp:80-236
+ *   tc_result_cost      CollisionCost::value / CollisionConstraint::value
+ *                                                                   trajopt/src/collision_terms.cpp:1287-1306,1367-1386
+ *   tc_allgather_best   (no reference counterpart: multi-start winner selection across GPUs)
+ *
+ * Conventions: plain C, opaque handles, int status (0 = TC_OK), thread-local error string.
+ * All matrices are row-major.  A pose is 12 doubles = the top 3x4 of a homogeneous transform.
+ * Distinct handles may be used from distinct host threads concurrently; one handle is not re-entrant
+ * (same rule as a reference evaluator instance, trajopt/include/trajopt/collision_terms.hpp:236-240).
+ * There is no CPU fallback: every call fails with TC_ERR_CUDA when no sm_100 device is usable.
+ */
+#ifndef TRAJOPT_CUDA_H
+#define TRAJOPT_CUDA_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define TC_ABI_VERSION 1
+
+/* status codes */
+enum {
+  TC_OK = 0,
+  TC_ERR_INVALID = 1,   /* bad argument / inconsistent description */
+  TC_ERR_CUDA = 2,      /* CUDA runtime error or no usable device  */
+  TC_ERR_UNSUPPORTED = 3, /* shape type / evaluator outside the scoped geometry */
+  TC_ERR_OVERFLOW = 4,  /* a bounded arena overflowed; counts tell which */
+  TC_ERR_NCCL = 5
+};
+
+/* joint types of the flattened kinematic tree */
+enum { TC_JOINT_FIXED = 0, TC_JOINT_REVOLUTE = 1, TC_JOINT_PRISMATIC = 2 };
+
+/* collision shape types (convex only; boxes and convex meshes are both vertex hulls) */
+enum { TC_SHAPE_SPHERE = 0, TC_SHAPE_HULL = 1, TC_SHAPE_CAPSULE = 2, TC_SHAPE_CYLINDER = 3, TC_SHAPE_CONE = 4 };
+
+/* evaluator kinds; values follow tesseract::collision::CollisionEvaluatorType as used by the JSON
+ * front end (trajopt/src/problem_description.cpp:1654-1657): DISCRETE=1 ... LVS_CONTINUOUS=4 */
+enum { TC_EVAL_DISCRETE = 1, TC_EVAL_LVS_DISCRETE = 2, TC_EVAL_CONTINUOUS = 3, TC_EVAL_LVS_CONTINUOUS = 4 };
+
+/* which stack's conventions apply where the two stacks differ (Jacobian evaluation state,
+ * CONTINUOUS = single sweep or not) */
+enum { TC_STACK_IFOPT = 0, TC_STACK_LEGACY = 1 };
+
+/* arithmetic of the narrow phase */
+enum { TC_PRECISION_F64 = 0, TC_PRECISION_F32 = 1 };
+
+/* tesseract::collision::ContinuousCollisionType */
+enum { TC_CC_NONE = 0, TC_CC_TIME0 = 1, TC_CC_TIME1 = 2, TC_CC_BETWEEN = 3 };
+
+/* what tc_eval has to produce */
+enum { TC_WANT_COST = 1, TC_WANT_CONTACTS = 2, TC_WANT_GRADIENTS = 4 };
+
+/* contact flags */
+enum { TC_FLAG_EPA = 1, TC_FLAG_DEGENERATE = 2, TC_FLAG_UNCONVERGED = 4 };
+
+typedef struct tc_scene tc_scene;
+typedef struct tc_result tc_result;
+
+/* Scene = robot kinematics + collision geometry + pair tables; immutable after creation.
+ * Active links (those moved by the planning group's joints) must come first in the link arrays. */
+typedef struct tc_scene_desc {
+  /* kinematic tree of the planning group, topologically ordered (frame_parent[f] < f, -1 = group base) */
+  int32_t n_dof;
+  int32_t n_frames;
+  const int32_t* frame_parent;     /* [n_frames] */
+  const int32_t* frame_joint_type; /* [n_frames] TC_JOINT_* */
+  const int32_t* frame_dof;        /* [n_frames] dof index or -1 */
+  const double* frame_axis;        /* [n_frames][3] unit axis in the joint frame */
+  const double* frame_origin;      /* [n_frames][12] parent frame -> joint frame at q = 0 */
+  double base_pose[12];            /* world <- group base link */
+  /* collision links */
+  int32_t n_links;
+  int32_t n_active_links;
+  const int32_t* link_frame;       /* [n_links] frame of an active link, -1 for static links */
+  const double* link_pose;         /* [n_links][12] world pose of static links (ignored for active) */
+  /* collision shapes */
+  int32_t n_shapes;
+  const int32_t* shape_type;       /* [n_shapes] TC_SHAPE_* */
+  const int32_t* shape_link;       /* [n_shapes] owning link */
+  const int32_t* shape_id;         /* [n_shapes] index of the shape within its link (ContactResult::shape_id) */
+  const double* shape_params;      /* [n_shapes][4] sphere: r; capsule/cylinder/cone: r, half length (axis = local z) */
+  const double* shape_pose;        /* [n_shapes][12] shape frame in the link frame */
+  const int32_t* shape_vert_offset;/* [n_shapes] first vertex of a hull in verts */
+  const int32_t* shape_vert_count; /* [n_shapes] */
+  int32_t n_verts;
+  const double* verts;             /* [n_verts][3] hull vertices in the shape frame */
+  /* pair tables */
+  const uint8_t* acm;              /* [n_links][n_links] non-zero = pair never checked (allowed collision) */
+  const double* pair_margin;       /* [n_links][n_links] or NULL -> default_margin everywhere */
+  const double* pair_coeff;        /* [n_links][n_links] or NULL -> default_coeff everywhere  */
+  double default_margin;           /* CollisionMarginData default, WITHOUT the buffer */
+  double default_coeff;
+  double margin_buffer;            /* TrajOptCollisionConfig::collision_margin_buffer */
+} tc_scene_desc;
+
+/* One batched evaluation: B trajectories x T timesteps, q[B][T][n_dof] row-major. */
+typedef struct tc_eval_desc {
+  int32_t evaluator;         /* TC_EVAL_* */
+  int32_t stack;             /* TC_STACK_* */
+  int32_t precision;         /* TC_PRECISION_* */
+  int32_t want;              /* TC_WANT_* mask */
+  double lvs_length;         /* longest_valid_segment_length */
+  const uint8_t* fixed_steps;/* [T] non-zero = timestep is fixed (host memory), or NULL */
+  int32_t q_on_device;       /* non-zero: q is a device pointer */
+  int32_t reserved;
+} tc_eval_desc;
+
+/* One contact = the fields of tesseract::collision::ContactResult the path reads
+ * (trajopt/src/collision_terms.cpp:105-124,215-223) plus its position in the batch. */
+typedef struct tc_contact {
+  double distance;
+  double normal[3];                  /* unit, from link_ids[0]'s shape towards link_ids[1]'s */
+  double nearest_points[2][3];       /* world */
+  double nearest_points_local[2][3]; /* in the link frame at transform[i] */
+  double cc_time[2];                 /* -1 when not continuous */
+  int32_t cc_type[2];                /* TC_CC_* */
+  int32_t link_ids[2];               /* scene link indices, link_ids[0] < link_ids[1] */
+  int32_t shape_id[2];
+  int32_t subshape_id[2];
+  int32_t traj;                      /* b */
+  int32_t term;                      /* timestep (DISCRETE) or segment t = (t, t+1) */
+  int32_t substep;                   /* LVS sub-state / sub-segment index */
+  int32_t pair;                      /* index into the scene's link-pair table */
+  int32_t state;                     /* global sub-state index of the T0 pose */
+  int32_t flags;                     /* TC_FLAG_* */
+} tc_contact;
+
+/* trajopt_common::GradientResults without the vectors (those come as a dense array) */
+typedef struct tc_gradient {
+  double error;              /* margin - distance */
+  double error_with_buffer;  /* margin + buffer - distance */
+  double scale0[2];          /* gradients[i].scale     (T0 block) */
+  double scale1[2];          /* cc_gradients[i].scale  (T1 block) */
+  int32_t has_gradient[2];
+  int32_t cc_type[2];
+} tc_gradient;
+
+typedef struct tc_counts {
+  int64_t n_states;      /* sub-states after LVS subdivision */
+  int64_t n_units;       /* tested states (discrete) or swept sub-segments (cast): S */
+  int64_t n_dense;       /* S x candidate link pairs  (the headline count)   */
+  int64_t n_candidates;  /* shape-pair tests entering the broadphase          */
+  int64_t n_narrowphase; /* shape-pair tests surviving the AABB test          */
+  int64_t n_contacts;
+  int64_t n_rows;
+  int64_t nnz;
+  int64_t gjk_iters;     /* sum of GJK iterations                              */
+  int64_t support_verts; /* sum of hull vertices scanned by support calls     */
+  int64_t n_epa;
+  int64_t n_unconverged;
+  int64_t n_terms;       /* B x terms per trajectory                          */
+  int64_t overflow;      /* non-zero if an arena overflowed                   */
+} tc_counts;
+
+/* one row set of the fixed-size constraints (GradientResultsSet reduced to what the constraint reads) */
+typedef struct tc_set {
+  int32_t traj, term, pair;
+  int32_t shape_key[2];      /* cantorHash(shape_id, subshape_id) per link */
+  int32_t n_results;
+  int32_t has_error[2][2];   /* [link][0: excluding T1, 1: excluding T0] */
+  double coeff;
+  double error[2][2];
+  double error_with_buffer[2][2];
+} tc_set;
+
+/* ---- lifetime ---- */
+int tc_init(int device_ordinal);
+const char* tc_last_error(void);
+int tc_abi_version(void);
+
+/* ---- scene ---- */
+int tc_scene_create(const tc_scene_desc* desc, tc_scene** out);
+void tc_scene_destroy(tc_scene* scene);
+/* candidate link pairs (>= 1 active link, not ACM-disabled, sorted by (link0, link1)) */
+int tc_scene_num_pairs(const tc_scene* scene);
+int tc_scene_pairs(const tc_scene* scene, int32_t* link0, int32_t* link1, double* margin, double* coeff);
+
+/* ---- evaluation ---- */
+int tc_result_create(tc_scene* scene, tc_result** out);
+void tc_result_destroy(tc_result* res);
+/* Runs the whole pass on `cuda_stream` (a cudaStream_t, NULL = default stream) and synchronises it
+ * before returning, so the accessors below can be called right away. */
+int tc_eval(tc_scene* scene, const tc_eval_desc* desc, const double* q, int32_t B, int32_t T,
+            tc_result* out, void* cuda_stream);
+/* Asynchronous variant used by benchmarks: enqueues everything, returns without synchronising.
+ * tc_result_sync() must be called before any accessor. */
+int tc_eval_async(tc_scene* scene, const tc_eval_desc* desc, const double* q, int32_t B, int32_t T,
+                  tc_result* out, void* cuda_stream);
+int tc_result_sync(tc_result* res);
+
+/* ---- result access (valid until the next tc_eval on the same result) ---- */
+int tc_result_counts(const tc_result* res, tc_counts* counts);
+/* contacts sorted by (traj, term, link pair, substep, shape pair) */
+int tc_result_contacts(const tc_result* res, tc_contact* dst, size_t cap);
+/* transform[i] and cc_transform[i] of every contact: dst[n_contacts][2 links][2 (T0, T1)][12] */
+int tc_result_contact_transforms(const tc_result* res, double* dst, size_t cap_contacts);
+/* first contact of every (traj, term): term_ptr[n_terms + 1] */
+int tc_result_term_ptr(const tc_result* res, int64_t* term_ptr);
+/* per-contact gradient records; grad[n_contacts][2 links][2 (T0 block, T1 block)][n_dof] */
+int tc_result_gradients(const tc_result* res, tc_gradient* rec, double* grad, size_t cap_contacts);
+/* One row per contact, in contact order.  Columns are trajectory-local variable indices
+ * t * n_dof + j.  ifopt stack: row_value = margin - distance, val = -(sum_i scale_i grad_i)
+ * (the D constraints).  legacy stack: row_value = constant of the affine distance expression
+ * d(x) = row_value + val . x  (CollisionsToDistanceExpressions + CalcDistExpressions*). */
+int tc_result_rows(const tc_result* res, int64_t* row_ptr, int32_t* col_idx, double* val, double* row_value,
+                   double* row_coeff, double* row_margin);
+/* fixed-size constraints: sets of every term sorted as the evaluator sorts them, the first
+ * min(max_num_cnt, n) of each term turned into rows.  set_ptr[n_terms + 1].
+ * values[n_terms][max_num_cnt], coeffs idem, jac[n_terms][max_num_cnt][2][n_dof] (T0 block, T1 block) */
+int tc_result_sets(const tc_result* res, int32_t max_num_cnt, int64_t* set_ptr, tc_set* sets, size_t cap_sets,
+                   double* values, double* coeffs, double* jac);
+/* sum over contacts of coeff * max(margin - distance, 0): per (traj, term) and per trajectory */
+int tc_result_cost(const tc_result* res, double* cost_per_term, double* cost_per_traj);
+/* device pointer to cost_per_traj[B] (stays on the GPU for multi-start selection) */
+int tc_result_cost_device(const tc_result* res, const double** dev_ptr);
+
+/* ---- multi-GPU helper for multi-start: every rank contributes its best (cost, global index);
+ * all ranks receive the global winner.  nccl_comm is an ncclComm_t. ---- */
+int tc_allgather_best(double local_best_cost, int64_t local_best_idx, void* nccl_comm, void* cuda_stream,
+                      double* best_cost, int64_t* best_idx, int32_t* best_rank);
+
+/* ---- measurement helpers (bench only) ---- */
+/* register-resident DFMA / FFMA loop: returns achieved TFLOP/s (2 flop per FMA) */
+int tc_measure_fma_peak(int precision, double* tflops);
+/* duration in ms of each kernel stage of the last tc_eval (CUDA events on the eval stream):
+ * [0] plan+FK, [1] broadphase+narrowphase, [2] EPA, [3] sort+gradients+rows, [4] total */
+int tc_result_stage_ms(const tc_result* res, float ms[5]);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* TRAJOPT_CUDA_H */

@@ -1,0 +1,323 @@
+"""ctypes view of the C ABI declared in include/trajopt_cuda.h.
+
+This is the thin Python driver used by tests, bench.py and __graft_entry__: it only marshals numpy
+arrays to the `tc_*` entry points of libtrajopt_cuda.so.  No arithmetic of the hot path happens here and
+there is no fallback: if the shared library (or a CUDA device) is missing the calls raise.
+
+The same class also drives any other library exporting the same entry points under another prefix
+(tests load the CPU oracle, `orc_*`, through it — the oracle is never loaded from this package).
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "csrc", "libtrajopt_cuda.so")
+
+# ---- enums (include/trajopt_cuda.h) ----
+TC_OK = 0
+JOINT_FIXED, JOINT_REVOLUTE, JOINT_PRISMATIC = 0, 1, 2
+SHAPE_SPHERE, SHAPE_HULL, SHAPE_CAPSULE, SHAPE_CYLINDER, SHAPE_CONE = 0, 1, 2, 3, 4
+EVAL_DISCRETE, EVAL_LVS_DISCRETE, EVAL_CONTINUOUS, EVAL_LVS_CONTINUOUS = 1, 2, 3, 4
+STACK_IFOPT, STACK_LEGACY = 0, 1
+PRECISION_F64, PRECISION_F32 = 0, 1
+CC_NONE, CC_TIME0, CC_TIME1, CC_BETWEEN = 0, 1, 2, 3
+WANT_COST, WANT_CONTACTS, WANT_GRADIENTS = 1, 2, 4
+WANT_ALL = 7
+FLAG_EPA, FLAG_DEGENERATE, FLAG_UNCONVERGED = 1, 2, 4
+
+_pd = C.POINTER(C.c_double)
+_pi = C.POINTER(C.c_int32)
+_pl = C.POINTER(C.c_int64)
+_pb = C.POINTER(C.c_uint8)
+
+
+class SceneDesc(C.Structure):
+    _fields_ = [
+        ("n_dof", C.c_int32), ("n_frames", C.c_int32),
+        ("frame_parent", _pi), ("frame_joint_type", _pi), ("frame_dof", _pi),
+        ("frame_axis", _pd), ("frame_origin", _pd), ("base_pose", C.c_double * 12),
+        ("n_links", C.c_int32), ("n_active_links", C.c_int32),
+        ("link_frame", _pi), ("link_pose", _pd),
+        ("n_shapes", C.c_int32),
+        ("shape_type", _pi), ("shape_link", _pi), ("shape_id", _pi),
+        ("shape_params", _pd), ("shape_pose", _pd),
+        ("shape_vert_offset", _pi), ("shape_vert_count", _pi),
+        ("n_verts", C.c_int32), ("verts", _pd),
+        ("acm", _pb), ("pair_margin", _pd), ("pair_coeff", _pd),
+        ("default_margin", C.c_double), ("default_coeff", C.c_double), ("margin_buffer", C.c_double),
+    ]
+
+
+class EvalDesc(C.Structure):
+    _fields_ = [
+        ("evaluator", C.c_int32), ("stack", C.c_int32), ("precision", C.c_int32), ("want", C.c_int32),
+        ("lvs_length", C.c_double), ("fixed_steps", _pb), ("q_on_device", C.c_int32), ("reserved", C.c_int32),
+    ]
+
+
+CONTACT_DTYPE = np.dtype([
+    ("distance", "<f8"), ("normal", "<f8", 3), ("nearest_points", "<f8", (2, 3)),
+    ("nearest_points_local", "<f8", (2, 3)), ("cc_time", "<f8", 2), ("cc_type", "<i4", 2),
+    ("link_ids", "<i4", 2), ("shape_id", "<i4", 2), ("subshape_id", "<i4", 2),
+    ("traj", "<i4"), ("term", "<i4"), ("substep", "<i4"), ("pair", "<i4"), ("state", "<i4"), ("flags", "<i4"),
+], align=True)
+assert CONTACT_DTYPE.itemsize == 200, CONTACT_DTYPE.itemsize
+
+GRADIENT_DTYPE = np.dtype([
+    ("error", "<f8"), ("error_with_buffer", "<f8"), ("scale0", "<f8", 2), ("scale1", "<f8", 2),
+    ("has_gradient", "<i4", 2), ("cc_type", "<i4", 2),
+], align=True)
+assert GRADIENT_DTYPE.itemsize == 64
+
+COUNT_FIELDS = ["n_states", "n_units", "n_dense", "n_candidates", "n_narrowphase", "n_contacts", "n_rows", "nnz",
+                "gjk_iters", "support_verts", "n_epa", "n_unconverged", "n_terms", "overflow"]
+
+SET_DTYPE = np.dtype([
+    ("traj", "<i4"), ("term", "<i4"), ("pair", "<i4"), ("shape_key", "<i4", 2), ("n_results", "<i4"),
+    ("has_error", "<i4", (2, 2)), ("coeff", "<f8"), ("error", "<f8", (2, 2)), ("error_with_buffer", "<f8", (2, 2)),
+], align=True)
+assert SET_DTYPE.itemsize == 112, SET_DTYPE.itemsize
+
+
+def _p(a, t):
+    return a.ctypes.data_as(t)
+
+
+class TcError(RuntimeError):
+    pass
+
+
+class Scene:
+    """Owns a tc_scene handle plus the numpy arrays the description points at."""
+
+    def __init__(self, lib, arrays, margin, coeff, margin_buffer, pair_margin=None, pair_coeff=None):
+        self.lib = lib
+        a = self.arrays = {k: np.ascontiguousarray(v) for k, v in arrays.items()
+                           if isinstance(v, np.ndarray) and v.dtype.kind in "fiu"}
+        d = SceneDesc()
+        d.n_dof = int(arrays["n_dof"])
+        d.n_frames = len(a["frame_parent"])
+        for k in ("frame_parent", "frame_joint_type", "frame_dof"):
+            a[k] = a[k].astype(np.int32)
+            setattr(d, k, _p(a[k], _pi))
+        for k in ("frame_axis", "frame_origin", "link_pose", "shape_params", "shape_pose", "verts"):
+            a[k] = np.ascontiguousarray(a[k], dtype=np.float64)
+            setattr(d, k, _p(a[k], _pd))
+        d.base_pose = (C.c_double * 12)(*[float(x) for x in arrays["base_pose"]])
+        d.n_links = len(a["link_frame"])
+        d.n_active_links = int(arrays["n_active_links"])
+        for k in ("link_frame", "shape_type", "shape_link", "shape_id", "shape_vert_offset", "shape_vert_count"):
+            a[k] = a[k].astype(np.int32)
+            setattr(d, k, _p(a[k], _pi))
+        d.n_shapes = len(a["shape_type"])
+        d.n_verts = len(a["verts"])
+        a["acm"] = np.ascontiguousarray(a["acm"], dtype=np.uint8)
+        d.acm = _p(a["acm"], _pb)
+        if pair_margin is not None:
+            a["pair_margin"] = np.ascontiguousarray(pair_margin, dtype=np.float64)
+            d.pair_margin = _p(a["pair_margin"], _pd)
+        if pair_coeff is not None:
+            a["pair_coeff"] = np.ascontiguousarray(pair_coeff, dtype=np.float64)
+            d.pair_coeff = _p(a["pair_coeff"], _pd)
+        d.default_margin, d.default_coeff, d.margin_buffer = float(margin), float(coeff), float(margin_buffer)
+        self.desc = d
+        self.n_dof = d.n_dof
+        self.n_links = d.n_links
+        self.n_active = d.n_active_links
+        self.margin_buffer = float(margin_buffer)
+        self.handle = C.c_void_p()
+        lib.check(lib.fn("scene_create")(C.byref(d), C.byref(self.handle)))
+
+    def num_pairs(self):
+        return self.lib.fn("scene_num_pairs")(self.handle)
+
+    def pairs(self):
+        n = self.num_pairs()
+        l0, l1 = np.zeros(n, np.int32), np.zeros(n, np.int32)
+        m, c = np.zeros(n), np.zeros(n)
+        self.lib.check(self.lib.fn("scene_pairs")(self.handle, _p(l0, _pi), _p(l1, _pi), _p(m, _pd), _p(c, _pd)))
+        return l0, l1, m, c
+
+    def close(self):
+        if self.handle:
+            self.lib.fn("scene_destroy")(self.handle)
+            self.handle = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+class Result:
+    def __init__(self, lib, scene, handle, B, T, owned=True):
+        self.lib, self.scene, self.handle, self.B, self.T, self.owned = lib, scene, handle, B, T, owned
+
+    def counts(self):
+        buf = np.zeros(len(COUNT_FIELDS), np.int64)
+        self.lib.check(self.lib.fn("result_counts")(self.handle, _p(buf, _pl)))
+        return dict(zip(COUNT_FIELDS, (int(x) for x in buf)))
+
+    def contacts(self):
+        n = self.counts()["n_contacts"]
+        out = np.zeros(n, CONTACT_DTYPE)
+        self.lib.check(self.lib.fn("result_contacts")(self.handle, out.ctypes.data_as(C.c_void_p), C.c_size_t(n)))
+        return out
+
+    def contact_transforms(self):
+        n = self.counts()["n_contacts"]
+        out = np.zeros((n, 2, 2, 12))
+        self.lib.check(self.lib.fn("result_contact_transforms")(self.handle, _p(out, _pd), C.c_size_t(n)))
+        return out
+
+    def term_ptr(self):
+        n = self.counts()["n_terms"]
+        out = np.zeros(n + 1, np.int64)
+        self.lib.check(self.lib.fn("result_term_ptr")(self.handle, _p(out, _pl)))
+        return out
+
+    def gradients(self):
+        n = self.counts()["n_contacts"]
+        rec = np.zeros(n, GRADIENT_DTYPE)
+        grad = np.zeros((n, 2, 2, self.scene.n_dof))
+        self.lib.check(self.lib.fn("result_gradients")(self.handle, rec.ctypes.data_as(C.c_void_p), _p(grad, _pd),
+                                                       C.c_size_t(n)))
+        return rec, grad
+
+    def rows(self):
+        n = self.counts()["n_contacts"]
+        nd = self.scene.n_dof
+        row_ptr = np.zeros(n + 1, np.int64)
+        col = np.zeros(max(1, 2 * n * nd), np.int32)
+        val = np.zeros(max(1, 2 * n * nd))
+        rv, rc, rm = np.zeros(n), np.zeros(n), np.zeros(n)
+        self.lib.check(self.lib.fn("result_rows")(self.handle, _p(row_ptr, _pl), _p(col, _pi), _p(val, _pd),
+                                                  _p(rv, _pd), _p(rc, _pd), _p(rm, _pd)))
+        nnz = int(row_ptr[-1])
+        return dict(row_ptr=row_ptr, col_idx=col[:nnz], val=val[:nnz], value=rv, coeff=rc, margin=rm)
+
+    def sets(self, max_num_cnt):
+        nt = self.counts()["n_terms"]
+        nc = self.counts()["n_contacts"]
+        nd = self.scene.n_dof
+        set_ptr = np.zeros(nt + 1, np.int64)
+        sets = np.zeros(max(1, nc), SET_DTYPE)
+        values = np.zeros((nt, max_num_cnt))
+        coeffs = np.zeros((nt, max_num_cnt))
+        jac = np.zeros((nt, max_num_cnt, 2, nd))
+        self.lib.check(self.lib.fn("result_sets")(self.handle, C.c_int32(max_num_cnt), _p(set_ptr, _pl),
+                                                  sets.ctypes.data_as(C.c_void_p), C.c_size_t(len(sets)),
+                                                  _p(values, _pd), _p(coeffs, _pd), _p(jac, _pd)))
+        return dict(set_ptr=set_ptr, sets=sets[:int(set_ptr[-1])], values=values, coeffs=coeffs, jac=jac)
+
+    def cost(self):
+        nt = self.counts()["n_terms"]
+        per_term, per_traj = np.zeros(max(1, nt)), np.zeros(self.B)
+        self.lib.check(self.lib.fn("result_cost")(self.handle, _p(per_term, _pd), _p(per_traj, _pd)))
+        return per_term[:nt], per_traj
+
+    def close(self):
+        if self.owned and self.handle:
+            self.lib.fn("result_destroy")(self.handle)
+            self.handle = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+def make_eval_desc(evaluator, stack=STACK_IFOPT, lvs=0.005, fixed=None, want=WANT_ALL, precision=PRECISION_F64,
+                   q_on_device=False):
+    d = EvalDesc()
+    d.evaluator, d.stack, d.precision, d.want = int(evaluator), int(stack), int(precision), int(want)
+    d.lvs_length = float(lvs)
+    keep = None
+    if fixed is not None:
+        keep = np.ascontiguousarray(fixed, dtype=np.uint8)
+        d.fixed_steps = _p(keep, _pb)
+    d.q_on_device = 1 if q_on_device else 0
+    return d, keep
+
+
+class Lib:
+    """A loaded shared library exporting `<prefix>scene_create`, `<prefix>eval`, ..."""
+
+    def __init__(self, path=LIB_PATH, prefix="tc_"):
+        if not os.path.exists(path):
+            raise TcError(f"{path} is missing: build it with __graft_entry__.build() (no fallback exists)")
+        self.dll = C.CDLL(path)
+        self.prefix = prefix
+        self.path = path
+        le = getattr(self.dll, prefix + "last_error")
+        le.restype = C.c_char_p
+        for name in ("scene_destroy", "result_destroy"):
+            getattr(self.dll, prefix + name).restype = None
+            getattr(self.dll, prefix + name).argtypes = [C.c_void_p]
+
+    def fn(self, name):
+        return getattr(self.dll, self.prefix + name)
+
+    def last_error(self):
+        return self.fn("last_error")().decode()
+
+    def check(self, status):
+        if status != TC_OK:
+            raise TcError(f"{self.prefix}* call failed with status {status}: {self.last_error()}")
+
+    def scene(self, arrays, margin, coeff, margin_buffer, **kw):
+        return Scene(self, arrays, margin, coeff, margin_buffer, **kw)
+
+
+class CudaLib(Lib):
+    """libtrajopt_cuda.so"""
+
+    def __init__(self, path=LIB_PATH, device=0):
+        super().__init__(path, "tc_")
+        self.check(self.dll.tc_init(C.c_int(device)))
+
+    def new_result(self, scene):
+        h = C.c_void_p()
+        self.check(self.dll.tc_result_create(scene.handle, C.byref(h)))
+        return h
+
+    def eval(self, scene, q, evaluator, stack=STACK_IFOPT, lvs=0.005, fixed=None, want=WANT_ALL,
+             precision=PRECISION_F64, result=None, stream=None):
+        """q: numpy [B, T, n_dof] (host) -> Result"""
+        q = np.ascontiguousarray(q, dtype=np.float64)
+        B, T, n = q.shape
+        assert n == scene.n_dof
+        d, keep = make_eval_desc(evaluator, stack, lvs, fixed, want, precision)
+        if result is None:
+            result = Result(self, scene, self.new_result(scene), B, T)
+        result.B, result.T = B, T
+        self.check(self.dll.tc_eval(scene.handle, C.byref(d), _p(q, _pd), C.c_int32(B), C.c_int32(T), result.handle,
+                                    C.c_void_p(stream or 0)))
+        return result
+
+    def eval_device(self, scene, q_dev_ptr, B, T, evaluator, result, stack=STACK_IFOPT, lvs=0.005, fixed=None,
+                    want=WANT_ALL, precision=PRECISION_F64, stream=None, sync=True):
+        """q already resident on the device (raw pointer); optionally asynchronous."""
+        d, keep = make_eval_desc(evaluator, stack, lvs, fixed, want, precision, q_on_device=True)
+        f = self.dll.tc_eval if sync else self.dll.tc_eval_async
+        result.B, result.T = B, T
+        self.check(f(scene.handle, C.byref(d), C.c_void_p(q_dev_ptr), C.c_int32(B), C.c_int32(T), result.handle,
+                     C.c_void_p(stream or 0)))
+        return result
+
+    def sync(self, result):
+        self.check(self.dll.tc_result_sync(result.handle))
+
+    def stage_ms(self, result):
+        ms = (C.c_float * 5)()
+        self.check(self.dll.tc_result_stage_ms(result.handle, ms))
+        return list(ms)
+
+    def measure_fma_peak(self, precision=PRECISION_F64):
+        v = C.c_double()
+        self.check(self.dll.tc_measure_fma_peak(C.c_int(precision), C.byref(v)))
+        return v.value
