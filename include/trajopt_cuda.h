@@ -182,6 +182,7 @@ typedef struct tc_counts {
   int64_t n_unconverged;
   int64_t n_terms;       /* B x terms per trajectory                          */
   int64_t overflow;      /* non-zero if an arena overflowed                   */
+  int64_t epa_iters;     /* sum of EPA expansion iterations                   */
 } tc_counts;
 
 /* one row set of the fixed-size constraints (GradientResultsSet reduced to what the constraint reads) */
@@ -246,10 +247,16 @@ int tc_result_cost(const tc_result* res, double* cost_per_term, double* cost_per
 /* device pointer to cost_per_traj[B] (stays on the GPU for multi-start selection) */
 int tc_result_cost_device(const tc_result* res, const double** dev_ptr);
 
-/* ---- multi-GPU helper for multi-start: every rank contributes its best (cost, global index);
- * all ranks receive the global winner.  nccl_comm is an ncclComm_t. ---- */
-int tc_allgather_best(double local_best_cost, int64_t local_best_idx, void* nccl_comm, void* cuda_stream,
-                      double* best_cost, int64_t* best_idx, int32_t* best_rank);
+/* ---- multi-GPU helpers for multi-start (one process per GPU).  NCCL is resolved from the process at
+ * run time (libnccl.so.2).  A communicator can come from the caller (an ncclComm_t) or be created here:
+ * rank 0 calls tc_nccl_unique_id and ships the 128 bytes to the other ranks by any side channel. ---- */
+int tc_nccl_unique_id(char id[128]);
+int tc_nccl_comm_create(int n_ranks, int rank, const char id[128], void** nccl_comm);
+void tc_nccl_comm_destroy(void* nccl_comm);
+/* every rank contributes its best (cost, global index); all ranks receive the global winner
+ * (one ncclAllGather of 16 bytes per rank over NVLink) */
+int tc_allgather_best(double local_best_cost, int64_t local_best_idx, void* nccl_comm, int n_ranks,
+                      void* cuda_stream, double* best_cost, int64_t* best_idx, int32_t* best_rank);
 
 /* ---- measurement helpers (bench only) ---- */
 /* register-resident DFMA / FFMA loop: returns achieved TFLOP/s (2 flop per FMA) */

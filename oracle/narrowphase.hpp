@@ -39,6 +39,7 @@ struct Shape
   V3 axis{ 0, 0, 1 };   // unit axis of capsule/cylinder/cone in the link frame
   std::vector<V3> verts;  // hull vertices in the link frame
   V3 aabb_c, aabb_h;    // link-frame AABB (radius included)
+  double brad{ 0 };     // bounding radius of the core about `center`
   double coreRadius() const { return (type == SPHERE || type == CAPSULE) ? radius : 0.0; }
 };
 
@@ -384,13 +385,13 @@ inline EpaResult epa(const Placed& A, const Placed& B, const Simplex& start)
   for (int i = 0; i < start.n; ++i)
     P.push_back({ start.w[i], start.a[i], start.b[i] });
 
-  // scale for "is this point new / is this volume non-zero" decisions
-  double scale = 0;
-  {
-    const V3 axes[3] = { { 1, 0, 0 }, { 0, 1, 0 }, { 0, 0, 1 } };
-    for (const V3& ax : axes)
-      scale = std::max(scale, dot(sup(ax).w - sup(-ax).w, ax));
-  }
+  // length scale of the Minkowski difference for the "is this point new / is this volume non-zero"
+  // decisions: bounding diameters of both cores plus the sweep lengths
+  double scale = 2 * (A.shape->brad + B.shape->brad);
+  if (A.cast)
+    scale += norm(A.pose1.apply(A.shape->center) - A.pose0.apply(A.shape->center));
+  if (B.cast)
+    scale += norm(B.pose1.apply(B.shape->center) - B.pose0.apply(B.shape->center));
   const double eps_len = 1e-9 * std::max(scale, 1e-3);
 
   // --- grow the GJK simplex to a tetrahedron with non-zero volume ---
@@ -500,6 +501,13 @@ inline EpaResult epa(const Placed& A, const Placed& B, const Simplex& start)
       f.n = V3(0, 0, 0);
       f.d = DBL_MAX;  // degenerate sliver: never selected
     }
+    // dead slots are reused first-fit so the face array stays bounded by the number of live faces
+    for (Face& slot : faces)
+      if (!slot.alive)
+      {
+        slot = f;
+        return;
+      }
     faces.push_back(f);
   };
   addFace(0, 1, 2, true);
@@ -558,12 +566,29 @@ inline EpaResult epa(const Placed& A, const Placed& B, const Simplex& start)
   r.ok = true;
   r.depth = bf.d;
   r.normal = bf.n;
-  // witness points: barycentric coordinates of the origin's projection onto the face
-  const V3 p = bf.d * bf.n;
-  double la, lb, lc;
-  const Vtx &a = P[static_cast<std::size_t>(bf.v[0])], &b = P[static_cast<std::size_t>(bf.v[1])],
-            &c = P[static_cast<std::size_t>(bf.v[2])];
-  detail::closestTriangle(a.w - p, b.w - p, c.w - p, la, lb, lc);
+  // Witness points: the face with the smallest PLANE distance may be one of several coplanar triangles of
+  // a larger Minkowski face; the witness is taken on the triangle that is actually closest to the origin.
+  std::size_t wf = static_cast<std::size_t>(best);
+  double wbest = DBL_MAX, la = 0, lb = 0, lc = 0;
+  for (std::size_t f = 0; f < faces.size(); ++f)
+  {
+    const Face& fc = faces[f];
+    if (!fc.alive || fc.d == DBL_MAX || fc.d > bf.d + eps_len)
+      continue;
+    double a0, a1, a2;
+    const V3 q = detail::closestTriangle(P[static_cast<std::size_t>(fc.v[0])].w, P[static_cast<std::size_t>(fc.v[1])].w,
+                                         P[static_cast<std::size_t>(fc.v[2])].w, a0, a1, a2);
+    const double q2 = norm2(q);
+    if (q2 < wbest)
+    {
+      wbest = q2;
+      wf = f;
+      la = a0, lb = a1, lc = a2;
+    }
+  }
+  const Face& wfc = faces[wf];
+  const Vtx &a = P[static_cast<std::size_t>(wfc.v[0])], &b = P[static_cast<std::size_t>(wfc.v[1])],
+            &c = P[static_cast<std::size_t>(wfc.v[2])];
   r.pa = la * a.a + lb * b.a + lc * c.a;
   r.pb = la * a.b + lb * b.b + lc * c.b;
   return r;
@@ -578,6 +603,7 @@ struct DistanceResult
   bool used_epa{ false };
   bool converged{ true };
   int gjk_iters{ 0 };
+  int epa_iters{ 0 };
   long scanned{ 0 };
 };
 
@@ -607,6 +633,7 @@ inline DistanceResult signedDistance(const Placed& A, const Placed& B, double th
   {
     EpaResult e = epa(A, B, g.simplex);
     out.used_epa = true;
+    out.epa_iters = e.iters;
     out.scanned += e.scanned;
     out.converged = out.converged && e.converged;
     d_core = -e.depth;

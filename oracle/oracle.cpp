@@ -164,6 +164,22 @@ static Scene* buildScene(const tc_scene_desc& d)
       default:
         throw std::runtime_error("unsupported shape type");
     }
+    switch (sh.type)
+    {
+      case TC_SHAPE_SPHERE:
+        sh.brad = 0;
+        break;
+      case TC_SHAPE_CAPSULE:
+        sh.brad = sh.half_len;
+        break;
+      case TC_SHAPE_CYLINDER:
+      case TC_SHAPE_CONE:
+        sh.brad = std::sqrt(sh.half_len * sh.half_len + sh.radius * sh.radius);
+        break;
+      default:
+        for (const V3& v : sh.verts)
+          sh.brad = std::max(sh.brad, norm(v - sh.center));
+    }
     sh.aabb_c = 0.5 * (lo + hi);
     sh.aabb_h = 0.5 * (hi - lo);
     s->link_shapes[static_cast<std::size_t>(sh.link)].push_back(i);
@@ -263,7 +279,7 @@ using ContactResultMap = std::map<int, std::vector<Contact>>;  // key = link-pai
 
 struct Stats
 {
-  long candidates{ 0 }, narrow{ 0 }, gjk_iters{ 0 }, scanned{ 0 }, epa{ 0 }, unconverged{ 0 };
+  long candidates{ 0 }, narrow{ 0 }, gjk_iters{ 0 }, scanned{ 0 }, epa{ 0 }, unconverged{ 0 }, epa_iters{ 0 };
 };
 
 // tesseract_collision bullet_utils GetAverageSupport [upstream, recalled]: for polyhedral shapes the
@@ -406,6 +422,7 @@ static void contactTest(const Scene& s, const std::vector<Pose>& poses0, const s
       st.gjk_iters += d.gjk_iters;
       st.scanned += d.scanned;
       st.epa += d.used_epa ? 1 : 0;
+      st.epa_iters += d.epa_iters;
       st.unconverged += d.converged ? 0 : 1;
       if (!d.contact)
         continue;
@@ -891,6 +908,9 @@ static Result* evaluate(const Scene& s, const tc_eval_desc& d, const double* q, 
   (void)shape_pairs;
   for (long k = 0; k < n_terms; ++k)
   {
+    // contacts carry the term-local sub-state index; make it global (states are numbered term by term)
+    for (Contact& c : per_term[static_cast<std::size_t>(k)])
+      c.c.state += static_cast<int>(r->counts.n_states);
     r->term_ptr[static_cast<std::size_t>(k) + 1] =
         r->term_ptr[static_cast<std::size_t>(k)] + static_cast<int64_t>(per_term[static_cast<std::size_t>(k)].size());
     r->contacts.insert(r->contacts.end(), per_term[static_cast<std::size_t>(k)].begin(),
@@ -906,6 +926,7 @@ static Result* evaluate(const Scene& s, const tc_eval_desc& d, const double* q, 
     r->counts.gjk_iters += st.gjk_iters;
     r->counts.support_verts += st.scanned;
     r->counts.n_epa += st.epa;
+    r->counts.epa_iters += st.epa_iters;
     r->counts.n_unconverged += st.unconverged;
   }
   r->counts.n_dense = r->counts.n_units * static_cast<int64_t>(s.pairs.size());

@@ -1,0 +1,88 @@
+// TEST INFRASTRUCTURE ONLY — host-compiled view of the device numerics (tc_narrow.cuh, tc_contact.cuh).
+// The per-thread functions of the kernels are `__host__ __device__`; this harness compiles them with g++
+// so their logic can be checked against the oracle on a machine without a GPU (pytest -m "not gpu").
+// It is never linked into libtrajopt_cuda.so and the product never loads it.
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "../../trajopt-1_b200/csrc/tc_scene.hpp"
+
+using namespace tc;
+
+static std::string g_err;
+
+extern "C" {
+const char* hc_last_error(void) { return g_err.c_str(); }
+
+int hc_scene_create(const tc_scene_desc* d, void** out)
+{
+  try
+  {
+    auto* s = new HostScene();
+    buildHostScene(*d, *s);
+    *out = s;
+    return TC_OK;
+  }
+  catch (const SceneError& e)
+  {
+    g_err = e.what();
+    return e.code;
+  }
+}
+void hc_scene_destroy(void* s) { delete static_cast<HostScene*>(s); }
+}  // extern "C"
+
+template <class R>
+static int shapeDistance(const HostScene& s, int sa, const double* a0, const double* a1, int sb, const double* b0,
+                         const double* b1, double threshold, int max_verts, int max_faces, int* status,
+                         double* distance, double* normal, double* pa, double* pb, int* used_epa, int* gjk_iters,
+                         int* epa_iters, int* scanned)
+{
+  std::vector<Vtx<R>> verts(s.verts.size());
+  for (size_t i = 0; i < verts.size(); ++i)
+    verts[i] = Vtx<R>{ static_cast<R>(s.verts[i].x), static_cast<R>(s.verts[i].y), static_cast<R>(s.verts[i].z), 0 };
+  const ShapeD& A = s.shapes[static_cast<size_t>(sa)];
+  const ShapeD& B = s.shapes[static_cast<size_t>(sb)];
+  Placed<R> PA, PB;
+  PA.sh = makeCore<R>(A, verts.data() + A.vert_off);
+  PB.sh = makeCore<R>(B, verts.data() + B.vert_off);
+  PA.p0 = Pose<R>::from12(a0);
+  PA.cast = a1 != nullptr;
+  PA.p1 = a1 ? Pose<R>::from12(a1) : PA.p0;
+  PB.p0 = Pose<R>::from12(b0);
+  PB.cast = b1 != nullptr;
+  PB.p1 = b1 ? Pose<R>::from12(b1) : PB.p0;
+  std::vector<Vec3<R>> pw(static_cast<size_t>(max_verts)), pav(static_cast<size_t>(max_verts)),
+      fn(static_cast<size_t>(max_faces));
+  std::vector<R> fd(static_cast<size_t>(max_faces));
+  std::vector<int> fv(static_cast<size_t>(max_faces)), edges(static_cast<size_t>(max_faces));
+  EpaStore<R> st{ pw.data(), pav.data(), fn.data(), fd.data(), fv.data(), edges.data(), max_verts, max_faces };
+  const DistOut<R> o = signedDistance<R>(PA, static_cast<R>(A.brad), PB, static_cast<R>(B.brad),
+                                         static_cast<R>(threshold), st);
+  *status = o.status;
+  *distance = o.distance;
+  normal[0] = o.normal.x, normal[1] = o.normal.y, normal[2] = o.normal.z;
+  pa[0] = o.pa.x, pa[1] = o.pa.y, pa[2] = o.pa.z;
+  pb[0] = o.pb.x, pb[1] = o.pb.y, pb[2] = o.pb.z;
+  *used_epa = o.used_epa;
+  *gjk_iters = o.gjk_iters;
+  *epa_iters = o.epa_iters;
+  *scanned = o.scanned;
+  return TC_OK;
+}
+
+extern "C" {
+int hc_shape_distance(const void* scene, int precision, int sa, const double* a0, const double* a1, int sb,
+                      const double* b0, const double* b1, double threshold, int max_verts, int max_faces, int* status,
+                      double* distance, double* normal, double* pa, double* pb, int* used_epa, int* gjk_iters,
+                      int* epa_iters, int* scanned)
+{
+  const HostScene& s = *static_cast<const HostScene*>(scene);
+  if (precision == TC_PRECISION_F32)
+    return shapeDistance<float>(s, sa, a0, a1, sb, b0, b1, threshold, max_verts, max_faces, status, distance, normal,
+                                pa, pb, used_epa, gjk_iters, epa_iters, scanned);
+  return shapeDistance<double>(s, sa, a0, a1, sb, b0, b1, threshold, max_verts, max_faces, status, distance, normal,
+                               pa, pb, used_epa, gjk_iters, epa_iters, scanned);
+}
+}

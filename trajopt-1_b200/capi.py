@@ -72,7 +72,7 @@ GRADIENT_DTYPE = np.dtype([
 assert GRADIENT_DTYPE.itemsize == 64
 
 COUNT_FIELDS = ["n_states", "n_units", "n_dense", "n_candidates", "n_narrowphase", "n_contacts", "n_rows", "nnz",
-                "gjk_iters", "support_verts", "n_epa", "n_unconverged", "n_terms", "overflow"]
+                "gjk_iters", "support_verts", "n_epa", "n_unconverged", "n_terms", "overflow", "epa_iters"]
 
 SET_DTYPE = np.dtype([
     ("traj", "<i4"), ("term", "<i4"), ("pair", "<i4"), ("shape_key", "<i4", 2), ("n_results", "<i4"),
@@ -256,8 +256,9 @@ class Lib:
         le = getattr(self.dll, prefix + "last_error")
         le.restype = C.c_char_p
         for name in ("scene_destroy", "result_destroy"):
-            getattr(self.dll, prefix + name).restype = None
-            getattr(self.dll, prefix + name).argtypes = [C.c_void_p]
+            if hasattr(self.dll, prefix + name):
+                getattr(self.dll, prefix + name).restype = None
+                getattr(self.dll, prefix + name).argtypes = [C.c_void_p]
 
     def fn(self, name):
         return getattr(self.dll, self.prefix + name)

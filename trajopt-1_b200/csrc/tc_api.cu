@@ -1,0 +1,890 @@
+// tc_api.cu — the C ABI of libtrajopt_cuda.so (include/trajopt_cuda.h): scene upload, orchestration of
+// one batched pass on a CUDA stream, result marshalling.  No arithmetic of the path happens on the host;
+// without a usable sm_100 device every entry point fails with TC_ERR_CUDA.
+#include <dlfcn.h>
+
+#include <cstring>
+#include <mutex>
+#include <new>
+
+#include "tc_internal.hpp"
+
+using namespace tc;
+
+namespace
+{
+thread_local std::string g_err;
+
+int fail(int code, const std::string& msg)
+{
+  g_err = msg;
+  return code;
+}
+int cudaFail(cudaError_t e, const char* what)
+{
+  g_err = std::string(what) + ": " + cudaGetErrorString(e);
+  return TC_ERR_CUDA;
+}
+#define TC_CUDA(call)                                                                                                \
+  do                                                                                                                 \
+  {                                                                                                                  \
+    cudaError_t e__ = (call);                                                                                        \
+    if (e__ != cudaSuccess)                                                                                          \
+      return cudaFail(e__, #call);                                                                                   \
+  } while (0)
+
+std::mutex g_init_mutex;
+int g_device = -1;
+}  // namespace
+
+struct tc_scene
+{
+  HostScene host;
+  SceneView dview{};
+  std::vector<void*> allocs;
+  int device{ 0 };
+};
+
+struct tc_result
+{
+  tc_scene* scene{ nullptr };
+  cudaStream_t stream{ nullptr };
+  tc_eval_desc desc{};
+  EvalParams ep{};
+  std::vector<int32_t> term_t;
+  std::vector<uint8_t> term_fixed;
+  bool pending{ false }, valid{ false };
+  bool have_grad{ false }, have_cost{ false }, have_rows{ false };
+  Work w{};
+  Counters* h_counters{ nullptr };  // pinned
+  Counters* d_counters{ nullptr };
+  tc_counts counts{};
+  cudaEvent_t ev[5]{};
+  float stage_ms[5]{};
+  // arenas
+  DevBuf<double> q;
+  DevBuf<int32_t> term_t_d, term_cnt, term_states, term_units, state_base, unit_base, unit_term;
+  DevBuf<uint8_t> term_fixed_d, term_interp;
+  DevBuf<double> poses, aabb;
+  DevBuf<int32_t> sp_count, sp_offset, sp_cursor, items, deep_items, idx, idx_alt, ghas;
+  DevBuf<RawContact> raw;
+  DevBuf<unsigned long long> keys, keys_alt;
+  DevBuf<tc_contact> contacts_tmp, contacts;
+  DevBuf<double> xf_tmp, xf, grad;
+  DevBuf<long long> term_ptr, row_ptr, term_row_base;
+  DevBuf<tc_gradient> grec;
+  DevBuf<unsigned char> sort_temp, deep_scratch;
+  DevBuf<double> cost_term, cost_traj;
+  // rows
+  DevBuf<int32_t> col_idx;
+  DevBuf<double> row_val, row_value, row_coeff, row_margin;
+  // sets
+  DevBuf<tc_set> sets;
+  DevBuf<int32_t> set_count, set_run;
+  DevBuf<double> set_values, set_coeffs, set_jac;
+};
+
+namespace
+{
+template <class T>
+int upload(tc_scene* s, const std::vector<T>& h, const T** out)
+{
+  void* d = nullptr;
+  const size_t bytes = std::max<size_t>(h.size(), 1) * sizeof(T);
+  TC_CUDA(cudaMalloc(&d, bytes));
+  s->allocs.push_back(d);
+  if (!h.empty())
+    TC_CUDA(cudaMemcpy(d, h.data(), h.size() * sizeof(T), cudaMemcpyHostToDevice));
+  *out = static_cast<const T*>(d);
+  return TC_OK;
+}
+
+int ensureDevice(int device)
+{
+  TC_CUDA(cudaSetDevice(device));
+  return TC_OK;
+}
+
+int readCounters(tc_result* r)
+{
+  TC_CUDA(cudaMemcpyAsync(r->h_counters, r->d_counters, sizeof(Counters), cudaMemcpyDeviceToHost, r->stream));
+  TC_CUDA(cudaStreamSynchronize(r->stream));
+  if (r->h_counters->overflow == 2)
+    return fail(TC_ERR_OVERFLOW, "a segment needs more than 16384 LVS sub-states");
+  if (r->h_counters->overflow)
+    return fail(TC_ERR_OVERFLOW, "an index arena exceeded 2^31 entries; split the batch");
+  return TC_OK;
+}
+
+template <class T>
+int reserve(DevBuf<T>& b, size_t n, const char* what)
+{
+  cudaError_t e = b.reserve(n);
+  if (e != cudaSuccess)
+    return cudaFail(e, what);
+  return TC_OK;
+}
+#define TC_RESERVE(buf, n)                                                                                           \
+  do                                                                                                                 \
+  {                                                                                                                  \
+    int s__ = reserve(buf, static_cast<size_t>(n), #buf);                                                            \
+    if (s__ != TC_OK)                                                                                                \
+      return s__;                                                                                                    \
+  } while (0)
+#define TC_TRY(call)                                                                                                 \
+  do                                                                                                                 \
+  {                                                                                                                  \
+    int s__ = (call);                                                                                                \
+    if (s__ != TC_OK)                                                                                                \
+      return s__;                                                                                                    \
+  } while (0)
+
+int runEval(tc_scene* scene, const tc_eval_desc* desc, const double* q, int32_t B, int32_t T, tc_result* r,
+            cudaStream_t st)
+{
+  if (!scene || !desc || !q || !r)
+    return fail(TC_ERR_INVALID, "null argument");
+  if (r->scene != scene)
+    return fail(TC_ERR_INVALID, "result object belongs to another scene");
+  if (desc->evaluator < TC_EVAL_DISCRETE || desc->evaluator > TC_EVAL_LVS_CONTINUOUS)
+    return fail(TC_ERR_INVALID, "invalid evaluator type");
+  if (desc->stack != TC_STACK_IFOPT && desc->stack != TC_STACK_LEGACY)
+    return fail(TC_ERR_INVALID, "invalid stack");
+  if (desc->precision != TC_PRECISION_F64 && desc->precision != TC_PRECISION_F32)
+    return fail(TC_ERR_INVALID, "invalid precision");
+  if (B <= 0 || T <= 0)
+    return fail(TC_ERR_INVALID, "empty batch");
+  if (desc->evaluator != TC_EVAL_DISCRETE && T < 2)
+    return fail(TC_ERR_INVALID, "segment evaluators need at least two timesteps");
+  if (desc->evaluator != TC_EVAL_DISCRETE && !(desc->lvs_length > 0))
+    return fail(TC_ERR_INVALID, "longest_valid_segment_length must be positive");
+  TC_TRY(ensureDevice(scene->device));
+  const HostScene& hs = scene->host;
+  const SceneView& v = scene->dview;
+  r->valid = false;
+  r->pending = false;
+  r->have_grad = r->have_cost = r->have_rows = false;
+  r->stream = st;
+  r->desc = *desc;
+  r->desc.fixed_steps = nullptr;
+  // term list per trajectory: CollisionTermInfo::hatch (trajopt/src/problem_description.cpp:1735-1858)
+  r->term_t.clear();
+  r->term_fixed.clear();
+  std::vector<uint8_t> fixed(static_cast<size_t>(T), 0);
+  if (desc->fixed_steps)
+    fixed.assign(desc->fixed_steps, desc->fixed_steps + T);
+  if (desc->evaluator == TC_EVAL_DISCRETE)
+  {
+    for (int t = 0; t < T; ++t)
+      if (!fixed[static_cast<size_t>(t)])
+      {
+        r->term_t.push_back(t);
+        r->term_fixed.push_back(0);
+        r->term_fixed.push_back(0);
+      }
+  }
+  else
+  {
+    for (int t = 0; t + 1 < T; ++t)
+    {
+      const bool cur = fixed[static_cast<size_t>(t)] != 0, nxt = fixed[static_cast<size_t>(t + 1)] != 0;
+      if (cur && nxt)
+        continue;
+      r->term_t.push_back(t);
+      r->term_fixed.push_back(cur ? 1 : 0);
+      r->term_fixed.push_back((!cur && nxt) ? 1 : 0);
+    }
+  }
+  EvalParams& ep = r->ep;
+  ep.evaluator = desc->evaluator;
+  ep.stack = desc->stack;
+  ep.B = B;
+  ep.T = T;
+  ep.terms_per_traj = static_cast<int>(r->term_t.size());
+  const long long n_terms = static_cast<long long>(B) * ep.terms_per_traj;
+  if (n_terms >= (1ll << 28))
+    return fail(TC_ERR_OVERFLOW, "more than 2^28 collision terms in one batch");
+  ep.n_terms = static_cast<int>(n_terms);
+  ep.lvs = desc->lvs_length;
+  std::memset(&r->counts, 0, sizeof(r->counts));
+  r->counts.n_terms = n_terms;
+  Work& w = r->w;
+  std::memset(&w, 0, sizeof(w));
+  w.ep = ep;
+  w.cast = (desc->evaluator == TC_EVAL_CONTINUOUS || desc->evaluator == TC_EVAL_LVS_CONTINUOUS) ? 1 : 0;
+  w.single_sweep = (desc->evaluator == TC_EVAL_CONTINUOUS && desc->stack == TC_STACK_IFOPT) ? 1 : 0;
+  w.counters = r->d_counters;
+  for (int i = 0; i < 5; ++i)
+    r->stage_ms[i] = 0;
+  TC_CUDA(cudaEventRecord(r->ev[0], st));
+  TC_CUDA(cudaMemsetAsync(r->d_counters, 0, sizeof(Counters), st));
+  if (n_terms == 0)
+  {
+    TC_RESERVE(r->term_ptr, 1);
+    TC_CUDA(cudaMemsetAsync(r->term_ptr.p, 0, sizeof(long long), st));
+    w.term_ptr = r->term_ptr.p;
+    for (int i = 1; i < 5; ++i)
+      TC_CUDA(cudaEventRecord(r->ev[i], st));
+    r->pending = true;
+    return TC_OK;
+  }
+  // ---- inputs ----
+  const size_t nq = static_cast<size_t>(B) * T * hs.n_dof;
+  if (desc->q_on_device)
+    w.q = q;
+  else
+  {
+    TC_RESERVE(r->q, nq);
+    TC_CUDA(cudaMemcpyAsync(r->q.p, q, nq * sizeof(double), cudaMemcpyHostToDevice, st));
+    w.q = r->q.p;
+  }
+  TC_RESERVE(r->term_t_d, ep.terms_per_traj);
+  TC_RESERVE(r->term_fixed_d, 2 * ep.terms_per_traj);
+  TC_CUDA(cudaMemcpyAsync(r->term_t_d.p, r->term_t.data(), sizeof(int32_t) * ep.terms_per_traj, cudaMemcpyHostToDevice,
+                          st));
+  TC_CUDA(cudaMemcpyAsync(r->term_fixed_d.p, r->term_fixed.data(), 2 * ep.terms_per_traj, cudaMemcpyHostToDevice, st));
+  w.term_t = r->term_t_d.p;
+  w.term_fixed = r->term_fixed_d.p;
+  // ---- K0 plan ----
+  TC_RESERVE(r->term_cnt, n_terms);
+  TC_RESERVE(r->term_states, n_terms);
+  TC_RESERVE(r->term_units, n_terms);
+  TC_RESERVE(r->term_interp, n_terms);
+  TC_RESERVE(r->state_base, n_terms + 1);
+  TC_RESERVE(r->unit_base, n_terms + 1);
+  w.term_cnt = r->term_cnt.p, w.term_states = r->term_states.p, w.term_units = r->term_units.p;
+  w.term_interp = r->term_interp.p, w.state_base = r->state_base.p, w.unit_base = r->unit_base.p;
+  TC_CUDA(launchPlan(v, w, st));
+  TC_TRY(readCounters(r));
+  w.n_states = r->h_counters->n_states;
+  w.n_units = r->h_counters->n_units;
+  // ---- K1 FK, K2 broadphase count ----
+  TC_RESERVE(r->poses, static_cast<size_t>(w.n_states) * hs.n_active * 12);
+  TC_RESERVE(r->aabb, static_cast<size_t>(w.n_states) * hs.n_active_shapes * 6);
+  TC_RESERVE(r->unit_term, w.n_units);
+  TC_RESERVE(r->sp_count, hs.spairs.size());
+  TC_RESERVE(r->sp_cursor, hs.spairs.size());
+  TC_RESERVE(r->sp_offset, hs.spairs.size() + 1);
+  w.poses = r->poses.p, w.aabb = r->aabb.p, w.unit_term = r->unit_term.p;
+  w.sp_count = r->sp_count.p, w.sp_cursor = r->sp_cursor.p, w.sp_offset = r->sp_offset.p;
+  TC_CUDA(launchFk(v, w, st));
+  TC_CUDA(cudaEventRecord(r->ev[1], st));
+  TC_CUDA(launchBroadCount(v, w, st));
+  TC_TRY(readCounters(r));
+  w.n_items_padded = r->h_counters->n_items_padded;
+  const long long n_items = r->h_counters->n_items;
+  // ---- K2 fill, K3 narrow phase ----
+  TC_RESERVE(r->items, w.n_items_padded);
+  TC_RESERVE(r->raw, n_items);
+  TC_RESERVE(r->deep_items, 2 * n_items);
+  w.items = r->items.p, w.raw = r->raw.p, w.deep_items = r->deep_items.p;
+  if (w.n_items_padded > 0)
+  {
+    TC_CUDA(launchBroadFill(v, w, st));
+    TC_CUDA(launchNarrow(v, w, desc->precision, st));
+  }
+  TC_CUDA(cudaEventRecord(r->ev[2], st));
+  TC_TRY(readCounters(r));
+  const long long n_deep = r->h_counters->n_deep;
+  if (n_deep > 0)
+  {
+    const int n_threads = 64 * static_cast<int>(std::min<long long>((n_deep + 63) / 64, 296));
+    const size_t per = deepScratchBytesPerThread(desc->precision);
+    TC_RESERVE(r->deep_scratch, per * n_threads);
+    TC_CUDA(launchNarrowDeep(v, w, desc->precision, n_deep, r->deep_scratch.p, per, n_threads, st));
+    TC_TRY(readCounters(r));
+  }
+  TC_CUDA(cudaEventRecord(r->ev[3], st));
+  w.n_raw = r->h_counters->n_raw;
+  // ---- contact finalisation + sort ----
+  TC_RESERVE(r->contacts_tmp, w.n_raw);
+  TC_RESERVE(r->xf_tmp, static_cast<size_t>(w.n_raw) * 48);
+  TC_RESERVE(r->keys, w.n_raw);
+  TC_RESERVE(r->keys_alt, w.n_raw);
+  TC_RESERVE(r->idx, w.n_raw);
+  TC_RESERVE(r->idx_alt, w.n_raw);
+  w.contacts_tmp = r->contacts_tmp.p, w.xf_tmp = r->xf_tmp.p;
+  w.keys = r->keys.p, w.keys_alt = r->keys_alt.p, w.idx = r->idx.p, w.idx_alt = r->idx_alt.p;
+  if (w.n_raw > 0)
+  {
+    TC_CUDA(launchFinalize(v, w, st));
+    size_t temp_bytes = 0;
+    TC_CUDA(sortContacts(w, nullptr, temp_bytes, st));
+    TC_RESERVE(r->sort_temp, temp_bytes);
+    TC_CUDA(sortContacts(w, r->sort_temp.p, temp_bytes, st));
+    TC_TRY(readCounters(r));
+  }
+  w.n_contacts = r->h_counters->n_valid;
+  TC_RESERVE(r->contacts, w.n_contacts);
+  TC_RESERVE(r->xf, static_cast<size_t>(w.n_contacts) * 48);
+  TC_RESERVE(r->term_ptr, n_terms + 1);
+  w.contacts = r->contacts.p, w.xf = r->xf.p, w.term_ptr = r->term_ptr.p;
+  TC_CUDA(launchGather(v, w, st));
+  // ---- K4 ----
+  if (desc->want & TC_WANT_GRADIENTS)
+  {
+    TC_RESERVE(r->grad, static_cast<size_t>(w.n_contacts) * 4 * hs.n_dof);
+    TC_RESERVE(r->grec, w.n_contacts);
+    TC_RESERVE(r->ghas, w.n_contacts);
+    w.grad = r->grad.p, w.grec = r->grec.p, w.ghas = r->ghas.p;
+    TC_CUDA(launchGradients(v, w, st));
+    r->have_grad = true;
+  }
+  if (desc->want & TC_WANT_COST)
+  {
+    TC_RESERVE(r->cost_term, n_terms);
+    TC_RESERVE(r->cost_traj, B);
+    TC_CUDA(launchCost(v, w, r->cost_term.p, r->cost_traj.p, st));
+    r->have_cost = true;
+  }
+  TC_CUDA(cudaEventRecord(r->ev[4], st));
+  r->pending = true;
+  return TC_OK;
+}
+
+int finishEval(tc_result* r)
+{
+  if (!r->pending)
+    return r->valid ? TC_OK : fail(TC_ERR_INVALID, "no evaluation to wait for");
+  TC_TRY(ensureDevice(r->scene->device));
+  if (r->ep.n_terms > 0)
+    TC_TRY(readCounters(r));
+  else
+  {
+    TC_CUDA(cudaStreamSynchronize(r->stream));
+    std::memset(r->h_counters, 0, sizeof(Counters));
+  }
+  r->pending = false;
+  const Counters& c = *r->h_counters;
+  const HostScene& hs = r->scene->host;
+  tc_counts& o = r->counts;
+  o.n_states = c.n_states;
+  o.n_units = c.n_units;
+  o.n_dense = c.n_units * static_cast<long long>(hs.pairs.size());
+  o.n_candidates = c.n_units * static_cast<long long>(hs.spairs.size());
+  o.n_narrowphase = c.n_items;
+  o.n_contacts = c.n_valid;
+  o.n_rows = c.n_valid;
+  o.nnz = 0;
+  o.gjk_iters = c.gjk_iters;
+  o.support_verts = c.support_verts;
+  o.n_epa = c.n_epa;
+  o.n_unconverged = c.n_unconverged;
+  o.overflow = c.overflow;
+  o.epa_iters = c.epa_iters;
+  for (int i = 0; i < 4; ++i)
+    cudaEventElapsedTime(&r->stage_ms[i], r->ev[i], r->ev[i + 1]);
+  cudaEventElapsedTime(&r->stage_ms[4], r->ev[0], r->ev[4]);
+  r->valid = true;
+  return TC_OK;
+}
+
+int needValid(const tc_result* r)
+{
+  if (!r)
+    return fail(TC_ERR_INVALID, "null result");
+  if (r->pending)
+    return fail(TC_ERR_INVALID, "tc_result_sync() has not been called");
+  if (!r->valid)
+    return fail(TC_ERR_INVALID, "result holds no evaluation");
+  return ensureDevice(r->scene->device);
+}
+
+int buildRows(tc_result* r)
+{
+  if (r->have_rows)
+    return TC_OK;
+  if (!r->have_grad)
+    return fail(TC_ERR_INVALID, "rows need an evaluation with TC_WANT_GRADIENTS");
+  const HostScene& hs = r->scene->host;
+  Work& w = r->w;
+  const size_t nc = static_cast<size_t>(w.n_contacts);
+  TC_RESERVE(r->row_ptr, nc + 1);
+  TC_RESERVE(r->term_row_base, r->ep.n_terms + 1);
+  TC_RESERVE(r->col_idx, 2 * nc * hs.n_dof);
+  TC_RESERVE(r->row_val, 2 * nc * hs.n_dof);
+  TC_RESERVE(r->row_value, nc);
+  TC_RESERVE(r->row_coeff, nc);
+  TC_RESERVE(r->row_margin, nc);
+  w.row_ptr = r->row_ptr.p;
+  TC_CUDA(launchRowBase(r->scene->dview, w, r->term_row_base.p, r->stream));
+  TC_CUDA(launchRows(r->scene->dview, w, r->term_row_base.p, r->col_idx.p, r->row_val.p, r->row_value.p,
+                     r->row_coeff.p, r->row_margin.p, r->stream));
+  TC_TRY(readCounters(r));
+  r->counts.nnz = r->h_counters->nnz;
+  r->have_rows = true;
+  return TC_OK;
+}
+}  // namespace
+
+// ---- multi-GPU helper: NCCL is resolved at run time from the process (torch ships libnccl.so.2) ----
+struct Id128
+{
+  char b[128];  // ncclUniqueId
+};
+namespace
+{
+struct NcclApi
+{
+  void* lib{ nullptr };
+  int (*allGather)(const void*, void*, size_t, int, void*, cudaStream_t){ nullptr };
+  int (*getUniqueId)(void*){ nullptr };
+  int (*commInitRank)(void**, int, Id128, int){ nullptr };
+  int (*commDestroy)(void*){ nullptr };
+  const char* (*getErrorString)(int){ nullptr };
+};
+NcclApi g_nccl;
+int loadNccl()
+{
+  if (g_nccl.lib)
+    return TC_OK;
+  const char* names[] = { "libnccl.so.2", "libnccl.so" };
+  for (const char* n : names)
+  {
+    g_nccl.lib = dlopen(n, RTLD_NOW | RTLD_GLOBAL);
+    if (g_nccl.lib)
+      break;
+  }
+  if (!g_nccl.lib)
+    return fail(TC_ERR_NCCL, "libnccl.so.2 not found in the process (import torch first or set LD_LIBRARY_PATH)");
+  g_nccl.allGather = reinterpret_cast<decltype(g_nccl.allGather)>(dlsym(g_nccl.lib, "ncclAllGather"));
+  g_nccl.getUniqueId = reinterpret_cast<decltype(g_nccl.getUniqueId)>(dlsym(g_nccl.lib, "ncclGetUniqueId"));
+  g_nccl.commInitRank = reinterpret_cast<decltype(g_nccl.commInitRank)>(dlsym(g_nccl.lib, "ncclCommInitRank"));
+  g_nccl.commDestroy = reinterpret_cast<decltype(g_nccl.commDestroy)>(dlsym(g_nccl.lib, "ncclCommDestroy"));
+  g_nccl.getErrorString = reinterpret_cast<decltype(g_nccl.getErrorString)>(dlsym(g_nccl.lib, "ncclGetErrorString"));
+  if (!g_nccl.allGather || !g_nccl.getUniqueId || !g_nccl.commInitRank || !g_nccl.commDestroy)
+    return fail(TC_ERR_NCCL, "libnccl lacks the expected entry points");
+  return TC_OK;
+}
+int ncclFail(int code, const char* what)
+{
+  g_err = std::string(what) + ": " + (g_nccl.getErrorString ? g_nccl.getErrorString(code) : "nccl error");
+  return TC_ERR_NCCL;
+}
+}  // namespace
+
+extern "C" {
+
+int tc_abi_version(void) { return TC_ABI_VERSION; }
+const char* tc_last_error(void) { return g_err.c_str(); }
+
+int tc_init(int device_ordinal)
+{
+  std::lock_guard<std::mutex> lock(g_init_mutex);
+  int n = 0;
+  cudaError_t e = cudaGetDeviceCount(&n);
+  if (e != cudaSuccess || n == 0)
+    return fail(TC_ERR_CUDA, std::string("no CUDA device: ") + (e != cudaSuccess ? cudaGetErrorString(e) : "count is 0"));
+  if (device_ordinal < 0 || device_ordinal >= n)
+    return fail(TC_ERR_INVALID, "device ordinal out of range");
+  cudaDeviceProp prop;
+  TC_CUDA(cudaGetDeviceProperties(&prop, device_ordinal));
+  if (prop.major != 10)
+    return fail(TC_ERR_CUDA, std::string("device is not sm_100 (B200): ") + prop.name);
+  TC_CUDA(cudaSetDevice(device_ordinal));
+  g_device = device_ordinal;
+  return TC_OK;
+}
+
+int tc_scene_create(const tc_scene_desc* desc, tc_scene** out)
+{
+  if (!desc || !out)
+    return fail(TC_ERR_INVALID, "null argument");
+  if (g_device < 0)
+    return fail(TC_ERR_CUDA, "tc_init() has not succeeded: no usable sm_100 device (there is no CPU fallback)");
+  tc_scene* s = new (std::nothrow) tc_scene();
+  if (!s)
+    return fail(TC_ERR_INVALID, "out of memory");
+  s->device = g_device;
+  try
+  {
+    buildHostScene(*desc, s->host);
+  }
+  catch (const SceneError& e)
+  {
+    delete s;
+    return fail(e.code, e.what());
+  }
+  const HostScene& h = s->host;
+  if (h.n_frames > MAX_FRAMES)
+  {
+    delete s;
+    return fail(TC_ERR_UNSUPPORTED, "kinematic tree with more than 64 frames");
+  }
+  int st = ensureDevice(s->device);
+  SceneView v = hostView(h);
+  std::vector<Vtx<float>> vf(h.verts.size());
+  for (size_t i = 0; i < vf.size(); ++i)
+    vf[i] = Vtx<float>{ static_cast<float>(h.verts[i].x), static_cast<float>(h.verts[i].y),
+                        static_cast<float>(h.verts[i].z), 0.f };
+#define UP(field, vec)                                                                                               \
+  if (st == TC_OK)                                                                                                   \
+  st = upload(s, vec, &v.field)
+  UP(frame_parent, h.frame_parent);
+  UP(frame_type, h.frame_type);
+  UP(frame_dof, h.frame_dof);
+  UP(frame_axis, h.frame_axis);
+  UP(frame_origin, h.frame_origin);
+  UP(path_ptr, h.path_ptr);
+  UP(path_frames, h.path_frames);
+  UP(link_frame, h.link_frame);
+  UP(link_pose, h.link_pose);
+  UP(shapes, h.shapes);
+  UP(verts, h.verts);
+  UP(verts_f32, vf);
+  UP(active_shapes, h.active_shapes);
+  UP(static_aabb, h.static_aabb);
+  UP(pairs, h.pairs);
+  UP(spairs, h.spairs);
+  UP(partner_ptr, h.partner_ptr);
+  UP(partner_sp, h.partner_sp);
+#undef UP
+  if (st != TC_OK)
+  {
+    tc_scene_destroy(s);
+    return st;
+  }
+  s->dview = v;
+  *out = s;
+  return TC_OK;
+}
+
+void tc_scene_destroy(tc_scene* s)
+{
+  if (!s)
+    return;
+  cudaSetDevice(s->device);
+  for (void* p : s->allocs)
+    cudaFree(p);
+  delete s;
+}
+
+int tc_scene_num_pairs(const tc_scene* s) { return s ? static_cast<int>(s->host.pairs.size()) : 0; }
+
+int tc_scene_pairs(const tc_scene* s, int32_t* l0, int32_t* l1, double* margin, double* coeff)
+{
+  if (!s)
+    return fail(TC_ERR_INVALID, "null scene");
+  for (size_t i = 0; i < s->host.pairs.size(); ++i)
+  {
+    if (l0)
+      l0[i] = s->host.pairs[i].a;
+    if (l1)
+      l1[i] = s->host.pairs[i].b;
+    if (margin)
+      margin[i] = s->host.pairs[i].margin;
+    if (coeff)
+      coeff[i] = s->host.pairs[i].coeff;
+  }
+  return TC_OK;
+}
+
+int tc_result_create(tc_scene* scene, tc_result** out)
+{
+  if (!scene || !out)
+    return fail(TC_ERR_INVALID, "null argument");
+  TC_TRY(ensureDevice(scene->device));
+  tc_result* r = new (std::nothrow) tc_result();
+  if (!r)
+    return fail(TC_ERR_INVALID, "out of memory");
+  r->scene = scene;
+  cudaError_t e = cudaMallocHost(reinterpret_cast<void**>(&r->h_counters), sizeof(Counters));
+  if (e == cudaSuccess)
+    e = cudaMalloc(reinterpret_cast<void**>(&r->d_counters), sizeof(Counters));
+  for (int i = 0; i < 5 && e == cudaSuccess; ++i)
+    e = cudaEventCreate(&r->ev[i]);
+  if (e != cudaSuccess)
+  {
+    tc_result_destroy(r);
+    return cudaFail(e, "tc_result_create");
+  }
+  *out = r;
+  return TC_OK;
+}
+
+void tc_result_destroy(tc_result* r)
+{
+  if (!r)
+    return;
+  cudaSetDevice(r->scene->device);
+  if (r->pending)
+    cudaStreamSynchronize(r->stream);
+  if (r->h_counters)
+    cudaFreeHost(r->h_counters);
+  if (r->d_counters)
+    cudaFree(r->d_counters);
+  for (int i = 0; i < 5; ++i)
+    if (r->ev[i])
+      cudaEventDestroy(r->ev[i]);
+  r->q.release(), r->term_t_d.release(), r->term_cnt.release(), r->term_states.release(), r->term_units.release();
+  r->state_base.release(), r->unit_base.release(), r->unit_term.release(), r->term_fixed_d.release();
+  r->term_interp.release(), r->poses.release(), r->aabb.release(), r->sp_count.release(), r->sp_offset.release();
+  r->sp_cursor.release(), r->items.release(), r->deep_items.release(), r->idx.release(), r->idx_alt.release();
+  r->ghas.release(), r->raw.release(), r->keys.release(), r->keys_alt.release(), r->contacts_tmp.release();
+  r->contacts.release(), r->xf_tmp.release(), r->xf.release(), r->grad.release(), r->term_ptr.release();
+  r->row_ptr.release(), r->term_row_base.release(), r->grec.release(), r->sort_temp.release();
+  r->deep_scratch.release(), r->cost_term.release(), r->cost_traj.release(), r->col_idx.release();
+  r->row_val.release(), r->row_value.release(), r->row_coeff.release(), r->row_margin.release();
+  r->sets.release(), r->set_count.release(), r->set_run.release(), r->set_values.release();
+  r->set_coeffs.release(), r->set_jac.release();
+  delete r;
+}
+
+int tc_eval_async(tc_scene* scene, const tc_eval_desc* desc, const double* q, int32_t B, int32_t T, tc_result* out,
+                  void* cuda_stream)
+{
+  return runEval(scene, desc, q, B, T, out, static_cast<cudaStream_t>(cuda_stream));
+}
+
+int tc_result_sync(tc_result* res)
+{
+  if (!res)
+    return fail(TC_ERR_INVALID, "null result");
+  return finishEval(res);
+}
+
+int tc_eval(tc_scene* scene, const tc_eval_desc* desc, const double* q, int32_t B, int32_t T, tc_result* out,
+            void* cuda_stream)
+{
+  TC_TRY(runEval(scene, desc, q, B, T, out, static_cast<cudaStream_t>(cuda_stream)));
+  return finishEval(out);
+}
+
+int tc_result_counts(const tc_result* res, tc_counts* counts)
+{
+  TC_TRY(needValid(res));
+  *counts = res->counts;
+  return TC_OK;
+}
+
+int tc_result_contacts(const tc_result* res, tc_contact* dst, size_t cap)
+{
+  TC_TRY(needValid(res));
+  const size_t n = std::min<size_t>(cap, static_cast<size_t>(res->w.n_contacts));
+  if (n)
+    TC_CUDA(cudaMemcpy(dst, res->w.contacts, n * sizeof(tc_contact), cudaMemcpyDeviceToHost));
+  return TC_OK;
+}
+
+int tc_result_contact_transforms(const tc_result* res, double* dst, size_t cap)
+{
+  TC_TRY(needValid(res));
+  const size_t n = std::min<size_t>(cap, static_cast<size_t>(res->w.n_contacts));
+  if (n)
+    TC_CUDA(cudaMemcpy(dst, res->w.xf, n * 48 * sizeof(double), cudaMemcpyDeviceToHost));
+  return TC_OK;
+}
+
+int tc_result_term_ptr(const tc_result* res, int64_t* term_ptr)
+{
+  TC_TRY(needValid(res));
+  static_assert(sizeof(long long) == sizeof(int64_t), "int64");
+  TC_CUDA(cudaMemcpy(term_ptr, res->w.term_ptr, (static_cast<size_t>(res->ep.n_terms) + 1) * sizeof(int64_t),
+                     cudaMemcpyDeviceToHost));
+  return TC_OK;
+}
+
+int tc_result_gradients(const tc_result* res, tc_gradient* rec, double* grad, size_t cap)
+{
+  TC_TRY(needValid(res));
+  if (!res->have_grad)
+    return fail(TC_ERR_INVALID, "evaluation ran without TC_WANT_GRADIENTS");
+  const size_t n = std::min<size_t>(cap, static_cast<size_t>(res->w.n_contacts));
+  if (n)
+  {
+    TC_CUDA(cudaMemcpy(rec, res->w.grec, n * sizeof(tc_gradient), cudaMemcpyDeviceToHost));
+    TC_CUDA(cudaMemcpy(grad, res->w.grad, n * 4 * res->scene->host.n_dof * sizeof(double), cudaMemcpyDeviceToHost));
+  }
+  return TC_OK;
+}
+
+int tc_result_rows(const tc_result* res_c, int64_t* row_ptr, int32_t* col_idx, double* val, double* row_value,
+                   double* row_coeff, double* row_margin)
+{
+  TC_TRY(needValid(res_c));
+  tc_result* r = const_cast<tc_result*>(res_c);
+  TC_TRY(buildRows(r));
+  const size_t nc = static_cast<size_t>(r->w.n_contacts);
+  const size_t nnz = static_cast<size_t>(r->counts.nnz);
+  TC_CUDA(cudaMemcpy(row_ptr, r->row_ptr.p, (nc + 1) * sizeof(int64_t), cudaMemcpyDeviceToHost));
+  if (nnz)
+  {
+    TC_CUDA(cudaMemcpy(col_idx, r->col_idx.p, nnz * sizeof(int32_t), cudaMemcpyDeviceToHost));
+    TC_CUDA(cudaMemcpy(val, r->row_val.p, nnz * sizeof(double), cudaMemcpyDeviceToHost));
+  }
+  if (nc)
+  {
+    TC_CUDA(cudaMemcpy(row_value, r->row_value.p, nc * sizeof(double), cudaMemcpyDeviceToHost));
+    TC_CUDA(cudaMemcpy(row_coeff, r->row_coeff.p, nc * sizeof(double), cudaMemcpyDeviceToHost));
+    TC_CUDA(cudaMemcpy(row_margin, r->row_margin.p, nc * sizeof(double), cudaMemcpyDeviceToHost));
+  }
+  return TC_OK;
+}
+
+int tc_result_sets(const tc_result* res_c, int32_t max_num_cnt, int64_t* set_ptr, tc_set* sets, size_t cap_sets,
+                   double* values, double* coeffs, double* jac)
+{
+  TC_TRY(needValid(res_c));
+  tc_result* r = const_cast<tc_result*>(res_c);
+  if (!r->have_grad)
+    return fail(TC_ERR_INVALID, "sets need an evaluation with TC_WANT_GRADIENTS");
+  if (max_num_cnt <= 0)
+    return fail(TC_ERR_INVALID, "max_num_cnt must be positive");
+  const HostScene& hs = r->scene->host;
+  const size_t nc = static_cast<size_t>(r->w.n_contacts), nt = static_cast<size_t>(r->ep.n_terms);
+  const size_t n = static_cast<size_t>(hs.n_dof), m = static_cast<size_t>(max_num_cnt);
+  set_ptr[0] = 0;
+  if (nt == 0)
+    return TC_OK;
+  TC_RESERVE(r->sets, nc);
+  TC_RESERVE(r->set_run, 2 * nc);
+  TC_RESERVE(r->set_count, nt);
+  TC_RESERVE(r->set_values, nt * m);
+  TC_RESERVE(r->set_coeffs, nt * m);
+  TC_RESERVE(r->set_jac, nt * m * 2 * n);
+  TC_CUDA(launchSets(r->scene->dview, r->w, max_num_cnt, r->sets.p, r->set_count.p, r->set_run.p, r->set_values.p,
+                     r->set_coeffs.p, r->set_jac.p, r->stream));
+  TC_CUDA(cudaStreamSynchronize(r->stream));
+  TC_CUDA(cudaMemcpy(values, r->set_values.p, nt * m * sizeof(double), cudaMemcpyDeviceToHost));
+  TC_CUDA(cudaMemcpy(coeffs, r->set_coeffs.p, nt * m * sizeof(double), cudaMemcpyDeviceToHost));
+  TC_CUDA(cudaMemcpy(jac, r->set_jac.p, nt * m * 2 * n * sizeof(double), cudaMemcpyDeviceToHost));
+  // marshalling only: the sets of term k sit at the term's contact offset; pack them back to back
+  std::vector<int32_t> cnt(nt);
+  std::vector<int64_t> tp(nt + 1);
+  TC_CUDA(cudaMemcpy(cnt.data(), r->set_count.p, nt * sizeof(int32_t), cudaMemcpyDeviceToHost));
+  TC_CUDA(cudaMemcpy(tp.data(), r->w.term_ptr, (nt + 1) * sizeof(int64_t), cudaMemcpyDeviceToHost));
+  std::vector<tc_set> all(nc);
+  if (nc)
+    TC_CUDA(cudaMemcpy(all.data(), r->sets.p, nc * sizeof(tc_set), cudaMemcpyDeviceToHost));
+  size_t ns = 0;
+  for (size_t k = 0; k < nt; ++k)
+  {
+    for (int32_t j = 0; j < cnt[k]; ++j)
+    {
+      if (sets && ns < cap_sets)
+        sets[ns] = all[static_cast<size_t>(tp[k]) + static_cast<size_t>(j)];
+      ++ns;
+    }
+    set_ptr[k + 1] = static_cast<int64_t>(ns);
+  }
+  return TC_OK;
+}
+
+int tc_result_cost(const tc_result* res_c, double* cost_per_term, double* cost_per_traj)
+{
+  TC_TRY(needValid(res_c));
+  tc_result* r = const_cast<tc_result*>(res_c);
+  if (r->ep.n_terms == 0)
+  {
+    if (cost_per_traj)
+      std::memset(cost_per_traj, 0, sizeof(double) * r->ep.B);
+    return TC_OK;
+  }
+  if (!r->have_cost)
+  {
+    TC_RESERVE(r->cost_term, r->ep.n_terms);
+    TC_RESERVE(r->cost_traj, r->ep.B);
+    TC_CUDA(launchCost(r->scene->dview, r->w, r->cost_term.p, r->cost_traj.p, r->stream));
+    TC_CUDA(cudaStreamSynchronize(r->stream));
+    r->have_cost = true;
+  }
+  if (cost_per_term)
+    TC_CUDA(cudaMemcpy(cost_per_term, r->cost_term.p, sizeof(double) * r->ep.n_terms, cudaMemcpyDeviceToHost));
+  if (cost_per_traj)
+    TC_CUDA(cudaMemcpy(cost_per_traj, r->cost_traj.p, sizeof(double) * r->ep.B, cudaMemcpyDeviceToHost));
+  return TC_OK;
+}
+
+int tc_result_cost_device(const tc_result* res, const double** dev_ptr)
+{
+  TC_TRY(needValid(res));
+  if (!res->have_cost)
+    return fail(TC_ERR_INVALID, "evaluation ran without TC_WANT_COST");
+  *dev_ptr = res->cost_traj.p;
+  return TC_OK;
+}
+
+int tc_result_stage_ms(const tc_result* res, float ms[5])
+{
+  TC_TRY(needValid(res));
+  for (int i = 0; i < 5; ++i)
+    ms[i] = res->stage_ms[i];
+  return TC_OK;
+}
+
+int tc_measure_fma_peak(int precision, double* tflops)
+{
+  if (g_device < 0)
+    return fail(TC_ERR_CUDA, "tc_init() has not succeeded");
+  TC_TRY(ensureDevice(g_device));
+  TC_CUDA(measureFmaPeak(precision, tflops));
+  return TC_OK;
+}
+
+int tc_nccl_unique_id(char id[128])
+{
+  TC_TRY(loadNccl());
+  const int e = g_nccl.getUniqueId(id);
+  return e ? ncclFail(e, "ncclGetUniqueId") : TC_OK;
+}
+
+int tc_nccl_comm_create(int n_ranks, int rank, const char id[128], void** comm)
+{
+  TC_TRY(loadNccl());
+  if (g_device < 0)
+    return fail(TC_ERR_CUDA, "tc_init() has not succeeded");
+  TC_TRY(ensureDevice(g_device));
+  Id128 uid;
+  std::memcpy(uid.b, id, 128);
+  const int e = g_nccl.commInitRank(comm, n_ranks, uid, rank);
+  return e ? ncclFail(e, "ncclCommInitRank") : TC_OK;
+}
+
+void tc_nccl_comm_destroy(void* comm)
+{
+  if (comm && g_nccl.commDestroy)
+    g_nccl.commDestroy(comm);
+}
+
+int tc_allgather_best(double local_best_cost, int64_t local_best_idx, void* nccl_comm, int n_ranks, void* cuda_stream,
+                      double* best_cost, int64_t* best_idx, int32_t* best_rank)
+{
+  if (!nccl_comm || n_ranks <= 0 || !best_cost || !best_idx || !best_rank)
+    return fail(TC_ERR_INVALID, "bad argument");
+  TC_TRY(loadNccl());
+  if (g_device < 0)
+    return fail(TC_ERR_CUDA, "tc_init() has not succeeded");
+  TC_TRY(ensureDevice(g_device));
+  cudaStream_t st = static_cast<cudaStream_t>(cuda_stream);
+  struct Rec
+  {
+    double cost;
+    int64_t idx;
+  };
+  Rec* d = nullptr;
+  TC_CUDA(cudaMalloc(reinterpret_cast<void**>(&d), sizeof(Rec) * (static_cast<size_t>(n_ranks) + 1)));
+  Rec mine{ local_best_cost, local_best_idx };
+  cudaError_t ce = cudaMemcpyAsync(d + n_ranks, &mine, sizeof(Rec), cudaMemcpyHostToDevice, st);
+  int ne = 0;
+  if (ce == cudaSuccess)
+    ne = g_nccl.allGather(d + n_ranks, d, sizeof(Rec), /* ncclChar */ 0, nccl_comm, st);
+  std::vector<Rec> all(static_cast<size_t>(n_ranks));
+  if (ce == cudaSuccess && ne == 0)
+    ce = cudaMemcpyAsync(all.data(), d, sizeof(Rec) * n_ranks, cudaMemcpyDeviceToHost, st);
+  if (ce == cudaSuccess && ne == 0)
+    ce = cudaStreamSynchronize(st);
+  cudaFree(d);
+  if (ne)
+    return ncclFail(ne, "ncclAllGather");
+  if (ce != cudaSuccess)
+    return cudaFail(ce, "tc_allgather_best");
+  int br = 0;
+  for (int i = 1; i < n_ranks; ++i)
+    if (all[static_cast<size_t>(i)].cost < all[static_cast<size_t>(br)].cost)
+      br = i;
+  *best_cost = all[static_cast<size_t>(br)].cost;
+  *best_idx = all[static_cast<size_t>(br)].idx;
+  *best_rank = br;
+  return TC_OK;
+}
+}  // extern "C"

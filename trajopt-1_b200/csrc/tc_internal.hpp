@@ -1,0 +1,119 @@
+// tc_internal.hpp — device-side working set of one batched evaluation and the kernel launchers.
+// Layout of the arenas in HBM (all sized from device-side counts, grown geometrically, never shrunk):
+//
+//   q            [B][T][n_dof] f64                       joint values of every trajectory
+//   term_*       [n_terms]                               cnt / #states / #units / LVS-merge flag per term
+//   state_base,unit_base [n_terms+1]                     exclusive scans (sub-states and tested units)
+//   poses        [n_states][n_active_links][12] f64      AoS: one 96-byte record per (state, link); the
+//                                                        narrow phase reads whole records at scattered states
+//   aabb         [n_active_shapes][6][n_states] f64      SoA: the broadphase streams them along the state axis
+//   unit_term    [n_units] i32
+//   sp_count/sp_offset/sp_cursor [n_shape_pairs(+1)]     survivors per shape pair, offsets padded to CHUNK
+//   items        [n_items_padded] i32                    unit index, bucketed per shape pair, -1 = padding
+//   raw          [<= n_items] RawContact (96 B)          narrow-phase hits in arrival order
+//   keys/idx     u64 / i32                               sort keys (term, link pair, substep, shape pair)
+//   contacts     [n_contacts] tc_contact (200 B), xf [n_contacts][4][12] f64, sorted
+//   grad         [n_contacts][2][2][n_dof] f64, grec, ghas
+#pragma once
+#include <cuda_runtime.h>
+
+#include <cstdint>
+#include <string>
+#include <vector>
+
+#include "tc_contact.cuh"
+
+namespace tc
+{
+constexpr int CHUNK = 128;       // items per narrow-phase CTA (all of one shape pair)
+constexpr int MAX_FRAMES = 64;
+constexpr int EPA_FAST_VERTS = 24, EPA_FAST_FACES = 48;
+constexpr int EPA_DEEP_VERTS = 4 + EPA_MAX_ITERS, EPA_DEEP_FACES = 8 + 2 * EPA_MAX_ITERS;
+
+struct Counters
+{
+  long long n_states, n_units, n_items, n_items_padded, n_raw, n_valid, n_deep;
+  long long gjk_iters, support_verts, n_epa, epa_iters, n_unconverged, overflow, nnz;
+};
+
+template <class T>
+struct DevBuf
+{
+  T* p{ nullptr };
+  size_t cap{ 0 };
+  // grows (never shrinks); contents are NOT preserved
+  cudaError_t reserve(size_t n)
+  {
+    if (n <= cap)
+      return cudaSuccess;
+    if (p)
+      cudaFree(p);
+    p = nullptr;
+    size_t want = n + n / 4 + 64;
+    cudaError_t e = cudaMalloc(reinterpret_cast<void**>(&p), want * sizeof(T));
+    cap = (e == cudaSuccess) ? want : 0;
+    return e;
+  }
+  void release()
+  {
+    if (p)
+      cudaFree(p);
+    p = nullptr;
+    cap = 0;
+  }
+};
+
+// device pointers of one evaluation handed to the kernels by value
+struct Work
+{
+  EvalParams ep;
+  int cast;  // evaluator sweeps (CONTINUOUS / LVS_CONTINUOUS)
+  int single_sweep;
+  const double* q;
+  const int32_t* term_t;       // [terms_per_traj]
+  const uint8_t* term_fixed;   // [terms_per_traj][2]
+  int32_t *term_cnt, *term_states, *term_units, *state_base, *unit_base;
+  uint8_t* term_interp;
+  double* poses;
+  double* aabb;
+  int32_t* unit_term;
+  int32_t *sp_count, *sp_offset, *sp_cursor;
+  int32_t* items;
+  RawContact* raw;
+  int32_t* deep_items;  // item slots whose EPA outgrew the thread-local polytope
+  unsigned long long *keys, *keys_alt;
+  int32_t *idx, *idx_alt;
+  tc_contact *contacts_tmp, *contacts;
+  double *xf_tmp, *xf;
+  long long* term_ptr;  // [n_terms+1]
+  double* grad;
+  tc_gradient* grec;
+  int32_t* ghas;
+  long long* row_ptr;
+  Counters* counters;
+  long long n_states, n_units, n_items_padded, n_raw, n_contacts;
+  long long raw_cap, deep_cap;
+};
+
+// ---- launchers (tc_pipeline.cu) ----
+cudaError_t launchPlan(const SceneView& v, const Work& w, cudaStream_t st);
+cudaError_t launchFk(const SceneView& v, const Work& w, cudaStream_t st);
+cudaError_t launchBroadCount(const SceneView& v, const Work& w, cudaStream_t st);
+cudaError_t launchBroadFill(const SceneView& v, const Work& w, cudaStream_t st);
+cudaError_t launchFinalize(const SceneView& v, const Work& w, cudaStream_t st);
+cudaError_t sortContacts(const Work& w, void* temp, size_t& temp_bytes, cudaStream_t st);  // result in *_alt
+cudaError_t launchGather(const SceneView& v, const Work& w, cudaStream_t st);
+cudaError_t launchGradients(const SceneView& v, const Work& w, cudaStream_t st);
+cudaError_t launchRowBase(const SceneView& v, const Work& w, long long* term_row_base, cudaStream_t st);
+cudaError_t launchRows(const SceneView& v, const Work& w, long long* term_row_base, int32_t* col_idx, double* val,
+                       double* row_value, double* row_coeff, double* row_margin, cudaStream_t st);
+cudaError_t launchCost(const SceneView& v, const Work& w, double* cost_term, double* cost_traj, cudaStream_t st);
+cudaError_t launchSets(const SceneView& v, const Work& w, int max_num_cnt, tc_set* sets, int32_t* set_count,
+                       int32_t* set_run, double* values, double* coeffs, double* jac, cudaStream_t st);
+// ---- launchers (tc_narrow.cu) ----
+cudaError_t launchNarrow(const SceneView& v, const Work& w, int precision, cudaStream_t st);
+cudaError_t launchNarrowDeep(const SceneView& v, const Work& w, int precision, long long n_deep, void* scratch,
+                             size_t scratch_bytes_per_thread, int n_threads, cudaStream_t st);
+size_t deepScratchBytesPerThread(int precision);
+cudaError_t measureFmaPeak(int precision, double* tflops);
+}  // namespace tc

@@ -1,0 +1,392 @@
+// tc_narrow.cu — K3: convex-convex GJK/EPA narrow phase over the bucketed pair list.
+//
+// The narrow-phase half of contact_manager_->contactTest(...)
+//   trajopt/src/collision_terms.cpp:667,889,1134,1157
+//   trajopt_ifopt/.../discrete_collision_evaluators.cpp:166; continuous_collision_evaluators.cpp:228,244,449
+// One CTA = CHUNK items of ONE shape pair.  Both hulls are staged global -> shared with TMA bulk copies
+// (cp.async.bulk + mbarrier); every lane then runs its own GJK (+EPA) against the staged vertices, so
+// vertex reads are warp-wide broadcasts.  Hits are appended to the raw contact arena with one atomic
+// per warp (ballot + popc).
+#include "tc_internal.hpp"
+
+namespace tc
+{
+namespace
+{
+__device__ __forceinline__ uint32_t smemAddr(const void* p) { return static_cast<uint32_t>(__cvta_generic_to_shared(p)); }
+
+__device__ __forceinline__ void mbarInit(uint64_t* bar, int count)
+{
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smemAddr(bar)), "r"(count));
+  asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void mbarExpectTx(uint64_t* bar, uint32_t bytes)
+{
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smemAddr(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void bulkCopyG2S(void* dst, const void* src, uint32_t bytes, uint64_t* bar)
+{
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                   smemAddr(dst)),
+               "l"(src), "r"(bytes), "r"(smemAddr(bar))
+               : "memory");
+}
+__device__ __forceinline__ void mbarWait(uint64_t* bar, uint32_t parity)
+{
+  uint32_t done = 0;
+  while (!done)
+  {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n"
+        "selp.u32 %0, 1, 0, p;\n"
+        "}\n"
+        : "=r"(done)
+        : "r"(smemAddr(bar)), "r"(parity)
+        : "memory");
+  }
+}
+
+template <class R>
+__device__ __forceinline__ const Vtx<R>* sceneVerts(const SceneView& v);
+template <>
+__device__ __forceinline__ const Vtx<double>* sceneVerts<double>(const SceneView& v)
+{
+  return v.verts;
+}
+template <>
+__device__ __forceinline__ const Vtx<float>* sceneVerts<float>(const SceneView& v)
+{
+  return v.verts_f32;
+}
+
+template <class R>
+__device__ __forceinline__ Pose<R> loadPose(const double* p)
+{
+  return Pose<R>::from12(p);
+}
+
+// builds the two placed shapes of item (unit u, shape pair sp)
+template <class R>
+__device__ __forceinline__ void placeItem(const SceneView& v, const Work& w, int u, const ShapePairD& spd,
+                                          const PairD& pr, const ShapeD& A, const ShapeD& B, const Vtx<R>* va,
+                                          const Vtx<R>* vb, Placed<R>& PA, Placed<R>& PB)
+{
+  const int k = w.unit_term[u];
+  const long long s0 = w.state_base[k] + (u - w.unit_base[k]);
+  const double* pa = w.poses + (static_cast<size_t>(s0) * v.n_active + pr.a) * 12;
+  PA.sh = makeCore<R>(A, va);
+  PA.p0 = loadPose<R>(pa);
+  PA.cast = w.cast != 0;
+  PA.p1 = w.cast ? loadPose<R>(pa + static_cast<size_t>(v.n_active) * 12) : PA.p0;
+  PB.sh = makeCore<R>(B, vb);
+  if (pr.b < v.n_active)
+  {
+    const double* pb = w.poses + (static_cast<size_t>(s0) * v.n_active + pr.b) * 12;
+    PB.p0 = loadPose<R>(pb);
+    PB.cast = w.cast != 0;
+    PB.p1 = w.cast ? loadPose<R>(pb + static_cast<size_t>(v.n_active) * 12) : PB.p0;
+  }
+  else
+  {
+    PB.p0 = loadPose<R>(v.link_pose + 12 * pr.b);
+    PB.cast = false;
+    PB.p1 = PB.p0;
+  }
+  (void)spd;
+}
+
+template <class R>
+__device__ __forceinline__ void storeHit(const Work& w, const DistOut<R>& d, int u, int sp, bool hit)
+{
+  const unsigned m = __ballot_sync(0xffffffffu, hit);
+  if (m == 0)
+    return;
+  const unsigned lane = threadIdx.x & 31;
+  const int leader = __ffs(m) - 1;
+  unsigned long long base = 0;
+  if (lane == leader)
+    base = atomicAdd(reinterpret_cast<unsigned long long*>(&w.counters->n_raw),
+                     static_cast<unsigned long long>(__popc(m)));
+  base = __shfl_sync(0xffffffffu, base, leader);
+  if (hit)
+  {
+    RawContact rc;
+    rc.unit = u;
+    rc.sp = sp;
+    rc.flags = (d.used_epa ? TC_FLAG_EPA : 0) | (d.converged ? 0 : TC_FLAG_UNCONVERGED);
+    rc.pad = 0;
+    rc.distance = static_cast<double>(d.distance);
+    rc.normal[0] = d.normal.x, rc.normal[1] = d.normal.y, rc.normal[2] = d.normal.z;
+    rc.pa[0] = d.pa.x, rc.pa[1] = d.pa.y, rc.pa[2] = d.pa.z;
+    rc.pb[0] = d.pb.x, rc.pb[1] = d.pb.y, rc.pb[2] = d.pb.z;
+    w.raw[base + __popc(m & ((1u << lane) - 1u))] = rc;
+  }
+}
+
+__device__ __forceinline__ long long warpSum(long long x)
+{
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1)
+    x += __shfl_xor_sync(0xffffffffu, x, o);
+  return x;
+}
+
+__device__ __forceinline__ void addStats(const Work& w, long long gjk, long long scanned, long long nepa,
+                                         long long epa_it, long long unconv)
+{
+  gjk = warpSum(gjk);
+  scanned = warpSum(scanned);
+  nepa = warpSum(nepa);
+  epa_it = warpSum(epa_it);
+  unconv = warpSum(unconv);
+  if ((threadIdx.x & 31) == 0)
+  {
+    typedef unsigned long long ull;
+    if (gjk)
+      atomicAdd(reinterpret_cast<ull*>(&w.counters->gjk_iters), static_cast<ull>(gjk));
+    if (scanned)
+      atomicAdd(reinterpret_cast<ull*>(&w.counters->support_verts), static_cast<ull>(scanned));
+    if (nepa)
+      atomicAdd(reinterpret_cast<ull*>(&w.counters->n_epa), static_cast<ull>(nepa));
+    if (epa_it)
+      atomicAdd(reinterpret_cast<ull*>(&w.counters->epa_iters), static_cast<ull>(epa_it));
+    if (unconv)
+      atomicAdd(reinterpret_cast<ull*>(&w.counters->n_unconverged), static_cast<ull>(unconv));
+  }
+}
+
+template <class R>
+__global__ void __launch_bounds__(CHUNK) k_narrow(SceneView v, Work w)
+{
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  __shared__ __align__(8) uint64_t bar;
+  __shared__ int s_sp;
+  Vtx<R>* sv = reinterpret_cast<Vtx<R>*>(smem_raw);
+  const int item0 = blockIdx.x * CHUNK;
+  if (threadIdx.x == 0)
+  {
+    // bucket of this chunk: last shape pair whose (padded) offset is <= item0
+    int lo = 0, hi = v.n_spairs;
+    while (hi - lo > 1)
+    {
+      const int mid = (lo + hi) >> 1;
+      if (w.sp_offset[mid] <= item0)
+        lo = mid;
+      else
+        hi = mid;
+    }
+    s_sp = lo;
+    mbarInit(&bar, 1);
+  }
+  __syncthreads();
+  const int sp = s_sp;
+  const ShapePairD spd = v.spairs[sp];
+  const PairD pr = v.pairs[spd.pair];
+  const ShapeD& A = v.shapes[spd.sa];
+  const ShapeD& B = v.shapes[spd.sb];
+  const int na = A.vert_cnt, nb = B.vert_cnt;
+  if (na + nb > 0)
+  {
+    if (threadIdx.x == 0)
+    {
+      const uint32_t ba = static_cast<uint32_t>(na * sizeof(Vtx<R>)), bb = static_cast<uint32_t>(nb * sizeof(Vtx<R>));
+      mbarExpectTx(&bar, ba + bb);
+      if (na)
+        bulkCopyG2S(sv, sceneVerts<R>(v) + A.vert_off, ba, &bar);
+      if (nb)
+        bulkCopyG2S(sv + na, sceneVerts<R>(v) + B.vert_off, bb, &bar);
+    }
+    mbarWait(&bar, 0);
+  }
+  const int u = w.items[item0 + threadIdx.x];
+  DistOut<R> d;
+  d.status = ND_NONE;
+  d.gjk_iters = 0, d.epa_iters = 0, d.scanned = 0;
+  d.used_epa = false;
+  d.converged = true;
+  if (u >= 0)
+  {
+    Placed<R> PA, PB;
+    placeItem<R>(v, w, u, spd, pr, A, B, sv, sv + na, PA, PB);
+    Vec3<R> e_pw[EPA_FAST_VERTS], e_pa[EPA_FAST_VERTS], e_fn[EPA_FAST_FACES];
+    R e_fd[EPA_FAST_FACES];
+    int e_fv[EPA_FAST_FACES], e_edges[EPA_FAST_FACES];
+    EpaStore<R> store{ e_pw, e_pa, e_fn, e_fd, e_fv, e_edges, EPA_FAST_VERTS, EPA_FAST_FACES };
+    d = signedDistance<R>(PA, static_cast<R>(A.brad), PB, static_cast<R>(B.brad), static_cast<R>(pr.thr), store);
+  }
+  storeHit<R>(w, d, u, sp, d.status == ND_CONTACT);
+  {
+    // rare: polytope outgrew the thread-local store -> deep-expansion queue
+    const bool deep = d.status == ND_EPA_OVERFLOW;
+    const unsigned m = __ballot_sync(0xffffffffu, deep);
+    if (m)
+    {
+      const unsigned lane = threadIdx.x & 31;
+      const int leader = __ffs(m) - 1;
+      unsigned long long base = 0;
+      if (lane == leader)
+        base = atomicAdd(reinterpret_cast<unsigned long long*>(&w.counters->n_deep),
+                         static_cast<unsigned long long>(__popc(m)));
+      base = __shfl_sync(0xffffffffu, base, leader);
+      if (deep)
+      {
+        const unsigned long long slot = base + __popc(m & ((1u << lane) - 1u));
+        w.deep_items[2 * slot] = u;
+        w.deep_items[2 * slot + 1] = sp;
+      }
+    }
+  }
+  const bool counted = d.status != ND_EPA_OVERFLOW;  // deep items are counted when they are re-run
+  addStats(w, counted ? d.gjk_iters : 0, counted ? d.scanned : 0, (counted && d.used_epa) ? 1 : 0,
+           counted ? d.epa_iters : 0, (counted && u >= 0 && !d.converged) ? 1 : 0);
+}
+
+// deep-expansion path: same arithmetic, polytope in global scratch, vertices read from global memory
+template <class R>
+__global__ void __launch_bounds__(64) k_narrow_deep(SceneView v, Work w, long long n_deep, unsigned char* scratch,
+                                                    size_t bytes_per_thread)
+{
+  const int tid = blockIdx.x * blockDim.x + threadIdx.x;
+  const int nthreads = gridDim.x * blockDim.x;
+  unsigned char* mine = scratch + static_cast<size_t>(tid) * bytes_per_thread;
+  Vec3<R>* pw = reinterpret_cast<Vec3<R>*>(mine);
+  Vec3<R>* pa = pw + EPA_DEEP_VERTS;
+  Vec3<R>* fn = pa + EPA_DEEP_VERTS;
+  R* fd = reinterpret_cast<R*>(fn + EPA_DEEP_FACES);
+  int* fv = reinterpret_cast<int*>(fd + EPA_DEEP_FACES);
+  int* edges = fv + EPA_DEEP_FACES;
+  const long long rounds = (n_deep + nthreads - 1) / nthreads;
+  for (long long r = 0; r < rounds; ++r)
+  {
+    const long long it = r * nthreads + tid;
+    DistOut<R> d;
+    d.status = ND_NONE;
+    d.gjk_iters = 0, d.epa_iters = 0, d.scanned = 0;
+    d.used_epa = false;
+    d.converged = true;
+    int u = -1, sp = 0;
+    if (it < n_deep)
+    {
+      u = w.deep_items[2 * it];
+      sp = w.deep_items[2 * it + 1];
+      const ShapePairD spd = v.spairs[sp];
+      const PairD pr = v.pairs[spd.pair];
+      const ShapeD& A = v.shapes[spd.sa];
+      const ShapeD& B = v.shapes[spd.sb];
+      Placed<R> PA, PB;
+      placeItem<R>(v, w, u, spd, pr, A, B, sceneVerts<R>(v) + A.vert_off, sceneVerts<R>(v) + B.vert_off, PA, PB);
+      EpaStore<R> store{ pw, pa, fn, fd, fv, edges, EPA_DEEP_VERTS, EPA_DEEP_FACES };
+      d = signedDistance<R>(PA, static_cast<R>(A.brad), PB, static_cast<R>(B.brad), static_cast<R>(pr.thr), store);
+    }
+    storeHit<R>(w, d, u, sp, d.status == ND_CONTACT);
+    addStats(w, d.gjk_iters, d.scanned, d.used_epa ? 1 : 0, d.epa_iters, (u >= 0 && !d.converged) ? 1 : 0);
+  }
+}
+
+template <class R, int ILP>
+__global__ void k_fma_peak(R* out, int iters)
+{
+  R acc[ILP];
+#pragma unroll
+  for (int i = 0; i < ILP; ++i)
+    acc[i] = static_cast<R>(threadIdx.x + i) * R(1e-3);
+  const R a = R(1.0000001), b = R(1e-7);
+  for (int it = 0; it < iters; ++it)
+  {
+#pragma unroll
+    for (int i = 0; i < ILP; ++i)
+      acc[i] = acc[i] * a + b;
+  }
+  R s = 0;
+#pragma unroll
+  for (int i = 0; i < ILP; ++i)
+    s += acc[i];
+  if (s == R(-1))
+    out[0] = s;
+}
+}  // namespace
+
+size_t deepScratchBytesPerThread(int precision)
+{
+  const size_t r = precision == TC_PRECISION_F32 ? 4 : 8;
+  size_t b = (2 * EPA_DEEP_VERTS + EPA_DEEP_FACES) * 3 * r + EPA_DEEP_FACES * r + 2 * EPA_DEEP_FACES * sizeof(int);
+  return (b + 15) / 16 * 16;
+}
+
+cudaError_t launchNarrow(const SceneView& v, const Work& w, int precision, cudaStream_t st)
+{
+  if (w.n_items_padded <= 0)
+    return cudaSuccess;
+  const unsigned grid = static_cast<unsigned>(w.n_items_padded / CHUNK);
+  if (precision == TC_PRECISION_F32)
+  {
+    const size_t smem = static_cast<size_t>(2 * v.max_hull_verts) * sizeof(Vtx<float>) + 16;
+    cudaFuncSetAttribute(k_narrow<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem));
+    k_narrow<float><<<grid, CHUNK, smem, st>>>(v, w);
+  }
+  else
+  {
+    const size_t smem = static_cast<size_t>(2 * v.max_hull_verts) * sizeof(Vtx<double>) + 16;
+    cudaFuncSetAttribute(k_narrow<double>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem));
+    k_narrow<double><<<grid, CHUNK, smem, st>>>(v, w);
+  }
+  return cudaGetLastError();
+}
+
+cudaError_t launchNarrowDeep(const SceneView& v, const Work& w, int precision, long long n_deep, void* scratch,
+                             size_t bytes_per_thread, int n_threads, cudaStream_t st)
+{
+  if (n_deep <= 0)
+    return cudaSuccess;
+  const unsigned grid = static_cast<unsigned>(n_threads / 64);
+  if (precision == TC_PRECISION_F32)
+    k_narrow_deep<float><<<grid, 64, 0, st>>>(v, w, n_deep, static_cast<unsigned char*>(scratch), bytes_per_thread);
+  else
+    k_narrow_deep<double><<<grid, 64, 0, st>>>(v, w, n_deep, static_cast<unsigned char*>(scratch), bytes_per_thread);
+  return cudaGetLastError();
+}
+
+cudaError_t measureFmaPeak(int precision, double* tflops)
+{
+  void* out = nullptr;
+  cudaError_t e = cudaMalloc(&out, 64);
+  if (e != cudaSuccess)
+    return e;
+  cudaDeviceProp prop;
+  int dev = 0;
+  cudaGetDevice(&dev);
+  cudaGetDeviceProperties(&prop, dev);
+  const int blocks = prop.multiProcessorCount * 8, threads = 256, iters = 1 << 14;
+  constexpr int ILP = 8;
+  cudaEvent_t a, b;
+  cudaEventCreate(&a);
+  cudaEventCreate(&b);
+  float best = 1e30f;
+  for (int rep = 0; rep < 10; ++rep)
+  {
+    cudaEventRecord(a);
+    if (precision == TC_PRECISION_F32)
+      k_fma_peak<float, ILP><<<blocks, threads>>>(static_cast<float*>(out), iters);
+    else
+      k_fma_peak<double, ILP><<<blocks, threads>>>(static_cast<double*>(out), iters);
+    cudaEventRecord(b);
+    e = cudaEventSynchronize(b);
+    if (e != cudaSuccess)
+      break;
+    float ms = 0;
+    cudaEventElapsedTime(&ms, a, b);
+    if (rep > 0 && ms < best)
+      best = ms;
+  }
+  cudaEventDestroy(a);
+  cudaEventDestroy(b);
+  cudaFree(out);
+  if (e != cudaSuccess)
+    return e;
+  const double fl = 2.0 * static_cast<double>(blocks) * threads * static_cast<double>(iters) * ILP;
+  *tflops = fl / (best * 1e-3) / 1e12;
+  return cudaGetLastError();
+}
+}  // namespace tc

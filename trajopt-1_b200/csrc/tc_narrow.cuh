@@ -1,0 +1,887 @@
+// tc_narrow.cuh — per-thread convex-convex signed distance (GJK + EPA) with swept-hull support.
+//
+// Stands where the reference calls contact_manager_->contactTest(...)
+//   trajopt/src/collision_terms.cpp:667,889,1134,1157
+//   trajopt_ifopt/src/constraints/collision/discrete_collision_evaluators.cpp:166
+//   trajopt_ifopt/src/constraints/collision/continuous_collision_evaluators.cpp:228,244,449
+// i.e. tesseract_collision's Bullet convex-convex narrow phase (GJK distance, EPA penetration) and its
+// CastHullShape support rule for the continuous managers [upstream of the reference tree].
+//
+// GPU mapping: ONE THREAD PER (unit, shape pair) item; the 32 lanes of a warp always hold items of
+// the SAME shape pair (the broadphase buckets items per shape pair), so every hull-vertex read in the
+// support scan is a shared-memory broadcast and the scan trip count is warp-uniform.  A swept (cast)
+// shape scans its vertices once for both end poses.  The simplex lives in registers: all indexing is
+// static after unrolling, sub-simplex compaction is done with selects.
+#pragma once
+#include "tc_math.cuh"
+
+namespace tc
+{
+enum
+{
+  SH_SPHERE = 0,
+  SH_HULL = 1,
+  SH_CAPSULE = 2,
+  SH_CYLINDER = 3,
+  SH_CONE = 4
+};
+
+// hull vertex as stored on the device: 32 B (FP64) so one 16-byte and one 8-byte broadcast load fetch it
+template <class R>
+struct alignas(16) Vtx
+{
+  R x, y, z, w;
+};
+
+// Collision shape in its LINK frame (shape_pose of the description already applied).
+struct ShapeD
+{
+  int32_t type, link, shape_id, vert_off, vert_cnt, active_index;
+  double radius, half_len;  // sphere/capsule: inflation radius of the core; cylinder/cone: solid radius
+  double center[3], axis[3];
+  double aabb_c[3], aabb_h[3];
+  double brad;  // bounding radius of the core about `center`
+};
+
+template <class R>
+struct ShapeCore
+{
+  int type, nverts;
+  const Vtx<R>* verts;
+  R radius, half_len;
+  Vec3<R> center, axis;
+  TC_HD R coreRadius() const { return (type == SH_SPHERE || type == SH_CAPSULE) ? radius : R(0); }
+};
+
+template <class R>
+TC_HD ShapeCore<R> makeCore(const ShapeD& s, const Vtx<R>* verts)
+{
+  ShapeCore<R> c;
+  c.type = s.type;
+  c.nverts = s.vert_cnt;
+  c.verts = verts;
+  c.radius = static_cast<R>(s.radius);
+  c.half_len = static_cast<R>(s.half_len);
+  c.center = Vec3<R>(static_cast<R>(s.center[0]), static_cast<R>(s.center[1]), static_cast<R>(s.center[2]));
+  c.axis = Vec3<R>(static_cast<R>(s.axis[0]), static_cast<R>(s.axis[1]), static_cast<R>(s.axis[2]));
+  return c;
+}
+
+template <class R>
+TC_HD R lowestReal();
+template <>
+TC_HD double lowestReal<double>()
+{
+  return -1.7976931348623157e308;
+}
+template <>
+TC_HD float lowestReal<float>()
+{
+  return -3.402823466e38f;
+}
+
+template <class R>
+struct Tol;
+template <>
+struct Tol<double>
+{
+  TC_HD static double gjkTol() { return 1e-10; }    // absolute gap |v| - v.w/|v| at which GJK stops [m]
+  TC_HD static double gjkTouch() { return 1e-7; }   // core distance below which the pair goes to EPA [m]
+  TC_HD static double dupRel() { return 1e-28; }
+  TC_HD static double epaTol() { return 1e-10; }
+  TC_HD static double epsLenRel() { return 1e-9; }
+  TC_HD static double visRel() { return 1e-14; }
+  TC_HD static double tiny() { return 1e-300; }
+  TC_HD static double degRel() { return 1e-14; }
+  TC_HD static double centerTiny() { return 1e-24; }
+};
+template <>
+struct Tol<float>
+{
+  TC_HD static float gjkTol() { return 2e-6f; }
+  TC_HD static float gjkTouch() { return 2e-5f; }
+  TC_HD static float dupRel() { return 1e-12f; }
+  TC_HD static float epaTol() { return 2e-6f; }
+  TC_HD static float epsLenRel() { return 1e-5f; }
+  TC_HD static float visRel() { return 1e-6f; }
+  TC_HD static float tiny() { return 1e-30f; }
+  TC_HD static float degRel() { return 1e-6f; }
+  TC_HD static float centerTiny() { return 1e-12f; }
+};
+
+// support of a primitive core (not a hull) in link-frame direction d
+template <class R>
+TC_HD Vec3<R> primitiveSupport(const ShapeCore<R>& s, Vec3<R> d)
+{
+  if (s.type == SH_SPHERE)
+    return s.center;
+  const R al = dot(d, s.axis);
+  if (s.type == SH_CAPSULE)
+    return s.center + ((al >= 0) ? s.half_len : -s.half_len) * s.axis;
+  const Vec3<R> rad = d - al * s.axis;
+  const R rn = norm(rad);
+  if (s.type == SH_CYLINDER)
+  {
+    Vec3<R> p = s.center + ((al >= 0) ? s.half_len : -s.half_len) * s.axis;
+    if (rn > Tol<R>::tiny())
+      p = p + (s.radius / rn) * rad;
+    return p;
+  }
+  // cone: apex at +half_len, base disc at -half_len
+  const R h = 2 * s.half_len;
+  const R sin_a = s.radius / tc_sqrt(s.radius * s.radius + h * h);
+  if (al > norm(d) * sin_a)
+    return s.center + s.half_len * s.axis;
+  Vec3<R> p = s.center - s.half_len * s.axis;
+  if (rn > Tol<R>::tiny())
+    p = p + (s.radius / rn) * rad;
+  return p;
+}
+
+// A shape placed in the world, optionally swept between two poses (convex hull of both placements):
+// support(d) = better of the supports at pose0 and pose1.
+template <class R>
+struct Placed
+{
+  ShapeCore<R> sh;
+  Pose<R> p0, p1;
+  bool cast;
+
+  TC_HD Vec3<R> support(Vec3<R> d, int& scanned) const
+  {
+    if (sh.type == SH_HULL)
+    {
+      const Vec3<R> d0 = p0.rotT(d);
+      if (!cast)
+      {
+        R best = lowestReal<R>();
+        int bi = 0;
+        for (int i = 0; i < sh.nverts; ++i)
+        {
+          const Vtx<R> q = sh.verts[i];
+          const R v = d0.x * q.x + d0.y * q.y + d0.z * q.z;
+          if (v > best)
+          {
+            best = v;
+            bi = i;
+          }
+        }
+        scanned += sh.nverts;
+        const Vtx<R> q = sh.verts[bi];
+        return p0.apply(Vec3<R>(q.x, q.y, q.z));
+      }
+      // swept hull: one pass over the vertices serves both end poses
+      const Vec3<R> d1 = p1.rotT(d);
+      R best0 = lowestReal<R>(), best1 = lowestReal<R>();
+      int b0 = 0, b1 = 0;
+      for (int i = 0; i < sh.nverts; ++i)
+      {
+        const Vtx<R> q = sh.verts[i];
+        const R v0 = d0.x * q.x + d0.y * q.y + d0.z * q.z;
+        const R v1 = d1.x * q.x + d1.y * q.y + d1.z * q.z;
+        if (v0 > best0)
+        {
+          best0 = v0;
+          b0 = i;
+        }
+        if (v1 > best1)
+        {
+          best1 = v1;
+          b1 = i;
+        }
+      }
+      scanned += 2 * sh.nverts;
+      const Vtx<R> q0 = sh.verts[b0], q1 = sh.verts[b1];
+      const Vec3<R> w0 = p0.apply(Vec3<R>(q0.x, q0.y, q0.z)), w1 = p1.apply(Vec3<R>(q1.x, q1.y, q1.z));
+      return (dot(d, w0) > dot(d, w1)) ? w0 : w1;
+    }
+    const Vec3<R> w0 = p0.apply(primitiveSupport(sh, p0.rotT(d)));
+    if (!cast)
+      return w0;
+    const Vec3<R> w1 = p1.apply(primitiveSupport(sh, p1.rotT(d)));
+    return (dot(d, w0) > dot(d, w1)) ? w0 : w1;
+  }
+  TC_HD Vec3<R> center() const
+  {
+    const Vec3<R> c0 = p0.apply(sh.center);
+    return cast ? R(0.5) * (c0 + p1.apply(sh.center)) : c0;
+  }
+};
+
+// ---------------------------------------------------------------------------------------------
+// simplex in registers: points 0..n-1, each the Minkowski-difference point w and its witness a on A
+// (the witness on B is a - w)
+// ---------------------------------------------------------------------------------------------
+template <class R>
+struct Simplex
+{
+  int n;
+  Vec3<R> w[4], a[4];
+  R lam[4];
+};
+
+// closest point of triangle (a,b,c) to the origin, barycentric weights out
+template <class R>
+TC_HD Vec3<R> closestTriangle(Vec3<R> a, Vec3<R> b, Vec3<R> c, R& la, R& lb, R& lc)
+{
+  const Vec3<R> ab = b - a, ac = c - a;
+  const R d1 = -dot(ab, a), d2 = -dot(ac, a);
+  if (d1 <= 0 && d2 <= 0)
+  {
+    la = 1, lb = 0, lc = 0;
+    return a;
+  }
+  const R d3 = -dot(ab, b), d4 = -dot(ac, b);
+  if (d3 >= 0 && d4 <= d3)
+  {
+    la = 0, lb = 1, lc = 0;
+    return b;
+  }
+  const R vc = d1 * d4 - d3 * d2;
+  if (vc <= 0 && d1 >= 0 && d3 <= 0)
+  {
+    const R t = d1 / (d1 - d3);
+    la = 1 - t, lb = t, lc = 0;
+    return a + t * ab;
+  }
+  const R d5 = -dot(ab, c), d6 = -dot(ac, c);
+  if (d6 >= 0 && d5 <= d6)
+  {
+    la = 0, lb = 0, lc = 1;
+    return c;
+  }
+  const R vb = d5 * d2 - d1 * d6;
+  if (vb <= 0 && d2 >= 0 && d6 <= 0)
+  {
+    const R t = d2 / (d2 - d6);
+    la = 1 - t, lb = 0, lc = t;
+    return a + t * ac;
+  }
+  const R va = d3 * d6 - d5 * d4;
+  if (va <= 0 && (d4 - d3) >= 0 && (d5 - d6) >= 0)
+  {
+    const R t = (d4 - d3) / ((d4 - d3) + (d5 - d6));
+    la = 0, lb = 1 - t, lc = t;
+    return b + t * (c - b);
+  }
+  const R den = R(1) / (va + vb + vc);
+  lb = vb * den;
+  lc = vc * den;
+  la = 1 - lb - lc;
+  return a + lb * ab + lc * ac;
+}
+
+// Closest point to the origin of the simplex spanned by points 0..m-1 of s (m = 2..4).
+// Outputs the barycentric weights aligned with the slots (0 for dropped points) and the keep mask.
+// mask == 15 means the origin is inside the tetrahedron.
+template <class R>
+TC_HD Vec3<R> closestOnSimplex(const Simplex<R>& s, int m, R lam[4], int& mask)
+{
+  lam[0] = lam[1] = lam[2] = lam[3] = 0;
+  if (m == 2)
+  {
+    const Vec3<R> ab = s.w[1] - s.w[0];
+    const R den = norm2(ab);
+    R t = (den > 0) ? -dot(s.w[0], ab) / den : R(0);
+    t = tc_min(R(1), tc_max(R(0), t));
+    lam[0] = 1 - t;
+    lam[1] = t;
+    mask = ((lam[0] > 0) ? 1 : 0) | ((lam[1] > 0) ? 2 : 0);
+    return s.w[0] + t * ab;
+  }
+  if (m == 3)
+  {
+    const Vec3<R> p = closestTriangle(s.w[0], s.w[1], s.w[2], lam[0], lam[1], lam[2]);
+    mask = ((lam[0] > 0) ? 1 : 0) | ((lam[1] > 0) ? 2 : 0) | ((lam[2] > 0) ? 4 : 0);
+    return p;
+  }
+  // tetrahedron: faces whose plane separates the origin from the opposite vertex
+  R best = -lowestReal<R>();
+  Vec3<R> bestp;
+  int bf = -1;
+  R bl0 = 0, bl1 = 0, bl2 = 0;
+#define TC_TETRA_FACE(F, I0, I1, I2, I3)                                                                             \
+  {                                                                                                                  \
+    const Vec3<R> a = s.w[I0], b = s.w[I1], c = s.w[I2], d = s.w[I3];                                                \
+    const Vec3<R> n = cross(b - a, c - a);                                                                           \
+    const R sp = -dot(a, n);                                                                                         \
+    const R sd = dot(d - a, n);                                                                                      \
+    const bool degenerate = tc_abs(sd) <= Tol<R>::degRel() * tc_sqrt(norm2(n) * norm2(d - a) + Tol<R>::tiny());                   \
+    if (sp * sd < 0 || degenerate)                                                                                   \
+    {                                                                                                                \
+      R la, lb, lc;                                                                                                  \
+      const Vec3<R> p = closestTriangle(a, b, c, la, lb, lc);                                                        \
+      const R d2 = norm2(p);                                                                                         \
+      if (d2 < best)                                                                                                 \
+      {                                                                                                              \
+        best = d2;                                                                                                   \
+        bestp = p;                                                                                                   \
+        bf = F;                                                                                                      \
+        bl0 = la, bl1 = lb, bl2 = lc;                                                                                \
+      }                                                                                                              \
+    }                                                                                                                \
+  }
+  TC_TETRA_FACE(0, 0, 1, 2, 3)
+  TC_TETRA_FACE(1, 0, 1, 3, 2)
+  TC_TETRA_FACE(2, 0, 2, 3, 1)
+  TC_TETRA_FACE(3, 1, 2, 3, 0)
+#undef TC_TETRA_FACE
+  if (bf < 0)
+  {
+    lam[0] = lam[1] = lam[2] = lam[3] = R(0.25);
+    mask = 15;
+    return Vec3<R>();
+  }
+  // scatter the three face weights back to their slots
+  if (bf == 0)
+    lam[0] = bl0, lam[1] = bl1, lam[2] = bl2;
+  else if (bf == 1)
+    lam[0] = bl0, lam[1] = bl1, lam[3] = bl2;
+  else if (bf == 2)
+    lam[0] = bl0, lam[2] = bl1, lam[3] = bl2;
+  else
+    lam[1] = bl0, lam[2] = bl1, lam[3] = bl2;
+  mask = ((lam[0] > 0) ? 1 : 0) | ((lam[1] > 0) ? 2 : 0) | ((lam[2] > 0) ? 4 : 0) | ((lam[3] > 0) ? 8 : 0);
+  return bestp;
+}
+
+// keep the points selected by `mask` (order preserved), select-only so the simplex stays in registers
+template <class R>
+TC_HD void compactSimplex(Simplex<R>& s, const R lam[4], int mask)
+{
+  const bool m0 = mask & 1, m1 = mask & 2, m2 = mask & 4, m3 = mask & 8;
+  // source slot of output slot k = k-th set bit
+  const int c0 = m0 ? 1 : 0, c1 = c0 + (m1 ? 1 : 0), c2 = c1 + (m2 ? 1 : 0);
+  // out0: first kept
+  const int s0 = m0 ? 0 : (m1 ? 1 : (m2 ? 2 : 3));
+  // out1: second kept
+  const int s1 = (m1 && c0 == 1) ? 1 : ((m2 && c1 == 1) ? 2 : 3);
+  // out2: third kept
+  const int s2 = (m2 && c1 == 2) ? 2 : 3;
+  (void)c2;
+  (void)m3;
+#define TC_SEL(arr, idx) ((idx) == 0 ? arr[0] : ((idx) == 1 ? arr[1] : ((idx) == 2 ? arr[2] : arr[3])))
+#define TC_SELV(arr, idx)                                                                                            \
+  Vec3<R>(TC_SEL(arr, idx).x, TC_SEL(arr, idx).y, TC_SEL(arr, idx).z)
+  const Vec3<R> w0 = TC_SELV(s.w, s0), w1 = TC_SELV(s.w, s1), w2 = TC_SELV(s.w, s2);
+  const Vec3<R> a0 = TC_SELV(s.a, s0), a1 = TC_SELV(s.a, s1), a2 = TC_SELV(s.a, s2);
+  const R l0 = TC_SEL(lam, s0), l1 = TC_SEL(lam, s1), l2 = TC_SEL(lam, s2);
+#undef TC_SELV
+#undef TC_SEL
+  s.w[0] = w0, s.w[1] = w1, s.w[2] = w2;
+  s.a[0] = a0, s.a[1] = a1, s.a[2] = a2;
+  s.lam[0] = l0, s.lam[1] = l1, s.lam[2] = l2;
+  s.lam[3] = lam[3];
+  s.n = (m0 ? 1 : 0) + (m1 ? 1 : 0) + (m2 ? 1 : 0) + (m3 ? 1 : 0);
+}
+
+enum
+{
+  GJK_MAX_ITERS = 128,
+  EPA_MAX_ITERS = 255
+};
+
+template <class R>
+struct GjkOut
+{
+  bool separated_beyond, intersect, converged;
+  R dist;
+  Vec3<R> pa, pb;
+  int iters;
+};
+
+template <class R>
+TC_HD void putPoint(Simplex<R>& s, int k, Vec3<R> w, Vec3<R> a)
+{
+  // predicated writes keep the arrays in registers
+  if (k == 0)
+    s.w[0] = w, s.a[0] = a;
+  if (k == 1)
+    s.w[1] = w, s.a[1] = a;
+  if (k == 2)
+    s.w[2] = w, s.a[2] = a;
+  if (k == 3)
+    s.w[3] = w, s.a[3] = a;
+}
+
+template <class R>
+TC_HD GjkOut<R> gjk(const Placed<R>& A, const Placed<R>& B, R threshold_core, Simplex<R>& S, int& scanned)
+{
+  GjkOut<R> r;
+  r.separated_beyond = false;
+  r.intersect = false;
+  r.converged = true;
+  r.dist = 0;
+  Vec3<R> v = A.center() - B.center();
+  if (norm2(v) < Tol<R>::centerTiny())
+    v = Vec3<R>(1, 0, 0);
+  {
+    const Vec3<R> a = A.support(-v, scanned), b = B.support(v, scanned);
+    S.w[0] = a - b;
+    S.a[0] = a;
+  }
+  S.n = 1;
+  S.lam[0] = 1, S.lam[1] = 0, S.lam[2] = 0, S.lam[3] = 0;
+  v = S.w[0];
+  R vv = norm2(v);
+  const R touch2 = Tol<R>::gjkTouch() * Tol<R>::gjkTouch();
+  for (r.iters = 1; r.iters <= GJK_MAX_ITERS; ++r.iters)
+  {
+    if (vv <= touch2)
+    {
+      r.intersect = true;
+      break;
+    }
+    const Vec3<R> a = A.support(-v, scanned), b = B.support(v, scanned);
+    const Vec3<R> w = a - b;
+    const R vw = dot(v, w);
+    if (vw > 0 && vw * vw > threshold_core * threshold_core * vv)
+    {
+      r.separated_beyond = true;
+      return r;
+    }
+    if (vv - vw <= Tol<R>::gjkTol() * tc_sqrt(vv))
+      break;
+    bool dup = false;
+    const R dupt = Tol<R>::dupRel() * tc_max(R(1), norm2(w));
+    if (norm2(w - S.w[0]) <= dupt)
+      dup = true;
+    if (S.n > 1 && norm2(w - S.w[1]) <= dupt)
+      dup = true;
+    if (S.n > 2 && norm2(w - S.w[2]) <= dupt)
+      dup = true;
+    if (dup)
+      break;
+    putPoint(S, S.n, w, a);  // slots >= n are free: S itself is untouched until the commit below
+    R lam[4];
+    int mask;
+    const Vec3<R> vn = closestOnSimplex(S, S.n + 1, lam, mask);
+    if (mask == 15)
+    {
+      S.n = 4;
+      S.lam[0] = S.lam[1] = S.lam[2] = S.lam[3] = R(0.25);
+      r.intersect = true;
+      break;
+    }
+    const R vvn = norm2(vn);
+    if (vvn >= vv)
+      break;  // no progress within rounding: S already holds the closest point
+    compactSimplex(S, lam, mask);
+    v = vn;
+    vv = vvn;
+    if (r.iters == GJK_MAX_ITERS)
+      r.converged = false;
+  }
+  if (!r.intersect)
+  {
+    r.dist = tc_sqrt(vv);
+    Vec3<R> pa, pw;
+    pa = S.lam[0] * S.a[0];
+    pw = S.lam[0] * S.w[0];
+    if (S.n > 1)
+      pa = pa + S.lam[1] * S.a[1], pw = pw + S.lam[1] * S.w[1];
+    if (S.n > 2)
+      pa = pa + S.lam[2] * S.a[2], pw = pw + S.lam[2] * S.w[2];
+    r.pa = pa;
+    r.pb = pa - pw;
+  }
+  return r;
+}
+
+// ---------------------------------------------------------------------------------------------
+// EPA on a bounded polytope store (thread-local on the fast path, global scratch on the rare
+// deep-expansion path; same code).  Dead face slots are reused first-fit.
+// ---------------------------------------------------------------------------------------------
+template <class R>
+struct EpaStore
+{
+  Vec3<R>* pw;  // [max_verts]
+  Vec3<R>* pa;
+  Vec3<R>* fn;  // [max_faces]
+  R* fd;
+  int* fv;      // packed v0 | v1 << 10 | v2 << 20 ; -1 = dead slot
+  int* edges;   // [max_faces] packed a | b << 16
+  int max_verts, max_faces;
+};
+
+template <class R>
+struct EpaOut
+{
+  bool ok;         // false: the store overflowed, nothing else valid
+  bool converged;
+  R depth;
+  Vec3<R> normal, pa, pb;
+  int iters;
+};
+
+template <class R>
+TC_HD Vec3<R> leastAxisCross(Vec3<R> e)
+{
+  Vec3<R> ax(1, 0, 0);
+  if (tc_abs(e.y) <= tc_abs(e.x) && tc_abs(e.y) <= tc_abs(e.z))
+    ax = Vec3<R>(0, 1, 0);
+  else if (tc_abs(e.z) <= tc_abs(e.x) && tc_abs(e.z) <= tc_abs(e.y))
+    ax = Vec3<R>(0, 0, 1);
+  return cross(e, ax);
+}
+
+template <class R>
+TC_HDN EpaOut<R> epa(const Placed<R>& A, const Placed<R>& B, const Simplex<R>& start, R scale, EpaStore<R>& st,
+                     int& scanned)
+{
+  EpaOut<R> r;
+  r.ok = true;
+  r.converged = true;
+  r.depth = 0;
+  r.iters = 0;
+  int np = start.n;
+  for (int i = 0; i < 4; ++i)
+    if (i < start.n)
+    {
+      st.pw[i] = start.w[i];
+      st.pa[i] = start.a[i];
+    }
+  const R eps_len = Tol<R>::epsLenRel() * tc_max(scale, R(1e-3));
+  const R vis_eps = Tol<R>::visRel() * tc_max(scale, R(1e-3));
+
+  // --- grow the GJK simplex to a tetrahedron with non-zero volume ---
+  if (np == 4)
+  {
+    const R vol = dot(cross(st.pw[1] - st.pw[0], st.pw[2] - st.pw[0]), st.pw[3] - st.pw[0]);
+    if (tc_abs(vol) <= eps_len * eps_len * eps_len)
+      np = 3;
+  }
+  if (np == 1)
+  {
+    for (int k = 0; k < 6 && np == 1; ++k)
+    {
+      const R sg = (k & 1) ? R(-1) : R(1);
+      const Vec3<R> d((k >> 1) == 0 ? sg : R(0), (k >> 1) == 1 ? sg : R(0), (k >> 1) == 2 ? sg : R(0));
+      const Vec3<R> a = A.support(d, scanned), b = B.support(-d, scanned);
+      const Vec3<R> w = a - b;
+      if (norm(w - st.pw[0]) > eps_len)
+      {
+        st.pw[1] = w;
+        st.pa[1] = a;
+        np = 2;
+      }
+    }
+  }
+  if (np == 2)
+  {
+    const Vec3<R> e = st.pw[1] - st.pw[0];
+    const Vec3<R> d0 = leastAxisCross(e);
+    const Vec3<R> d1 = cross(e, d0);
+    const R en = norm(e);
+    for (int k = 0; k < 4 && np == 2; ++k)
+    {
+      const Vec3<R> d = (k == 0) ? d0 : ((k == 1) ? -d0 : ((k == 2) ? d1 : -d1));
+      const Vec3<R> a = A.support(d, scanned), b = B.support(-d, scanned);
+      const Vec3<R> w = a - b;
+      if (norm(cross(w - st.pw[0], e)) > eps_len * en)
+      {
+        st.pw[2] = w;
+        st.pa[2] = a;
+        np = 3;
+      }
+    }
+  }
+  if (np == 3)
+  {
+    const Vec3<R> n = cross(st.pw[1] - st.pw[0], st.pw[2] - st.pw[0]);
+    const R area = norm(n);
+    for (int sgn = 0; sgn < 2 && np == 3; ++sgn)
+    {
+      const Vec3<R> d = (sgn == 0) ? n : -n;
+      const Vec3<R> a = A.support(d, scanned), b = B.support(-d, scanned);
+      const Vec3<R> w = a - b;
+      if (tc_abs(dot(w - st.pw[0], n)) > eps_len * area)
+      {
+        st.pw[3] = w;
+        st.pa[3] = a;
+        np = 4;
+      }
+    }
+  }
+  if (np < 4)
+  {
+    // flat Minkowski difference (point / segment / polygon cores): core depth is zero, the normal is
+    // the direction in which the difference has no extent
+    Vec3<R> n(0, 0, 1);
+    if (np == 3)
+      n = cross(st.pw[1] - st.pw[0], st.pw[2] - st.pw[0]);
+    else if (np == 2)
+      n = leastAxisCross(st.pw[1] - st.pw[0]);
+    const R nn = norm(n);
+    r.normal = (nn > 0) ? (R(1) / nn) * n : Vec3<R>(0, 0, 1);
+    Vec3<R> pa, pw;
+    if (start.n == 1)
+    {
+      pa = start.a[0];
+      pw = start.w[0];
+    }
+    else
+    {
+      R lam[4];
+      int mask;
+      closestOnSimplex(start, start.n, lam, mask);
+      pa = lam[0] * start.a[0] + lam[1] * start.a[1];
+      pw = lam[0] * start.w[0] + lam[1] * start.w[1];
+      if (start.n > 2)
+        pa = pa + lam[2] * start.a[2], pw = pw + lam[2] * start.w[2];
+      if (start.n > 3)
+        pa = pa + lam[3] * start.a[3], pw = pw + lam[3] * start.w[3];
+    }
+    r.pa = pa;
+    r.pb = pa - pw;
+    return r;
+  }
+
+  int nf = 0;  // high-water mark of the face array
+  const Vec3<R> centroid = R(0.25) * (st.pw[0] + st.pw[1] + st.pw[2] + st.pw[3]);
+  // returns false on overflow
+  auto addFace = [&](int i, int j, int k, bool orient) -> bool {
+    Vec3<R> n = cross(st.pw[j] - st.pw[i], st.pw[k] - st.pw[i]);
+    if (orient && dot(n, st.pw[i] - centroid) < 0)
+    {
+      const int t = j;
+      j = k;
+      k = t;
+      n = -n;
+    }
+    int slot = -1;
+    for (int f = 0; f < nf; ++f)
+      if (st.fv[f] < 0)
+      {
+        slot = f;
+        break;
+      }
+    if (slot < 0)
+    {
+      if (nf >= st.max_faces)
+        return false;
+      slot = nf++;
+    }
+    const R nn = norm(n);
+    st.fv[slot] = i | (j << 10) | (k << 20);
+    if (nn > Tol<R>::tiny())
+    {
+      st.fn[slot] = (R(1) / nn) * n;
+      st.fd[slot] = dot(st.fn[slot], st.pw[i]);
+    }
+    else
+    {
+      st.fn[slot] = Vec3<R>(0, 0, 0);
+      st.fd[slot] = -lowestReal<R>();  // degenerate sliver: never selected
+    }
+    return true;
+  };
+  addFace(0, 1, 2, true);
+  addFace(0, 1, 3, true);
+  addFace(0, 2, 3, true);
+  addFace(1, 2, 3, true);
+
+  int best = -1;
+  for (r.iters = 1; r.iters <= EPA_MAX_ITERS; ++r.iters)
+  {
+    best = -1;
+    R bd = 0;
+    for (int f = 0; f < nf; ++f)
+      if (st.fv[f] >= 0 && (best < 0 || st.fd[f] < bd))
+      {
+        best = f;
+        bd = st.fd[f];
+      }
+    const Vec3<R> bn = st.fn[best];
+    const Vec3<R> xa = A.support(bn, scanned), xb = B.support(-bn, scanned);
+    const Vec3<R> xw = xa - xb;
+    if (dot(bn, xw) - bd <= Tol<R>::epaTol())
+      break;
+    if (r.iters == EPA_MAX_ITERS)
+    {
+      r.converged = false;
+      break;
+    }
+    if (np >= st.max_verts)
+    {
+      r.ok = false;
+      return r;
+    }
+    const int xi = np;
+    st.pw[np] = xw;
+    st.pa[np] = xa;
+    ++np;
+    // remove the faces that see x, collect the horizon
+    int ne = 0;
+    for (int f = 0; f < nf; ++f)
+    {
+      const int fv = st.fv[f];
+      if (fv < 0 || st.fd[f] == -lowestReal<R>())
+        continue;
+      const int v0 = fv & 1023, v1 = (fv >> 10) & 1023, v2 = (fv >> 20) & 1023;
+      if (dot(st.fn[f], xw - st.pw[v0]) > vis_eps)
+      {
+        st.fv[f] = -1;
+        for (int e = 0; e < 3; ++e)
+        {
+          const int ea = (e == 0) ? v0 : ((e == 1) ? v1 : v2);
+          const int eb = (e == 0) ? v1 : ((e == 1) ? v2 : v0);
+          const int twin = eb | (ea << 16);
+          int found = -1;
+          for (int q = 0; q < ne; ++q)
+            if (st.edges[q] == twin)
+            {
+              found = q;
+              break;
+            }
+          if (found >= 0)
+          {
+            for (int q = found; q + 1 < ne; ++q)
+              st.edges[q] = st.edges[q + 1];
+            --ne;
+          }
+          else
+          {
+            if (ne >= st.max_faces)
+            {
+              r.ok = false;
+              return r;
+            }
+            st.edges[ne++] = ea | (eb << 16);
+          }
+        }
+      }
+    }
+    if (ne == 0)
+    {
+      // numerically x is not outside any face although the gap test said so: accept the current face
+      --np;
+      break;
+    }
+    for (int q = 0; q < ne; ++q)
+      if (!addFace(st.edges[q] & 65535, st.edges[q] >> 16, xi, false))
+      {
+        r.ok = false;
+        return r;
+      }
+  }
+  // `best` may have been killed in the last expansion only when the loop ran out of iterations with
+  // converged == false; it still holds the face data
+  const int fv = st.fv[best] >= 0 ? st.fv[best] : -1;
+  r.depth = st.fd[best];
+  r.normal = st.fn[best];
+  if (fv < 0)
+  {
+    r.converged = false;
+    r.pa = Vec3<R>();
+    r.pb = Vec3<R>();
+    return r;
+  }
+  // Witness points: the face with the smallest PLANE distance may be one of several coplanar triangles of
+  // a larger Minkowski face; the witness is taken on the triangle that is actually closest to the origin.
+  int wf = best;
+  R wbest = -lowestReal<R>(), la = 0, lb = 0, lc = 0;
+  for (int f = 0; f < nf; ++f)
+  {
+    const int gv = st.fv[f];
+    if (gv < 0 || st.fd[f] == -lowestReal<R>() || st.fd[f] > r.depth + eps_len)
+      continue;
+    R a0, a1, a2;
+    const Vec3<R> q = closestTriangle(st.pw[gv & 1023], st.pw[(gv >> 10) & 1023], st.pw[(gv >> 20) & 1023], a0, a1, a2);
+    const R q2 = norm2(q);
+    if (q2 < wbest)
+    {
+      wbest = q2;
+      wf = f;
+      la = a0, lb = a1, lc = a2;
+    }
+  }
+  const int gv = st.fv[wf];
+  const int v0 = gv & 1023, v1 = (gv >> 10) & 1023, v2 = (gv >> 20) & 1023;
+  r.pa = la * st.pa[v0] + lb * st.pa[v1] + lc * st.pa[v2];
+  const Vec3<R> pw = la * st.pw[v0] + lb * st.pw[v1] + lc * st.pw[v2];
+  r.pb = r.pa - pw;
+  return r;
+}
+
+// length scale of the Minkowski difference used by EPA's degeneracy thresholds
+template <class R>
+TC_HD R epaScale(const Placed<R>& A, R brad_a, const Placed<R>& B, R brad_b)
+{
+  R s = 2 * (brad_a + brad_b);
+  if (A.cast)
+    s += norm(A.p1.apply(A.sh.center) - A.p0.apply(A.sh.center));
+  if (B.cast)
+    s += norm(B.p1.apply(B.sh.center) - B.p0.apply(B.sh.center));
+  return s;
+}
+
+enum
+{
+  ND_NONE = 0,        // farther apart than the threshold
+  ND_CONTACT = 1,
+  ND_EPA_OVERFLOW = 2  // polytope store too small: item must be re-run on the deep-expansion path
+};
+
+template <class R>
+struct DistOut
+{
+  int status;
+  R distance;
+  Vec3<R> normal, pa, pb;  // normal from A to B; world witness points on the surfaces
+  bool used_epa, converged;
+  int gjk_iters, epa_iters, scanned;
+};
+
+template <class R>
+TC_HDN DistOut<R> signedDistance(const Placed<R>& A, R brad_a, const Placed<R>& B, R brad_b, R threshold,
+                                 EpaStore<R>& store)
+{
+  DistOut<R> out;
+  out.status = ND_NONE;
+  out.distance = 0;
+  out.used_epa = false;
+  out.epa_iters = 0;
+  out.scanned = 0;
+  const R ra = A.sh.coreRadius(), rb = B.sh.coreRadius();
+  Simplex<R> S;
+  const GjkOut<R> g = gjk(A, B, threshold + ra + rb, S, out.scanned);
+  out.gjk_iters = g.iters;
+  out.converged = g.converged;
+  if (g.separated_beyond)
+    return out;
+  Vec3<R> n, pa, pb;
+  R d_core;
+  if (!g.intersect)
+  {
+    d_core = g.dist;
+    n = (R(1) / g.dist) * (g.pb - g.pa);
+    pa = g.pa;
+    pb = g.pb;
+  }
+  else
+  {
+    const EpaOut<R> e = epa(A, B, S, epaScale(A, brad_a, B, brad_b), store, out.scanned);
+    out.used_epa = true;
+    out.epa_iters = e.iters;
+    if (!e.ok)
+    {
+      out.status = ND_EPA_OVERFLOW;
+      return out;
+    }
+    out.converged = out.converged && e.converged;
+    d_core = -e.depth;
+    n = e.normal;
+    pa = e.pa;
+    pb = e.pb;
+  }
+  out.distance = d_core - ra - rb;
+  if (out.distance > threshold)
+    return out;
+  out.status = ND_CONTACT;
+  out.normal = n;
+  out.pa = pa + ra * n;
+  out.pb = pb - rb * n;
+  return out;
+}
+}  // namespace tc

@@ -1,0 +1,935 @@
+// tc_pipeline.cu — every kernel of the pass except the narrow phase:
+//   K0 plan (LVS subdivision counts) + scans, K1 batched FK with per-shape AABBs, K2 AABB broadphase with
+//   a warp-cooperative (ballot + popc) per-shape-pair bucket list, contact finalisation + key sort,
+//   K4 gradient rows / constraint rows / GradientResultsSets / cost.
+// Reference call sites are cited at each kernel.
+#include <cub/device/device_radix_sort.cuh>
+
+#include "tc_internal.hpp"
+
+namespace tc
+{
+namespace
+{
+constexpr int TPB = 128;
+
+__device__ __forceinline__ int lastLE(const int32_t* a, int n, int x)
+{
+  // largest i in [0, n) with a[i] <= x   (a ascending, a[0] <= x)
+  int lo = 0, hi = n;
+  while (hi - lo > 1)
+  {
+    const int mid = (lo + hi) >> 1;
+    if (a[mid] <= x)
+      lo = mid;
+    else
+      hi = mid;
+  }
+  return lo;
+}
+
+// ---------------------------------------------------------------------------------------------
+// K0: LVS subdivision of every term
+//   dist = ||q1 - q0||, cnt = dist > LVS ? ceil(dist / LVS) + 1 : 2
+//   trajopt/src/collision_terms.cpp:825-843,1068-1080; continuous_collision_evaluators.cpp:204-212,423-434
+// ---------------------------------------------------------------------------------------------
+__global__ void k_plan(SceneView v, Work w)
+{
+  const int k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= w.ep.n_terms)
+    return;
+  int cnt = 1, states = 1, units = 1, interp = 0;
+  if (w.ep.evaluator != TC_EVAL_DISCRETE)
+  {
+    const int b = k / w.ep.terms_per_traj, ti = k % w.ep.terms_per_traj;
+    const int n = v.n_dof;
+    const double* q0 = w.q + (static_cast<size_t>(b) * w.ep.T + w.term_t[ti]) * n;
+    const double* q1 = q0 + n;
+    double d2 = 0;
+    for (int j = 0; j < n; ++j)
+    {
+      const double d = q1[j] - q0[j];
+      d2 = __dadd_rn(d2, __dmul_rn(d, d));  // no FMA contraction: cnt is a discrete decision
+    }
+    const double dist = sqrt(d2);
+    cnt = 2;
+    if (dist > w.ep.lvs)
+    {
+      const double c = ceil(dist / w.ep.lvs) + 1.0;
+      if (c > 16384.0)
+      {
+        atomicExch(reinterpret_cast<unsigned long long*>(&w.counters->overflow), 2ull);
+        cnt = 16384;
+      }
+      else
+        cnt = static_cast<int>(c);
+    }
+    if (w.ep.evaluator == TC_EVAL_LVS_DISCRETE)
+    {
+      states = units = cnt;
+      interp = 1;
+    }
+    else if (!w.single_sweep && cnt > 2)
+    {
+      states = cnt;
+      units = cnt - 1;
+      interp = 1;
+    }
+    else
+    {
+      states = 2;
+      units = 1;
+    }
+  }
+  w.term_cnt[k] = cnt;
+  w.term_states[k] = states;
+  w.term_units[k] = units;
+  w.term_interp[k] = static_cast<uint8_t>(interp);
+}
+
+// single-block exclusive scan helper: returns the exclusive prefix of `val` within the block and the
+// block total (all threads)
+__device__ __forceinline__ long long blockExclusive(long long val, long long& total, long long* smem /*[33]*/)
+{
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  long long incl = val;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1)
+  {
+    const long long t = __shfl_up_sync(0xffffffffu, incl, o);
+    if (lane >= o)
+      incl += t;
+  }
+  if (lane == 31)
+    smem[wid] = incl;
+  __syncthreads();
+  if (wid == 0)
+  {
+    long long x = (lane < (blockDim.x >> 5)) ? smem[lane] : 0;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1)
+    {
+      const long long t = __shfl_up_sync(0xffffffffu, x, o);
+      if (lane >= o)
+        x += t;
+    }
+    smem[lane] = x;  // inclusive warp totals
+    if (lane == 31)
+      smem[32] = x;
+  }
+  __syncthreads();
+  const long long before = (wid > 0) ? smem[wid - 1] : 0;
+  total = smem[32];
+  __syncthreads();
+  return before + incl - val;
+}
+
+__global__ void __launch_bounds__(1024) k_scan_terms(Work w)
+{
+  __shared__ long long sm[33];
+  long long carry_s = 0, carry_u = 0;
+  const int n = w.ep.n_terms;
+  for (int base = 0; base < n; base += blockDim.x)
+  {
+    const int k = base + threadIdx.x;
+    const long long a = (k < n) ? w.term_states[k] : 0, b = (k < n) ? w.term_units[k] : 0;
+    long long ta, tb;
+    const long long ea = blockExclusive(a, ta, sm);
+    const long long eb = blockExclusive(b, tb, sm);
+    if (k < n)
+    {
+      w.state_base[k] = static_cast<int32_t>(carry_s + ea);
+      w.unit_base[k] = static_cast<int32_t>(carry_u + eb);
+    }
+    carry_s += ta;
+    carry_u += tb;
+  }
+  if (threadIdx.x == 0)
+  {
+    w.state_base[n] = static_cast<int32_t>(carry_s);
+    w.unit_base[n] = static_cast<int32_t>(carry_u);
+    w.counters->n_states = carry_s;
+    w.counters->n_units = carry_u;
+    if (carry_s > 2000000000ll)
+      w.counters->overflow = 3;
+  }
+}
+
+__global__ void k_unit_term(Work w)
+{
+  const int u = blockIdx.x * blockDim.x + threadIdx.x;
+  if (u < w.n_units)
+    w.unit_term[u] = lastLE(w.unit_base, w.ep.n_terms, u);
+}
+
+// ---------------------------------------------------------------------------------------------
+// K1: batched forward kinematics of every sub-state + world AABB of every active shape
+//   get_state_fn_ -> JointGroup::calcFwdKin (trajopt/src/collision_terms.cpp:401-417,656,880-885,1123-1124;
+//   discrete_collision_evaluators.cpp:57-73; continuous_collision_evaluators.cpp:65-81,285-301) and the
+//   sub-state interpolation LinSpaced(cnt, q0, q1) (collision_terms.cpp:846-848)
+// One thread per sub-state; frame poses live in a thread-local array (the tree has branches).
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(TPB) k_fk(SceneView v, Work w)
+{
+  const long long s = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (s >= w.n_states)
+    return;
+  const int k = lastLE(w.state_base, w.ep.n_terms, static_cast<int>(s));
+  const int i = static_cast<int>(s) - w.state_base[k];
+  const int b = k / w.ep.terms_per_traj, ti = k % w.ep.terms_per_traj;
+  const int n = v.n_dof;
+  const double* q0 = w.q + (static_cast<size_t>(b) * w.ep.T + w.term_t[ti]) * n;
+  double q[64];
+  if (w.ep.evaluator == TC_EVAL_DISCRETE)
+  {
+    for (int j = 0; j < n; ++j)
+      q[j] = q0[j];
+  }
+  else
+  {
+    const int cnt = w.term_interp[k] ? w.term_cnt[k] : 2;
+    for (int j = 0; j < n; ++j)
+      q[j] = linspaced(cnt, q0[j], q0[n + j], i);
+  }
+  Pose<double> F[MAX_FRAMES];
+  const Pose<double> base = Pose<double>::from12(v.base_pose);
+  for (int f = 0; f < v.n_frames; ++f)
+  {
+    const int p = v.frame_parent[f];
+    Vec3<double> z;
+    F[f] = frameStep(v, p < 0 ? base : F[p], f, q, z);
+  }
+  double* out = w.poses + static_cast<size_t>(s) * v.n_active * 12;
+  for (int l = 0; l < v.n_active; ++l)
+    F[v.link_frame[l]].to12(out + 12 * l);
+  for (int a = 0; a < v.n_active_shapes; ++a)
+  {
+    const ShapeD& sh = v.shapes[v.active_shapes[a]];
+    const Pose<double>& T = F[v.link_frame[sh.link]];
+    const Vec3<double> c = T.apply(Vec3<double>(sh.aabb_c[0], sh.aabb_c[1], sh.aabb_c[2]));
+    double* dst = w.aabb + static_cast<size_t>(a) * 6 * w.n_states + s;
+#pragma unroll
+    for (int r = 0; r < 3; ++r)
+    {
+      const double e =
+          fabs(T.r[3 * r + 0]) * sh.aabb_h[0] + fabs(T.r[3 * r + 1]) * sh.aabb_h[1] + fabs(T.r[3 * r + 2]) * sh.aabb_h[2];
+      dst[static_cast<size_t>(r) * w.n_states] = c.get(r) - e;
+      dst[static_cast<size_t>(3 + r) * w.n_states] = c.get(r) + e;
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// K2: AABB broadphase.  setCollisionObjectsTransform + the broadphase half of contactTest
+//   (trajopt/src/collision_terms.cpp:665-667,887-889,1132-1134,1155-1157).
+// One thread per (unit, active shape): its (swept) AABB stays in registers while the thread walks the
+// shape's partner list (static partner boxes are warp-uniform loads).  A warp = 32 consecutive units of
+// the same shape pair, so survivors are appended to that shape pair's bucket with one ballot + one
+// atomic per warp.  Pass 1 counts, pass 2 fills.
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ void loadBox(const Work& w, int a, long long s0, long long s1, double lo[3], double hi[3])
+{
+  const double* p = w.aabb + static_cast<size_t>(a) * 6 * w.n_states;
+#pragma unroll
+  for (int r = 0; r < 3; ++r)
+  {
+    lo[r] = p[static_cast<size_t>(r) * w.n_states + s0];
+    hi[r] = p[static_cast<size_t>(3 + r) * w.n_states + s0];
+  }
+  if (s1 != s0)
+  {
+#pragma unroll
+    for (int r = 0; r < 3; ++r)
+    {
+      lo[r] = fmin(lo[r], p[static_cast<size_t>(r) * w.n_states + s1]);
+      hi[r] = fmax(hi[r], p[static_cast<size_t>(3 + r) * w.n_states + s1]);
+    }
+  }
+}
+
+template <bool FILL>
+__global__ void __launch_bounds__(TPB) k_broad(SceneView v, Work w)
+{
+  const long long u = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+  const int a = blockIdx.y;
+  const bool inb = u < w.n_units;
+  long long s0 = 0, s1 = 0;
+  if (inb)
+  {
+    const int k = w.unit_term[u];
+    s0 = w.state_base[k] + (u - w.unit_base[k]);
+    s1 = w.cast ? s0 + 1 : s0;
+  }
+  double alo[3], ahi[3];
+  loadBox(w, a, s0, s1, alo, ahi);
+  const unsigned lane = threadIdx.x & 31;
+  for (int pi = v.partner_ptr[a]; pi < v.partner_ptr[a + 1]; ++pi)
+  {
+    const int sp = v.partner_sp[pi];
+    const ShapePairD spd = v.spairs[sp];
+    const double thr = v.pairs[spd.pair].thr;
+    const int bidx = v.shapes[spd.sb].active_index;
+    double blo[3], bhi[3];
+    if (bidx < 0)
+    {
+#pragma unroll
+      for (int r = 0; r < 3; ++r)
+      {
+        blo[r] = v.static_aabb[6 * spd.sb + r];
+        bhi[r] = v.static_aabb[6 * spd.sb + 3 + r];
+      }
+    }
+    else
+      loadBox(w, bidx, s0, s1, blo, bhi);
+    bool overlap = inb;
+#pragma unroll
+    for (int r = 0; r < 3; ++r)
+      if (alo[r] - bhi[r] > thr || blo[r] - ahi[r] > thr)
+        overlap = false;
+    const unsigned m = __ballot_sync(0xffffffffu, overlap);
+    if (m == 0)
+      continue;
+    const int leader = __ffs(m) - 1;
+    if (FILL)
+    {
+      int base = 0;
+      if (lane == leader)
+        base = atomicAdd(&w.sp_cursor[sp], __popc(m));
+      base = __shfl_sync(0xffffffffu, base, leader);
+      if (overlap)
+        w.items[w.sp_offset[sp] + base + __popc(m & ((1u << lane) - 1u))] = static_cast<int32_t>(u);
+    }
+    else if (lane == leader)
+      atomicAdd(&w.sp_count[sp], __popc(m));
+  }
+}
+
+// bucket offsets, every bucket padded to a whole narrow-phase CTA
+__global__ void __launch_bounds__(1024) k_scan_sp(SceneView v, Work w)
+{
+  __shared__ long long sm[33];
+  long long carry = 0, raw_total = 0;
+  const int n = v.n_spairs;
+  for (int base = 0; base < n; base += blockDim.x)
+  {
+    const int k = base + threadIdx.x;
+    const long long c = (k < n) ? w.sp_count[k] : 0;
+    const long long padded = (c + CHUNK - 1) / CHUNK * CHUNK;
+    long long t, t2;
+    const long long e = blockExclusive(padded, t, sm);
+    blockExclusive(c, t2, sm);
+    if (k < n)
+      w.sp_offset[k] = static_cast<int32_t>(carry + e);
+    carry += t;
+    raw_total += t2;
+  }
+  if (threadIdx.x == 0)
+  {
+    w.sp_offset[n] = static_cast<int32_t>(carry);
+    w.counters->n_items_padded = carry;
+    w.counters->n_items = raw_total;
+    if (carry > 2000000000ll)
+      w.counters->overflow = 4;
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// contact finalisation: ContactResult fields, cast bookkeeping, LVS merge, filters, sort key
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ UnitInfo unitInfo(const Work& w, int u)
+{
+  UnitInfo ui;
+  const int k = w.unit_term[u];
+  const int ti = k % w.ep.terms_per_traj;
+  ui.term = k;
+  ui.traj = k / w.ep.terms_per_traj;
+  ui.t = w.term_t[ti];
+  ui.substep = u - w.unit_base[k];
+  ui.last = w.term_cnt[k] - 1;
+  ui.state0 = w.state_base[k] + ui.substep;
+  ui.interp = w.term_interp[k] != 0;
+  ui.f0 = w.term_fixed[2 * ti] != 0;
+  ui.f1 = w.term_fixed[2 * ti + 1] != 0;
+  return ui;
+}
+
+__global__ void __launch_bounds__(TPB) k_finalize(SceneView v, Work w)
+{
+  const long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+  bool valid = false;
+  if (i < w.n_raw)
+  {
+    const RawContact raw = w.raw[i];
+    const UnitInfo ui = unitInfo(w, raw.unit);
+    const ShapePairD sp = v.spairs[raw.sp];
+    const PairD pr = v.pairs[sp.pair];
+    Pose<double> p0[2], p1[2];
+    const int links[2] = { pr.a, pr.b };
+#pragma unroll
+    for (int j = 0; j < 2; ++j)
+    {
+      if (links[j] < v.n_active)
+      {
+        const double* src = w.poses + (static_cast<size_t>(ui.state0) * v.n_active + links[j]) * 12;
+        p0[j] = Pose<double>::from12(src);
+        p1[j] = w.cast ? Pose<double>::from12(src + static_cast<size_t>(v.n_active) * 12) : p0[j];
+      }
+      else
+      {
+        p0[j] = Pose<double>::from12(v.link_pose + 12 * links[j]);
+        p1[j] = p0[j];
+      }
+    }
+    tc_contact c;
+    valid = finalizeContact(v, w.ep, raw, ui, p0, p1, c, w.xf_tmp + static_cast<size_t>(i) * 48);
+    w.contacts_tmp[i] = c;
+    unsigned long long key = ~0ull;
+    if (valid)
+      key = (static_cast<unsigned long long>(ui.term) << 36) | (static_cast<unsigned long long>(sp.pair) << 22) |
+            (static_cast<unsigned long long>(ui.substep) << 8) | static_cast<unsigned long long>(sp.k);
+    w.keys[i] = key;
+    w.idx[i] = static_cast<int32_t>(i);
+  }
+  const unsigned m = __ballot_sync(0xffffffffu, valid);
+  if ((threadIdx.x & 31) == 0 && m)
+    atomicAdd(reinterpret_cast<unsigned long long*>(&w.counters->n_valid), static_cast<unsigned long long>(__popc(m)));
+}
+
+// sorted order -> final arrays, one thread per 8-byte word (25 words of tc_contact + 48 of transforms)
+__global__ void __launch_bounds__(256) k_gather(Work w, const int32_t* idx)
+{
+  constexpr int WC = sizeof(tc_contact) / 8, WX = 48, WT = WC + WX;
+  const long long g = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+  const long long i = g / WT;
+  const int word = static_cast<int>(g % WT);
+  if (i >= w.n_contacts)
+    return;
+  const long long src = idx[i];
+  if (word < WC)
+    reinterpret_cast<double*>(w.contacts + i)[word] = reinterpret_cast<const double*>(w.contacts_tmp + src)[word];
+  else
+    w.xf[i * WX + (word - WC)] = w.xf_tmp[src * WX + (word - WC)];
+}
+
+__global__ void k_term_ptr(Work w, const unsigned long long* keys)
+{
+  const int k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k > w.ep.n_terms)
+    return;
+  const unsigned long long target = static_cast<unsigned long long>(k) << 36;
+  long long lo = 0, hi = w.n_contacts;  // first index with key >= target
+  while (lo < hi)
+  {
+    const long long mid = (lo + hi) >> 1;
+    if (keys[mid] < target)
+      lo = mid + 1;
+    else
+      hi = mid;
+  }
+  w.term_ptr[k] = lo;
+}
+
+// ---------------------------------------------------------------------------------------------
+// K4: gradients, rows, cost, sets
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ int termOfContact(const Work& w, long long i)
+{
+  // contacts are sorted by term: binary search the term pointer
+  int lo = 0, hi = w.ep.n_terms;
+  while (hi - lo > 1)
+  {
+    const int mid = (lo + hi) >> 1;
+    if (w.term_ptr[mid] <= i)
+      lo = mid;
+    else
+      hi = mid;
+  }
+  return lo;
+}
+
+__global__ void __launch_bounds__(TPB) k_grad(SceneView v, Work w)
+{
+  const long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (i >= w.n_contacts)
+    return;
+  const tc_contact c = w.contacts[i];
+  const int ti = termOfContact(w, i) % w.ep.terms_per_traj;
+  const int n = v.n_dof;
+  const double* q0 = w.q + (static_cast<size_t>(c.traj) * w.ep.T + c.term) * n;
+  const double* q1 = (w.ep.evaluator == TC_EVAL_DISCRETE) ? q0 : q0 + n;
+  double qt[64];
+  GradOut out;
+  contactGradient(v, w.ep, c, w.xf + i * 48, q0, q1, w.term_fixed[2 * ti] != 0, w.term_fixed[2 * ti + 1] != 0, qt,
+                  w.grad + static_cast<size_t>(i) * 4 * n, out);
+  w.grec[i] = out.rec;
+  w.ghas[i] = out.has;
+}
+
+// per-term row offsets: rows of a term all have n_dof * (#free blocks) entries
+__global__ void __launch_bounds__(1024) k_row_base(SceneView v, Work w, long long* term_row_base)
+{
+  __shared__ long long sm[33];
+  long long carry = 0;
+  const int n = w.ep.n_terms;
+  const bool single = w.ep.evaluator == TC_EVAL_DISCRETE;
+  for (int base = 0; base < n; base += blockDim.x)
+  {
+    const int k = base + threadIdx.x;
+    long long val = 0;
+    if (k < n)
+    {
+      const int ti = k % w.ep.terms_per_traj;
+      const int nb = (w.term_fixed[2 * ti] ? 0 : 1) + ((single || w.term_fixed[2 * ti + 1]) ? 0 : 1);
+      val = (w.term_ptr[k + 1] - w.term_ptr[k]) * nb * v.n_dof;
+    }
+    long long t;
+    const long long e = blockExclusive(val, t, sm);
+    if (k < n)
+      term_row_base[k] = carry + e;
+    carry += t;
+  }
+  if (threadIdx.x == 0)
+  {
+    term_row_base[n] = carry;
+    w.counters->nnz = carry;
+  }
+}
+
+// DiscreteCollisionConstraintD / ContinuousCollisionConstraintD getValues + getJacobian
+// (discrete_collision_constraint.cpp:214-283, continuous_collision_constraint.cpp:311-417) and the legacy
+// CollisionsToDistanceExpressions / CalcDistExpressions* (collision_terms.cpp:341-386,463-554)
+__global__ void __launch_bounds__(TPB) k_rows(SceneView v, Work w, const long long* term_row_base, int32_t* col_idx,
+                                              double* val, double* row_value, double* row_coeff, double* row_margin)
+{
+  const long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (i > w.n_contacts)
+    return;
+  if (i == w.n_contacts)
+  {
+    w.row_ptr[i] = term_row_base[w.ep.n_terms];
+    return;
+  }
+  const int k = termOfContact(w, i);
+  const int ti = k % w.ep.terms_per_traj;
+  const bool f0 = w.term_fixed[2 * ti] != 0, f1 = w.term_fixed[2 * ti + 1] != 0;
+  const bool single = w.ep.evaluator == TC_EVAL_DISCRETE;
+  const int n = v.n_dof;
+  const int nb = (f0 ? 0 : 1) + ((single || f1) ? 0 : 1);
+  long long nnz = term_row_base[k] + (i - w.term_ptr[k]) * nb * n;
+  w.row_ptr[i] = nnz;
+  const tc_contact& c = w.contacts[i];
+  const PairD pr = v.pairs[c.pair];
+  const double* g = w.grad + static_cast<size_t>(i) * 4 * n;
+  const tc_gradient rec = w.grec[i];
+  const int has = w.ghas[i];
+  const double* q0 = w.q + (static_cast<size_t>(c.traj) * w.ep.T + c.term) * n;
+  double constant = c.distance;
+  for (int blk = 0; blk < 2; ++blk)
+  {
+    if (blk == 0 && f0)
+      continue;
+    if (blk == 1 && (single || f1))
+      continue;
+    const double* qb = blk ? q0 + n : q0;
+    for (int j = 0; j < n; ++j)
+    {
+      double s = 0;
+#pragma unroll
+      for (int l = 0; l < 2; ++l)
+        if (has & (1 << (2 * l + blk)))
+          s += (blk ? rec.scale1[l] : rec.scale0[l]) * g[(2 * l + blk) * n + j];
+      if (w.ep.stack == TC_STACK_LEGACY)
+      {
+        constant -= s * qb[j];
+        val[nnz] = s;
+      }
+      else
+        val[nnz] = -1.0 * s;
+      col_idx[nnz] = (c.term + blk) * n + j;
+      ++nnz;
+    }
+  }
+  row_value[i] = (w.ep.stack == TC_STACK_LEGACY) ? constant : (pr.margin - c.distance);
+  row_coeff[i] = pr.coeff;
+  row_margin[i] = pr.margin;
+}
+
+// CollisionCost::value / CollisionConstraint::value (collision_terms.cpp:1287-1306,1367-1386)
+__global__ void k_cost_term(SceneView v, Work w, double* cost_term)
+{
+  const int k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= w.ep.n_terms)
+    return;
+  double out = 0;
+  for (long long i = w.term_ptr[k]; i < w.term_ptr[k + 1]; ++i)
+  {
+    const PairD pr = v.pairs[w.contacts[i].pair];
+    out += fmax(pr.margin - w.contacts[i].distance, 0.0) * pr.coeff;
+  }
+  cost_term[k] = out;
+}
+__global__ void k_cost_traj(Work w, const double* cost_term, double* cost_traj)
+{
+  const int b = blockIdx.x * blockDim.x + threadIdx.x;
+  if (b >= w.ep.B)
+    return;
+  double out = 0;
+  for (int ti = 0; ti < w.ep.terms_per_traj; ++ti)
+    out += cost_term[static_cast<size_t>(b) * w.ep.terms_per_traj + ti];
+  cost_traj[b] = out;
+}
+
+// GradientResultsSet grouping, ordering and the fixed-size constraint rows
+//   discrete_collision_evaluators.cpp:101-148, continuous_collision_evaluators.cpp:113-162,
+//   trajopt_common/src/collision_types.cpp:173-333, weighted_average_methods.cpp:31-107,
+//   discrete_collision_constraint.cpp:68-141, continuous_collision_constraint.cpp:80-236
+__device__ __forceinline__ int cantorKey(int shape_id, int subshape_id)
+{
+  if (subshape_id < 0)
+    return shape_id;
+  return static_cast<int>(1 / 2.0 * (shape_id + subshape_id) * (shape_id + subshape_id + 1) + subshape_id);
+}
+constexpr double LOWEST = -1.7976931348623157e308;
+
+__device__ bool setMaxError(const tc_set& s, int which, bool buffer, double& e)
+{
+  e = LOWEST;
+  bool found = false;
+#pragma unroll
+  for (int i = 0; i < 2; ++i)
+#pragma unroll
+    for (int k = 0; k < 2; ++k)
+    {
+      if (which != 2 && which != k)
+        continue;
+      const double val = buffer ? s.error_with_buffer[i][k] : s.error[i][k];
+      if (s.has_error[i][k] && val > e)
+      {
+        e = val;
+        found = true;
+      }
+    }
+  return found;
+}
+
+__device__ void weightedAvgRow(const SceneView& v, const Work& w, const tc_set& s, int i0, int i1, double max_ewb,
+                               bool t1, double* row)
+{
+  const int n = v.n_dof;
+  double total = 0;
+  long cnt = 0;
+  for (int c = i0; c < i1; ++c)
+  {
+    const tc_contact& ct = w.contacts[c];
+    if (cantorKey(ct.shape_id[0], ct.subshape_id[0]) != s.shape_key[0] ||
+        cantorKey(ct.shape_id[1], ct.subshape_id[1]) != s.shape_key[1])
+      continue;
+    const int has = w.ghas[c];
+    const tc_gradient& rec = w.grec[c];
+    for (int i = 0; i < 2; ++i)
+    {
+      if (!(has & (1 << (2 * i + (t1 ? 1 : 0)))))
+        continue;
+      if (ct.cc_type[i] == (t1 ? TC_CC_TIME0 : TC_CC_TIME1))
+        continue;
+      if (s.error_with_buffer[i][t1 ? 1 : 0] > 0)
+      {
+        const double wt = fmax(rec.error_with_buffer, 0.0) / max_ewb;
+        total += wt;
+        const double sc = t1 ? rec.scale1[i] : rec.scale0[i];
+        const double* g = w.grad + (static_cast<size_t>(c) * 4 + 2 * i + (t1 ? 1 : 0)) * n;
+        for (int j = 0; j < n; ++j)
+          row[j] += wt * (sc * g[j]);
+        ++cnt;
+      }
+    }
+  }
+  if (cnt == 0)
+    return;
+  const double scale = 1 / total;
+  for (int j = 0; j < n; ++j)
+    row[j] = -1.0 * (row[j] * scale);
+}
+
+__global__ void __launch_bounds__(64) k_sets(SceneView v, Work w, int max_num_cnt, tc_set* sets, int32_t* set_count,
+                                             int32_t* set_run, double* values, double* coeffs, double* jac)
+{
+  const int k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= w.ep.n_terms)
+    return;
+  const int n = v.n_dof;
+  const long long lo = w.term_ptr[k], hi = w.term_ptr[k + 1];
+  tc_set* S = sets + lo;
+  int32_t* RUN = set_run + 2 * lo;
+  const int ti = k % w.ep.terms_per_traj;
+  const bool f0 = w.term_fixed[2 * ti] != 0, f1 = w.term_fixed[2 * ti + 1] != 0;
+  const bool single = w.ep.evaluator == TC_EVAL_DISCRETE;
+  int ns = 0;
+  long long i = lo;
+  while (i < hi)
+  {
+    const int pair = w.contacts[i].pair;
+    const long long i0 = i;
+    while (i < hi && w.contacts[i].pair == pair)
+      ++i;
+    const int first = ns;
+    for (long long c = i0; c < i; ++c)
+    {
+      const tc_contact& ct = w.contacts[c];
+      const int k0 = cantorKey(ct.shape_id[0], ct.subshape_id[0]), k1 = cantorKey(ct.shape_id[1], ct.subshape_id[1]);
+      int j = first;
+      for (; j < ns; ++j)
+        if (S[j].shape_key[0] == k0 && S[j].shape_key[1] == k1)
+          break;
+      if (j == ns)
+      {
+        tc_set t;
+        t.traj = ct.traj, t.term = ct.term, t.pair = pair;
+        t.shape_key[0] = k0, t.shape_key[1] = k1;
+        t.n_results = 0;
+        t.coeff = v.pairs[pair].coeff;
+        for (int a = 0; a < 2; ++a)
+          for (int b = 0; b < 2; ++b)
+            t.has_error[a][b] = 0, t.error[a][b] = LOWEST, t.error_with_buffer[a][b] = LOWEST;
+        S[ns] = t;
+        RUN[2 * ns] = static_cast<int32_t>(i0);
+        RUN[2 * ns + 1] = static_cast<int32_t>(i);
+        ++ns;
+      }
+      // GradientResultsSet::add
+      tc_set& t = S[j];
+      const tc_gradient& rec = w.grec[c];
+      const int has = w.ghas[c];
+      for (int l = 0; l < 2; ++l)
+      {
+        if (!(has & (1 << (2 * l))))
+          continue;
+        if (rec.cc_type[l] != TC_CC_TIME1)
+        {
+          t.has_error[l][0] = 1;
+          t.error[l][0] = fmax(t.error[l][0], rec.error);
+          t.error_with_buffer[l][0] = fmax(t.error_with_buffer[l][0], rec.error_with_buffer);
+        }
+        if (rec.cc_type[l] != TC_CC_TIME0)
+        {
+          t.has_error[l][1] = 1;
+          t.error[l][1] = fmax(t.error[l][1], rec.error);
+          t.error_with_buffer[l][1] = fmax(t.error_with_buffer[l][1], rec.error_with_buffer);
+        }
+      }
+      t.n_results += 1;
+    }
+    // std::map order of the shape keys inside one link pair
+    for (int a = first + 1; a < ns; ++a)
+    {
+      const tc_set x = S[a];
+      const int r0 = RUN[2 * a], r1 = RUN[2 * a + 1];
+      int j = a;
+      while (j > first && (x.shape_key[0] < S[j - 1].shape_key[0] ||
+                           (x.shape_key[0] == S[j - 1].shape_key[0] && x.shape_key[1] < S[j - 1].shape_key[1])))
+      {
+        S[j] = S[j - 1];
+        RUN[2 * j] = RUN[2 * j - 2], RUN[2 * j + 1] = RUN[2 * j - 1];
+        --j;
+      }
+      S[j] = x;
+      RUN[2 * j] = r0, RUN[2 * j + 1] = r1;
+    }
+  }
+  set_count[k] = ns;
+  if (ns > max_num_cnt)
+  {
+    const int which = single ? 0 : ((!f0 && !f1) ? 2 : (!f0 ? 0 : 1));
+    // stable insertion sort, largest error first
+    for (int a = 1; a < ns; ++a)
+    {
+      const tc_set x = S[a];
+      const int r0 = RUN[2 * a], r1 = RUN[2 * a + 1];
+      int j = a;
+      while (j > 0)
+      {
+        bool before;  // x strictly before S[j-1]
+        if (single)
+        {
+          // std::array<double,2> operator> on max_error[0].error
+          const double *xa = x.error[0], *ya = S[j - 1].error[0];
+          before = (ya[0] < xa[0]) || (!(xa[0] < ya[0]) && ya[1] < xa[1]);
+        }
+        else
+        {
+          double ex, ey;
+          setMaxError(x, which, true, ex);
+          setMaxError(S[j - 1], which, true, ey);
+          before = ex > ey;
+        }
+        if (!before)
+          break;
+        S[j] = S[j - 1];
+        RUN[2 * j] = RUN[2 * j - 2], RUN[2 * j + 1] = RUN[2 * j - 1];
+        --j;
+      }
+      S[j] = x;
+      RUN[2 * j] = r0, RUN[2 * j + 1] = r1;
+    }
+  }
+  double* val = values + static_cast<size_t>(k) * max_num_cnt;
+  double* cf = coeffs + static_cast<size_t>(k) * max_num_cnt;
+  double* J = jac + static_cast<size_t>(k) * max_num_cnt * 2 * n;
+  for (int a = 0; a < max_num_cnt; ++a)
+  {
+    val[a] = -v.margin_buffer;
+    cf[a] = 1.0;
+  }
+  for (int a = 0; a < max_num_cnt * 2 * n; ++a)
+    J[a] = 0.0;
+  const int cnt = ns < max_num_cnt ? ns : max_num_cnt;
+  for (int a = 0; a < cnt; ++a)
+  {
+    const tc_set& g = S[a];
+    const int r0 = RUN[2 * a], r1 = RUN[2 * a + 1];
+    cf[a] = g.coeff;
+    double* J0 = J + (static_cast<size_t>(a) * 2 + 0) * n;
+    double* J1 = J + (static_cast<size_t>(a) * 2 + 1) * n;
+    double e, m;
+    if (single)
+    {
+      setMaxError(g, 0, false, e);
+      val[a] = e;
+      setMaxError(g, 0, true, m);
+      weightedAvgRow(v, w, g, r0, r1, m, false, J0);
+      continue;
+    }
+    const bool h0 = g.has_error[0][0] || g.has_error[1][0];
+    const bool h1 = g.has_error[0][1] || g.has_error[1][1];
+    if (!f0 && !f1)
+    {
+      setMaxError(g, 2, false, e);
+      val[a] = e;
+    }
+    else if (!f0)
+    {
+      if (h0)
+      {
+        setMaxError(g, 0, false, e);
+        val[a] = e;
+      }
+    }
+    else if (h1)
+    {
+      setMaxError(g, 1, false, e);
+      val[a] = e;
+    }
+    if (!f0 && h0)
+    {
+      setMaxError(g, !f1 ? 2 : 0, true, m);
+      weightedAvgRow(v, w, g, r0, r1, m, false, J0);
+    }
+    if (!f1 && h1)
+    {
+      setMaxError(g, !f0 ? 2 : 1, true, m);
+      weightedAvgRow(v, w, g, r0, r1, m, true, J1);
+    }
+  }
+}
+
+inline unsigned gridFor(long long n, int tpb) { return static_cast<unsigned>((n + tpb - 1) / tpb); }
+}  // namespace
+
+cudaError_t launchPlan(const SceneView& v, const Work& w, cudaStream_t st)
+{
+  k_plan<<<gridFor(w.ep.n_terms, TPB), TPB, 0, st>>>(v, w);
+  k_scan_terms<<<1, 1024, 0, st>>>(w);
+  return cudaGetLastError();
+}
+
+cudaError_t launchFk(const SceneView& v, const Work& w, cudaStream_t st)
+{
+  k_unit_term<<<gridFor(w.n_units, 256), 256, 0, st>>>(w);
+  k_fk<<<gridFor(w.n_states, TPB), TPB, 0, st>>>(v, w);
+  return cudaGetLastError();
+}
+
+cudaError_t launchBroadCount(const SceneView& v, const Work& w, cudaStream_t st)
+{
+  cudaError_t e = cudaMemsetAsync(w.sp_count, 0, sizeof(int32_t) * v.n_spairs, st);
+  if (e != cudaSuccess)
+    return e;
+  e = cudaMemsetAsync(w.sp_cursor, 0, sizeof(int32_t) * v.n_spairs, st);
+  if (e != cudaSuccess)
+    return e;
+  const dim3 grid(gridFor(w.n_units, TPB), static_cast<unsigned>(v.n_active_shapes));
+  k_broad<false><<<grid, TPB, 0, st>>>(v, w);
+  k_scan_sp<<<1, 1024, 0, st>>>(v, w);
+  return cudaGetLastError();
+}
+
+cudaError_t launchBroadFill(const SceneView& v, const Work& w, cudaStream_t st)
+{
+  cudaError_t e = cudaMemsetAsync(w.items, 0xff, sizeof(int32_t) * static_cast<size_t>(w.n_items_padded), st);
+  if (e != cudaSuccess)
+    return e;
+  const dim3 grid(gridFor(w.n_units, TPB), static_cast<unsigned>(v.n_active_shapes));
+  k_broad<true><<<grid, TPB, 0, st>>>(v, w);
+  return cudaGetLastError();
+}
+
+cudaError_t launchFinalize(const SceneView& v, const Work& w, cudaStream_t st)
+{
+  if (w.n_raw > 0)
+    k_finalize<<<gridFor(w.n_raw, TPB), TPB, 0, st>>>(v, w);
+  return cudaGetLastError();
+}
+
+cudaError_t sortContacts(const Work& w, void* temp, size_t& temp_bytes, cudaStream_t st)
+{
+  return cub::DeviceRadixSort::SortPairs(temp, temp_bytes, w.keys, w.keys_alt, w.idx, w.idx_alt,
+                                         static_cast<int>(w.n_raw), 0, 64, st);
+}
+
+cudaError_t launchGather(const SceneView& v, const Work& w, cudaStream_t st)
+{
+  (void)v;
+  if (w.n_contacts > 0)
+  {
+    const long long words = w.n_contacts * (static_cast<long long>(sizeof(tc_contact)) / 8 + 48);
+    k_gather<<<gridFor(words, 256), 256, 0, st>>>(w, w.idx_alt);
+  }
+  k_term_ptr<<<gridFor(w.ep.n_terms + 1, 256), 256, 0, st>>>(w, w.keys_alt);
+  return cudaGetLastError();
+}
+
+cudaError_t launchGradients(const SceneView& v, const Work& w, cudaStream_t st)
+{
+  if (w.n_contacts > 0)
+    k_grad<<<gridFor(w.n_contacts, TPB), TPB, 0, st>>>(v, w);
+  return cudaGetLastError();
+}
+
+cudaError_t launchRows(const SceneView& v, const Work& w, long long* term_row_base, int32_t* col_idx, double* val,
+                       double* row_value, double* row_coeff, double* row_margin, cudaStream_t st)
+{
+  k_rows<<<gridFor(w.n_contacts + 1, TPB), TPB, 0, st>>>(v, w, term_row_base, col_idx, val, row_value, row_coeff,
+                                                       row_margin);
+  return cudaGetLastError();
+}
+
+cudaError_t launchRowBase(const SceneView& v, const Work& w, long long* term_row_base, cudaStream_t st)
+{
+  k_row_base<<<1, 1024, 0, st>>>(v, w, term_row_base);
+  return cudaGetLastError();
+}
+
+cudaError_t launchCost(const SceneView& v, const Work& w, double* cost_term, double* cost_traj, cudaStream_t st)
+{
+  k_cost_term<<<gridFor(w.ep.n_terms, TPB), TPB, 0, st>>>(v, w, cost_term);
+  k_cost_traj<<<gridFor(w.ep.B, TPB), TPB, 0, st>>>(w, cost_term, cost_traj);
+  return cudaGetLastError();
+}
+
+cudaError_t launchSets(const SceneView& v, const Work& w, int max_num_cnt, tc_set* sets, int32_t* set_count,
+                       int32_t* set_run, double* values, double* coeffs, double* jac, cudaStream_t st)
+{
+  k_sets<<<gridFor(w.ep.n_terms, 64), 64, 0, st>>>(v, w, max_num_cnt, sets, set_count, set_run, values, coeffs, jac);
+  return cudaGetLastError();
+}
+}  // namespace tc
