@@ -75,3 +75,80 @@ class HostCheck(capi.Lib):
                                               capi._p(pb, _pd), C.byref(epa), C.byref(gi), C.byref(ei), C.byref(sc)))
         return dict(status=status.value, contact=status.value == 1, distance=dist.value, normal=n, pa=pa, pb=pb,
                     epa=bool(epa.value), iters=gi.value, epa_iters=ei.value, scanned=sc.value)
+
+
+def contact_keys(c):
+    """unique key of a contact inside one evaluation"""
+    return list(zip(c["traj"].tolist(), c["term"].tolist(), c["pair"].tolist(), c["substep"].tolist(),
+                    c["shape_id"][:, 0].tolist(), c["shape_id"][:, 1].tolist()))
+
+
+def compare(ro, rg, band=1e-9, want_rows=True):
+    """Parity report oracle result `ro` vs CUDA result `rg` (same scene, same inputs).
+
+    Contacts are matched by (traj, term, link pair, substep, shape ids).  Contacts whose oracle distance
+    lies within `band` of margin+buffer may be present on one side only (SURVEY 8c parity protocol)."""
+    co, cg = ro.contacts(), rg.contacts()
+    ko, kg = contact_keys(co), contact_keys(cg)
+    io = {k: i for i, k in enumerate(ko)}
+    ig = {k: i for i, k in enumerate(kg)}
+    assert len(io) == len(ko) and len(ig) == len(kg), "duplicate contact keys"
+    _, _, margin, _ = ro.scene.pairs()
+    thr = margin + ro.scene.margin_buffer
+    only_o = [k for k in ko if k not in ig]
+    only_g = [k for k in kg if k not in io]
+    bad_o = [k for k in only_o if abs(co["distance"][io[k]] - thr[k[2]]) > band]
+    bad_g = [k for k in only_g if abs(cg["distance"][ig[k]] - thr[k[2]]) > band]
+    common = [k for k in ko if k in ig]
+    a = np.array([io[k] for k in common], dtype=np.int64)
+    b = np.array([ig[k] for k in common], dtype=np.int64)
+    rep = dict(n_contacts=len(ko), n_contacts_gpu=len(kg), n_common=len(common), unmatched_outside_band=len(bad_o) + len(bad_g),
+               same_order=(ko == kg))
+    cto, ctg = ro.counts(), rg.counts()
+    rep["counts_equal"] = all(cto[f] == ctg[f] for f in ("n_states", "n_units", "n_dense", "n_candidates", "n_terms"))
+    rep["n_narrowphase"] = (cto["n_narrowphase"], ctg["n_narrowphase"])
+    rep["n_epa"] = (cto["n_epa"], ctg["n_epa"])
+    rep["gjk_iters"] = (cto["gjk_iters"], ctg["gjk_iters"])
+    rep["n_unconverged"] = (cto["n_unconverged"], ctg["n_unconverged"])
+    if len(common) == 0:
+        rep.update(max_dist_err=0.0, max_normal_err=0.0, max_point_err=0.0, max_cc_time_err=0.0, cc_type_mismatch=0,
+                   max_grad_rel_err=0.0, max_row_rel_err=0.0, max_row_value_err=0.0, max_cost_err=0.0)
+        return rep
+    A, G = co[a], cg[b]
+    rep["max_dist_err"] = float(np.abs(A["distance"] - G["distance"]).max())
+    rep["max_normal_err"] = float(np.abs(A["normal"] - G["normal"]).max())
+    rep["max_point_err"] = float(max(np.abs(A["nearest_points"] - G["nearest_points"]).max(),
+                                     np.abs(A["nearest_points_local"] - G["nearest_points_local"]).max()))
+    rep["max_cc_time_err"] = float(np.abs(A["cc_time"] - G["cc_time"]).max())
+    rep["cc_type_mismatch"] = int((A["cc_type"] != G["cc_type"]).any(axis=1).sum())
+    rep["ids_equal"] = bool((A["link_ids"] == G["link_ids"]).all() and (A["state"] == G["state"]).all())
+    xo, xg = ro.contact_transforms()[a], rg.contact_transforms()[b]
+    rep["max_transform_err"] = float(np.abs(xo - xg).max())
+    same_cc = ~(A["cc_type"] != G["cc_type"]).any(axis=1)
+    if want_rows:
+        reco, go = ro.gradients()
+        recg, gg = rg.gradients()
+        go, gg = go[a], gg[b]
+        den = np.maximum(np.abs(go).reshape(len(a), -1).max(axis=1), 1e-12)
+        rel = np.abs(go - gg).reshape(len(a), -1).max(axis=1) / den
+        rep["max_grad_rel_err"] = float(rel[same_cc].max()) if same_cc.any() else 0.0
+        rowo, rowg = ro.rows(), rg.rows()
+        worst, worst_v = 0.0, 0.0
+        for i, j in zip(a, b):
+            vo = rowo["val"][rowo["row_ptr"][i]:rowo["row_ptr"][i + 1]]
+            vg = rowg["val"][rowg["row_ptr"][j]:rowg["row_ptr"][j + 1]]
+            assert len(vo) == len(vg)
+            assert (rowo["col_idx"][rowo["row_ptr"][i]:rowo["row_ptr"][i + 1]] ==
+                    rowg["col_idx"][rowg["row_ptr"][j]:rowg["row_ptr"][j + 1]]).all()
+            if len(vo) and not (A["cc_type"][np.where(a == i)[0][0]] != G["cc_type"][np.where(a == i)[0][0]]).any():
+                worst = max(worst, float(np.abs(vo - vg).max() / max(np.abs(vo).max(), 1e-12)))
+            worst_v = max(worst_v, abs(float(rowo["value"][i] - rowg["value"][j])))
+        rep["max_row_rel_err"] = worst
+        rep["max_row_value_err"] = worst_v
+        rep["rec_equal"] = bool((reco["has_gradient"][a] == recg["has_gradient"][b]).all())
+    cto_term, cto_traj = ro.cost()
+    ctg_term, ctg_traj = rg.cost()
+    rep["max_cost_err"] = float(np.abs(cto_traj - ctg_traj).max()) if len(cto_traj) else 0.0
+    if ko == kg:
+        rep["term_ptr_equal"] = bool((ro.term_ptr() == rg.term_ptr()).all())
+    return rep

@@ -1,0 +1,120 @@
+"""GPU parity tests proper: CUDA path (through the C ABI) vs the CPU oracle on the same seeded inputs.
+Tolerances are the north_star's: identical contact sets outside a 1e-9 m band around margin+buffer,
+distances within 1e-6 m, gradient rows within 1e-5 relative (FP64 mode)."""
+import numpy as np
+import pytest
+
+from tests import helpers
+
+capi = helpers.capi
+pytestmark = pytest.mark.gpu
+
+DIST_TOL, ROW_TOL = 1e-6, 1e-5
+
+
+def check(rep, rows=True):
+    assert rep["counts_equal"], rep
+    assert rep["unmatched_outside_band"] == 0, rep
+    assert rep["max_dist_err"] <= DIST_TOL, rep
+    assert rep["max_normal_err"] <= 1e-5, rep
+    assert rep["max_cost_err"] <= 1e-6 * max(1.0, rep["n_contacts"]), rep
+    if rows:
+        assert rep["max_grad_rel_err"] <= ROW_TOL, rep
+        assert rep["max_row_rel_err"] <= ROW_TOL, rep
+        assert rep["max_row_value_err"] <= 1e-6, rep
+
+
+def pair(cuda, oracle, name, margin, coeff, buf):
+    s = helpers.load_scene(name)
+    return s, cuda.scene(s, margin, coeff, buf), oracle.scene(s, margin, coeff, buf)
+
+
+def test_boxbot_known_answers(cuda):
+    """trajopt_ifopt/test/collision_unit.cpp:97-159: DiscreteCollisionConstraint(max_num_cnt=1) on boxbot"""
+    s = helpers.load_scene("boxbot")
+    sg = cuda.scene(s, 0.1, 1.0, 0.01)
+    cases = [((-1.9, 0.01), -0.01, (0, 0)), ((-1.0, 0.01), 0.1, (1, 0)), ((0.01, 1.0), 0.1, (0, -1)),
+             ((-0.9, 0.01), 0.2, (1, 0))]
+    for q, val, jac in cases:
+        r = cuda.eval(sg, np.array(q).reshape(1, 1, 2), capi.EVAL_DISCRETE)
+        st = r.sets(1)
+        assert abs(st["values"][0, 0] - val) <= 1e-6, (q, st["values"])
+        assert np.abs(st["jac"][0, 0, 0] - np.array(jac)).max() <= 1e-6, (q, st["jac"])
+
+
+@pytest.mark.parametrize("evaluator", [capi.EVAL_DISCRETE, capi.EVAL_LVS_DISCRETE, capi.EVAL_CONTINUOUS,
+                                       capi.EVAL_LVS_CONTINUOUS])
+@pytest.mark.parametrize("stack", [capi.STACK_IFOPT, capi.STACK_LEGACY])
+def test_arm_around_table_seed(cuda, oracle, evaluator, stack):
+    s, sg, so = pair(cuda, oracle, "arm_around_table", 0.025, 20.0, 0.01)
+    q = s["seed_traj"][None]
+    fixed = np.zeros(q.shape[1], np.uint8)
+    fixed[0] = fixed[-1] = 1
+    rg = cuda.eval(sg, q, evaluator, stack=stack, lvs=0.02, fixed=fixed)
+    ro = oracle.eval(so, q, evaluator, stack=stack, lvs=0.02, fixed=fixed)
+    rep = helpers.compare(ro, rg)
+    assert rep["n_contacts"] > 0
+    check(rep)
+    assert rep["same_order"] and rep["term_ptr_equal"]
+
+
+@pytest.mark.parametrize("evaluator", [capi.EVAL_LVS_DISCRETE, capi.EVAL_LVS_CONTINUOUS])
+def test_arm_batch_random_seeds(cuda, oracle, evaluator):
+    s, sg, so = pair(cuda, oracle, "arm_around_table", 0.025, 20.0, 0.01)
+    rng = np.random.default_rng(7)
+    B = 24
+    q = np.repeat(s["seed_traj"][None], B, 0)
+    q[:, 1:-1] += rng.normal(0, 0.3, (B, q.shape[1] - 2, 7))
+    lim = s["joint_limits"]
+    q = np.clip(q, lim[:, 0], lim[:, 1])
+    fixed = np.zeros(q.shape[1], np.uint8)
+    fixed[0] = fixed[-1] = 1
+    rg = cuda.eval(sg, q, evaluator, lvs=0.05, fixed=fixed)
+    ro = oracle.eval(so, q, evaluator, lvs=0.05, fixed=fixed, n_threads=8)
+    check(helpers.compare(ro, rg))
+
+
+@pytest.mark.parametrize("name", ["boxbot", "spherebot"])
+@pytest.mark.parametrize("evaluator", [capi.EVAL_DISCRETE, capi.EVAL_LVS_DISCRETE, capi.EVAL_LVS_CONTINUOUS])
+def test_small_bots(cuda, oracle, name, evaluator):
+    s, sg, so = pair(cuda, oracle, name, 0.2, 1.0, 0.05)
+    q = np.array([[[-1.9, 0.0], [0.0, 1.9], [1.9, 3.8]], [[-0.75, 0.75], [-0.2, 0.3], [0.4, 0.1]]])
+    rg = cuda.eval(sg, q, evaluator, lvs=0.05)
+    ro = oracle.eval(so, q, evaluator, lvs=0.05)
+    rep = helpers.compare(ro, rg)
+    assert rep["n_contacts"] > 0
+    # face-face box contacts have non-unique witness points; the robots are prismatic so rows are immune
+    check(rep)
+
+
+@pytest.mark.parametrize("evaluator,max_cnt", [(capi.EVAL_DISCRETE, 3), (capi.EVAL_LVS_CONTINUOUS, 3),
+                                               (capi.EVAL_LVS_DISCRETE, 2)])
+def test_fixed_size_sets(cuda, oracle, evaluator, max_cnt):
+    s, sg, so = pair(cuda, oracle, "arm_around_table", 0.025, 20.0, 0.01)
+    q = s["seed_traj"][None]
+    fixed = np.zeros(q.shape[1], np.uint8)
+    fixed[0] = fixed[-1] = 1
+    rg = cuda.eval(sg, q, evaluator, lvs=0.02, fixed=fixed)
+    ro = oracle.eval(so, q, evaluator, lvs=0.02, fixed=fixed)
+    a, b = ro.sets(max_cnt), rg.sets(max_cnt)
+    assert (a["set_ptr"] == b["set_ptr"]).all()
+    assert (a["sets"]["pair"] == b["sets"]["pair"]).all()
+    assert np.abs(a["values"] - b["values"]).max() <= 1e-6
+    assert np.abs(a["coeffs"] - b["coeffs"]).max() == 0
+    den = np.maximum(np.abs(a["jac"]).max(axis=-1, keepdims=True), 1e-12)
+    assert (np.abs(a["jac"] - b["jac"]) / den).max() <= ROW_TOL
+
+
+def test_empty_and_errors(cuda):
+    s = helpers.load_scene("boxbot")
+    sg = cuda.scene(s, 0.1, 1.0, 0.01)
+    r = cuda.eval(sg, np.array([[[5.0, 5.0]]]), capi.EVAL_DISCRETE)  # far away: no contacts
+    assert r.counts()["n_contacts"] == 0 and len(r.contacts()) == 0
+    assert r.rows()["row_ptr"].tolist() == [0]
+    assert r.sets(2)["values"].tolist() == [[-0.01, -0.01]]
+    r = cuda.eval(sg, np.zeros((1, 2, 2)), capi.EVAL_LVS_CONTINUOUS, fixed=[1, 1])  # all fixed: no terms
+    assert r.counts()["n_terms"] == 0
+    with pytest.raises(capi.TcError):
+        cuda.eval(sg, np.zeros((1, 1, 2)), capi.EVAL_LVS_CONTINUOUS)  # segment evaluator needs T >= 2
+    with pytest.raises(capi.TcError):
+        cuda.eval(sg, np.zeros((1, 2, 2)), 7)
