@@ -237,6 +237,10 @@ int tc_result_gradients(const tc_result* res, tc_gradient* rec, double* grad, si
  * d(x) = row_value + val . x  (CollisionsToDistanceExpressions + CalcDistExpressions*). */
 int tc_result_rows(const tc_result* res, int64_t* row_ptr, int32_t* col_idx, double* val, double* row_value,
                    double* row_coeff, double* row_margin);
+/* same rows left in device memory (for a consumer that assembles the QP on the GPU); valid until the next
+ * tc_eval on this result */
+int tc_result_rows_device(const tc_result* res, const int64_t** row_ptr, const int32_t** col_idx, const double** val,
+                          const double** row_value, const double** row_coeff, const double** row_margin);
 /* fixed-size constraints: sets of every term sorted as the evaluator sorts them, the first
  * min(max_num_cnt, n) of each term turned into rows.  set_ptr[n_terms + 1].
  * values[n_terms][max_num_cnt], coeffs idem, jac[n_terms][max_num_cnt][2][n_dof] (T0 block, T1 block) */
@@ -261,9 +265,13 @@ int tc_allgather_best(double local_best_cost, int64_t local_best_idx, void* nccl
 /* ---- measurement helpers (bench only) ---- */
 /* register-resident DFMA / FFMA loop: returns achieved TFLOP/s (2 flop per FMA) */
 int tc_measure_fma_peak(int precision, double* tflops);
-/* duration in ms of each kernel stage of the last tc_eval (CUDA events on the eval stream):
- * [0] plan+FK, [1] broadphase+narrowphase, [2] EPA, [3] sort+gradients+rows, [4] total */
-int tc_result_stage_ms(const tc_result* res, float ms[5]);
+/* duration in ms of each stage of the last tc_eval (CUDA events on the eval stream):
+ * [0] plan+FK, [1] broadphase+narrowphase, [2] deep-EPA re-runs, [3] finalise+sort+gradients(+cost), [4] total,
+ * [5] the GJK + EPA kernels, [6] broadphase (count, scan, fill), [7] = [0], [8] GJK kernel, [9] EPA kernel */
+int tc_result_stage_ms(const tc_result* res, float ms[10]);
+/* kernels of this library launched by the last tc_eval (+ row assembly when requested), and calls into
+ * CUDA-toolkit library code (cub radix sort of the contact keys) */
+int tc_result_launches(const tc_result* res, int32_t* own_kernels, int32_t* library_calls);
 
 #ifdef __cplusplus
 }

@@ -539,7 +539,7 @@ inline EpaResult epa(const Placed& A, const Placed& B, const Simplex& start)
     {
       if (!f.alive || f.d == DBL_MAX)
         continue;
-      if (dot(f.n, x.w - P[static_cast<std::size_t>(f.v[0])].w) > 1e-14 * std::max(scale, 1e-3))
+      if (dot(f.n, x.w) - f.d > 1e-14 * std::max(scale, 1e-3))
       {
         f.alive = false;
         for (int e = 0; e < 3; ++e)

@@ -57,21 +57,21 @@ def test_swept_sphere_closed_form(oracle):
         assert abs(ct["cc_time"][0] - (cb[0] + 1.5) / 3.0) <= 1e-6
 
 
-@pytest.mark.parametrize("evaluator", [capi.EVAL_DISCRETE, capi.EVAL_LVS_CONTINUOUS])
+@pytest.mark.parametrize("evaluator", [capi.EVAL_DISCRETE, capi.EVAL_LVS_DISCRETE])
 def test_gradient_rows_finite_difference(oracle, evaluator):
     """executable form of the reference's Debug check (collision_terms.cpp:295-309): analytic rows vs central
     differences of the signed distance of the same contact"""
     s = helpers.load_scene("arm_around_table")
     so = oracle.scene(s, 0.025, 20.0, 0.01)
-    q = s["seed_traj"][1:3].copy()[None]
+    q = s["seed_traj"][2:4].copy()[None]
     if evaluator == capi.EVAL_DISCRETE:
         q = q[:, :1]
-    r = oracle.eval(so, q, evaluator, lvs=10.0)
+    r = oracle.eval(so, q, evaluator, lvs=0.25)
     c = r.contacts()
     rows = r.rows()
     keys = helpers.contact_keys(c)
-    # GJK-only (separated) contacts with a single moving block: d(q) is smooth there
-    pick = [i for i in range(len(c)) if not (c["flags"][i] & capi.FLAG_EPA)][:4]
+    # separated (GJK) contacts first, then penetrating ones: the signed distance is smooth in both regimes
+    pick = ([i for i in range(len(c)) if not (c["flags"][i] & capi.FLAG_EPA)] + list(range(len(c))))[:4]
     assert pick
     h = 1e-6
     for i in pick:
@@ -83,9 +83,12 @@ def test_gradient_rows_finite_difference(oracle, evaluator):
             for sgn in (1, -1):
                 qq = q.copy().reshape(-1)
                 qq[col] += sgn * h
-                rr = oracle.eval(so, qq.reshape(q.shape), evaluator, lvs=10.0, want=capi.WANT_CONTACTS)
+                rr = oracle.eval(so, qq.reshape(q.shape), evaluator, lvs=0.25, want=capi.WANT_CONTACTS)
                 cc = rr.contacts()
                 kk = helpers.contact_keys(cc)
                 d.append(cc["distance"][kk.index(keys[i])])
             num[k] = -(d[0] - d[1]) / (2 * h)  # row = -d(distance)/dq
-        assert np.abs(num - val).max() <= 2e-3 * max(1.0, np.abs(val).max()), (i, num, val)
+        # (the swept-shape rows of the cast evaluators are trajopt's cc_time-weighted approximation, not an
+        # exact derivative, so they are not checked this way)
+        tol = 2e-3
+        assert np.abs(num - val).max() <= tol * max(1.0, np.abs(val).max()), (i, num, val)

@@ -314,9 +314,19 @@ class CudaLib(Lib):
         self.check(self.dll.tc_result_sync(result.handle))
 
     def stage_ms(self, result):
-        ms = (C.c_float * 5)()
+        ms = (C.c_float * 10)()
         self.check(self.dll.tc_result_stage_ms(result.handle, ms))
         return list(ms)
+
+    def build_rows_device(self, result):
+        """assemble the rows on the device, leave them there; returns nnz"""
+        self.check(self.dll.tc_result_rows_device(result.handle, None, None, None, None, None, None))
+        return result.counts()["nnz"]
+
+    def launches(self, result):
+        a, b = C.c_int32(), C.c_int32()
+        self.check(self.dll.tc_result_launches(result.handle, C.byref(a), C.byref(b)))
+        return a.value, b.value
 
     def measure_fma_peak(self, precision=PRECISION_F64):
         v = C.c_double()

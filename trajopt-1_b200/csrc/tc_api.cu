@@ -59,18 +59,20 @@ struct tc_result
   Counters* h_counters{ nullptr };  // pinned
   Counters* d_counters{ nullptr };
   tc_counts counts{};
-  cudaEvent_t ev[5]{};
-  float stage_ms[5]{};
+  cudaEvent_t ev[7]{};
+  float stage_ms[10]{};
+  int own_launches{ 0 }, lib_launches{ 0 };
   // arenas
   DevBuf<double> q;
   DevBuf<int32_t> term_t_d, term_cnt, term_states, term_units, state_base, unit_base, unit_term;
   DevBuf<uint8_t> term_fixed_d, term_interp;
   DevBuf<double> poses, aabb;
-  DevBuf<int32_t> sp_count, sp_offset, sp_cursor, items, deep_items, idx, idx_alt, ghas;
+  DevBuf<int32_t> sp_count, sp_offset, sp_cursor, items, deep_items, idx, idx_alt, ghas, epa_cursor, epa_unit, epa_n;
+  DevBuf<double> epa_simplex;
   DevBuf<RawContact> raw;
   DevBuf<unsigned long long> keys, keys_alt;
   DevBuf<tc_contact> contacts_tmp, contacts;
-  DevBuf<double> xf_tmp, xf, grad;
+  DevBuf<double> xf, grad;
   DevBuf<long long> term_ptr, row_ptr, term_row_base;
   DevBuf<tc_gradient> grec;
   DevBuf<unsigned char> sort_temp, deep_scratch;
@@ -214,8 +216,9 @@ int runEval(tc_scene* scene, const tc_eval_desc* desc, const double* q, int32_t 
   w.cast = (desc->evaluator == TC_EVAL_CONTINUOUS || desc->evaluator == TC_EVAL_LVS_CONTINUOUS) ? 1 : 0;
   w.single_sweep = (desc->evaluator == TC_EVAL_CONTINUOUS && desc->stack == TC_STACK_IFOPT) ? 1 : 0;
   w.counters = r->d_counters;
-  for (int i = 0; i < 5; ++i)
+  for (int i = 0; i < 10; ++i)
     r->stage_ms[i] = 0;
+  r->own_launches = r->lib_launches = 0;
   TC_CUDA(cudaEventRecord(r->ev[0], st));
   TC_CUDA(cudaMemsetAsync(r->d_counters, 0, sizeof(Counters), st));
   if (n_terms == 0)
@@ -223,7 +226,7 @@ int runEval(tc_scene* scene, const tc_eval_desc* desc, const double* q, int32_t 
     TC_RESERVE(r->term_ptr, 1);
     TC_CUDA(cudaMemsetAsync(r->term_ptr.p, 0, sizeof(long long), st));
     w.term_ptr = r->term_ptr.p;
-    for (int i = 1; i < 5; ++i)
+    for (int i = 1; i < 7; ++i)
       TC_CUDA(cudaEventRecord(r->ev[i], st));
     r->pending = true;
     return TC_OK;
@@ -255,6 +258,7 @@ int runEval(tc_scene* scene, const tc_eval_desc* desc, const double* q, int32_t 
   w.term_cnt = r->term_cnt.p, w.term_states = r->term_states.p, w.term_units = r->term_units.p;
   w.term_interp = r->term_interp.p, w.state_base = r->state_base.p, w.unit_base = r->unit_base.p;
   TC_CUDA(launchPlan(v, w, st));
+  r->own_launches += 2;
   TC_TRY(readCounters(r));
   w.n_states = r->h_counters->n_states;
   w.n_units = r->h_counters->n_units;
@@ -270,6 +274,7 @@ int runEval(tc_scene* scene, const tc_eval_desc* desc, const double* q, int32_t 
   TC_CUDA(launchFk(v, w, st));
   TC_CUDA(cudaEventRecord(r->ev[1], st));
   TC_CUDA(launchBroadCount(v, w, st));
+  r->own_launches += 4;
   TC_TRY(readCounters(r));
   w.n_items_padded = r->h_counters->n_items_padded;
   const long long n_items = r->h_counters->n_items;
@@ -277,11 +282,23 @@ int runEval(tc_scene* scene, const tc_eval_desc* desc, const double* q, int32_t 
   TC_RESERVE(r->items, w.n_items_padded);
   TC_RESERVE(r->raw, n_items);
   TC_RESERVE(r->deep_items, 2 * n_items);
+  TC_RESERVE(r->epa_cursor, hs.spairs.size());
+  TC_RESERVE(r->epa_unit, w.n_items_padded);
+  TC_RESERVE(r->epa_n, w.n_items_padded);
+  TC_RESERVE(r->epa_simplex, 24 * static_cast<size_t>(w.n_items_padded));
   w.items = r->items.p, w.raw = r->raw.p, w.deep_items = r->deep_items.p;
+  w.epa_cursor = r->epa_cursor.p, w.epa_unit = r->epa_unit.p, w.epa_n = r->epa_n.p, w.epa_simplex = r->epa_simplex.p;
   if (w.n_items_padded > 0)
   {
     TC_CUDA(launchBroadFill(v, w, st));
-    TC_CUDA(launchNarrow(v, w, desc->precision, st));
+    TC_CUDA(cudaEventRecord(r->ev[5], st));
+    TC_CUDA(launchNarrow(v, w, desc->precision, st, r->ev[6]));
+    r->own_launches += 3;
+  }
+  else
+  {
+    TC_CUDA(cudaEventRecord(r->ev[5], st));
+    TC_CUDA(cudaEventRecord(r->ev[6], st));
   }
   TC_CUDA(cudaEventRecord(r->ev[2], st));
   TC_TRY(readCounters(r));
@@ -292,18 +309,18 @@ int runEval(tc_scene* scene, const tc_eval_desc* desc, const double* q, int32_t 
     const size_t per = deepScratchBytesPerThread(desc->precision);
     TC_RESERVE(r->deep_scratch, per * n_threads);
     TC_CUDA(launchNarrowDeep(v, w, desc->precision, n_deep, r->deep_scratch.p, per, n_threads, st));
+    r->own_launches += 1;
     TC_TRY(readCounters(r));
   }
   TC_CUDA(cudaEventRecord(r->ev[3], st));
   w.n_raw = r->h_counters->n_raw;
   // ---- contact finalisation + sort ----
   TC_RESERVE(r->contacts_tmp, w.n_raw);
-  TC_RESERVE(r->xf_tmp, static_cast<size_t>(w.n_raw) * 48);
   TC_RESERVE(r->keys, w.n_raw);
   TC_RESERVE(r->keys_alt, w.n_raw);
   TC_RESERVE(r->idx, w.n_raw);
   TC_RESERVE(r->idx_alt, w.n_raw);
-  w.contacts_tmp = r->contacts_tmp.p, w.xf_tmp = r->xf_tmp.p;
+  w.contacts_tmp = r->contacts_tmp.p;
   w.keys = r->keys.p, w.keys_alt = r->keys_alt.p, w.idx = r->idx.p, w.idx_alt = r->idx_alt.p;
   if (w.n_raw > 0)
   {
@@ -312,14 +329,16 @@ int runEval(tc_scene* scene, const tc_eval_desc* desc, const double* q, int32_t 
     TC_CUDA(sortContacts(w, nullptr, temp_bytes, st));
     TC_RESERVE(r->sort_temp, temp_bytes);
     TC_CUDA(sortContacts(w, r->sort_temp.p, temp_bytes, st));
+    r->own_launches += 1;
+    r->lib_launches += 1;  // cub::DeviceRadixSort (several kernels of the CUDA toolkit's library)
     TC_TRY(readCounters(r));
   }
   w.n_contacts = r->h_counters->n_valid;
   TC_RESERVE(r->contacts, w.n_contacts);
-  TC_RESERVE(r->xf, static_cast<size_t>(w.n_contacts) * 48);
   TC_RESERVE(r->term_ptr, n_terms + 1);
-  w.contacts = r->contacts.p, w.xf = r->xf.p, w.term_ptr = r->term_ptr.p;
+  w.contacts = r->contacts.p, w.term_ptr = r->term_ptr.p;
   TC_CUDA(launchGather(v, w, st));
+  r->own_launches += (w.n_contacts > 0) ? 2 : 1;
   // ---- K4 ----
   if (desc->want & TC_WANT_GRADIENTS)
   {
@@ -328,6 +347,7 @@ int runEval(tc_scene* scene, const tc_eval_desc* desc, const double* q, int32_t 
     TC_RESERVE(r->ghas, w.n_contacts);
     w.grad = r->grad.p, w.grec = r->grec.p, w.ghas = r->ghas.p;
     TC_CUDA(launchGradients(v, w, st));
+    r->own_launches += (w.n_contacts > 0) ? 1 : 0;
     r->have_grad = true;
   }
   if (desc->want & TC_WANT_COST)
@@ -335,6 +355,7 @@ int runEval(tc_scene* scene, const tc_eval_desc* desc, const double* q, int32_t 
     TC_RESERVE(r->cost_term, n_terms);
     TC_RESERVE(r->cost_traj, B);
     TC_CUDA(launchCost(v, w, r->cost_term.p, r->cost_traj.p, st));
+    r->own_launches += 2;
     r->have_cost = true;
   }
   TC_CUDA(cudaEventRecord(r->ev[4], st));
@@ -375,6 +396,11 @@ int finishEval(tc_result* r)
   for (int i = 0; i < 4; ++i)
     cudaEventElapsedTime(&r->stage_ms[i], r->ev[i], r->ev[i + 1]);
   cudaEventElapsedTime(&r->stage_ms[4], r->ev[0], r->ev[4]);
+  cudaEventElapsedTime(&r->stage_ms[5], r->ev[5], r->ev[2]);
+  cudaEventElapsedTime(&r->stage_ms[6], r->ev[1], r->ev[5]);
+  cudaEventElapsedTime(&r->stage_ms[7], r->ev[0], r->ev[1]);
+  cudaEventElapsedTime(&r->stage_ms[8], r->ev[5], r->ev[6]);
+  cudaEventElapsedTime(&r->stage_ms[9], r->ev[6], r->ev[2]);
   r->valid = true;
   return TC_OK;
 }
@@ -410,6 +436,7 @@ int buildRows(tc_result* r)
   TC_CUDA(launchRowBase(r->scene->dview, w, r->term_row_base.p, r->stream));
   TC_CUDA(launchRows(r->scene->dview, w, r->term_row_base.p, r->col_idx.p, r->row_val.p, r->row_value.p,
                      r->row_coeff.p, r->row_margin.p, r->stream));
+  r->own_launches += 2;
   TC_TRY(readCounters(r));
   r->counts.nnz = r->h_counters->nnz;
   r->have_rows = true;
@@ -528,11 +555,13 @@ int tc_scene_create(const tc_scene_desc* desc, tc_scene** out)
   UP(path_ptr, h.path_ptr);
   UP(path_frames, h.path_frames);
   UP(link_frame, h.link_frame);
+  UP(frame_link, h.frame_link);
   UP(link_pose, h.link_pose);
   UP(shapes, h.shapes);
   UP(verts, h.verts);
   UP(verts_f32, vf);
   UP(active_shapes, h.active_shapes);
+  UP(active_shape_frame, h.active_shape_frame);
   UP(static_aabb, h.static_aabb);
   UP(pairs, h.pairs);
   UP(spairs, h.spairs);
@@ -591,7 +620,7 @@ int tc_result_create(tc_scene* scene, tc_result** out)
   cudaError_t e = cudaMallocHost(reinterpret_cast<void**>(&r->h_counters), sizeof(Counters));
   if (e == cudaSuccess)
     e = cudaMalloc(reinterpret_cast<void**>(&r->d_counters), sizeof(Counters));
-  for (int i = 0; i < 5 && e == cudaSuccess; ++i)
+  for (int i = 0; i < 7 && e == cudaSuccess; ++i)
     e = cudaEventCreate(&r->ev[i]);
   if (e != cudaSuccess)
   {
@@ -613,7 +642,7 @@ void tc_result_destroy(tc_result* r)
     cudaFreeHost(r->h_counters);
   if (r->d_counters)
     cudaFree(r->d_counters);
-  for (int i = 0; i < 5; ++i)
+  for (int i = 0; i < 7; ++i)
     if (r->ev[i])
       cudaEventDestroy(r->ev[i]);
   r->q.release(), r->term_t_d.release(), r->term_cnt.release(), r->term_states.release(), r->term_units.release();
@@ -621,10 +650,11 @@ void tc_result_destroy(tc_result* r)
   r->term_interp.release(), r->poses.release(), r->aabb.release(), r->sp_count.release(), r->sp_offset.release();
   r->sp_cursor.release(), r->items.release(), r->deep_items.release(), r->idx.release(), r->idx_alt.release();
   r->ghas.release(), r->raw.release(), r->keys.release(), r->keys_alt.release(), r->contacts_tmp.release();
-  r->contacts.release(), r->xf_tmp.release(), r->xf.release(), r->grad.release(), r->term_ptr.release();
+  r->contacts.release(), r->xf.release(), r->grad.release(), r->term_ptr.release();
   r->row_ptr.release(), r->term_row_base.release(), r->grec.release(), r->sort_temp.release();
   r->deep_scratch.release(), r->cost_term.release(), r->cost_traj.release(), r->col_idx.release();
   r->row_val.release(), r->row_value.release(), r->row_coeff.release(), r->row_margin.release();
+  r->epa_cursor.release(), r->epa_unit.release(), r->epa_n.release(), r->epa_simplex.release();
   r->sets.release(), r->set_count.release(), r->set_run.release(), r->set_values.release();
   r->set_coeffs.release(), r->set_jac.release();
   delete r;
@@ -669,9 +699,15 @@ int tc_result_contacts(const tc_result* res, tc_contact* dst, size_t cap)
 int tc_result_contact_transforms(const tc_result* res, double* dst, size_t cap)
 {
   TC_TRY(needValid(res));
-  const size_t n = std::min<size_t>(cap, static_cast<size_t>(res->w.n_contacts));
+  tc_result* r = const_cast<tc_result*>(res);
+  const size_t n = std::min<size_t>(cap, static_cast<size_t>(r->w.n_contacts));
   if (n)
-    TC_CUDA(cudaMemcpy(dst, res->w.xf, n * 48 * sizeof(double), cudaMemcpyDeviceToHost));
+  {
+    TC_RESERVE(r->xf, static_cast<size_t>(r->w.n_contacts) * 48);
+    TC_CUDA(launchTransforms(r->scene->dview, r->w, r->xf.p, r->stream));
+    TC_CUDA(cudaStreamSynchronize(r->stream));
+    TC_CUDA(cudaMemcpy(dst, r->xf.p, n * 48 * sizeof(double), cudaMemcpyDeviceToHost));
+  }
   return TC_OK;
 }
 
@@ -718,6 +754,27 @@ int tc_result_rows(const tc_result* res_c, int64_t* row_ptr, int32_t* col_idx, d
     TC_CUDA(cudaMemcpy(row_coeff, r->row_coeff.p, nc * sizeof(double), cudaMemcpyDeviceToHost));
     TC_CUDA(cudaMemcpy(row_margin, r->row_margin.p, nc * sizeof(double), cudaMemcpyDeviceToHost));
   }
+  return TC_OK;
+}
+
+int tc_result_rows_device(const tc_result* res_c, const int64_t** row_ptr, const int32_t** col_idx, const double** val,
+                          const double** row_value, const double** row_coeff, const double** row_margin)
+{
+  TC_TRY(needValid(res_c));
+  tc_result* r = const_cast<tc_result*>(res_c);
+  TC_TRY(buildRows(r));
+  if (row_ptr)
+    *row_ptr = reinterpret_cast<const int64_t*>(r->row_ptr.p);
+  if (col_idx)
+    *col_idx = r->col_idx.p;
+  if (val)
+    *val = r->row_val.p;
+  if (row_value)
+    *row_value = r->row_value.p;
+  if (row_coeff)
+    *row_coeff = r->row_coeff.p;
+  if (row_margin)
+    *row_margin = r->row_margin.p;
   return TC_OK;
 }
 
@@ -804,11 +861,21 @@ int tc_result_cost_device(const tc_result* res, const double** dev_ptr)
   return TC_OK;
 }
 
-int tc_result_stage_ms(const tc_result* res, float ms[5])
+int tc_result_stage_ms(const tc_result* res, float ms[10])
 {
   TC_TRY(needValid(res));
-  for (int i = 0; i < 5; ++i)
+  for (int i = 0; i < 10; ++i)
     ms[i] = res->stage_ms[i];
+  return TC_OK;
+}
+
+int tc_result_launches(const tc_result* res, int32_t* own_kernels, int32_t* library_calls)
+{
+  TC_TRY(needValid(res));
+  if (own_kernels)
+    *own_kernels = res->own_launches;
+  if (library_calls)
+    *library_calls = res->lib_launches;
   return TC_OK;
 }
 

@@ -58,6 +58,20 @@ TC_HD Pose<double> frameStep(const SceneView& v, const Pose<double>& parent, int
   return T;
 }
 
+// same with the joint value passed in (the FK kernel interpolates it on the fly)
+TC_HD Pose<double> frameStepQ(const SceneView& v, const Pose<double>& parent, int f, double qf)
+{
+  const Pose<double> origin = Pose<double>::from12(v.frame_origin + 12 * f);
+  Pose<double> T = compose(parent, origin);
+  const Vec3<double> ax(v.frame_axis[3 * f], v.frame_axis[3 * f + 1], v.frame_axis[3 * f + 2]);
+  const int type = v.frame_type[f];
+  if (type == TC_JOINT_REVOLUTE)
+    T = rotateAbout(T, ax, qf);
+  else if (type == TC_JOINT_PRISMATIC)
+    T.t = T.t + qf * T.rot(ax);
+  return T;
+}
+
 // world pose of frame lf at joint values q (walks the ancestor path)
 TC_HDN inline Pose<double> framePose(const SceneView& v, int lf, const double* q)
 {
@@ -200,8 +214,8 @@ struct UnitInfo
   bool f0, f1;   // vars0_fixed, vars1_fixed
 };
 
-// Builds the ContactResult of a raw hit.  xf = transform[0], cc_transform[0], transform[1], cc_transform[1]
-// (4 x 12 doubles).  pose0/pose1: link poses of both links at the unit's T0 / T1 state.
+// Builds the ContactResult of a raw hit.  xf (optional) = transform[0], cc_transform[0], transform[1],
+// cc_transform[1] (4 x 12 doubles).  pose0/pose1: link poses of both links at the unit's T0 / T1 state.
 // Returns false when the evaluators' filters drop the contact.
 TC_HDN inline bool finalizeContact(const SceneView& v, const EvalParams& ep, const RawContact& raw, const UnitInfo& u,
                                    const Pose<double> pose0[2], const Pose<double> pose1[2], tc_contact& c, double* xf)
@@ -272,10 +286,13 @@ TC_HDN inline bool finalizeContact(const SceneView& v, const EvalParams& ep, con
       }
     }
   }
-  pose0[0].to12(xf + 0);
-  cc_tf[0].to12(xf + 12);
-  pose0[1].to12(xf + 24);
-  cc_tf[1].to12(xf + 36);
+  if (xf)
+  {
+    pose0[0].to12(xf + 0);
+    cc_tf[0].to12(xf + 12);
+    pose0[1].to12(xf + 24);
+    cc_tf[1].to12(xf + 36);
+  }
   if (pr.zero_coeff)
     return false;
   if (ep.evaluator == TC_EVAL_DISCRETE)

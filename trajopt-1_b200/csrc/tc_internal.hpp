@@ -10,9 +10,10 @@
 //   unit_term    [n_units] i32
 //   sp_count/sp_offset/sp_cursor [n_shape_pairs(+1)]     survivors per shape pair, offsets padded to CHUNK
 //   items        [n_items_padded] i32                    unit index, bucketed per shape pair, -1 = padding
+//   epa_unit/epa_n/epa_simplex [n_items_padded]          GJK -> EPA hand-off (SoA), packed per shape pair
 //   raw          [<= n_items] RawContact (96 B)          narrow-phase hits in arrival order
 //   keys/idx     u64 / i32                               sort keys (term, link pair, substep, shape pair)
-//   contacts     [n_contacts] tc_contact (200 B), xf [n_contacts][4][12] f64, sorted
+//   contacts     [n_contacts] tc_contact (200 B), sorted (their transforms are records of `poses`)
 //   grad         [n_contacts][2][2][n_dof] f64, grec, ghas
 #pragma once
 #include <cuda_runtime.h>
@@ -80,11 +81,12 @@ struct Work
   int32_t *sp_count, *sp_offset, *sp_cursor;
   int32_t* items;
   RawContact* raw;
-  int32_t* deep_items;  // item slots whose EPA outgrew the thread-local polytope
+  int32_t* deep_items;  // (unit, shape pair) of items whose EPA outgrew the thread-local polytope
+  int32_t *epa_cursor, *epa_unit, *epa_n;  // GJK -> EPA hand-off, packed per shape pair at the bucket offsets
+  double* epa_simplex;                      // [24][n_items_padded]
   unsigned long long *keys, *keys_alt;
   int32_t *idx, *idx_alt;
   tc_contact *contacts_tmp, *contacts;
-  double *xf_tmp, *xf;
   long long* term_ptr;  // [n_terms+1]
   double* grad;
   tc_gradient* grec;
@@ -104,6 +106,7 @@ cudaError_t launchFinalize(const SceneView& v, const Work& w, cudaStream_t st);
 cudaError_t sortContacts(const Work& w, void* temp, size_t& temp_bytes, cudaStream_t st);  // result in *_alt
 cudaError_t launchGather(const SceneView& v, const Work& w, cudaStream_t st);
 cudaError_t launchGradients(const SceneView& v, const Work& w, cudaStream_t st);
+cudaError_t launchTransforms(const SceneView& v, const Work& w, double* xf, cudaStream_t st);
 cudaError_t launchRowBase(const SceneView& v, const Work& w, long long* term_row_base, cudaStream_t st);
 cudaError_t launchRows(const SceneView& v, const Work& w, long long* term_row_base, int32_t* col_idx, double* val,
                        double* row_value, double* row_coeff, double* row_margin, cudaStream_t st);
@@ -111,7 +114,7 @@ cudaError_t launchCost(const SceneView& v, const Work& w, double* cost_term, dou
 cudaError_t launchSets(const SceneView& v, const Work& w, int max_num_cnt, tc_set* sets, int32_t* set_count,
                        int32_t* set_run, double* values, double* coeffs, double* jac, cudaStream_t st);
 // ---- launchers (tc_narrow.cu) ----
-cudaError_t launchNarrow(const SceneView& v, const Work& w, int precision, cudaStream_t st);
+cudaError_t launchNarrow(const SceneView& v, const Work& w, int precision, cudaStream_t st, cudaEvent_t mid);
 cudaError_t launchNarrowDeep(const SceneView& v, const Work& w, int precision, long long n_deep, void* scratch,
                              size_t scratch_bytes_per_thread, int n_threads, cudaStream_t st);
 size_t deepScratchBytesPerThread(int precision);

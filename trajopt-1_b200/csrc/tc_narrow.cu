@@ -157,14 +157,11 @@ __device__ __forceinline__ void addStats(const Work& w, long long gjk, long long
   }
 }
 
+// shape pair of a chunk + TMA staging of its two hulls into shared memory
 template <class R>
-__global__ void __launch_bounds__(CHUNK) k_narrow(SceneView v, Work w)
+__device__ __forceinline__ int stageChunk(const SceneView& v, const Work& w, int item0, Vtx<R>* sv, uint64_t* bar,
+                                          int* s_sp)
 {
-  extern __shared__ __align__(16) unsigned char smem_raw[];
-  __shared__ __align__(8) uint64_t bar;
-  __shared__ int s_sp;
-  Vtx<R>* sv = reinterpret_cast<Vtx<R>*>(smem_raw);
-  const int item0 = blockIdx.x * CHUNK;
   if (threadIdx.x == 0)
   {
     // bucket of this chunk: last shape pair whose (padded) offset is <= item0
@@ -177,44 +174,140 @@ __global__ void __launch_bounds__(CHUNK) k_narrow(SceneView v, Work w)
       else
         hi = mid;
     }
-    s_sp = lo;
-    mbarInit(&bar, 1);
+    *s_sp = lo;
+    mbarInit(bar, 1);
   }
   __syncthreads();
-  const int sp = s_sp;
+  return *s_sp;
+}
+
+template <class R>
+__device__ __forceinline__ void stageHulls(const SceneView& v, const ShapeD& A, const ShapeD& B, Vtx<R>* sv,
+                                           uint64_t* bar)
+{
+  const int na = A.vert_cnt, nb = B.vert_cnt;
+  if (na + nb == 0)
+    return;
+  if (threadIdx.x == 0)
+  {
+    const uint32_t ba = static_cast<uint32_t>(na * sizeof(Vtx<R>)), bb = static_cast<uint32_t>(nb * sizeof(Vtx<R>));
+    mbarExpectTx(bar, ba + bb);
+    if (na)
+      bulkCopyG2S(sv, sceneVerts<R>(v) + A.vert_off, ba, bar);
+    if (nb)
+      bulkCopyG2S(sv + na, sceneVerts<R>(v) + B.vert_off, bb, bar);
+  }
+  mbarWait(bar, 0);
+}
+
+// K3a: GJK for every bucketed item.  Separated pairs are finished here; touching / penetrating pairs hand
+// their simplex to the EPA stage through a per-shape-pair packed arena (SoA, 24 doubles per item).
+template <class R>
+__global__ void __launch_bounds__(CHUNK) k_gjk(SceneView v, Work w)
+{
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  __shared__ __align__(8) uint64_t bar;
+  __shared__ int s_sp;
+  Vtx<R>* sv = reinterpret_cast<Vtx<R>*>(smem_raw);
+  const int item0 = blockIdx.x * CHUNK;
+  const int sp = stageChunk<R>(v, w, item0, sv, &bar, &s_sp);
   const ShapePairD spd = v.spairs[sp];
   const PairD pr = v.pairs[spd.pair];
   const ShapeD& A = v.shapes[spd.sa];
   const ShapeD& B = v.shapes[spd.sb];
-  const int na = A.vert_cnt, nb = B.vert_cnt;
-  if (na + nb > 0)
-  {
-    if (threadIdx.x == 0)
-    {
-      const uint32_t ba = static_cast<uint32_t>(na * sizeof(Vtx<R>)), bb = static_cast<uint32_t>(nb * sizeof(Vtx<R>));
-      mbarExpectTx(&bar, ba + bb);
-      if (na)
-        bulkCopyG2S(sv, sceneVerts<R>(v) + A.vert_off, ba, &bar);
-      if (nb)
-        bulkCopyG2S(sv + na, sceneVerts<R>(v) + B.vert_off, bb, &bar);
-    }
-    mbarWait(&bar, 0);
-  }
+  stageHulls<R>(v, A, B, sv, &bar);
   const int u = w.items[item0 + threadIdx.x];
   DistOut<R> d;
-  d.status = ND_NONE;
-  d.gjk_iters = 0, d.epa_iters = 0, d.scanned = 0;
-  d.used_epa = false;
-  d.converged = true;
+  clearDist(d);
+  Simplex<R> S;
+  S.n = 0;
   if (u >= 0)
   {
     Placed<R> PA, PB;
-    placeItem<R>(v, w, u, spd, pr, A, B, sv, sv + na, PA, PB);
-    Vec3<R> e_pw[EPA_FAST_VERTS], e_pa[EPA_FAST_VERTS], e_fn[EPA_FAST_FACES];
-    R e_fd[EPA_FAST_FACES];
-    int e_fv[EPA_FAST_FACES], e_edges[EPA_FAST_FACES];
-    EpaStore<R> store{ e_pw, e_pa, e_fn, e_fd, e_fv, e_edges, EPA_FAST_VERTS, EPA_FAST_FACES };
-    d = signedDistance<R>(PA, static_cast<R>(A.brad), PB, static_cast<R>(B.brad), static_cast<R>(pr.thr), store);
+    placeItem<R>(v, w, u, spd, pr, A, B, sv, sv + A.vert_cnt, PA, PB);
+    distanceGjk<R>(PA, PB, static_cast<R>(pr.thr), S, d);
+  }
+  storeHit<R>(w, d, u, sp, d.status == ND_CONTACT);
+  {
+    const bool need = d.status == ND_NEED_EPA;
+    const unsigned m = __ballot_sync(0xffffffffu, need);
+    if (m)
+    {
+      const unsigned lane = threadIdx.x & 31;
+      const int leader = __ffs(m) - 1;
+      int base = 0;
+      if (lane == leader)
+        base = atomicAdd(&w.epa_cursor[sp], __popc(m));
+      base = __shfl_sync(0xffffffffu, base, leader);
+      if (need)
+      {
+        const size_t slot = static_cast<size_t>(w.sp_offset[sp]) + base + __popc(m & ((1u << lane) - 1u));
+        const size_t stride = static_cast<size_t>(w.n_items_padded);
+        w.epa_unit[slot] = u;
+        w.epa_n[slot] = S.n | (d.converged ? 0 : 8);
+        double* dst = w.epa_simplex + slot;
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+        {
+          dst[(6 * i + 0) * stride] = S.w[i].x, dst[(6 * i + 1) * stride] = S.w[i].y, dst[(6 * i + 2) * stride] = S.w[i].z;
+          dst[(6 * i + 3) * stride] = S.a[i].x, dst[(6 * i + 4) * stride] = S.a[i].y, dst[(6 * i + 5) * stride] = S.a[i].z;
+        }
+      }
+    }
+  }
+  addStats(w, d.gjk_iters, d.scanned, 0, 0, (u >= 0 && d.status != ND_NEED_EPA && !d.converged) ? 1 : 0);
+}
+
+// K3b: EPA over the packed hand-off arena; every lane of a CTA (except in the last chunk of a bucket) is live.
+template <class R>
+__global__ void __launch_bounds__(CHUNK) k_epa(SceneView v, Work w)
+{
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  __shared__ __align__(8) uint64_t bar;
+  __shared__ int s_sp;
+  Vtx<R>* sv = reinterpret_cast<Vtx<R>*>(smem_raw);
+  const int item0 = blockIdx.x * CHUNK;
+  const int sp = stageChunk<R>(v, w, item0, sv, &bar, &s_sp);
+  const int live = w.epa_cursor[sp] - (item0 - w.sp_offset[sp]);  // hand-off items in this chunk
+  if (live <= 0)
+    return;
+  const ShapePairD spd = v.spairs[sp];
+  const PairD pr = v.pairs[spd.pair];
+  const ShapeD& A = v.shapes[spd.sa];
+  const ShapeD& B = v.shapes[spd.sb];
+  stageHulls<R>(v, A, B, sv, &bar);
+  DistOut<R> d;
+  clearDist(d);
+  int u = -1;
+  if (static_cast<int>(threadIdx.x) < live)
+  {
+    const size_t slot = static_cast<size_t>(item0) + threadIdx.x;
+    const size_t stride = static_cast<size_t>(w.n_items_padded);
+    u = w.epa_unit[slot];
+    const int nflag = w.epa_n[slot];
+    Simplex<R> S;
+    S.n = nflag & 7;
+    d.converged = (nflag & 8) == 0;
+    const double* src = w.epa_simplex + slot;
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+    {
+      S.w[i] = Vec3<R>(static_cast<R>(src[(6 * i + 0) * stride]), static_cast<R>(src[(6 * i + 1) * stride]),
+                       static_cast<R>(src[(6 * i + 2) * stride]));
+      S.a[i] = Vec3<R>(static_cast<R>(src[(6 * i + 3) * stride]), static_cast<R>(src[(6 * i + 4) * stride]),
+                       static_cast<R>(src[(6 * i + 5) * stride]));
+      S.lam[i] = 0;
+    }
+    Placed<R> PA, PB;
+    placeItem<R>(v, w, u, spd, pr, A, B, sv, sv + A.vert_cnt, PA, PB);
+    // thread-local polytope store; raw arrays so that nothing is zero-filled
+    R e_raw[(2 * EPA_FAST_VERTS + EPA_FAST_FACES) * 3 + EPA_FAST_FACES];
+    int e_int[2 * EPA_FAST_FACES];
+    Vec3<R>* e_pw = reinterpret_cast<Vec3<R>*>(e_raw);
+    EpaStore<R> store{ e_pw, e_pw + EPA_FAST_VERTS, e_pw + 2 * EPA_FAST_VERTS,
+                       e_raw + (2 * EPA_FAST_VERTS + EPA_FAST_FACES) * 3, e_int, e_int + EPA_FAST_FACES, EPA_FAST_VERTS,
+                       EPA_FAST_FACES };
+    distanceEpa<R, true>(PA, static_cast<R>(A.brad), PB, static_cast<R>(B.brad), static_cast<R>(pr.thr), S, store, d);
   }
   storeHit<R>(w, d, u, sp, d.status == ND_CONTACT);
   {
@@ -238,9 +331,8 @@ __global__ void __launch_bounds__(CHUNK) k_narrow(SceneView v, Work w)
       }
     }
   }
-  const bool counted = d.status != ND_EPA_OVERFLOW;  // deep items are counted when they are re-run
-  addStats(w, counted ? d.gjk_iters : 0, counted ? d.scanned : 0, (counted && d.used_epa) ? 1 : 0,
-           counted ? d.epa_iters : 0, (counted && u >= 0 && !d.converged) ? 1 : 0);
+  const bool counted = u >= 0 && d.status != ND_EPA_OVERFLOW;  // deep items are counted when they are re-run
+  addStats(w, 0, counted ? d.scanned : 0, counted ? 1 : 0, counted ? d.epa_iters : 0, (counted && !d.converged) ? 1 : 0);
 }
 
 // deep-expansion path: same arithmetic, polytope in global scratch, vertices read from global memory
@@ -278,10 +370,16 @@ __global__ void __launch_bounds__(64) k_narrow_deep(SceneView v, Work w, long lo
       Placed<R> PA, PB;
       placeItem<R>(v, w, u, spd, pr, A, B, sceneVerts<R>(v) + A.vert_off, sceneVerts<R>(v) + B.vert_off, PA, PB);
       EpaStore<R> store{ pw, pa, fn, fd, fv, edges, EPA_DEEP_VERTS, EPA_DEEP_FACES };
-      d = signedDistance<R>(PA, static_cast<R>(A.brad), PB, static_cast<R>(B.brad), static_cast<R>(pr.thr), store);
+      Simplex<R> S;
+      int gjk_scanned;
+      distanceGjk<R>(PA, PB, static_cast<R>(pr.thr), S, d);  // already counted by k_gjk
+      gjk_scanned = d.scanned;
+      if (d.status == ND_NEED_EPA)
+        distanceEpa<R, false>(PA, static_cast<R>(A.brad), PB, static_cast<R>(B.brad), static_cast<R>(pr.thr), S, store, d);
+      d.scanned -= gjk_scanned;
     }
     storeHit<R>(w, d, u, sp, d.status == ND_CONTACT);
-    addStats(w, d.gjk_iters, d.scanned, d.used_epa ? 1 : 0, d.epa_iters, (u >= 0 && !d.converged) ? 1 : 0);
+    addStats(w, 0, d.scanned, d.used_epa ? 1 : 0, d.epa_iters, (u >= 0 && !d.converged) ? 1 : 0);
   }
 }
 
@@ -315,24 +413,28 @@ size_t deepScratchBytesPerThread(int precision)
   return (b + 15) / 16 * 16;
 }
 
-cudaError_t launchNarrow(const SceneView& v, const Work& w, int precision, cudaStream_t st)
+template <class R>
+static cudaError_t launchNarrowT(const SceneView& v, const Work& w, cudaStream_t st, cudaEvent_t mid)
+{
+  const unsigned grid = static_cast<unsigned>(w.n_items_padded / CHUNK);
+  const size_t smem = static_cast<size_t>(2 * v.max_hull_verts) * sizeof(Vtx<R>) + 16;
+  cudaFuncSetAttribute(k_gjk<R>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem));
+  cudaFuncSetAttribute(k_epa<R>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem));
+  cudaError_t e = cudaMemsetAsync(w.epa_cursor, 0, sizeof(int32_t) * v.n_spairs, st);
+  if (e != cudaSuccess)
+    return e;
+  k_gjk<R><<<grid, CHUNK, smem, st>>>(v, w);
+  if (mid)
+    cudaEventRecord(mid, st);
+  k_epa<R><<<grid, CHUNK, smem, st>>>(v, w);
+  return cudaGetLastError();
+}
+
+cudaError_t launchNarrow(const SceneView& v, const Work& w, int precision, cudaStream_t st, cudaEvent_t mid)
 {
   if (w.n_items_padded <= 0)
     return cudaSuccess;
-  const unsigned grid = static_cast<unsigned>(w.n_items_padded / CHUNK);
-  if (precision == TC_PRECISION_F32)
-  {
-    const size_t smem = static_cast<size_t>(2 * v.max_hull_verts) * sizeof(Vtx<float>) + 16;
-    cudaFuncSetAttribute(k_narrow<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem));
-    k_narrow<float><<<grid, CHUNK, smem, st>>>(v, w);
-  }
-  else
-  {
-    const size_t smem = static_cast<size_t>(2 * v.max_hull_verts) * sizeof(Vtx<double>) + 16;
-    cudaFuncSetAttribute(k_narrow<double>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem));
-    k_narrow<double><<<grid, CHUNK, smem, st>>>(v, w);
-  }
-  return cudaGetLastError();
+  return precision == TC_PRECISION_F32 ? launchNarrowT<float>(v, w, st, mid) : launchNarrowT<double>(v, w, st, mid);
 }
 
 cudaError_t launchNarrowDeep(const SceneView& v, const Work& w, int precision, long long n_deep, void* scratch,

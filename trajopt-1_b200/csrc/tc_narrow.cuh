@@ -525,7 +525,7 @@ TC_HD Vec3<R> leastAxisCross(Vec3<R> e)
   return cross(e, ax);
 }
 
-template <class R>
+template <class R, bool MASK>
 TC_HDN EpaOut<R> epa(const Placed<R>& A, const Placed<R>& B, const Simplex<R>& start, R scale, EpaStore<R>& st,
                      int& scanned)
 {
@@ -638,11 +638,16 @@ TC_HDN EpaOut<R> epa(const Placed<R>& A, const Placed<R>& B, const Simplex<R>& s
   }
 
   int nf = 0;  // high-water mark of the face array
+  // MASK: the live-face set is also kept as a 64-bit register mask (max_faces <= 64), so dead slots cost no
+  // memory access and the first free slot is one ffs
+  unsigned long long alive = 0;
+  const R DEGENERATE = -lowestReal<R>();
   const Vec3<R> centroid = R(0.25) * (st.pw[0] + st.pw[1] + st.pw[2] + st.pw[3]);
-  // returns false on overflow
-  auto addFace = [&](int i, int j, int k, bool orient) -> bool {
-    Vec3<R> n = cross(st.pw[j] - st.pw[i], st.pw[k] - st.pw[i]);
-    if (orient && dot(n, st.pw[i] - centroid) < 0)
+  // adds a face in the first dead slot (else appends); returns the slot or -1 on overflow; d_out = plane distance
+  auto addFace = [&](int i, int j, int k, bool orient, R& d_out) -> int {
+    const Vec3<R> pi = st.pw[i];
+    Vec3<R> n = cross(st.pw[j] - pi, st.pw[k] - pi);
+    if (orient && dot(n, pi - centroid) < 0)
     {
       const int t = j;
       j = k;
@@ -650,48 +655,79 @@ TC_HDN EpaOut<R> epa(const Placed<R>& A, const Placed<R>& B, const Simplex<R>& s
       n = -n;
     }
     int slot = -1;
-    for (int f = 0; f < nf; ++f)
-      if (st.fv[f] < 0)
+    if (MASK)
+    {
+      const unsigned long long dead = ~alive & ((nf >= 64) ? ~0ull : ((1ull << nf) - 1ull));
+      if (dead)
       {
-        slot = f;
-        break;
+        // index of the lowest set bit, written so that it also compiles on the host
+        unsigned long long x = dead;
+        slot = 0;
+        while (!(x & 1ull))
+        {
+          x >>= 1;
+          ++slot;
+        }
       }
+    }
+    else
+    {
+      for (int f = 0; f < nf; ++f)
+        if (st.fv[f] < 0)
+        {
+          slot = f;
+          break;
+        }
+    }
     if (slot < 0)
     {
       if (nf >= st.max_faces)
-        return false;
+        return -1;
       slot = nf++;
     }
     const R nn = norm(n);
     st.fv[slot] = i | (j << 10) | (k << 20);
+    if (MASK)
+      alive |= 1ull << slot;
     if (nn > Tol<R>::tiny())
     {
-      st.fn[slot] = (R(1) / nn) * n;
-      st.fd[slot] = dot(st.fn[slot], st.pw[i]);
+      const Vec3<R> un = (R(1) / nn) * n;
+      st.fn[slot] = un;
+      d_out = dot(un, pi);
     }
     else
     {
       st.fn[slot] = Vec3<R>(0, 0, 0);
-      st.fd[slot] = -lowestReal<R>();  // degenerate sliver: never selected
+      d_out = DEGENERATE;  // degenerate sliver: never selected
     }
-    return true;
+    st.fd[slot] = d_out;
+    return slot;
   };
-  addFace(0, 1, 2, true);
-  addFace(0, 1, 3, true);
-  addFace(0, 2, 3, true);
-  addFace(1, 2, 3, true);
-
+  auto isAlive = [&](int f) -> bool { return MASK ? ((alive >> f) & 1ull) != 0 : st.fv[f] >= 0; };
+  // smallest plane distance, lowest slot on ties (= first minimum of a scan in slot order)
   int best = -1;
+  R bd = 0;
+  auto offer = [&](int f, R d) {
+    if (best < 0 || d < bd || (d == bd && f < best))
+    {
+      best = f;
+      bd = d;
+    }
+  };
+  {
+    R d;
+    int f = addFace(0, 1, 2, true, d);
+    offer(f, d);
+    f = addFace(0, 1, 3, true, d);
+    offer(f, d);
+    f = addFace(0, 2, 3, true, d);
+    offer(f, d);
+    f = addFace(1, 2, 3, true, d);
+    offer(f, d);
+  }
+
   for (r.iters = 1; r.iters <= EPA_MAX_ITERS; ++r.iters)
   {
-    best = -1;
-    R bd = 0;
-    for (int f = 0; f < nf; ++f)
-      if (st.fv[f] >= 0 && (best < 0 || st.fd[f] < bd))
-      {
-        best = f;
-        bd = st.fd[f];
-      }
     const Vec3<R> bn = st.fn[best];
     const Vec3<R> xa = A.support(bn, scanned), xb = B.support(-bn, scanned);
     const Vec3<R> xw = xa - xb;
@@ -707,85 +743,99 @@ TC_HDN EpaOut<R> epa(const Placed<R>& A, const Placed<R>& B, const Simplex<R>& s
       r.ok = false;
       return r;
     }
-    const int xi = np;
-    st.pw[np] = xw;
-    st.pa[np] = xa;
-    ++np;
-    // remove the faces that see x, collect the horizon
-    int ne = 0;
+    // one pass over the live faces: kill those that see x, collect the horizon, and track the closest
+    // survivor so that no separate "find the closest face" scan is needed
+    int ne = 0, sbest = -1;
+    R sbd = 0;
+    unsigned long long killed = 0;
     for (int f = 0; f < nf; ++f)
     {
-      const int fv = st.fv[f];
-      if (fv < 0 || st.fd[f] == -lowestReal<R>())
+      if (!isAlive(f))
         continue;
-      const int v0 = fv & 1023, v1 = (fv >> 10) & 1023, v2 = (fv >> 20) & 1023;
-      if (dot(st.fn[f], xw - st.pw[v0]) > vis_eps)
+      const R fd = st.fd[f];
+      bool visible = false;
+      if (fd != DEGENERATE)
+        visible = dot(st.fn[f], xw) - fd > vis_eps;
+      if (!visible)
       {
-        st.fv[f] = -1;
-        for (int e = 0; e < 3; ++e)
+        if (sbest < 0 || fd < sbd)
         {
-          const int ea = (e == 0) ? v0 : ((e == 1) ? v1 : v2);
-          const int eb = (e == 0) ? v1 : ((e == 1) ? v2 : v0);
-          const int twin = eb | (ea << 16);
-          int found = -1;
-          for (int q = 0; q < ne; ++q)
-            if (st.edges[q] == twin)
-            {
-              found = q;
-              break;
-            }
-          if (found >= 0)
+          sbest = f;
+          sbd = fd;
+        }
+        continue;
+      }
+      const int fv = st.fv[f];
+      const int v0 = fv & 1023, v1 = (fv >> 10) & 1023, v2 = (fv >> 20) & 1023;
+      if (MASK)
+        killed |= 1ull << f;
+      else
+        st.fv[f] = -1;
+      for (int e = 0; e < 3; ++e)
+      {
+        const int ea = (e == 0) ? v0 : ((e == 1) ? v1 : v2);
+        const int eb = (e == 0) ? v1 : ((e == 1) ? v2 : v0);
+        const int twin = eb | (ea << 16);
+        int found = -1;
+        for (int q = 0; q < ne; ++q)
+          if (st.edges[q] == twin)
           {
-            for (int q = found; q + 1 < ne; ++q)
-              st.edges[q] = st.edges[q + 1];
-            --ne;
+            found = q;
+            break;
           }
-          else
+        if (found >= 0)
+        {
+          for (int q = found; q + 1 < ne; ++q)
+            st.edges[q] = st.edges[q + 1];
+          --ne;
+        }
+        else
+        {
+          if (ne >= st.max_faces)
           {
-            if (ne >= st.max_faces)
-            {
-              r.ok = false;
-              return r;
-            }
-            st.edges[ne++] = ea | (eb << 16);
+            r.ok = false;
+            return r;
           }
+          st.edges[ne++] = ea | (eb << 16);
         }
       }
     }
     if (ne == 0)
-    {
-      // numerically x is not outside any face although the gap test said so: accept the current face
-      --np;
-      break;
-    }
+      break;  // numerically x is not outside any face although the gap test said so: accept the current face
+    alive &= ~killed;
+    const int xi = np;
+    st.pw[np] = xw;
+    st.pa[np] = xa;
+    ++np;
+    best = sbest;
+    bd = sbd;
     for (int q = 0; q < ne; ++q)
-      if (!addFace(st.edges[q] & 65535, st.edges[q] >> 16, xi, false))
+    {
+      R d;
+      const int e = st.edges[q];
+      const int f = addFace(e & 65535, e >> 16, xi, false, d);
+      if (f < 0)
       {
         r.ok = false;
         return r;
       }
+      offer(f, d);
+    }
   }
-  // `best` may have been killed in the last expansion only when the loop ran out of iterations with
-  // converged == false; it still holds the face data
-  const int fv = st.fv[best] >= 0 ? st.fv[best] : -1;
-  r.depth = st.fd[best];
+  r.depth = bd;
   r.normal = st.fn[best];
-  if (fv < 0)
-  {
-    r.converged = false;
-    r.pa = Vec3<R>();
-    r.pb = Vec3<R>();
-    return r;
-  }
   // Witness points: the face with the smallest PLANE distance may be one of several coplanar triangles of
   // a larger Minkowski face; the witness is taken on the triangle that is actually closest to the origin.
   int wf = best;
   R wbest = -lowestReal<R>(), la = 0, lb = 0, lc = 0;
   for (int f = 0; f < nf; ++f)
   {
-    const int gv = st.fv[f];
-    if (gv < 0 || st.fd[f] == -lowestReal<R>() || st.fd[f] > r.depth + eps_len)
+    if (!isAlive(f))
       continue;
+    const R fd = st.fd[f];
+    if (fd == DEGENERATE || fd > r.depth + eps_len)
+      continue;
+    const int gv = st.fv[f];
     R a0, a1, a2;
     const Vec3<R> q = closestTriangle(st.pw[gv & 1023], st.pw[(gv >> 10) & 1023], st.pw[(gv >> 20) & 1023], a0, a1, a2);
     const R q2 = norm2(q);
@@ -818,9 +868,10 @@ TC_HD R epaScale(const Placed<R>& A, R brad_a, const Placed<R>& B, R brad_b)
 
 enum
 {
-  ND_NONE = 0,        // farther apart than the threshold
+  ND_NONE = 0,         // farther apart than the threshold
   ND_CONTACT = 1,
-  ND_EPA_OVERFLOW = 2  // polytope store too small: item must be re-run on the deep-expansion path
+  ND_EPA_OVERFLOW = 2, // polytope store too small: item must be re-run on the deep-expansion path
+  ND_NEED_EPA = 3      // cores touch / overlap: the simplex goes to the EPA stage
 };
 
 template <class R>
@@ -834,54 +885,79 @@ struct DistOut
 };
 
 template <class R>
-TC_HDN DistOut<R> signedDistance(const Placed<R>& A, R brad_a, const Placed<R>& B, R brad_b, R threshold,
-                                 EpaStore<R>& store)
+TC_HD void clearDist(DistOut<R>& out)
 {
-  DistOut<R> out;
   out.status = ND_NONE;
   out.distance = 0;
   out.used_epa = false;
+  out.converged = true;
+  out.gjk_iters = 0;
   out.epa_iters = 0;
   out.scanned = 0;
+}
+
+template <class R>
+TC_HD void finishDist(const Placed<R>& A, const Placed<R>& B, R threshold, R d_core, Vec3<R> n, Vec3<R> pa, Vec3<R> pb,
+                      DistOut<R>& out)
+{
   const R ra = A.sh.coreRadius(), rb = B.sh.coreRadius();
-  Simplex<R> S;
-  const GjkOut<R> g = gjk(A, B, threshold + ra + rb, S, out.scanned);
-  out.gjk_iters = g.iters;
-  out.converged = g.converged;
-  if (g.separated_beyond)
-    return out;
-  Vec3<R> n, pa, pb;
-  R d_core;
-  if (!g.intersect)
-  {
-    d_core = g.dist;
-    n = (R(1) / g.dist) * (g.pb - g.pa);
-    pa = g.pa;
-    pb = g.pb;
-  }
-  else
-  {
-    const EpaOut<R> e = epa(A, B, S, epaScale(A, brad_a, B, brad_b), store, out.scanned);
-    out.used_epa = true;
-    out.epa_iters = e.iters;
-    if (!e.ok)
-    {
-      out.status = ND_EPA_OVERFLOW;
-      return out;
-    }
-    out.converged = out.converged && e.converged;
-    d_core = -e.depth;
-    n = e.normal;
-    pa = e.pa;
-    pb = e.pb;
-  }
   out.distance = d_core - ra - rb;
   if (out.distance > threshold)
-    return out;
+  {
+    out.status = ND_NONE;
+    return;
+  }
   out.status = ND_CONTACT;
   out.normal = n;
   out.pa = pa + ra * n;
   out.pb = pb - rb * n;
+}
+
+// stage 1: GJK.  ND_NONE / ND_CONTACT are final; ND_NEED_EPA leaves the simplex in S for stage 2
+template <class R>
+TC_HD void distanceGjk(const Placed<R>& A, const Placed<R>& B, R threshold, Simplex<R>& S, DistOut<R>& out)
+{
+  clearDist(out);
+  const R ra = A.sh.coreRadius(), rb = B.sh.coreRadius();
+  const GjkOut<R> g = gjk(A, B, threshold + ra + rb, S, out.scanned);
+  out.gjk_iters = g.iters;
+  out.converged = g.converged;
+  if (g.separated_beyond)
+    return;
+  if (g.intersect)
+  {
+    out.status = ND_NEED_EPA;
+    return;
+  }
+  finishDist(A, B, threshold, g.dist, (R(1) / g.dist) * (g.pb - g.pa), g.pa, g.pb, out);
+}
+
+// stage 2: EPA from the GJK simplex (out carries the stage-1 counters and convergence flag)
+template <class R, bool MASK>
+TC_HD void distanceEpa(const Placed<R>& A, R brad_a, const Placed<R>& B, R brad_b, R threshold, const Simplex<R>& S,
+                       EpaStore<R>& store, DistOut<R>& out)
+{
+  const EpaOut<R> e = epa<R, MASK>(A, B, S, epaScale(A, brad_a, B, brad_b), store, out.scanned);
+  out.used_epa = true;
+  out.epa_iters = e.iters;
+  if (!e.ok)
+  {
+    out.status = ND_EPA_OVERFLOW;
+    return;
+  }
+  out.converged = out.converged && e.converged;
+  finishDist(A, B, threshold, -e.depth, e.normal, e.pa, e.pb, out);
+}
+
+template <class R, bool MASK>
+TC_HDN DistOut<R> signedDistance(const Placed<R>& A, R brad_a, const Placed<R>& B, R brad_b, R threshold,
+                                 EpaStore<R>& store)
+{
+  DistOut<R> out;
+  Simplex<R> S;
+  distanceGjk(A, B, threshold, S, out);
+  if (out.status == ND_NEED_EPA)
+    distanceEpa<R, MASK>(A, brad_a, B, brad_b, threshold, S, store, out);
   return out;
 }
 }  // namespace tc

@@ -167,7 +167,7 @@ __global__ void k_unit_term(Work w)
 //   get_state_fn_ -> JointGroup::calcFwdKin (trajopt/src/collision_terms.cpp:401-417,656,880-885,1123-1124;
 //   discrete_collision_evaluators.cpp:57-73; continuous_collision_evaluators.cpp:65-81,285-301) and the
 //   sub-state interpolation LinSpaced(cnt, q0, q1) (collision_terms.cpp:846-848)
-// One thread per sub-state; frame poses live in a thread-local array (the tree has branches).
+// One thread per sub-state, frames visited in topological order.
 // ---------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(TPB) k_fk(SceneView v, Work w)
 {
@@ -179,42 +179,65 @@ __global__ void __launch_bounds__(TPB) k_fk(SceneView v, Work w)
   const int b = k / w.ep.terms_per_traj, ti = k % w.ep.terms_per_traj;
   const int n = v.n_dof;
   const double* q0 = w.q + (static_cast<size_t>(b) * w.ep.T + w.term_t[ti]) * n;
-  double q[64];
-  if (w.ep.evaluator == TC_EVAL_DISCRETE)
-  {
-    for (int j = 0; j < n; ++j)
-      q[j] = q0[j];
-  }
-  else
-  {
-    const int cnt = w.term_interp[k] ? w.term_cnt[k] : 2;
-    for (int j = 0; j < n; ++j)
-      q[j] = linspaced(cnt, q0[j], q0[n + j], i);
-  }
-  Pose<double> F[MAX_FRAMES];
+  const bool discrete = w.ep.evaluator == TC_EVAL_DISCRETE;
+  const int cnt = w.term_interp[k] ? w.term_cnt[k] : 2;
+  double* out = w.poses + static_cast<size_t>(s) * v.n_active * 12;
+  // Frames are visited in topological order with the previous frame's pose in registers; a branch reads
+  // its parent back from this thread's own records in the pose arena (no thread-local frame array).
   const Pose<double> base = Pose<double>::from12(v.base_pose);
+  Pose<double> cur = base;
   for (int f = 0; f < v.n_frames; ++f)
   {
     const int p = v.frame_parent[f];
-    Vec3<double> z;
-    F[f] = frameStep(v, p < 0 ? base : F[p], f, q, z);
-  }
-  double* out = w.poses + static_cast<size_t>(s) * v.n_active * 12;
-  for (int l = 0; l < v.n_active; ++l)
-    F[v.link_frame[l]].to12(out + 12 * l);
-  for (int a = 0; a < v.n_active_shapes; ++a)
-  {
-    const ShapeD& sh = v.shapes[v.active_shapes[a]];
-    const Pose<double>& T = F[v.link_frame[sh.link]];
-    const Vec3<double> c = T.apply(Vec3<double>(sh.aabb_c[0], sh.aabb_c[1], sh.aabb_c[2]));
-    double* dst = w.aabb + static_cast<size_t>(a) * 6 * w.n_states + s;
-#pragma unroll
-    for (int r = 0; r < 3; ++r)
+    Pose<double> parent;
+    if (p < 0)
+      parent = base;
+    else if (p == f - 1)
+      parent = cur;
+    else if (v.frame_link[p] >= 0)
+      parent = Pose<double>::from12(out + 12 * v.frame_link[p]);
+    else
     {
-      const double e =
-          fabs(T.r[3 * r + 0]) * sh.aabb_h[0] + fabs(T.r[3 * r + 1]) * sh.aabb_h[1] + fabs(T.r[3 * r + 2]) * sh.aabb_h[2];
-      dst[static_cast<size_t>(r) * w.n_states] = c.get(r) - e;
-      dst[static_cast<size_t>(3 + r) * w.n_states] = c.get(r) + e;
+      // a branching frame that carries no collision link: rebuild it from the root (rare)
+      parent = base;
+      for (int a = v.path_ptr[p]; a < v.path_ptr[p + 1]; ++a)
+      {
+        const int g = v.path_frames[a];
+        double qa = 0;
+        if (v.frame_type[g] != TC_JOINT_FIXED)
+        {
+          const int j = v.frame_dof[g];
+          qa = discrete ? q0[j] : linspaced(cnt, q0[j], q0[n + j], i);
+        }
+        parent = frameStepQ(v, parent, g, qa);
+      }
+    }
+    double qf = 0;
+    if (v.frame_type[f] != TC_JOINT_FIXED)
+    {
+      const int j = v.frame_dof[f];
+      qf = discrete ? q0[j] : linspaced(cnt, q0[j], q0[n + j], i);
+    }
+    cur = frameStepQ(v, parent, f, qf);
+    // every active link / active shape riding on this frame
+    for (int l = 0; l < v.n_active; ++l)
+      if (v.link_frame[l] == f)
+        cur.to12(out + 12 * l);
+    for (int a = 0; a < v.n_active_shapes; ++a)
+    {
+      if (v.active_shape_frame[a] != f)
+        continue;
+      const ShapeD& sh = v.shapes[v.active_shapes[a]];
+      const Vec3<double> c = cur.apply(Vec3<double>(sh.aabb_c[0], sh.aabb_c[1], sh.aabb_c[2]));
+      double* dst = w.aabb + static_cast<size_t>(a) * 6 * w.n_states + s;
+#pragma unroll
+      for (int r = 0; r < 3; ++r)
+      {
+        const double e = fabs(cur.r[3 * r + 0]) * sh.aabb_h[0] + fabs(cur.r[3 * r + 1]) * sh.aabb_h[1] +
+                         fabs(cur.r[3 * r + 2]) * sh.aabb_h[2];
+        dst[static_cast<size_t>(r) * w.n_states] = c.get(r) - e;
+        dst[static_cast<size_t>(3 + r) * w.n_states] = c.get(r) + e;
+      }
     }
   }
 }
@@ -381,7 +404,7 @@ __global__ void __launch_bounds__(TPB) k_finalize(SceneView v, Work w)
       }
     }
     tc_contact c;
-    valid = finalizeContact(v, w.ep, raw, ui, p0, p1, c, w.xf_tmp + static_cast<size_t>(i) * 48);
+    valid = finalizeContact(v, w.ep, raw, ui, p0, p1, c, nullptr);
     w.contacts_tmp[i] = c;
     unsigned long long key = ~0ull;
     if (valid)
@@ -395,20 +418,44 @@ __global__ void __launch_bounds__(TPB) k_finalize(SceneView v, Work w)
     atomicAdd(reinterpret_cast<unsigned long long*>(&w.counters->n_valid), static_cast<unsigned long long>(__popc(m)));
 }
 
-// sorted order -> final arrays, one thread per 8-byte word (25 words of tc_contact + 48 of transforms)
+// transform[i] / cc_transform[i] of a finalised contact are not stored: they are records of the pose arena
+// (ContactResult::transform, cc_transform; trajopt/src/collision_terms.cpp:215-223)
+__device__ __forceinline__ void contactTransforms(const SceneView& v, const Work& w, const tc_contact& c, double* xf)
+{
+  const bool lvs_discrete = w.ep.evaluator == TC_EVAL_LVS_DISCRETE;
+#pragma unroll
+  for (int i = 0; i < 2; ++i)
+  {
+    const int link = c.link_ids[i];
+    const bool active = link < v.n_active;
+    const double* t0 = active ? w.poses + (static_cast<size_t>(c.state) * v.n_active + link) * 12 : v.link_pose + 12 * link;
+    const double* t1 = (active && w.cast) ? t0 + static_cast<size_t>(v.n_active) * 12 : (lvs_discrete ? t0 : nullptr);
+    for (int k = 0; k < 12; ++k)
+    {
+      xf[24 * i + k] = t0[k];
+      xf[24 * i + 12 + k] = t1 ? t1[k] : ((k == 0 || k == 5 || k == 10) ? 1.0 : 0.0);
+    }
+  }
+}
+
+__global__ void __launch_bounds__(TPB) k_transforms(SceneView v, Work w, double* xf)
+{
+  const long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (i < w.n_contacts)
+    contactTransforms(v, w, w.contacts[i], xf + i * 48);
+}
+
+// sorted order -> final array, one thread per 8-byte word of tc_contact
 __global__ void __launch_bounds__(256) k_gather(Work w, const int32_t* idx)
 {
-  constexpr int WC = sizeof(tc_contact) / 8, WX = 48, WT = WC + WX;
+  constexpr int WC = sizeof(tc_contact) / 8;
   const long long g = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
-  const long long i = g / WT;
-  const int word = static_cast<int>(g % WT);
+  const long long i = g / WC;
+  const int word = static_cast<int>(g % WC);
   if (i >= w.n_contacts)
     return;
   const long long src = idx[i];
-  if (word < WC)
-    reinterpret_cast<double*>(w.contacts + i)[word] = reinterpret_cast<const double*>(w.contacts_tmp + src)[word];
-  else
-    w.xf[i * WX + (word - WC)] = w.xf_tmp[src * WX + (word - WC)];
+  reinterpret_cast<double*>(w.contacts + i)[word] = reinterpret_cast<const double*>(w.contacts_tmp + src)[word];
 }
 
 __global__ void k_term_ptr(Work w, const unsigned long long* keys)
@@ -457,9 +504,10 @@ __global__ void __launch_bounds__(TPB) k_grad(SceneView v, Work w)
   const int n = v.n_dof;
   const double* q0 = w.q + (static_cast<size_t>(c.traj) * w.ep.T + c.term) * n;
   const double* q1 = (w.ep.evaluator == TC_EVAL_DISCRETE) ? q0 : q0 + n;
-  double qt[64];
+  double qt[64], xf[48];
+  contactTransforms(v, w, c, xf);
   GradOut out;
-  contactGradient(v, w.ep, c, w.xf + i * 48, q0, q1, w.term_fixed[2 * ti] != 0, w.term_fixed[2 * ti + 1] != 0, qt,
+  contactGradient(v, w.ep, c, xf, q0, q1, w.term_fixed[2 * ti] != 0, w.term_fixed[2 * ti + 1] != 0, qt,
                   w.grad + static_cast<size_t>(i) * 4 * n, out);
   w.grec[i] = out.rec;
   w.ghas[i] = out.has;
@@ -891,10 +939,17 @@ cudaError_t launchGather(const SceneView& v, const Work& w, cudaStream_t st)
   (void)v;
   if (w.n_contacts > 0)
   {
-    const long long words = w.n_contacts * (static_cast<long long>(sizeof(tc_contact)) / 8 + 48);
+    const long long words = w.n_contacts * (static_cast<long long>(sizeof(tc_contact)) / 8);
     k_gather<<<gridFor(words, 256), 256, 0, st>>>(w, w.idx_alt);
   }
   k_term_ptr<<<gridFor(w.ep.n_terms + 1, 256), 256, 0, st>>>(w, w.keys_alt);
+  return cudaGetLastError();
+}
+
+cudaError_t launchTransforms(const SceneView& v, const Work& w, double* xf, cudaStream_t st)
+{
+  if (w.n_contacts > 0)
+    k_transforms<<<gridFor(w.n_contacts, TPB), TPB, 0, st>>>(v, w, xf);
   return cudaGetLastError();
 }
 

@@ -45,10 +45,12 @@ struct HostScene
   double base_pose[12];
   std::vector<int32_t> path_ptr, path_frames;    // ancestor frames (root first, incl. self) of every frame
   std::vector<int32_t> link_frame;
+  std::vector<int32_t> frame_link;               // first active link riding on a frame, -1 if none
   std::vector<double> link_pose;                 // [n_links][12] (static links)
   std::vector<ShapeD> shapes;
   std::vector<Vtx<double>> verts;                // link-frame hull vertices, 32 B each
   std::vector<int32_t> active_shapes;            // shape index of every active shape
+  std::vector<int32_t> active_shape_frame;       // frame its link rides on
   std::vector<double> static_aabb;               // [n_shapes][6] world lo/hi (static shapes only)
   std::vector<PairD> pairs;
   std::vector<ShapePairD> spairs;
@@ -66,11 +68,13 @@ struct SceneView
   double base_pose[12];
   const int32_t *path_ptr, *path_frames;
   const int32_t* link_frame;
+  const int32_t* frame_link;
   const double* link_pose;
   const ShapeD* shapes;
   const Vtx<double>* verts;
   const Vtx<float>* verts_f32;
   const int32_t* active_shapes;
+  const int32_t* active_shape_frame;
   const double* static_aabb;
   const PairD* pairs;
   const ShapePairD* spairs;
@@ -91,8 +95,10 @@ inline SceneView hostView(const HostScene& s)
     v.base_pose[i] = s.base_pose[i];
   v.path_ptr = s.path_ptr.data(), v.path_frames = s.path_frames.data();
   v.link_frame = s.link_frame.data(), v.link_pose = s.link_pose.data();
+  v.frame_link = s.frame_link.data();
   v.shapes = s.shapes.data(), v.verts = s.verts.data(), v.verts_f32 = nullptr;
   v.active_shapes = s.active_shapes.data(), v.static_aabb = s.static_aabb.data();
+  v.active_shape_frame = s.active_shape_frame.data();
   v.pairs = s.pairs.data(), v.spairs = s.spairs.data();
   v.partner_ptr = s.partner_ptr.data(), v.partner_sp = s.partner_sp.data();
   v.margin_buffer = s.margin_buffer;
@@ -148,6 +154,9 @@ inline void buildHostScene(const tc_scene_desc& d, HostScene& s)
     if (d.link_frame[l] >= d.n_frames)
       fail("link frame out of range");
   }
+  s.frame_link.assign(static_cast<size_t>(d.n_frames), -1);
+  for (int l = d.n_active_links - 1; l >= 0; --l)
+    s.frame_link[static_cast<size_t>(d.link_frame[l])] = l;
   s.n_shapes = d.n_shapes;
   s.margin_buffer = d.margin_buffer;
   std::vector<std::vector<int>> link_shapes(static_cast<size_t>(d.n_links));
@@ -233,6 +242,7 @@ inline void buildHostScene(const tc_scene_desc& d, HostScene& s)
     {
       sh.active_index = static_cast<int32_t>(s.active_shapes.size());
       s.active_shapes.push_back(i);
+      s.active_shape_frame.push_back(d.link_frame[sh.link]);
     }
     else
     {
