@@ -13,7 +13,7 @@ import os
 import numpy as np
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "csrc", "libtrajopt_cuda.so")
+LIB_PATH = os.environ.get("TC_LIB_PATH", os.path.join(HERE, "csrc", "libtrajopt_cuda.so"))
 
 # ---- enums (include/trajopt_cuda.h) ----
 TC_OK = 0

@@ -67,8 +67,8 @@ struct tc_result
   DevBuf<int32_t> term_t_d, term_cnt, term_states, term_units, state_base, unit_base, unit_term;
   DevBuf<uint8_t> term_fixed_d, term_interp;
   DevBuf<double> poses, aabb;
-  DevBuf<int32_t> sp_count, sp_offset, sp_cursor, items, deep_items, idx, idx_alt, ghas, epa_cursor, epa_unit, epa_n;
-  DevBuf<double> epa_simplex;
+  DevBuf<int32_t> sp_count, sp_offset, sp_cursor, items, deep_items, idx, idx_alt, ghas, epa_cursor, item_state;
+  DevBuf<EpaRec> epa_rec;
   DevBuf<RawContact> raw;
   DevBuf<unsigned long long> keys, keys_alt;
   DevBuf<tc_contact> contacts_tmp, contacts;
@@ -283,11 +283,10 @@ int runEval(tc_scene* scene, const tc_eval_desc* desc, const double* q, int32_t 
   TC_RESERVE(r->raw, n_items);
   TC_RESERVE(r->deep_items, 2 * n_items);
   TC_RESERVE(r->epa_cursor, hs.spairs.size());
-  TC_RESERVE(r->epa_unit, w.n_items_padded);
-  TC_RESERVE(r->epa_n, w.n_items_padded);
-  TC_RESERVE(r->epa_simplex, 24 * static_cast<size_t>(w.n_items_padded));
+  TC_RESERVE(r->item_state, w.n_items_padded);
+  TC_RESERVE(r->epa_rec, w.n_items_padded);
   w.items = r->items.p, w.raw = r->raw.p, w.deep_items = r->deep_items.p;
-  w.epa_cursor = r->epa_cursor.p, w.epa_unit = r->epa_unit.p, w.epa_n = r->epa_n.p, w.epa_simplex = r->epa_simplex.p;
+  w.epa_cursor = r->epa_cursor.p, w.item_state = r->item_state.p, w.epa_rec = r->epa_rec.p;
   if (w.n_items_padded > 0)
   {
     TC_CUDA(launchBroadFill(v, w, st));
@@ -654,7 +653,7 @@ void tc_result_destroy(tc_result* r)
   r->row_ptr.release(), r->term_row_base.release(), r->grec.release(), r->sort_temp.release();
   r->deep_scratch.release(), r->cost_term.release(), r->cost_traj.release(), r->col_idx.release();
   r->row_val.release(), r->row_value.release(), r->row_coeff.release(), r->row_margin.release();
-  r->epa_cursor.release(), r->epa_unit.release(), r->epa_n.release(), r->epa_simplex.release();
+  r->epa_cursor.release(), r->item_state.release(), r->epa_rec.release();
   r->sets.release(), r->set_count.release(), r->set_run.release(), r->set_values.release();
   r->set_coeffs.release(), r->set_jac.release();
   delete r;

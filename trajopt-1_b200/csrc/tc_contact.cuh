@@ -106,6 +106,32 @@ TC_HDN inline void pointGradient(const SceneView& v, int link, const double* q, 
   }
 }
 
+// two reference points on the same link at the same joint values in one walk of the chain (the T0 and T1
+// blocks of trajopt_common::getGradient(q0, q1, ...), collision_utils.cpp:215-216)
+TC_HDN inline void pointGradient2(const SceneView& v, int link, const double* q, Vec3<double> ref0, Vec3<double> ref1,
+                                  Vec3<double> tv, double* g0, double* g1)
+{
+  const int lf = v.link_frame[link];
+  for (int j = 0; j < v.n_dof; ++j)
+    g0[j] = g1[j] = 0.0;
+  const Vec3<double> pl = framePose(v, lf, q).t;
+  const Vec3<double> p0 = pl + ref0, p1 = pl + ref1;
+  Pose<double> T = Pose<double>::from12(v.base_pose);
+  for (int k = v.path_ptr[lf]; k < v.path_ptr[lf + 1]; ++k)
+  {
+    const int f = v.path_frames[k];
+    Vec3<double> z;
+    T = frameStep(v, T, f, q, z);
+    const int type = v.frame_type[f];
+    if (type == TC_JOINT_FIXED)
+      continue;
+    const Vec3<double> c0 = (type == TC_JOINT_REVOLUTE) ? cross(z, p0 - T.t) : z;
+    const Vec3<double> c1 = (type == TC_JOINT_REVOLUTE) ? cross(z, p1 - T.t) : z;
+    g0[v.frame_dof[f]] = c0.x * tv.x + c0.y * tv.y + c0.z * tv.z;
+    g1[v.frame_dof[f]] = c1.x * tv.x + c1.y * tv.y + c1.z * tv.z;
+  }
+}
+
 // GetAverageSupport: mean of all hull vertices within BULLET_EPSILON of the running maximum
 TC_HDN inline void averageSupport(const SceneView& v, const ShapeD& sh, Vec3<double> nl, double& outsupport,
                                   Vec3<double>& outpt)
@@ -384,8 +410,18 @@ TC_HDN inline void contactGradient(const SceneView& v, const EvalParams& ep, con
       else
         for (int j = 0; j < n; ++j)
           qt[j] = q0[j] + (q1[j] - q0[j]) * c.cc_time[i];
-      out.rec.scale0[i] = linkGradient(v, c, xf, i, qe, false, cc0, g0);
-      out.rec.scale1[i] = linkGradient(v, c, xf, i, qe, true, cc1, g1);
+      // both blocks share the joint values: one chain walk, two reference points
+      const bool cc = c.cc_type[i] != TC_CC_NONE;
+      out.rec.scale0[i] = cc ? (1 - c.cc_time[i]) : 1.0;
+      out.rec.scale1[i] = cc ? c.cc_time[i] : 1.0;
+      cc0 = cc1 = cc ? c.cc_type[i] : TC_CC_NONE;
+      const Pose<double> T0 = Pose<double>::from12(xf + 24 * i);
+      const Pose<double> T1 = cc ? Pose<double>::from12(xf + 24 * i + 12) : T0;
+      const Vec3<double> pl(c.nearest_points_local[i][0], c.nearest_points_local[i][1], c.nearest_points_local[i][2]);
+      Vec3<double> tv(c.normal[0], c.normal[1], c.normal[2]);
+      if (i == 0)
+        tv = -tv;
+      pointGradient2(v, c.link_ids[i], qe, T0.rot(pl), T1.rot(pl), tv, g0, g1);
       h0 = h1 = true;
     }
     out.rec.has_gradient[i] = (h0 || h1) ? 1 : 0;

@@ -10,7 +10,8 @@
 //   unit_term    [n_units] i32
 //   sp_count/sp_offset/sp_cursor [n_shape_pairs(+1)]     survivors per shape pair, offsets padded to CHUNK
 //   items        [n_items_padded] i32                    unit index, bucketed per shape pair, -1 = padding
-//   epa_unit/epa_n/epa_simplex [n_items_padded]          GJK -> EPA hand-off (SoA), packed per shape pair
+//   item_state   [n_items_padded] i32                    T0 sub-state of the item
+//   epa_rec      [n_items_padded] EpaRec (208 B)         GJK -> EPA hand-off, packed per shape pair
 //   raw          [<= n_items] RawContact (96 B)          narrow-phase hits in arrival order
 //   keys/idx     u64 / i32                               sort keys (term, link pair, substep, shape pair)
 //   contacts     [n_contacts] tc_contact (200 B), sorted (their transforms are records of `poses`)
@@ -26,9 +27,15 @@
 
 namespace tc
 {
-constexpr int CHUNK = 128;       // items per narrow-phase CTA (all of one shape pair)
+constexpr int CHUNK = 128;       // bucket padding unit = threads per narrow-phase CTA
+// chunks one narrow-phase CTA works through (hulls are staged once per run of one shape pair)
+constexpr int GJK_RUN_CHUNKS = 1, EPA_RUN_CHUNKS = 4;
 constexpr int MAX_FRAMES = 64;
-constexpr int EPA_FAST_VERTS = 24, EPA_FAST_FACES = 48;
+#ifndef TC_EPA_VERTS
+#define TC_EPA_VERTS 34
+#endif
+// thread-local polytope capacity (the live-face mask is 64 bits)
+constexpr int EPA_FAST_VERTS = TC_EPA_VERTS, EPA_FAST_FACES = (2 * TC_EPA_VERTS - 4 > 64) ? 64 : 2 * TC_EPA_VERTS - 4;
 constexpr int EPA_DEEP_VERTS = 4 + EPA_MAX_ITERS, EPA_DEEP_FACES = 8 + 2 * EPA_MAX_ITERS;
 
 struct Counters
@@ -64,6 +71,13 @@ struct DevBuf
   }
 };
 
+// GJK -> EPA hand-off record (208 B)
+struct EpaRec
+{
+  int32_t unit, state, nflag, pad;
+  double s[24];  // simplex: 4 x (w, a)
+};
+
 // device pointers of one evaluation handed to the kernels by value
 struct Work
 {
@@ -82,8 +96,9 @@ struct Work
   int32_t* items;
   RawContact* raw;
   int32_t* deep_items;  // (unit, shape pair) of items whose EPA outgrew the thread-local polytope
-  int32_t *epa_cursor, *epa_unit, *epa_n;  // GJK -> EPA hand-off, packed per shape pair at the bucket offsets
-  double* epa_simplex;                      // [24][n_items_padded]
+  int32_t* item_state;   // T0 sub-state of every item (parallel to items)
+  int32_t* epa_cursor;   // GJK -> EPA hand-off: records packed per shape pair at the bucket offsets
+  EpaRec* epa_rec;
   unsigned long long *keys, *keys_alt;
   int32_t *idx, *idx_alt;
   tc_contact *contacts_tmp, *contacts;

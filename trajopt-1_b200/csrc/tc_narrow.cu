@@ -7,6 +7,8 @@
 // (cp.async.bulk + mbarrier); every lane then runs its own GJK (+EPA) against the staged vertices, so
 // vertex reads are warp-wide broadcasts.  Hits are appended to the raw contact arena with one atomic
 // per warp (ballot + popc).
+#include <cstdlib>
+
 #include "tc_internal.hpp"
 
 namespace tc
@@ -67,14 +69,12 @@ __device__ __forceinline__ Pose<R> loadPose(const double* p)
   return Pose<R>::from12(p);
 }
 
-// builds the two placed shapes of item (unit u, shape pair sp)
+// builds the two placed shapes of an item (T0 sub-state s0, shape pair sp)
 template <class R>
-__device__ __forceinline__ void placeItem(const SceneView& v, const Work& w, int u, const ShapePairD& spd,
+__device__ __forceinline__ void placeItem(const SceneView& v, const Work& w, long long s0, const ShapePairD& spd,
                                           const PairD& pr, const ShapeD& A, const ShapeD& B, const Vtx<R>* va,
                                           const Vtx<R>* vb, Placed<R>& PA, Placed<R>& PB)
 {
-  const int k = w.unit_term[u];
-  const long long s0 = w.state_base[k] + (u - w.unit_base[k]);
   const double* pa = w.poses + (static_cast<size_t>(s0) * v.n_active + pr.a) * 12;
   PA.sh = makeCore<R>(A, va);
   PA.p0 = loadPose<R>(pa);
@@ -157,10 +157,18 @@ __device__ __forceinline__ void addStats(const Work& w, long long gjk, long long
   }
 }
 
-// shape pair of a chunk + TMA staging of its two hulls into shared memory
-template <class R>
-__device__ __forceinline__ int stageChunk(const SceneView& v, const Work& w, int item0, Vtx<R>* sv, uint64_t* bar,
-                                          int* s_sp)
+// ---------------------------------------------------------------------------------------------
+// Run = the part of ONE shape pair's bucket that falls into this CTA's range of chunks.  Per run the two
+// hulls are staged with TMA bulk copies; the lanes then work through the run's items with lane refill:
+// every trip of the loop is one GJK (or EPA) iteration for all busy lanes, a lane whose item finished
+// takes the next item of the run, so iteration-count variance between items does not idle lanes.
+// ---------------------------------------------------------------------------------------------
+struct RunInfo
+{
+  int sp, q0, q1;  // shape pair, item range [q0, q1) of the run (q1 = end of the CTA range or of the bucket)
+};
+
+__device__ __forceinline__ RunInfo findRun(const SceneView& v, const Work& w, int item0, int range_end, RunInfo* s_run)
 {
   if (threadIdx.x == 0)
   {
@@ -174,22 +182,27 @@ __device__ __forceinline__ int stageChunk(const SceneView& v, const Work& w, int
       else
         hi = mid;
     }
-    *s_sp = lo;
-    mbarInit(bar, 1);
+    const int bucket_end = w.sp_offset[lo] + (w.sp_count[lo] + CHUNK - 1) / CHUNK * CHUNK;
+    s_run->sp = lo;
+    s_run->q0 = item0;
+    s_run->q1 = bucket_end < range_end ? bucket_end : range_end;
   }
   __syncthreads();
-  return *s_sp;
+  const RunInfo r = *s_run;
+  return r;
 }
 
 template <class R>
 __device__ __forceinline__ void stageHulls(const SceneView& v, const ShapeD& A, const ShapeD& B, Vtx<R>* sv,
-                                           uint64_t* bar)
+                                           uint64_t* bar, uint32_t parity)
 {
   const int na = A.vert_cnt, nb = B.vert_cnt;
   if (na + nb == 0)
     return;
   if (threadIdx.x == 0)
   {
+    // the previous run's generic-proxy reads of this buffer are ordered before the async-proxy writes
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
     const uint32_t ba = static_cast<uint32_t>(na * sizeof(Vtx<R>)), bb = static_cast<uint32_t>(nb * sizeof(Vtx<R>));
     mbarExpectTx(bar, ba + bb);
     if (na)
@@ -197,144 +210,196 @@ __device__ __forceinline__ void stageHulls(const SceneView& v, const ShapeD& A, 
     if (nb)
       bulkCopyG2S(sv + na, sceneVerts<R>(v) + B.vert_off, bb, bar);
   }
-  mbarWait(bar, 0);
+  mbarWait(bar, parity);
 }
 
 // K3a: GJK for every bucketed item.  Separated pairs are finished here; touching / penetrating pairs hand
 // their simplex to the EPA stage through a per-shape-pair packed arena (SoA, 24 doubles per item).
-template <class R>
-__global__ void __launch_bounds__(CHUNK) k_gjk(SceneView v, Work w)
+template <class R, int MINB>
+__global__ void __launch_bounds__(CHUNK, MINB) k_gjk(SceneView v, Work w)
+#define RUN_CHUNKS GJK_RUN_CHUNKS
 {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   __shared__ __align__(8) uint64_t bar;
-  __shared__ int s_sp;
+  __shared__ RunInfo s_run;
   Vtx<R>* sv = reinterpret_cast<Vtx<R>*>(smem_raw);
-  const int item0 = blockIdx.x * CHUNK;
-  const int sp = stageChunk<R>(v, w, item0, sv, &bar, &s_sp);
-  const ShapePairD spd = v.spairs[sp];
-  const PairD pr = v.pairs[spd.pair];
-  const ShapeD& A = v.shapes[spd.sa];
-  const ShapeD& B = v.shapes[spd.sb];
-  stageHulls<R>(v, A, B, sv, &bar);
-  const int u = w.items[item0 + threadIdx.x];
-  DistOut<R> d;
-  clearDist(d);
-  Simplex<R> S;
-  S.n = 0;
-  if (u >= 0)
+  const int range_end = min(static_cast<long long>(blockIdx.x + 1) * RUN_CHUNKS * CHUNK, w.n_items_padded);
+  if (threadIdx.x == 0)
+    mbarInit(&bar, 1);
+  long long st_gjk = 0, st_scan = 0, st_unconv = 0;
+  uint32_t phase = 0;
+  for (int item0 = blockIdx.x * RUN_CHUNKS * CHUNK; item0 < range_end;)
   {
-    Placed<R> PA, PB;
-    placeItem<R>(v, w, u, spd, pr, A, B, sv, sv + A.vert_cnt, PA, PB);
-    distanceGjk<R>(PA, PB, static_cast<R>(pr.thr), S, d);
-  }
-  storeHit<R>(w, d, u, sp, d.status == ND_CONTACT);
-  {
-    const bool need = d.status == ND_NEED_EPA;
-    const unsigned m = __ballot_sync(0xffffffffu, need);
-    if (m)
+    const RunInfo run = findRun(v, w, item0, range_end, &s_run);
+    const int sp = run.sp;
+    const ShapePairD spd = v.spairs[sp];
+    const PairD pr = v.pairs[spd.pair];
+    const ShapeD& A = v.shapes[spd.sa];
+    const ShapeD& B = v.shapes[spd.sb];
+    const int valid_end = min(run.q1, w.sp_offset[sp] + w.sp_count[sp]);
+    if (A.vert_cnt + B.vert_cnt > 0)
     {
-      const unsigned lane = threadIdx.x & 31;
-      const int leader = __ffs(m) - 1;
-      int base = 0;
-      if (lane == leader)
-        base = atomicAdd(&w.epa_cursor[sp], __popc(m));
-      base = __shfl_sync(0xffffffffu, base, leader);
-      if (need)
+      stageHulls<R>(v, A, B, sv, &bar, phase & 1);
+      ++phase;
+    }
+    const R thr = static_cast<R>(pr.thr);
+    // lock-step rounds: in every round each lane takes one item and all lanes iterate together, so the lanes
+    // of a warp sit in the same simplex case most of the time
+    for (int base = run.q0; base < valid_end; base += CHUNK)
+    {
+      const int slot = base + threadIdx.x;
+      const bool live = slot < valid_end;
+      DistOut<R> d;
+      clearDist(d);
+      int u = -1;
+      Simplex<R> S;
+      S.n = 0;
+      if (live)
       {
-        const size_t slot = static_cast<size_t>(w.sp_offset[sp]) + base + __popc(m & ((1u << lane) - 1u));
-        const size_t stride = static_cast<size_t>(w.n_items_padded);
-        w.epa_unit[slot] = u;
-        w.epa_n[slot] = S.n | (d.converged ? 0 : 8);
-        double* dst = w.epa_simplex + slot;
-#pragma unroll
-        for (int i = 0; i < 4; ++i)
+        u = w.items[slot];
+        Placed<R> PA, PB;
+        placeItem<R>(v, w, w.item_state[slot], spd, pr, A, B, sv, sv + A.vert_cnt, PA, PB);
+        distanceGjk<R>(PA, PB, thr, S, d);
+        st_gjk += d.gjk_iters;
+        st_scan += d.scanned;
+        st_unconv += (d.status != ND_NEED_EPA && !d.converged) ? 1 : 0;
+      }
+      storeHit<R>(w, d, u, sp, d.status == ND_CONTACT);
+      const bool need = d.status == ND_NEED_EPA;
+      const unsigned m = __ballot_sync(0xffffffffu, need);
+      if (m)
+      {
+        const unsigned lane = threadIdx.x & 31;
+        const int leader = __ffs(m) - 1;
+        int cur = 0;
+        if (lane == leader)
+          cur = atomicAdd(&w.epa_cursor[sp], __popc(m));
+        cur = __shfl_sync(0xffffffffu, cur, leader);
+        if (need)
         {
-          dst[(6 * i + 0) * stride] = S.w[i].x, dst[(6 * i + 1) * stride] = S.w[i].y, dst[(6 * i + 2) * stride] = S.w[i].z;
-          dst[(6 * i + 3) * stride] = S.a[i].x, dst[(6 * i + 4) * stride] = S.a[i].y, dst[(6 * i + 5) * stride] = S.a[i].z;
+          EpaRec& rec = w.epa_rec[static_cast<size_t>(w.sp_offset[sp]) + cur + __popc(m & ((1u << lane) - 1u))];
+          rec.unit = u;
+          rec.state = w.item_state[slot];
+          rec.nflag = S.n | (d.converged ? 0 : 8);
+          rec.pad = 0;
+#pragma unroll
+          for (int i = 0; i < 4; ++i)
+          {
+            rec.s[6 * i + 0] = S.w[i].x, rec.s[6 * i + 1] = S.w[i].y, rec.s[6 * i + 2] = S.w[i].z;
+            rec.s[6 * i + 3] = S.a[i].x, rec.s[6 * i + 4] = S.a[i].y, rec.s[6 * i + 5] = S.a[i].z;
+          }
         }
       }
     }
+    __syncthreads();
+    item0 = run.q1;
   }
-  addStats(w, d.gjk_iters, d.scanned, 0, 0, (u >= 0 && d.status != ND_NEED_EPA && !d.converged) ? 1 : 0);
+  addStats(w, st_gjk, st_scan, 0, 0, st_unconv);
 }
 
-// K3b: EPA over the packed hand-off arena; every lane of a CTA (except in the last chunk of a bucket) is live.
-template <class R>
-__global__ void __launch_bounds__(CHUNK) k_epa(SceneView v, Work w)
+#undef RUN_CHUNKS
+#define RUN_CHUNKS EPA_RUN_CHUNKS
+// K3b: EPA over the packed hand-off arena, same run structure.
+template <class R, int MINB>
+__global__ void __launch_bounds__(CHUNK, MINB) k_epa(SceneView v, Work w)
 {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   __shared__ __align__(8) uint64_t bar;
-  __shared__ int s_sp;
+  __shared__ RunInfo s_run;
   Vtx<R>* sv = reinterpret_cast<Vtx<R>*>(smem_raw);
-  const int item0 = blockIdx.x * CHUNK;
-  const int sp = stageChunk<R>(v, w, item0, sv, &bar, &s_sp);
-  const int live = w.epa_cursor[sp] - (item0 - w.sp_offset[sp]);  // hand-off items in this chunk
-  if (live <= 0)
-    return;
-  const ShapePairD spd = v.spairs[sp];
-  const PairD pr = v.pairs[spd.pair];
-  const ShapeD& A = v.shapes[spd.sa];
-  const ShapeD& B = v.shapes[spd.sb];
-  stageHulls<R>(v, A, B, sv, &bar);
-  DistOut<R> d;
-  clearDist(d);
-  int u = -1;
-  if (static_cast<int>(threadIdx.x) < live)
+  const int range_end = min(static_cast<long long>(blockIdx.x + 1) * RUN_CHUNKS * CHUNK, w.n_items_padded);
+  if (threadIdx.x == 0)
+    mbarInit(&bar, 1);
+  // thread-local polytope store; raw arrays so that nothing is zero-filled
+  R e_raw[(2 * EPA_FAST_VERTS + EPA_FAST_FACES) * 3 + EPA_FAST_FACES];
+  int e_int[2 * EPA_FAST_FACES];
+  Vec3<R>* e_pw = reinterpret_cast<Vec3<R>*>(e_raw);
+  EpaStore<R> store{ e_pw, e_pw + EPA_FAST_VERTS, e_pw + 2 * EPA_FAST_VERTS,
+                     e_raw + (2 * EPA_FAST_VERTS + EPA_FAST_FACES) * 3, e_int, e_int + EPA_FAST_FACES, EPA_FAST_VERTS,
+                     EPA_FAST_FACES };
+  long long st_scan = 0, st_epa = 0, st_it = 0, st_unconv = 0;
+  uint32_t phase = 0;
+  for (int item0 = blockIdx.x * RUN_CHUNKS * CHUNK; item0 < range_end;)
   {
-    const size_t slot = static_cast<size_t>(item0) + threadIdx.x;
-    const size_t stride = static_cast<size_t>(w.n_items_padded);
-    u = w.epa_unit[slot];
-    const int nflag = w.epa_n[slot];
-    Simplex<R> S;
-    S.n = nflag & 7;
-    d.converged = (nflag & 8) == 0;
-    const double* src = w.epa_simplex + slot;
-#pragma unroll
-    for (int i = 0; i < 4; ++i)
+    const RunInfo run = findRun(v, w, item0, range_end, &s_run);
+    const int sp = run.sp;
+    const int valid_end = min(run.q1, w.sp_offset[sp] + w.epa_cursor[sp]);  // hand-off items of this run
+    if (valid_end <= run.q0)
     {
-      S.w[i] = Vec3<R>(static_cast<R>(src[(6 * i + 0) * stride]), static_cast<R>(src[(6 * i + 1) * stride]),
-                       static_cast<R>(src[(6 * i + 2) * stride]));
-      S.a[i] = Vec3<R>(static_cast<R>(src[(6 * i + 3) * stride]), static_cast<R>(src[(6 * i + 4) * stride]),
-                       static_cast<R>(src[(6 * i + 5) * stride]));
-      S.lam[i] = 0;
+      __syncthreads();
+      item0 = run.q1;
+      continue;
     }
-    Placed<R> PA, PB;
-    placeItem<R>(v, w, u, spd, pr, A, B, sv, sv + A.vert_cnt, PA, PB);
-    // thread-local polytope store; raw arrays so that nothing is zero-filled
-    R e_raw[(2 * EPA_FAST_VERTS + EPA_FAST_FACES) * 3 + EPA_FAST_FACES];
-    int e_int[2 * EPA_FAST_FACES];
-    Vec3<R>* e_pw = reinterpret_cast<Vec3<R>*>(e_raw);
-    EpaStore<R> store{ e_pw, e_pw + EPA_FAST_VERTS, e_pw + 2 * EPA_FAST_VERTS,
-                       e_raw + (2 * EPA_FAST_VERTS + EPA_FAST_FACES) * 3, e_int, e_int + EPA_FAST_FACES, EPA_FAST_VERTS,
-                       EPA_FAST_FACES };
-    distanceEpa<R, true>(PA, static_cast<R>(A.brad), PB, static_cast<R>(B.brad), static_cast<R>(pr.thr), S, store, d);
-  }
-  storeHit<R>(w, d, u, sp, d.status == ND_CONTACT);
-  {
-    // rare: polytope outgrew the thread-local store -> deep-expansion queue
-    const bool deep = d.status == ND_EPA_OVERFLOW;
-    const unsigned m = __ballot_sync(0xffffffffu, deep);
-    if (m)
+    const ShapePairD spd = v.spairs[sp];
+    const PairD pr = v.pairs[spd.pair];
+    const ShapeD& A = v.shapes[spd.sa];
+    const ShapeD& B = v.shapes[spd.sb];
+    if (A.vert_cnt + B.vert_cnt > 0)
     {
-      const unsigned lane = threadIdx.x & 31;
-      const int leader = __ffs(m) - 1;
-      unsigned long long base = 0;
-      if (lane == leader)
-        base = atomicAdd(reinterpret_cast<unsigned long long*>(&w.counters->n_deep),
-                         static_cast<unsigned long long>(__popc(m)));
-      base = __shfl_sync(0xffffffffu, base, leader);
-      if (deep)
+      stageHulls<R>(v, A, B, sv, &bar, phase & 1);
+      ++phase;
+    }
+    const R thr = static_cast<R>(pr.thr);
+    for (int base = run.q0; base < valid_end; base += CHUNK)
+    {
+      const int slot = base + threadIdx.x;
+      DistOut<R> d;
+      clearDist(d);
+      d.used_epa = true;
+      int u = -1;
+      if (slot < valid_end)
       {
-        const unsigned long long slot = base + __popc(m & ((1u << lane) - 1u));
-        w.deep_items[2 * slot] = u;
-        w.deep_items[2 * slot + 1] = sp;
+        const EpaRec& rec = w.epa_rec[slot];
+        u = rec.unit;
+        const int nflag = rec.nflag;
+        Simplex<R> S;
+        S.n = nflag & 7;
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+        {
+          S.w[i] = Vec3<R>(static_cast<R>(rec.s[6 * i + 0]), static_cast<R>(rec.s[6 * i + 1]), static_cast<R>(rec.s[6 * i + 2]));
+          S.a[i] = Vec3<R>(static_cast<R>(rec.s[6 * i + 3]), static_cast<R>(rec.s[6 * i + 4]), static_cast<R>(rec.s[6 * i + 5]));
+          S.lam[i] = 0;
+        }
+        Placed<R> PA, PB;
+        placeItem<R>(v, w, rec.state, spd, pr, A, B, sv, sv + A.vert_cnt, PA, PB);
+        d.converged = (nflag & 8) == 0;
+        distanceEpa<R, true>(PA, static_cast<R>(A.brad), PB, static_cast<R>(B.brad), thr, S, store, d);
+        if (d.status != ND_EPA_OVERFLOW)
+        {
+          st_scan += d.scanned;
+          st_epa += 1;
+          st_it += d.epa_iters;
+          st_unconv += d.converged ? 0 : 1;
+        }
+      }
+      storeHit<R>(w, d, u, sp, d.status == ND_CONTACT);
+      const bool deep = d.status == ND_EPA_OVERFLOW;
+      const unsigned m = __ballot_sync(0xffffffffu, deep);
+      if (m)
+      {
+        const unsigned lane = threadIdx.x & 31;
+        const int leader = __ffs(m) - 1;
+        unsigned long long dbase = 0;
+        if (lane == leader)
+          dbase = atomicAdd(reinterpret_cast<unsigned long long*>(&w.counters->n_deep),
+                            static_cast<unsigned long long>(__popc(m)));
+        dbase = __shfl_sync(0xffffffffu, dbase, leader);
+        if (deep)
+        {
+          const unsigned long long ds = dbase + __popc(m & ((1u << lane) - 1u));
+          w.deep_items[2 * ds] = u;
+          w.deep_items[2 * ds + 1] = sp;
+        }
       }
     }
+    __syncthreads();
+    item0 = run.q1;
   }
-  const bool counted = u >= 0 && d.status != ND_EPA_OVERFLOW;  // deep items are counted when they are re-run
-  addStats(w, 0, counted ? d.scanned : 0, counted ? 1 : 0, counted ? d.epa_iters : 0, (counted && !d.converged) ? 1 : 0);
+  addStats(w, 0, st_scan, st_epa, st_it, st_unconv);
 }
 
+#undef RUN_CHUNKS
 // deep-expansion path: same arithmetic, polytope in global scratch, vertices read from global memory
 template <class R>
 __global__ void __launch_bounds__(64) k_narrow_deep(SceneView v, Work w, long long n_deep, unsigned char* scratch,
@@ -368,7 +433,9 @@ __global__ void __launch_bounds__(64) k_narrow_deep(SceneView v, Work w, long lo
       const ShapeD& A = v.shapes[spd.sa];
       const ShapeD& B = v.shapes[spd.sb];
       Placed<R> PA, PB;
-      placeItem<R>(v, w, u, spd, pr, A, B, sceneVerts<R>(v) + A.vert_off, sceneVerts<R>(v) + B.vert_off, PA, PB);
+      const int kt = w.unit_term[u];
+      placeItem<R>(v, w, w.state_base[kt] + (u - w.unit_base[kt]), spd, pr, A, B, sceneVerts<R>(v) + A.vert_off,
+                   sceneVerts<R>(v) + B.vert_off, PA, PB);
       EpaStore<R> store{ pw, pa, fn, fd, fv, edges, EPA_DEEP_VERTS, EPA_DEEP_FACES };
       Simplex<R> S;
       int gjk_scanned;
@@ -413,20 +480,22 @@ size_t deepScratchBytesPerThread(int precision)
   return (b + 15) / 16 * 16;
 }
 
-template <class R>
+template <class R, int GB, int EB>
 static cudaError_t launchNarrowT(const SceneView& v, const Work& w, cudaStream_t st, cudaEvent_t mid)
 {
-  const unsigned grid = static_cast<unsigned>(w.n_items_padded / CHUNK);
+  const long long chunks = w.n_items_padded / CHUNK;
+  const unsigned grid_g = static_cast<unsigned>((chunks + GJK_RUN_CHUNKS - 1) / GJK_RUN_CHUNKS);
+  const unsigned grid_e = static_cast<unsigned>((chunks + EPA_RUN_CHUNKS - 1) / EPA_RUN_CHUNKS);
   const size_t smem = static_cast<size_t>(2 * v.max_hull_verts) * sizeof(Vtx<R>) + 16;
-  cudaFuncSetAttribute(k_gjk<R>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem));
-  cudaFuncSetAttribute(k_epa<R>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem));
+  cudaFuncSetAttribute(k_gjk<R, GB>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem));
+  cudaFuncSetAttribute(k_epa<R, EB>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem));
   cudaError_t e = cudaMemsetAsync(w.epa_cursor, 0, sizeof(int32_t) * v.n_spairs, st);
   if (e != cudaSuccess)
     return e;
-  k_gjk<R><<<grid, CHUNK, smem, st>>>(v, w);
+  k_gjk<R, GB><<<grid_g, CHUNK, smem, st>>>(v, w);
   if (mid)
     cudaEventRecord(mid, st);
-  k_epa<R><<<grid, CHUNK, smem, st>>>(v, w);
+  k_epa<R, EB><<<grid_e, CHUNK, smem, st>>>(v, w);
   return cudaGetLastError();
 }
 
@@ -434,7 +503,20 @@ cudaError_t launchNarrow(const SceneView& v, const Work& w, int precision, cudaS
 {
   if (w.n_items_padded <= 0)
     return cudaSuccess;
-  return precision == TC_PRECISION_F32 ? launchNarrowT<float>(v, w, st, mid) : launchNarrowT<double>(v, w, st, mid);
+  if (precision == TC_PRECISION_F32)
+    return launchNarrowT<float, 3, 2>(v, w, st, mid);
+  // tuning hook (bench only): TC_NARROW_VARIANT=gb,eb selects the min-blocks-per-SM register budget
+  static const char* var = getenv("TC_NARROW_VARIANT");
+  const int code = var ? (var[0] - '0') * 10 + (var[2] - '0') : 22;
+  switch (code)
+  {
+    case 32: return launchNarrowT<double, 3, 2>(v, w, st, mid);
+    case 33: return launchNarrowT<double, 3, 3>(v, w, st, mid);
+    case 42: return launchNarrowT<double, 4, 2>(v, w, st, mid);
+    case 44: return launchNarrowT<double, 4, 4>(v, w, st, mid);
+    case 23: return launchNarrowT<double, 2, 3>(v, w, st, mid);
+    default: return launchNarrowT<double, 2, 2>(v, w, st, mid);
+  }
 }
 
 cudaError_t launchNarrowDeep(const SceneView& v, const Work& w, int precision, long long n_deep, void* scratch,

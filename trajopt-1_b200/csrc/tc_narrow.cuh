@@ -525,92 +525,186 @@ TC_HD Vec3<R> leastAxisCross(Vec3<R> e)
   return cross(e, ax);
 }
 
-template <class R, bool MASK>
-TC_HDN EpaOut<R> epa(const Placed<R>& A, const Placed<R>& B, const Simplex<R>& start, R scale, EpaStore<R>& st,
-                     int& scanned)
+// resumable EPA: epaInit (tetrahedron + first faces), epaTrip (one support query + one polytope expansion),
+// epaFinish (depth, normal, witness points)
+template <class R>
+struct EpaState
 {
-  EpaOut<R> r;
+  int np, nf, best, iters;
+  unsigned long long alive;  // live-face mask (MASK mode)
+  R bd, eps_len, vis_eps;
+  Vec3<R> centroid;
+};
+
+template <class R, bool MASK>
+TC_HD bool epaIsAlive(const EpaState<R>& E, const EpaStore<R>& st, int f)
+{
+  return MASK ? ((E.alive >> f) & 1ull) != 0 : st.fv[f] >= 0;
+}
+
+// adds a face in the first dead slot (else appends); returns the slot or -1 on overflow; d_out = plane distance
+template <class R, bool MASK>
+TC_HD int epaAddFace(EpaState<R>& E, EpaStore<R>& st, int i, int j, int k, bool orient, R& d_out)
+{
+  const Vec3<R> pi = st.pw[i];
+  Vec3<R> n = cross(st.pw[j] - pi, st.pw[k] - pi);
+  if (orient && dot(n, pi - E.centroid) < 0)
+  {
+    const int t = j;
+    j = k;
+    k = t;
+    n = -n;
+  }
+  int slot = -1;
+  if (MASK)
+  {
+    const unsigned long long dead = ~E.alive & ((E.nf >= 64) ? ~0ull : ((1ull << E.nf) - 1ull));
+    if (dead)
+    {
+#if defined(__CUDA_ARCH__)
+      slot = __ffsll(static_cast<long long>(dead)) - 1;
+#else
+      unsigned long long x = dead;
+      slot = 0;
+      while (!(x & 1ull))
+      {
+        x >>= 1;
+        ++slot;
+      }
+#endif
+    }
+  }
+  else
+  {
+    for (int f = 0; f < E.nf; ++f)
+      if (st.fv[f] < 0)
+      {
+        slot = f;
+        break;
+      }
+  }
+  if (slot < 0)
+  {
+    if (E.nf >= st.max_faces)
+      return -1;
+    slot = E.nf++;
+  }
+  const R nn = norm(n);
+  st.fv[slot] = i | (j << 10) | (k << 20);
+  if (MASK)
+    E.alive |= 1ull << slot;
+  if (nn > Tol<R>::tiny())
+  {
+    const Vec3<R> un = (R(1) / nn) * n;
+    st.fn[slot] = un;
+    d_out = dot(un, pi);
+  }
+  else
+  {
+    st.fn[slot] = Vec3<R>(0, 0, 0);
+    d_out = -lowestReal<R>();  // degenerate sliver: never selected
+  }
+  st.fd[slot] = d_out;
+  return slot;
+}
+
+// smallest plane distance, lowest slot on ties (= first minimum of a scan in slot order)
+template <class R>
+TC_HD void epaOffer(EpaState<R>& E, int f, R d)
+{
+  if (E.best < 0 || d < E.bd || (d == E.bd && f < E.best))
+  {
+    E.best = f;
+    E.bd = d;
+  }
+}
+
+// returns 0: polytope ready, run trips; 1: finished already (flat Minkowski difference), r is final
+template <class R, bool MASK>
+TC_HDN int epaInit(const Placed<R>& A, const Placed<R>& B, const Simplex<R>& start, R scale, EpaStore<R>& st,
+                   EpaState<R>& E, EpaOut<R>& r, int& scanned)
+{
   r.ok = true;
   r.converged = true;
   r.depth = 0;
   r.iters = 0;
-  int np = start.n;
+  E.np = start.n;
   for (int i = 0; i < 4; ++i)
     if (i < start.n)
     {
       st.pw[i] = start.w[i];
       st.pa[i] = start.a[i];
     }
-  const R eps_len = Tol<R>::epsLenRel() * tc_max(scale, R(1e-3));
-  const R vis_eps = Tol<R>::visRel() * tc_max(scale, R(1e-3));
+  E.eps_len = Tol<R>::epsLenRel() * tc_max(scale, R(1e-3));
+  E.vis_eps = Tol<R>::visRel() * tc_max(scale, R(1e-3));
 
   // --- grow the GJK simplex to a tetrahedron with non-zero volume ---
-  if (np == 4)
+  if (E.np == 4)
   {
     const R vol = dot(cross(st.pw[1] - st.pw[0], st.pw[2] - st.pw[0]), st.pw[3] - st.pw[0]);
-    if (tc_abs(vol) <= eps_len * eps_len * eps_len)
-      np = 3;
+    if (tc_abs(vol) <= E.eps_len * E.eps_len * E.eps_len)
+      E.np = 3;
   }
-  if (np == 1)
+  if (E.np == 1)
   {
-    for (int k = 0; k < 6 && np == 1; ++k)
+    for (int k = 0; k < 6 && E.np == 1; ++k)
     {
       const R sg = (k & 1) ? R(-1) : R(1);
       const Vec3<R> d((k >> 1) == 0 ? sg : R(0), (k >> 1) == 1 ? sg : R(0), (k >> 1) == 2 ? sg : R(0));
       const Vec3<R> a = A.support(d, scanned), b = B.support(-d, scanned);
       const Vec3<R> w = a - b;
-      if (norm(w - st.pw[0]) > eps_len)
+      if (norm(w - st.pw[0]) > E.eps_len)
       {
         st.pw[1] = w;
         st.pa[1] = a;
-        np = 2;
+        E.np = 2;
       }
     }
   }
-  if (np == 2)
+  if (E.np == 2)
   {
     const Vec3<R> e = st.pw[1] - st.pw[0];
     const Vec3<R> d0 = leastAxisCross(e);
     const Vec3<R> d1 = cross(e, d0);
     const R en = norm(e);
-    for (int k = 0; k < 4 && np == 2; ++k)
+    for (int k = 0; k < 4 && E.np == 2; ++k)
     {
       const Vec3<R> d = (k == 0) ? d0 : ((k == 1) ? -d0 : ((k == 2) ? d1 : -d1));
       const Vec3<R> a = A.support(d, scanned), b = B.support(-d, scanned);
       const Vec3<R> w = a - b;
-      if (norm(cross(w - st.pw[0], e)) > eps_len * en)
+      if (norm(cross(w - st.pw[0], e)) > E.eps_len * en)
       {
         st.pw[2] = w;
         st.pa[2] = a;
-        np = 3;
+        E.np = 3;
       }
     }
   }
-  if (np == 3)
+  if (E.np == 3)
   {
     const Vec3<R> n = cross(st.pw[1] - st.pw[0], st.pw[2] - st.pw[0]);
     const R area = norm(n);
-    for (int sgn = 0; sgn < 2 && np == 3; ++sgn)
+    for (int sgn = 0; sgn < 2 && E.np == 3; ++sgn)
     {
       const Vec3<R> d = (sgn == 0) ? n : -n;
       const Vec3<R> a = A.support(d, scanned), b = B.support(-d, scanned);
       const Vec3<R> w = a - b;
-      if (tc_abs(dot(w - st.pw[0], n)) > eps_len * area)
+      if (tc_abs(dot(w - st.pw[0], n)) > E.eps_len * area)
       {
         st.pw[3] = w;
         st.pa[3] = a;
-        np = 4;
+        E.np = 4;
       }
     }
   }
-  if (np < 4)
+  if (E.np < 4)
   {
     // flat Minkowski difference (point / segment / polygon cores): core depth is zero, the normal is
     // the direction in which the difference has no extent
     Vec3<R> n(0, 0, 1);
-    if (np == 3)
+    if (E.np == 3)
       n = cross(st.pw[1] - st.pw[0], st.pw[2] - st.pw[0]);
-    else if (np == 2)
+    else if (E.np == 2)
       n = leastAxisCross(st.pw[1] - st.pw[0]);
     const R nn = norm(n);
     r.normal = (nn > 0) ? (R(1) / nn) * n : Vec3<R>(0, 0, 1);
@@ -634,206 +728,141 @@ TC_HDN EpaOut<R> epa(const Placed<R>& A, const Placed<R>& B, const Simplex<R>& s
     }
     r.pa = pa;
     r.pb = pa - pw;
-    return r;
+    return 1;
   }
 
-  int nf = 0;  // high-water mark of the face array
-  // MASK: the live-face set is also kept as a 64-bit register mask (max_faces <= 64), so dead slots cost no
-  // memory access and the first free slot is one ffs
-  unsigned long long alive = 0;
+  E.nf = 0;
+  E.alive = 0;
+  E.best = -1;
+  E.bd = 0;
+  E.iters = 1;
+  E.centroid = R(0.25) * (st.pw[0] + st.pw[1] + st.pw[2] + st.pw[3]);
+  R d;
+  int f = epaAddFace<R, MASK>(E, st, 0, 1, 2, true, d);
+  epaOffer(E, f, d);
+  f = epaAddFace<R, MASK>(E, st, 0, 1, 3, true, d);
+  epaOffer(E, f, d);
+  f = epaAddFace<R, MASK>(E, st, 0, 2, 3, true, d);
+  epaOffer(E, f, d);
+  f = epaAddFace<R, MASK>(E, st, 1, 2, 3, true, d);
+  epaOffer(E, f, d);
+  return 0;
+}
+
+enum
+{
+  EPA_CONTINUE = 0,
+  EPA_DONE = 1,
+  EPA_UNCONVERGED = 2,
+  EPA_OVERFLOW = 3
+};
+
+template <class R, bool MASK>
+TC_HDN int epaTrip(const Placed<R>& A, const Placed<R>& B, EpaStore<R>& st, EpaState<R>& E, int& scanned)
+{
   const R DEGENERATE = -lowestReal<R>();
-  const Vec3<R> centroid = R(0.25) * (st.pw[0] + st.pw[1] + st.pw[2] + st.pw[3]);
-  // adds a face in the first dead slot (else appends); returns the slot or -1 on overflow; d_out = plane distance
-  auto addFace = [&](int i, int j, int k, bool orient, R& d_out) -> int {
-    const Vec3<R> pi = st.pw[i];
-    Vec3<R> n = cross(st.pw[j] - pi, st.pw[k] - pi);
-    if (orient && dot(n, pi - centroid) < 0)
-    {
-      const int t = j;
-      j = k;
-      k = t;
-      n = -n;
-    }
-    int slot = -1;
-    if (MASK)
-    {
-      const unsigned long long dead = ~alive & ((nf >= 64) ? ~0ull : ((1ull << nf) - 1ull));
-      if (dead)
-      {
-        // index of the lowest set bit, written so that it also compiles on the host
-        unsigned long long x = dead;
-        slot = 0;
-        while (!(x & 1ull))
-        {
-          x >>= 1;
-          ++slot;
-        }
-      }
-    }
-    else
-    {
-      for (int f = 0; f < nf; ++f)
-        if (st.fv[f] < 0)
-        {
-          slot = f;
-          break;
-        }
-    }
-    if (slot < 0)
-    {
-      if (nf >= st.max_faces)
-        return -1;
-      slot = nf++;
-    }
-    const R nn = norm(n);
-    st.fv[slot] = i | (j << 10) | (k << 20);
-    if (MASK)
-      alive |= 1ull << slot;
-    if (nn > Tol<R>::tiny())
-    {
-      const Vec3<R> un = (R(1) / nn) * n;
-      st.fn[slot] = un;
-      d_out = dot(un, pi);
-    }
-    else
-    {
-      st.fn[slot] = Vec3<R>(0, 0, 0);
-      d_out = DEGENERATE;  // degenerate sliver: never selected
-    }
-    st.fd[slot] = d_out;
-    return slot;
-  };
-  auto isAlive = [&](int f) -> bool { return MASK ? ((alive >> f) & 1ull) != 0 : st.fv[f] >= 0; };
-  // smallest plane distance, lowest slot on ties (= first minimum of a scan in slot order)
-  int best = -1;
-  R bd = 0;
-  auto offer = [&](int f, R d) {
-    if (best < 0 || d < bd || (d == bd && f < best))
-    {
-      best = f;
-      bd = d;
-    }
-  };
+  const Vec3<R> bn = st.fn[E.best];
+  const Vec3<R> xa = A.support(bn, scanned), xb = B.support(-bn, scanned);
+  const Vec3<R> xw = xa - xb;
+  if (dot(bn, xw) - E.bd <= Tol<R>::epaTol())
+    return EPA_DONE;
+  if (E.iters == EPA_MAX_ITERS)
+    return EPA_UNCONVERGED;
+  if (E.np >= st.max_verts)
+    return EPA_OVERFLOW;
+  // one pass over the live faces: kill those that see x, collect the horizon, and track the closest
+  // survivor so that no separate "find the closest face" scan is needed
+  int ne = 0, sbest = -1;
+  R sbd = 0;
+  unsigned long long killed = 0;
+  for (int f = 0; f < E.nf; ++f)
   {
-    R d;
-    int f = addFace(0, 1, 2, true, d);
-    offer(f, d);
-    f = addFace(0, 1, 3, true, d);
-    offer(f, d);
-    f = addFace(0, 2, 3, true, d);
-    offer(f, d);
-    f = addFace(1, 2, 3, true, d);
-    offer(f, d);
-  }
-
-  for (r.iters = 1; r.iters <= EPA_MAX_ITERS; ++r.iters)
-  {
-    const Vec3<R> bn = st.fn[best];
-    const Vec3<R> xa = A.support(bn, scanned), xb = B.support(-bn, scanned);
-    const Vec3<R> xw = xa - xb;
-    if (dot(bn, xw) - bd <= Tol<R>::epaTol())
-      break;
-    if (r.iters == EPA_MAX_ITERS)
-    {
-      r.converged = false;
-      break;
-    }
-    if (np >= st.max_verts)
-    {
-      r.ok = false;
-      return r;
-    }
-    // one pass over the live faces: kill those that see x, collect the horizon, and track the closest
-    // survivor so that no separate "find the closest face" scan is needed
-    int ne = 0, sbest = -1;
-    R sbd = 0;
-    unsigned long long killed = 0;
-    for (int f = 0; f < nf; ++f)
-    {
-      if (!isAlive(f))
-        continue;
-      const R fd = st.fd[f];
-      bool visible = false;
-      if (fd != DEGENERATE)
-        visible = dot(st.fn[f], xw) - fd > vis_eps;
-      if (!visible)
-      {
-        if (sbest < 0 || fd < sbd)
-        {
-          sbest = f;
-          sbd = fd;
-        }
-        continue;
-      }
-      const int fv = st.fv[f];
-      const int v0 = fv & 1023, v1 = (fv >> 10) & 1023, v2 = (fv >> 20) & 1023;
-      if (MASK)
-        killed |= 1ull << f;
-      else
-        st.fv[f] = -1;
-      for (int e = 0; e < 3; ++e)
-      {
-        const int ea = (e == 0) ? v0 : ((e == 1) ? v1 : v2);
-        const int eb = (e == 0) ? v1 : ((e == 1) ? v2 : v0);
-        const int twin = eb | (ea << 16);
-        int found = -1;
-        for (int q = 0; q < ne; ++q)
-          if (st.edges[q] == twin)
-          {
-            found = q;
-            break;
-          }
-        if (found >= 0)
-        {
-          for (int q = found; q + 1 < ne; ++q)
-            st.edges[q] = st.edges[q + 1];
-          --ne;
-        }
-        else
-        {
-          if (ne >= st.max_faces)
-          {
-            r.ok = false;
-            return r;
-          }
-          st.edges[ne++] = ea | (eb << 16);
-        }
-      }
-    }
-    if (ne == 0)
-      break;  // numerically x is not outside any face although the gap test said so: accept the current face
-    alive &= ~killed;
-    const int xi = np;
-    st.pw[np] = xw;
-    st.pa[np] = xa;
-    ++np;
-    best = sbest;
-    bd = sbd;
-    for (int q = 0; q < ne; ++q)
-    {
-      R d;
-      const int e = st.edges[q];
-      const int f = addFace(e & 65535, e >> 16, xi, false, d);
-      if (f < 0)
-      {
-        r.ok = false;
-        return r;
-      }
-      offer(f, d);
-    }
-  }
-  r.depth = bd;
-  r.normal = st.fn[best];
-  // Witness points: the face with the smallest PLANE distance may be one of several coplanar triangles of
-  // a larger Minkowski face; the witness is taken on the triangle that is actually closest to the origin.
-  int wf = best;
-  R wbest = -lowestReal<R>(), la = 0, lb = 0, lc = 0;
-  for (int f = 0; f < nf; ++f)
-  {
-    if (!isAlive(f))
+    if (!epaIsAlive<R, MASK>(E, st, f))
       continue;
     const R fd = st.fd[f];
-    if (fd == DEGENERATE || fd > r.depth + eps_len)
+    bool visible = false;
+    if (fd != DEGENERATE)
+      visible = dot(st.fn[f], xw) - fd > E.vis_eps;
+    if (!visible)
+    {
+      if (sbest < 0 || fd < sbd)
+      {
+        sbest = f;
+        sbd = fd;
+      }
+      continue;
+    }
+    const int fv = st.fv[f];
+    const int v0 = fv & 1023, v1 = (fv >> 10) & 1023, v2 = (fv >> 20) & 1023;
+    if (MASK)
+      killed |= 1ull << f;
+    else
+      st.fv[f] = -1;
+    for (int e = 0; e < 3; ++e)
+    {
+      const int ea = (e == 0) ? v0 : ((e == 1) ? v1 : v2);
+      const int eb = (e == 0) ? v1 : ((e == 1) ? v2 : v0);
+      const int twin = eb | (ea << 16);
+      int found = -1;
+      for (int q = 0; q < ne; ++q)
+        if (st.edges[q] == twin)
+        {
+          found = q;
+          break;
+        }
+      if (found >= 0)
+      {
+        for (int q = found; q + 1 < ne; ++q)
+          st.edges[q] = st.edges[q + 1];
+        --ne;
+      }
+      else
+      {
+        if (ne >= st.max_faces)
+          return EPA_OVERFLOW;
+        st.edges[ne++] = ea | (eb << 16);
+      }
+    }
+  }
+  if (ne == 0)
+    return EPA_DONE;  // numerically x is not outside any face although the gap test said so: accept the face
+  E.alive &= ~killed;
+  const int xi = E.np;
+  st.pw[xi] = xw;
+  st.pa[xi] = xa;
+  E.np += 1;
+  E.best = sbest;
+  E.bd = sbd;
+  for (int q = 0; q < ne; ++q)
+  {
+    R d;
+    const int e = st.edges[q];
+    const int f = epaAddFace<R, MASK>(E, st, e & 65535, e >> 16, xi, false, d);
+    if (f < 0)
+      return EPA_OVERFLOW;
+    epaOffer(E, f, d);
+  }
+  E.iters += 1;
+  return EPA_CONTINUE;
+}
+
+template <class R, bool MASK>
+TC_HDN void epaFinish(const EpaStore<R>& st, const EpaState<R>& E, EpaOut<R>& r)
+{
+  const R DEGENERATE = -lowestReal<R>();
+  r.iters = E.iters;
+  r.depth = E.bd;
+  r.normal = st.fn[E.best];
+  // Witness points: the face with the smallest PLANE distance may be one of several coplanar triangles of
+  // a larger Minkowski face; the witness is taken on the triangle that is actually closest to the origin.
+  int wf = E.best;
+  R wbest = -lowestReal<R>(), la = 0, lb = 0, lc = 0;
+  for (int f = 0; f < E.nf; ++f)
+  {
+    if (!epaIsAlive<R, MASK>(E, st, f))
+      continue;
+    const R fd = st.fd[f];
+    if (fd == DEGENERATE || fd > r.depth + E.eps_len)
       continue;
     const int gv = st.fv[f];
     R a0, a1, a2;
@@ -851,6 +880,28 @@ TC_HDN EpaOut<R> epa(const Placed<R>& A, const Placed<R>& B, const Simplex<R>& s
   r.pa = la * st.pa[v0] + lb * st.pa[v1] + lc * st.pa[v2];
   const Vec3<R> pw = la * st.pw[v0] + lb * st.pw[v1] + lc * st.pw[v2];
   r.pb = r.pa - pw;
+}
+
+template <class R, bool MASK>
+TC_HDN EpaOut<R> epa(const Placed<R>& A, const Placed<R>& B, const Simplex<R>& start, R scale, EpaStore<R>& st,
+                     int& scanned)
+{
+  EpaOut<R> r;
+  EpaState<R> E;
+  if (epaInit<R, MASK>(A, B, start, scale, st, E, r, scanned))
+    return r;
+  int code;
+  while ((code = epaTrip<R, MASK>(A, B, st, E, scanned)) == EPA_CONTINUE)
+  {
+  }
+  if (code == EPA_OVERFLOW)
+  {
+    r.ok = false;
+    r.iters = E.iters;
+    return r;
+  }
+  r.converged = code != EPA_UNCONVERGED;
+  epaFinish<R, MASK>(st, E, r);
   return r;
 }
 

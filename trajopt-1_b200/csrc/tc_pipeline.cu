@@ -320,7 +320,11 @@ __global__ void __launch_bounds__(TPB) k_broad(SceneView v, Work w)
         base = atomicAdd(&w.sp_cursor[sp], __popc(m));
       base = __shfl_sync(0xffffffffu, base, leader);
       if (overlap)
-        w.items[w.sp_offset[sp] + base + __popc(m & ((1u << lane) - 1u))] = static_cast<int32_t>(u);
+      {
+        const int slot = w.sp_offset[sp] + base + __popc(m & ((1u << lane) - 1u));
+        w.items[slot] = static_cast<int32_t>(u);
+        w.item_state[slot] = static_cast<int32_t>(s0);
+      }
     }
     else if (lane == leader)
       atomicAdd(&w.sp_count[sp], __popc(m));
