@@ -25,26 +25,12 @@ sys.path.insert(0, ROOT)
 
 METRIC = "collision evals/sec (timestep x link-pair)"
 UNIT = "evals/s"
-T_STEPS, LVS, MARGIN, COEFF, BUFFER, SIGMA = 10, 0.02, 0.025, 20.0, 0.01, 0.3
+import tcb200  # noqa: E402
 
-
-def make_batch(scene, first_seed, n):
-    """C4 of SURVEY.md 8(d): start/goal of the fixture path resampled to T=10, interior waypoints perturbed by
-    N(0, 0.3^2) rad per joint (rng seed 4000 + k), clamped to the URDF limits."""
-    w = np.linspace(0.0, 1.0, T_STEPS)[:, None]
-    base = scene["seed_traj"][0] * (1 - w) + scene["seed_traj"][-1] * w
-    q = np.repeat(base[None], n, 0)
-    for i in range(n):
-        rng = np.random.default_rng(4000 + first_seed + i)
-        q[i, 1:-1] += rng.normal(0.0, SIGMA, (T_STEPS - 2, base.shape[1]))
-    lim = scene["joint_limits"]
-    return np.ascontiguousarray(np.clip(q, lim[:, 0], lim[:, 1]))
-
-
-def fixed_steps():
-    f = np.zeros(T_STEPS, np.uint8)
-    f[0] = f[-1] = 1
-    return f
+pkg = tcb200.load()
+ms_ = pkg.multistart
+T_STEPS, LVS, MARGIN, COEFF, BUFFER = ms_.T_STEPS, ms_.LVS, ms_.MARGIN, ms_.COEFF, ms_.BUFFER
+make_batch, fixed_steps = ms_.make_batch, ms_.fixed_steps
 
 
 class ClockSampler(threading.Thread):
@@ -140,8 +126,6 @@ def run_reference(args, scene, rank, world):
 def run_ours(args, scene, rank, world, local_rank):
     import ctypes as C
     import torch
-    import tcb200
-    pkg = tcb200.load()
     capi = pkg.capi
     torch.cuda.set_device(local_rank)
     dist = None
@@ -261,7 +245,8 @@ def run_ours(args, scene, rank, world, local_rank):
             pass
         traffic = None
         try:
-            traffic = json.load(open(os.path.join(ROOT, "profiles", "narrow_traffic.json")))["dram_bytes_per_launch"]
+            tr = json.load(open(os.path.join(ROOT, "profiles", "r1_traffic.json")))
+            traffic = sum(v["dram_bytes_per_launch"] for k, v in tr.items() if k.startswith(("k_gjk<double", "k_epa<double")))
         except Exception:
             pass
         base, _, _ = cpu_baseline(scene) if not args.no_cpu_baseline else ({"value": None, "unit": UNIT, "cores": 0,
@@ -312,8 +297,7 @@ def main():
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
-    from tests import helpers
-    scene = helpers.load_scene("arm_around_table")
+    scene = ms_.load_scene("arm_around_table")
     if args.impl == "reference":
         run_reference(args, scene, rank, world)
     else:

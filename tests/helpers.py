@@ -152,3 +152,118 @@ def compare(ro, rg, band=1e-9, want_rows=True):
     if ko == kg:
         rep["term_ptr_equal"] = bool((ro.term_ptr() == rg.term_ptr()).all())
     return rep
+
+
+def save_scene_file(arrays, path):
+    """flat named-array container read by trajopt-1_b200/host/tc_scene_file.hpp"""
+    import struct
+    items = []
+    for k, v in arrays.items():
+        v = np.asarray(v)
+        if v.dtype.kind == "f":
+            items.append((k, 0, np.ascontiguousarray(v, dtype="<f8")))
+        elif v.dtype == np.uint8:
+            items.append((k, 2, np.ascontiguousarray(v)))
+        elif v.dtype.kind in "iu":
+            items.append((k, 1, np.ascontiguousarray(v, dtype="<i4")))
+    with open(path, "wb") as f:
+        f.write(b"TCSCENE1" + struct.pack("<I", len(items)))
+        for k, code, v in items:
+            name = k.encode()
+            f.write(struct.pack("<I", len(name)) + name + struct.pack("<IQ", code, v.size) + v.tobytes())
+
+
+class GoldenResult:
+    """a frozen oracle result (tests/golden/*.npz, tools/make_golden.py) with the accessors compare() uses"""
+
+    class _Scene:
+        def __init__(self, pairs, margin_buffer):
+            self._pairs, self.margin_buffer = pairs, margin_buffer
+
+        def pairs(self):
+            return self._pairs
+
+    def __init__(self, name, live_scene):
+        self.d = dict(np.load(os.path.join(ROOT, "tests", "golden", name + ".npz")))
+        self.scene = GoldenResult._Scene(live_scene.pairs(), float(self.d["params"][2]))
+
+    def contacts(self):
+        return self.d["contacts"]
+
+    def contact_transforms(self):
+        return self.d["transforms"]
+
+    def term_ptr(self):
+        return self.d["term_ptr"]
+
+    def gradients(self):
+        return self.d["grad_rec"], self.d["grad"]
+
+    def rows(self):
+        d = self.d
+        return dict(row_ptr=d["row_ptr"], col_idx=d["col_idx"], val=d["val"], value=d["row_value"], coeff=d["row_coeff"],
+                    margin=d["row_margin"])
+
+    def cost(self):
+        return self.d["cost_term"], self.d["cost_traj"]
+
+    def counts(self):
+        c = dict(zip(("n_states", "n_units", "n_dense", "n_candidates", "n_terms"), self.d["counts"].tolist()))
+        c.update(n_narrowphase=-1, n_epa=-1, gjk_iters=-1, n_unconverged=-1)
+        return c
+
+
+def packed_keys(c):
+    """int64 key per contact, ordered like the result (traj, term, link pair, substep, shape ids)"""
+    k = c["traj"].astype(np.int64)
+    k = k * 64 + c["term"]
+    k = k * 16384 + c["pair"]
+    k = k * 16384 + c["substep"]
+    return k * 64 + c["shape_id"][:, 0].astype(np.int64) * 8 + c["shape_id"][:, 1]
+
+
+def compare_fast(ro, rg, band=1e-9):
+    """vectorised parity report for large batches (same protocol as compare(); rows are compared through the
+    dense per-contact gradient blocks and, when both sides hold the same contact sequence, the CSR arrays)"""
+    co, cg = ro.contacts(), rg.contacts()
+    ko, kg = packed_keys(co), packed_keys(cg)
+    assert (np.diff(ko) > 0).all() and (np.diff(kg) > 0).all(), "contacts not strictly sorted by key"
+    common, a, b = np.intersect1d(ko, kg, assume_unique=True, return_indices=True)
+    _, _, margin, _ = ro.scene.pairs()
+    thr = margin + ro.scene.margin_buffer
+    mo, mg = np.ones(len(ko), bool), np.ones(len(kg), bool)
+    mo[a], mg[b] = False, False
+    bad = int((np.abs(co["distance"][mo] - thr[co["pair"][mo]]) > band).sum() +
+              (np.abs(cg["distance"][mg] - thr[cg["pair"][mg]]) > band).sum())
+    A, G = co[a], cg[b]
+    rep = dict(n_contacts=len(ko), n_contacts_gpu=len(kg), n_common=len(common), unmatched_outside_band=bad,
+               same_order=bool(len(ko) == len(kg) and (ko == kg).all()))
+    rep["max_dist_err"] = float(np.abs(A["distance"] - G["distance"]).max())
+    rep["max_normal_err"] = float(np.abs(A["normal"] - G["normal"]).max())
+    rep["max_point_err"] = float(np.abs(A["nearest_points"] - G["nearest_points"]).max())
+    rep["max_cc_time_err"] = float(np.abs(A["cc_time"] - G["cc_time"]).max())
+    same_cc = (A["cc_type"] == G["cc_type"]).all(axis=1)
+    rep["cc_type_mismatch"] = int((~same_cc).sum())
+    reco, go = ro.gradients()
+    recg, gg = rg.gradients()
+    go, gg = go[a].reshape(len(a), -1), gg[b].reshape(len(b), -1)
+    den = np.maximum(np.abs(go).max(axis=1), 1e-12)
+    rel = np.abs(go - gg).max(axis=1) / den
+    rep["max_grad_rel_err"] = float(rel[same_cc].max()) if same_cc.any() else 0.0
+    rep["rec_equal"] = bool((reco["has_gradient"][a] == recg["has_gradient"][b]).all())
+    if rep["same_order"]:
+        rowo, rowg = ro.rows(), rg.rows()
+        rep["rows_same_structure"] = bool((rowo["row_ptr"] == rowg["row_ptr"]).all() and
+                                          (rowo["col_idx"] == rowg["col_idx"]).all())
+        if rep["rows_same_structure"] and len(rowo["val"]):
+            starts = rowo["row_ptr"][:-1]
+            nz = np.diff(rowo["row_ptr"]) > 0
+            dmax = np.maximum.reduceat(np.abs(rowo["val"] - rowg["val"]), starts[nz])
+            vmax = np.maximum.reduceat(np.abs(rowo["val"]), starts[nz])
+            ok = same_cc[nz]
+            rep["max_row_rel_err"] = float((dmax / np.maximum(vmax, 1e-12))[ok].max())
+            rep["max_row_value_err"] = float(np.abs(rowo["value"] - rowg["value"]).max())
+    _, to = ro.cost()
+    _, tg = rg.cost()
+    rep["max_cost_rel_err"] = float((np.abs(to - tg) / np.maximum(np.abs(to), 1.0)).max())
+    return rep

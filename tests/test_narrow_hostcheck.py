@@ -1,0 +1,57 @@
+"""CPU suite: the kernels' per-thread numerics (csrc/*.cuh compiled for the host, -ffp-contract=off) against
+the oracle on random shape pairs — same contact decision, same iteration counts, distances to 1e-12."""
+import numpy as np
+import pytest
+
+from tests import helpers
+
+capi = helpers.capi
+
+
+@pytest.mark.parametrize("scene_name,n,seed", [("arm_around_table", 500, 1), ("boxbot", 150, 2), ("spherebot", 150, 3)])
+def test_signed_distance_matches_oracle(oracle, hostcheck, scene_name, n, seed):
+    s = helpers.load_scene(scene_name)
+    so, sh = oracle.scene(s, 0.025, 20, 0.01), hostcheck.scene(s, 0.025, 20, 0.01)
+    rng = np.random.default_rng(seed)
+    nshape = len(s["shape_type"])
+    n_contact = n_epa = 0
+    for it in range(n):
+        sa, sb = rng.integers(0, nshape, 2)
+        scale = 0.3 if scene_name == "arm_around_table" else 1.0
+        pa0, pb0 = helpers.rand_pose(rng, scale), helpers.rand_pose(rng, scale)
+        pa1 = helpers.perturb_pose(rng, pa0, 0.2, 0.05) if it % 2 == 0 else None
+        ro = oracle.shape_distance(so, sa, pa0, sb, pb0, 0.05, pose_a1=pa1)
+        rh = hostcheck.shape_distance(sh, sa, pa0, sb, pb0, 0.05, pose_a1=pa1)
+        assert ro["contact"] == rh["contact"], (it, ro["distance"], rh["distance"])
+        if not ro["contact"]:
+            continue
+        n_contact += 1
+        n_epa += int(ro["epa"])
+        assert ro["epa"] == rh["epa"] and ro["iters"] == rh["iters"], (it, ro, rh)
+        assert abs(ro["distance"] - rh["distance"]) <= 1e-12, (it, ro["distance"], rh["distance"])
+        assert np.abs(ro["normal"] - rh["normal"]).max() <= 1e-9, it
+        assert max(np.abs(ro["pa"] - rh["pa"]).max(), np.abs(ro["pb"] - rh["pb"]).max()) <= 1e-9, it
+    assert n_contact > n // 20
+    if scene_name != "spherebot":  # sphere cores never penetrate: pure GJK
+        assert n_epa > 0
+
+
+def test_fast_and_deep_polytope_agree(oracle, hostcheck):
+    """an EPA that overflows the thread-local polytope is re-run with the large store: same answer as the oracle"""
+    s = helpers.load_scene("arm_around_table")
+    so, sh = oracle.scene(s, 0.025, 20, 0.01), hostcheck.scene(s, 0.025, 20, 0.01)
+    rng = np.random.default_rng(7)
+    nshape = len(s["shape_type"])
+    seen_overflow = 0
+    for it in range(400):
+        sa, sb = rng.integers(0, nshape, 2)
+        pa0, pb0 = helpers.rand_pose(rng, 0.05), helpers.rand_pose(rng, 0.05)  # deep overlaps
+        ro = oracle.shape_distance(so, sa, pa0, sb, pb0, 0.05)
+        small = hostcheck.shape_distance(sh, sa, pa0, sb, pb0, 0.05, max_verts=12, max_faces=20)
+        if small["status"] == 2:  # ND_EPA_OVERFLOW: the device hands these to the deep kernel
+            seen_overflow += 1
+            small = hostcheck.shape_distance(sh, sa, pa0, sb, pb0, 0.05)
+        assert small["contact"] == ro["contact"]
+        if ro["contact"]:
+            assert abs(ro["distance"] - small["distance"]) <= 1e-12
+    assert seen_overflow > 0

@@ -2,6 +2,6 @@
 
 The product is the C-ABI library csrc/libtrajopt_cuda.so (include/trajopt_cuda.h) plus the C++ host
 adaptors in host/ that mirror the reference's evaluator classes.  This Python package only contains
-the ctypes driver used by tests and benchmarks."""
-from . import capi  # noqa: F401
+the ctypes driver used by tests and benchmarks and the host-side multi-start logic (multistart.py)."""
+from . import capi, multistart  # noqa: F401
 from .capi import CudaLib, LIB_PATH  # noqa: F401

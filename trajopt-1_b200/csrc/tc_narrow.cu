@@ -216,7 +216,7 @@ __device__ __forceinline__ void stageHulls(const SceneView& v, const ShapeD& A, 
 // K3a: GJK for every bucketed item.  Separated pairs are finished here; touching / penetrating pairs hand
 // their simplex to the EPA stage through a per-shape-pair packed arena (SoA, 24 doubles per item).
 template <class R, int MINB>
-__global__ void __launch_bounds__(CHUNK, MINB) k_gjk(SceneView v, Work w)
+__global__ void __launch_bounds__(CHUNK, MINB * 128 / CHUNK) k_gjk(SceneView v, Work w)
 #define RUN_CHUNKS GJK_RUN_CHUNKS
 {
   extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -301,7 +301,7 @@ __global__ void __launch_bounds__(CHUNK, MINB) k_gjk(SceneView v, Work w)
 #define RUN_CHUNKS EPA_RUN_CHUNKS
 // K3b: EPA over the packed hand-off arena, same run structure.
 template <class R, int MINB>
-__global__ void __launch_bounds__(CHUNK, MINB) k_epa(SceneView v, Work w)
+__global__ void __launch_bounds__(CHUNK, MINB * 128 / CHUNK) k_epa(SceneView v, Work w)
 {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   __shared__ __align__(8) uint64_t bar;
