@@ -249,7 +249,7 @@ def run_ours(args, scene, rank, world, local_rank):
             traffic = sum(v["dram_bytes_per_launch"] for k, v in tr.items() if k.startswith(("k_gjk<double", "k_epa<double")))
         except Exception:
             pass
-        base, _, _ = cpu_baseline(scene) if not args.no_cpu_baseline else ({"value": None, "unit": UNIT, "cores": 0,
+        base, _, _ = cpu_baseline(scene) if (world == 1 and not args.no_cpu_baseline) else ({"value": None, "unit": UNIT, "cores": 0,
                                                                             "kind": "port", "sample": "skipped"}, 0, 0)
         out = {
             "metric": METRIC, "value": dense_total / (ms * 1e-3), "unit": UNIT, "n_gpus": world, "steps": args.steps,
