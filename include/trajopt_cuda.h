@@ -208,6 +208,11 @@ void tc_scene_destroy(tc_scene* scene);
 int tc_scene_num_pairs(const tc_scene* scene);
 int tc_scene_pairs(const tc_scene* scene, int32_t* link0, int32_t* link1, double* margin, double* coeff);
 
+/* ---- streams: for hosts that do not link a CUDA runtime of their own (a trajopt build does not).  Any
+ * cudaStream_t of the process may be passed to tc_eval instead. ---- */
+int tc_stream_create(void** stream);
+void tc_stream_destroy(void* stream);
+
 /* ---- evaluation ---- */
 int tc_result_create(tc_scene* scene, tc_result** out);
 void tc_result_destroy(tc_result* res);
@@ -237,6 +242,12 @@ int tc_result_gradients(const tc_result* res, tc_gradient* rec, double* grad, si
  * d(x) = row_value + val . x  (CollisionsToDistanceExpressions + CalcDistExpressions*). */
 int tc_result_rows(const tc_result* res, int64_t* row_ptr, int32_t* col_idx, double* val, double* row_value,
                    double* row_coeff, double* row_margin);
+/* tc_result_rows without the final wait: the copies are enqueued on the evaluation's stream and the call returns;
+ * the host arrays (pinned memory, or the copies degrade to synchronous ones) are valid after tc_result_wait().
+ * Lets a caller overlap the download of one sub-batch with the evaluation of the next on another stream. */
+int tc_result_rows_async(const tc_result* res, int64_t* row_ptr, int32_t* col_idx, double* val, double* row_value,
+                         double* row_coeff, double* row_margin);
+int tc_result_wait(const tc_result* res);
 /* same rows left in device memory (for a consumer that assembles the QP on the GPU); valid until the next
  * tc_eval on this result */
 int tc_result_rows_device(const tc_result* res, const int64_t** row_ptr, const int32_t** col_idx, const double** val,

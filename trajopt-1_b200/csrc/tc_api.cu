@@ -56,7 +56,12 @@ struct tc_result
   bool pending{ false }, valid{ false };
   bool have_grad{ false }, have_cost{ false }, have_rows{ false };
   Work w{};
-  Counters* h_counters{ nullptr };  // pinned
+  Counters* h_counters{ nullptr };  // pinned + mapped: the device writes the snapshot itself
+  Counters* h_counters_dev{ nullptr };  // device alias of h_counters
+  int32_t* h_stage{ nullptr };          // pinned + mapped staging of the small per-eval tables
+  int32_t* h_stage_dev{ nullptr };
+  size_t h_stage_words{ 0 };
+  DevBuf<int32_t> stage_d;
   Counters* d_counters{ nullptr };
   tc_counts counts{};
   cudaEvent_t ev[7]{};
@@ -101,6 +106,26 @@ int upload(tc_scene* s, const std::vector<T>& h, const T** out)
   return TC_OK;
 }
 
+// adds the kernels this thread launches while the scope is alive to the result's own_launches
+struct LaunchScope
+{
+  tc_result* r;
+  int mark;
+  explicit LaunchScope(tc_result* res) : r(res), mark(launchCounter()) {}
+  ~LaunchScope() { r->own_launches += launchCounter() - mark; }
+};
+
+// TC_TRACE=1: host-side timestamps of the synchronisation points (diagnostics for stream overlap)
+void trace(const tc_result* r, const char* what)
+{
+  static const bool on = getenv("TC_TRACE") != nullptr;
+  if (!on)
+    return;
+  timespec ts;
+  clock_gettime(CLOCK_MONOTONIC, &ts);
+  fprintf(stderr, "[tc %p] %.3f ms %s\n", static_cast<const void*>(r), ts.tv_sec * 1e3 + ts.tv_nsec * 1e-6, what);
+}
+
 int ensureDevice(int device)
 {
   TC_CUDA(cudaSetDevice(device));
@@ -109,8 +134,11 @@ int ensureDevice(int device)
 
 int readCounters(tc_result* r)
 {
-  TC_CUDA(cudaMemcpyAsync(r->h_counters, r->d_counters, sizeof(Counters), cudaMemcpyDeviceToHost, r->stream));
+  // snapshot through mapped host memory (SM stores over PCIe), not the D2H copy engine: a bulk result
+  // download of another tc_result may own that engine for milliseconds and would stall this pass
+  TC_CUDA(launchSnapshot(r->d_counters, r->h_counters_dev, r->stream));
   TC_CUDA(cudaStreamSynchronize(r->stream));
+  trace(r, "counters read");
   if (r->h_counters->overflow == 2)
     return fail(TC_ERR_OVERFLOW, "a segment needs more than 16384 LVS sub-states");
   if (r->h_counters->overflow)
@@ -219,12 +247,17 @@ int runEval(tc_scene* scene, const tc_eval_desc* desc, const double* q, int32_t 
   for (int i = 0; i < 10; ++i)
     r->stage_ms[i] = 0;
   r->own_launches = r->lib_launches = 0;
+  LaunchScope scope(r);
+  trace(r, "eval begin");
+  // The first operation on the stream is a kernel, not the event record: when the stream's previous operation
+  // was a device-to-host copy (a result download), an event record is queued on the copy engine, behind any bulk
+  // download another tc_result has in flight there, and every kernel of this pass would wait for it.
+  TC_CUDA(launchFill(r->d_counters, 0, sizeof(Counters) / 4, st));
   TC_CUDA(cudaEventRecord(r->ev[0], st));
-  TC_CUDA(cudaMemsetAsync(r->d_counters, 0, sizeof(Counters), st));
   if (n_terms == 0)
   {
     TC_RESERVE(r->term_ptr, 1);
-    TC_CUDA(cudaMemsetAsync(r->term_ptr.p, 0, sizeof(long long), st));
+    TC_CUDA(launchFill(r->term_ptr.p, 0, sizeof(long long) / 4, st));
     w.term_ptr = r->term_ptr.p;
     for (int i = 1; i < 7; ++i)
       TC_CUDA(cudaEventRecord(r->ev[i], st));
@@ -233,21 +266,46 @@ int runEval(tc_scene* scene, const tc_eval_desc* desc, const double* q, int32_t 
   }
   // ---- inputs ----
   const size_t nq = static_cast<size_t>(B) * T * hs.n_dof;
+  // Host inputs reach the device through kernels that read mapped pinned memory, not through the copy
+  // engines: a bulk result download of another tc_result may occupy an engine for milliseconds, and an
+  // input copy queued behind it would stall this whole pass.
   if (desc->q_on_device)
     w.q = q;
   else
   {
     TC_RESERVE(r->q, nq);
-    TC_CUDA(cudaMemcpyAsync(r->q.p, q, nq * sizeof(double), cudaMemcpyHostToDevice, st));
+    cudaPointerAttributes attr{};
+    const bool pinned = cudaPointerGetAttributes(&attr, q) == cudaSuccess && attr.type == cudaMemoryTypeHost &&
+                        attr.devicePointer != nullptr;
+    if (pinned)
+      TC_CUDA(launchCopy64(r->q.p, attr.devicePointer, nq, st));
+    else
+    {
+      cudaGetLastError();  // pageable memory: cudaPointerGetAttributes may have set an error state
+      TC_CUDA(cudaMemcpyAsync(r->q.p, q, nq * sizeof(double), cudaMemcpyHostToDevice, st));
+    }
     w.q = r->q.p;
   }
-  TC_RESERVE(r->term_t_d, ep.terms_per_traj);
-  TC_RESERVE(r->term_fixed_d, 2 * ep.terms_per_traj);
-  TC_CUDA(cudaMemcpyAsync(r->term_t_d.p, r->term_t.data(), sizeof(int32_t) * ep.terms_per_traj, cudaMemcpyHostToDevice,
-                          st));
-  TC_CUDA(cudaMemcpyAsync(r->term_fixed_d.p, r->term_fixed.data(), 2 * ep.terms_per_traj, cudaMemcpyHostToDevice, st));
-  w.term_t = r->term_t_d.p;
-  w.term_fixed = r->term_fixed_d.p;
+  {
+    const size_t n = static_cast<size_t>(ep.terms_per_traj), words = n + (2 * n + 3) / 4;
+    if (words > r->h_stage_words)
+    {
+      if (r->h_stage)
+        cudaFreeHost(r->h_stage);
+      r->h_stage = nullptr;
+      r->h_stage_words = 0;
+      TC_CUDA(cudaHostAlloc(reinterpret_cast<void**>(&r->h_stage), (words + 256) * 4, cudaHostAllocMapped));
+      TC_CUDA(cudaHostGetDevicePointer(reinterpret_cast<void**>(&r->h_stage_dev), r->h_stage, 0));
+      r->h_stage_words = words + 256;
+    }
+    std::memcpy(r->h_stage, r->term_t.data(), n * 4);
+    r->h_stage[words - 1] = 0;
+    std::memcpy(r->h_stage + n, r->term_fixed.data(), 2 * n);
+    TC_RESERVE(r->stage_d, words);
+    TC_CUDA(launchCopy32(r->stage_d.p, r->h_stage_dev, words, st));
+    w.term_t = r->stage_d.p;
+    w.term_fixed = reinterpret_cast<const uint8_t*>(r->stage_d.p + n);
+  }
   // ---- K0 plan ----
   TC_RESERVE(r->term_cnt, n_terms);
   TC_RESERVE(r->term_states, n_terms);
@@ -258,7 +316,6 @@ int runEval(tc_scene* scene, const tc_eval_desc* desc, const double* q, int32_t 
   w.term_cnt = r->term_cnt.p, w.term_states = r->term_states.p, w.term_units = r->term_units.p;
   w.term_interp = r->term_interp.p, w.state_base = r->state_base.p, w.unit_base = r->unit_base.p;
   TC_CUDA(launchPlan(v, w, st));
-  r->own_launches += 2;
   TC_TRY(readCounters(r));
   w.n_states = r->h_counters->n_states;
   w.n_units = r->h_counters->n_units;
@@ -274,7 +331,6 @@ int runEval(tc_scene* scene, const tc_eval_desc* desc, const double* q, int32_t 
   TC_CUDA(launchFk(v, w, st));
   TC_CUDA(cudaEventRecord(r->ev[1], st));
   TC_CUDA(launchBroadCount(v, w, st));
-  r->own_launches += 4;
   TC_TRY(readCounters(r));
   w.n_items_padded = r->h_counters->n_items_padded;
   const long long n_items = r->h_counters->n_items;
@@ -292,7 +348,6 @@ int runEval(tc_scene* scene, const tc_eval_desc* desc, const double* q, int32_t 
     TC_CUDA(launchBroadFill(v, w, st));
     TC_CUDA(cudaEventRecord(r->ev[5], st));
     TC_CUDA(launchNarrow(v, w, desc->precision, st, r->ev[6]));
-    r->own_launches += 3;
   }
   else
   {
@@ -308,7 +363,6 @@ int runEval(tc_scene* scene, const tc_eval_desc* desc, const double* q, int32_t 
     const size_t per = deepScratchBytesPerThread(desc->precision);
     TC_RESERVE(r->deep_scratch, per * n_threads);
     TC_CUDA(launchNarrowDeep(v, w, desc->precision, n_deep, r->deep_scratch.p, per, n_threads, st));
-    r->own_launches += 1;
     TC_TRY(readCounters(r));
   }
   TC_CUDA(cudaEventRecord(r->ev[3], st));
@@ -328,7 +382,6 @@ int runEval(tc_scene* scene, const tc_eval_desc* desc, const double* q, int32_t 
     TC_CUDA(sortContacts(w, nullptr, temp_bytes, st));
     TC_RESERVE(r->sort_temp, temp_bytes);
     TC_CUDA(sortContacts(w, r->sort_temp.p, temp_bytes, st));
-    r->own_launches += 1;
     r->lib_launches += 1;  // cub::DeviceRadixSort (several kernels of the CUDA toolkit's library)
     TC_TRY(readCounters(r));
   }
@@ -337,7 +390,6 @@ int runEval(tc_scene* scene, const tc_eval_desc* desc, const double* q, int32_t 
   TC_RESERVE(r->term_ptr, n_terms + 1);
   w.contacts = r->contacts.p, w.term_ptr = r->term_ptr.p;
   TC_CUDA(launchGather(v, w, st));
-  r->own_launches += (w.n_contacts > 0) ? 2 : 1;
   // ---- K4 ----
   if (desc->want & TC_WANT_GRADIENTS)
   {
@@ -346,7 +398,6 @@ int runEval(tc_scene* scene, const tc_eval_desc* desc, const double* q, int32_t 
     TC_RESERVE(r->ghas, w.n_contacts);
     w.grad = r->grad.p, w.grec = r->grec.p, w.ghas = r->ghas.p;
     TC_CUDA(launchGradients(v, w, st));
-    r->own_launches += (w.n_contacts > 0) ? 1 : 0;
     r->have_grad = true;
   }
   if (desc->want & TC_WANT_COST)
@@ -354,7 +405,6 @@ int runEval(tc_scene* scene, const tc_eval_desc* desc, const double* q, int32_t 
     TC_RESERVE(r->cost_term, n_terms);
     TC_RESERVE(r->cost_traj, B);
     TC_CUDA(launchCost(v, w, r->cost_term.p, r->cost_traj.p, st));
-    r->own_launches += 2;
     r->have_cost = true;
   }
   TC_CUDA(cudaEventRecord(r->ev[4], st));
@@ -366,6 +416,7 @@ int finishEval(tc_result* r)
 {
   if (!r->pending)
     return r->valid ? TC_OK : fail(TC_ERR_INVALID, "no evaluation to wait for");
+  LaunchScope scope(r);
   TC_TRY(ensureDevice(r->scene->device));
   if (r->ep.n_terms > 0)
     TC_TRY(readCounters(r));
@@ -421,6 +472,7 @@ int buildRows(tc_result* r)
     return TC_OK;
   if (!r->have_grad)
     return fail(TC_ERR_INVALID, "rows need an evaluation with TC_WANT_GRADIENTS");
+  LaunchScope scope(r);
   const HostScene& hs = r->scene->host;
   Work& w = r->w;
   const size_t nc = static_cast<size_t>(w.n_contacts);
@@ -435,7 +487,6 @@ int buildRows(tc_result* r)
   TC_CUDA(launchRowBase(r->scene->dview, w, r->term_row_base.p, r->stream));
   TC_CUDA(launchRows(r->scene->dview, w, r->term_row_base.p, r->col_idx.p, r->row_val.p, r->row_value.p,
                      r->row_coeff.p, r->row_margin.p, r->stream));
-  r->own_launches += 2;
   TC_TRY(readCounters(r));
   r->counts.nnz = r->h_counters->nnz;
   r->have_rows = true;
@@ -616,7 +667,9 @@ int tc_result_create(tc_scene* scene, tc_result** out)
   if (!r)
     return fail(TC_ERR_INVALID, "out of memory");
   r->scene = scene;
-  cudaError_t e = cudaMallocHost(reinterpret_cast<void**>(&r->h_counters), sizeof(Counters));
+  cudaError_t e = cudaHostAlloc(reinterpret_cast<void**>(&r->h_counters), sizeof(Counters), cudaHostAllocMapped);
+  if (e == cudaSuccess)
+    e = cudaHostGetDevicePointer(reinterpret_cast<void**>(&r->h_counters_dev), r->h_counters, 0);
   if (e == cudaSuccess)
     e = cudaMalloc(reinterpret_cast<void**>(&r->d_counters), sizeof(Counters));
   for (int i = 0; i < 7 && e == cudaSuccess; ++i)
@@ -639,6 +692,9 @@ void tc_result_destroy(tc_result* r)
     cudaStreamSynchronize(r->stream);
   if (r->h_counters)
     cudaFreeHost(r->h_counters);
+  if (r->h_stage)
+    cudaFreeHost(r->h_stage);
+  r->stage_d.release();
   if (r->d_counters)
     cudaFree(r->d_counters);
   for (int i = 0; i < 7; ++i)
@@ -691,7 +747,8 @@ int tc_result_contacts(const tc_result* res, tc_contact* dst, size_t cap)
   TC_TRY(needValid(res));
   const size_t n = std::min<size_t>(cap, static_cast<size_t>(res->w.n_contacts));
   if (n)
-    TC_CUDA(cudaMemcpy(dst, res->w.contacts, n * sizeof(tc_contact), cudaMemcpyDeviceToHost));
+    TC_CUDA(cudaMemcpyAsync(dst, res->w.contacts, n * sizeof(tc_contact), cudaMemcpyDeviceToHost, res->stream));
+  TC_CUDA(cudaStreamSynchronize(res->stream));
   return TC_OK;
 }
 
@@ -705,8 +762,9 @@ int tc_result_contact_transforms(const tc_result* res, double* dst, size_t cap)
     TC_RESERVE(r->xf, static_cast<size_t>(r->w.n_contacts) * 48);
     TC_CUDA(launchTransforms(r->scene->dview, r->w, r->xf.p, r->stream));
     TC_CUDA(cudaStreamSynchronize(r->stream));
-    TC_CUDA(cudaMemcpy(dst, r->xf.p, n * 48 * sizeof(double), cudaMemcpyDeviceToHost));
+    TC_CUDA(cudaMemcpyAsync(dst, r->xf.p, n * 48 * sizeof(double), cudaMemcpyDeviceToHost, r->stream));
   }
+  TC_CUDA(cudaStreamSynchronize(r->stream));
   return TC_OK;
 }
 
@@ -714,8 +772,9 @@ int tc_result_term_ptr(const tc_result* res, int64_t* term_ptr)
 {
   TC_TRY(needValid(res));
   static_assert(sizeof(long long) == sizeof(int64_t), "int64");
-  TC_CUDA(cudaMemcpy(term_ptr, res->w.term_ptr, (static_cast<size_t>(res->ep.n_terms) + 1) * sizeof(int64_t),
-                     cudaMemcpyDeviceToHost));
+  TC_CUDA(cudaMemcpyAsync(term_ptr, res->w.term_ptr, (static_cast<size_t>(res->ep.n_terms) + 1) * sizeof(int64_t),
+                      cudaMemcpyDeviceToHost, res->stream));
+  TC_CUDA(cudaStreamSynchronize(res->stream));
   return TC_OK;
 }
 
@@ -727,32 +786,76 @@ int tc_result_gradients(const tc_result* res, tc_gradient* rec, double* grad, si
   const size_t n = std::min<size_t>(cap, static_cast<size_t>(res->w.n_contacts));
   if (n)
   {
-    TC_CUDA(cudaMemcpy(rec, res->w.grec, n * sizeof(tc_gradient), cudaMemcpyDeviceToHost));
-    TC_CUDA(cudaMemcpy(grad, res->w.grad, n * 4 * res->scene->host.n_dof * sizeof(double), cudaMemcpyDeviceToHost));
+    TC_CUDA(cudaMemcpyAsync(rec, res->w.grec, n * sizeof(tc_gradient), cudaMemcpyDeviceToHost, res->stream));
+    TC_CUDA(cudaMemcpyAsync(grad, res->w.grad, n * 4 * res->scene->host.n_dof * sizeof(double), cudaMemcpyDeviceToHost, res->stream));
   }
+  TC_CUDA(cudaStreamSynchronize(res->stream));
   return TC_OK;
 }
 
-int tc_result_rows(const tc_result* res_c, int64_t* row_ptr, int32_t* col_idx, double* val, double* row_value,
-                   double* row_coeff, double* row_margin)
+static int rowsDownload(const tc_result* res_c, int64_t* row_ptr, int32_t* col_idx, double* val, double* row_value,
+                        double* row_coeff, double* row_margin, bool wait)
 {
   TC_TRY(needValid(res_c));
   tc_result* r = const_cast<tc_result*>(res_c);
   TC_TRY(buildRows(r));
+  trace(r, "rows download begin");
   const size_t nc = static_cast<size_t>(r->w.n_contacts);
   const size_t nnz = static_cast<size_t>(r->counts.nnz);
-  TC_CUDA(cudaMemcpy(row_ptr, r->row_ptr.p, (nc + 1) * sizeof(int64_t), cudaMemcpyDeviceToHost));
+  TC_CUDA(cudaMemcpyAsync(row_ptr, r->row_ptr.p, (nc + 1) * sizeof(int64_t), cudaMemcpyDeviceToHost, r->stream));
   if (nnz)
   {
-    TC_CUDA(cudaMemcpy(col_idx, r->col_idx.p, nnz * sizeof(int32_t), cudaMemcpyDeviceToHost));
-    TC_CUDA(cudaMemcpy(val, r->row_val.p, nnz * sizeof(double), cudaMemcpyDeviceToHost));
+    TC_CUDA(cudaMemcpyAsync(col_idx, r->col_idx.p, nnz * sizeof(int32_t), cudaMemcpyDeviceToHost, r->stream));
+    TC_CUDA(cudaMemcpyAsync(val, r->row_val.p, nnz * sizeof(double), cudaMemcpyDeviceToHost, r->stream));
   }
   if (nc)
   {
-    TC_CUDA(cudaMemcpy(row_value, r->row_value.p, nc * sizeof(double), cudaMemcpyDeviceToHost));
-    TC_CUDA(cudaMemcpy(row_coeff, r->row_coeff.p, nc * sizeof(double), cudaMemcpyDeviceToHost));
-    TC_CUDA(cudaMemcpy(row_margin, r->row_margin.p, nc * sizeof(double), cudaMemcpyDeviceToHost));
+    TC_CUDA(cudaMemcpyAsync(row_value, r->row_value.p, nc * sizeof(double), cudaMemcpyDeviceToHost, r->stream));
+    TC_CUDA(cudaMemcpyAsync(row_coeff, r->row_coeff.p, nc * sizeof(double), cudaMemcpyDeviceToHost, r->stream));
+    TC_CUDA(cudaMemcpyAsync(row_margin, r->row_margin.p, nc * sizeof(double), cudaMemcpyDeviceToHost, r->stream));
   }
+  trace(r, "rows download enqueued");
+  if (wait)
+  {
+    TC_CUDA(cudaStreamSynchronize(r->stream));
+    trace(r, "rows download done");
+  }
+  return TC_OK;
+}
+
+int tc_result_rows(const tc_result* res, int64_t* row_ptr, int32_t* col_idx, double* val, double* row_value,
+                   double* row_coeff, double* row_margin)
+{
+  return rowsDownload(res, row_ptr, col_idx, val, row_value, row_coeff, row_margin, true);
+}
+
+int tc_result_rows_async(const tc_result* res, int64_t* row_ptr, int32_t* col_idx, double* val, double* row_value,
+                         double* row_coeff, double* row_margin)
+{
+  return rowsDownload(res, row_ptr, col_idx, val, row_value, row_coeff, row_margin, false);
+}
+
+int tc_stream_create(void** stream)
+{
+  if (!stream)
+    return fail(TC_ERR_INVALID, "null argument");
+  cudaStream_t st = nullptr;
+  TC_CUDA(cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking));
+  *stream = st;
+  return TC_OK;
+}
+
+void tc_stream_destroy(void* stream)
+{
+  if (stream)
+    cudaStreamDestroy(static_cast<cudaStream_t>(stream));
+}
+
+int tc_result_wait(const tc_result* res)
+{
+  TC_TRY(needValid(res));
+  TC_CUDA(cudaStreamSynchronize(res->stream));
+  trace(res, "wait done");
   return TC_OK;
 }
 
@@ -801,17 +904,18 @@ int tc_result_sets(const tc_result* res_c, int32_t max_num_cnt, int64_t* set_ptr
   TC_CUDA(launchSets(r->scene->dview, r->w, max_num_cnt, r->sets.p, r->set_count.p, r->set_run.p, r->set_values.p,
                      r->set_coeffs.p, r->set_jac.p, r->stream));
   TC_CUDA(cudaStreamSynchronize(r->stream));
-  TC_CUDA(cudaMemcpy(values, r->set_values.p, nt * m * sizeof(double), cudaMemcpyDeviceToHost));
-  TC_CUDA(cudaMemcpy(coeffs, r->set_coeffs.p, nt * m * sizeof(double), cudaMemcpyDeviceToHost));
-  TC_CUDA(cudaMemcpy(jac, r->set_jac.p, nt * m * 2 * n * sizeof(double), cudaMemcpyDeviceToHost));
+  TC_CUDA(cudaMemcpyAsync(values, r->set_values.p, nt * m * sizeof(double), cudaMemcpyDeviceToHost, r->stream));
+  TC_CUDA(cudaMemcpyAsync(coeffs, r->set_coeffs.p, nt * m * sizeof(double), cudaMemcpyDeviceToHost, r->stream));
+  TC_CUDA(cudaMemcpyAsync(jac, r->set_jac.p, nt * m * 2 * n * sizeof(double), cudaMemcpyDeviceToHost, r->stream));
   // marshalling only: the sets of term k sit at the term's contact offset; pack them back to back
   std::vector<int32_t> cnt(nt);
   std::vector<int64_t> tp(nt + 1);
-  TC_CUDA(cudaMemcpy(cnt.data(), r->set_count.p, nt * sizeof(int32_t), cudaMemcpyDeviceToHost));
-  TC_CUDA(cudaMemcpy(tp.data(), r->w.term_ptr, (nt + 1) * sizeof(int64_t), cudaMemcpyDeviceToHost));
+  TC_CUDA(cudaMemcpyAsync(cnt.data(), r->set_count.p, nt * sizeof(int32_t), cudaMemcpyDeviceToHost, r->stream));
+  TC_CUDA(cudaMemcpyAsync(tp.data(), r->w.term_ptr, (nt + 1) * sizeof(int64_t), cudaMemcpyDeviceToHost, r->stream));
   std::vector<tc_set> all(nc);
   if (nc)
-    TC_CUDA(cudaMemcpy(all.data(), r->sets.p, nc * sizeof(tc_set), cudaMemcpyDeviceToHost));
+    TC_CUDA(cudaMemcpyAsync(all.data(), r->sets.p, nc * sizeof(tc_set), cudaMemcpyDeviceToHost, r->stream));
+  TC_CUDA(cudaStreamSynchronize(r->stream));
   size_t ns = 0;
   for (size_t k = 0; k < nt; ++k)
   {
@@ -838,6 +942,7 @@ int tc_result_cost(const tc_result* res_c, double* cost_per_term, double* cost_p
   }
   if (!r->have_cost)
   {
+    LaunchScope scope(r);
     TC_RESERVE(r->cost_term, r->ep.n_terms);
     TC_RESERVE(r->cost_traj, r->ep.B);
     TC_CUDA(launchCost(r->scene->dview, r->w, r->cost_term.p, r->cost_traj.p, r->stream));
@@ -845,9 +950,10 @@ int tc_result_cost(const tc_result* res_c, double* cost_per_term, double* cost_p
     r->have_cost = true;
   }
   if (cost_per_term)
-    TC_CUDA(cudaMemcpy(cost_per_term, r->cost_term.p, sizeof(double) * r->ep.n_terms, cudaMemcpyDeviceToHost));
+    TC_CUDA(cudaMemcpyAsync(cost_per_term, r->cost_term.p, sizeof(double) * r->ep.n_terms, cudaMemcpyDeviceToHost, r->stream));
   if (cost_per_traj)
-    TC_CUDA(cudaMemcpy(cost_per_traj, r->cost_traj.p, sizeof(double) * r->ep.B, cudaMemcpyDeviceToHost));
+    TC_CUDA(cudaMemcpyAsync(cost_per_traj, r->cost_traj.p, sizeof(double) * r->ep.B, cudaMemcpyDeviceToHost, r->stream));
+  TC_CUDA(cudaStreamSynchronize(r->stream));
   return TC_OK;
 }
 
@@ -872,7 +978,7 @@ int tc_result_launches(const tc_result* res, int32_t* own_kernels, int32_t* libr
 {
   TC_TRY(needValid(res));
   if (own_kernels)
-    *own_kernels = res->own_launches;
+    *own_kernels = res->own_launches;  // accumulated by finishEval / buildRows / cost from launchCounter()
   if (library_calls)
     *library_calls = res->lib_launches;
   return TC_OK;

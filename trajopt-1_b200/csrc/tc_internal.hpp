@@ -122,6 +122,13 @@ struct Work
 };
 
 // ---- launchers (tc_pipeline.cu) ----
+// number of kernels of this library launched by the calling thread (every <<< >>> site bumps it)
+int& launchCounter();
+// fills / copies done by kernels (never by the copy engines, see tc_api.cu runEval)
+cudaError_t launchFill(void* dst, uint32_t word, size_t n_words, cudaStream_t st);
+cudaError_t launchCopy32(void* dst, const void* src, size_t n_words, cudaStream_t st);
+cudaError_t launchCopy64(void* dst, const void* src, size_t n_dwords, cudaStream_t st);
+cudaError_t launchSnapshot(const Counters* dev, Counters* mapped_host, cudaStream_t st);
 cudaError_t launchPlan(const SceneView& v, const Work& w, cudaStream_t st);
 cudaError_t launchFk(const SceneView& v, const Work& w, cudaStream_t st);
 cudaError_t launchBroadCount(const SceneView& v, const Work& w, cudaStream_t st);

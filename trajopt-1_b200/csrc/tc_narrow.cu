@@ -489,12 +489,14 @@ static cudaError_t launchNarrowT(const SceneView& v, const Work& w, cudaStream_t
   const size_t smem = static_cast<size_t>(2 * v.max_hull_verts) * sizeof(Vtx<R>) + 16;
   cudaFuncSetAttribute(k_gjk<R, GB>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem));
   cudaFuncSetAttribute(k_epa<R, EB>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem));
-  cudaError_t e = cudaMemsetAsync(w.epa_cursor, 0, sizeof(int32_t) * v.n_spairs, st);
+  cudaError_t e = launchFill(w.epa_cursor, 0, v.n_spairs, st);
   if (e != cudaSuccess)
     return e;
+  ++launchCounter();
   k_gjk<R, GB><<<grid_g, CHUNK, smem, st>>>(v, w);
   if (mid)
     cudaEventRecord(mid, st);
+  ++launchCounter();
   k_epa<R, EB><<<grid_e, CHUNK, smem, st>>>(v, w);
   return cudaGetLastError();
 }
@@ -525,6 +527,7 @@ cudaError_t launchNarrowDeep(const SceneView& v, const Work& w, int precision, l
   if (n_deep <= 0)
     return cudaSuccess;
   const unsigned grid = static_cast<unsigned>(n_threads / 64);
+  ++launchCounter();
   if (precision == TC_PRECISION_F32)
     k_narrow_deep<float><<<grid, 64, 0, st>>>(v, w, n_deep, static_cast<unsigned char*>(scratch), bytes_per_thread);
   else

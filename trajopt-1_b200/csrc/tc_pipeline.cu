@@ -887,40 +887,121 @@ __global__ void __launch_bounds__(64) k_sets(SceneView v, Work w, int max_num_cn
 inline unsigned gridFor(long long n, int tpb) { return static_cast<unsigned>((n + tpb - 1) / tpb); }
 }  // namespace
 
+namespace
+{
+// copies the counters into mapped host memory with ordinary stores (no copy engine involved)
+__global__ void k_snapshot(const Counters* dev, Counters* host)
+{
+  constexpr int N = sizeof(Counters) / sizeof(long long);
+  if (threadIdx.x < N)
+    reinterpret_cast<long long*>(host)[threadIdx.x] = reinterpret_cast<const long long*>(dev)[threadIdx.x];
+  __threadfence_system();
+}
+}  // namespace
+
+namespace
+{
+template <class W>
+__global__ void k_fill(W* dst, W word, size_t n)
+{
+  for (size_t i = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x; i < n; i += static_cast<size_t>(gridDim.x) * blockDim.x)
+    dst[i] = word;
+}
+template <class W>
+__global__ void k_copy(W* dst, const W* src, size_t n)
+{
+  for (size_t i = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x; i < n; i += static_cast<size_t>(gridDim.x) * blockDim.x)
+    dst[i] = src[i];
+}
+inline unsigned gridFor(size_t n)
+{
+  const size_t b = (n + 255) / 256;
+  return static_cast<unsigned>(b < 1 ? 1 : (b > 148 * 8 ? 148 * 8 : b));
+}
+}  // namespace
+
+int& launchCounter()
+{
+  static thread_local int n = 0;
+  return n;
+}
+
+cudaError_t launchFill(void* dst, uint32_t word, size_t n_words, cudaStream_t st)
+{
+  if (n_words == 0)
+    return cudaSuccess;
+  ++launchCounter();
+  k_fill<uint32_t><<<gridFor(n_words), 256, 0, st>>>(static_cast<uint32_t*>(dst), word, n_words);
+  return cudaGetLastError();
+}
+
+cudaError_t launchCopy32(void* dst, const void* src, size_t n_words, cudaStream_t st)
+{
+  if (n_words == 0)
+    return cudaSuccess;
+  ++launchCounter();
+  k_copy<uint32_t><<<gridFor(n_words), 256, 0, st>>>(static_cast<uint32_t*>(dst), static_cast<const uint32_t*>(src), n_words);
+  return cudaGetLastError();
+}
+
+cudaError_t launchCopy64(void* dst, const void* src, size_t n_dwords, cudaStream_t st)
+{
+  if (n_dwords == 0)
+    return cudaSuccess;
+  ++launchCounter();
+  k_copy<unsigned long long><<<gridFor(n_dwords), 256, 0, st>>>(static_cast<unsigned long long*>(dst),
+                                                                static_cast<const unsigned long long*>(src), n_dwords);
+  return cudaGetLastError();
+}
+
+cudaError_t launchSnapshot(const Counters* dev, Counters* mapped_host, cudaStream_t st)
+{
+  ++launchCounter();
+  k_snapshot<<<1, 32, 0, st>>>(dev, mapped_host);
+  return cudaGetLastError();
+}
+
 cudaError_t launchPlan(const SceneView& v, const Work& w, cudaStream_t st)
 {
+  ++launchCounter();
   k_plan<<<gridFor(w.ep.n_terms, TPB), TPB, 0, st>>>(v, w);
+  ++launchCounter();
   k_scan_terms<<<1, 1024, 0, st>>>(w);
   return cudaGetLastError();
 }
 
 cudaError_t launchFk(const SceneView& v, const Work& w, cudaStream_t st)
 {
+  ++launchCounter();
   k_unit_term<<<gridFor(w.n_units, 256), 256, 0, st>>>(w);
+  ++launchCounter();
   k_fk<<<gridFor(w.n_states, TPB), TPB, 0, st>>>(v, w);
   return cudaGetLastError();
 }
 
 cudaError_t launchBroadCount(const SceneView& v, const Work& w, cudaStream_t st)
 {
-  cudaError_t e = cudaMemsetAsync(w.sp_count, 0, sizeof(int32_t) * v.n_spairs, st);
+  cudaError_t e = launchFill(w.sp_count, 0, v.n_spairs, st);
   if (e != cudaSuccess)
     return e;
-  e = cudaMemsetAsync(w.sp_cursor, 0, sizeof(int32_t) * v.n_spairs, st);
+  e = launchFill(w.sp_cursor, 0, v.n_spairs, st);
   if (e != cudaSuccess)
     return e;
   const dim3 grid(gridFor(w.n_units, TPB), static_cast<unsigned>(v.n_active_shapes));
+  ++launchCounter();
   k_broad<false><<<grid, TPB, 0, st>>>(v, w);
+  ++launchCounter();
   k_scan_sp<<<1, 1024, 0, st>>>(v, w);
   return cudaGetLastError();
 }
 
 cudaError_t launchBroadFill(const SceneView& v, const Work& w, cudaStream_t st)
 {
-  cudaError_t e = cudaMemsetAsync(w.items, 0xff, sizeof(int32_t) * static_cast<size_t>(w.n_items_padded), st);
+  cudaError_t e = launchFill(w.items, 0xffffffffu, static_cast<size_t>(w.n_items_padded), st);
   if (e != cudaSuccess)
     return e;
   const dim3 grid(gridFor(w.n_units, TPB), static_cast<unsigned>(v.n_active_shapes));
+  ++launchCounter();
   k_broad<true><<<grid, TPB, 0, st>>>(v, w);
   return cudaGetLastError();
 }
@@ -928,7 +1009,10 @@ cudaError_t launchBroadFill(const SceneView& v, const Work& w, cudaStream_t st)
 cudaError_t launchFinalize(const SceneView& v, const Work& w, cudaStream_t st)
 {
   if (w.n_raw > 0)
+  {
+    ++launchCounter();
     k_finalize<<<gridFor(w.n_raw, TPB), TPB, 0, st>>>(v, w);
+  }
   return cudaGetLastError();
 }
 
@@ -944,8 +1028,10 @@ cudaError_t launchGather(const SceneView& v, const Work& w, cudaStream_t st)
   if (w.n_contacts > 0)
   {
     const long long words = w.n_contacts * (static_cast<long long>(sizeof(tc_contact)) / 8);
+    ++launchCounter();
     k_gather<<<gridFor(words, 256), 256, 0, st>>>(w, w.idx_alt);
   }
+  ++launchCounter();
   k_term_ptr<<<gridFor(w.ep.n_terms + 1, 256), 256, 0, st>>>(w, w.keys_alt);
   return cudaGetLastError();
 }
@@ -953,20 +1039,27 @@ cudaError_t launchGather(const SceneView& v, const Work& w, cudaStream_t st)
 cudaError_t launchTransforms(const SceneView& v, const Work& w, double* xf, cudaStream_t st)
 {
   if (w.n_contacts > 0)
+  {
+    ++launchCounter();
     k_transforms<<<gridFor(w.n_contacts, TPB), TPB, 0, st>>>(v, w, xf);
+  }
   return cudaGetLastError();
 }
 
 cudaError_t launchGradients(const SceneView& v, const Work& w, cudaStream_t st)
 {
   if (w.n_contacts > 0)
+  {
+    ++launchCounter();
     k_grad<<<gridFor(w.n_contacts, TPB), TPB, 0, st>>>(v, w);
+  }
   return cudaGetLastError();
 }
 
 cudaError_t launchRows(const SceneView& v, const Work& w, long long* term_row_base, int32_t* col_idx, double* val,
                        double* row_value, double* row_coeff, double* row_margin, cudaStream_t st)
 {
+  ++launchCounter();
   k_rows<<<gridFor(w.n_contacts + 1, TPB), TPB, 0, st>>>(v, w, term_row_base, col_idx, val, row_value, row_coeff,
                                                        row_margin);
   return cudaGetLastError();
@@ -974,13 +1067,16 @@ cudaError_t launchRows(const SceneView& v, const Work& w, long long* term_row_ba
 
 cudaError_t launchRowBase(const SceneView& v, const Work& w, long long* term_row_base, cudaStream_t st)
 {
+  ++launchCounter();
   k_row_base<<<1, 1024, 0, st>>>(v, w, term_row_base);
   return cudaGetLastError();
 }
 
 cudaError_t launchCost(const SceneView& v, const Work& w, double* cost_term, double* cost_traj, cudaStream_t st)
 {
+  ++launchCounter();
   k_cost_term<<<gridFor(w.ep.n_terms, TPB), TPB, 0, st>>>(v, w, cost_term);
+  ++launchCounter();
   k_cost_traj<<<gridFor(w.ep.B, TPB), TPB, 0, st>>>(w, cost_term, cost_traj);
   return cudaGetLastError();
 }
@@ -988,6 +1084,7 @@ cudaError_t launchCost(const SceneView& v, const Work& w, double* cost_term, dou
 cudaError_t launchSets(const SceneView& v, const Work& w, int max_num_cnt, tc_set* sets, int32_t* set_count,
                        int32_t* set_run, double* values, double* coeffs, double* jac, cudaStream_t st)
 {
+  ++launchCounter();
   k_sets<<<gridFor(w.ep.n_terms, 64), 64, 0, st>>>(v, w, max_num_cnt, sets, set_count, set_run, values, coeffs, jac);
   return cudaGetLastError();
 }

@@ -76,3 +76,103 @@ def allgather_best(local_cost, local_index, group=None):
     out = [torch.zeros(2, dtype=torch.float64) for _ in range(world)]
     dist.all_gather(out, mine, group=group)
     return reduce_best([(float(t[0]), int(t[1])) for t in out])
+
+
+class PipelinedEvaluator:
+    """End-to-end multi-start pass with HOST buffers: the batch is cut into sub-batches that go round-robin to a
+    few worker threads, each with its own CUDA stream, tc_result and pinned output buffers.  While one worker's
+    rows travel device -> host, the other workers' kernels run, so the PCIe time of the rows (the bulk of the
+    bytes) hides behind the compute of the next sub-batch.  Every sub-batch is an ordinary
+    tc_eval + tc_result_rows + tc_result_cost through the C ABI; seeds are independent, so the host QP of a
+    sub-batch can start as soon as its rows have landed.
+
+    torch is used for pinned host memory and stream objects only."""
+
+    def __init__(self, cu, scene, evaluator, lvs, fixed, n_dof, chunk=1024, n_workers=2, rows_per_seed=1400,
+                 concurrent=1):
+        import queue
+        import threading
+        import torch
+        self.cu, self.scene, self.evaluator, self.lvs, self.fixed = cu, scene, evaluator, lvs, fixed
+        self.chunk, self.n_dof = chunk, n_dof
+        self.torch = torch
+        self.capi = cu.capi if hasattr(cu, "capi") else None
+        self.workers = []
+        self.jobs = [queue.Queue() for _ in range(n_workers)]
+        self.done = queue.Queue()
+        self.cap = int(chunk * rows_per_seed)
+        # at most `concurrent` sub-batches compute at a time; the slot is given up once the device -> host copies
+        # are enqueued, so a worker's copies run under other workers' kernels instead of all workers moving in
+        # lock step
+        self.compute = threading.Semaphore(concurrent)
+        for w in range(n_workers):
+            st = torch.cuda.Stream()
+            bufs = self._alloc(self.cap)
+            t = threading.Thread(target=self._work, args=(w, st, bufs), daemon=True)
+            t.start()
+            self.workers.append((t, st, bufs))
+
+    def _alloc(self, cap):
+        torch, nd = self.torch, self.n_dof
+        pin = lambda n, dt: torch.empty(n, dtype=dt).pin_memory().numpy()
+        return dict(cap=cap, row_ptr=pin(cap + 1, torch.int64), col=pin(2 * cap * nd, torch.int32),
+                    val=pin(2 * cap * nd, torch.float64), value=pin(cap, torch.float64), coeff=pin(cap, torch.float64),
+                    margin=pin(cap, torch.float64), cost=pin(self.chunk, torch.float64))
+
+    def _work(self, w, stream, bufs):
+        import ctypes as C
+        from . import capi
+        cu = self.cu
+        torch = self.torch
+        res = None
+        pd, pi, pl = C.POINTER(C.c_double), C.POINTER(C.c_int32), C.POINTER(C.c_int64)
+        while True:
+            job = self.jobs[w].get()
+            if job is None:
+                return
+            idx, q = job
+            try:
+                if res is None:
+                    res = capi.Result(cu, self.scene, cu.new_result(self.scene), len(q), q.shape[1])
+                with self.compute:
+                    r = cu.eval(self.scene, q, self.evaluator, lvs=self.lvs, fixed=self.fixed, result=res,
+                                stream=stream.cuda_stream)
+                    n = r.counts()["n_contacts"]
+                    if n > bufs["cap"]:
+                        bufs.update(self._alloc(int(n * 1.25)))
+                    # the copies are enqueued before the next sub-batch may start (still under the lock) and
+                    # awaited after it has started
+                    cu.check(cu.dll.tc_result_rows_async(
+                        res.handle, bufs["row_ptr"].ctypes.data_as(pl), bufs["col"].ctypes.data_as(pi),
+                        bufs["val"].ctypes.data_as(pd), bufs["value"].ctypes.data_as(pd),
+                        bufs["coeff"].ctypes.data_as(pd), bufs["margin"].ctypes.data_as(pd)))
+                cu.check(cu.dll.tc_result_wait(res.handle))
+                cu.check(cu.dll.tc_result_cost(res.handle, None, bufs["cost"].ctypes.data_as(pd)))
+                c = r.counts()
+                self.done.put((idx, w, n, c["nnz"], c["n_dense"], bufs["cost"][:len(q)].copy(), None))
+            except Exception as e:  # surfaced by run()
+                self.done.put((idx, w, 0, 0, 0, None, e))
+
+    def run(self, q_pinned):
+        """q_pinned: numpy view of pinned host memory [B, T, n_dof].  Returns (costs[B], n_rows, nnz, n_dense);
+        the rows of sub-batch i are in worker (i % n_workers)'s pinned buffers when its entry arrives."""
+        B = len(q_pinned)
+        n_jobs = 0
+        for i, lo in enumerate(range(0, B, self.chunk)):
+            self.jobs[i % len(self.jobs)].put((i, q_pinned[lo:lo + self.chunk]))
+            n_jobs += 1
+        costs = np.zeros(B)
+        rows = nnz = dense = 0
+        for _ in range(n_jobs):
+            idx, w, n, z, d, cost, err = self.done.get()
+            if err is not None:
+                raise err
+            costs[idx * self.chunk: idx * self.chunk + len(cost)] = cost
+            rows, nnz, dense = rows + n, nnz + z, dense + d
+        return costs, rows, nnz, dense
+
+    def close(self):
+        for q in self.jobs:
+            q.put(None)
+        for t, _, _ in self.workers:
+            t.join(timeout=10)
