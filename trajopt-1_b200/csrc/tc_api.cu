@@ -72,6 +72,7 @@ struct tc_result
   DevBuf<int32_t> term_t_d, term_cnt, term_states, term_units, state_base, unit_base, unit_term;
   DevBuf<uint8_t> term_fixed_d, term_interp;
   DevBuf<double> poses, aabb;
+  DevBuf<uint32_t> bp_mask;
   DevBuf<int32_t> sp_count, sp_offset, sp_cursor, items, deep_items, idx, idx_alt, ghas, epa_cursor, item_state;
   DevBuf<EpaRec> epa_rec;
   DevBuf<RawContact> raw;
@@ -323,6 +324,8 @@ int runEval(tc_scene* scene, const tc_eval_desc* desc, const double* q, int32_t 
   TC_RESERVE(r->poses, static_cast<size_t>(w.n_states) * hs.n_active * 12);
   TC_RESERVE(r->aabb, static_cast<size_t>(w.n_states) * hs.n_active_shapes * 6);
   TC_RESERVE(r->unit_term, w.n_units);
+  TC_RESERVE(r->bp_mask, static_cast<size_t>(hs.partner_word_ptr.back()) * static_cast<size_t>(w.n_units));
+  w.bp_mask = r->bp_mask.p;
   TC_RESERVE(r->sp_count, hs.spairs.size());
   TC_RESERVE(r->sp_cursor, hs.spairs.size());
   TC_RESERVE(r->sp_offset, hs.spairs.size() + 1);
@@ -617,6 +620,7 @@ int tc_scene_create(const tc_scene_desc* desc, tc_scene** out)
   UP(spairs, h.spairs);
   UP(partner_ptr, h.partner_ptr);
   UP(partner_sp, h.partner_sp);
+  UP(partner_word_ptr, h.partner_word_ptr);
 #undef UP
   if (st != TC_OK)
   {
@@ -702,7 +706,7 @@ void tc_result_destroy(tc_result* r)
       cudaEventDestroy(r->ev[i]);
   r->q.release(), r->term_t_d.release(), r->term_cnt.release(), r->term_states.release(), r->term_units.release();
   r->state_base.release(), r->unit_base.release(), r->unit_term.release(), r->term_fixed_d.release();
-  r->term_interp.release(), r->poses.release(), r->aabb.release(), r->sp_count.release(), r->sp_offset.release();
+  r->term_interp.release(), r->poses.release(), r->aabb.release(), r->bp_mask.release(), r->sp_count.release(), r->sp_offset.release();
   r->sp_cursor.release(), r->items.release(), r->deep_items.release(), r->idx.release(), r->idx_alt.release();
   r->ghas.release(), r->raw.release(), r->keys.release(), r->keys_alt.release(), r->contacts_tmp.release();
   r->contacts.release(), r->xf.release(), r->grad.release(), r->term_ptr.release();

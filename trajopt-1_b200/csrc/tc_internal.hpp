@@ -4,10 +4,12 @@
 //   q            [B][T][n_dof] f64                       joint values of every trajectory
 //   term_*       [n_terms]                               cnt / #states / #units / LVS-merge flag per term
 //   state_base,unit_base [n_terms+1]                     exclusive scans (sub-states and tested units)
-//   poses        [n_states][n_active_links][12] f64      AoS: one 96-byte record per (state, link); the
-//                                                        narrow phase reads whole records at scattered states
+//   poses        [n_active_links][n_states][12] f64      one 96-byte record per (link, state); consecutive sub-states
+//                                                        of a link are adjacent, so a sweep's T0/T1 poses are one
+//                                                        192-byte read and the FK warps write whole 3 KB runs
 //   aabb         [n_active_shapes][6][n_states] f64      SoA: the broadphase streams them along the state axis
 //   unit_term    [n_units] i32
+//   bp_mask      [partner words][n_units] u32            broadphase survivors as bits (count pass -> fill pass)
 //   sp_count/sp_offset/sp_cursor [n_shape_pairs(+1)]     survivors per shape pair, offsets padded to CHUNK
 //   items        [n_items_padded] i32                    unit index, bucketed per shape pair, -1 = padding
 //   item_state   [n_items_padded] i32                    T0 sub-state of the item
@@ -101,6 +103,7 @@ struct Work
   double* poses;
   double* aabb;
   int32_t* unit_term;
+  uint32_t* bp_mask;  // [partner words][n_units]: AABB survivors found by the counting pass, replayed by the fill pass
   int32_t *sp_count, *sp_offset, *sp_cursor;
   int32_t* items;
   RawContact* raw;
@@ -120,6 +123,12 @@ struct Work
   long long n_states, n_units, n_items_padded, n_raw, n_contacts;
   long long raw_cap, deep_cap;
 };
+
+// record of (link, state) in the pose arena; the next sub-state of the same link follows at +12
+__host__ __device__ inline const double* posePtr(const Work& w, int link, long long state)
+{
+  return w.poses + (static_cast<size_t>(link) * static_cast<size_t>(w.n_states) + static_cast<size_t>(state)) * 12;
+}
 
 // ---- launchers (tc_pipeline.cu) ----
 // number of kernels of this library launched by the calling thread (every <<< >>> site bumps it)

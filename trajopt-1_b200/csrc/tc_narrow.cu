@@ -75,18 +75,18 @@ __device__ __forceinline__ void placeItem(const SceneView& v, const Work& w, lon
                                           const PairD& pr, const ShapeD& A, const ShapeD& B, const Vtx<R>* va,
                                           const Vtx<R>* vb, Placed<R>& PA, Placed<R>& PB)
 {
-  const double* pa = w.poses + (static_cast<size_t>(s0) * v.n_active + pr.a) * 12;
+  const double* pa = posePtr(w, pr.a, s0);
   PA.sh = makeCore<R>(A, va);
   PA.p0 = loadPose<R>(pa);
   PA.cast = w.cast != 0;
-  PA.p1 = w.cast ? loadPose<R>(pa + static_cast<size_t>(v.n_active) * 12) : PA.p0;
+  PA.p1 = w.cast ? loadPose<R>(pa + 12) : PA.p0;
   PB.sh = makeCore<R>(B, vb);
   if (pr.b < v.n_active)
   {
-    const double* pb = w.poses + (static_cast<size_t>(s0) * v.n_active + pr.b) * 12;
+    const double* pb = posePtr(w, pr.b, s0);
     PB.p0 = loadPose<R>(pb);
     PB.cast = w.cast != 0;
-    PB.p1 = w.cast ? loadPose<R>(pb + static_cast<size_t>(v.n_active) * 12) : PB.p0;
+    PB.p1 = w.cast ? loadPose<R>(pb + 12) : PB.p0;
   }
   else
   {

@@ -171,9 +171,15 @@ __global__ void k_unit_term(Work w)
 // ---------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(TPB) k_fk(SceneView v, Work w)
 {
-  const long long s = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
-  if (s >= w.n_states)
-    return;
+  // per-warp staging tile: 32 poses, rows padded to 13 doubles (bank spread)
+  __shared__ double tile[TPB / 32][32 * 13];
+  const long long s_raw = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+  const bool live = s_raw < w.n_states;
+  const long long s = live ? s_raw : w.n_states - 1;  // idle lanes shadow the last state and write nothing
+  const unsigned lane = threadIdx.x & 31;
+  const long long warp_s0 = s_raw - lane;
+  const int warp_n = static_cast<int>(min(32ll, w.n_states - warp_s0));  // live lanes of this warp (may be <= 0)
+  double* my_tile = tile[threadIdx.x >> 5];
   const int k = lastLE(w.state_base, w.ep.n_terms, static_cast<int>(s));
   const int i = static_cast<int>(s) - w.state_base[k];
   const int b = k / w.ep.terms_per_traj, ti = k % w.ep.terms_per_traj;
@@ -181,9 +187,8 @@ __global__ void __launch_bounds__(TPB) k_fk(SceneView v, Work w)
   const double* q0 = w.q + (static_cast<size_t>(b) * w.ep.T + w.term_t[ti]) * n;
   const bool discrete = w.ep.evaluator == TC_EVAL_DISCRETE;
   const int cnt = w.term_interp[k] ? w.term_cnt[k] : 2;
-  double* out = w.poses + static_cast<size_t>(s) * v.n_active * 12;
   // Frames are visited in topological order with the previous frame's pose in registers; a branch reads
-  // its parent back from this thread's own records in the pose arena (no thread-local frame array).
+  // its parent back from this thread's own record in the pose arena (no thread-local frame array).
   const Pose<double> base = Pose<double>::from12(v.base_pose);
   Pose<double> cur = base;
   for (int f = 0; f < v.n_frames; ++f)
@@ -195,7 +200,7 @@ __global__ void __launch_bounds__(TPB) k_fk(SceneView v, Work w)
     else if (p == f - 1)
       parent = cur;
     else if (v.frame_link[p] >= 0)
-      parent = Pose<double>::from12(out + 12 * v.frame_link[p]);
+      parent = Pose<double>::from12(posePtr(w, v.frame_link[p], s));
     else
     {
       // a branching frame that carries no collision link: rebuild it from the root (rare)
@@ -219,10 +224,30 @@ __global__ void __launch_bounds__(TPB) k_fk(SceneView v, Work w)
       qf = discrete ? q0[j] : linspaced(cnt, q0[j], q0[n + j], i);
     }
     cur = frameStepQ(v, parent, f, qf);
-    // every active link / active shape riding on this frame
+    // every active link riding on this frame: the warp's 32 records of one link are one contiguous run of
+    // the arena, written with coalesced stores after a transpose through shared memory
     for (int l = 0; l < v.n_active; ++l)
-      if (v.link_frame[l] == f)
-        cur.to12(out + 12 * l);
+    {
+      if (v.link_frame[l] != f)
+        continue;
+      cur.to12(my_tile + lane * 13);
+      __syncwarp();
+      if (warp_n > 0)
+      {
+        double* dst = w.poses + (static_cast<size_t>(l) * static_cast<size_t>(w.n_states) + static_cast<size_t>(warp_s0)) * 12;
+        const int total = warp_n * 12;
+#pragma unroll
+        for (int j = 0; j < 12; ++j)
+        {
+          const int e = j * 32 + static_cast<int>(lane);
+          if (e < total)
+            dst[e] = my_tile[(e / 12) * 13 + (e % 12)];
+        }
+      }
+      __syncwarp();
+    }
+    if (!live)
+      continue;
     for (int a = 0; a < v.n_active_shapes; ++a)
     {
       if (v.active_shape_frame[a] != f)
@@ -276,6 +301,43 @@ __global__ void __launch_bounds__(TPB) k_broad(SceneView v, Work w)
   const long long u = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
   const int a = blockIdx.y;
   const bool inb = u < w.n_units;
+  const unsigned lane = threadIdx.x & 31;
+  const int p_begin = v.partner_ptr[a], p_end = v.partner_ptr[a + 1];
+  uint32_t* mask = w.bp_mask + static_cast<size_t>(v.partner_word_ptr[a]) * static_cast<size_t>(w.n_units);
+  if (FILL)
+  {
+    // replay the survivors the counting pass found: no AABB is read again
+    long long s0 = 0;
+    if (inb)
+    {
+      const int k = w.unit_term[u];
+      s0 = w.state_base[k] + (u - w.unit_base[k]);
+    }
+    uint32_t bits = 0;
+    for (int pi = p_begin; pi < p_end; ++pi)
+    {
+      const int j = (pi - p_begin) & 31;
+      if (j == 0)
+        bits = inb ? mask[static_cast<size_t>((pi - p_begin) >> 5) * static_cast<size_t>(w.n_units) + u] : 0u;
+      const bool overlap = (bits >> j) & 1u;
+      const unsigned m = __ballot_sync(0xffffffffu, overlap);
+      if (m == 0)
+        continue;
+      const int sp = v.partner_sp[pi];
+      const int leader = __ffs(m) - 1;
+      int base = 0;
+      if (lane == leader)
+        base = atomicAdd(&w.sp_cursor[sp], __popc(m));
+      base = __shfl_sync(0xffffffffu, base, leader);
+      if (overlap)
+      {
+        const int slot = w.sp_offset[sp] + base + __popc(m & ((1u << lane) - 1u));
+        w.items[slot] = static_cast<int32_t>(u);
+        w.item_state[slot] = static_cast<int32_t>(s0);
+      }
+    }
+    return;
+  }
   long long s0 = 0, s1 = 0;
   if (inb)
   {
@@ -285,8 +347,8 @@ __global__ void __launch_bounds__(TPB) k_broad(SceneView v, Work w)
   }
   double alo[3], ahi[3];
   loadBox(w, a, s0, s1, alo, ahi);
-  const unsigned lane = threadIdx.x & 31;
-  for (int pi = v.partner_ptr[a]; pi < v.partner_ptr[a + 1]; ++pi)
+  uint32_t bits = 0;
+  for (int pi = p_begin; pi < p_end; ++pi)
   {
     const int sp = v.partner_sp[pi];
     const ShapePairD spd = v.spairs[sp];
@@ -309,24 +371,15 @@ __global__ void __launch_bounds__(TPB) k_broad(SceneView v, Work w)
     for (int r = 0; r < 3; ++r)
       if (alo[r] - bhi[r] > thr || blo[r] - ahi[r] > thr)
         overlap = false;
-    const unsigned m = __ballot_sync(0xffffffffu, overlap);
-    if (m == 0)
-      continue;
-    const int leader = __ffs(m) - 1;
-    if (FILL)
+    const int j = (pi - p_begin) & 31;
+    bits |= (overlap ? 1u : 0u) << j;
+    if ((j == 31 || pi + 1 == p_end) && inb)
     {
-      int base = 0;
-      if (lane == leader)
-        base = atomicAdd(&w.sp_cursor[sp], __popc(m));
-      base = __shfl_sync(0xffffffffu, base, leader);
-      if (overlap)
-      {
-        const int slot = w.sp_offset[sp] + base + __popc(m & ((1u << lane) - 1u));
-        w.items[slot] = static_cast<int32_t>(u);
-        w.item_state[slot] = static_cast<int32_t>(s0);
-      }
+      mask[static_cast<size_t>((pi - p_begin) >> 5) * static_cast<size_t>(w.n_units) + u] = bits;
+      bits = 0;
     }
-    else if (lane == leader)
+    const unsigned m = __ballot_sync(0xffffffffu, overlap);
+    if (m && lane == static_cast<unsigned>(__ffs(m) - 1))
       atomicAdd(&w.sp_count[sp], __popc(m));
   }
 }
@@ -397,9 +450,9 @@ __global__ void __launch_bounds__(TPB) k_finalize(SceneView v, Work w)
     {
       if (links[j] < v.n_active)
       {
-        const double* src = w.poses + (static_cast<size_t>(ui.state0) * v.n_active + links[j]) * 12;
+        const double* src = posePtr(w, links[j], ui.state0);
         p0[j] = Pose<double>::from12(src);
-        p1[j] = w.cast ? Pose<double>::from12(src + static_cast<size_t>(v.n_active) * 12) : p0[j];
+        p1[j] = w.cast ? Pose<double>::from12(src + 12) : p0[j];
       }
       else
       {
@@ -432,8 +485,8 @@ __device__ __forceinline__ void contactTransforms(const SceneView& v, const Work
   {
     const int link = c.link_ids[i];
     const bool active = link < v.n_active;
-    const double* t0 = active ? w.poses + (static_cast<size_t>(c.state) * v.n_active + link) * 12 : v.link_pose + 12 * link;
-    const double* t1 = (active && w.cast) ? t0 + static_cast<size_t>(v.n_active) * 12 : (lvs_discrete ? t0 : nullptr);
+    const double* t0 = active ? posePtr(w, link, c.state) : v.link_pose + 12 * link;
+    const double* t1 = (active && w.cast) ? t0 + 12 : (lvs_discrete ? t0 : nullptr);
     for (int k = 0; k < 12; ++k)
     {
       xf[24 * i + k] = t0[k];

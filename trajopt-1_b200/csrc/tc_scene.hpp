@@ -55,6 +55,7 @@ struct HostScene
   std::vector<PairD> pairs;
   std::vector<ShapePairD> spairs;
   std::vector<int32_t> partner_ptr, partner_sp;  // per active shape: the shape pairs it leads
+  std::vector<int32_t> partner_word_ptr;         // per active shape: first 32-bit word of its broadphase mask
   double margin_buffer{ 0 };
   int max_hull_verts{ 0 };
 };
@@ -78,7 +79,7 @@ struct SceneView
   const double* static_aabb;
   const PairD* pairs;
   const ShapePairD* spairs;
-  const int32_t *partner_ptr, *partner_sp;
+  const int32_t *partner_ptr, *partner_sp, *partner_word_ptr;
   double margin_buffer;
 };
 
@@ -101,6 +102,7 @@ inline SceneView hostView(const HostScene& s)
   v.active_shape_frame = s.active_shape_frame.data();
   v.pairs = s.pairs.data(), v.spairs = s.spairs.data();
   v.partner_ptr = s.partner_ptr.data(), v.partner_sp = s.partner_sp.data();
+  v.partner_word_ptr = s.partner_word_ptr.data();
   v.margin_buffer = s.margin_buffer;
   return v;
 }
@@ -296,10 +298,12 @@ inline void buildHostScene(const tc_scene_desc& d, HostScene& s)
   if (s.pairs.size() > 16384)
     throw SceneError(TC_ERR_UNSUPPORTED, "more than 16384 candidate link pairs");
   s.partner_ptr.assign(1, 0);
+  s.partner_word_ptr.assign(1, 0);
   for (const auto& v : partners)
   {
     s.partner_sp.insert(s.partner_sp.end(), v.begin(), v.end());
     s.partner_ptr.push_back(static_cast<int32_t>(s.partner_sp.size()));
+    s.partner_word_ptr.push_back(s.partner_word_ptr.back() + static_cast<int32_t>((v.size() + 31) / 32));
   }
 }
 }  // namespace tc
