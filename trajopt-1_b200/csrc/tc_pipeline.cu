@@ -173,6 +173,40 @@ __global__ void __launch_bounds__(TPB) k_fk(SceneView v, Work w)
 {
   // per-warp staging tile: 32 poses, rows padded to 13 doubles (bank spread)
   __shared__ double tile[TPB / 32][32 * 13];
+  // the kinematic tables are the same for every thread: one copy per block in shared memory (small scenes; large
+  // ones keep reading them through L1)
+  constexpr int SF = 48, SL = 32;
+  __shared__ double s_origin[SF * 12], s_axis[SF * 3], s_box[SL * 6];
+  __shared__ int s_parent[SF], s_type[SF], s_dof[SF], s_flink[SF], s_lframe[SL], s_sframe[SL];
+  const bool staged = v.n_frames <= SF && v.n_active <= SL && v.n_active_shapes <= SL;
+  if (staged)
+  {
+    for (int e = threadIdx.x; e < v.n_frames * 12; e += blockDim.x)
+      s_origin[e] = v.frame_origin[e];
+    for (int e = threadIdx.x; e < v.n_frames * 3; e += blockDim.x)
+      s_axis[e] = v.frame_axis[e];
+    for (int e = threadIdx.x; e < v.n_frames; e += blockDim.x)
+    {
+      s_parent[e] = v.frame_parent[e], s_type[e] = v.frame_type[e], s_dof[e] = v.frame_dof[e];
+      s_flink[e] = v.frame_link[e];
+    }
+    for (int e = threadIdx.x; e < v.n_active; e += blockDim.x)
+      s_lframe[e] = v.link_frame[e];
+    for (int e = threadIdx.x; e < v.n_active_shapes; e += blockDim.x)
+    {
+      s_sframe[e] = v.active_shape_frame[e];
+      const ShapeD& sh = v.shapes[v.active_shapes[e]];
+      for (int r = 0; r < 3; ++r)
+        s_box[6 * e + r] = sh.aabb_c[r], s_box[6 * e + 3 + r] = sh.aabb_h[r];
+    }
+    __syncthreads();
+  }
+  SceneView t = v;  // table pointers redirected to the staged copies
+  if (staged)
+  {
+    t.frame_origin = s_origin, t.frame_axis = s_axis, t.frame_parent = s_parent, t.frame_type = s_type;
+    t.frame_dof = s_dof, t.frame_link = s_flink, t.link_frame = s_lframe, t.active_shape_frame = s_sframe;
+  }
   const long long s_raw = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
   const bool live = s_raw < w.n_states;
   const long long s = live ? s_raw : w.n_states - 1;  // idle lanes shadow the last state and write nothing
@@ -193,14 +227,14 @@ __global__ void __launch_bounds__(TPB) k_fk(SceneView v, Work w)
   Pose<double> cur = base;
   for (int f = 0; f < v.n_frames; ++f)
   {
-    const int p = v.frame_parent[f];
+    const int p = t.frame_parent[f];
     Pose<double> parent;
     if (p < 0)
       parent = base;
     else if (p == f - 1)
       parent = cur;
-    else if (v.frame_link[p] >= 0)
-      parent = Pose<double>::from12(posePtr(w, v.frame_link[p], s));
+    else if (t.frame_link[p] >= 0)
+      parent = Pose<double>::from12(posePtr(w, t.frame_link[p], s));
     else
     {
       // a branching frame that carries no collision link: rebuild it from the root (rare)
@@ -209,26 +243,26 @@ __global__ void __launch_bounds__(TPB) k_fk(SceneView v, Work w)
       {
         const int g = v.path_frames[a];
         double qa = 0;
-        if (v.frame_type[g] != TC_JOINT_FIXED)
+        if (t.frame_type[g] != TC_JOINT_FIXED)
         {
-          const int j = v.frame_dof[g];
+          const int j = t.frame_dof[g];
           qa = discrete ? q0[j] : linspaced(cnt, q0[j], q0[n + j], i);
         }
-        parent = frameStepQ(v, parent, g, qa);
+        parent = frameStepQ(t, parent, g, qa);
       }
     }
     double qf = 0;
-    if (v.frame_type[f] != TC_JOINT_FIXED)
+    if (t.frame_type[f] != TC_JOINT_FIXED)
     {
-      const int j = v.frame_dof[f];
+      const int j = t.frame_dof[f];
       qf = discrete ? q0[j] : linspaced(cnt, q0[j], q0[n + j], i);
     }
-    cur = frameStepQ(v, parent, f, qf);
+    cur = frameStepQ(t, parent, f, qf);
     // every active link riding on this frame: the warp's 32 records of one link are one contiguous run of
     // the arena, written with coalesced stores after a transpose through shared memory
     for (int l = 0; l < v.n_active; ++l)
     {
-      if (v.link_frame[l] != f)
+      if (t.link_frame[l] != f)
         continue;
       cur.to12(my_tile + lane * 13);
       __syncwarp();
@@ -250,16 +284,28 @@ __global__ void __launch_bounds__(TPB) k_fk(SceneView v, Work w)
       continue;
     for (int a = 0; a < v.n_active_shapes; ++a)
     {
-      if (v.active_shape_frame[a] != f)
+      if (t.active_shape_frame[a] != f)
         continue;
-      const ShapeD& sh = v.shapes[v.active_shapes[a]];
-      const Vec3<double> c = cur.apply(Vec3<double>(sh.aabb_c[0], sh.aabb_c[1], sh.aabb_c[2]));
+      double bc[3], bh[3];
+      if (staged)
+      {
+#pragma unroll
+        for (int r = 0; r < 3; ++r)
+          bc[r] = s_box[6 * a + r], bh[r] = s_box[6 * a + 3 + r];
+      }
+      else
+      {
+        const ShapeD& sh = v.shapes[v.active_shapes[a]];
+#pragma unroll
+        for (int r = 0; r < 3; ++r)
+          bc[r] = sh.aabb_c[r], bh[r] = sh.aabb_h[r];
+      }
+      const Vec3<double> c = cur.apply(Vec3<double>(bc[0], bc[1], bc[2]));
       double* dst = w.aabb + static_cast<size_t>(a) * 6 * w.n_states + s;
 #pragma unroll
       for (int r = 0; r < 3; ++r)
       {
-        const double e = fabs(cur.r[3 * r + 0]) * sh.aabb_h[0] + fabs(cur.r[3 * r + 1]) * sh.aabb_h[1] +
-                         fabs(cur.r[3 * r + 2]) * sh.aabb_h[2];
+        const double e = fabs(cur.r[3 * r + 0]) * bh[0] + fabs(cur.r[3 * r + 1]) * bh[1] + fabs(cur.r[3 * r + 2]) * bh[2];
         dst[static_cast<size_t>(r) * w.n_states] = c.get(r) - e;
         dst[static_cast<size_t>(3 + r) * w.n_states] = c.get(r) + e;
       }
@@ -347,40 +393,61 @@ __global__ void __launch_bounds__(TPB) k_broad(SceneView v, Work w)
   }
   double alo[3], ahi[3];
   loadBox(w, a, s0, s1, alo, ahi);
-  uint32_t bits = 0;
-  for (int pi = p_begin; pi < p_end; ++pi)
+  // the partner list is the same for the whole block: its records (threshold, partner box or partner shape) are
+  // gathered once per tile into shared memory instead of being chased through four tables by every thread
+  struct Partner
   {
-    const int sp = v.partner_sp[pi];
-    const ShapePairD spd = v.spairs[sp];
-    const double thr = v.pairs[spd.pair].thr;
-    const int bidx = v.shapes[spd.sb].active_index;
-    double blo[3], bhi[3];
-    if (bidx < 0)
+    double thr, lo[3], hi[3];
+    int sp, bidx;
+  };
+  constexpr int TILE = 32;
+  __shared__ Partner tile[TILE];
+  uint32_t bits = 0;
+  for (int t0 = p_begin; t0 < p_end; t0 += TILE)
+  {
+    const int tn = min(TILE, p_end - t0);
+    __syncthreads();
+    if (static_cast<int>(threadIdx.x) < tn)
     {
+      Partner pr;
+      pr.sp = v.partner_sp[t0 + threadIdx.x];
+      const ShapePairD spd = v.spairs[pr.sp];
+      pr.thr = v.pairs[spd.pair].thr;
+      pr.bidx = v.shapes[spd.sb].active_index;
 #pragma unroll
       for (int r = 0; r < 3; ++r)
       {
-        blo[r] = v.static_aabb[6 * spd.sb + r];
-        bhi[r] = v.static_aabb[6 * spd.sb + 3 + r];
+        pr.lo[r] = pr.bidx < 0 ? v.static_aabb[6 * spd.sb + r] : 0.0;
+        pr.hi[r] = pr.bidx < 0 ? v.static_aabb[6 * spd.sb + 3 + r] : 0.0;
       }
+      tile[threadIdx.x] = pr;
     }
-    else
-      loadBox(w, bidx, s0, s1, blo, bhi);
-    bool overlap = inb;
-#pragma unroll
-    for (int r = 0; r < 3; ++r)
-      if (alo[r] - bhi[r] > thr || blo[r] - ahi[r] > thr)
-        overlap = false;
-    const int j = (pi - p_begin) & 31;
-    bits |= (overlap ? 1u : 0u) << j;
-    if ((j == 31 || pi + 1 == p_end) && inb)
+    __syncthreads();
+    for (int j = 0; j < tn; ++j)
     {
-      mask[static_cast<size_t>((pi - p_begin) >> 5) * static_cast<size_t>(w.n_units) + u] = bits;
-      bits = 0;
+      const Partner& pr = tile[j];
+      double blo[3], bhi[3];
+      if (pr.bidx < 0)
+      {
+#pragma unroll
+        for (int r = 0; r < 3; ++r)
+          blo[r] = pr.lo[r], bhi[r] = pr.hi[r];
+      }
+      else
+        loadBox(w, pr.bidx, s0, s1, blo, bhi);
+      bool overlap = inb;
+#pragma unroll
+      for (int r = 0; r < 3; ++r)
+        if (alo[r] - bhi[r] > pr.thr || blo[r] - ahi[r] > pr.thr)
+          overlap = false;
+      bits |= (overlap ? 1u : 0u) << j;
+      const unsigned m = __ballot_sync(0xffffffffu, overlap);
+      if (m && lane == static_cast<unsigned>(__ffs(m) - 1))
+        atomicAdd(&w.sp_count[pr.sp], __popc(m));
     }
-    const unsigned m = __ballot_sync(0xffffffffu, overlap);
-    if (m && lane == static_cast<unsigned>(__ffs(m) - 1))
-      atomicAdd(&w.sp_count[sp], __popc(m));
+    if (inb)
+      mask[static_cast<size_t>((t0 - p_begin) >> 5) * static_cast<size_t>(w.n_units) + u] = bits;
+    bits = 0;
   }
 }
 
@@ -413,6 +480,9 @@ __global__ void __launch_bounds__(1024) k_scan_sp(SceneView v, Work w)
   }
 }
 
+#ifndef TC_FINALIZE_MINB
+#define TC_FINALIZE_MINB 3
+#endif
 // ---------------------------------------------------------------------------------------------
 // contact finalisation: ContactResult fields, cast bookkeeping, LVS merge, filters, sort key
 // ---------------------------------------------------------------------------------------------
@@ -433,7 +503,7 @@ __device__ __forceinline__ UnitInfo unitInfo(const Work& w, int u)
   return ui;
 }
 
-__global__ void __launch_bounds__(TPB) k_finalize(SceneView v, Work w)
+__global__ void __launch_bounds__(TPB, TC_FINALIZE_MINB) k_finalize(SceneView v, Work w)
 {
   const long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
   bool valid = false;
@@ -660,18 +730,24 @@ __global__ void __launch_bounds__(TPB) k_rows(SceneView v, Work w, const long lo
 }
 
 // CollisionCost::value / CollisionConstraint::value (collision_terms.cpp:1287-1306,1367-1386)
-__global__ void k_cost_term(SceneView v, Work w, double* cost_term)
+__global__ void __launch_bounds__(TPB) k_cost_term(SceneView v, Work w, double* cost_term)
 {
-  const int k = blockIdx.x * blockDim.x + threadIdx.x;
+  // one warp per term: lanes stride over the term's contacts, fixed-order tree reduction
+  const int k = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const unsigned lane = threadIdx.x & 31;
   if (k >= w.ep.n_terms)
     return;
   double out = 0;
-  for (long long i = w.term_ptr[k]; i < w.term_ptr[k + 1]; ++i)
+  for (long long i = w.term_ptr[k] + lane; i < w.term_ptr[k + 1]; i += 32)
   {
-    const PairD pr = v.pairs[w.contacts[i].pair];
+    const PairD& pr = v.pairs[w.contacts[i].pair];
     out += fmax(pr.margin - w.contacts[i].distance, 0.0) * pr.coeff;
   }
-  cost_term[k] = out;
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1)
+    out += __shfl_down_sync(0xffffffffu, out, o);
+  if (lane == 0)
+    cost_term[k] = out;
 }
 __global__ void k_cost_traj(Work w, const double* cost_term, double* cost_traj)
 {
@@ -1128,7 +1204,7 @@ cudaError_t launchRowBase(const SceneView& v, const Work& w, long long* term_row
 cudaError_t launchCost(const SceneView& v, const Work& w, double* cost_term, double* cost_traj, cudaStream_t st)
 {
   ++launchCounter();
-  k_cost_term<<<gridFor(w.ep.n_terms, TPB), TPB, 0, st>>>(v, w, cost_term);
+  k_cost_term<<<gridFor(static_cast<long long>(w.ep.n_terms) * 32, TPB), TPB, 0, st>>>(v, w, cost_term);
   ++launchCounter();
   k_cost_traj<<<gridFor(w.ep.B, TPB), TPB, 0, st>>>(w, cost_term, cost_traj);
   return cudaGetLastError();
