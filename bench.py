@@ -165,9 +165,9 @@ def run_ours(args, scene, rank, world, local_rank):
         return bc.value, bi.value, br.value
 
     def step_device():
+        # want = cost + contacts + rows: the gradient vectors are folded into the CSR rows inside the pass
         cu.eval_device(sg, q_dev.data_ptr(), B, T_STEPS, capi.EVAL_LVS_CONTINUOUS, res, lvs=LVS, fixed=fixed,
-                       stream=stream)
-        cu.build_rows_device(res)
+                       stream=stream, want=capi.WANT_LINEARISE)
         return pick_best()
 
     def barrier():

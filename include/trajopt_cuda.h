@@ -80,7 +80,13 @@ enum { TC_PRECISION_F64 = 0, TC_PRECISION_F32 = 1 };
 enum { TC_CC_NONE = 0, TC_CC_TIME0 = 1, TC_CC_TIME1 = 2, TC_CC_BETWEEN = 3 };
 
 /* what tc_eval has to produce */
-enum { TC_WANT_COST = 1, TC_WANT_CONTACTS = 2, TC_WANT_GRADIENTS = 4 };
+enum {
+  TC_WANT_COST = 1,
+  TC_WANT_CONTACTS = 2,
+  TC_WANT_GRADIENTS = 4, /* per-contact GradientResults (tc_result_gradients, tc_result_sets, and rows on demand) */
+  TC_WANT_ROWS = 8       /* assemble the constraint rows inside tc_eval; without TC_WANT_GRADIENTS the per-link
+                            gradient vectors are folded into the rows on the fly and never stored */
+};
 
 /* contact flags */
 enum { TC_FLAG_EPA = 1, TC_FLAG_DEGENERATE = 2, TC_FLAG_UNCONVERGED = 4 };

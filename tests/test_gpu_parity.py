@@ -118,3 +118,23 @@ def test_empty_and_errors(cuda):
         cuda.eval(sg, np.zeros((1, 1, 2)), capi.EVAL_LVS_CONTINUOUS)  # segment evaluator needs T >= 2
     with pytest.raises(capi.TcError):
         cuda.eval(sg, np.zeros((1, 2, 2)), 7)
+
+
+@pytest.mark.parametrize("evaluator,stack", [(capi.EVAL_LVS_CONTINUOUS, capi.STACK_IFOPT),
+                                             (capi.EVAL_LVS_CONTINUOUS, capi.STACK_LEGACY),
+                                             (capi.EVAL_DISCRETE, capi.STACK_IFOPT)])
+def test_rows_folded_inside_the_pass_equal_rows_on_demand(cuda, evaluator, stack):
+    """TC_WANT_ROWS without TC_WANT_GRADIENTS (what bench.py times) gives bit-identical rows"""
+    s = helpers.load_scene("arm_around_table")
+    sg = cuda.scene(s, 0.025, 20.0, 0.01)
+    q = helpers.pkg.multistart.make_batch(s, 50, 8, t_steps=6)
+    fixed = np.zeros(q.shape[1], np.uint8)
+    fixed[0] = fixed[-1] = 1
+    a = cuda.eval(sg, q, evaluator, stack=stack, lvs=0.02, fixed=fixed).rows()
+    rb = cuda.eval(sg, q, evaluator, stack=stack, lvs=0.02, fixed=fixed, want=capi.WANT_LINEARISE)
+    b = rb.rows()
+    assert rb.counts()["nnz"] == len(b["val"]) > 0
+    for k in ("row_ptr", "col_idx", "val", "value", "coeff", "margin"):
+        assert (a[k] == b[k]).all(), k
+    with pytest.raises(capi.TcError):
+        rb.gradients()

@@ -23,8 +23,9 @@ EVAL_DISCRETE, EVAL_LVS_DISCRETE, EVAL_CONTINUOUS, EVAL_LVS_CONTINUOUS = 1, 2, 3
 STACK_IFOPT, STACK_LEGACY = 0, 1
 PRECISION_F64, PRECISION_F32 = 0, 1
 CC_NONE, CC_TIME0, CC_TIME1, CC_BETWEEN = 0, 1, 2, 3
-WANT_COST, WANT_CONTACTS, WANT_GRADIENTS = 1, 2, 4
+WANT_COST, WANT_CONTACTS, WANT_GRADIENTS, WANT_ROWS = 1, 2, 4, 8
 WANT_ALL = 7
+WANT_LINEARISE = WANT_COST | WANT_CONTACTS | WANT_ROWS  # rows folded from the gradients on the fly
 FLAG_EPA, FLAG_DEGENERATE, FLAG_UNCONVERGED = 1, 2, 4
 
 _pd = C.POINTER(C.c_double)

@@ -170,6 +170,8 @@ int reserve(DevBuf<T>& b, size_t n, const char* what)
       return s__;                                                                                                    \
   } while (0)
 
+int enqueueRows(tc_result* r, bool fused);
+
 int runEval(tc_scene* scene, const tc_eval_desc* desc, const double* q, int32_t B, int32_t T, tc_result* r,
             cudaStream_t st)
 {
@@ -403,6 +405,8 @@ int runEval(tc_scene* scene, const tc_eval_desc* desc, const double* q, int32_t 
     TC_CUDA(launchGradients(v, w, st));
     r->have_grad = true;
   }
+  if (desc->want & TC_WANT_ROWS)
+    TC_TRY(enqueueRows(r, !r->have_grad));
   if (desc->want & TC_WANT_COST)
   {
     TC_RESERVE(r->cost_term, n_terms);
@@ -439,7 +443,7 @@ int finishEval(tc_result* r)
   o.n_narrowphase = c.n_items;
   o.n_contacts = c.n_valid;
   o.n_rows = c.n_valid;
-  o.nnz = 0;
+  o.nnz = r->have_rows ? c.nnz : 0;
   o.gjk_iters = c.gjk_iters;
   o.support_verts = c.support_verts;
   o.n_epa = c.n_epa;
@@ -469,13 +473,9 @@ int needValid(const tc_result* r)
   return ensureDevice(r->scene->device);
 }
 
-int buildRows(tc_result* r)
+// row assembly on the result's stream; `fused` = gradients recomputed inside the row kernel (no gradient arena)
+int enqueueRows(tc_result* r, bool fused)
 {
-  if (r->have_rows)
-    return TC_OK;
-  if (!r->have_grad)
-    return fail(TC_ERR_INVALID, "rows need an evaluation with TC_WANT_GRADIENTS");
-  LaunchScope scope(r);
   const HostScene& hs = r->scene->host;
   Work& w = r->w;
   const size_t nc = static_cast<size_t>(w.n_contacts);
@@ -488,11 +488,26 @@ int buildRows(tc_result* r)
   TC_RESERVE(r->row_margin, nc);
   w.row_ptr = r->row_ptr.p;
   TC_CUDA(launchRowBase(r->scene->dview, w, r->term_row_base.p, r->stream));
-  TC_CUDA(launchRows(r->scene->dview, w, r->term_row_base.p, r->col_idx.p, r->row_val.p, r->row_value.p,
-                     r->row_coeff.p, r->row_margin.p, r->stream));
+  if (fused)
+    TC_CUDA(launchGradRows(r->scene->dview, w, r->term_row_base.p, r->col_idx.p, r->row_val.p, r->row_value.p,
+                           r->row_coeff.p, r->row_margin.p, r->stream));
+  else
+    TC_CUDA(launchRows(r->scene->dview, w, r->term_row_base.p, r->col_idx.p, r->row_val.p, r->row_value.p,
+                       r->row_coeff.p, r->row_margin.p, r->stream));
+  r->have_rows = true;  // nnz arrives with the next counter snapshot (finishEval / buildRows)
+  return TC_OK;
+}
+
+int buildRows(tc_result* r)
+{
+  if (r->have_rows)
+    return TC_OK;
+  if (!r->have_grad)
+    return fail(TC_ERR_INVALID, "rows need an evaluation with TC_WANT_ROWS or TC_WANT_GRADIENTS");
+  LaunchScope scope(r);
+  TC_TRY(enqueueRows(r, false));
   TC_TRY(readCounters(r));
   r->counts.nnz = r->h_counters->nnz;
-  r->have_rows = true;
   return TC_OK;
 }
 }  // namespace

@@ -150,6 +150,8 @@ cudaError_t launchTransforms(const SceneView& v, const Work& w, double* xf, cuda
 cudaError_t launchRowBase(const SceneView& v, const Work& w, long long* term_row_base, cudaStream_t st);
 cudaError_t launchRows(const SceneView& v, const Work& w, long long* term_row_base, int32_t* col_idx, double* val,
                        double* row_value, double* row_coeff, double* row_margin, cudaStream_t st);
+cudaError_t launchGradRows(const SceneView& v, const Work& w, long long* term_row_base, int32_t* col_idx, double* val,
+                           double* row_value, double* row_coeff, double* row_margin, cudaStream_t st);
 cudaError_t launchCost(const SceneView& v, const Work& w, double* cost_term, double* cost_traj, cudaStream_t st);
 cudaError_t launchSets(const SceneView& v, const Work& w, int max_num_cnt, tc_set* sets, int32_t* set_count,
                        int32_t* set_run, double* values, double* coeffs, double* jac, cudaStream_t st);

@@ -621,6 +621,7 @@ __device__ __forceinline__ int termOfContact(const Work& w, long long i)
   return lo;
 }
 
+template <int NMAX>
 __global__ void __launch_bounds__(TPB) k_grad(SceneView v, Work w)
 {
   const long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
@@ -631,7 +632,7 @@ __global__ void __launch_bounds__(TPB) k_grad(SceneView v, Work w)
   const int n = v.n_dof;
   const double* q0 = w.q + (static_cast<size_t>(c.traj) * w.ep.T + c.term) * n;
   const double* q1 = (w.ep.evaluator == TC_EVAL_DISCRETE) ? q0 : q0 + n;
-  double qt[64], xf[48];
+  double qt[NMAX], xf[48];
   contactTransforms(v, w, c, xf);
   GradOut out;
   contactGradient(v, w.ep, c, xf, q0, q1, w.term_fixed[2 * ti] != 0, w.term_fixed[2 * ti + 1] != 0, qt,
@@ -673,17 +674,11 @@ __global__ void __launch_bounds__(1024) k_row_base(SceneView v, Work w, long lon
 // DiscreteCollisionConstraintD / ContinuousCollisionConstraintD getValues + getJacobian
 // (discrete_collision_constraint.cpp:214-283, continuous_collision_constraint.cpp:311-417) and the legacy
 // CollisionsToDistanceExpressions / CalcDistExpressions* (collision_terms.cpp:341-386,463-554)
-__global__ void __launch_bounds__(TPB) k_rows(SceneView v, Work w, const long long* term_row_base, int32_t* col_idx,
-                                              double* val, double* row_value, double* row_coeff, double* row_margin)
+__device__ __forceinline__ void writeRow(const SceneView& v, const Work& w, long long i, const tc_contact& c,
+                                         const double* g, const tc_gradient& rec, int has,
+                                         const long long* term_row_base, int32_t* col_idx, double* val,
+                                         double* row_value, double* row_coeff, double* row_margin)
 {
-  const long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
-  if (i > w.n_contacts)
-    return;
-  if (i == w.n_contacts)
-  {
-    w.row_ptr[i] = term_row_base[w.ep.n_terms];
-    return;
-  }
   const int k = termOfContact(w, i);
   const int ti = k % w.ep.terms_per_traj;
   const bool f0 = w.term_fixed[2 * ti] != 0, f1 = w.term_fixed[2 * ti + 1] != 0;
@@ -692,11 +687,7 @@ __global__ void __launch_bounds__(TPB) k_rows(SceneView v, Work w, const long lo
   const int nb = (f0 ? 0 : 1) + ((single || f1) ? 0 : 1);
   long long nnz = term_row_base[k] + (i - w.term_ptr[k]) * nb * n;
   w.row_ptr[i] = nnz;
-  const tc_contact& c = w.contacts[i];
   const PairD pr = v.pairs[c.pair];
-  const double* g = w.grad + static_cast<size_t>(i) * 4 * n;
-  const tc_gradient rec = w.grec[i];
-  const int has = w.ghas[i];
   const double* q0 = w.q + (static_cast<size_t>(c.traj) * w.ep.T + c.term) * n;
   double constant = c.distance;
   for (int blk = 0; blk < 2; ++blk)
@@ -727,6 +718,48 @@ __global__ void __launch_bounds__(TPB) k_rows(SceneView v, Work w, const long lo
   row_value[i] = (w.ep.stack == TC_STACK_LEGACY) ? constant : (pr.margin - c.distance);
   row_coeff[i] = pr.coeff;
   row_margin[i] = pr.margin;
+}
+
+__global__ void __launch_bounds__(TPB) k_rows(SceneView v, Work w, const long long* term_row_base, int32_t* col_idx,
+                                              double* val, double* row_value, double* row_coeff, double* row_margin)
+{
+  const long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (i > w.n_contacts)
+    return;
+  if (i == w.n_contacts)
+  {
+    w.row_ptr[i] = term_row_base[w.ep.n_terms];
+    return;
+  }
+  writeRow(v, w, i, w.contacts[i], w.grad + static_cast<size_t>(i) * 4 * v.n_dof, w.grec[i], w.ghas[i], term_row_base,
+           col_idx, val, row_value, row_coeff, row_margin);
+}
+
+// gradients folded straight into the rows (TC_WANT_ROWS without TC_WANT_GRADIENTS): same arithmetic as k_grad
+// followed by k_rows, the per-link gradient vectors live in thread-local memory only
+template <int NMAX>
+__global__ void __launch_bounds__(TPB) k_grad_rows(SceneView v, Work w, const long long* term_row_base, int32_t* col_idx,
+                                                   double* val, double* row_value, double* row_coeff,
+                                                   double* row_margin)
+{
+  const long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (i > w.n_contacts)
+    return;
+  if (i == w.n_contacts)
+  {
+    w.row_ptr[i] = term_row_base[w.ep.n_terms];
+    return;
+  }
+  const tc_contact c = w.contacts[i];
+  const int ti = termOfContact(w, i) % w.ep.terms_per_traj;
+  const int n = v.n_dof;
+  const double* q0 = w.q + (static_cast<size_t>(c.traj) * w.ep.T + c.term) * n;
+  const double* q1 = (w.ep.evaluator == TC_EVAL_DISCRETE) ? q0 : q0 + n;
+  double qt[NMAX], xf[48], g[4 * NMAX];
+  contactTransforms(v, w, c, xf);
+  GradOut out;
+  contactGradient(v, w.ep, c, xf, q0, q1, w.term_fixed[2 * ti] != 0, w.term_fixed[2 * ti + 1] != 0, qt, g, out);
+  writeRow(v, w, i, c, g, out.rec, out.has, term_row_base, col_idx, val, row_value, row_coeff, row_margin);
 }
 
 // CollisionCost::value / CollisionConstraint::value (collision_terms.cpp:1287-1306,1367-1386)
@@ -1180,7 +1213,10 @@ cudaError_t launchGradients(const SceneView& v, const Work& w, cudaStream_t st)
   if (w.n_contacts > 0)
   {
     ++launchCounter();
-    k_grad<<<gridFor(w.n_contacts, TPB), TPB, 0, st>>>(v, w);
+    if (v.n_dof <= 8)
+      k_grad<8><<<gridFor(w.n_contacts, TPB), TPB, 0, st>>>(v, w);
+    else
+      k_grad<64><<<gridFor(w.n_contacts, TPB), TPB, 0, st>>>(v, w);
   }
   return cudaGetLastError();
 }
@@ -1198,6 +1234,19 @@ cudaError_t launchRowBase(const SceneView& v, const Work& w, long long* term_row
 {
   ++launchCounter();
   k_row_base<<<1, 1024, 0, st>>>(v, w, term_row_base);
+  return cudaGetLastError();
+}
+
+cudaError_t launchGradRows(const SceneView& v, const Work& w, long long* term_row_base, int32_t* col_idx, double* val,
+                           double* row_value, double* row_coeff, double* row_margin, cudaStream_t st)
+{
+  ++launchCounter();
+  if (v.n_dof <= 8)
+    k_grad_rows<8><<<gridFor(w.n_contacts + 1, TPB), TPB, 0, st>>>(v, w, term_row_base, col_idx, val, row_value,
+                                                                    row_coeff, row_margin);
+  else
+    k_grad_rows<64><<<gridFor(w.n_contacts + 1, TPB), TPB, 0, st>>>(v, w, term_row_base, col_idx, val, row_value,
+                                                                     row_coeff, row_margin);
   return cudaGetLastError();
 }
 
