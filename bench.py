@@ -296,8 +296,8 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--seeds", type=int, default=4096, help="trajectories per GPU")
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--e2e-chunk", type=int, default=512, help="seeds per sub-batch of the host-buffer (e2e) leg")
-    ap.add_argument("--e2e-workers", type=int, default=4, help="streams / host threads of the e2e leg")
+    ap.add_argument("--e2e-chunk", type=int, default=1024, help="seeds per sub-batch of the host-buffer (e2e) leg")
+    ap.add_argument("--e2e-workers", type=int, default=3, help="streams / host threads of the e2e leg")
     ap.add_argument("--e2e-concurrent", type=int, default=2, help="sub-batches allowed to compute at the same time")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))

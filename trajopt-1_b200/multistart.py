@@ -136,7 +136,7 @@ class PipelinedEvaluator:
                     res = capi.Result(cu, self.scene, cu.new_result(self.scene), len(q), q.shape[1])
                 with self.compute:
                     r = cu.eval(self.scene, q, self.evaluator, lvs=self.lvs, fixed=self.fixed, result=res,
-                                stream=stream.cuda_stream)
+                                stream=stream.cuda_stream, want=capi.WANT_LINEARISE)
                     n = r.counts()["n_contacts"]
                     if n > bufs["cap"]:
                         bufs.update(self._alloc(int(n * 1.25)))
