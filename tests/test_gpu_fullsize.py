@@ -53,37 +53,9 @@ def _properties(cuda, B, min_contacts, lo):
     s, sg = _scene(cuda)
     q = ms.make_batch(s, 0, B)
     r = cuda.eval(sg, q, capi.EVAL_LVS_CONTINUOUS, lvs=ms.LVS, fixed=ms.fixed_steps())
-    c = r.contacts()
-    cnt = r.counts()
+    c = helpers.check_invariants(r, sg, q, capi.EVAL_LVS_CONTINUOUS, ms.LVS, ms.fixed_steps(), ms.BUFFER)
+    assert len(c) > min_contacts
     keys = helpers.packed_keys(c)
-    assert cnt["overflow"] == 0 and cnt["n_unconverged"] == 0 and len(c) == cnt["n_contacts"] > min_contacts
-    assert (np.diff(keys) > 0).all()  # sorted, no duplicates
-    # dense count = sum over segments of (cnt - 1) sweeps x candidate pairs, cnt from the LVS rule
-    seg = np.linalg.norm(np.diff(q, axis=1), axis=2)
-    sweeps = np.where(seg > ms.LVS, np.ceil(seg / ms.LVS) + 1, 2).astype(np.int64) - 1
-    assert cnt["n_units"] == sweeps.sum() and cnt["n_dense"] == sweeps.sum() * sg.num_pairs()
-    assert cnt["n_terms"] == B * (ms.T_STEPS - 1)
-    # term offsets partition the contacts
-    tp = r.term_ptr()
-    term_of = c["traj"].astype(np.int64) * (ms.T_STEPS - 1) + c["term"]
-    assert tp[0] == 0 and tp[-1] == len(c) and (np.diff(tp) >= 0).all()
-    assert (np.searchsorted(term_of, np.arange(cnt["n_terms"] + 1)) == tp).all()
-    # cost = checksum of the contacts: sum coeff * max(margin - d, 0), margin WITHOUT the buffer
-    _, _, margin, coeff = sg.pairs()
-    per = coeff[c["pair"]] * np.maximum(margin[c["pair"]] - c["distance"], 0.0)
-    want = np.bincount(c["traj"], weights=per, minlength=B)
-    _, got = r.cost()
-    assert np.abs(got - want).max() <= 1e-9 * max(1.0, want.max())
-    assert (c["distance"] <= margin[c["pair"]] + ms.BUFFER).all()
-    # rows: one per contact, value = margin - distance, two timestep blocks of n_dof columns at most
-    rows = r.rows()
-    assert len(rows["value"]) == len(c) and rows["row_ptr"][-1] == len(rows["val"])
-    assert np.abs(rows["value"] - (margin[c["pair"]] - c["distance"])).max() <= 1e-12
-    assert (np.diff(rows["row_ptr"]) <= 2 * sg.n_dof).all()
-    first_col = c["term"].astype(np.int64) * sg.n_dof
-    nz = np.diff(rows["row_ptr"]) > 0
-    assert (rows["col_idx"][rows["row_ptr"][:-1][nz]] >= first_col[nz]).all()
-    assert (rows["col_idx"][rows["row_ptr"][1:][nz] - 1] < first_col[nz] + 2 * sg.n_dof).all()
     # determinism and independence from batching
     r2 = cuda.eval(sg, q, capi.EVAL_LVS_CONTINUOUS, lvs=ms.LVS, fixed=ms.fixed_steps())
     c2 = r2.contacts()
