@@ -11,6 +11,7 @@
 #include <cstdlib>
 
 #include "../../trajopt-1_b200/host/tc_evaluators.hpp"
+#include "../../trajopt-1_b200/host/tc_legacy_evaluators.hpp"
 #include "../../trajopt-1_b200/host/tc_scene_file.hpp"
 
 using namespace trajopt_cuda;
@@ -119,6 +120,28 @@ static bool same(const Rows& a, const Rows& b)
   return a.values == b.values && a.jac0 == b.jac0 && a.jac1 == b.jac1;
 }
 
+// legacy stack: one line per affine expression, coefficients scattered over the optimiser's full variable vector
+static void printExprs(const char* tag, int term, legacy::CollisionEvaluator& ev, const legacy::DblVec& x)
+{
+  legacy::AffExprVector exprs;
+  std::vector<double> margins, coeffs;
+  ev.CalcDistExpressions(x, exprs, margins, coeffs);
+  ContactResultMap contacts;
+  ev.CalcCollisions(x, contacts);
+  std::printf("%s %d exprs %zu contacts %zu vars %zu\n", tag, term, exprs.size(), contacts.count(), ev.GetVars().size());
+  for (std::size_t i = 0; i < exprs.size(); ++i)
+  {
+    std::vector<double> dense(x.size(), 0.0);
+    for (std::size_t k = 0; k < exprs[i].size(); ++k)
+      dense[static_cast<std::size_t>(exprs[i].vars[k].index)] += exprs[i].coeffs[k];
+    std::printf("%sX %d %zu %.17g %.17g %.17g %.17g coeffs", tag, term, i, exprs[i].constant, margins[i], coeffs[i],
+                exprs[i].value(x));
+    for (double v : dense)
+      std::printf(" %.17g", v);
+    std::printf("\n");
+  }
+}
+
 int main(int argc, char** argv)
 {
   if (argc < 3)
@@ -156,6 +179,23 @@ int main(int argc, char** argv)
         threw = true;
       }
       std::printf("BADCONFIG %d\n", threw ? 1 : 0);
+      // legacy stack, same four states: SingleTimestepCollisionEvaluator::CalcDistExpressions
+      {
+        legacy::SingleTimestepCollisionEvaluator lev(scene, cfg, legacy::VarVector{ { 0 }, { 1 } });
+        for (int k = 0; k < 4; ++k)
+          printExprs("LEGS", k, lev, legacy::DblVec{ states[k][0], states[k][1] });
+        bool lthrew = false;
+        try
+        {
+          legacy::CastCollisionEvaluator nope(scene, cfg, legacy::VarVector{ { 0 }, { 1 } }, legacy::VarVector{ { 2 }, { 3 } },
+                                              legacy::CollisionExpressionEvaluatorType::START_FREE_END_FREE);
+        }
+        catch (const std::runtime_error&)
+        {
+          lthrew = true;
+        }
+        std::printf("LEGACY_BADCONFIG %d\n", lthrew ? 1 : 0);
+      }
       // max_allowed == 0: contacts only
       ev.calcCollisions(data, VectorXd{ -0.9, 0.01 }, 0);
       std::printf("NOSETS contacts %zu sets %zu\n", data.contact_results_map.count(), data.gradient_results_sets.size());
@@ -207,6 +247,31 @@ int main(int argc, char** argv)
           }
         }
         std::printf("BATCH_PASSES %d %ld\n", kind, batch->passes());
+        // legacy stack: CastCollisionEvaluator / DiscreteCollisionEvaluator per segment, variables of the whole
+        // trajectory in one vector as the legacy problem lays them out (trajopt/src/problem_description.cpp)
+        const legacy::DblVec x(traj.begin(), traj.end());
+        for (int t = 0; t + 1 < T; ++t)
+        {
+          legacy::VarVector v0, v1;
+          for (std::size_t j = 0; j < n; ++j)
+          {
+            v0.push_back({ static_cast<int>(static_cast<std::size_t>(t) * n + j) });
+            v1.push_back({ static_cast<int>(static_cast<std::size_t>(t + 1) * n + j) });
+          }
+          using ET = legacy::CollisionExpressionEvaluatorType;
+          const ET type = fixed[static_cast<std::size_t>(t)] ? ET::START_FIXED_END_FREE :
+                          fixed[static_cast<std::size_t>(t) + 1] ? ET::START_FREE_END_FIXED : ET::START_FREE_END_FREE;
+          if (kind)
+          {
+            legacy::DiscreteCollisionEvaluator lev(scene, cfg, v0, v1, type);
+            printExprs("LEGD", t, lev, x);
+          }
+          else
+          {
+            legacy::CastCollisionEvaluator lev(scene, cfg, v0, v1, type);
+            printExprs("LEGC", t, lev, x);
+          }
+        }
       }
     }
   }

@@ -85,3 +85,79 @@ def test_adaptor_matches_known_answers_and_oracle(tmp_path, oracle):
                 ref = st["jac"][t, :, blk].reshape(-1)
                 err = np.abs(g[key] - ref).max() / max(np.abs(ref).max(), 1e-12)
                 assert err <= 1e-5, (tag, t, key, err)
+
+
+def _parse_exprs(lines, tag):
+    """{term: (n_exprs, n_contacts, n_vars, [constant, margin, coeff, value_at_x], dense coefficients)}"""
+    out = {}
+    for l in lines:
+        tok = l.split()
+        if tok[0] == tag:
+            out[int(tok[1])] = dict(exprs=int(tok[3]), contacts=int(tok[5]), vars=int(tok[7]), head=[], dense=[])
+        elif tok[0] == tag + "X":
+            e = out[int(tok[1])]
+            e["head"].append([float(v) for v in tok[3:7]])
+            e["dense"].append([float(v) for v in tok[tok.index("coeffs") + 1:]])
+    return out
+
+
+def _check_exprs(got, ro, x, term, n_vars_total):
+    """legacy seam: AffExpr i of a term == row i of the oracle's legacy rows for that term, after cleanupAff"""
+    rows, tp = ro.rows(), ro.term_ptr()
+    lo, hi = int(tp[term]), int(tp[term + 1])
+    assert got["exprs"] == hi - lo and got["contacts"] == hi - lo, (term, got["exprs"], hi - lo)
+    for i in range(lo, hi):
+        a, b = int(rows["row_ptr"][i]), int(rows["row_ptr"][i + 1])
+        dense = np.zeros(n_vars_total)
+        np.add.at(dense, rows["col_idx"][a:b], rows["val"][a:b])
+        dense[np.abs(dense) <= 1e-7] = 0.0
+        const, margin, coeff, value = got["head"][i - lo]
+        g = np.array(got["dense"][i - lo])
+        # coefficients that sit within 1e-11 of the pruning threshold may fall either side of it
+        edge = np.abs(np.abs(g + (g == 0) * dense) - 1e-7) < 1e-11
+        err = np.abs(g - dense)[~edge].max() / max(np.abs(dense).max(), 1e-9)
+        assert err <= 1e-5, (term, i, err)
+        assert abs(margin - rows["margin"][i]) <= 1e-12 and abs(coeff - rows["coeff"][i]) <= 1e-12
+        assert abs(const - rows["value"][i]) <= 1e-5 * max(1.0, abs(rows["value"][i])), (term, i, const, rows["value"][i])
+        # the expression evaluated at the linearisation point is the signed distance
+        assert abs(value - (rows["value"][i] + dense @ x)) <= 2e-6, (term, i)
+
+
+@pytest.mark.gpu
+def test_legacy_evaluators_match_oracle_rows(tmp_path, oracle):
+    """seam B2: CalcDistExpressions / CalcCollisions of the legacy evaluator mirror against the oracle's legacy rows"""
+    cmd = _build(tmp_path)
+    r = subprocess.run(cmd, capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr + r.stdout
+    lines = r.stdout.strip().splitlines()
+    assert "LEGACY_BADCONFIG 1" in lines
+    # boxbot, single timestep
+    sb = helpers.load_scene("boxbot")
+    ob = oracle.scene(sb, 0.1, 1.0, 0.01)
+    legs = _parse_exprs(lines, "LEGS")
+    states = [(-1.9, 0.01), (-1.0, 0.01), (0.01, 1.0), (-0.9, 0.01)]
+    assert sorted(legs) == [0, 1, 2, 3]
+    for k, st in enumerate(states):
+        x = np.array(st)
+        ro = oracle.eval(ob, x[None, None], capi.EVAL_DISCRETE, stack=capi.STACK_LEGACY, want=capi.WANT_ALL)
+        assert legs[k]["vars"] == 2
+        _check_exprs(legs[k], ro, x, 0, 2)
+    assert legs[0]["exprs"] == 0 and legs[1]["exprs"] == 1
+    # signed distance of the reference's known answers (error = margin - distance, collision_unit.cpp:103-158)
+    for k, err in ((1, 0.1), (2, 0.1), (3, 0.2)):
+        assert abs((0.1 - legs[k]["head"][0][3]) - err) <= 1e-6
+    # arm_around_table seed trajectory, both two-state evaluators, segment by segment
+    s = helpers.load_scene("arm_around_table")
+    so = oracle.scene(s, 0.025, 20.0, 0.01)
+    traj = s["seed_traj"]
+    T, n = traj.shape
+    fixed = np.zeros(T, np.uint8)
+    fixed[0] = fixed[-1] = 1
+    for tag, ev in (("LEGC", capi.EVAL_LVS_CONTINUOUS), ("LEGD", capi.EVAL_LVS_DISCRETE)):
+        got = _parse_exprs(lines, tag)
+        assert sorted(got) == list(range(T - 1))
+        ro = oracle.eval(so, traj[None], ev, stack=capi.STACK_LEGACY, lvs=0.02, fixed=fixed, want=capi.WANT_ALL)
+        assert sum(g["exprs"] for g in got.values()) > 0
+        for t in range(T - 1):
+            assert got[t]["vars"] == 2 * n
+            _check_exprs(got[t], ro, traj.reshape(-1), t, T * n)

@@ -94,11 +94,12 @@ public:
   Evaluation& operator=(const Evaluation&) = delete;
 
   // one pass over q[B][T][n_dof]; contacts and gradients are copied to the host
-  void run(const TrajOptCollisionConfig& cfg, const double* q, int B, int T, const uint8_t* fixed, HostResult& out)
+  void run(const TrajOptCollisionConfig& cfg, const double* q, int B, int T, const uint8_t* fixed, HostResult& out,
+           int stack = TC_STACK_IFOPT)
   {
     tc_eval_desc d{};
     d.evaluator = static_cast<int32_t>(cfg.type);
-    d.stack = TC_STACK_IFOPT;
+    d.stack = stack;
     d.precision = cfg.precision;
     d.want = TC_WANT_CONTACTS | TC_WANT_GRADIENTS;
     d.lvs_length = cfg.longest_valid_segment_length;
