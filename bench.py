@@ -152,6 +152,7 @@ def run_ours(args, scene, rank, world, local_rank):
         comm = C.c_void_p()
         cu.check(cu.dll.tc_nccl_comm_create(C.c_int(world), C.c_int(rank), idbuf[0], C.byref(comm)))
     cost_traj = np.zeros(B)
+    win_traj = np.zeros(q_host.shape[1:])
     pd = C.POINTER(C.c_double)
 
     def pick_best():
@@ -162,6 +163,10 @@ def run_ours(args, scene, rank, world, local_rank):
         bc, bi, br = C.c_double(), C.c_int64(), C.c_int32()
         cu.check(cu.dll.tc_allgather_best(C.c_double(cost_traj[i]), C.c_int64(rank * B + i), comm, C.c_int(world),
                                           C.c_void_p(stream), C.byref(bc), C.byref(bi), C.byref(br)))
+        # the owner ships the winning trajectory to every rank (T x n_dof doubles)
+        win_traj[:] = q_host[i]
+        cu.check(cu.dll.tc_broadcast_trajectory(win_traj.ctypes.data_as(pd), C.c_size_t(win_traj.size), C.c_int(br.value),
+                                                comm, C.c_void_p(stream)))
         return bc.value, bi.value, br.value
 
     def step_device():

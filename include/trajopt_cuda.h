@@ -278,6 +278,9 @@ void tc_nccl_comm_destroy(void* nccl_comm);
  * (one ncclAllGather of 16 bytes per rank over NVLink) */
 int tc_allgather_best(double local_best_cost, int64_t local_best_idx, void* nccl_comm, int n_ranks,
                       void* cuda_stream, double* best_cost, int64_t* best_idx, int32_t* best_rank);
+/* the owner of the winning seed (best_rank) ships its trajectory traj[n_values] (host memory, T * n_dof doubles) to
+ * every rank: one ncclBroadcast; on return every rank's buffer holds the root's values */
+int tc_broadcast_trajectory(double* traj, size_t n_values, int root_rank, void* nccl_comm, void* cuda_stream);
 
 /* ---- measurement helpers (bench only) ---- */
 /* register-resident DFMA / FFMA loop: returns achieved TFLOP/s (2 flop per FMA) */

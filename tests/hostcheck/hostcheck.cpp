@@ -57,7 +57,8 @@ static int shapeDistance(const HostScene& s, int sa, const double* a0, const dou
       fn(static_cast<size_t>(max_faces));
   std::vector<R> fd(static_cast<size_t>(max_faces));
   std::vector<int> fv(static_cast<size_t>(max_faces)), edges(static_cast<size_t>(max_faces));
-  EpaStore<R> st{ pw.data(), pav.data(), fn.data(), fd.data(), fv.data(), edges.data(), max_verts, max_faces };
+  std::vector<unsigned long long> erow(static_cast<size_t>(max_verts), 0ull);
+  EpaStore<R> st{ pw.data(), pav.data(), fn.data(), fd.data(), fv.data(), edges.data(), max_verts, max_faces, erow.data() };
   // small stores exercise the register-mask fast path of the kernels, large ones the deep-expansion path
   const DistOut<R> o = (max_faces <= 64) ? signedDistance<R, true>(PA, static_cast<R>(A.brad), PB, static_cast<R>(B.brad),
                                                                    static_cast<R>(threshold), st) :

@@ -59,9 +59,13 @@ def _rank_main(rank, world, port, n_seeds, out):
         q = ms.make_batch(scene, first, count)
         r = orc.eval(so, q, capi.EVAL_LVS_CONTINUOUS, lvs=ms.LVS, fixed=ms.fixed_steps(), n_threads=2)
         _, cost = r.cost()
-        best = ms.allgather_best(*ms.select_best(cost, first))
+        local = ms.select_best(cost, first)
+        best = ms.allgather_best(*local)
+        # the owner ships the winning trajectory; the other ranks pass a buffer of the same shape
+        mine = q[local[1] - first] if count else np.zeros(q.shape[1:])
+        win = ms.broadcast_trajectory(mine, best[2])
         dense = r.counts()["n_dense"]
-        out.put((rank, best, dense))
+        out.put((rank, best, dense, win))
     finally:
         dist.destroy_process_group()
 
@@ -77,7 +81,7 @@ def test_two_ranks_agree_with_one(oracle):
     procs = [ctx.Process(target=_rank_main, args=(r, world, port, n_seeds, out)) for r in range(world)]
     for p in procs:
         p.start()
-    got = sorted(out.get(timeout=240) for _ in range(world))
+    got = sorted((out.get(timeout=240) for _ in range(world)), key=lambda g: g[0])
     for p in procs:
         p.join(timeout=60)
         assert p.exitcode == 0
@@ -91,3 +95,6 @@ def test_two_ranks_agree_with_one(oracle):
     assert i == want_idx and abs(c - want_cost) <= 1e-12 * max(1.0, abs(want_cost))
     assert owner == (0 if i < ms.shard(n_seeds, 0, world)[1] else 1)
     assert got[0][2] + got[1][2] == r.counts()["n_dense"]
+    # every rank holds the winner's trajectory after the broadcast
+    want_traj = ms.make_batch(scene, want_idx, 1)[0]
+    assert np.array_equal(got[0][3], want_traj) and np.array_equal(got[1][3], want_traj)

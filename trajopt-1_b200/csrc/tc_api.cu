@@ -523,6 +523,7 @@ struct NcclApi
 {
   void* lib{ nullptr };
   int (*allGather)(const void*, void*, size_t, int, void*, cudaStream_t){ nullptr };
+  int (*broadcast)(const void*, void*, size_t, int, int, void*, cudaStream_t){ nullptr };
   int (*getUniqueId)(void*){ nullptr };
   int (*commInitRank)(void**, int, Id128, int){ nullptr };
   int (*commDestroy)(void*){ nullptr };
@@ -543,11 +544,12 @@ int loadNccl()
   if (!g_nccl.lib)
     return fail(TC_ERR_NCCL, "libnccl.so.2 not found in the process (import torch first or set LD_LIBRARY_PATH)");
   g_nccl.allGather = reinterpret_cast<decltype(g_nccl.allGather)>(dlsym(g_nccl.lib, "ncclAllGather"));
+  g_nccl.broadcast = reinterpret_cast<decltype(g_nccl.broadcast)>(dlsym(g_nccl.lib, "ncclBroadcast"));
   g_nccl.getUniqueId = reinterpret_cast<decltype(g_nccl.getUniqueId)>(dlsym(g_nccl.lib, "ncclGetUniqueId"));
   g_nccl.commInitRank = reinterpret_cast<decltype(g_nccl.commInitRank)>(dlsym(g_nccl.lib, "ncclCommInitRank"));
   g_nccl.commDestroy = reinterpret_cast<decltype(g_nccl.commDestroy)>(dlsym(g_nccl.lib, "ncclCommDestroy"));
   g_nccl.getErrorString = reinterpret_cast<decltype(g_nccl.getErrorString)>(dlsym(g_nccl.lib, "ncclGetErrorString"));
-  if (!g_nccl.allGather || !g_nccl.getUniqueId || !g_nccl.commInitRank || !g_nccl.commDestroy)
+  if (!g_nccl.allGather || !g_nccl.broadcast || !g_nccl.getUniqueId || !g_nccl.commInitRank || !g_nccl.commDestroy)
     return fail(TC_ERR_NCCL, "libnccl lacks the expected entry points");
   return TC_OK;
 }
@@ -1076,6 +1078,35 @@ int tc_allgather_best(double local_best_cost, int64_t local_best_idx, void* nccl
   *best_cost = all[static_cast<size_t>(br)].cost;
   *best_idx = all[static_cast<size_t>(br)].idx;
   *best_rank = br;
+  return TC_OK;
+}
+
+int tc_broadcast_trajectory(double* traj, size_t n_values, int root_rank, void* nccl_comm, void* cuda_stream)
+{
+  if (!nccl_comm || !traj || n_values == 0 || root_rank < 0)
+    return fail(TC_ERR_INVALID, "bad argument");
+  TC_TRY(loadNccl());
+  if (g_device < 0)
+    return fail(TC_ERR_CUDA, "tc_init() has not succeeded");
+  TC_TRY(ensureDevice(g_device));
+  cudaStream_t st = static_cast<cudaStream_t>(cuda_stream);
+  const size_t bytes = n_values * sizeof(double);
+  double* d = nullptr;
+  TC_CUDA(cudaMalloc(reinterpret_cast<void**>(&d), bytes));
+  // every rank uploads its buffer; only the root's content is read by the collective
+  cudaError_t ce = cudaMemcpyAsync(d, traj, bytes, cudaMemcpyHostToDevice, st);
+  int ne = 0;
+  if (ce == cudaSuccess)
+    ne = g_nccl.broadcast(d, d, bytes, /* ncclChar */ 0, root_rank, nccl_comm, st);
+  if (ce == cudaSuccess && ne == 0)
+    ce = cudaMemcpyAsync(traj, d, bytes, cudaMemcpyDeviceToHost, st);
+  if (ce == cudaSuccess && ne == 0)
+    ce = cudaStreamSynchronize(st);
+  cudaFree(d);
+  if (ne)
+    return ncclFail(ne, "ncclBroadcast");
+  if (ce != cudaSuccess)
+    return cudaFail(ce, "tc_broadcast_trajectory");
   return TC_OK;
 }
 }  // extern "C"

@@ -33,14 +33,14 @@ namespace tc
 #define TC_CHUNK 128
 #endif
 #ifndef TC_GJK_RUN
-#define TC_GJK_RUN 1
+#define TC_GJK_RUN 128
 #endif
 #ifndef TC_EPA_RUN
-#define TC_EPA_RUN 4
+#define TC_EPA_RUN 1024
 #endif
 constexpr int CHUNK = TC_CHUNK;  // bucket padding unit = threads per narrow-phase CTA
-// chunks one narrow-phase CTA works through (hulls are staged once per run of one shape pair)
-constexpr int GJK_RUN_CHUNKS = TC_GJK_RUN, EPA_RUN_CHUNKS = TC_EPA_RUN;
+// items one narrow-phase CTA works through (hulls are staged once per run of one shape pair)
+constexpr int GJK_RUN_ITEMS = TC_GJK_RUN, EPA_RUN_ITEMS = TC_EPA_RUN;
 constexpr int MAX_FRAMES = 64;
 #ifndef TC_EPA_VERTS
 #define TC_EPA_VERTS 34

@@ -3,13 +3,27 @@
 // The narrow-phase half of contact_manager_->contactTest(...)
 //   trajopt/src/collision_terms.cpp:667,889,1134,1157
 //   trajopt_ifopt/.../discrete_collision_evaluators.cpp:166; continuous_collision_evaluators.cpp:228,244,449
-// One CTA = CHUNK items of ONE shape pair.  Both hulls are staged global -> shared with TMA bulk copies
+// One CTA = a run of items of ONE shape pair.  Both hulls are staged global -> shared with TMA bulk copies
 // (cp.async.bulk + mbarrier); every lane then runs its own GJK (+EPA) against the staged vertices, so
 // vertex reads are warp-wide broadcasts.  Hits are appended to the raw contact arena with one atomic
 // per warp (ballot + popc).
 #include <cstdlib>
 
 #include "tc_internal.hpp"
+
+#ifndef TC_GJK_DYN
+#define TC_GJK_DYN 1
+#endif
+#ifndef TC_EPA_DYN
+#define TC_EPA_DYN 1
+#endif
+// threads per narrow-phase CTA (the bucket padding unit stays CHUNK); a CTA works through `run_items` items
+#ifndef TC_GJK_NT
+#define TC_GJK_NT 128
+#endif
+#ifndef TC_EPA_NT
+#define TC_EPA_NT 128
+#endif
 
 namespace tc
 {
@@ -159,16 +173,17 @@ __device__ __forceinline__ void addStats(const Work& w, long long gjk, long long
 
 // ---------------------------------------------------------------------------------------------
 // Run = the part of ONE shape pair's bucket that falls into this CTA's range of chunks.  Per run the two
-// hulls are staged with TMA bulk copies; the lanes then work through the run's items with lane refill:
-// every trip of the loop is one GJK (or EPA) iteration for all busy lanes, a lane whose item finished
-// takes the next item of the run, so iteration-count variance between items does not idle lanes.
+// hulls are staged with TMA bulk copies; the warps then take 32-item groups of the run from a shared cursor
+// (s_next) until it is drained, so a warp that drew short items does not wait at the end-of-run barrier for
+// one that drew long ones.
 // ---------------------------------------------------------------------------------------------
 struct RunInfo
 {
   int sp, q0, q1;  // shape pair, item range [q0, q1) of the run (q1 = end of the CTA range or of the bucket)
 };
 
-__device__ __forceinline__ RunInfo findRun(const SceneView& v, const Work& w, int item0, int range_end, RunInfo* s_run)
+__device__ __forceinline__ RunInfo findRun(const SceneView& v, const Work& w, int item0, int range_end, RunInfo* s_run,
+                                           int* s_next)
 {
   if (threadIdx.x == 0)
   {
@@ -186,10 +201,26 @@ __device__ __forceinline__ RunInfo findRun(const SceneView& v, const Work& w, in
     s_run->sp = lo;
     s_run->q0 = item0;
     s_run->q1 = bucket_end < range_end ? bucket_end : range_end;
+    *s_next = item0;
   }
   __syncthreads();
   const RunInfo r = *s_run;
   return r;
+}
+
+// next 32-item group of the run for this warp: DYN takes it from the shared cursor, otherwise warps stride through
+// the run CHUNK items at a time (static assignment)
+template <int DYN>
+__device__ __forceinline__ int nextGroup(int* s_next, int round, int nt)
+{
+  if (DYN)
+  {
+    int group = 0;
+    if ((threadIdx.x & 31) == 0)
+      group = atomicAdd(s_next, 32);
+    return __shfl_sync(0xffffffffu, group, 0);
+  }
+  return *s_next + round * nt + (static_cast<int>(threadIdx.x) & ~31);
 }
 
 template <class R>
@@ -216,21 +247,21 @@ __device__ __forceinline__ void stageHulls(const SceneView& v, const ShapeD& A, 
 // K3a: GJK for every bucketed item.  Separated pairs are finished here; touching / penetrating pairs hand
 // their simplex to the EPA stage through a per-shape-pair packed arena (SoA, 24 doubles per item).
 template <class R, int MINB>
-__global__ void __launch_bounds__(CHUNK, MINB * 128 / CHUNK) k_gjk(SceneView v, Work w)
-#define RUN_CHUNKS GJK_RUN_CHUNKS
+__global__ void __launch_bounds__(TC_GJK_NT, MINB * 128 / TC_GJK_NT) k_gjk(SceneView v, Work w, int run_items)
 {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   __shared__ __align__(8) uint64_t bar;
   __shared__ RunInfo s_run;
+  __shared__ int s_next;
   Vtx<R>* sv = reinterpret_cast<Vtx<R>*>(smem_raw);
-  const int range_end = min(static_cast<long long>(blockIdx.x + 1) * RUN_CHUNKS * CHUNK, w.n_items_padded);
+  const int range_end = static_cast<int>(min(static_cast<long long>(blockIdx.x + 1) * run_items, static_cast<long long>(w.n_items_padded)));
   if (threadIdx.x == 0)
     mbarInit(&bar, 1);
   long long st_gjk = 0, st_scan = 0, st_unconv = 0;
   uint32_t phase = 0;
-  for (int item0 = blockIdx.x * RUN_CHUNKS * CHUNK; item0 < range_end;)
+  for (int item0 = blockIdx.x * run_items; item0 < range_end;)
   {
-    const RunInfo run = findRun(v, w, item0, range_end, &s_run);
+    const RunInfo run = findRun(v, w, item0, range_end, &s_run, &s_next);
     const int sp = run.sp;
     const ShapePairD spd = v.spairs[sp];
     const PairD pr = v.pairs[spd.pair];
@@ -243,11 +274,12 @@ __global__ void __launch_bounds__(CHUNK, MINB * 128 / CHUNK) k_gjk(SceneView v, 
       ++phase;
     }
     const R thr = static_cast<R>(pr.thr);
-    // lock-step rounds: in every round each lane takes one item and all lanes iterate together, so the lanes
-    // of a warp sit in the same simplex case most of the time
-    for (int base = run.q0; base < valid_end; base += CHUNK)
+    for (int round = 0;;)
     {
-      const int slot = base + threadIdx.x;
+      const int group = nextGroup<TC_GJK_DYN>(&s_next, round++, TC_GJK_NT);
+      if (group >= valid_end)
+        break;
+      const int slot = group + (threadIdx.x & 31);
       const bool live = slot < valid_end;
       DistOut<R> d;
       clearDist(d);
@@ -297,31 +329,34 @@ __global__ void __launch_bounds__(CHUNK, MINB * 128 / CHUNK) k_gjk(SceneView v, 
   addStats(w, st_gjk, st_scan, 0, 0, st_unconv);
 }
 
-#undef RUN_CHUNKS
-#define RUN_CHUNKS EPA_RUN_CHUNKS
 // K3b: EPA over the packed hand-off arena, same run structure.
 template <class R, int MINB>
-__global__ void __launch_bounds__(CHUNK, MINB * 128 / CHUNK) k_epa(SceneView v, Work w)
+__global__ void __launch_bounds__(TC_EPA_NT, MINB * 128 / TC_EPA_NT) k_epa(SceneView v, Work w, int run_items)
 {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   __shared__ __align__(8) uint64_t bar;
   __shared__ RunInfo s_run;
+  __shared__ int s_next;
   Vtx<R>* sv = reinterpret_cast<Vtx<R>*>(smem_raw);
-  const int range_end = min(static_cast<long long>(blockIdx.x + 1) * RUN_CHUNKS * CHUNK, w.n_items_padded);
+  const int range_end = static_cast<int>(min(static_cast<long long>(blockIdx.x + 1) * run_items, static_cast<long long>(w.n_items_padded)));
   if (threadIdx.x == 0)
     mbarInit(&bar, 1);
   // thread-local polytope store; raw arrays so that nothing is zero-filled
   R e_raw[(2 * EPA_FAST_VERTS + EPA_FAST_FACES) * 3 + EPA_FAST_FACES];
   int e_int[2 * EPA_FAST_FACES];
+  unsigned long long e_row[EPA_FAST_VERTS];
+#pragma unroll 1
+  for (int i = 0; i < EPA_FAST_VERTS; ++i)
+    e_row[i] = 0;
   Vec3<R>* e_pw = reinterpret_cast<Vec3<R>*>(e_raw);
   EpaStore<R> store{ e_pw, e_pw + EPA_FAST_VERTS, e_pw + 2 * EPA_FAST_VERTS,
                      e_raw + (2 * EPA_FAST_VERTS + EPA_FAST_FACES) * 3, e_int, e_int + EPA_FAST_FACES, EPA_FAST_VERTS,
-                     EPA_FAST_FACES };
+                     EPA_FAST_FACES, e_row };
   long long st_scan = 0, st_epa = 0, st_it = 0, st_unconv = 0;
   uint32_t phase = 0;
-  for (int item0 = blockIdx.x * RUN_CHUNKS * CHUNK; item0 < range_end;)
+  for (int item0 = blockIdx.x * run_items; item0 < range_end;)
   {
-    const RunInfo run = findRun(v, w, item0, range_end, &s_run);
+    const RunInfo run = findRun(v, w, item0, range_end, &s_run, &s_next);
     const int sp = run.sp;
     const int valid_end = min(run.q1, w.sp_offset[sp] + w.epa_cursor[sp]);  // hand-off items of this run
     if (valid_end <= run.q0)
@@ -340,9 +375,12 @@ __global__ void __launch_bounds__(CHUNK, MINB * 128 / CHUNK) k_epa(SceneView v, 
       ++phase;
     }
     const R thr = static_cast<R>(pr.thr);
-    for (int base = run.q0; base < valid_end; base += CHUNK)
+    for (int round = 0;;)
     {
-      const int slot = base + threadIdx.x;
+      const int group = nextGroup<TC_EPA_DYN>(&s_next, round++, TC_EPA_NT);
+      if (group >= valid_end)
+        break;
+      const int slot = group + (threadIdx.x & 31);
       DistOut<R> d;
       clearDist(d);
       d.used_epa = true;
@@ -399,7 +437,6 @@ __global__ void __launch_bounds__(CHUNK, MINB * 128 / CHUNK) k_epa(SceneView v, 
   addStats(w, 0, st_scan, st_epa, st_it, st_unconv);
 }
 
-#undef RUN_CHUNKS
 // deep-expansion path: same arithmetic, polytope in global scratch, vertices read from global memory
 template <class R>
 __global__ void __launch_bounds__(64) k_narrow_deep(SceneView v, Work w, long long n_deep, unsigned char* scratch,
@@ -436,7 +473,7 @@ __global__ void __launch_bounds__(64) k_narrow_deep(SceneView v, Work w, long lo
       const int kt = w.unit_term[u];
       placeItem<R>(v, w, w.state_base[kt] + (u - w.unit_base[kt]), spd, pr, A, B, sceneVerts<R>(v) + A.vert_off,
                    sceneVerts<R>(v) + B.vert_off, PA, PB);
-      EpaStore<R> store{ pw, pa, fn, fd, fv, edges, EPA_DEEP_VERTS, EPA_DEEP_FACES };
+      EpaStore<R> store{ pw, pa, fn, fd, fv, edges, EPA_DEEP_VERTS, EPA_DEEP_FACES, nullptr };
       Simplex<R> S;
       int gjk_scanned;
       distanceGjk<R>(PA, PB, static_cast<R>(pr.thr), S, d);  // already counted by k_gjk
@@ -483,9 +520,12 @@ size_t deepScratchBytesPerThread(int precision)
 template <class R, int GB, int EB>
 static cudaError_t launchNarrowT(const SceneView& v, const Work& w, cudaStream_t st, cudaEvent_t mid)
 {
-  const long long chunks = w.n_items_padded / CHUNK;
-  const unsigned grid_g = static_cast<unsigned>((chunks + GJK_RUN_CHUNKS - 1) / GJK_RUN_CHUNKS);
-  const unsigned grid_e = static_cast<unsigned>((chunks + EPA_RUN_CHUNKS - 1) / EPA_RUN_CHUNKS);
+  // items per CTA; tuning hooks (bench only): TC_GJK_RUN / TC_EPA_RUN in items (multiples of 32)
+  static const char* env_g = getenv("TC_GJK_RUN");
+  static const char* env_e = getenv("TC_EPA_RUN");
+  const int run_g = env_g ? atoi(env_g) : GJK_RUN_ITEMS, run_e = env_e ? atoi(env_e) : EPA_RUN_ITEMS;
+  const unsigned grid_g = static_cast<unsigned>((w.n_items_padded + run_g - 1) / run_g);
+  const unsigned grid_e = static_cast<unsigned>((w.n_items_padded + run_e - 1) / run_e);
   const size_t smem = static_cast<size_t>(2 * v.max_hull_verts) * sizeof(Vtx<R>) + 16;
   cudaFuncSetAttribute(k_gjk<R, GB>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem));
   cudaFuncSetAttribute(k_epa<R, EB>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem));
@@ -493,11 +533,11 @@ static cudaError_t launchNarrowT(const SceneView& v, const Work& w, cudaStream_t
   if (e != cudaSuccess)
     return e;
   ++launchCounter();
-  k_gjk<R, GB><<<grid_g, CHUNK, smem, st>>>(v, w);
+  k_gjk<R, GB><<<grid_g, TC_GJK_NT, smem, st>>>(v, w, run_g);
   if (mid)
     cudaEventRecord(mid, st);
   ++launchCounter();
-  k_epa<R, EB><<<grid_e, CHUNK, smem, st>>>(v, w);
+  k_epa<R, EB><<<grid_e, TC_EPA_NT, smem, st>>>(v, w, run_e);
   return cudaGetLastError();
 }
 

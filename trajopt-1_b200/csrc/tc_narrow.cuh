@@ -15,6 +15,10 @@
 #pragma once
 #include "tc_math.cuh"
 
+#ifndef TC_SCAN_ACC
+#define TC_SCAN_ACC 1  // arg-max accumulators per pose in the hull support scan
+#endif
+
 namespace tc
 {
 enum
@@ -152,6 +156,101 @@ struct Placed
     if (sh.type == SH_HULL)
     {
       const Vec3<R> d0 = p0.rotT(d);
+#if TC_SCAN_ACC == 2
+      // The running arg-max is a serial compare/select chain through `best`; two accumulators per pose (even and odd
+      // vertices) halve it.  Merging with "larger value, lower index on ties" gives the first maximum, as one chain would.
+      const int n2 = sh.nverts & ~1;
+      if (!cast)
+      {
+        R be = lowestReal<R>(), bo = lowestReal<R>();
+        int ie = 0, io = 1;
+        for (int i = 0; i < n2; i += 2)
+        {
+          const Vtx<R> q = sh.verts[i], p = sh.verts[i + 1];
+          const R ve = d0.x * q.x + d0.y * q.y + d0.z * q.z;
+          const R vo = d0.x * p.x + d0.y * p.y + d0.z * p.z;
+          if (ve > be)
+          {
+            be = ve;
+            ie = i;
+          }
+          if (vo > bo)
+          {
+            bo = vo;
+            io = i + 1;
+          }
+        }
+        if (n2 < sh.nverts)
+        {
+          const Vtx<R> q = sh.verts[n2];
+          const R ve = d0.x * q.x + d0.y * q.y + d0.z * q.z;
+          if (ve > be)
+          {
+            be = ve;
+            ie = n2;
+          }
+        }
+        scanned += sh.nverts;
+        const int bi = (bo > be || (bo == be && io < ie)) ? io : ie;
+        const Vtx<R> q = sh.verts[bi];
+        return p0.apply(Vec3<R>(q.x, q.y, q.z));
+      }
+      // swept hull: one pass over the vertices serves both end poses
+      const Vec3<R> d1 = p1.rotT(d);
+      R be0 = lowestReal<R>(), bo0 = lowestReal<R>(), be1 = lowestReal<R>(), bo1 = lowestReal<R>();
+      int ie0 = 0, io0 = 1, ie1 = 0, io1 = 1;
+      for (int i = 0; i < n2; i += 2)
+      {
+        const Vtx<R> q = sh.verts[i], p = sh.verts[i + 1];
+        const R ve0 = d0.x * q.x + d0.y * q.y + d0.z * q.z;
+        const R ve1 = d1.x * q.x + d1.y * q.y + d1.z * q.z;
+        const R vo0 = d0.x * p.x + d0.y * p.y + d0.z * p.z;
+        const R vo1 = d1.x * p.x + d1.y * p.y + d1.z * p.z;
+        if (ve0 > be0)
+        {
+          be0 = ve0;
+          ie0 = i;
+        }
+        if (ve1 > be1)
+        {
+          be1 = ve1;
+          ie1 = i;
+        }
+        if (vo0 > bo0)
+        {
+          bo0 = vo0;
+          io0 = i + 1;
+        }
+        if (vo1 > bo1)
+        {
+          bo1 = vo1;
+          io1 = i + 1;
+        }
+      }
+      if (n2 < sh.nverts)
+      {
+        const Vtx<R> q = sh.verts[n2];
+        const R ve0 = d0.x * q.x + d0.y * q.y + d0.z * q.z;
+        const R ve1 = d1.x * q.x + d1.y * q.y + d1.z * q.z;
+        if (ve0 > be0)
+        {
+          be0 = ve0;
+          ie0 = n2;
+        }
+        if (ve1 > be1)
+        {
+          be1 = ve1;
+          ie1 = n2;
+        }
+      }
+      scanned += 2 * sh.nverts;
+      const int b0 = (bo0 > be0 || (bo0 == be0 && io0 < ie0)) ? io0 : ie0;
+      const int b1 = (bo1 > be1 || (bo1 == be1 && io1 < ie1)) ? io1 : ie1;
+      const Vtx<R> q0 = sh.verts[b0], q1 = sh.verts[b1];
+      const Vec3<R> w0 = p0.apply(Vec3<R>(q0.x, q0.y, q0.z)), w1 = p1.apply(Vec3<R>(q1.x, q1.y, q1.z));
+      return (dot(d, w0) > dot(d, w1)) ? w0 : w1;
+    }
+#else
       if (!cast)
       {
         R best = lowestReal<R>();
@@ -195,6 +294,7 @@ struct Placed
       const Vec3<R> w0 = p0.apply(Vec3<R>(q0.x, q0.y, q0.z)), w1 = p1.apply(Vec3<R>(q1.x, q1.y, q1.z));
       return (dot(d, w0) > dot(d, w1)) ? w0 : w1;
     }
+#endif
     const Vec3<R> w0 = p0.apply(primitiveSupport(sh, p0.rotT(d)));
     if (!cast)
       return w0;
@@ -502,6 +602,7 @@ struct EpaStore
   int* fv;      // packed v0 | v1 << 10 | v2 << 20 ; -1 = dead slot
   int* edges;   // [max_faces] packed a | b << 16
   int max_verts, max_faces;
+  unsigned long long* erow;  // [max_verts] directed-edge bit matrix of the register-mask path (all zero between trips)
 };
 
 template <class R>
@@ -757,6 +858,141 @@ enum
   EPA_OVERFLOW = 3
 };
 
+TC_HD int lowestBit(unsigned long long x)
+{
+#if defined(__CUDA_ARCH__)
+  return __ffsll(static_cast<long long>(x)) - 1;
+#else
+  return __builtin_ffsll(static_cast<long long>(x)) - 1;
+#endif
+}
+
+// One expansion of the register-mask polytope (fast path, <= 64 faces).  The face loop of the general form below
+// runs the horizon bookkeeping inside the per-face loop, so a warp executes it whenever ANY lane sees a visible face
+// at that slot; here the work is split into passes whose trip counts are what each lane needs:
+//   1. every live face: visibility bit + closest surviving face            (uniform body, no branches taken)
+//   2. visible faces only: toggle their directed edges in a per-vertex bit matrix (an interior edge meets its twin
+//      and cancels), 3. visible faces again, slot order: the edges still set are the horizon, in the order the
+//      list-based form produces them, 4. one new face per horizon edge.
+// `erow` is all-zero on entry and on exit.
+template <class R>
+TC_HD int epaTripMasked(const Placed<R>& A, const Placed<R>& B, EpaStore<R>& st, EpaState<R>& E,
+                        unsigned long long* erow, int& scanned)
+{
+  const R DEGENERATE = -lowestReal<R>();
+  const Vec3<R> bn = st.fn[E.best];
+  const Vec3<R> xa = A.support(bn, scanned), xb = B.support(-bn, scanned);
+  const Vec3<R> xw = xa - xb;
+  if (dot(bn, xw) - E.bd <= Tol<R>::epaTol())
+    return EPA_DONE;
+  if (E.iters == EPA_MAX_ITERS)
+    return EPA_UNCONVERGED;
+  if (E.np >= st.max_verts)
+    return EPA_OVERFLOW;
+  int sbest = -1;
+  R sbd = 0;
+  unsigned long long vis = 0;
+  // four faces per trip: their planes are fetched from the thread-local store together, so the loads overlap
+  // instead of each face waiting for its own; the decisions are then applied in slot order
+  for (unsigned long long m = E.alive; m;)
+  {
+    int f[4];
+    bool ok[4];
+    R fd[4];
+    Vec3<R> fn[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k)
+    {
+      ok[k] = m != 0;
+      f[k] = ok[k] ? lowestBit(m) : f[0];
+      m &= m - 1;
+    }
+#pragma unroll
+    for (int k = 0; k < 4; ++k)
+    {
+      fd[k] = st.fd[f[k]];
+      fn[k] = st.fn[f[k]];
+    }
+#pragma unroll
+    for (int k = 0; k < 4; ++k)
+    {
+      const bool visible = (fd[k] != DEGENERATE) && (dot(fn[k], xw) - fd[k] > E.vis_eps);
+      if (ok[k])
+      {
+        if (visible)
+          vis |= 1ull << f[k];
+        else if (sbest < 0 || fd[k] < sbd)
+        {
+          sbest = f[k];
+          sbd = fd[k];
+        }
+      }
+    }
+  }
+  if (vis == 0)
+    return EPA_DONE;  // numerically x is not outside any face although the gap test said so: accept the face
+  for (unsigned long long m = vis; m; m &= m - 1)
+  {
+    const int fv = st.fv[lowestBit(m)];
+    const int v0 = fv & 1023, v1 = (fv >> 10) & 1023, v2 = (fv >> 20) & 1023;
+#pragma unroll
+    for (int e = 0; e < 3; ++e)
+    {
+      const int ea = (e == 0) ? v0 : ((e == 1) ? v1 : v2);
+      const int eb = (e == 0) ? v1 : ((e == 1) ? v2 : v0);
+      const unsigned long long twin = erow[eb];
+      if ((twin >> ea) & 1ull)
+        erow[eb] = twin & ~(1ull << ea);
+      else
+        erow[ea] |= 1ull << eb;
+    }
+  }
+  int ne = 0;
+  bool overflow = false;
+  for (unsigned long long m = vis; m; m &= m - 1)
+  {
+    const int fv = st.fv[lowestBit(m)];
+    const int v0 = fv & 1023, v1 = (fv >> 10) & 1023, v2 = (fv >> 20) & 1023;
+#pragma unroll
+    for (int e = 0; e < 3; ++e)
+    {
+      const int ea = (e == 0) ? v0 : ((e == 1) ? v1 : v2);
+      const int eb = (e == 0) ? v1 : ((e == 1) ? v2 : v0);
+      const unsigned long long row = erow[ea];
+      if ((row >> eb) & 1ull)
+      {
+        erow[ea] = row & ~(1ull << eb);
+        if (ne < st.max_faces)
+          st.edges[ne++] = ea | (eb << 16);
+        else
+          overflow = true;
+      }
+    }
+  }
+  if (overflow)
+    return EPA_OVERFLOW;
+  if (ne == 0)
+    return EPA_DONE;
+  E.alive &= ~vis;
+  const int xi = E.np;
+  st.pw[xi] = xw;
+  st.pa[xi] = xa;
+  E.np += 1;
+  E.best = sbest;
+  E.bd = sbd;
+  for (int q = 0; q < ne; ++q)
+  {
+    R d;
+    const int e = st.edges[q];
+    const int f = epaAddFace<R, true>(E, st, e & 65535, e >> 16, xi, false, d);
+    if (f < 0)
+      return EPA_OVERFLOW;
+    epaOffer(E, f, d);
+  }
+  E.iters += 1;
+  return EPA_CONTINUE;
+}
+
 template <class R, bool MASK>
 TC_HDN int epaTrip(const Placed<R>& A, const Placed<R>& B, EpaStore<R>& st, EpaState<R>& E, int& scanned)
 {
@@ -857,13 +1093,31 @@ TC_HDN void epaFinish(const EpaStore<R>& st, const EpaState<R>& E, EpaOut<R>& r)
   // a larger Minkowski face; the witness is taken on the triangle that is actually closest to the origin.
   int wf = E.best;
   R wbest = -lowestReal<R>(), la = 0, lb = 0, lc = 0;
-  for (int f = 0; f < E.nf; ++f)
+  unsigned long long cand = 0;  // fast path: candidate faces are collected first, then visited
+  if (MASK)
   {
-    if (!epaIsAlive<R, MASK>(E, st, f))
-      continue;
-    const R fd = st.fd[f];
-    if (fd == DEGENERATE || fd > r.depth + E.eps_len)
-      continue;
+    for (unsigned long long m = E.alive; m;)
+    {
+      int f[4];
+      bool ok[4];
+      R fd[4];
+#pragma unroll
+      for (int k = 0; k < 4; ++k)
+      {
+        ok[k] = m != 0;
+        f[k] = ok[k] ? lowestBit(m) : f[0];
+        m &= m - 1;
+      }
+#pragma unroll
+      for (int k = 0; k < 4; ++k)
+        fd[k] = st.fd[f[k]];
+#pragma unroll
+      for (int k = 0; k < 4; ++k)
+        if (ok[k] && fd[k] != DEGENERATE && !(fd[k] > r.depth + E.eps_len))
+          cand |= 1ull << f[k];
+    }
+  }
+  auto visit = [&](int f) {
     const int gv = st.fv[f];
     R a0, a1, a2;
     const Vec3<R> q = closestTriangle(st.pw[gv & 1023], st.pw[(gv >> 10) & 1023], st.pw[(gv >> 20) & 1023], a0, a1, a2);
@@ -873,6 +1127,23 @@ TC_HDN void epaFinish(const EpaStore<R>& st, const EpaState<R>& E, EpaOut<R>& r)
       wbest = q2;
       wf = f;
       la = a0, lb = a1, lc = a2;
+    }
+  };
+  if (MASK)
+  {
+    for (; cand; cand &= cand - 1)
+      visit(lowestBit(cand));
+  }
+  else
+  {
+    for (int f = 0; f < E.nf; ++f)
+    {
+      if (!epaIsAlive<R, MASK>(E, st, f))
+        continue;
+      const R fd = st.fd[f];
+      if (fd == DEGENERATE || fd > r.depth + E.eps_len)
+        continue;
+      visit(f);
     }
   }
   const int gv = st.fv[wf];
@@ -891,8 +1162,17 @@ TC_HDN EpaOut<R> epa(const Placed<R>& A, const Placed<R>& B, const Simplex<R>& s
   if (epaInit<R, MASK>(A, B, start, scale, st, E, r, scanned))
     return r;
   int code;
-  while ((code = epaTrip<R, MASK>(A, B, st, E, scanned)) == EPA_CONTINUE)
+  if constexpr (MASK)
   {
+    while ((code = epaTripMasked<R>(A, B, st, E, st.erow, scanned)) == EPA_CONTINUE)
+    {
+    }
+  }
+  else
+  {
+    while ((code = epaTrip<R, MASK>(A, B, st, E, scanned)) == EPA_CONTINUE)
+    {
+    }
   }
   if (code == EPA_OVERFLOW)
   {

@@ -2,8 +2,8 @@
 seed generation, contiguous sharding of seeds over ranks, and winner selection.
 
 The path shards over independent trajectories only; there is no data-path collective.  The single exchange
-is the all-gather of every rank's (best cost, global seed index): `tc_allgather_best` (NCCL, inside
-libtrajopt_cuda.so) on GPUs; `allgather_best` below is the same reduction over any torch.distributed group and
+is the all-gather of every rank's (best cost, global seed index), followed by a broadcast of the winning
+trajectory from its owner: `tc_allgather_best` / `tc_broadcast_trajectory` (NCCL, inside libtrajopt_cuda.so) on GPUs; `allgather_best` below is the same reduction over any torch.distributed group and
 is what the world_size-2 gloo tests exercise on CPU."""
 import os
 
@@ -76,6 +76,16 @@ def allgather_best(local_cost, local_index, group=None):
     out = [torch.zeros(2, dtype=torch.float64) for _ in range(world)]
     dist.all_gather(out, mine, group=group)
     return reduce_best([(float(t[0]), int(t[1])) for t in out])
+
+
+def broadcast_trajectory(traj, root, group=None):
+    """same exchange as tc_broadcast_trajectory over a torch.distributed group: the owner of the winning seed
+    ships its [T, n_dof] trajectory to every rank"""
+    import torch
+    import torch.distributed as dist
+    t = torch.from_numpy(np.ascontiguousarray(traj, dtype=np.float64).copy())
+    dist.broadcast(t, src=root, group=group)
+    return t.numpy()
 
 
 class PipelinedEvaluator:
