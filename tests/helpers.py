@@ -76,6 +76,15 @@ class HostCheck(capi.Lib):
         return dict(status=status.value, contact=status.value == 1, distance=dist.value, normal=n, pa=pa, pb=pb,
                     epa=bool(epa.value), iters=gi.value, epa_iters=ei.value, scanned=sc.value)
 
+    def support_lut_check(self, scene, dirs):
+        """support look-up table vs full vertex scan on every hull that has a table"""
+        dirs = np.ascontiguousarray(dirs, dtype=np.float64).reshape(-1, 3)
+        mism, cand, vert = C.c_longlong(), C.c_longlong(), C.c_longlong()
+        self.dll.hc_support_lut_check.restype = C.c_int
+        hulls = self.dll.hc_support_lut_check(scene.handle, capi._p(dirs, _pd), C.c_int(len(dirs)), C.byref(mism),
+                                              C.byref(cand), C.byref(vert))
+        return dict(hulls=hulls, mismatches=mism.value, candidates=cand.value, vertices=vert.value)
+
 
 def contact_keys(c):
     """unique key of a contact inside one evaluation"""

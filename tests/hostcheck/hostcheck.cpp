@@ -31,6 +31,43 @@ int hc_scene_create(const tc_scene_desc* d, void** out)
   }
 }
 void hc_scene_destroy(void* s) { delete static_cast<HostScene*>(s); }
+
+// Support look-up table against the full vertex scan: for every hull that has a table, `n_dirs` directions
+// (dirs[n_dirs][3], shape frame) are queried through Placed::support with and without the table.  Returns the number
+// of hulls checked; *mismatches counts queries whose support points differ in any bit.
+int hc_support_lut_check(void* scene, const double* dirs, int n_dirs, long long* mismatches, long long* cand_total,
+                         long long* vert_total)
+{
+  const HostScene& s = *static_cast<HostScene*>(scene);
+  int hulls = 0;
+  *mismatches = 0, *cand_total = 0, *vert_total = 0;
+  for (const ShapeD& sh : s.shapes)
+  {
+    if (!sh.lut_bytes)
+      continue;
+    ++hulls;
+    Placed<double> full, fast;
+    full.sh = makeCore<double>(sh, s.verts.data() + sh.vert_off);
+    fast.sh = makeCore<double>(sh, s.verts.data() + sh.vert_off, s.lut.data() + sh.lut_off);
+    const double ident[12] = { 1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1, 0 };
+    full.p0 = full.p1 = fast.p0 = fast.p1 = Pose<double>::from12(ident);
+    full.cast = fast.cast = false;
+    const uint16_t* off = reinterpret_cast<const uint16_t*>(s.lut.data() + sh.lut_off);
+    for (int k = 0; k < n_dirs; ++k)
+    {
+      const Vec3<double> d(dirs[3 * k], dirs[3 * k + 1], dirs[3 * k + 2]);
+      int sc = 0;
+      const Vec3<double> a = full.support(d, sc), b = fast.support(d, sc);
+      if (std::memcmp(&a, &b, sizeof(a)) != 0)
+        ++*mismatches;
+      const int c = lutCellF(static_cast<float>(d.x), static_cast<float>(d.y), static_cast<float>(d.z));
+      if (c >= 0)
+        *cand_total += off[c + 1] - off[c];
+      *vert_total += sh.vert_cnt;
+    }
+  }
+  return hulls;
+}
 }  // extern "C"
 
 template <class R>
@@ -45,8 +82,9 @@ static int shapeDistance(const HostScene& s, int sa, const double* a0, const dou
   const ShapeD& A = s.shapes[static_cast<size_t>(sa)];
   const ShapeD& B = s.shapes[static_cast<size_t>(sb)];
   Placed<R> PA, PB;
-  PA.sh = makeCore<R>(A, verts.data() + A.vert_off);
-  PB.sh = makeCore<R>(B, verts.data() + B.vert_off);
+  // the support look-up tables are used exactly as the kernels use them
+  PA.sh = makeCore<R>(A, verts.data() + A.vert_off, A.lut_bytes ? s.lut.data() + A.lut_off : nullptr);
+  PB.sh = makeCore<R>(B, verts.data() + B.vert_off, B.lut_bytes ? s.lut.data() + B.lut_off : nullptr);
   PA.p0 = Pose<R>::from12(a0);
   PA.cast = a1 != nullptr;
   PA.p1 = a1 ? Pose<R>::from12(a1) : PA.p0;

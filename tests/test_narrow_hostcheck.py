@@ -55,3 +55,37 @@ def test_fast_and_deep_polytope_agree(oracle, hostcheck):
         if ro["contact"]:
             assert abs(ro["distance"] - small["distance"]) <= 1e-12
     assert seen_overflow > 0
+
+
+def _lut_directions(rng, n):
+    """random directions plus the awkward ones: axes, cube-map face / cell boundaries, tiny and huge magnitudes"""
+    d = [rng.normal(size=(n, 3))]
+    ax = np.concatenate([np.eye(3), -np.eye(3)])
+    d.append(ax)
+    g = np.linspace(-1, 1, 9)  # cell boundaries of the 8 x 8 cube-map faces
+    for m in range(3):
+        for sg in (1.0, -1.0):
+            for u in g:
+                for v in (g[0], g[3], g[4], g[8], 0.123):
+                    e = np.zeros(3)
+                    e[m], e[(m + 1) % 3], e[(m + 2) % 3] = sg, u, v
+                    d.append(e[None])
+                    d.append((e * (1 + 1e-7 * rng.normal(size=3)))[None])
+    out = np.concatenate(d)
+    out = np.concatenate([out, 1e-9 * out[:200], 1e12 * out[:200], 1e-200 * out[:50]])
+    return out
+
+
+@pytest.mark.parametrize("scene_name", ["arm_around_table", "cluttered", "dual_arm"])
+def test_support_lut_equals_full_scan(hostcheck, scene_name):
+    """the cube-map support table returns bit-for-bit the vertex the full scan returns, and prunes most vertices"""
+    from tests import synthetic
+    if scene_name == "arm_around_table":
+        s = helpers.load_scene(scene_name)
+    else:
+        s = synthetic.cluttered_scene() if scene_name == "cluttered" else synthetic.dual_arm_scene()
+    sh = hostcheck.scene(s, 0.025, 20, 0.01)
+    r = hostcheck.support_lut_check(sh, _lut_directions(np.random.default_rng(11), 4000))
+    assert r["hulls"] > 0, r
+    assert r["mismatches"] == 0, r
+    assert r["candidates"] < 0.25 * r["vertices"], r

@@ -630,6 +630,7 @@ int tc_scene_create(const tc_scene_desc* desc, tc_scene** out)
   UP(shapes, h.shapes);
   UP(verts, h.verts);
   UP(verts_f32, vf);
+  UP(lut, h.lut);
   UP(active_shapes, h.active_shapes);
   UP(active_shape_frame, h.active_shape_frame);
   UP(static_aabb, h.static_aabb);

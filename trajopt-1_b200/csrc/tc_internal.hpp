@@ -53,6 +53,7 @@ struct Counters
 {
   long long n_states, n_units, n_items, n_items_padded, n_raw, n_valid, n_deep;
   long long gjk_iters, support_verts, n_epa, epa_iters, n_unconverged, overflow, nnz;
+  long long gjk_cursor, epa_cursor_g;  // work cursors of the warp-persistent narrow-phase kernels
 };
 
 template <class T>

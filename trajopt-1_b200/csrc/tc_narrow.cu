@@ -87,14 +87,15 @@ __device__ __forceinline__ Pose<R> loadPose(const double* p)
 template <class R>
 __device__ __forceinline__ void placeItem(const SceneView& v, const Work& w, long long s0, const ShapePairD& spd,
                                           const PairD& pr, const ShapeD& A, const ShapeD& B, const Vtx<R>* va,
-                                          const Vtx<R>* vb, Placed<R>& PA, Placed<R>& PB)
+                                          const Vtx<R>* vb, Placed<R>& PA, Placed<R>& PB, const void* la = nullptr,
+                                          const void* lb = nullptr)
 {
   const double* pa = posePtr(w, pr.a, s0);
-  PA.sh = makeCore<R>(A, va);
+  PA.sh = makeCore<R>(A, va, la);
   PA.p0 = loadPose<R>(pa);
   PA.cast = w.cast != 0;
   PA.p1 = w.cast ? loadPose<R>(pa + 12) : PA.p0;
-  PB.sh = makeCore<R>(B, vb);
+  PB.sh = makeCore<R>(B, vb, lb);
   if (pr.b < v.n_active)
   {
     const double* pb = posePtr(w, pr.b, s0);
@@ -235,13 +236,32 @@ __device__ __forceinline__ void stageHulls(const SceneView& v, const ShapeD& A, 
     // the previous run's generic-proxy reads of this buffer are ordered before the async-proxy writes
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
     const uint32_t ba = static_cast<uint32_t>(na * sizeof(Vtx<R>)), bb = static_cast<uint32_t>(nb * sizeof(Vtx<R>));
-    mbarExpectTx(bar, ba + bb);
+    mbarExpectTx(bar, ba + bb + static_cast<uint32_t>(A.lut_bytes + B.lut_bytes));
     if (na)
       bulkCopyG2S(sv, sceneVerts<R>(v) + A.vert_off, ba, bar);
     if (nb)
       bulkCopyG2S(sv + na, sceneVerts<R>(v) + B.vert_off, bb, bar);
+    // support look-up tables behind the vertices (all sizes are multiples of 16 bytes)
+    unsigned char* lut = reinterpret_cast<unsigned char*>(sv + na + nb);
+    if (A.lut_bytes)
+      bulkCopyG2S(lut, v.lut + A.lut_off, static_cast<uint32_t>(A.lut_bytes), bar);
+    if (B.lut_bytes)
+      bulkCopyG2S(lut + A.lut_bytes, v.lut + B.lut_off, static_cast<uint32_t>(B.lut_bytes), bar);
   }
   mbarWait(bar, parity);
+}
+
+// staged look-up tables of a run (null for shapes without one)
+template <class R>
+__device__ __forceinline__ const void* stagedLutA(const ShapeD& A, const ShapeD& B, const Vtx<R>* sv)
+{
+  return A.lut_bytes ? static_cast<const void*>(sv + A.vert_cnt + B.vert_cnt) : nullptr;
+}
+template <class R>
+__device__ __forceinline__ const void* stagedLutB(const ShapeD& A, const ShapeD& B, const Vtx<R>* sv)
+{
+  return B.lut_bytes ? static_cast<const void*>(reinterpret_cast<const unsigned char*>(sv + A.vert_cnt + B.vert_cnt) + A.lut_bytes)
+                     : nullptr;
 }
 
 // K3a: GJK for every bucketed item.  Separated pairs are finished here; touching / penetrating pairs hand
@@ -290,7 +310,8 @@ __global__ void __launch_bounds__(TC_GJK_NT, MINB * 128 / TC_GJK_NT) k_gjk(Scene
       {
         u = w.items[slot];
         Placed<R> PA, PB;
-        placeItem<R>(v, w, w.item_state[slot], spd, pr, A, B, sv, sv + A.vert_cnt, PA, PB);
+        placeItem<R>(v, w, w.item_state[slot], spd, pr, A, B, sv, sv + A.vert_cnt, PA, PB, stagedLutA<R>(A, B, sv),
+                     stagedLutB<R>(A, B, sv));
         distanceGjk<R>(PA, PB, thr, S, d);
         st_gjk += d.gjk_iters;
         st_scan += d.scanned;
@@ -400,7 +421,8 @@ __global__ void __launch_bounds__(TC_EPA_NT, MINB * 128 / TC_EPA_NT) k_epa(Scene
           S.lam[i] = 0;
         }
         Placed<R> PA, PB;
-        placeItem<R>(v, w, rec.state, spd, pr, A, B, sv, sv + A.vert_cnt, PA, PB);
+        placeItem<R>(v, w, rec.state, spd, pr, A, B, sv, sv + A.vert_cnt, PA, PB, stagedLutA<R>(A, B, sv),
+                     stagedLutB<R>(A, B, sv));
         d.converged = (nflag & 8) == 0;
         distanceEpa<R, true>(PA, static_cast<R>(A.brad), PB, static_cast<R>(B.brad), thr, S, store, d);
         if (d.status != ND_EPA_OVERFLOW)
@@ -433,6 +455,264 @@ __global__ void __launch_bounds__(TC_EPA_NT, MINB * 128 / TC_EPA_NT) k_epa(Scene
     }
     __syncthreads();
     item0 = run.q1;
+  }
+  addStats(w, 0, st_scan, st_epa, st_it, st_unconv);
+}
+
+// ---------------------------------------------------------------------------------------------
+// Warp-persistent forms (TC_NARROW_WP=1).  Every WARP owns a hull buffer and an mbarrier and draws 32-item groups
+// from ONE global cursor over the padded item space, so there is no CTA barrier to wait at and no tail of long CTAs:
+// consecutive groups mostly belong to the same shape pair, whose hulls then stay staged.
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ int bucketOf(const SceneView& v, const Work& w, int item)
+{
+  int lo = 0, hi = v.n_spairs;
+  while (hi - lo > 1)
+  {
+    const int mid = (lo + hi) >> 1;
+    if (w.sp_offset[mid] <= item)
+      lo = mid;
+    else
+      hi = mid;
+  }
+  return lo;
+}
+
+template <class R>
+__device__ __forceinline__ void stageHullsWarp(const SceneView& v, const ShapeD& A, const ShapeD& B, Vtx<R>* sv,
+                                               uint64_t* bar, uint32_t parity)
+{
+  const int na = A.vert_cnt, nb = B.vert_cnt;
+  __syncwarp();  // every lane is done with the previous pair's vertices
+  if ((threadIdx.x & 31) == 0)
+  {
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    const uint32_t ba = static_cast<uint32_t>(na * sizeof(Vtx<R>)), bb = static_cast<uint32_t>(nb * sizeof(Vtx<R>));
+    mbarExpectTx(bar, ba + bb + static_cast<uint32_t>(A.lut_bytes + B.lut_bytes));
+    if (na)
+      bulkCopyG2S(sv, sceneVerts<R>(v) + A.vert_off, ba, bar);
+    if (nb)
+      bulkCopyG2S(sv + na, sceneVerts<R>(v) + B.vert_off, bb, bar);
+    // support look-up tables behind the vertices (all sizes are multiples of 16 bytes)
+    unsigned char* lut = reinterpret_cast<unsigned char*>(sv + na + nb);
+    if (A.lut_bytes)
+      bulkCopyG2S(lut, v.lut + A.lut_off, static_cast<uint32_t>(A.lut_bytes), bar);
+    if (B.lut_bytes)
+      bulkCopyG2S(lut + A.lut_bytes, v.lut + B.lut_off, static_cast<uint32_t>(B.lut_bytes), bar);
+  }
+  mbarWait(bar, parity);
+}
+
+template <class R, int MINB>
+__global__ void __launch_bounds__(128, MINB) k_gjk_wp(SceneView v, Work w, int hull_stride)
+{
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  __shared__ __align__(8) uint64_t bars[4];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  Vtx<R>* sv = reinterpret_cast<Vtx<R>*>(smem_raw) + static_cast<size_t>(warp) * hull_stride;
+  uint64_t* bar = &bars[warp];
+  if (lane == 0)
+    mbarInit(bar, 1);
+  __syncwarp();
+  long long st_gjk = 0, st_scan = 0, st_unconv = 0;
+  uint32_t phase = 0;
+  int sp = -1, bucket_end = 0, valid_end = 0;
+  ShapePairD spd{};
+  PairD pr{};
+  const ShapeD* A = nullptr;
+  const ShapeD* B = nullptr;
+  R thr = 0;
+  for (;;)
+  {
+    int group = 0;
+    if (lane == 0)
+      group = static_cast<int>(atomicAdd(reinterpret_cast<unsigned long long*>(&w.counters->gjk_cursor), 32ull));
+    group = __shfl_sync(0xffffffffu, group, 0);
+    if (group >= w.n_items_padded)
+      break;
+    if (sp < 0 || group >= bucket_end)
+    {
+      sp = bucketOf(v, w, group);
+      const int off = w.sp_offset[sp], cnt = w.sp_count[sp];
+      bucket_end = off + (cnt + CHUNK - 1) / CHUNK * CHUNK;
+      valid_end = off + cnt;
+      if (group >= valid_end)
+      {
+        sp = -1;  // padding group: nothing staged for this bucket yet
+        continue;
+      }
+      spd = v.spairs[sp];
+      pr = v.pairs[spd.pair];
+      A = &v.shapes[spd.sa];
+      B = &v.shapes[spd.sb];
+      thr = static_cast<R>(pr.thr);
+      if (A->vert_cnt + B->vert_cnt > 0)
+      {
+        stageHullsWarp<R>(v, *A, *B, sv, bar, phase & 1);
+        ++phase;
+      }
+    }
+    if (group >= valid_end)
+      continue;
+    const int slot = group + lane;
+    const bool live = slot < valid_end;
+    DistOut<R> d;
+    clearDist(d);
+    int u = -1;
+    Simplex<R> S;
+    S.n = 0;
+    if (live)
+    {
+      u = w.items[slot];
+      Placed<R> PA, PB;
+      placeItem<R>(v, w, w.item_state[slot], spd, pr, *A, *B, sv, sv + A->vert_cnt, PA, PB, stagedLutA<R>(*A, *B, sv),
+                   stagedLutB<R>(*A, *B, sv));
+      distanceGjk<R>(PA, PB, thr, S, d);
+      st_gjk += d.gjk_iters;
+      st_scan += d.scanned;
+      st_unconv += (d.status != ND_NEED_EPA && !d.converged) ? 1 : 0;
+    }
+    storeHit<R>(w, d, u, sp, d.status == ND_CONTACT);
+    const bool need = d.status == ND_NEED_EPA;
+    const unsigned m = __ballot_sync(0xffffffffu, need);
+    if (m)
+    {
+      const int leader = __ffs(m) - 1;
+      int cur = 0;
+      if (lane == leader)
+        cur = atomicAdd(&w.epa_cursor[sp], __popc(m));
+      cur = __shfl_sync(0xffffffffu, cur, leader);
+      if (need)
+      {
+        EpaRec& rec = w.epa_rec[static_cast<size_t>(w.sp_offset[sp]) + cur + __popc(m & ((1u << lane) - 1u))];
+        rec.unit = u;
+        rec.state = w.item_state[slot];
+        rec.nflag = S.n | (d.converged ? 0 : 8);
+        rec.pad = 0;
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+        {
+          rec.s[6 * i + 0] = S.w[i].x, rec.s[6 * i + 1] = S.w[i].y, rec.s[6 * i + 2] = S.w[i].z;
+          rec.s[6 * i + 3] = S.a[i].x, rec.s[6 * i + 4] = S.a[i].y, rec.s[6 * i + 5] = S.a[i].z;
+        }
+      }
+    }
+  }
+  addStats(w, st_gjk, st_scan, 0, 0, st_unconv);
+}
+
+template <class R, int MINB>
+__global__ void __launch_bounds__(128, MINB) k_epa_wp(SceneView v, Work w, int hull_stride)
+{
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  __shared__ __align__(8) uint64_t bars[4];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  Vtx<R>* sv = reinterpret_cast<Vtx<R>*>(smem_raw) + static_cast<size_t>(warp) * hull_stride;
+  uint64_t* bar = &bars[warp];
+  if (lane == 0)
+    mbarInit(bar, 1);
+  __syncwarp();
+  R e_raw[(2 * EPA_FAST_VERTS + EPA_FAST_FACES) * 3 + EPA_FAST_FACES];
+  int e_int[2 * EPA_FAST_FACES];
+  unsigned long long e_row[EPA_FAST_VERTS];
+#pragma unroll 1
+  for (int i = 0; i < EPA_FAST_VERTS; ++i)
+    e_row[i] = 0;
+  Vec3<R>* e_pw = reinterpret_cast<Vec3<R>*>(e_raw);
+  EpaStore<R> store{ e_pw, e_pw + EPA_FAST_VERTS, e_pw + 2 * EPA_FAST_VERTS,
+                     e_raw + (2 * EPA_FAST_VERTS + EPA_FAST_FACES) * 3, e_int, e_int + EPA_FAST_FACES, EPA_FAST_VERTS,
+                     EPA_FAST_FACES, e_row };
+  long long st_scan = 0, st_epa = 0, st_it = 0, st_unconv = 0;
+  uint32_t phase = 0;
+  int sp = -1, bucket_end = 0, valid_end = 0;
+  ShapePairD spd{};
+  PairD pr{};
+  const ShapeD* A = nullptr;
+  const ShapeD* B = nullptr;
+  R thr = 0;
+  for (;;)
+  {
+    // the cursor runs over the PACKED hand-off space: epa_base[sp] = exclusive scan of the 32-padded hand-off counts
+    int group = 0;
+    if (lane == 0)
+      group = static_cast<int>(atomicAdd(reinterpret_cast<unsigned long long*>(&w.counters->epa_cursor_g), 32ull));
+    group = __shfl_sync(0xffffffffu, group, 0);
+    if (group >= w.n_items_padded)
+      break;
+    if (sp < 0 || group >= bucket_end)
+    {
+      sp = bucketOf(v, w, group);
+      const int off = w.sp_offset[sp];
+      bucket_end = off + (w.sp_count[sp] + CHUNK - 1) / CHUNK * CHUNK;
+      valid_end = off + w.epa_cursor[sp];
+      if (group >= valid_end)
+      {
+        sp = -1;
+        continue;
+      }
+      spd = v.spairs[sp];
+      pr = v.pairs[spd.pair];
+      A = &v.shapes[spd.sa];
+      B = &v.shapes[spd.sb];
+      thr = static_cast<R>(pr.thr);
+      if (A->vert_cnt + B->vert_cnt > 0)
+      {
+        stageHullsWarp<R>(v, *A, *B, sv, bar, phase & 1);
+        ++phase;
+      }
+    }
+    if (group >= valid_end)
+      continue;
+    const int slot = group + lane;
+    DistOut<R> d;
+    clearDist(d);
+    d.used_epa = true;
+    int u = -1;
+    if (slot < valid_end)
+    {
+      const EpaRec& rec = w.epa_rec[slot];
+      u = rec.unit;
+      const int nflag = rec.nflag;
+      Simplex<R> S;
+      S.n = nflag & 7;
+#pragma unroll
+      for (int i = 0; i < 4; ++i)
+      {
+        S.w[i] = Vec3<R>(static_cast<R>(rec.s[6 * i + 0]), static_cast<R>(rec.s[6 * i + 1]), static_cast<R>(rec.s[6 * i + 2]));
+        S.a[i] = Vec3<R>(static_cast<R>(rec.s[6 * i + 3]), static_cast<R>(rec.s[6 * i + 4]), static_cast<R>(rec.s[6 * i + 5]));
+        S.lam[i] = 0;
+      }
+      Placed<R> PA, PB;
+      placeItem<R>(v, w, rec.state, spd, pr, *A, *B, sv, sv + A->vert_cnt, PA, PB, stagedLutA<R>(*A, *B, sv),
+                   stagedLutB<R>(*A, *B, sv));
+      d.converged = (nflag & 8) == 0;
+      distanceEpa<R, true>(PA, static_cast<R>(A->brad), PB, static_cast<R>(B->brad), thr, S, store, d);
+      if (d.status != ND_EPA_OVERFLOW)
+      {
+        st_scan += d.scanned;
+        st_epa += 1;
+        st_it += d.epa_iters;
+        st_unconv += d.converged ? 0 : 1;
+      }
+    }
+    storeHit<R>(w, d, u, sp, d.status == ND_CONTACT);
+    const bool deep = d.status == ND_EPA_OVERFLOW;
+    const unsigned m = __ballot_sync(0xffffffffu, deep);
+    if (m)
+    {
+      const int leader = __ffs(m) - 1;
+      unsigned long long dbase = 0;
+      if (lane == leader)
+        dbase = atomicAdd(reinterpret_cast<unsigned long long*>(&w.counters->n_deep),
+                          static_cast<unsigned long long>(__popc(m)));
+      dbase = __shfl_sync(0xffffffffu, dbase, leader);
+      if (deep)
+      {
+        const unsigned long long ds = dbase + __popc(m & ((1u << lane) - 1u));
+        w.deep_items[2 * ds] = u;
+        w.deep_items[2 * ds + 1] = sp;
+      }
+    }
   }
   addStats(w, 0, st_scan, st_epa, st_it, st_unconv);
 }
@@ -472,7 +752,8 @@ __global__ void __launch_bounds__(64) k_narrow_deep(SceneView v, Work w, long lo
       Placed<R> PA, PB;
       const int kt = w.unit_term[u];
       placeItem<R>(v, w, w.state_base[kt] + (u - w.unit_base[kt]), spd, pr, A, B, sceneVerts<R>(v) + A.vert_off,
-                   sceneVerts<R>(v) + B.vert_off, PA, PB);
+                   sceneVerts<R>(v) + B.vert_off, PA, PB, A.lut_bytes ? v.lut + A.lut_off : nullptr,
+                   B.lut_bytes ? v.lut + B.lut_off : nullptr);
       EpaStore<R> store{ pw, pa, fn, fd, fv, edges, EPA_DEEP_VERTS, EPA_DEEP_FACES, nullptr };
       Simplex<R> S;
       int gjk_scanned;
@@ -526,12 +807,41 @@ static cudaError_t launchNarrowT(const SceneView& v, const Work& w, cudaStream_t
   const int run_g = env_g ? atoi(env_g) : GJK_RUN_ITEMS, run_e = env_e ? atoi(env_e) : EPA_RUN_ITEMS;
   const unsigned grid_g = static_cast<unsigned>((w.n_items_padded + run_g - 1) / run_g);
   const unsigned grid_e = static_cast<unsigned>((w.n_items_padded + run_e - 1) / run_e);
-  const size_t smem = static_cast<size_t>(2 * v.max_hull_verts) * sizeof(Vtx<R>) + 16;
+  const size_t smem = static_cast<size_t>(2 * v.max_hull_verts) * sizeof(Vtx<R>) + 2 * static_cast<size_t>(v.max_lut_bytes) + 16;
   cudaFuncSetAttribute(k_gjk<R, GB>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem));
   cudaFuncSetAttribute(k_epa<R, EB>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem));
   cudaError_t e = launchFill(w.epa_cursor, 0, v.n_spairs, st);
   if (e != cudaSuccess)
     return e;
+  static const char* env_wp = getenv("TC_NARROW_WP");
+  const int wp = env_wp ? atoi(env_wp) : 0;  // bit 0: GJK, bit 1: EPA
+  if (wp)
+  {
+    static int n_sm = 0;
+    if (!n_sm)
+    {
+      int dev = 0;
+      cudaGetDevice(&dev);
+      cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev);
+    }
+    const int stride = 2 * v.max_hull_verts + (2 * v.max_lut_bytes + static_cast<int>(sizeof(Vtx<R>)) - 1) / static_cast<int>(sizeof(Vtx<R>));
+    const size_t smem_wp = static_cast<size_t>(4 * stride) * sizeof(Vtx<R>) + 16;
+    cudaFuncSetAttribute(k_gjk_wp<R, GB>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem_wp));
+    cudaFuncSetAttribute(k_epa_wp<R, EB>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem_wp));
+    ++launchCounter();
+    if (wp & 1)
+      k_gjk_wp<R, GB><<<n_sm * GB, 128, smem_wp, st>>>(v, w, stride);
+    else
+      k_gjk<R, GB><<<grid_g, TC_GJK_NT, smem, st>>>(v, w, run_g);
+    if (mid)
+      cudaEventRecord(mid, st);
+    ++launchCounter();
+    if (wp & 2)
+      k_epa_wp<R, EB><<<n_sm * EB, 128, smem_wp, st>>>(v, w, stride);
+    else
+      k_epa<R, EB><<<grid_e, TC_EPA_NT, smem, st>>>(v, w, run_e);
+    return cudaGetLastError();
+  }
   ++launchCounter();
   k_gjk<R, GB><<<grid_g, TC_GJK_NT, smem, st>>>(v, w, run_g);
   if (mid)

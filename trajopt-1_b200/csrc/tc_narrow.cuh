@@ -15,10 +15,6 @@
 #pragma once
 #include "tc_math.cuh"
 
-#ifndef TC_SCAN_ACC
-#define TC_SCAN_ACC 1  // arg-max accumulators per pose in the hull support scan
-#endif
-
 namespace tc
 {
 enum
@@ -41,29 +37,69 @@ struct alignas(16) Vtx
 struct ShapeD
 {
   int32_t type, link, shape_id, vert_off, vert_cnt, active_index;
+  int32_t lut_off, lut_bytes;  // support look-up table of a hull in the scene's LUT blob (bytes, 16-aligned); -1 = none
   double radius, half_len;  // sphere/capsule: inflation radius of the core; cylinder/cone: solid radius
   double center[3], axis[3];
   double aabb_c[3], aabb_h[3];
   double brad;  // bounding radius of the core about `center`
 };
 
+// ---------------------------------------------------------------------------------------------
+// Support look-up table of a hull.  Directions are binned on a cube map (6 faces x LUT_G x LUT_G cells); a cell
+// lists, in ascending index order, every vertex that can attain the maximum of d.v for SOME direction d of the cell
+// (built conservatively on the host, tc_scene.hpp buildSupportLut: a vertex is left out only when one other vertex
+// beats it by a margin over the whole cone around the cell).  Scanning the list with the same compare therefore
+// returns the vertex a scan of all vertices returns, ties included.  Layout: uint16 off[LUT_CELLS + 1], uint8 cand[].
+// ---------------------------------------------------------------------------------------------
+enum
+{
+  LUT_G = 8,
+  LUT_CELLS = 6 * LUT_G * LUT_G,
+  LUT_MIN_VERTS = 13,  // smaller hulls are scanned in full
+  LUT_MAX_VERTS = 255
+};
+
+// cube-map cell of direction (x, y, z); -1 when the direction cannot be binned (zero / non-finite in float)
+TC_HD int lutCellF(float x, float y, float z)
+{
+  const float ax = x < 0 ? -x : x, ay = y < 0 ? -y : y, az = z < 0 ? -z : z;
+  int m;
+  float mj, u, v;
+  if (ax >= ay && ax >= az)
+    m = 0, mj = x, u = y, v = z;
+  else if (ay >= az)
+    m = 1, mj = y, u = z, v = x;
+  else
+    m = 2, mj = z, u = x, v = y;
+  const float am = mj < 0 ? -mj : mj;
+  if (!(am > 1e-30f) || !(am < 1e30f))
+    return -1;
+  const float inv = (0.5f * LUT_G) / am;
+  int iu = static_cast<int>(u * inv + 0.5f * LUT_G), iv = static_cast<int>(v * inv + 0.5f * LUT_G);
+  iu = iu < 0 ? 0 : (iu > LUT_G - 1 ? LUT_G - 1 : iu);
+  iv = iv < 0 ? 0 : (iv > LUT_G - 1 ? LUT_G - 1 : iv);
+  return ((2 * m + (mj < 0 ? 1 : 0)) * LUT_G + iv) * LUT_G + iu;
+}
+
 template <class R>
 struct ShapeCore
 {
   int type, nverts;
   const Vtx<R>* verts;
+  const uint16_t* lut;  // support look-up table (see above) or null
   R radius, half_len;
   Vec3<R> center, axis;
   TC_HD R coreRadius() const { return (type == SH_SPHERE || type == SH_CAPSULE) ? radius : R(0); }
 };
 
 template <class R>
-TC_HD ShapeCore<R> makeCore(const ShapeD& s, const Vtx<R>* verts)
+TC_HD ShapeCore<R> makeCore(const ShapeD& s, const Vtx<R>* verts, const void* lut = nullptr)
 {
   ShapeCore<R> c;
   c.type = s.type;
   c.nverts = s.vert_cnt;
   c.verts = verts;
+  c.lut = static_cast<const uint16_t*>(lut);
   c.radius = static_cast<R>(s.radius);
   c.half_len = static_cast<R>(s.half_len);
   c.center = Vec3<R>(static_cast<R>(s.center[0]), static_cast<R>(s.center[1]), static_cast<R>(s.center[2]));
@@ -142,6 +178,65 @@ TC_HD Vec3<R> primitiveSupport(const ShapeCore<R>& s, Vec3<R> d)
   return p;
 }
 
+// Out-of-line pieces of the support function.  The narrow-phase kernels are bound by instruction fetch (their hot
+// code is several times the 32 KB L1.5 instruction cache), so everything that is not the common case — a hull without
+// a look-up table, a primitive — is a call, and the inlined part of Placed::support stays small.
+#if defined(__CUDACC__)
+#define TC_NI __host__ __device__ __noinline__
+#else
+#define TC_NI
+#endif
+
+// full scan of a hull for one direction (d0) or, swept, for the directions in both end poses in one pass over the
+// vertices; first maximum in index order.  Returns b0 | b1 << 16.
+template <class R>
+TC_NI int hullScanFull(const Vtx<R>* verts, int n, Vec3<R> d0, Vec3<R> d1, bool cast)
+{
+  R best0 = lowestReal<R>(), best1 = lowestReal<R>();
+  int b0 = 0, b1 = 0;
+  if (!cast)
+  {
+    for (int i = 0; i < n; ++i)
+    {
+      const Vtx<R> q = verts[i];
+      const R v = d0.x * q.x + d0.y * q.y + d0.z * q.z;
+      if (v > best0)
+      {
+        best0 = v;
+        b0 = i;
+      }
+    }
+    return b0;
+  }
+  for (int i = 0; i < n; ++i)
+  {
+    const Vtx<R> q = verts[i];
+    const R v0 = d0.x * q.x + d0.y * q.y + d0.z * q.z;
+    const R v1 = d1.x * q.x + d1.y * q.y + d1.z * q.z;
+    if (v0 > best0)
+    {
+      best0 = v0;
+      b0 = i;
+    }
+    if (v1 > best1)
+    {
+      best1 = v1;
+      b1 = i;
+    }
+  }
+  return b0 | (b1 << 16);
+}
+
+template <class R>
+TC_NI Vec3<R> primitiveSupportPlaced(ShapeCore<R> sh, Pose<R> p0, Pose<R> p1, bool cast, Vec3<R> d)
+{
+  const Vec3<R> w0 = p0.apply(primitiveSupport(sh, p0.rotT(d)));
+  if (!cast)
+    return w0;
+  const Vec3<R> w1 = p1.apply(primitiveSupport(sh, p1.rotT(d)));
+  return (dot(d, w0) > dot(d, w1)) ? w0 : w1;
+}
+
 // A shape placed in the world, optionally swept between two poses (convex hull of both placements):
 // support(d) = better of the supports at pose0 and pose1.
 template <class R>
@@ -151,154 +246,74 @@ struct Placed
   Pose<R> p0, p1;
   bool cast;
 
+  // `scanned` counts the vertices of the hull per queried pose (the work of the plain scan the reference's
+  // convex-hull support does), whether or not the look-up table let most of them be skipped
   TC_HD Vec3<R> support(Vec3<R> d, int& scanned) const
   {
-    if (sh.type == SH_HULL)
+    if (sh.type != SH_HULL)
+      return primitiveSupportPlaced(sh, p0, p1, cast, d);
+    const Vec3<R> d0 = p0.rotT(d);
+    const Vec3<R> d1 = cast ? p1.rotT(d) : d0;
+    int b0 = 0, b1 = 0;
+    bool done = false;
+    if (sh.lut)
     {
-      const Vec3<R> d0 = p0.rotT(d);
-#if TC_SCAN_ACC == 2
-      // The running arg-max is a serial compare/select chain through `best`; two accumulators per pose (even and odd
-      // vertices) halve it.  Merging with "larger value, lower index on ties" gives the first maximum, as one chain would.
-      const int n2 = sh.nverts & ~1;
-      if (!cast)
-      {
-        R be = lowestReal<R>(), bo = lowestReal<R>();
-        int ie = 0, io = 1;
-        for (int i = 0; i < n2; i += 2)
-        {
-          const Vtx<R> q = sh.verts[i], p = sh.verts[i + 1];
-          const R ve = d0.x * q.x + d0.y * q.y + d0.z * q.z;
-          const R vo = d0.x * p.x + d0.y * p.y + d0.z * p.z;
-          if (ve > be)
-          {
-            be = ve;
-            ie = i;
-          }
-          if (vo > bo)
-          {
-            bo = vo;
-            io = i + 1;
-          }
-        }
-        if (n2 < sh.nverts)
-        {
-          const Vtx<R> q = sh.verts[n2];
-          const R ve = d0.x * q.x + d0.y * q.y + d0.z * q.z;
-          if (ve > be)
-          {
-            be = ve;
-            ie = n2;
-          }
-        }
-        scanned += sh.nverts;
-        const int bi = (bo > be || (bo == be && io < ie)) ? io : ie;
-        const Vtx<R> q = sh.verts[bi];
-        return p0.apply(Vec3<R>(q.x, q.y, q.z));
-      }
-      // swept hull: one pass over the vertices serves both end poses
-      const Vec3<R> d1 = p1.rotT(d);
-      R be0 = lowestReal<R>(), bo0 = lowestReal<R>(), be1 = lowestReal<R>(), bo1 = lowestReal<R>();
-      int ie0 = 0, io0 = 1, ie1 = 0, io1 = 1;
-      for (int i = 0; i < n2; i += 2)
-      {
-        const Vtx<R> q = sh.verts[i], p = sh.verts[i + 1];
-        const R ve0 = d0.x * q.x + d0.y * q.y + d0.z * q.z;
-        const R ve1 = d1.x * q.x + d1.y * q.y + d1.z * q.z;
-        const R vo0 = d0.x * p.x + d0.y * p.y + d0.z * p.z;
-        const R vo1 = d1.x * p.x + d1.y * p.y + d1.z * p.z;
-        if (ve0 > be0)
-        {
-          be0 = ve0;
-          ie0 = i;
-        }
-        if (ve1 > be1)
-        {
-          be1 = ve1;
-          ie1 = i;
-        }
-        if (vo0 > bo0)
-        {
-          bo0 = vo0;
-          io0 = i + 1;
-        }
-        if (vo1 > bo1)
-        {
-          bo1 = vo1;
-          io1 = i + 1;
-        }
-      }
-      if (n2 < sh.nverts)
-      {
-        const Vtx<R> q = sh.verts[n2];
-        const R ve0 = d0.x * q.x + d0.y * q.y + d0.z * q.z;
-        const R ve1 = d1.x * q.x + d1.y * q.y + d1.z * q.z;
-        if (ve0 > be0)
-        {
-          be0 = ve0;
-          ie0 = n2;
-        }
-        if (ve1 > be1)
-        {
-          be1 = ve1;
-          ie1 = n2;
-        }
-      }
-      scanned += 2 * sh.nverts;
-      const int b0 = (bo0 > be0 || (bo0 == be0 && io0 < ie0)) ? io0 : ie0;
-      const int b1 = (bo1 > be1 || (bo1 == be1 && io1 < ie1)) ? io1 : ie1;
-      const Vtx<R> q0 = sh.verts[b0], q1 = sh.verts[b1];
-      const Vec3<R> w0 = p0.apply(Vec3<R>(q0.x, q0.y, q0.z)), w1 = p1.apply(Vec3<R>(q1.x, q1.y, q1.z));
-      return (dot(d, w0) > dot(d, w1)) ? w0 : w1;
-    }
-#else
-      if (!cast)
+      // look-up table path: only the vertices that can be extreme for directions of d's cube-map cell are compared
+      const uint8_t* cand = reinterpret_cast<const uint8_t*>(sh.lut + (LUT_CELLS + 1));
+      const int c0 = lutCellF(static_cast<float>(d0.x), static_cast<float>(d0.y), static_cast<float>(d0.z));
+      const int c1 = cast ? lutCellF(static_cast<float>(d1.x), static_cast<float>(d1.y), static_cast<float>(d1.z)) : c0;
+      if (c0 >= 0 && c1 >= 0)
       {
         R best = lowestReal<R>();
-        int bi = 0;
-        for (int i = 0; i < sh.nverts; ++i)
+        const int e0 = sh.lut[c0 + 1];
+#pragma unroll 1
+        for (int k = sh.lut[c0]; k < e0; ++k)
         {
+          const int i = cand[k];
           const Vtx<R> q = sh.verts[i];
-          const R v = d0.x * q.x + d0.y * q.y + d0.z * q.z;
-          if (v > best)
+          const R val = d0.x * q.x + d0.y * q.y + d0.z * q.z;
+          if (val > best)
           {
-            best = v;
-            bi = i;
+            best = val;
+            b0 = i;
           }
         }
-        scanned += sh.nverts;
-        const Vtx<R> q = sh.verts[bi];
-        return p0.apply(Vec3<R>(q.x, q.y, q.z));
-      }
-      // swept hull: one pass over the vertices serves both end poses
-      const Vec3<R> d1 = p1.rotT(d);
-      R best0 = lowestReal<R>(), best1 = lowestReal<R>();
-      int b0 = 0, b1 = 0;
-      for (int i = 0; i < sh.nverts; ++i)
-      {
-        const Vtx<R> q = sh.verts[i];
-        const R v0 = d0.x * q.x + d0.y * q.y + d0.z * q.z;
-        const R v1 = d1.x * q.x + d1.y * q.y + d1.z * q.z;
-        if (v0 > best0)
+        if (cast)
         {
-          best0 = v0;
-          b0 = i;
+          best = lowestReal<R>();
+          const int e1 = sh.lut[c1 + 1];
+#pragma unroll 1
+          for (int k = sh.lut[c1]; k < e1; ++k)
+          {
+            const int i = cand[k];
+            const Vtx<R> q = sh.verts[i];
+            const R val = d1.x * q.x + d1.y * q.y + d1.z * q.z;
+            if (val > best)
+            {
+              best = val;
+              b1 = i;
+            }
+          }
         }
-        if (v1 > best1)
-        {
-          best1 = v1;
-          b1 = i;
-        }
+        done = true;
       }
-      scanned += 2 * sh.nverts;
-      const Vtx<R> q0 = sh.verts[b0], q1 = sh.verts[b1];
-      const Vec3<R> w0 = p0.apply(Vec3<R>(q0.x, q0.y, q0.z)), w1 = p1.apply(Vec3<R>(q1.x, q1.y, q1.z));
-      return (dot(d, w0) > dot(d, w1)) ? w0 : w1;
     }
-#endif
-    const Vec3<R> w0 = p0.apply(primitiveSupport(sh, p0.rotT(d)));
+    if (!done)
+    {
+      const int packed = hullScanFull(sh.verts, sh.nverts, d0, d1, cast);
+      b0 = packed & 65535;
+      b1 = packed >> 16;
+    }
+    const Vtx<R> q0 = sh.verts[b0];
+    const Vec3<R> w0 = p0.apply(Vec3<R>(q0.x, q0.y, q0.z));
     if (!cast)
+    {
+      scanned += sh.nverts;
       return w0;
-    const Vec3<R> w1 = p1.apply(primitiveSupport(sh, p1.rotT(d)));
+    }
+    scanned += 2 * sh.nverts;
+    const Vtx<R> q1 = sh.verts[b1];
+    const Vec3<R> w1 = p1.apply(Vec3<R>(q1.x, q1.y, q1.z));
     return (dot(d, w0) > dot(d, w1)) ? w0 : w1;
   }
   TC_HD Vec3<R> center() const
@@ -389,43 +404,45 @@ TC_HD Vec3<R> closestOnSimplex(const Simplex<R>& s, int m, R lam[4], int& mask)
     mask = ((lam[0] > 0) ? 1 : 0) | ((lam[1] > 0) ? 2 : 0);
     return s.w[0] + t * ab;
   }
-  if (m == 3)
-  {
-    const Vec3<R> p = closestTriangle(s.w[0], s.w[1], s.w[2], lam[0], lam[1], lam[2]);
-    mask = ((lam[0] > 0) ? 1 : 0) | ((lam[1] > 0) ? 2 : 0) | ((lam[2] > 0) ? 4 : 0);
-    return p;
-  }
-  // tetrahedron: faces whose plane separates the origin from the opposite vertex
+  // Triangle (m == 3) and tetrahedron (m == 4) share one instance of the triangle case analysis (code size): the
+  // tetrahedron visits its four faces (0,1,2 | 3), (0,1,3 | 2), (0,2,3 | 1), (1,2,3 | 0) in this order and keeps the
+  // closest point among the faces whose plane separates the origin from the opposite vertex; the triangle is the
+  // single face (0,1,2) taken unconditionally.
   R best = -lowestReal<R>();
   Vec3<R> bestp;
   int bf = -1;
   R bl0 = 0, bl1 = 0, bl2 = 0;
-#define TC_TETRA_FACE(F, I0, I1, I2, I3)                                                                             \
-  {                                                                                                                  \
-    const Vec3<R> a = s.w[I0], b = s.w[I1], c = s.w[I2], d = s.w[I3];                                                \
-    const Vec3<R> n = cross(b - a, c - a);                                                                           \
-    const R sp = -dot(a, n);                                                                                         \
-    const R sd = dot(d - a, n);                                                                                      \
-    const bool degenerate = tc_abs(sd) <= Tol<R>::degRel() * tc_sqrt(norm2(n) * norm2(d - a) + Tol<R>::tiny());                   \
-    if (sp * sd < 0 || degenerate)                                                                                   \
-    {                                                                                                                \
-      R la, lb, lc;                                                                                                  \
-      const Vec3<R> p = closestTriangle(a, b, c, la, lb, lc);                                                        \
-      const R d2 = norm2(p);                                                                                         \
-      if (d2 < best)                                                                                                 \
-      {                                                                                                              \
-        best = d2;                                                                                                   \
-        bestp = p;                                                                                                   \
-        bf = F;                                                                                                      \
-        bl0 = la, bl1 = lb, bl2 = lc;                                                                                \
-      }                                                                                                              \
-    }                                                                                                                \
+  const int nfaces = (m == 4) ? 4 : 1;
+#pragma unroll 1
+  for (int f = 0; f < nfaces; ++f)
+  {
+    const Vec3<R> a = (f < 3) ? s.w[0] : s.w[1];
+    const Vec3<R> b = (f < 2) ? s.w[1] : s.w[2];
+    const Vec3<R> c = (f < 1) ? s.w[2] : s.w[3];
+    bool take = true;
+    if (m == 4)
+    {
+      const Vec3<R> d = (f == 0) ? s.w[3] : ((f == 1) ? s.w[2] : ((f == 2) ? s.w[1] : s.w[0]));
+      const Vec3<R> n = cross(b - a, c - a);
+      const R sp = -dot(a, n);
+      const R sd = dot(d - a, n);
+      const bool degenerate = tc_abs(sd) <= Tol<R>::degRel() * tc_sqrt(norm2(n) * norm2(d - a) + Tol<R>::tiny());
+      take = sp * sd < 0 || degenerate;
+    }
+    if (take)
+    {
+      R la, lb, lc;
+      const Vec3<R> p = closestTriangle(a, b, c, la, lb, lc);
+      const R d2 = norm2(p);
+      if (d2 < best)
+      {
+        best = d2;
+        bestp = p;
+        bf = f;
+        bl0 = la, bl1 = lb, bl2 = lc;
+      }
+    }
   }
-  TC_TETRA_FACE(0, 0, 1, 2, 3)
-  TC_TETRA_FACE(1, 0, 1, 3, 2)
-  TC_TETRA_FACE(2, 0, 2, 3, 1)
-  TC_TETRA_FACE(3, 1, 2, 3, 0)
-#undef TC_TETRA_FACE
   if (bf < 0)
   {
     lam[0] = lam[1] = lam[2] = lam[3] = R(0.25);
@@ -515,25 +532,30 @@ TC_HD GjkOut<R> gjk(const Placed<R>& A, const Placed<R>& B, R threshold_core, Si
   Vec3<R> v = A.center() - B.center();
   if (norm2(v) < Tol<R>::centerTiny())
     v = Vec3<R>(1, 0, 0);
-  {
-    const Vec3<R> a = A.support(-v, scanned), b = B.support(v, scanned);
-    S.w[0] = a - b;
-    S.a[0] = a;
-  }
-  S.n = 1;
+  S.n = 0;
   S.lam[0] = 1, S.lam[1] = 0, S.lam[2] = 0, S.lam[3] = 0;
-  v = S.w[0];
-  R vv = norm2(v);
+  R vv = 0;
   const R touch2 = Tol<R>::gjkTouch() * Tol<R>::gjkTouch();
-  for (r.iters = 1; r.iters <= GJK_MAX_ITERS; ++r.iters)
+  // trip 0 places the first simplex point (support along the centre difference); it shares the one support site
+  // of the loop so that the support code exists once in the kernel
+  for (r.iters = 0; r.iters <= GJK_MAX_ITERS; ++r.iters)
   {
-    if (vv <= touch2)
+    if (r.iters > 0 && vv <= touch2)
     {
       r.intersect = true;
       break;
     }
     const Vec3<R> a = A.support(-v, scanned), b = B.support(v, scanned);
     const Vec3<R> w = a - b;
+    if (r.iters == 0)
+    {
+      S.w[0] = w;
+      S.a[0] = a;
+      S.n = 1;
+      v = w;
+      vv = norm2(v);
+      continue;
+    }
     const R vw = dot(v, w);
     if (vw > 0 && vw * vw > threshold_core * threshold_core * vv)
     {
@@ -746,56 +768,51 @@ TC_HDN int epaInit(const Placed<R>& A, const Placed<R>& B, const Simplex<R>& sta
     if (tc_abs(vol) <= E.eps_len * E.eps_len * E.eps_len)
       E.np = 3;
   }
-  if (E.np == 1)
+  // Probing for the missing points, one support site for all three stages (code size): a point (np == 1) tries the
+  // six axis directions for a second point, a segment (np == 2) four directions across it for a third, a triangle
+  // (np == 3) its two normals for a fourth.  A stage that finds nothing ends the probing (flat difference).
+  for (int k = 0; E.np < 4;)
   {
-    for (int k = 0; k < 6 && E.np == 1; ++k)
+    const int lim = (E.np == 1) ? 6 : ((E.np == 2) ? 4 : 2);
+    if (k >= lim)
+      break;
+    Vec3<R> d, e, n;
+    R en = 0, area = 0;
+    if (E.np == 1)
     {
       const R sg = (k & 1) ? R(-1) : R(1);
-      const Vec3<R> d((k >> 1) == 0 ? sg : R(0), (k >> 1) == 1 ? sg : R(0), (k >> 1) == 2 ? sg : R(0));
-      const Vec3<R> a = A.support(d, scanned), b = B.support(-d, scanned);
-      const Vec3<R> w = a - b;
-      if (norm(w - st.pw[0]) > E.eps_len)
-      {
-        st.pw[1] = w;
-        st.pa[1] = a;
-        E.np = 2;
-      }
+      d = Vec3<R>((k >> 1) == 0 ? sg : R(0), (k >> 1) == 1 ? sg : R(0), (k >> 1) == 2 ? sg : R(0));
     }
-  }
-  if (E.np == 2)
-  {
-    const Vec3<R> e = st.pw[1] - st.pw[0];
-    const Vec3<R> d0 = leastAxisCross(e);
-    const Vec3<R> d1 = cross(e, d0);
-    const R en = norm(e);
-    for (int k = 0; k < 4 && E.np == 2; ++k)
+    else if (E.np == 2)
     {
-      const Vec3<R> d = (k == 0) ? d0 : ((k == 1) ? -d0 : ((k == 2) ? d1 : -d1));
-      const Vec3<R> a = A.support(d, scanned), b = B.support(-d, scanned);
-      const Vec3<R> w = a - b;
-      if (norm(cross(w - st.pw[0], e)) > E.eps_len * en)
-      {
-        st.pw[2] = w;
-        st.pa[2] = a;
-        E.np = 3;
-      }
+      e = st.pw[1] - st.pw[0];
+      const Vec3<R> d0 = leastAxisCross(e);
+      const Vec3<R> d1 = cross(e, d0);
+      en = norm(e);
+      d = (k == 0) ? d0 : ((k == 1) ? -d0 : ((k == 2) ? d1 : -d1));
     }
-  }
-  if (E.np == 3)
-  {
-    const Vec3<R> n = cross(st.pw[1] - st.pw[0], st.pw[2] - st.pw[0]);
-    const R area = norm(n);
-    for (int sgn = 0; sgn < 2 && E.np == 3; ++sgn)
+    else
     {
-      const Vec3<R> d = (sgn == 0) ? n : -n;
-      const Vec3<R> a = A.support(d, scanned), b = B.support(-d, scanned);
-      const Vec3<R> w = a - b;
-      if (tc_abs(dot(w - st.pw[0], n)) > E.eps_len * area)
-      {
-        st.pw[3] = w;
-        st.pa[3] = a;
-        E.np = 4;
-      }
+      n = cross(st.pw[1] - st.pw[0], st.pw[2] - st.pw[0]);
+      area = norm(n);
+      d = (k == 0) ? n : -n;
+    }
+    const Vec3<R> a = A.support(d, scanned), b = B.support(-d, scanned);
+    const Vec3<R> w = a - b;
+    bool accept;
+    if (E.np == 1)
+      accept = norm(w - st.pw[0]) > E.eps_len;
+    else if (E.np == 2)
+      accept = norm(cross(w - st.pw[0], e)) > E.eps_len * en;
+    else
+      accept = tc_abs(dot(w - st.pw[0], n)) > E.eps_len * area;
+    ++k;
+    if (accept)
+    {
+      st.pw[E.np] = w;
+      st.pa[E.np] = a;
+      E.np += 1;
+      k = 0;
     }
   }
   if (E.np < 4)

@@ -7,6 +7,7 @@
 // unit-test harness can reuse it without CUDA.
 #pragma once
 #include <cmath>
+#include <cstring>
 #include <cstdint>
 #include <stdexcept>
 #include <string>
@@ -58,12 +59,16 @@ struct HostScene
   std::vector<int32_t> partner_word_ptr;         // per active shape: first 32-bit word of its broadphase mask
   double margin_buffer{ 0 };
   int max_hull_verts{ 0 };
+  std::vector<uint8_t> lut;  // support look-up tables of the hulls (ShapeD::lut_off / lut_bytes)
+  int max_lut_bytes{ 0 };
 };
 
 // raw-pointer view of the tables (host vectors in the test harness, device arrays in the kernels)
 struct SceneView
 {
   int n_dof, n_frames, n_links, n_active, n_shapes, n_active_shapes, n_pairs, n_spairs, max_hull_verts;
+  int max_lut_bytes;
+  const uint8_t* lut;
   const int32_t *frame_parent, *frame_type, *frame_dof;
   const double *frame_axis, *frame_origin;
   double base_pose[12];
@@ -90,6 +95,8 @@ inline SceneView hostView(const HostScene& s)
   v.n_shapes = s.n_shapes, v.n_active_shapes = s.n_active_shapes;
   v.n_pairs = static_cast<int>(s.pairs.size()), v.n_spairs = static_cast<int>(s.spairs.size());
   v.max_hull_verts = s.max_hull_verts;
+  v.max_lut_bytes = s.max_lut_bytes;
+  v.lut = s.lut.data();
   v.frame_parent = s.frame_parent.data(), v.frame_type = s.frame_type.data(), v.frame_dof = s.frame_dof.data();
   v.frame_axis = s.frame_axis.data(), v.frame_origin = s.frame_origin.data();
   for (int i = 0; i < 12; ++i)
@@ -105,6 +112,68 @@ inline SceneView hostView(const HostScene& s)
   v.partner_word_ptr = s.partner_word_ptr.data();
   v.margin_buffer = s.margin_buffer;
   return v;
+}
+
+// Support look-up table of one hull (layout and use: tc_narrow.cuh).  For every cube-map cell take the cone around
+// the cell's centre direction c that contains the cell (half-angle theta = largest angle to a corner, plus slack for
+// the float binning on the device).  Vertex i cannot be extreme for any direction of the cone when some vertex j has
+// d.(v_j - v_i) > 0 for every d of the cone, i.e. c.e > |e| sin(theta) with e = v_j - v_i; a margin keeps the
+// decision clear of rounding on either side.  Everything else is listed.  Appends to `blob`, 16-byte aligned.
+inline void buildSupportLut(const Vtx<double>* verts, int n, std::vector<uint8_t>& blob)
+{
+  std::vector<uint16_t> off(LUT_CELLS + 1, 0);
+  std::vector<uint8_t> cand;
+  std::vector<double> proj(static_cast<size_t>(n));
+  for (int cell = 0; cell < LUT_CELLS; ++cell)
+  {
+    const int iu = cell % LUT_G, iv = (cell / LUT_G) % LUT_G, face = cell / (LUT_G * LUT_G);
+    const int m = face / 2;
+    const double sg = (face & 1) ? -1.0 : 1.0;
+    auto dir = [&](double u, double v) {
+      double d[3];
+      d[m] = sg;
+      d[(m + 1) % 3] = u;
+      d[(m + 2) % 3] = v;
+      const double nn = std::sqrt(d[0] * d[0] + d[1] * d[1] + d[2] * d[2]);
+      return Vec3<double>(d[0] / nn, d[1] / nn, d[2] / nn);
+    };
+    const double u0 = -1.0 + 2.0 * iu / LUT_G, u1 = -1.0 + 2.0 * (iu + 1) / LUT_G;
+    const double v0 = -1.0 + 2.0 * iv / LUT_G, v1 = -1.0 + 2.0 * (iv + 1) / LUT_G;
+    const Vec3<double> c = dir(0.5 * (u0 + u1), 0.5 * (v0 + v1));
+    double cmin = 1.0;
+    for (int k = 0; k < 4; ++k)
+      cmin = std::fmin(cmin, dot(c, dir((k & 1) ? u1 : u0, (k & 2) ? v1 : v0)));
+    const double theta = std::acos(std::fmax(-1.0, std::fmin(1.0, cmin))) + 1e-4;
+    const double sin_t = std::sin(theta);
+    int jbest = 0;
+    for (int i = 0; i < n; ++i)
+    {
+      proj[static_cast<size_t>(i)] = c.x * verts[i].x + c.y * verts[i].y + c.z * verts[i].z;
+      if (proj[static_cast<size_t>(i)] > proj[static_cast<size_t>(jbest)])
+        jbest = i;
+    }
+    auto beats = [&](int j, int i) {
+      const double ex = verts[j].x - verts[i].x, ey = verts[j].y - verts[i].y, ez = verts[j].z - verts[i].z;
+      const double len = std::sqrt(ex * ex + ey * ey + ez * ez);
+      return proj[static_cast<size_t>(j)] - proj[static_cast<size_t>(i)] > len * (sin_t + 1e-9) + 1e-12;
+    };
+    for (int i = 0; i < n; ++i)
+    {
+      bool out = beats(jbest, i);
+      for (int j = 0; j < n && !out; ++j)
+        out = beats(j, i);
+      if (!out)
+        cand.push_back(static_cast<uint8_t>(i));
+    }
+    if (cand.size() > 65535)
+      throw SceneError(TC_ERR_UNSUPPORTED, "support look-up table too large");
+    off[static_cast<size_t>(cell) + 1] = static_cast<uint16_t>(cand.size());
+  }
+  const size_t base = blob.size();
+  const size_t bytes = (off.size() * sizeof(uint16_t) + cand.size() + 15) / 16 * 16;
+  blob.resize(base + bytes, 0);
+  std::memcpy(blob.data() + base, off.data(), off.size() * sizeof(uint16_t));
+  std::memcpy(blob.data() + base + off.size() * sizeof(uint16_t), cand.data(), cand.size());
 }
 
 inline void buildHostScene(const tc_scene_desc& d, HostScene& s)
@@ -178,6 +247,8 @@ inline void buildHostScene(const tc_scene_desc& d, HostScene& s)
     double lo[3] = { 1e300, 1e300, 1e300 }, hi[3] = { -1e300, -1e300, -1e300 };
     sh.vert_off = static_cast<int32_t>(s.verts.size());
     sh.vert_cnt = 0;
+    sh.lut_off = -1;
+    sh.lut_bytes = 0;
     switch (sh.type)
     {
       case TC_SHAPE_SPHERE:
@@ -227,6 +298,14 @@ inline void buildHostScene(const tc_scene_desc& d, HostScene& s)
         }
         if (n > s.max_hull_verts)
           s.max_hull_verts = n;
+        if (n >= LUT_MIN_VERTS && n <= LUT_MAX_VERTS)
+        {
+          sh.lut_off = static_cast<int32_t>(s.lut.size());
+          buildSupportLut(s.verts.data() + sh.vert_off, n, s.lut);
+          sh.lut_bytes = static_cast<int32_t>(s.lut.size()) - sh.lut_off;
+          if (sh.lut_bytes > s.max_lut_bytes)
+            s.max_lut_bytes = sh.lut_bytes;
+        }
         break;
       }
       default:
