@@ -3,6 +3,7 @@
 // without a usable sm_100 device every entry point fails with TC_ERR_CUDA.
 #include <dlfcn.h>
 
+#include <cstdio>
 #include <cstring>
 #include <mutex>
 #include <new>
@@ -362,6 +363,11 @@ int runEval(tc_scene* scene, const tc_eval_desc* desc, const double* q, int32_t 
   TC_CUDA(cudaEventRecord(r->ev[2], st));
   TC_TRY(readCounters(r));
   const long long n_deep = r->h_counters->n_deep;
+  {
+    static const char* trace_deep = getenv("TC_TRACE_DEEP");  // tuning aid: how many items outgrew the fast polytope
+    if (trace_deep)
+      fprintf(stderr, "[tc] n_epa=%lld n_deep=%lld\n", r->h_counters->n_epa, n_deep);
+  }
   if (n_deep > 0)
   {
     const int n_threads = 64 * static_cast<int>(std::min<long long>((n_deep + 63) / 64, 296));

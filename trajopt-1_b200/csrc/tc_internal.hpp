@@ -33,7 +33,7 @@ namespace tc
 #define TC_CHUNK 128
 #endif
 #ifndef TC_GJK_RUN
-#define TC_GJK_RUN 128
+#define TC_GJK_RUN 512
 #endif
 #ifndef TC_EPA_RUN
 #define TC_EPA_RUN 1024

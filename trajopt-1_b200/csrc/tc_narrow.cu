@@ -814,7 +814,7 @@ static cudaError_t launchNarrowT(const SceneView& v, const Work& w, cudaStream_t
   if (e != cudaSuccess)
     return e;
   static const char* env_wp = getenv("TC_NARROW_WP");
-  const int wp = env_wp ? atoi(env_wp) : 0;  // bit 0: GJK, bit 1: EPA
+  const int wp = env_wp ? atoi(env_wp) : 2;  // bit 0: GJK, bit 1: EPA (measured on C4: EPA gains, GJK does not)
   if (wp)
   {
     static int n_sm = 0;
@@ -859,7 +859,7 @@ cudaError_t launchNarrow(const SceneView& v, const Work& w, int precision, cudaS
     return launchNarrowT<float, 3, 2>(v, w, st, mid);
   // tuning hook (bench only): TC_NARROW_VARIANT=gb,eb selects the min-blocks-per-SM register budget
   static const char* var = getenv("TC_NARROW_VARIANT");
-  const int code = var ? (var[0] - '0') * 10 + (var[2] - '0') : 22;
+  const int code = var ? (var[0] - '0') * 10 + (var[2] - '0') : 33;
   switch (code)
   {
     case 32: return launchNarrowT<double, 3, 2>(v, w, st, mid);
@@ -867,7 +867,10 @@ cudaError_t launchNarrow(const SceneView& v, const Work& w, int precision, cudaS
     case 42: return launchNarrowT<double, 4, 2>(v, w, st, mid);
     case 44: return launchNarrowT<double, 4, 4>(v, w, st, mid);
     case 23: return launchNarrowT<double, 2, 3>(v, w, st, mid);
-    default: return launchNarrowT<double, 2, 2>(v, w, st, mid);
+    case 22: return launchNarrowT<double, 2, 2>(v, w, st, mid);
+    case 43: return launchNarrowT<double, 4, 3>(v, w, st, mid);
+    case 34: return launchNarrowT<double, 3, 4>(v, w, st, mid);
+    default: return launchNarrowT<double, 3, 3>(v, w, st, mid);
   }
 }
 
