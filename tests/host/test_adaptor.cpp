@@ -196,6 +196,27 @@ int main(int argc, char** argv)
         }
         std::printf("LEGACY_BADCONFIG %d\n", lthrew ? 1 : 0);
       }
+      // numerical-gradient constraint (A18) on the same four states: one batched pass each
+      {
+        DiscreteCollisionNumericalConstraint num(scene, cfg, 1);
+        std::vector<double> values, coeffs, jac;
+        for (int k = 0; k < 4; ++k)
+        {
+          num.evaluate(VectorXd{ states[k][0], states[k][1] }, values, coeffs, jac);
+          std::printf("NUMKAT %d value %.12g coeff %.12g jac %.9g %.9g passes %ld\n", k, values[0], coeffs[0], jac[0], jac[1],
+                      num.passes());
+        }
+        bool nthrew = false;
+        try
+        {
+          ContinuousCollisionNumericalConstraint nope(scene, cfg, false, false, 1);
+        }
+        catch (const std::runtime_error&)
+        {
+          nthrew = true;
+        }
+        std::printf("NUM_BADCONFIG %d\n", nthrew ? 1 : 0);
+      }
       // max_allowed == 0: contacts only
       ev.calcCollisions(data, VectorXd{ -0.9, 0.01 }, 0);
       std::printf("NOSETS contacts %zu sets %zu\n", data.contact_results_map.count(), data.gradient_results_sets.size());
@@ -247,6 +268,25 @@ int main(int argc, char** argv)
           }
         }
         std::printf("BATCH_PASSES %d %ld\n", kind, batch->passes());
+        // numerical-gradient constraint on segment (1, 2), both ends free, and the batched trajectory check
+        {
+          const VectorXd q1(traj.begin() + static_cast<long>(n), traj.begin() + static_cast<long>(2 * n));
+          const VectorXd q2(traj.begin() + static_cast<long>(2 * n), traj.begin() + static_cast<long>(3 * n));
+          ContinuousCollisionNumericalConstraint num(scene, cfg, false, false, static_cast<int>(max_num_cnt));
+          std::vector<double> values, coeffs, jac;
+          num.evaluate(q1, q2, values, coeffs, jac);
+          std::printf("%s values", kind ? "NUMD" : "NUMC");
+          for (double v : values)
+            std::printf(" %.12g", v);
+          std::printf(" jac");
+          for (double v : jac)
+            std::printf(" %.9g", v);
+          std::printf(" passes %ld\n", num.passes());
+          Evaluation ev(scene);
+          std::vector<double> md;
+          const std::vector<bool> hit = checkTrajectories(ev, cfg, traj.data(), 1, T, 0.0, &md);
+          std::printf("%s in_collision %d min_distance %.12g\n", kind ? "CHECKD" : "CHECKC", hit[0] ? 1 : 0, md[0]);
+        }
         // legacy stack: CastCollisionEvaluator / DiscreteCollisionEvaluator per segment, variables of the whole
         // trajectory in one vector as the legacy problem lays them out (trajopt/src/problem_description.cpp)
         const legacy::DblVec x(traj.begin(), traj.end());

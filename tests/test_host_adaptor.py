@@ -85,6 +85,29 @@ def test_adaptor_matches_known_answers_and_oracle(tmp_path, oracle):
                 ref = st["jac"][t, :, blk].reshape(-1)
                 err = np.abs(g[key] - ref).max() / max(np.abs(ref).max(), 1e-12)
                 assert err <= 1e-5, (tag, t, key, err)
+    # numerical-gradient constraints (A18) and trajectory check (N2) of the C++ adaptor against the same host logic
+    # driven by the oracle (tests/test_constraints.py states the tolerances)
+    cons = helpers.pkg.constraints
+    num = [l.split() for l in lines if l.startswith("NUMKAT")]
+    assert len(num) == 4 and "NUM_BADCONFIG 1" in lines
+    for tok, (val, jac) in zip(num, want):
+        assert abs(float(tok[3]) - val) <= 1e-6 and float(tok[5]) == 1.0
+        assert np.abs(np.array([float(tok[7]), float(tok[8])]) - np.array(jac)).max() <= 2e-2, tok
+    assert [int(tok[10]) for tok in num] == [1, 2, 3, 4]
+    for tag, chk, ev in (("NUMC", "CHECKC", capi.EVAL_LVS_CONTINUOUS), ("NUMD", "CHECKD", capi.EVAL_LVS_DISCRETE)):
+        tok = [l.split() for l in lines if l.startswith(tag + " ")][0]
+        i, j, k = tok.index("values"), tok.index("jac"), tok.index("passes")
+        vals = np.array([float(x) for x in tok[i + 1:j]])
+        J = np.array([float(x) for x in tok[j + 1:k]]).reshape(3, 2, n)
+        assert int(tok[k + 1]) == 1
+        vo, co, Jo = cons.ContinuousCollisionNumericalConstraint(oracle, so, ev, 0.02, False, False, 3).evaluate(
+            traj[1], traj[2])
+        assert np.abs(vals - vo).max() <= 1e-6, (tag, vals, vo)
+        assert np.abs(J - Jo).max() <= 2e-2, (tag, J, Jo)
+        tok = [l.split() for l in lines if l.startswith(chk + " ")][0]
+        o = cons.check_trajectories(oracle, so, traj[None], ev, lvs=0.02)
+        assert int(tok[2]) == int(o["in_collision"][0]) == 1
+        assert abs(float(tok[4]) - o["min_distance"][0]) <= 1e-6
 
 
 def _parse_exprs(lines, tag):

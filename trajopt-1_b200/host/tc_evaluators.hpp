@@ -20,7 +20,9 @@
 //                   trajopt_common/include/trajopt_common/cache.h:32-329, lifted to the whole iterate).
 //                   A call whose joint values are not the batch's falls back to a standalone GPU pass.
 #pragma once
+#include <algorithm>
 #include <cstring>
+#include <limits>
 #include <mutex>
 #include <string>
 
@@ -459,4 +461,185 @@ private:
     return c;
   }
 };
+// ---------------------------------------------------------------------------------------------
+// SURVEY 8a A18 — numerical-gradient constraints, batched.
+//   trajopt_ifopt/src/constraints/collision/discrete_collision_numerical_constraint.cpp:65-200
+//   trajopt_ifopt/src/constraints/collision/continuous_collision_numerical_constraint.cpp:91-232
+// The reference evaluates once at x and once per perturbed joint (delta = 1e-8) and matches the perturbed
+// gradient-result sets to the baseline's by (key, shape_key).  The classes below run the n_dof + 1 (2 n_dof + 1)
+// states as ONE tc_eval of independent "trajectories" and then follow the reference's matching loops.
+// (An unchanged reference numerical constraint also works on top of the evaluators above: one small pass per call.)
+// ---------------------------------------------------------------------------------------------
+class DiscreteCollisionNumericalConstraint
+{
+public:
+  DiscreteCollisionNumericalConstraint(Scene::Ptr scene, const TrajOptCollisionConfig& cfg, int max_num_cnt = 1)
+    : eval_(scene), scene_(std::move(scene)), cfg_(cfg), rows_(static_cast<std::size_t>(std::max(max_num_cnt, 0)))
+  {
+    if (cfg_.type != CollisionEvaluatorType::DISCRETE)
+      throw std::runtime_error("SingleTimestepCollisionEvaluator, should be configured with DISCRETE");
+    if (max_num_cnt < 1)
+      throw std::runtime_error("max_num_cnt must be greater than zero!");
+  }
+  // values[rows], coeffs[rows], jac[rows][n_dof] (row-major)
+  void evaluate(const VectorXd& joint_vals, std::vector<double>& values, std::vector<double>& coeffs,
+                std::vector<double>& jac)
+  {
+    const std::size_t n = static_cast<std::size_t>(scene_->nDof());
+    if (joint_vals.size() != n)
+      throw std::runtime_error("DiscreteCollisionNumericalConstraint: joint_vals has the wrong size");
+    const double delta = 1e-8, mb = scene_->marginBuffer();
+    q_.assign((n + 1) * n, 0.0);
+    for (std::size_t b = 0; b <= n; ++b)
+      for (std::size_t j = 0; j < n; ++j)
+        q_[b * n + j] = joint_vals[j] + ((b == j + 1) ? delta : 0.0);
+    eval_.run(cfg_, q_.data(), static_cast<int>(n + 1), 1, nullptr, host_);
+    ++passes_;
+    detail::fillCacheData(base_, *scene_, host_, host_.term_ptr[0], host_.term_ptr[1], false, false, false, rows_);
+    values.assign(rows_, -mb);
+    coeffs.assign(rows_, 1.0);
+    jac.assign(rows_ * n, 0.0);
+    const std::size_t cnt = std::min(rows_, base_.gradient_results_sets.size());
+    for (std::size_t i = 0; i < cnt; ++i)
+    {
+      values[i] = base_.gradient_results_sets[i].getMaxErrorT0();
+      coeffs[i] = base_.gradient_results_sets[i].coeff;
+    }
+    for (std::size_t j = 0; j < n && cnt > 0; ++j)
+    {
+      detail::fillCacheData(delta_, *scene_, host_, host_.term_ptr[j + 1], host_.term_ptr[j + 2], false, false, false,
+                            rows_);
+      for (std::size_t i = 0; i < cnt; ++i)
+      {
+        const GradientResultsSet& baseline = base_.gradient_results_sets[i];
+        double e = -mb;
+        for (const GradientResultsSet& cr : delta_.gradient_results_sets)
+          if (cr.key == baseline.key && cr.shape_key == baseline.shape_key)
+          {
+            e = cr.getMaxErrorT0();
+            break;
+          }
+        jac[i * n + j] = (e - baseline.getMaxErrorT0()) / delta;
+      }
+    }
+  }
+  long passes() const { return passes_; }
+
+private:
+  Evaluation eval_;
+  Scene::Ptr scene_;
+  TrajOptCollisionConfig cfg_;
+  std::size_t rows_;
+  std::vector<double> q_;
+  HostResult host_;
+  CollisionCacheData base_, delta_;
+  long passes_{ 0 };
+};
+
+class ContinuousCollisionNumericalConstraint
+{
+public:
+  ContinuousCollisionNumericalConstraint(Scene::Ptr scene, const TrajOptCollisionConfig& cfg, bool vars0_fixed,
+                                         bool vars1_fixed, int max_num_cnt = 1)
+    : eval_(scene)
+    , scene_(std::move(scene))
+    , cfg_(cfg)
+    , f0_(vars0_fixed)
+    , f1_(vars1_fixed)
+    , rows_(static_cast<std::size_t>(std::max(max_num_cnt, 0)))
+  {
+    if (cfg_.type == CollisionEvaluatorType::DISCRETE || cfg_.type == CollisionEvaluatorType::NONE)
+      throw std::runtime_error("ContinuousCollisionNumericalConstraint needs a two-state evaluator type");
+    if (f0_ && f1_)
+      throw std::runtime_error("position_vars are both fixed!");
+    if (max_num_cnt < 1)
+      throw std::runtime_error("max_num_cnt must be greater than zero!");
+  }
+  // values[rows], coeffs[rows], jac[rows][2][n_dof] (block p = state p)
+  void evaluate(const VectorXd& joint_vals0, const VectorXd& joint_vals1, std::vector<double>& values,
+                std::vector<double>& coeffs, std::vector<double>& jac)
+  {
+    const std::size_t n = static_cast<std::size_t>(scene_->nDof());
+    if (joint_vals0.size() != n || joint_vals1.size() != n)
+      throw std::runtime_error("ContinuousCollisionNumericalConstraint: joint_vals have the wrong size");
+    const double delta = 1e-8, mb = scene_->marginBuffer();
+    const std::size_t B = 2 * n + 1;
+    q_.assign(B * 2 * n, 0.0);
+    auto put = [&](std::size_t b, const VectorXd& a0, const VectorXd& a1) {
+      for (std::size_t j = 0; j < n; ++j)
+        q_[(b * 2) * n + j] = a0[j], q_[(b * 2 + 1) * n + j] = a1[j];
+    };
+    put(0, joint_vals0, joint_vals1);
+    for (std::size_t p = 0; p < 2; ++p)
+      for (std::size_t j = 0; j < n; ++j)
+      {
+        VectorXd jv = p ? joint_vals1 : joint_vals0;
+        jv[j] += delta;
+        put(1 + p * n + j, jv, joint_vals1);  // as the reference: (jv, joint_vals1) for both blocks (:182-183)
+      }
+    const uint8_t fixed[2] = { static_cast<uint8_t>(f0_), static_cast<uint8_t>(f1_) };
+    eval_.run(cfg_, q_.data(), static_cast<int>(B), 2, fixed, host_);
+    ++passes_;
+    detail::fillCacheData(base_, *scene_, host_, host_.term_ptr[0], host_.term_ptr[1], true, f0_, f1_, rows_);
+    values.assign(rows_, -mb);
+    coeffs.assign(rows_, 1.0);
+    jac.assign(rows_ * 2 * n, 0.0);
+    const std::size_t cnt = std::min(rows_, base_.gradient_results_sets.size());
+    auto err = [&](const GradientResultsSet& s) {
+      return (!f0_ && !f1_) ? s.getMaxError() : (!f0_ ? s.getMaxErrorT0() : s.getMaxErrorT1());
+    };
+    for (std::size_t i = 0; i < cnt; ++i)
+    {
+      values[i] = err(base_.gradient_results_sets[i]);
+      coeffs[i] = base_.gradient_results_sets[i].coeff;
+    }
+    for (std::size_t k = 0; k < 2 * n && cnt > 0; ++k)
+    {
+      detail::fillCacheData(delta_, *scene_, host_, host_.term_ptr[k + 1], host_.term_ptr[k + 2], true, f0_, f1_, rows_);
+      for (std::size_t i = 0; i < cnt; ++i)
+      {
+        const GradientResultsSet& baseline = base_.gradient_results_sets[i];
+        double e = -mb;
+        for (const GradientResultsSet& cr : delta_.gradient_results_sets)
+          if (cr.key == baseline.key && cr.shape_key == baseline.shape_key)
+          {
+            e = err(cr);
+            break;
+          }
+        jac[(i * 2 + k / n) * n + k % n] = (e - err(baseline)) / delta;
+      }
+    }
+  }
+  long passes() const { return passes_; }
+
+private:
+  Evaluation eval_;
+  Scene::Ptr scene_;
+  TrajOptCollisionConfig cfg_;
+  bool f0_, f1_;
+  std::size_t rows_;
+  std::vector<double> q_;
+  HostResult host_;
+  CollisionCacheData base_, delta_;
+  long passes_{ 0 };
+};
+
+// SURVEY 8f N2 — the outcome tests' checkTrajectory (trajopt/test/planning_unit.cpp:99-100,145-148) as one batched
+// pass: trajs[B][T][n_dof] -> minimum signed distance of every trajectory (+inf when nothing is within margin +
+// buffer); a trajectory is in collision when that minimum is below `contact_distance`.
+inline std::vector<bool> checkTrajectories(Evaluation& eval, const TrajOptCollisionConfig& cfg, const double* trajs, int B,
+                                           int T, double contact_distance, std::vector<double>* min_distance = nullptr)
+{
+  HostResult h;
+  eval.run(cfg, trajs, B, T, nullptr, h);
+  std::vector<double> md(static_cast<std::size_t>(B), std::numeric_limits<double>::infinity());
+  for (const tc_contact& c : h.contacts)
+    md[static_cast<std::size_t>(c.traj)] = std::min(md[static_cast<std::size_t>(c.traj)], c.distance);
+  std::vector<bool> hit(static_cast<std::size_t>(B));
+  for (std::size_t b = 0; b < md.size(); ++b)
+    hit[b] = md[b] < contact_distance;
+  if (min_distance)
+    *min_distance = md;
+  return hit;
+}
 }  // namespace trajopt_cuda
