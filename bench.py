@@ -251,11 +251,18 @@ def run_ours(args, scene, rank, world, local_rank):
         traffic = None
         try:
             tr = json.load(open(os.path.join(ROOT, "profiles", "r1_traffic.json")))
-            traffic = sum(v["dram_bytes_per_launch"] for k, v in tr.items() if k.startswith(("k_gjk<double", "k_epa<double")))
+            traffic = sum(v["dram_bytes_per_launch"] for k, v in tr.items() if k.startswith(("k_gjk", "k_epa")))
         except Exception:
             pass
         base, _, _ = cpu_baseline(scene) if (world == 1 and not args.no_cpu_baseline) else ({"value": None, "unit": UNIT, "cores": 0,
                                                                             "kind": "port", "sample": "skipped"}, 0, 0)
+        # HBM-bound rest of the pass (FK, broadphase, finalise, sort, gradients + rows, cost): algorithmic bytes of
+        # SURVEY.md 8(d) over the time of everything that is not the narrow phase
+        n_act = int(scene["n_active_links"])
+        r_row = 2 * nd * 12 + 24
+        hbm_bytes = (counts["n_states"] * (8 * nd + (96 + 96 + 48) * n_act) + 16 * counts["n_narrowphase"] +
+                     counts["n_contacts"] * (176 + r_row))
+        rest_ms = ms - nms
         out = {
             "metric": METRIC, "value": dense_total / (ms * 1e-3), "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": max(3, args.warmup), "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
@@ -272,11 +279,17 @@ def run_ours(args, scene, rank, world, local_rank):
                            "time), pinned host buffers, "
                            "wall clock around the whole batch"},
             "gpu_launches": launches, "library_calls_per_step": cu.launches(res)[1],
-            "roofline": {"bound": "fp64", "kernel": "narrow phase: k_gjk<double> + k_epa<double> (2 launches)", "achieved": flops / (nms * 1e-3) / 1e12,
+            "roofline": {"bound": "fp64", "kernel": "narrow phase: k_gjk<double> + k_epa_wp<double> (2 launches)", "achieved": flops / (nms * 1e-3) / 1e12,
                          "peak": peak64, "unit": "TFLOP/s", "frac": flops / (nms * 1e-3) / 1e12 / peak64,
                          "traffic": traffic, "peak_source": "DFMA loop measured in this run (tc_measure_fma_peak)",
                          "kernel_ms": nms, "algorithmic_flops_per_launch": flops,
                          "hbm_peak_gbs": peaks.get("hbm_gbs")},
+            "roofline_hbm": {"bound": "hbm", "kernel": "everything but the narrow phase (FK, broadphase, finalise, sort, "
+                             "gradient rows, cost)", "achieved": hbm_bytes / (rest_ms * 1e-3) / 1e9,
+                             "peak": peaks.get("hbm_gbs"), "unit": "GB/s",
+                             "frac": (hbm_bytes / (rest_ms * 1e-3) / 1e9 / peaks["hbm_gbs"]) if peaks.get("hbm_gbs") else None,
+                             "algorithmic_bytes": int(hbm_bytes), "ms": rest_ms,
+                             "peak_source": "MEASURED_PEAKS.json hbm_gbs (burst copy)"},
             "cpu_baseline": base,
             "counters": {k: counts[k] for k in ("n_dense", "n_units", "n_narrowphase", "n_contacts", "gjk_iters",
                                                 "epa_iters", "n_epa", "support_verts", "n_unconverged")},

@@ -655,7 +655,7 @@ __global__ void __launch_bounds__(128, MINB) k_epa_wp(SceneView v, Work w, int h
       A = &v.shapes[spd.sa];
       B = &v.shapes[spd.sb];
       thr = static_cast<R>(pr.thr);
-      if (A->vert_cnt + B->vert_cnt > 0)
+      if (hull_stride > 0 && A->vert_cnt + B->vert_cnt > 0)
       {
         stageHullsWarp<R>(v, *A, *B, sv, bar, phase & 1);
         ++phase;
@@ -683,8 +683,14 @@ __global__ void __launch_bounds__(128, MINB) k_epa_wp(SceneView v, Work w, int h
         S.lam[i] = 0;
       }
       Placed<R> PA, PB;
-      placeItem<R>(v, w, rec.state, spd, pr, *A, *B, sv, sv + A->vert_cnt, PA, PB, stagedLutA<R>(*A, *B, sv),
-                   stagedLutB<R>(*A, *B, sv));
+      // hull_stride == 0: nothing is staged, vertices and look-up tables are read through L1 (the table keeps the
+      // reads to a handful per support call) and the whole of L1 stays with the thread-local polytopes
+      if (hull_stride > 0)
+        placeItem<R>(v, w, rec.state, spd, pr, *A, *B, sv, sv + A->vert_cnt, PA, PB, stagedLutA<R>(*A, *B, sv),
+                     stagedLutB<R>(*A, *B, sv));
+      else
+        placeItem<R>(v, w, rec.state, spd, pr, *A, *B, sceneVerts<R>(v) + A->vert_off, sceneVerts<R>(v) + B->vert_off, PA,
+                     PB, A->lut_bytes ? v.lut + A->lut_off : nullptr, B->lut_bytes ? v.lut + B->lut_off : nullptr);
       d.converged = (nflag & 8) == 0;
       distanceEpa<R, true>(PA, static_cast<R>(A->brad), PB, static_cast<R>(B->brad), thr, S, store, d);
       if (d.status != ND_EPA_OVERFLOW)
@@ -836,7 +842,14 @@ static cudaError_t launchNarrowT(const SceneView& v, const Work& w, cudaStream_t
     if (mid)
       cudaEventRecord(mid, st);
     ++launchCounter();
-    if (wp & 2)
+    static const char* env_gl = getenv("TC_EPA_GLOBAL");
+    const bool epa_global = env_gl ? atoi(env_gl) != 0 : true;  // measured on C4: 8.1 -> 7.0 ms
+    if ((wp & 2) && epa_global)
+    {
+      cudaFuncSetAttribute(k_epa_wp<R, EB>, cudaFuncAttributePreferredSharedMemoryCarveout, 0);
+      k_epa_wp<R, EB><<<n_sm * EB, 128, 0, st>>>(v, w, 0);
+    }
+    else if (wp & 2)
       k_epa_wp<R, EB><<<n_sm * EB, 128, smem_wp, st>>>(v, w, stride);
     else
       k_epa<R, EB><<<grid_e, TC_EPA_NT, smem, st>>>(v, w, run_e);
@@ -859,18 +872,14 @@ cudaError_t launchNarrow(const SceneView& v, const Work& w, int precision, cudaS
     return launchNarrowT<float, 3, 2>(v, w, st, mid);
   // tuning hook (bench only): TC_NARROW_VARIANT=gb,eb selects the min-blocks-per-SM register budget
   static const char* var = getenv("TC_NARROW_VARIANT");
-  const int code = var ? (var[0] - '0') * 10 + (var[2] - '0') : 33;
+  const int code = var ? (var[0] - '0') * 10 + (var[2] - '0') : 34;
   switch (code)
   {
+    case 22: return launchNarrowT<double, 2, 2>(v, w, st, mid);
     case 32: return launchNarrowT<double, 3, 2>(v, w, st, mid);
     case 33: return launchNarrowT<double, 3, 3>(v, w, st, mid);
-    case 42: return launchNarrowT<double, 4, 2>(v, w, st, mid);
     case 44: return launchNarrowT<double, 4, 4>(v, w, st, mid);
-    case 23: return launchNarrowT<double, 2, 3>(v, w, st, mid);
-    case 22: return launchNarrowT<double, 2, 2>(v, w, st, mid);
-    case 43: return launchNarrowT<double, 4, 3>(v, w, st, mid);
-    case 34: return launchNarrowT<double, 3, 4>(v, w, st, mid);
-    default: return launchNarrowT<double, 3, 3>(v, w, st, mid);
+    default: return launchNarrowT<double, 3, 4>(v, w, st, mid);
   }
 }
 

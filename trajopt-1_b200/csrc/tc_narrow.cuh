@@ -181,6 +181,7 @@ TC_HD Vec3<R> primitiveSupport(const ShapeCore<R>& s, Vec3<R> d)
 // Out-of-line pieces of the support function.  The narrow-phase kernels are bound by instruction fetch (their hot
 // code is several times the 32 KB L1.5 instruction cache), so everything that is not the common case — a hull without
 // a look-up table, a primitive — is a call, and the inlined part of Placed::support stays small.
+#define TC_UNLIKELY(x) __builtin_expect(!!(x), 0)
 #if defined(__CUDACC__)
 #define TC_NI __host__ __device__ __noinline__
 #else
@@ -250,7 +251,7 @@ struct Placed
   // convex-hull support does), whether or not the look-up table let most of them be skipped
   TC_HD Vec3<R> support(Vec3<R> d, int& scanned) const
   {
-    if (sh.type != SH_HULL)
+    if (TC_UNLIKELY(sh.type != SH_HULL))
       return primitiveSupportPlaced(sh, p0, p1, cast, d);
     const Vec3<R> d0 = p0.rotT(d);
     const Vec3<R> d1 = cast ? p1.rotT(d) : d0;
@@ -298,7 +299,7 @@ struct Placed
         done = true;
       }
     }
-    if (!done)
+    if (TC_UNLIKELY(!done))
     {
       const int packed = hullScanFull(sh.verts, sh.nverts, d0, d1, cast);
       b0 = packed & 65535;
@@ -665,12 +666,14 @@ TC_HD bool epaIsAlive(const EpaState<R>& E, const EpaStore<R>& st, int f)
   return MASK ? ((E.alive >> f) & 1ull) != 0 : st.fv[f] >= 0;
 }
 
-// adds a face in the first dead slot (else appends); returns the slot or -1 on overflow; d_out = plane distance
+// adds a face in the first dead slot (else appends); returns the slot or -1 on overflow; d_out = plane distance.
+// pi, pj, pk are the face's points (callers that already hold them in registers pass them instead of re-reading the
+// store: the apex of every face of an expansion is the new support point)
 template <class R, bool MASK>
-TC_HD int epaAddFace(EpaState<R>& E, EpaStore<R>& st, int i, int j, int k, bool orient, R& d_out)
+TC_HD int epaAddFacePts(EpaState<R>& E, EpaStore<R>& st, int i, int j, int k, Vec3<R> pi, Vec3<R> pj, Vec3<R> pk,
+                        bool orient, R& d_out)
 {
-  const Vec3<R> pi = st.pw[i];
-  Vec3<R> n = cross(st.pw[j] - pi, st.pw[k] - pi);
+  Vec3<R> n = cross(pj - pi, pk - pi);
   if (orient && dot(n, pi - E.centroid) < 0)
   {
     const int t = j;
@@ -729,6 +732,12 @@ TC_HD int epaAddFace(EpaState<R>& E, EpaStore<R>& st, int i, int j, int k, bool 
   }
   st.fd[slot] = d_out;
   return slot;
+}
+
+template <class R, bool MASK>
+TC_HD int epaAddFace(EpaState<R>& E, EpaStore<R>& st, int i, int j, int k, bool orient, R& d_out)
+{
+  return epaAddFacePts<R, MASK>(E, st, i, j, k, st.pw[i], st.pw[j], st.pw[k], orient, d_out);
 }
 
 // smallest plane distance, lowest slot on ties (= first minimum of a scan in slot order)
@@ -997,11 +1006,13 @@ TC_HD int epaTripMasked(const Placed<R>& A, const Placed<R>& B, EpaStore<R>& st,
   E.np += 1;
   E.best = sbest;
   E.bd = sbd;
+  // the apex of every new face is the support point just found: passed in registers, not re-read from the store
   for (int q = 0; q < ne; ++q)
   {
     R d;
     const int e = st.edges[q];
-    const int f = epaAddFace<R, true>(E, st, e & 65535, e >> 16, xi, false, d);
+    const int a = e & 65535, b = e >> 16;
+    const int f = epaAddFacePts<R, true>(E, st, a, b, xi, st.pw[a], st.pw[b], xw, false, d);
     if (f < 0)
       return EPA_OVERFLOW;
     epaOffer(E, f, d);
