@@ -307,6 +307,12 @@ def run_ours(args, scene, rank, world, local_rank):
 
 
 def main():
+    # Exactly ONE line may reach stdout (the JSON): libraries print there too (NCCL announces its version on the first
+    # communicator), so file descriptor 1 is pointed at stderr for the run and the JSON goes to the saved descriptor.
+    sys.stdout.flush()
+    real_stdout = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
+    sys.stdout = real_stdout
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=10)
@@ -326,6 +332,7 @@ def main():
         run_reference(args, scene, rank, world)
     else:
         run_ours(args, scene, rank, world, local_rank)
+    real_stdout.flush()
 
 
 if __name__ == "__main__":
