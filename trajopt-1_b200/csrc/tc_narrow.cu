@@ -10,7 +10,6 @@
 #include <cstdlib>
 
 #include "tc_internal.hpp"
-#include "tc_epa_coop.cuh"
 
 #ifndef TC_GJK_DYN
 #define TC_GJK_DYN 1
@@ -724,191 +723,6 @@ __global__ void __launch_bounds__(128, MINB) k_epa_wp(SceneView v, Work w, int h
   addStats(w, 0, st_scan, st_epa, st_it, st_unconv);
 }
 
-// ---------------------------------------------------------------------------------------------
-// K3b, cooperative form (tc_epa_coop.cuh): 8 lanes per item, polytopes in shared memory, persistent warps.  A warp
-// draws 32-item batches of the hand-off arena from one global cursor; its four groups take items of the batch one
-// by one, so a group that finishes an item early starts the next while the others are still expanding theirs.
-// ---------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(128, 4) k_epa_coop(SceneView v, Work w)
-{
-  extern __shared__ __align__(16) unsigned char smem_raw[];
-  coop::Item* items = reinterpret_cast<coop::Item*>(smem_raw);
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  coop::Lanes L;
-  L.g = lane >> 3;
-  L.gl = lane & 7;
-  L.gmask = 0xffu << (8 * L.g);
-  coop::Item& it = items[warp * 4 + L.g];
-  for (int i = L.gl; i < coop::EC_V; i += coop::GROUP)
-    it.erow[i] = 0;
-  __syncwarp();
-  // warp-uniform batch state
-  int next = 0, batch_end = 0, batch_sp = -1;
-  bool no_more = false;
-  // group-uniform item state
-  bool busy = false;
-  int slot = -1, u = -1, sp = 0, n_start = 0;
-  bool conv0 = true;
-  double thr = 0, ra = 0, rb = 0;
-  coop::Shapes sh{};
-  coop::State E{};
-  long long st_scan = 0, st_epa = 0, st_it = 0, st_unconv = 0;
-  for (;;)
-  {
-    // ---- hand items of the batch to idle groups ----
-    const unsigned idle = __ballot_sync(0xffffffffu, !busy);
-    bool fresh = false;
-    for (int g = 0; g < 4; ++g)
-    {
-      if (!((idle >> (8 * g)) & 1u))
-        continue;
-      while (!no_more && next >= batch_end)
-      {
-        int group = 0;
-        if (lane == 0)
-          group = static_cast<int>(atomicAdd(reinterpret_cast<unsigned long long*>(&w.counters->epa_cursor_g), 32ull));
-        group = __shfl_sync(0xffffffffu, group, 0);
-        if (group >= w.n_items_padded)
-        {
-          no_more = true;
-          break;
-        }
-        const int b = bucketOf(v, w, group);
-        const int vend = w.sp_offset[b] + w.epa_cursor[b];
-        if (group >= vend)
-          continue;  // this part of the bucket received no hand-off
-        batch_sp = b;
-        next = group;
-        batch_end = min(group + 32, vend);
-      }
-      if (next >= batch_end)
-        break;
-      if (L.g == g)
-      {
-        busy = true;
-        fresh = true;
-        slot = next;
-        sp = batch_sp;
-      }
-      ++next;
-    }
-    if (!__any_sync(0xffffffffu, busy))
-      break;
-    int code = coop::C_CONTINUE, scanned = 0;
-    Vec3<double> normal, pa, pb;
-    double depth = 0;
-    // ---- start of a new item: poses and GJK simplex into shared memory, first polytope ----
-    if (fresh)
-    {
-      const EpaRec& rec = w.epa_rec[slot];
-      u = rec.unit;
-      const int nflag = rec.nflag;
-      const int state = rec.state;
-      n_start = nflag & 7;
-      conv0 = (nflag & 8) == 0;
-      const ShapePairD spd = v.spairs[sp];
-      const PairD pr = v.pairs[spd.pair];
-      sh.A = &v.shapes[spd.sa];
-      sh.B = &v.shapes[spd.sb];
-      sh.va = v.verts + sh.A->vert_off;
-      sh.vb = v.verts + sh.B->vert_off;
-      sh.la = sh.A->lut_bytes ? reinterpret_cast<const uint16_t*>(v.lut + sh.A->lut_off) : nullptr;
-      sh.lb = sh.B->lut_bytes ? reinterpret_cast<const uint16_t*>(v.lut + sh.B->lut_off) : nullptr;
-      thr = pr.thr;
-      ra = (sh.A->type == SH_SPHERE || sh.A->type == SH_CAPSULE) ? sh.A->radius : 0.0;
-      rb = (sh.B->type == SH_SPHERE || sh.B->type == SH_CAPSULE) ? sh.B->radius : 0.0;
-      const double* a0 = posePtr(w, pr.a, state);
-      const double* a1 = w.cast ? a0 + 12 : a0;
-      const bool b_active = pr.b < v.n_active;
-      const double* b0 = b_active ? posePtr(w, pr.b, state) : v.link_pose + 12 * pr.b;
-      const double* b1 = (b_active && w.cast) ? b0 + 12 : b0;
-      sh.cast_a = w.cast != 0;
-      sh.cast_b = b_active && w.cast != 0;
-      for (int e = L.gl; e < 48; e += coop::GROUP)
-      {
-        const int which = e / 12, k = e % 12;
-        const double* src = which == 0 ? a0 : (which == 1 ? a1 : (which == 2 ? b0 : b1));
-        it.pose[which][k] = src[k];
-      }
-      if (L.gl < 4)
-      {
-        const double* q = rec.s + 6 * L.gl;
-        it.pw[L.gl][0] = q[0], it.pw[L.gl][1] = q[1], it.pw[L.gl][2] = q[2];
-        it.pa[L.gl][0] = q[3], it.pa[L.gl][1] = q[4], it.pa[L.gl][2] = q[5];
-      }
-      coop::gsync(L);
-      // epaScale
-      double scale = 2 * (sh.A->brad + sh.B->brad);
-      {
-        const Vec3<double> ca(sh.A->center[0], sh.A->center[1], sh.A->center[2]);
-        const Vec3<double> cb(sh.B->center[0], sh.B->center[1], sh.B->center[2]);
-        if (sh.cast_a)
-          scale += norm(Pose<double>::from12(it.pose[1]).apply(ca) - Pose<double>::from12(it.pose[0]).apply(ca));
-        if (sh.cast_b)
-          scale += norm(Pose<double>::from12(it.pose[3]).apply(cb) - Pose<double>::from12(it.pose[2]).apply(cb));
-      }
-      code = coop::init(L, sh, it, E, n_start, scale, normal, pa, pb, scanned);
-    }
-    // ---- one expansion for every group that holds a polytope ----
-    if (busy && code == coop::C_CONTINUE)
-      code = coop::trip(L, sh, it, E, scanned);
-    // ---- finished items ----
-    const bool fin = busy && code != coop::C_CONTINUE;
-    DistOut<double> d;
-    clearDist(d);
-    d.used_epa = true;
-    if (fin && code != coop::C_OVERFLOW)
-    {
-      int iters = 0;
-      if (code != coop::C_FLAT)
-      {
-        coop::finish(L, it, E, depth, normal, pa, pb);
-        iters = E.iters;
-      }
-      d.converged = conv0 && code != coop::C_UNCONVERGED;
-      d.distance = -depth - ra - rb;
-      if (d.distance <= thr)
-      {
-        d.status = ND_CONTACT;
-        d.normal = normal;
-        d.pa = pa + ra * normal;
-        d.pb = pb - rb * normal;
-      }
-      if (L.gl == 0)
-      {
-        st_scan += scanned;
-        st_epa += 1;
-        st_it += iters;
-        st_unconv += d.converged ? 0 : 1;
-      }
-    }
-    else if (busy && L.gl == 0 && !fin)
-      st_scan += scanned;
-    __syncwarp();
-    storeHit<double>(w, d, u, sp, fin && L.gl == 0 && d.status == ND_CONTACT);
-    const bool deep = fin && L.gl == 0 && code == coop::C_OVERFLOW;
-    const unsigned m = __ballot_sync(0xffffffffu, deep);
-    if (m)
-    {
-      const int leader = __ffs(m) - 1;
-      unsigned long long dbase = 0;
-      if (lane == leader)
-        dbase = atomicAdd(reinterpret_cast<unsigned long long*>(&w.counters->n_deep),
-                          static_cast<unsigned long long>(__popc(m)));
-      dbase = __shfl_sync(0xffffffffu, dbase, leader);
-      if (deep)
-      {
-        const unsigned long long ds = dbase + __popc(m & ((1u << lane) - 1u));
-        w.deep_items[2 * ds] = u;
-        w.deep_items[2 * ds + 1] = sp;
-      }
-    }
-    if (fin)
-      busy = false;
-  }
-  addStats(w, 0, st_scan, st_epa, st_it, st_unconv);
-}
-
 // deep-expansion path: same arithmetic, polytope in global scratch, vertices read from global memory
 template <class R>
 __global__ void __launch_bounds__(64) k_narrow_deep(SceneView v, Work w, long long n_deep, unsigned char* scratch,
@@ -1030,15 +844,7 @@ static cudaError_t launchNarrowT(const SceneView& v, const Work& w, cudaStream_t
     ++launchCounter();
     static const char* env_gl = getenv("TC_EPA_GLOBAL");
     const bool epa_global = env_gl ? atoi(env_gl) != 0 : true;  // measured on C4: 8.1 -> 7.0 ms
-    static const char* env_coop = getenv("TC_EPA_COOP");
-    const bool epa_coop = sizeof(R) == sizeof(double) && (env_coop ? atoi(env_coop) != 0 : false);
-    if (epa_coop)
-    {
-      const int smem_coop = static_cast<int>(coop::ITEMS_PER_CTA * sizeof(coop::Item));
-      cudaFuncSetAttribute(k_epa_coop, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_coop);
-      k_epa_coop<<<n_sm * 4, 128, smem_coop, st>>>(v, w);
-    }
-    else if ((wp & 2) && epa_global)
+    if ((wp & 2) && epa_global)
     {
       cudaFuncSetAttribute(k_epa_wp<R, EB>, cudaFuncAttributePreferredSharedMemoryCarveout, 0);
       k_epa_wp<R, EB><<<n_sm * EB, 128, 0, st>>>(v, w, 0);
