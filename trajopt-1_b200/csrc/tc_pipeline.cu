@@ -169,7 +169,10 @@ __global__ void k_unit_term(Work w)
 //   sub-state interpolation LinSpaced(cnt, q0, q1) (collision_terms.cpp:846-848)
 // One thread per sub-state, frames visited in topological order.
 // ---------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(TPB) k_fk(SceneView v, Work w)
+#ifndef TC_FK_MINB
+#define TC_FK_MINB 6
+#endif
+__global__ void __launch_bounds__(TPB, TC_FK_MINB) k_fk(SceneView v, Work w)
 {
   // per-warp staging tile: 32 poses, rows padded to 13 doubles (bank spread)
   __shared__ double tile[TPB / 32][32 * 13];
@@ -481,7 +484,7 @@ __global__ void __launch_bounds__(1024) k_scan_sp(SceneView v, Work w)
 }
 
 #ifndef TC_FINALIZE_MINB
-#define TC_FINALIZE_MINB 3
+#define TC_FINALIZE_MINB 4
 #endif
 // ---------------------------------------------------------------------------------------------
 // contact finalisation: ContactResult fields, cast bookkeeping, LVS merge, filters, sort key
@@ -737,8 +740,11 @@ __global__ void __launch_bounds__(TPB) k_rows(SceneView v, Work w, const long lo
 
 // gradients folded straight into the rows (TC_WANT_ROWS without TC_WANT_GRADIENTS): same arithmetic as k_grad
 // followed by k_rows, the per-link gradient vectors live in thread-local memory only
+#ifndef TC_GRADROWS_MINB
+#define TC_GRADROWS_MINB 6
+#endif
 template <int NMAX>
-__global__ void __launch_bounds__(TPB) k_grad_rows(SceneView v, Work w, const long long* term_row_base, int32_t* col_idx,
+__global__ void __launch_bounds__(TPB, TC_GRADROWS_MINB) k_grad_rows(SceneView v, Work w, const long long* term_row_base, int32_t* col_idx,
                                                    double* val, double* row_value, double* row_coeff,
                                                    double* row_margin)
 {
