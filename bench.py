@@ -206,7 +206,8 @@ def run_ours(args, scene, rank, world, local_rank):
     # (multistart.PipelinedEvaluator); each sub-batch is a plain tc_eval + tc_result_rows + tc_result_cost.
     nd = sg.n_dof
     pipe = ms_.PipelinedEvaluator(cu, sg, capi.EVAL_LVS_CONTINUOUS, LVS, fixed, nd, chunk=args.e2e_chunk,
-                                  n_workers=args.e2e_workers, concurrent=args.e2e_concurrent)
+                                  n_workers=args.e2e_workers, concurrent=args.e2e_concurrent,
+                                  taper=bool(args.e2e_taper), compact=args.e2e_rows == "blocks")
     q_np = q_pin.numpy()
 
     def step_e2e():
@@ -229,7 +230,8 @@ def run_ours(args, scene, rank, world, local_rank):
     barrier()
     e2e_ms = 1e3 * (time.perf_counter() - t0) / args.steps
     pipe.close()
-    d2h = 8 * (nc + B // args.e2e_chunk) + 12 * nnz + 24 * nc + 8 * B
+    n_sub = -(-B // args.e2e_chunk) + (2 if args.e2e_taper else 0)
+    d2h = 8 * (nc + n_sub) + (8 * nnz + 8 * nc if args.e2e_rows == "blocks" else 12 * nnz) + 24 * nc + 8 * B
     h2d = q_host.nbytes
 
     t = torch.tensor([ms, e2e_ms], dtype=torch.float64, device="cuda")
@@ -276,7 +278,7 @@ def run_ours(args, scene, rank, world, local_rank):
             "e2e": {"value": dense_total / (e2e_ms * 1e-3), "unit": UNIT, "ms_per_step": e2e_ms,
                     "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
                     "how": f"{args.e2e_workers} streams x sub-batches of {args.e2e_chunk} seeds ({args.e2e_concurrent} computing at a "
-                           "time), pinned host buffers, "
+                           f"time{', last one tapered' if args.e2e_taper else ''}), rows as {args.e2e_rows}, pinned host buffers, "
                            "wall clock around the whole batch"},
             "gpu_launches": launches, "library_calls_per_step": cu.launches(res)[1],
             "roofline": {"bound": "fp64", "kernel": "narrow phase: k_gjk<double> + k_epa_wp<double> (2 launches)", "achieved": flops / (nms * 1e-3) / 1e12,
@@ -323,6 +325,11 @@ def main():
     ap.add_argument("--e2e-chunk", type=int, default=1024, help="seeds per sub-batch of the host-buffer (e2e) leg")
     ap.add_argument("--e2e-workers", type=int, default=3, help="streams / host threads of the e2e leg")
     ap.add_argument("--e2e-concurrent", type=int, default=2, help="sub-batches allowed to compute at the same time")
+    ap.add_argument("--e2e-rows", default="blocks", choices=["blocks", "csr"],
+                    help="form in which the rows reach the host: block form (tc_result_rows_blocks: first column of the "
+                         "T0 / T1 run per row) or full CSR with one column index per non-zero (tc_result_rows)")
+    ap.add_argument("--e2e-taper", type=int, default=1, help="cut the last sub-batch into 1/2 + 1/4 + 1/4 (its download "
+                    "is the part nothing overlaps)")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))

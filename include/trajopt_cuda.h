@@ -254,6 +254,17 @@ int tc_result_rows(const tc_result* res, int64_t* row_ptr, int32_t* col_idx, dou
 int tc_result_rows_async(const tc_result* res, int64_t* row_ptr, int32_t* col_idx, double* val, double* row_value,
                          double* row_coeff, double* row_margin);
 int tc_result_wait(const tc_result* res);
+/* The same rows without explicit column indices.  A row's non-zeros are runs of n_dof consecutive columns — the
+ * variables of timestep `term` (T0 block) and of `term + 1` (T1 block) — exactly what the reference's D constraints
+ * write with insertBack(row, var.getIndex() + j) (discrete_collision_constraint.cpp:262-281,
+ * continuous_collision_constraint.cpp:353-413).  row_first_col[n_rows][2] = first column of the T0 / T1 run, -1 where
+ * the block is absent (fixed timestep, single-timestep evaluator); val holds the runs back to back as in tc_result_rows
+ * (row i at val[row_ptr[i]]).  Saves the 4 bytes per non-zero of col_idx on the device -> host path, which is what
+ * bounds the host-buffer pass.  The _async form follows tc_result_rows_async. */
+int tc_result_rows_blocks(const tc_result* res, int64_t* row_ptr, int32_t* row_first_col, double* val, double* row_value,
+                          double* row_coeff, double* row_margin);
+int tc_result_rows_blocks_async(const tc_result* res, int64_t* row_ptr, int32_t* row_first_col, double* val,
+                                double* row_value, double* row_coeff, double* row_margin);
 /* same rows left in device memory (for a consumer that assembles the QP on the GPU); valid until the next
  * tc_eval on this result */
 int tc_result_rows_device(const tc_result* res, const int64_t** row_ptr, const int32_t** col_idx, const double** val,

@@ -138,3 +138,20 @@ def test_rows_folded_inside_the_pass_equal_rows_on_demand(cuda, evaluator, stack
         assert (a[k] == b[k]).all(), k
     with pytest.raises(capi.TcError):
         rb.gradients()
+
+
+def test_block_rows_equal_csr_rows(cuda):
+    """tc_result_rows_blocks carries the same rows as tc_result_rows; the column indices follow from the block form"""
+    s = helpers.load_scene("arm_around_table")
+    sg = cuda.scene(s, 0.025, 20.0, 0.01)
+    q = s["seed_traj"][None]
+    fixed = np.zeros(q.shape[1], np.uint8)
+    fixed[0] = fixed[-1] = 1
+    for ev in (capi.EVAL_LVS_CONTINUOUS, capi.EVAL_DISCRETE):
+        for want in (capi.WANT_LINEARISE, capi.WANT_ALL):
+            r = cuda.eval(sg, q, ev, lvs=0.02, fixed=fixed, want=want)
+            a, b = r.rows(), r.rows_blocks()
+            assert len(a["val"]) > 0
+            assert np.array_equal(a["row_ptr"], b["row_ptr"]) and np.array_equal(a["val"], b["val"])
+            assert np.array_equal(a["value"], b["value"]) and np.array_equal(a["coeff"], b["coeff"])
+            assert np.array_equal(a["col_idx"], capi.expand_columns(b["row_ptr"], b["first_col"], sg.n_dof))

@@ -21,14 +21,19 @@ sg = cu.scene(scene, ms_.MARGIN, ms_.COEFF, ms_.BUFFER)
 q = torch.from_numpy(ms_.make_batch(scene, 0, B)).cuda()
 res = capi.Result(cu, sg, cu.new_result(sg), B, ms_.T_STEPS)
 st = torch.cuda.current_stream().cuda_stream
-acc = []
+prec = capi.PRECISION_F32 if os.environ.get("TC_PROBE_PREC") == "f32" else capi.PRECISION_F64
+acc, wall = [], []
+import time
 for i in range(3 + reps):
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
     cu.eval_device(sg, q.data_ptr(), B, ms_.T_STEPS, capi.EVAL_LVS_CONTINUOUS, res, lvs=ms_.LVS, fixed=ms_.fixed_steps(),
-                   stream=st, want=capi.WANT_LINEARISE)
+                   stream=st, want=capi.WANT_LINEARISE, precision=prec)
     cu.sync(res)
     if i >= 3:
+        wall.append(1e3 * (time.perf_counter() - t0))
         acc.append(cu.stage_ms(res))
 m = np.mean(np.array(acc), axis=0)
 c = res.counts()
-print("tag=%s gjk=%.3f epa=%.3f narrow=%.3f fk=%.3f broad=%.3f tail=%.3f total=%.3f contacts=%d" % (
-    os.environ.get("TAG", ""), m[8], m[9], m[5], m[0], m[6], m[3], m[4], c["n_contacts"]))
+print("tag=%s gjk=%.3f epa=%.3f narrow=%.3f fk=%.3f broad=%.3f tail=%.3f total=%.3f wall=%.3f contacts=%d" % (
+    os.environ.get("TAG", ""), m[8], m[9], m[5], m[0], m[6], m[3], m[4], float(np.mean(wall)), c["n_contacts"]))

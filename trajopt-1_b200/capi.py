@@ -86,6 +86,21 @@ def _p(a, t):
     return a.ctypes.data_as(t)
 
 
+def expand_columns(row_ptr, first_col, n_dof):
+    """col_idx of tc_result_rows from the block form of tc_result_rows_blocks: every present block of a row is a run
+    of n_dof consecutive columns"""
+    col = np.zeros(int(row_ptr[-1]), np.int32)
+    if len(first_col) == 0:
+        return col
+    present = first_col >= 0
+    start = row_ptr[:-1, None] + np.cumsum(present, axis=1) * n_dof - present * n_dof  # first non-zero of each block
+    for b in range(2):
+        rows = np.nonzero(present[:, b])[0]
+        idx = start[rows, b][:, None] + np.arange(n_dof)[None, :]
+        col[idx] = first_col[rows, b][:, None] + np.arange(n_dof, dtype=np.int32)[None, :]
+    return col
+
+
 class TcError(RuntimeError):
     pass
 
@@ -199,6 +214,19 @@ class Result:
                                                   _p(rv, _pd), _p(rc, _pd), _p(rm, _pd)))
         nnz = int(row_ptr[-1])
         return dict(row_ptr=row_ptr, col_idx=col[:nnz], val=val[:nnz], value=rv, coeff=rc, margin=rm)
+
+    def rows_blocks(self):
+        """rows without explicit column indices (tc_result_rows_blocks); `expand_columns` rebuilds col_idx"""
+        n = self.counts()["n_contacts"]
+        nd = self.scene.n_dof
+        row_ptr = np.zeros(n + 1, np.int64)
+        first = np.full((max(1, n), 2), -1, np.int32)
+        val = np.zeros(max(1, 2 * n * nd))
+        rv, rc, rm = np.zeros(n), np.zeros(n), np.zeros(n)
+        self.lib.check(self.lib.fn("result_rows_blocks")(self.handle, _p(row_ptr, _pl), _p(first, _pi), _p(val, _pd),
+                                                         _p(rv, _pd), _p(rc, _pd), _p(rm, _pd)))
+        nnz = int(row_ptr[-1])
+        return dict(row_ptr=row_ptr, first_col=first[:n], val=val[:nnz], value=rv, coeff=rc, margin=rm)
 
     def sets(self, max_num_cnt):
         nt = self.counts()["n_terms"]

@@ -85,7 +85,7 @@ struct tc_result
   DevBuf<unsigned char> sort_temp, deep_scratch;
   DevBuf<double> cost_term, cost_traj;
   // rows
-  DevBuf<int32_t> col_idx;
+  DevBuf<int32_t> col_idx, row_block;
   DevBuf<double> row_val, row_value, row_coeff, row_margin;
   // sets
   DevBuf<tc_set> sets;
@@ -488,11 +488,13 @@ int enqueueRows(tc_result* r, bool fused)
   TC_RESERVE(r->row_ptr, nc + 1);
   TC_RESERVE(r->term_row_base, r->ep.n_terms + 1);
   TC_RESERVE(r->col_idx, 2 * nc * hs.n_dof);
+  TC_RESERVE(r->row_block, 2 * nc);
   TC_RESERVE(r->row_val, 2 * nc * hs.n_dof);
   TC_RESERVE(r->row_value, nc);
   TC_RESERVE(r->row_coeff, nc);
   TC_RESERVE(r->row_margin, nc);
   w.row_ptr = r->row_ptr.p;
+  w.row_block = r->row_block.p;
   TC_CUDA(launchRowBase(r->scene->dview, w, r->term_row_base.p, r->stream));
   if (fused)
     TC_CUDA(launchGradRows(r->scene->dview, w, r->term_row_base.p, r->col_idx.p, r->row_val.p, r->row_value.p,
@@ -735,7 +737,7 @@ void tc_result_destroy(tc_result* r)
   r->ghas.release(), r->raw.release(), r->keys.release(), r->keys_alt.release(), r->contacts_tmp.release();
   r->contacts.release(), r->xf.release(), r->grad.release(), r->term_ptr.release();
   r->row_ptr.release(), r->term_row_base.release(), r->grec.release(), r->sort_temp.release();
-  r->deep_scratch.release(), r->cost_term.release(), r->cost_traj.release(), r->col_idx.release();
+  r->deep_scratch.release(), r->cost_term.release(), r->cost_traj.release(), r->col_idx.release(), r->row_block.release();
   r->row_val.release(), r->row_value.release(), r->row_coeff.release(), r->row_margin.release();
   r->epa_cursor.release(), r->item_state.release(), r->epa_rec.release();
   r->sets.release(), r->set_count.release(), r->set_run.release(), r->set_values.release();
@@ -822,7 +824,7 @@ int tc_result_gradients(const tc_result* res, tc_gradient* rec, double* grad, si
 }
 
 static int rowsDownload(const tc_result* res_c, int64_t* row_ptr, int32_t* col_idx, double* val, double* row_value,
-                        double* row_coeff, double* row_margin, bool wait)
+                        double* row_coeff, double* row_margin, bool wait, int32_t* row_first_col = nullptr)
 {
   TC_TRY(needValid(res_c));
   tc_result* r = const_cast<tc_result*>(res_c);
@@ -833,7 +835,8 @@ static int rowsDownload(const tc_result* res_c, int64_t* row_ptr, int32_t* col_i
   TC_CUDA(cudaMemcpyAsync(row_ptr, r->row_ptr.p, (nc + 1) * sizeof(int64_t), cudaMemcpyDeviceToHost, r->stream));
   if (nnz)
   {
-    TC_CUDA(cudaMemcpyAsync(col_idx, r->col_idx.p, nnz * sizeof(int32_t), cudaMemcpyDeviceToHost, r->stream));
+    if (col_idx)
+      TC_CUDA(cudaMemcpyAsync(col_idx, r->col_idx.p, nnz * sizeof(int32_t), cudaMemcpyDeviceToHost, r->stream));
     TC_CUDA(cudaMemcpyAsync(val, r->row_val.p, nnz * sizeof(double), cudaMemcpyDeviceToHost, r->stream));
   }
   if (nc)
@@ -841,6 +844,8 @@ static int rowsDownload(const tc_result* res_c, int64_t* row_ptr, int32_t* col_i
     TC_CUDA(cudaMemcpyAsync(row_value, r->row_value.p, nc * sizeof(double), cudaMemcpyDeviceToHost, r->stream));
     TC_CUDA(cudaMemcpyAsync(row_coeff, r->row_coeff.p, nc * sizeof(double), cudaMemcpyDeviceToHost, r->stream));
     TC_CUDA(cudaMemcpyAsync(row_margin, r->row_margin.p, nc * sizeof(double), cudaMemcpyDeviceToHost, r->stream));
+    if (row_first_col)
+      TC_CUDA(cudaMemcpyAsync(row_first_col, r->row_block.p, 2 * nc * sizeof(int32_t), cudaMemcpyDeviceToHost, r->stream));
   }
   trace(r, "rows download enqueued");
   if (wait)
@@ -861,6 +866,22 @@ int tc_result_rows_async(const tc_result* res, int64_t* row_ptr, int32_t* col_id
                          double* row_coeff, double* row_margin)
 {
   return rowsDownload(res, row_ptr, col_idx, val, row_value, row_coeff, row_margin, false);
+}
+
+int tc_result_rows_blocks(const tc_result* res, int64_t* row_ptr, int32_t* row_first_col, double* val, double* row_value,
+                          double* row_coeff, double* row_margin)
+{
+  if (!row_first_col)
+    return fail(TC_ERR_INVALID, "null argument");
+  return rowsDownload(res, row_ptr, nullptr, val, row_value, row_coeff, row_margin, true, row_first_col);
+}
+
+int tc_result_rows_blocks_async(const tc_result* res, int64_t* row_ptr, int32_t* row_first_col, double* val,
+                                double* row_value, double* row_coeff, double* row_margin)
+{
+  if (!row_first_col)
+    return fail(TC_ERR_INVALID, "null argument");
+  return rowsDownload(res, row_ptr, nullptr, val, row_value, row_coeff, row_margin, false, row_first_col);
 }
 
 int tc_stream_create(void** stream)

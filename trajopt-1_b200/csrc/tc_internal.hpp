@@ -120,6 +120,7 @@ struct Work
   tc_gradient* grec;
   int32_t* ghas;
   long long* row_ptr;
+  int32_t* row_block;    // [n_rows][2] first column of the T0 / T1 run of every row (-1 = block absent)
   Counters* counters;
   long long n_states, n_units, n_items_padded, n_raw, n_contacts;
   long long raw_cap, deep_cap;

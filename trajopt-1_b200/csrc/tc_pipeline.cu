@@ -690,6 +690,8 @@ __device__ __forceinline__ void writeRow(const SceneView& v, const Work& w, long
   const int nb = (f0 ? 0 : 1) + ((single || f1) ? 0 : 1);
   long long nnz = term_row_base[k] + (i - w.term_ptr[k]) * nb * n;
   w.row_ptr[i] = nnz;
+  w.row_block[2 * i] = f0 ? -1 : c.term * n;
+  w.row_block[2 * i + 1] = (single || f1) ? -1 : (c.term + 1) * n;
   const PairD pr = v.pairs[c.pair];
   const double* q0 = w.q + (static_cast<size_t>(c.traj) * w.ep.T + c.term) * n;
   double constant = c.distance;
@@ -1186,8 +1188,13 @@ cudaError_t launchFinalize(const SceneView& v, const Work& w, cudaStream_t st)
 
 cudaError_t sortContacts(const Work& w, void* temp, size_t& temp_bytes, cudaStream_t st)
 {
+  // key = term << 36 | pair << 22 | substep << 8 | k: only the bits below 36 + bits(n_terms) can differ between valid
+  // keys; the all-ones key of a dropped contact stays the largest within any bit range
+  int end_bit = 37;
+  while (end_bit < 64 && (static_cast<long long>(w.ep.n_terms) >> (end_bit - 36)) != 0)
+    ++end_bit;
   return cub::DeviceRadixSort::SortPairs(temp, temp_bytes, w.keys, w.keys_alt, w.idx, w.idx_alt,
-                                         static_cast<int>(w.n_raw), 0, 64, st);
+                                         static_cast<int>(w.n_raw), 0, end_bit, st);
 }
 
 cudaError_t launchGather(const SceneView& v, const Work& w, cudaStream_t st)

@@ -99,12 +99,12 @@ class PipelinedEvaluator:
     torch is used for pinned host memory and stream objects only."""
 
     def __init__(self, cu, scene, evaluator, lvs, fixed, n_dof, chunk=1024, n_workers=2, rows_per_seed=1400,
-                 concurrent=1):
+                 concurrent=1, taper=True, compact=True):
         import queue
         import threading
         import torch
         self.cu, self.scene, self.evaluator, self.lvs, self.fixed = cu, scene, evaluator, lvs, fixed
-        self.chunk, self.n_dof = chunk, n_dof
+        self.chunk, self.n_dof, self.taper, self.compact = chunk, n_dof, taper, compact
         self.torch = torch
         self.capi = cu.capi if hasattr(cu, "capi") else None
         self.workers = []
@@ -127,7 +127,8 @@ class PipelinedEvaluator:
         pin = lambda n, dt: torch.empty(n, dtype=dt).pin_memory().numpy()
         return dict(cap=cap, row_ptr=pin(cap + 1, torch.int64), col=pin(2 * cap * nd, torch.int32),
                     val=pin(2 * cap * nd, torch.float64), value=pin(cap, torch.float64), coeff=pin(cap, torch.float64),
-                    margin=pin(cap, torch.float64), cost=pin(self.chunk, torch.float64))
+                    margin=pin(cap, torch.float64), cost=pin(self.chunk, torch.float64),
+                    first=pin(2 * cap, torch.int32))
 
     def _work(self, w, stream, bufs):
         import ctypes as C
@@ -152,10 +153,14 @@ class PipelinedEvaluator:
                         bufs.update(self._alloc(int(n * 1.25)))
                     # the copies are enqueued before the next sub-batch may start (still under the lock) and
                     # awaited after it has started
-                    cu.check(cu.dll.tc_result_rows_async(
-                        res.handle, bufs["row_ptr"].ctypes.data_as(pl), bufs["col"].ctypes.data_as(pi),
-                        bufs["val"].ctypes.data_as(pd), bufs["value"].ctypes.data_as(pd),
-                        bufs["coeff"].ctypes.data_as(pd), bufs["margin"].ctypes.data_as(pd)))
+                    # compact: the rows travel in block form (first column of the T0 / T1 run of every row instead
+                    # of one column index per non-zero, tc_result_rows_blocks_async) — the device -> host path is what
+                    # bounds this pass
+                    fn = cu.dll.tc_result_rows_blocks_async if self.compact else cu.dll.tc_result_rows_async
+                    cols = bufs["first"] if self.compact else bufs["col"]
+                    cu.check(fn(res.handle, bufs["row_ptr"].ctypes.data_as(pl), cols.ctypes.data_as(pi),
+                                bufs["val"].ctypes.data_as(pd), bufs["value"].ctypes.data_as(pd),
+                                bufs["coeff"].ctypes.data_as(pd), bufs["margin"].ctypes.data_as(pd)))
                 cu.check(cu.dll.tc_result_wait(res.handle))
                 cu.check(cu.dll.tc_result_cost(res.handle, None, bufs["cost"].ctypes.data_as(pd)))
                 c = r.counts()
@@ -167,17 +172,26 @@ class PipelinedEvaluator:
         """q_pinned: numpy view of pinned host memory [B, T, n_dof].  Returns (costs[B], n_rows, nnz, n_dense);
         the rows of sub-batch i are in worker (i % n_workers)'s pinned buffers when its entry arrives."""
         B = len(q_pinned)
-        n_jobs = 0
-        for i, lo in enumerate(range(0, B, self.chunk)):
-            self.jobs[i % len(self.jobs)].put((i, q_pinned[lo:lo + self.chunk]))
-            n_jobs += 1
+        # sub-batch bounds: whole chunks, the last one cut in halves and quarters — the run ends with the download of
+        # the last sub-batch, which nothing overlaps, so that one is kept small
+        bounds, lo = [], 0
+        while lo < B:
+            hi = min(B, lo + self.chunk)
+            if hi == B and self.taper and hi - lo >= 4:
+                h, q = lo + (hi - lo) // 2, lo + 3 * (hi - lo) // 4
+                bounds += [(lo, h), (h, q), (q, hi)]
+            else:
+                bounds.append((lo, hi))
+            lo = hi
+        for i, (lo, hi) in enumerate(bounds):
+            self.jobs[i % len(self.jobs)].put((i, q_pinned[lo:hi]))
         costs = np.zeros(B)
         rows = nnz = dense = 0
-        for _ in range(n_jobs):
+        for _ in range(len(bounds)):
             idx, w, n, z, d, cost, err = self.done.get()
             if err is not None:
                 raise err
-            costs[idx * self.chunk: idx * self.chunk + len(cost)] = cost
+            costs[bounds[idx][0]: bounds[idx][0] + len(cost)] = cost
             rows, nnz, dense = rows + n, nnz + z, dense + d
         return costs, rows, nnz, dense
 
