@@ -406,6 +406,21 @@ __global__ void __launch_bounds__(TPB) k_broad(SceneView v, Work w)
   constexpr int TILE = 32;
   __shared__ Partner tile[TILE];
   uint32_t bits = 0;
+  // box of the warp's 32 units (mostly consecutive sub-segments of one trajectory): a static partner that misses it
+  // misses every lane, and is dismissed with one warp-uniform test instead of 32 tests, a ballot and a branch
+  double wlo[3], whi[3];
+#pragma unroll
+  for (int r = 0; r < 3; ++r)
+  {
+    wlo[r] = inb ? alo[r] : 1e300;
+    whi[r] = inb ? ahi[r] : -1e300;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1)
+    {
+      wlo[r] = fmin(wlo[r], __shfl_xor_sync(0xffffffffu, wlo[r], o));
+      whi[r] = fmax(whi[r], __shfl_xor_sync(0xffffffffu, whi[r], o));
+    }
+  }
   for (int t0 = p_begin; t0 < p_end; t0 += TILE)
   {
     const int tn = min(TILE, p_end - t0);
@@ -432,6 +447,13 @@ __global__ void __launch_bounds__(TPB) k_broad(SceneView v, Work w)
       double blo[3], bhi[3];
       if (pr.bidx < 0)
       {
+        bool miss = false;
+#pragma unroll
+        for (int r = 0; r < 3; ++r)
+          if (wlo[r] - pr.hi[r] > pr.thr || pr.lo[r] - whi[r] > pr.thr)
+            miss = true;
+        if (miss)
+          continue;
 #pragma unroll
         for (int r = 0; r < 3; ++r)
           blo[r] = pr.lo[r], bhi[r] = pr.hi[r];
