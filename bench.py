@@ -201,6 +201,18 @@ def run_ours(args, scene, rank, world, local_rank):
     counts = res.counts()
     stage = cu.stage_ms(res)
 
+    # ---- device-side assembly of the hinge-cost QP block in CSC form, timed on its own: not part of
+    # the step, reported next to it
+    csc_ms = []
+    for _ in range(3):
+        step_device()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        cu.check(cu.dll.tc_result_qp_csc_device(res.handle, None, None, None, None, None, None, None, None))
+        b.record()
+        torch.cuda.synchronize()
+        csc_ms.append(a.elapsed_time(b))
+
     # ---- end to end through the C ABI with HOST buffers: H2D of q, D2H of rows + costs, every step.
     # Sub-batches of 1024 seeds alternate between two streams so the D2H of one overlaps the kernels of the next
     # (multistart.PipelinedEvaluator); each sub-batch is a plain tc_eval + tc_result_rows + tc_result_cost.
@@ -292,6 +304,9 @@ def run_ours(args, scene, rank, world, local_rank):
                              "frac": (hbm_bytes / (rest_ms * 1e-3) / 1e9 / peaks["hbm_gbs"]) if peaks.get("hbm_gbs") else None,
                              "algorithmic_bytes": int(hbm_bytes), "ms": rest_ms,
                              "peak_source": "MEASURED_PEAKS.json hbm_gbs (burst copy)"},
+            "qp_csc": {"ms": float(np.mean(csc_ms[1:])), "what": "tc_result_qp_csc_device: hinge-cost QP block [A_x | -I] of "
+                       "all rows assembled on the device in CSC form (3 kernels), outside the timed step",
+                       "nnz": int(counts["nnz"] + counts["n_contacts"])},
             "cpu_baseline": base,
             "counters": {k: counts[k] for k in ("n_dense", "n_units", "n_narrowphase", "n_contacts", "gjk_iters",
                                                 "epa_iters", "n_epa", "support_verts", "n_unconverged")},

@@ -29,6 +29,9 @@
  *                                                                   trajopt_ifopt/.../continuous_collision_constraint.cpp:80-236
  *   tc_result_cost      CollisionCost::value / CollisionConstraint::value
  *                                                                   trajopt/src/collision_terms.cpp:1287-1306,1367-1386
+ *   tc_result_qp_csc    CollisionCost::convex + addHinge rows as the CSC matrix OSQPModel::updateConstraints builds
+ *                                                                   trajopt/src/collision_terms.cpp:1267-1285
+ *                                                                   trajopt_sco/src/modeling.cpp:19-27, osqp_interface.cpp:213-280
  *   tc_allgather_best   (no reference counterpart: multi-start winner selection across GPUs)
  *
  * Conventions: plain C, opaque handles, int status (0 = TC_OK), thread-local error string.
@@ -269,6 +272,24 @@ int tc_result_rows_blocks_async(const tc_result* res, int64_t* row_ptr, int32_t*
  * tc_eval on this result */
 int tc_result_rows_device(const tc_result* res, const int64_t** row_ptr, const int32_t** col_idx, const double** val,
                           const double** row_value, const double** row_coeff, const double** row_margin);
+/* QP constraint block of the collision hinge costs in compressed-sparse-COLUMN form, assembled on the device — what
+ * CollisionCost::convex + ConvexObjective::addHinge produce (trajopt/src/collision_terms.cpp:1267-1285,
+ * trajopt_sco/src/modeling.cpp:19-27) after OSQPModel::updateConstraints / exprToEigen have turned the expressions
+ * into OSQP's matrix (trajopt_sco/src/osqp_interface.cpp:213-280, solver_utils.cpp:111-144).
+ *   rows    : the contact rows of tc_result_rows, same order (n_rows)
+ *   columns : [ B*T*n_dof trajectory variables, column b*T*n_dof + t*n_dof + j | one slack variable per row ]
+ *   A = [ -G | -I ], upper = constant - margin    (legacy stack: d(x) = constant + G.x, row: margin - d(x) - s <= 0)
+ *   A = [  J | -I ], upper = J.x0 - (margin - d)  (ifopt stack: violation linearised at the iterate x0)
+ *   slack_cost[i] = coeff of row i (objective term coeff * s_i; s_i >= 0 is the caller's variable bound)
+ * col_ptr[n_cols + 1], row_idx[nnz], val[nnz] with n_cols = B*T*n_dof + n_rows and nnz = counts.nnz + n_rows; row
+ * indices ascend inside every column.  The block of trajectory b is the contiguous row range of its terms and the
+ * columns b*T*n_dof .. (b+1)*T*n_dof - 1 plus its rows' slack columns. */
+int tc_result_qp_csc(const tc_result* res, int64_t* col_ptr, int32_t* row_idx, double* val, double* upper,
+                     double* slack_cost);
+/* the same arrays left on the device (valid until the next tc_eval on this result); any output pointer may be NULL */
+int tc_result_qp_csc_device(const tc_result* res, const int64_t** col_ptr, const int32_t** row_idx, const double** val,
+                            const double** upper, const double** slack_cost, int64_t* n_rows, int64_t* n_cols,
+                            int64_t* nnz);
 /* fixed-size constraints: sets of every term sorted as the evaluator sorts them, the first
  * min(max_num_cnt, n) of each term turned into rows.  set_ptr[n_terms + 1].
  * values[n_terms][max_num_cnt], coeffs idem, jac[n_terms][max_num_cnt][2][n_dof] (T0 block, T1 block) */

@@ -155,3 +155,42 @@ def test_block_rows_equal_csr_rows(cuda):
             assert np.array_equal(a["row_ptr"], b["row_ptr"]) and np.array_equal(a["val"], b["val"])
             assert np.array_equal(a["value"], b["value"]) and np.array_equal(a["coeff"], b["coeff"])
             assert np.array_equal(a["col_idx"], capi.expand_columns(b["row_ptr"], b["first_col"], sg.n_dof))
+
+
+@pytest.mark.parametrize("stack", [capi.STACK_LEGACY, capi.STACK_IFOPT])
+@pytest.mark.parametrize("evaluator", [capi.EVAL_LVS_CONTINUOUS, capi.EVAL_LVS_DISCRETE, capi.EVAL_DISCRETE])
+def test_qp_csc_block_matches_rows(cuda, oracle, stack, evaluator):
+    """device-assembled hinge block [A_x | -I] (tc_result_qp_csc) against the same matrix built on the
+    host with scipy from the rows (which the other tests hold against the oracle): identical structure and values"""
+    import scipy.sparse as sp
+    s, sg, so = pair(cuda, oracle, "arm_around_table", 0.025, 20.0, 0.01)
+    q = helpers.pkg.multistart.make_batch(s, 7, 3, t_steps=6)
+    B, T, n = q.shape
+    fixed = np.zeros(T, np.uint8)
+    fixed[0] = fixed[-1] = 1
+    rg = cuda.eval(sg, q, evaluator, stack=stack, lvs=0.02, fixed=fixed, want=capi.WANT_ALL)
+    m = rg.qp_csc()
+    rows, co = rg.rows(), rg.contacts()
+    check(helpers.compare(oracle.eval(so, q, evaluator, stack=stack, lvs=0.02, fixed=fixed), rg))
+    nr = len(co)
+    assert m["shape"] == (nr, B * T * n + nr) and nr > 0
+    # host construction: global column = traj * T * n + local column
+    counts = np.diff(rows["row_ptr"])
+    ri = np.repeat(np.arange(nr), counts)
+    gc = rows["col_idx"].astype(np.int64) + np.repeat(co["traj"].astype(np.int64), counts) * T * n
+    sign = -1.0 if stack == capi.STACK_LEGACY else 1.0
+    ax = sp.csr_matrix((sign * rows["val"], (ri, gc)), shape=(nr, B * T * n))
+    want = sp.hstack([ax, -sp.identity(nr)]).tocsc()
+    want.sort_indices()
+    assert np.array_equal(m["col_ptr"], want.indptr)
+    assert np.array_equal(m["row_idx"], want.indices)
+    assert np.array_equal(m["val"], want.data)
+    if stack == capi.STACK_LEGACY:
+        upper = rows["value"] - rows["margin"]
+    else:
+        x0 = q.reshape(B, T * n)
+        jx0 = np.array([rows["val"][rows["row_ptr"][i]:rows["row_ptr"][i + 1]] @
+                        x0[co["traj"][i]][rows["col_idx"][rows["row_ptr"][i]:rows["row_ptr"][i + 1]]] for i in range(nr)])
+        upper = jx0 - rows["value"]
+    assert np.abs(m["upper"] - upper).max() <= 1e-12 * max(1.0, np.abs(upper).max())
+    assert np.array_equal(m["slack_cost"], rows["coeff"])

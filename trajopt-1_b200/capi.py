@@ -228,6 +228,22 @@ class Result:
         nnz = int(row_ptr[-1])
         return dict(row_ptr=row_ptr, first_col=first[:n], val=val[:nnz], value=rv, coeff=rc, margin=rm)
 
+    def qp_csc(self):
+        """hinge-cost QP block [A_x | -I] in CSC form (tc_result_qp_csc)"""
+        nr, ncol, nz = C.c_int64(), C.c_int64(), C.c_int64()
+        # sizes first (this assembles the block on the device if it has not been yet)
+        self.lib.check(self.lib.fn("result_qp_csc_device")(self.handle, None, None, None, None, None, C.byref(nr),
+                                                           C.byref(ncol), C.byref(nz)))
+        n, n_cols, nnz = nr.value, ncol.value, nz.value
+        col_ptr = np.zeros(n_cols + 1, np.int64)
+        row_idx = np.zeros(max(1, nnz), np.int32)
+        val = np.zeros(max(1, nnz))
+        upper, cost = np.zeros(max(1, n)), np.zeros(max(1, n))
+        self.lib.check(self.lib.fn("result_qp_csc")(self.handle, _p(col_ptr, _pl), _p(row_idx, _pi), _p(val, _pd),
+                                                    _p(upper, _pd), _p(cost, _pd)))
+        return dict(col_ptr=col_ptr, row_idx=row_idx[:nnz], val=val[:nnz], upper=upper[:n], slack_cost=cost[:n],
+                    shape=(n, n_cols))
+
     def sets(self, max_num_cnt):
         nt = self.counts()["n_terms"]
         nc = self.counts()["n_contacts"]

@@ -80,7 +80,10 @@ struct tc_result
   DevBuf<unsigned long long> keys, keys_alt;
   DevBuf<tc_contact> contacts_tmp, contacts;
   DevBuf<double> xf, grad;
-  DevBuf<long long> term_ptr, row_ptr, term_row_base;
+  DevBuf<long long> term_ptr, row_ptr, term_row_base, csc_bt_base, csc_col_ptr;
+  DevBuf<int32_t> csc_row_idx;
+  DevBuf<double> csc_val, csc_upper, csc_cost;
+  bool have_csc{ false };
   DevBuf<tc_gradient> grec;
   DevBuf<unsigned char> sort_temp, deep_scratch;
   DevBuf<double> cost_term, cost_traj;
@@ -198,6 +201,7 @@ int runEval(tc_scene* scene, const tc_eval_desc* desc, const double* q, int32_t 
   r->valid = false;
   r->pending = false;
   r->have_grad = r->have_cost = r->have_rows = false;
+  r->have_csc = false;
   r->stream = st;
   r->desc = *desc;
   r->desc.fixed_steps = nullptr;
@@ -738,6 +742,8 @@ void tc_result_destroy(tc_result* r)
   r->contacts.release(), r->xf.release(), r->grad.release(), r->term_ptr.release();
   r->row_ptr.release(), r->term_row_base.release(), r->grec.release(), r->sort_temp.release();
   r->deep_scratch.release(), r->cost_term.release(), r->cost_traj.release(), r->col_idx.release(), r->row_block.release();
+  r->csc_bt_base.release(), r->csc_col_ptr.release(), r->csc_row_idx.release(), r->csc_val.release();
+  r->csc_upper.release(), r->csc_cost.release();
   r->row_val.release(), r->row_value.release(), r->row_coeff.release(), r->row_margin.release();
   r->epa_cursor.release(), r->item_state.release(), r->epa_rec.release();
   r->sets.release(), r->set_count.release(), r->set_run.release(), r->set_values.release();
@@ -926,6 +932,85 @@ int tc_result_rows_device(const tc_result* res_c, const int64_t** row_ptr, const
     *row_coeff = r->row_coeff.p;
   if (row_margin)
     *row_margin = r->row_margin.p;
+  return TC_OK;
+}
+
+// CSC assembly on the result's stream (once per evaluation)
+static int buildQpCsc(tc_result* r)
+{
+  TC_TRY(buildRows(r));
+  if (r->have_csc)
+    return TC_OK;
+  LaunchScope scope(r);
+  const size_t nc = static_cast<size_t>(r->w.n_contacts);
+  const size_t n_bt = static_cast<size_t>(r->ep.B) * static_cast<size_t>(r->ep.T);
+  const size_t n_cols = n_bt * static_cast<size_t>(r->scene->host.n_dof) + nc;
+  const size_t nnz = static_cast<size_t>(r->counts.nnz) + nc;
+  TC_RESERVE(r->csc_bt_base, n_bt + 1);
+  TC_RESERVE(r->csc_col_ptr, n_cols + 1);
+  TC_RESERVE(r->csc_row_idx, nnz);
+  TC_RESERVE(r->csc_val, nnz);
+  TC_RESERVE(r->csc_upper, nc);
+  TC_RESERVE(r->csc_cost, nc);
+  TC_CUDA(launchQpCsc(r->scene->dview, r->w, r->csc_bt_base.p, r->row_val.p, r->row_value.p, r->row_coeff.p,
+                      r->row_margin.p, r->csc_col_ptr.p, r->csc_row_idx.p, r->csc_val.p, r->csc_upper.p, r->csc_cost.p,
+                      r->stream));
+  r->have_csc = true;
+  return TC_OK;
+}
+
+int tc_result_qp_csc_device(const tc_result* res_c, const int64_t** col_ptr, const int32_t** row_idx, const double** val,
+                            const double** upper, const double** slack_cost, int64_t* n_rows, int64_t* n_cols,
+                            int64_t* nnz)
+{
+  TC_TRY(needValid(res_c));
+  tc_result* r = const_cast<tc_result*>(res_c);
+  TC_TRY(buildQpCsc(r));
+  const int64_t nc = r->w.n_contacts;
+  if (col_ptr)
+    *col_ptr = reinterpret_cast<const int64_t*>(r->csc_col_ptr.p);
+  if (row_idx)
+    *row_idx = r->csc_row_idx.p;
+  if (val)
+    *val = r->csc_val.p;
+  if (upper)
+    *upper = r->csc_upper.p;
+  if (slack_cost)
+    *slack_cost = r->csc_cost.p;
+  if (n_rows)
+    *n_rows = nc;
+  if (n_cols)
+    *n_cols = static_cast<int64_t>(r->ep.B) * r->ep.T * r->scene->host.n_dof + nc;
+  if (nnz)
+    *nnz = r->counts.nnz + nc;
+  return TC_OK;
+}
+
+int tc_result_qp_csc(const tc_result* res_c, int64_t* col_ptr, int32_t* row_idx, double* val, double* upper,
+                     double* slack_cost)
+{
+  if (!col_ptr || !row_idx || !val || !upper || !slack_cost)
+    return fail(TC_ERR_INVALID, "null argument");
+  int64_t n_rows = 0, n_cols = 0, nnz = 0;
+  TC_TRY(tc_result_qp_csc_device(res_c, nullptr, nullptr, nullptr, nullptr, nullptr, &n_rows, &n_cols, &nnz));
+  tc_result* r = const_cast<tc_result*>(res_c);
+  TC_CUDA(cudaMemcpyAsync(col_ptr, r->csc_col_ptr.p, static_cast<size_t>(n_cols + 1) * sizeof(int64_t),
+                          cudaMemcpyDeviceToHost, r->stream));
+  if (nnz)
+  {
+    TC_CUDA(cudaMemcpyAsync(row_idx, r->csc_row_idx.p, static_cast<size_t>(nnz) * sizeof(int32_t), cudaMemcpyDeviceToHost,
+                            r->stream));
+    TC_CUDA(cudaMemcpyAsync(val, r->csc_val.p, static_cast<size_t>(nnz) * sizeof(double), cudaMemcpyDeviceToHost,
+                            r->stream));
+  }
+  if (n_rows)
+  {
+    TC_CUDA(cudaMemcpyAsync(upper, r->csc_upper.p, static_cast<size_t>(n_rows) * sizeof(double), cudaMemcpyDeviceToHost,
+                            r->stream));
+    TC_CUDA(cudaMemcpyAsync(slack_cost, r->csc_cost.p, static_cast<size_t>(n_rows) * sizeof(double),
+                            cudaMemcpyDeviceToHost, r->stream));
+  }
+  TC_CUDA(cudaStreamSynchronize(r->stream));
   return TC_OK;
 }
 

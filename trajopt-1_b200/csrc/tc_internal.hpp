@@ -155,6 +155,9 @@ cudaError_t launchRows(const SceneView& v, const Work& w, long long* term_row_ba
 cudaError_t launchGradRows(const SceneView& v, const Work& w, long long* term_row_base, int32_t* col_idx, double* val,
                            double* row_value, double* row_coeff, double* row_margin, cudaStream_t st);
 cudaError_t launchCost(const SceneView& v, const Work& w, double* cost_term, double* cost_traj, cudaStream_t st);
+cudaError_t launchQpCsc(const SceneView& v, const Work& w, long long* bt_base, const double* val, const double* row_value,
+                        const double* row_coeff, const double* row_margin, long long* col_ptr, int32_t* row_idx,
+                        double* out, double* upper, double* slack_cost, cudaStream_t st);
 cudaError_t launchSets(const SceneView& v, const Work& w, int max_num_cnt, tc_set* sets, int32_t* set_count,
                        int32_t* set_run, double* values, double* coeffs, double* jac, cudaStream_t st);
 // ---- launchers (tc_narrow.cu) ----

@@ -792,6 +792,147 @@ __global__ void __launch_bounds__(TPB, TC_GRADROWS_MINB) k_grad_rows(SceneView v
   writeRow(v, w, i, c, g, out.rec, out.has, term_row_base, col_idx, val, row_value, row_coeff, row_margin);
 }
 
+// ---------------------------------------------------------------------------------------------
+// QP constraint block of the collision hinge costs in compressed-sparse-COLUMN form, assembled on the device.
+//   CollisionCost::convex + ConvexObjective::addHinge: per expression a slack s >= 0, the row viol - s <= 0 and the
+//   objective term coeff * s                 (trajopt/src/collision_terms.cpp:1267-1285, trajopt_sco/src/modeling.cpp:19-27)
+//   OSQPModel::updateConstraints / exprToEigen turn those rows into the CSC matrix OSQP takes
+//                                            (trajopt_sco/src/osqp_interface.cpp:213-280, solver_utils.cpp:111-144)
+// Rows = the contact rows in their global order.  Columns = [ B*T*n_dof trajectory variables | one slack per row ].
+// A row touches the n_dof variables of its segment's two timesteps, and the contacts are sorted by (trajectory, term),
+// so the entries of a variable column are two contiguous runs of rows (the T1 blocks of the segment ending at that
+// timestep, then the T0 blocks of the segment starting there): column pointers follow from the term pointer with one
+// scan, and every row writes its entries to computed places — no atomics, no sort.
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ void termBlocks(const Work& w, int ti, bool& has0, bool& has1)
+{
+  const bool single = w.ep.evaluator == TC_EVAL_DISCRETE;
+  has0 = w.term_fixed[2 * ti] == 0;
+  has1 = !(single || w.term_fixed[2 * ti + 1] != 0);
+}
+
+// rows of trajectory b that put a T1 block (rows1) / a T0 block (rows0) into the columns of timestep t
+__device__ __forceinline__ void columnRuns(const Work& w, int b, int t, long long& rows1, long long& rows0)
+{
+  rows1 = rows0 = 0;
+  const int tpt = w.ep.terms_per_traj;
+  for (int ti = 0; ti < tpt; ++ti)
+  {
+    const int tt = w.term_t[ti];
+    if (tt != t && tt != t - 1)
+      continue;
+    bool has0, has1;
+    termBlocks(w, ti, has0, has1);
+    const long long k = static_cast<long long>(b) * tpt + ti;
+    const long long nr = w.term_ptr[k + 1] - w.term_ptr[k];
+    if (tt == t && has0)
+      rows0 = nr;
+    if (tt == t - 1 && has1)
+      rows1 = nr;
+  }
+}
+
+// bt_base[b*T + t] = first entry of the n_dof columns of (b, t); bt_base[B*T] = entries of the variable columns
+__global__ void __launch_bounds__(1024) k_csc_base(SceneView v, Work w, long long* bt_base)
+{
+  __shared__ long long sm[33];
+  long long carry = 0;
+  const int n = w.ep.B * w.ep.T;
+  for (int base = 0; base < n; base += blockDim.x)
+  {
+    const int e = base + threadIdx.x;
+    long long val = 0;
+    if (e < n)
+    {
+      long long r1, r0;
+      columnRuns(w, e / w.ep.T, e % w.ep.T, r1, r0);
+      val = (r1 + r0) * v.n_dof;
+    }
+    long long t;
+    const long long ex = blockExclusive(val, t, sm);
+    if (e < n)
+      bt_base[e] = carry + ex;
+    carry += t;
+  }
+  if (threadIdx.x == 0)
+    bt_base[n] = carry;
+}
+
+__global__ void __launch_bounds__(256) k_csc_colptr(SceneView v, Work w, const long long* bt_base, long long* col_ptr)
+{
+  const long long g = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+  const long long n_bt = static_cast<long long>(w.ep.B) * w.ep.T;
+  const long long n_x = n_bt * v.n_dof;
+  const long long nnz_x = bt_base[n_bt];
+  if (g < n_x)
+  {
+    const long long e = g / v.n_dof;
+    const int j = static_cast<int>(g % v.n_dof);
+    const long long c = (bt_base[e + 1] - bt_base[e]) / v.n_dof;
+    col_ptr[g] = bt_base[e] + j * c;
+  }
+  else if (g <= n_x + w.n_contacts)
+    col_ptr[g] = nnz_x + (g - n_x);  // slack columns hold one entry each; the last value closes the array
+}
+
+__global__ void __launch_bounds__(TPB) k_csc_fill(SceneView v, Work w, const long long* bt_base, const double* val,
+                                                  const double* row_value, const double* row_coeff,
+                                                  const double* row_margin, int32_t* row_idx, double* out,
+                                                  double* upper, double* slack_cost)
+{
+  const long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (i >= w.n_contacts)
+    return;
+  const int k = termOfContact(w, i);
+  const int tpt = w.ep.terms_per_traj;
+  const int b = k / tpt, ti = k % tpt, t = w.term_t[ti], n = v.n_dof;
+  bool has0, has1;
+  termBlocks(w, ti, has0, has1);
+  const long long local = i - w.term_ptr[k];
+  const long long r0 = w.row_ptr[i];
+  const bool legacy = w.ep.stack == TC_STACK_LEGACY;
+  // legacy rows hold the affine distance d(x) = c + g.x: the hinge row is  -g.x - s <= c - margin.
+  // ifopt rows hold the violation margin - d and its Jacobian J at x0:     J.x - s <= J.x0 - (margin - d)
+  const double sign = legacy ? -1.0 : 1.0;
+  const double* x0 = w.q + (static_cast<size_t>(b) * w.ep.T + t) * n;
+  double jx0 = 0;
+  int blk = 0;
+  if (has0)
+  {
+    const long long e = static_cast<long long>(b) * w.ep.T + t;
+    const long long c = (bt_base[e + 1] - bt_base[e]) / n;
+    long long r1, rr0;
+    columnRuns(w, b, t, r1, rr0);
+    for (int j = 0; j < n; ++j)
+    {
+      const double a = val[r0 + j];
+      const long long pos = bt_base[e] + j * c + r1 + local;
+      row_idx[pos] = static_cast<int32_t>(i);
+      out[pos] = sign * a;
+      jx0 += a * x0[j];
+    }
+    ++blk;
+  }
+  if (has1)
+  {
+    const long long e = static_cast<long long>(b) * w.ep.T + t + 1;
+    const long long c = (bt_base[e + 1] - bt_base[e]) / n;
+    for (int j = 0; j < n; ++j)
+    {
+      const double a = val[r0 + blk * n + j];
+      const long long pos = bt_base[e] + j * c + local;
+      row_idx[pos] = static_cast<int32_t>(i);
+      out[pos] = sign * a;
+      jx0 += a * x0[n + j];
+    }
+  }
+  const long long nnz_x = bt_base[static_cast<long long>(w.ep.B) * w.ep.T];
+  row_idx[nnz_x + i] = static_cast<int32_t>(i);
+  out[nnz_x + i] = -1.0;
+  upper[i] = legacy ? row_value[i] - row_margin[i] : jx0 - row_value[i];
+  slack_cost[i] = row_coeff[i];
+}
+
 // CollisionCost::value / CollisionConstraint::value (collision_terms.cpp:1287-1306,1367-1386)
 __global__ void __launch_bounds__(TPB) k_cost_term(SceneView v, Work w, double* cost_term)
 {
@@ -1291,6 +1432,24 @@ cudaError_t launchCost(const SceneView& v, const Work& w, double* cost_term, dou
   k_cost_term<<<gridFor(static_cast<long long>(w.ep.n_terms) * 32, TPB), TPB, 0, st>>>(v, w, cost_term);
   ++launchCounter();
   k_cost_traj<<<gridFor(w.ep.B, TPB), TPB, 0, st>>>(w, cost_term, cost_traj);
+  return cudaGetLastError();
+}
+
+cudaError_t launchQpCsc(const SceneView& v, const Work& w, long long* bt_base, const double* val, const double* row_value,
+                        const double* row_coeff, const double* row_margin, long long* col_ptr, int32_t* row_idx,
+                        double* out, double* upper, double* slack_cost, cudaStream_t st)
+{
+  ++launchCounter();
+  k_csc_base<<<1, 1024, 0, st>>>(v, w, bt_base);
+  const long long n_cols = static_cast<long long>(w.ep.B) * w.ep.T * v.n_dof + w.n_contacts + 1;
+  ++launchCounter();
+  k_csc_colptr<<<gridFor(n_cols, 256), 256, 0, st>>>(v, w, bt_base, col_ptr);
+  if (w.n_contacts > 0)
+  {
+    ++launchCounter();
+    k_csc_fill<<<gridFor(w.n_contacts, TPB), TPB, 0, st>>>(v, w, bt_base, val, row_value, row_coeff, row_margin, row_idx,
+                                                         out, upper, slack_cost);
+  }
   return cudaGetLastError();
 }
 
