@@ -175,6 +175,49 @@ TC_HDN inline void averageSupport(const SceneView& v, const ShapeD& sh, Vec3<dou
   }
 }
 
+// the two GetAverageSupport scans of calculateContinuousData (directions in the T0 and the T1 frame) in ONE pass over
+// the hull's vertices; each direction keeps its own running maximum and sum, updated in vertex order exactly as in
+// averageSupport
+TC_HDN inline void averageSupportHull2(const SceneView& v, const ShapeD& sh, Vec3<double> n0, Vec3<double> n1, double& out0,
+                                       Vec3<double>& pt0, double& out1, Vec3<double>& pt1)
+{
+  const double BULLET_EPSILON = 1e-3;
+  Vec3<double> sum0, sum1;
+  double cnt0 = 0, cnt1 = 0, max0 = -1000, max1 = -1000;
+  for (int i = 0; i < sh.vert_cnt; ++i)
+  {
+    const Vtx<double> q = v.verts[sh.vert_off + i];
+    const Vec3<double> pt(q.x, q.y, q.z);
+    const double a = dot(pt, n0), b = dot(pt, n1);
+    if (a > max0 + BULLET_EPSILON)
+    {
+      cnt0 = 1;
+      sum0 = pt;
+      max0 = a;
+    }
+    else if (!(a < max0 - BULLET_EPSILON))
+    {
+      cnt0 += 1;
+      sum0 = sum0 + pt;
+    }
+    if (b > max1 + BULLET_EPSILON)
+    {
+      cnt1 = 1;
+      sum1 = pt;
+      max1 = b;
+    }
+    else if (!(b < max1 - BULLET_EPSILON))
+    {
+      cnt1 += 1;
+      sum1 = sum1 + pt;
+    }
+  }
+  out0 = max0;
+  pt0 = (1.0 / cnt0) * sum0;
+  out1 = max1;
+  pt1 = (1.0 / cnt1) * sum1;
+}
+
 // calculateContinuousData for link slot i of a cast contact
 TC_HDN inline void continuousData(const SceneView& v, tc_contact& c, const ShapeD& sh, const Pose<double>& tf0,
                                   const Pose<double>& tf1, Vec3<double> pt_world, Vec3<double> normal_world, int i)
@@ -182,8 +225,13 @@ TC_HDN inline void continuousData(const SceneView& v, tc_contact& c, const Shape
   const double SUPPORT_TOL = 0.01, LENGTH_TOL = 0.001;
   double s0, s1;
   Vec3<double> pl0, pl1;
-  averageSupport(v, sh, tf0.rotT(normal_world), s0, pl0);
-  averageSupport(v, sh, tf1.rotT(normal_world), s1, pl1);
+  if (sh.type == SH_HULL)
+    averageSupportHull2(v, sh, tf0.rotT(normal_world), tf1.rotT(normal_world), s0, pl0, s1, pl1);
+  else
+  {
+    averageSupport(v, sh, tf0.rotT(normal_world), s0, pl0);
+    averageSupport(v, sh, tf1.rotT(normal_world), s1, pl1);
+  }
   const Vec3<double> pw0 = tf0.apply(pl0), pw1 = tf1.apply(pl1);
   const double sup0 = dot(normal_world, pw0), sup1 = dot(normal_world, pw1);
   if (sup0 - sup1 > SUPPORT_TOL)
