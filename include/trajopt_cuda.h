@@ -213,6 +213,12 @@ int tc_abi_version(void);
 /* ---- scene ---- */
 int tc_scene_create(const tc_scene_desc* desc, tc_scene** out);
 void tc_scene_destroy(tc_scene* scene);
+/* Dynamic environment (trajopt/src/collision_terms.cpp:399-411,659-660,828-836): links outside the planning group may
+ * move between evaluations (another robot, a positioner, an attached object).  The reference reads their poses from
+ * the environment state on every call; here the caller pushes them: link_pose[n_links][12], world poses; the entries
+ * of the planning group's own links are ignored.  Takes effect for the next tc_eval; must not overlap an evaluation
+ * that uses this scene.  Pairs of two non-group links stay untested (they carry no gradient for this group). */
+int tc_scene_set_link_poses(tc_scene* scene, const double* link_pose);
 /* candidate link pairs (>= 1 active link, not ACM-disabled, sorted by (link0, link1)) */
 int tc_scene_num_pairs(const tc_scene* scene);
 int tc_scene_pairs(const tc_scene* scene, int32_t* link0, int32_t* link1, double* margin, double* coeff);

@@ -194,3 +194,26 @@ def test_qp_csc_block_matches_rows(cuda, oracle, stack, evaluator):
         upper = jx0 - rows["value"]
     assert np.abs(m["upper"] - upper).max() <= 1e-12 * max(1.0, np.abs(upper).max())
     assert np.array_equal(m["slack_cost"], rows["coeff"])
+
+
+def test_dynamic_environment_pose_update(cuda, oracle):
+    """links outside the planning group moved between evaluations (tc_scene_set_link_poses): same results as a scene
+    created with the new poses (collision_terms.cpp:399-411,659-660: dynamic_environment)"""
+    s = helpers.load_scene("arm_around_table")
+    sg = cuda.scene(s, 0.025, 20.0, 0.01)
+    q = s["seed_traj"][None]
+    fixed = np.zeros(q.shape[1], np.uint8)
+    fixed[0] = fixed[-1] = 1
+    before = cuda.eval(sg, q, capi.EVAL_LVS_CONTINUOUS, lvs=0.02, fixed=fixed).counts()["n_contacts"]
+    moved = dict(s)
+    lp = np.array(s["link_pose"], dtype=np.float64).reshape(-1, 12).copy()
+    table = [i for i, nm in enumerate(s["link_names"]) if str(nm) == "table_link"][0]
+    lp[table, [3, 7, 11]] += np.array([-0.12, 0.05, 0.08])  # the table comes closer to the arm
+    moved["link_pose"] = lp
+    sg.set_link_poses(lp)
+    rg = cuda.eval(sg, q, capi.EVAL_LVS_CONTINUOUS, lvs=0.02, fixed=fixed)
+    ro = oracle.eval(oracle.scene(moved, 0.025, 20.0, 0.01), q, capi.EVAL_LVS_CONTINUOUS, lvs=0.02, fixed=fixed)
+    assert ro.counts()["n_contacts"] != before
+    check(helpers.compare(ro, rg))
+    fresh = cuda.eval(cuda.scene(moved, 0.025, 20.0, 0.01), q, capi.EVAL_LVS_CONTINUOUS, lvs=0.02, fixed=fixed)
+    assert np.array_equal(fresh.contacts()["distance"], rg.contacts()["distance"])

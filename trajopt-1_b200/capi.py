@@ -146,6 +146,12 @@ class Scene:
         self.handle = C.c_void_p()
         lib.check(lib.fn("scene_create")(C.byref(d), C.byref(self.handle)))
 
+    def set_link_poses(self, link_pose):
+        """dynamic environment: new world poses of the links outside the planning group (tc_scene_set_link_poses)"""
+        lp = np.ascontiguousarray(link_pose, dtype=np.float64).reshape(self.n_links, 12)
+        self.lib.check(self.lib.fn("scene_set_link_poses")(self.handle, _p(lp, _pd)))
+        self.arrays["link_pose"] = lp
+
     def num_pairs(self):
         return self.lib.fn("scene_num_pairs")(self.handle)
 

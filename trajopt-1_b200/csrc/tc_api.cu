@@ -662,6 +662,21 @@ int tc_scene_create(const tc_scene_desc* desc, tc_scene** out)
   return TC_OK;
 }
 
+int tc_scene_set_link_poses(tc_scene* s, const double* link_pose)
+{
+  if (!s || !link_pose)
+    return fail(TC_ERR_INVALID, "null argument");
+  TC_TRY(ensureDevice(s->device));
+  updateStaticPoses(s->host, link_pose);
+  // plain synchronous copies: the call is not allowed to overlap an evaluation on this scene
+  TC_CUDA(cudaDeviceSynchronize());
+  TC_CUDA(cudaMemcpy(const_cast<double*>(s->dview.link_pose), s->host.link_pose.data(),
+                     s->host.link_pose.size() * sizeof(double), cudaMemcpyHostToDevice));
+  TC_CUDA(cudaMemcpy(const_cast<double*>(s->dview.static_aabb), s->host.static_aabb.data(),
+                     s->host.static_aabb.size() * sizeof(double), cudaMemcpyHostToDevice));
+  return TC_OK;
+}
+
 void tc_scene_destroy(tc_scene* s)
 {
   if (!s)

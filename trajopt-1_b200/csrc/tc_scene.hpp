@@ -176,6 +176,35 @@ inline void buildSupportLut(const Vtx<double>* verts, int n, std::vector<uint8_t
   std::memcpy(blob.data() + base + off.size() * sizeof(uint16_t), cand.data(), cand.size());
 }
 
+// world AABB of static shape i at its link's current pose
+inline void staticShapeAabb(HostScene& s, int i)
+{
+  const ShapeD& sh = s.shapes[static_cast<size_t>(i)];
+  const Pose<double> T = Pose<double>::from12(s.link_pose.data() + 12 * sh.link);
+  const Vec3<double> wc = T.apply(Vec3<double>(sh.aabb_c[0], sh.aabb_c[1], sh.aabb_c[2]));
+  for (int k = 0; k < 3; ++k)
+  {
+    const double e = std::fabs(T.r[3 * k + 0]) * sh.aabb_h[0] + std::fabs(T.r[3 * k + 1]) * sh.aabb_h[1] +
+                     std::fabs(T.r[3 * k + 2]) * sh.aabb_h[2];
+    s.static_aabb[static_cast<size_t>(6 * i + k)] = wc.get(k) - e;
+    s.static_aabb[static_cast<size_t>(6 * i + 3 + k)] = wc.get(k) + e;
+  }
+}
+
+// Dynamic environment (trajopt/src/collision_terms.cpp:399-411,659-660,828-836): links that are not moved by the
+// planning group may still move between evaluations (another robot, a positioner, an attached object).  The reference
+// reads their poses from the environment state on every call; here the caller pushes the new world poses of the
+// non-group links and the static boxes are refreshed.  Poses of group links in `link_pose` are ignored.
+inline void updateStaticPoses(HostScene& s, const double* link_pose)
+{
+  for (int l = s.n_active; l < s.n_links; ++l)
+    for (int k = 0; k < 12; ++k)
+      s.link_pose[static_cast<size_t>(12 * l + k)] = link_pose[12 * l + k];
+  for (int i = 0; i < s.n_shapes; ++i)
+    if (s.shapes[static_cast<size_t>(i)].active_index < 0)
+      staticShapeAabb(s, i);
+}
+
 inline void buildHostScene(const tc_scene_desc& d, HostScene& s)
 {
   auto fail = [](const std::string& m) { throw SceneError(TC_ERR_INVALID, m); };

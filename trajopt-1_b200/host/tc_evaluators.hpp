@@ -63,6 +63,9 @@ public:
   Scene(const Scene&) = delete;
   Scene& operator=(const Scene&) = delete;
   tc_scene* handle() const { return scene_; }
+  // dynamic environment (collision_terms.cpp:399-411): new world poses of the links outside the planning group,
+  // link_pose[n_links][12]; must not overlap an evaluation on this scene
+  void setLinkPoses(const double* link_pose) { check(tc_scene_set_link_poses(scene_, link_pose), "tc_scene_set_link_poses"); }
   int nDof() const { return n_dof_; }
   double marginBuffer() const { return margin_buffer_; }
   const std::vector<Pair>& pairs() const { return pairs_; }  // CollisionMarginData + CollisionCoeffData per pair
