@@ -460,9 +460,9 @@ __global__ void __launch_bounds__(TC_EPA_NT, MINB * 128 / TC_EPA_NT) k_epa(Scene
 }
 
 // ---------------------------------------------------------------------------------------------
-// Warp-persistent forms (TC_NARROW_WP=1).  Every WARP owns a hull buffer and an mbarrier and draws 32-item groups
-// from ONE global cursor over the padded item space, so there is no CTA barrier to wait at and no tail of long CTAs:
-// consecutive groups mostly belong to the same shape pair, whose hulls then stay staged.
+// Warp-persistent EPA.  Every WARP draws 32-item groups from ONE global cursor over the padded item space, so there
+// is no CTA barrier to wait at and no tail of long CTAs; consecutive groups mostly belong to the same shape pair.  (The
+// same form of the GJK kernel was measured slower — instruction fetch, DESIGN.md 4.1 — and is not kept.)
 // ---------------------------------------------------------------------------------------------
 __device__ __forceinline__ int bucketOf(const SceneView& v, const Work& w, int item)
 {
@@ -501,104 +501,6 @@ __device__ __forceinline__ void stageHullsWarp(const SceneView& v, const ShapeD&
       bulkCopyG2S(lut + A.lut_bytes, v.lut + B.lut_off, static_cast<uint32_t>(B.lut_bytes), bar);
   }
   mbarWait(bar, parity);
-}
-
-template <class R, int MINB>
-__global__ void __launch_bounds__(128, MINB) k_gjk_wp(SceneView v, Work w, int hull_stride)
-{
-  extern __shared__ __align__(16) unsigned char smem_raw[];
-  __shared__ __align__(8) uint64_t bars[4];
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  Vtx<R>* sv = reinterpret_cast<Vtx<R>*>(smem_raw) + static_cast<size_t>(warp) * hull_stride;
-  uint64_t* bar = &bars[warp];
-  if (lane == 0)
-    mbarInit(bar, 1);
-  __syncwarp();
-  long long st_gjk = 0, st_scan = 0, st_unconv = 0;
-  uint32_t phase = 0;
-  int sp = -1, bucket_end = 0, valid_end = 0;
-  ShapePairD spd{};
-  PairD pr{};
-  const ShapeD* A = nullptr;
-  const ShapeD* B = nullptr;
-  R thr = 0;
-  for (;;)
-  {
-    int group = 0;
-    if (lane == 0)
-      group = static_cast<int>(atomicAdd(reinterpret_cast<unsigned long long*>(&w.counters->gjk_cursor), 32ull));
-    group = __shfl_sync(0xffffffffu, group, 0);
-    if (group >= w.n_items_padded)
-      break;
-    if (sp < 0 || group >= bucket_end)
-    {
-      sp = bucketOf(v, w, group);
-      const int off = w.sp_offset[sp], cnt = w.sp_count[sp];
-      bucket_end = off + (cnt + CHUNK - 1) / CHUNK * CHUNK;
-      valid_end = off + cnt;
-      if (group >= valid_end)
-      {
-        sp = -1;  // padding group: nothing staged for this bucket yet
-        continue;
-      }
-      spd = v.spairs[sp];
-      pr = v.pairs[spd.pair];
-      A = &v.shapes[spd.sa];
-      B = &v.shapes[spd.sb];
-      thr = static_cast<R>(pr.thr);
-      if (A->vert_cnt + B->vert_cnt > 0)
-      {
-        stageHullsWarp<R>(v, *A, *B, sv, bar, phase & 1);
-        ++phase;
-      }
-    }
-    if (group >= valid_end)
-      continue;
-    const int slot = group + lane;
-    const bool live = slot < valid_end;
-    DistOut<R> d;
-    clearDist(d);
-    int u = -1;
-    Simplex<R> S;
-    S.n = 0;
-    if (live)
-    {
-      u = w.items[slot];
-      Placed<R> PA, PB;
-      placeItem<R>(v, w, w.item_state[slot], spd, pr, *A, *B, sv, sv + A->vert_cnt, PA, PB, stagedLutA<R>(*A, *B, sv),
-                   stagedLutB<R>(*A, *B, sv));
-      distanceGjk<R>(PA, PB, thr, S, d);
-      st_gjk += d.gjk_iters;
-      st_scan += d.scanned;
-      st_unconv += (d.status != ND_NEED_EPA && !d.converged) ? 1 : 0;
-    }
-    storeHit<R>(w, d, u, sp, d.status == ND_CONTACT);
-    const bool need = d.status == ND_NEED_EPA;
-    const unsigned m = __ballot_sync(0xffffffffu, need);
-    if (m)
-    {
-      const int leader = __ffs(m) - 1;
-      int cur = 0;
-      if (lane == leader)
-        cur = atomicAdd(&w.epa_cursor[sp], __popc(m));
-      cur = __shfl_sync(0xffffffffu, cur, leader);
-      if (need)
-      {
-        EpaRec& rec = w.epa_rec[static_cast<size_t>(w.sp_offset[sp]) + cur + __popc(m & ((1u << lane) - 1u))];
-        rec.unit = u;
-        rec.state = w.item_state[slot];
-        rec.nflag = S.n | (d.converged ? 0 : 8);
-        rec.pad = 0;
-#pragma unroll
-        for (int i = 0; i < 4; ++i)
-        {
-          rec.s[6 * i + 0] = S.w[i].x, rec.s[6 * i + 1] = S.w[i].y, rec.s[6 * i + 2] = S.w[i].z;
-          rec.s[6 * i + 3] = S.a[i].x, rec.s[6 * i + 4] = S.a[i].y, rec.s[6 * i + 5] = S.a[i].z;
-        }
-      }
-    }
-  }
-  addStats(w, st_gjk, st_scan, 0, 0, st_unconv);
 }
 
 template <class R, int MINB>
@@ -819,48 +721,41 @@ static cudaError_t launchNarrowT(const SceneView& v, const Work& w, cudaStream_t
   cudaError_t e = launchFill(w.epa_cursor, 0, v.n_spairs, st);
   if (e != cudaSuccess)
     return e;
-  static const char* env_wp = getenv("TC_NARROW_WP");
-  const int wp = env_wp ? atoi(env_wp) : 2;  // bit 0: GJK, bit 1: EPA (measured on C4: EPA gains, GJK does not)
-  if (wp)
-  {
-    static int n_sm = 0;
-    if (!n_sm)
-    {
-      int dev = 0;
-      cudaGetDevice(&dev);
-      cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev);
-    }
-    const int stride = 2 * v.max_hull_verts + (2 * v.max_lut_bytes + static_cast<int>(sizeof(Vtx<R>)) - 1) / static_cast<int>(sizeof(Vtx<R>));
-    const size_t smem_wp = static_cast<size_t>(4 * stride) * sizeof(Vtx<R>) + 16;
-    cudaFuncSetAttribute(k_gjk_wp<R, GB>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem_wp));
-    cudaFuncSetAttribute(k_epa_wp<R, EB>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem_wp));
-    ++launchCounter();
-    if (wp & 1)
-      k_gjk_wp<R, GB><<<n_sm * GB, 128, smem_wp, st>>>(v, w, stride);
-    else
-      k_gjk<R, GB><<<grid_g, TC_GJK_NT, smem, st>>>(v, w, run_g);
-    if (mid)
-      cudaEventRecord(mid, st);
-    ++launchCounter();
-    static const char* env_gl = getenv("TC_EPA_GLOBAL");
-    const bool epa_global = env_gl ? atoi(env_gl) != 0 : true;  // measured on C4: 8.1 -> 7.0 ms
-    if ((wp & 2) && epa_global)
-    {
-      cudaFuncSetAttribute(k_epa_wp<R, EB>, cudaFuncAttributePreferredSharedMemoryCarveout, 0);
-      k_epa_wp<R, EB><<<n_sm * EB, 128, 0, st>>>(v, w, 0);
-    }
-    else if (wp & 2)
-      k_epa_wp<R, EB><<<n_sm * EB, 128, smem_wp, st>>>(v, w, stride);
-    else
-      k_epa<R, EB><<<grid_e, TC_EPA_NT, smem, st>>>(v, w, run_e);
-    return cudaGetLastError();
-  }
   ++launchCounter();
   k_gjk<R, GB><<<grid_g, TC_GJK_NT, smem, st>>>(v, w, run_g);
   if (mid)
     cudaEventRecord(mid, st);
+  // EPA: persistent warps drawing from one global cursor (default), hulls read through L1 (default) or staged per warp;
+  // TC_NARROW_WP=0 selects the CTA-run form (tuning hooks, bench only)
+  static const char* env_wp = getenv("TC_NARROW_WP");
+  static const char* env_gl = getenv("TC_EPA_GLOBAL");
+  const bool persistent = env_wp ? atoi(env_wp) != 0 : true;
+  const bool epa_global = env_gl ? atoi(env_gl) != 0 : true;  // measured on C4: 8.1 -> 7.0 ms
   ++launchCounter();
-  k_epa<R, EB><<<grid_e, TC_EPA_NT, smem, st>>>(v, w, run_e);
+  if (!persistent)
+  {
+    k_epa<R, EB><<<grid_e, TC_EPA_NT, smem, st>>>(v, w, run_e);
+    return cudaGetLastError();
+  }
+  static int n_sm = 0;
+  if (!n_sm)
+  {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev);
+  }
+  if (epa_global)
+  {
+    cudaFuncSetAttribute(k_epa_wp<R, EB>, cudaFuncAttributePreferredSharedMemoryCarveout, 0);
+    k_epa_wp<R, EB><<<n_sm * EB, 128, 0, st>>>(v, w, 0);
+  }
+  else
+  {
+    const int stride = 2 * v.max_hull_verts + (2 * v.max_lut_bytes + static_cast<int>(sizeof(Vtx<R>)) - 1) / static_cast<int>(sizeof(Vtx<R>));
+    const size_t smem_wp = static_cast<size_t>(4 * stride) * sizeof(Vtx<R>) + 16;
+    cudaFuncSetAttribute(k_epa_wp<R, EB>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem_wp));
+    k_epa_wp<R, EB><<<n_sm * EB, 128, smem_wp, st>>>(v, w, stride);
+  }
   return cudaGetLastError();
 }
 
@@ -875,10 +770,7 @@ cudaError_t launchNarrow(const SceneView& v, const Work& w, int precision, cudaS
   const int code = var ? (var[0] - '0') * 10 + (var[2] - '0') : 34;
   switch (code)
   {
-    case 22: return launchNarrowT<double, 2, 2>(v, w, st, mid);
-    case 32: return launchNarrowT<double, 3, 2>(v, w, st, mid);
     case 33: return launchNarrowT<double, 3, 3>(v, w, st, mid);
-    case 44: return launchNarrowT<double, 4, 4>(v, w, st, mid);
     default: return launchNarrowT<double, 3, 4>(v, w, st, mid);
   }
 }
