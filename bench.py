@@ -87,6 +87,54 @@ def cpu_baseline(scene, seconds=12.0, n_seeds=None):
                       f"best wall time in {seconds:.0f} s, std::thread over terms"}, best, dense
 
 
+def sqp_iteration_latency(cu, with_cpu):
+    """BASELINE.json's second metric, ms per SQP iteration = one linearisation pass at x + one geometry (value-only)
+    pass at the trial x, for ONE problem of the single-problem configs — the latency-bound regime a
+    10-100-timestep problem lives in.  Host buffers, wall clock around the plain tc_eval calls (B = 1), median of 20.
+    With `with_cpu` the same two passes through the CPU port (single thread, as one SQP thread would run them)."""
+    capi = pkg.capi
+    from tests import synthetic  # scene generators shared with the parity tests (no oracle involved)
+    arm = ms_.load_scene("arm_around_table")
+    c3, c5 = synthetic.cluttered_scene(), synthetic.dual_arm_scene()
+    cases = [
+        ("C2 arm_around_table T=10 LVS_CONTINUOUS", arm, make_batch(arm, 0, 1)[0], dict(margin=MARGIN, coeff=COEFF, buffer=BUFFER, lvs=LVS)),
+        ("C3 64-hull clutter T=50 LVS_CONTINUOUS", c3, c3["traj"], dict(margin=0.025, coeff=20.0, buffer=0.05, lvs=0.02)),
+        ("C5 dual arm 16 dof T=100 LVS_CONTINUOUS", c5, c5["traj"], dict(margin=0.025, coeff=20.0, buffer=0.01, lvs=0.05)),
+    ]
+    orc = None
+    if with_cpu:
+        from oracle import pyoracle
+        orc = pyoracle.OracleLib()
+    out = {}
+    for name, sc, traj, prm in cases:
+        q = np.ascontiguousarray(traj[None], dtype=np.float64)
+        fixed = np.zeros(q.shape[1], np.uint8)
+        fixed[0] = fixed[-1] = 1
+        sg = cu.scene(sc, prm["margin"], prm["coeff"], prm["buffer"])
+        res = capi.Result(cu, sg, cu.new_result(sg), 1, q.shape[1])
+
+        def one(lib, scene, result=None):
+            kw = dict(result=result) if result is not None else {}
+            t0 = time.perf_counter()
+            # the CPU port assembles its rows from stored gradients; the device folds them into the rows on the fly
+            lin = capi.WANT_LINEARISE if result is not None else capi.WANT_ALL
+            r = lib.eval(scene, q, capi.EVAL_LVS_CONTINUOUS, lvs=prm["lvs"], fixed=fixed, want=lin, **kw)
+            r.rows()
+            r2 = lib.eval(scene, q, capi.EVAL_LVS_CONTINUOUS, lvs=prm["lvs"], fixed=fixed,
+                          want=capi.WANT_COST | capi.WANT_CONTACTS, **kw)
+            r2.cost()
+            return 1e3 * (time.perf_counter() - t0), r2.counts()["n_dense"]
+        for _ in range(3):
+            one(cu, sg, res)
+        ts = [one(cu, sg, res) for _ in range(20)]
+        entry = {"gpu_ms": float(np.median([t for t, _ in ts])), "dense_evals_per_pass": int(ts[0][1])}
+        if orc is not None:
+            so = orc.scene(sc, prm["margin"], prm["coeff"], prm["buffer"])
+            entry["cpu_port_1thread_ms"] = float(np.median([one(orc, so)[0] for _ in range(3)]))
+        out[name] = entry
+    return out
+
+
 def run_reference(args, scene, rank, world):
     """--impl reference: the reference's CPU path.  tesseract/Bullet/KDL cannot be built in this image
     (DESIGN.md), so this times the CPU restatement (oracle/) with all host threads, each step a bounded sample."""
@@ -277,6 +325,7 @@ def run_ours(args, scene, rank, world, local_rank):
         hbm_bytes = (counts["n_states"] * (8 * nd + (96 + 96 + 48) * n_act) + 16 * counts["n_narrowphase"] +
                      counts["n_contacts"] * (176 + r_row))
         rest_ms = ms - nms
+        latency = sqp_iteration_latency(cu, with_cpu=not args.no_cpu_baseline) if world == 1 else None
         out = {
             "metric": METRIC, "value": dense_total / (ms * 1e-3), "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": max(3, args.warmup), "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
@@ -307,6 +356,7 @@ def run_ours(args, scene, rank, world, local_rank):
             "qp_csc": {"ms": float(np.mean(csc_ms[1:])), "what": "tc_result_qp_csc_device: hinge-cost QP block [A_x | -I] of "
                        "all rows assembled on the device in CSC form (3 kernels), outside the timed step",
                        "nnz": int(counts["nnz"] + counts["n_contacts"])},
+            "sqp_iteration_ms": latency,
             "cpu_baseline": base,
             "counters": {k: counts[k] for k in ("n_dense", "n_units", "n_narrowphase", "n_contacts", "gjk_iters",
                                                 "epa_iters", "n_epa", "support_verts", "n_unconverged")},

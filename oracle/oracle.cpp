@@ -1294,6 +1294,11 @@ int orc_result_rows(const void* res, int64_t* row_ptr, int32_t* col_idx, double*
   const bool single = r.desc.evaluator == TC_EVAL_DISCRETE;
   int64_t nnz = 0;
   row_ptr[0] = 0;
+  if (r.grads.size() != r.contacts.size())
+  {
+    g_err = "rows need an evaluation with TC_WANT_GRADIENTS";
+    return TC_ERR_INVALID;
+  }
   for (std::size_t i = 0; i < r.contacts.size(); ++i)
   {
     const Contact& c = r.contacts[i];
