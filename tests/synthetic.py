@@ -12,6 +12,8 @@ from scipy.spatial import ConvexHull
 
 from tests import helpers
 
+capi = helpers.capi
+
 IDENT = np.array([1.0, 0, 0, 0, 0, 1.0, 0, 0, 0, 0, 1.0, 0])
 
 
@@ -163,4 +165,40 @@ def dual_arm_scene(seed=5):
     tk, tt = np.linspace(0, 1, 5), np.linspace(0, 1, 100)
     coef = [np.polyfit(tk, knots[:, j], 3) for j in range(knots.shape[1])]
     s["traj"] = np.stack([np.polyval(c, tt) for c in coef], axis=1)
+    return s
+
+
+def primitives_scene():
+    """spherebot's kinematics (two prismatic joints) carrying a capsule and a small box hull; obstacles: cylinder, cone,
+    sphere, capsule and a box hull, each with a tilted pose — every shape type of include/trajopt_cuda.h meets every
+    other through the out-of-line primitive support path"""
+    s = {k: np.array(v) for k, v in helpers.load_scene("spherebot").items()}
+    rng = np.random.default_rng(21)
+
+    def tilt(t):
+        a = rng.normal(size=3)
+        a /= np.linalg.norm(a)
+        th = rng.uniform(0.2, 1.2)
+        K = np.array([[0, -a[2], a[1]], [a[2], 0, -a[0]], [-a[1], a[0], 0]])
+        return _pose(np.eye(3) + np.sin(th) * K + (1 - np.cos(th)) * K @ K, t)
+
+    box = np.array([[x, y, z] for x in (-0.2, 0.2) for y in (-0.3, 0.3) for z in (-0.25, 0.25)], dtype=np.float64)
+    n_links = 6  # 0 = robot link, 1..5 obstacles
+    s["link_names"] = np.array(["bot", "cyl", "cone", "ball", "cap", "crate"])
+    s["link_frame"] = np.array([2, -1, -1, -1, -1, -1], np.int32)
+    s["link_pose"] = np.stack([IDENT, _pose(t=(0.0, 0.0, 0.0)), _pose(t=(-1.2, 0.3, 0.1)), _pose(t=(0.4, 1.3, -0.1)),
+                               _pose(t=(1.4, -0.6, 0.2)), _pose(t=(-0.5, -1.4, 0.0))]).reshape(n_links, 12)
+    #            type                 link  id  params (r, half length)
+    shapes = [(capi.SHAPE_CAPSULE, 0, 0, (0.25, 0.4)), (capi.SHAPE_HULL, 0, 1, (0, 0)),
+              (capi.SHAPE_CYLINDER, 1, 0, (0.35, 0.5)), (capi.SHAPE_CONE, 2, 0, (0.4, 0.45)),
+              (capi.SHAPE_SPHERE, 3, 0, (0.45, 0)), (capi.SHAPE_CAPSULE, 4, 0, (0.2, 0.6)), (capi.SHAPE_HULL, 5, 0, (0, 0))]
+    s["shape_type"] = np.array([t for t, *_ in shapes], np.int32)
+    s["shape_link"] = np.array([l for _, l, *_ in shapes], np.int32)
+    s["shape_id"] = np.array([i for _, _, i, _ in shapes], np.int32)
+    s["shape_params"] = np.array([[p[0], p[1], 0, 0] for *_, p in shapes], dtype=np.float64)
+    s["shape_pose"] = np.stack([tilt((0, 0, 0)), tilt((0.3, 0.1, 0.0))] + [tilt((0, 0, 0)) for _ in range(5)]).reshape(-1, 12)
+    s["shape_vert_offset"] = np.array([0, 0, 0, 0, 0, 0, 8], np.int32)
+    s["shape_vert_count"] = np.array([0, 8, 0, 0, 0, 0, 8], np.int32)
+    s["verts"] = np.concatenate([box, 1.5 * box])
+    s["acm"] = np.zeros((n_links, n_links), np.uint8)
     return s

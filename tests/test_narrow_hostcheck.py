@@ -89,3 +89,30 @@ def test_support_lut_equals_full_scan(hostcheck, scene_name):
     assert r["hulls"] > 0, r
     assert r["mismatches"] == 0, r
     assert r["candidates"] < 0.25 * r["vertices"], r
+
+
+def test_primitive_shapes_match_oracle(oracle, hostcheck):
+    """capsule, cylinder, cone, sphere and small hulls against each other (tests/synthetic.primitives_scene): the
+    out-of-line primitive support of the kernels against the oracle, discrete and swept"""
+    from tests import synthetic
+    s = synthetic.primitives_scene()
+    so, sh = oracle.scene(s, 0.1, 1.0, 0.05), hostcheck.scene(s, 0.1, 1.0, 0.05)
+    rng = np.random.default_rng(5)
+    n = len(s["shape_type"])
+    seen, n_contact, n_epa = set(), 0, 0
+    for it in range(600):
+        sa, sb = rng.integers(0, n, 2)
+        pa0, pb0 = helpers.rand_pose(rng, 0.6), helpers.rand_pose(rng, 0.6)
+        pa1 = helpers.perturb_pose(rng, pa0, 0.3, 0.1) if it % 2 == 0 else None
+        ro = oracle.shape_distance(so, sa, pa0, sb, pb0, 0.2, pose_a1=pa1)
+        rh = hostcheck.shape_distance(sh, sa, pa0, sb, pb0, 0.2, pose_a1=pa1)
+        assert ro["contact"] == rh["contact"], (it, sa, sb)
+        if not ro["contact"]:
+            continue
+        n_contact += 1
+        n_epa += int(ro["epa"])
+        seen.add((int(s["shape_type"][sa]), int(s["shape_type"][sb])))
+        assert ro["epa"] == rh["epa"] and ro["iters"] == rh["iters"], (it, sa, sb, ro, rh)
+        assert abs(ro["distance"] - rh["distance"]) <= 1e-12
+        assert np.abs(ro["normal"] - rh["normal"]).max() <= 1e-9
+    assert n_contact > 100 and n_epa > 10 and len(seen) >= 12, (n_contact, n_epa, sorted(seen))
