@@ -116,3 +116,30 @@ def test_primitive_shapes_match_oracle(oracle, hostcheck):
         assert abs(ro["distance"] - rh["distance"]) <= 1e-12
         assert np.abs(ro["normal"] - rh["normal"]).max() <= 1e-9
     assert n_contact > 100 and n_epa > 10 and len(seen) >= 12, (n_contact, n_epa, sorted(seen))
+
+
+def test_large_hull_without_table_matches_oracle(oracle, hostcheck):
+    """a 400-vertex hull is beyond the look-up table's 8-bit vertex indices: the kernels fall back to the full scan
+    (hullScanFull, both end poses of a sweep in one pass) — same answers as the oracle"""
+    from tests import synthetic
+    s = synthetic.primitives_scene()
+    rng = np.random.default_rng(9)
+    p = rng.normal(size=(400, 3))
+    p = 0.5 * p / np.linalg.norm(p, axis=1, keepdims=True) * np.array([1.0, 0.7, 0.5])
+    s["verts"] = np.concatenate([s["verts"], p])
+    s["shape_vert_offset"][1], s["shape_vert_count"][1] = 16, 400  # the robot's hull shape
+    so, sh = oracle.scene(s, 0.1, 1.0, 0.05), hostcheck.scene(s, 0.1, 1.0, 0.05)
+    r = hostcheck.support_lut_check(sh, rng.normal(size=(10, 3)))
+    assert r["hulls"] == 0  # the 8-vertex crate is below the table's minimum size, the 400-vertex hull above its maximum
+    n_contact = 0
+    for it in range(150):
+        sb = int(rng.integers(2, 7))
+        pa0, pb0 = helpers.rand_pose(rng, 0.6), helpers.rand_pose(rng, 0.6)
+        pa1 = helpers.perturb_pose(rng, pa0, 0.3, 0.1) if it % 2 == 0 else None
+        ro = oracle.shape_distance(so, 1, pa0, sb, pb0, 0.2, pose_a1=pa1)
+        rh = hostcheck.shape_distance(sh, 1, pa0, sb, pb0, 0.2, pose_a1=pa1)
+        assert ro["contact"] == rh["contact"], it
+        if ro["contact"]:
+            n_contact += 1
+            assert ro["iters"] == rh["iters"] and abs(ro["distance"] - rh["distance"]) <= 1e-12, (it, ro, rh)
+    assert n_contact > 30
