@@ -312,7 +312,16 @@ __global__ void __launch_bounds__(TC_GJK_NT, MINB * 128 / TC_GJK_NT) k_gjk(Scene
         Placed<R> PA, PB;
         placeItem<R>(v, w, w.item_state[slot], spd, pr, A, B, sv, sv + A.vert_cnt, PA, PB, stagedLutA<R>(A, B, sv),
                      stagedLutB<R>(A, B, sv));
-        distanceGjk<R>(PA, PB, thr, S, d);
+        if (pr.b >= v.n_active)
+        {
+          // static partner (uniform over the run, the common case): `cast` is a literal here, so this copy of the GJK
+          // loop carries neither the partner's second pose nor the swept branch of its support
+          PB.cast = false;
+          PB.p1 = PB.p0;
+          distanceGjk<R>(PA, PB, thr, S, d);
+        }
+        else
+          distanceGjk<R>(PA, PB, thr, S, d);
         st_gjk += d.gjk_iters;
         st_scan += d.scanned;
         st_unconv += (d.status != ND_NEED_EPA && !d.converged) ? 1 : 0;
@@ -594,7 +603,15 @@ __global__ void __launch_bounds__(128, MINB) k_epa_wp(SceneView v, Work w, int h
         placeItem<R>(v, w, rec.state, spd, pr, *A, *B, sceneVerts<R>(v) + A->vert_off, sceneVerts<R>(v) + B->vert_off, PA,
                      PB, A->lut_bytes ? v.lut + A->lut_off : nullptr, B->lut_bytes ? v.lut + B->lut_off : nullptr);
       d.converged = (nflag & 8) == 0;
-      distanceEpa<R, true>(PA, static_cast<R>(A->brad), PB, static_cast<R>(B->brad), thr, S, store, d);
+      if (pr.b >= v.n_active)
+      {
+        // static partner: a copy of the expansion in which the partner is known not to be swept (see k_gjk)
+        PB.cast = false;
+        PB.p1 = PB.p0;
+        distanceEpa<R, true>(PA, static_cast<R>(A->brad), PB, static_cast<R>(B->brad), thr, S, store, d);
+      }
+      else
+        distanceEpa<R, true>(PA, static_cast<R>(A->brad), PB, static_cast<R>(B->brad), thr, S, store, d);
       if (d.status != ND_EPA_OVERFLOW)
       {
         st_scan += d.scanned;
