@@ -318,7 +318,15 @@ __global__ void __launch_bounds__(TC_GJK_NT, MINB * 128 / TC_GJK_NT) k_gjk(Scene
           // loop carries neither the partner's second pose nor the swept branch of its support
           PB.cast = false;
           PB.p1 = PB.p0;
-          distanceGjk<R>(PA, PB, thr, S, d);
+          if (A.type == SH_HULL && B.type == SH_HULL)
+          {
+            // ... and both shapes are hulls: no primitive support in this copy
+            PA.sh.type = SH_HULL;
+            PB.sh.type = SH_HULL;
+            distanceGjk<R>(PA, PB, thr, S, d);
+          }
+          else
+            distanceGjk<R>(PA, PB, thr, S, d);
         }
         else
           distanceGjk<R>(PA, PB, thr, S, d);
@@ -608,7 +616,14 @@ __global__ void __launch_bounds__(128, MINB) k_epa_wp(SceneView v, Work w, int h
         // static partner: a copy of the expansion in which the partner is known not to be swept (see k_gjk)
         PB.cast = false;
         PB.p1 = PB.p0;
-        distanceEpa<R, true>(PA, static_cast<R>(A->brad), PB, static_cast<R>(B->brad), thr, S, store, d);
+        if (A->type == SH_HULL && B->type == SH_HULL)
+        {
+          PA.sh.type = SH_HULL;
+          PB.sh.type = SH_HULL;
+          distanceEpa<R, true>(PA, static_cast<R>(A->brad), PB, static_cast<R>(B->brad), thr, S, store, d);
+        }
+        else
+          distanceEpa<R, true>(PA, static_cast<R>(A->brad), PB, static_cast<R>(B->brad), thr, S, store, d);
       }
       else
         distanceEpa<R, true>(PA, static_cast<R>(A->brad), PB, static_cast<R>(B->brad), thr, S, store, d);
