@@ -22,12 +22,13 @@ q = torch.from_numpy(ms_.make_batch(scene, 0, B)).cuda()
 res = capi.Result(cu, sg, cu.new_result(sg), B, ms_.T_STEPS)
 st = torch.cuda.current_stream().cuda_stream
 prec = capi.PRECISION_F32 if os.environ.get("TC_PROBE_PREC") == "f32" else capi.PRECISION_F64
+ev = capi.EVAL_LVS_DISCRETE if os.environ.get("TC_PROBE_EVAL") == "discrete" else capi.EVAL_LVS_CONTINUOUS
 acc, wall = [], []
 import time
 for i in range(3 + reps):
     torch.cuda.synchronize()
     t0 = time.perf_counter()
-    cu.eval_device(sg, q.data_ptr(), B, ms_.T_STEPS, capi.EVAL_LVS_CONTINUOUS, res, lvs=ms_.LVS, fixed=ms_.fixed_steps(),
+    cu.eval_device(sg, q.data_ptr(), B, ms_.T_STEPS, ev, res, lvs=ms_.LVS, fixed=ms_.fixed_steps(),
                    stream=st, want=capi.WANT_LINEARISE, precision=prec)
     cu.sync(res)
     if i >= 3:

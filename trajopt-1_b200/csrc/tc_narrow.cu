@@ -320,10 +320,18 @@ __global__ void __launch_bounds__(TC_GJK_NT, MINB * 128 / TC_GJK_NT) k_gjk(Scene
           PB.p1 = PB.p0;
           if (A.type == SH_HULL && B.type == SH_HULL)
           {
-            // ... and both shapes are hulls: no primitive support in this copy
+            // ... and both shapes are hulls: no primitive support in these copies; one for a swept moving shape, one
+            // for a discrete test (no second pose of the moving shape either)
             PA.sh.type = SH_HULL;
             PB.sh.type = SH_HULL;
-            distanceGjk<R>(PA, PB, thr, S, d);
+            if (w.cast)
+              distanceGjk<R>(PA, PB, thr, S, d);
+            else
+            {
+              PA.cast = false;
+              PA.p1 = PA.p0;
+              distanceGjk<R>(PA, PB, thr, S, d);
+            }
           }
           else
             distanceGjk<R>(PA, PB, thr, S, d);
@@ -620,7 +628,14 @@ __global__ void __launch_bounds__(128, MINB) k_epa_wp(SceneView v, Work w, int h
         {
           PA.sh.type = SH_HULL;
           PB.sh.type = SH_HULL;
-          distanceEpa<R, true>(PA, static_cast<R>(A->brad), PB, static_cast<R>(B->brad), thr, S, store, d);
+          if (w.cast)
+            distanceEpa<R, true>(PA, static_cast<R>(A->brad), PB, static_cast<R>(B->brad), thr, S, store, d);
+          else
+          {
+            PA.cast = false;
+            PA.p1 = PA.p0;
+            distanceEpa<R, true>(PA, static_cast<R>(A->brad), PB, static_cast<R>(B->brad), thr, S, store, d);
+          }
         }
         else
           distanceEpa<R, true>(PA, static_cast<R>(A->brad), PB, static_cast<R>(B->brad), thr, S, store, d);
