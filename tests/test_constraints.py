@@ -119,3 +119,13 @@ def test_check_trajectories_gpu_vs_oracle(cuda, oracle):
         assert np.array_equal(fin, np.isfinite(g["min_distance"]))
         assert np.abs(g["min_distance"][fin] - o["min_distance"][fin]).max() <= 1e-6
         assert np.array_equal(g["n_contacts"], o["n_contacts"])
+
+
+def test_expand_columns_rebuilds_csr_indices():
+    """block form of the rows (tc_result_rows_blocks) -> CSR column indices, incl. absent blocks and an empty result"""
+    first = np.array([[0, 7], [-1, 14], [7, -1], [21, 28]], np.int32)
+    row_ptr = np.array([0, 14, 21, 28, 42], np.int64)
+    col = capi.expand_columns(row_ptr, first, 7)
+    want = np.concatenate([np.arange(0, 14), np.arange(14, 21), np.arange(7, 14), np.arange(21, 35)])
+    assert np.array_equal(col, want)
+    assert len(capi.expand_columns(np.array([0], np.int64), np.zeros((0, 2), np.int32), 7)) == 0
