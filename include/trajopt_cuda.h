@@ -289,7 +289,9 @@ int tc_result_rows_device(const tc_result* res, const int64_t** row_ptr, const i
  *   slack_cost[i] = coeff of row i (objective term coeff * s_i; s_i >= 0 is the caller's variable bound)
  * col_ptr[n_cols + 1], row_idx[nnz], val[nnz] with n_cols = B*T*n_dof + n_rows and nnz = counts.nnz + n_rows; row
  * indices ascend inside every column.  The block of trajectory b is the contiguous row range of its terms and the
- * columns b*T*n_dof .. (b+1)*T*n_dof - 1 plus its rows' slack columns. */
+ * columns b*T*n_dof .. (b+1)*T*n_dof - 1 plus its rows' slack columns.
+ * CollisionConstraint::convex (addIneqCnt(coeff * viol), collision_terms.cpp:1347-1365) is the same block without the
+ * slack columns (the first B*T*n_dof + 1 entries of col_ptr), row i and upper[i] scaled by slack_cost[i]. */
 int tc_result_qp_csc(const tc_result* res, int64_t* col_ptr, int32_t* row_idx, double* val, double* upper,
                      double* slack_cost);
 /* the same arrays left on the device (valid until the next tc_eval on this result); any output pointer may be NULL */
