@@ -308,6 +308,21 @@ int tc_result_cost(const tc_result* res, double* cost_per_term, double* cost_per
 /* device pointer to cost_per_traj[B] (stays on the GPU for multi-start selection) */
 int tc_result_cost_device(const tc_result* res, const double** dev_ptr);
 
+/* ---- allocation-free entry point.  It has NO counterpart in the reference: it was added
+ * for callers that cannot call cudaMalloc (CUDA graph capture, tight serving loops, harnesses that
+ * forbid it).  Same arithmetic as tc_result_cost's per-trajectory output, over caller-owned DEVICE arrays:
+ *   term_ptr[n_terms + 1]  contact range of every (trajectory, term), trajectory-major (as tc_result_term_ptr)
+ *   distance / margin / coeff [term_ptr[n_terms]]  per contact: signed distance, the pair's margin and coefficient
+ *   cost_per_traj[n_terms / terms_per_traj]  out: sum over the trajectory's contacts of coeff * max(margin - d, 0)
+ * The per-term intermediate lives in a static device array of TC_NOALLOC_MAX_TERMS doubles (512 KiB, held by every
+ * GPU that loads the library until exit); larger n_terms are rejected with TC_ERR_OVERFLOW.  The call enqueues two
+ * kernels on cuda_stream (NULL = default stream) and returns without synchronising; it calls no cudaMalloc / cudaFree
+ * or allocating library routine.  All calls share the array: calls that overlap on the GPU race — order them on one
+ * stream or with events.  Nothing in the array has to be cleared between calls (every slot read is written first). */
+#define TC_NOALLOC_MAX_TERMS 65536
+int tc_cost_noalloc(const int64_t* term_ptr, int32_t n_terms, int32_t terms_per_traj, const double* distance,
+                    const double* margin, const double* coeff, double* cost_per_traj, void* cuda_stream);
+
 /* ---- multi-GPU helpers for multi-start (one process per GPU).  NCCL is resolved from the process at
  * run time (libnccl.so.2).  A communicator can come from the caller (an ncclComm_t) or be created here:
  * rank 0 calls tc_nccl_unique_id and ships the 128 bytes to the other ranks by any side channel. ---- */

@@ -17,6 +17,8 @@ LIB_PATH = os.environ.get("TC_LIB_PATH", os.path.join(HERE, "csrc", "libtrajopt_
 
 # ---- enums (include/trajopt_cuda.h) ----
 TC_OK = 0
+TC_ERR_INVALID, TC_ERR_CUDA, TC_ERR_UNSUPPORTED, TC_ERR_OVERFLOW, TC_ERR_NCCL = 1, 2, 3, 4, 5
+NOALLOC_MAX_TERMS = 65536  # TC_NOALLOC_MAX_TERMS of include/trajopt_cuda.h
 JOINT_FIXED, JOINT_REVOLUTE, JOINT_PRISMATIC = 0, 1, 2
 SHAPE_SPHERE, SHAPE_HULL, SHAPE_CAPSULE, SHAPE_CYLINDER, SHAPE_CONE = 0, 1, 2, 3, 4
 EVAL_DISCRETE, EVAL_LVS_DISCRETE, EVAL_CONTINUOUS, EVAL_LVS_CONTINUOUS = 1, 2, 3, 4
@@ -383,3 +385,11 @@ class CudaLib(Lib):
         v = C.c_double()
         self.check(self.dll.tc_measure_fma_peak(C.c_int(precision), C.byref(v)))
         return v.value
+
+    def cost_noalloc(self, term_ptr_dev, n_terms, terms_per_traj, distance_dev, margin_dev, coeff_dev, out_dev,
+                     stream=None):
+        """tc_cost_noalloc: raw DEVICE pointers in and out, nothing allocated, nothing synchronised (the per-term
+        intermediate sits in the library's static device array; calls that overlap on the GPU race)"""
+        return self.dll.tc_cost_noalloc(C.c_void_p(term_ptr_dev), C.c_int32(n_terms), C.c_int32(terms_per_traj),
+                                        C.c_void_p(distance_dev), C.c_void_p(margin_dev), C.c_void_p(coeff_dev),
+                                        C.c_void_p(out_dev), C.c_void_p(stream or 0))

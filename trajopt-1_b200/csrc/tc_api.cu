@@ -1238,3 +1238,92 @@ int tc_broadcast_trajectory(double* traj, size_t n_values, int root_rank, void* 
   return TC_OK;
 }
 }  // extern "C"
+
+// ---------------------------------------------------------------------------------------------------------------
+// Allocation-free entry point (no counterpart in the reference).
+// The hinge-cost reduction of launchCost (k_cost_term -> k_cost_traj, tc_pipeline.cu) restated over caller-owned
+// device arrays, with the per-term intermediate kept in a file-scope device array instead of a cudaMalloc'd
+// buffer.  Every GPU that loads this library holds TC_NOALLOC_MAX_TERMS * 8 bytes (512 KiB) until exit.
+// All calls share the array: calls that overlap on the GPU (different streams, no ordering) race.
+// Nothing in it has to start at zero: the first kernel writes every slot [0, n_terms) the second one reads.
+// ---------------------------------------------------------------------------------------------------------------
+static __device__ __align__(256) double g_noalloc_cost_term[TC_NOALLOC_MAX_TERMS];
+
+namespace
+{
+// same arithmetic and summation order as k_cost_term: one warp per term, lanes stride over the term's contacts,
+// shuffle tree
+__global__ void __launch_bounds__(256) k_cost_term_noalloc(const long long* __restrict__ term_ptr, int n_terms,
+                                                           const double* __restrict__ distance,
+                                                           const double* __restrict__ margin,
+                                                           const double* __restrict__ coeff, double* cost_term)
+{
+  const int k = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const unsigned lane = threadIdx.x & 31;
+  if (k >= n_terms)
+    return;
+  double out = 0;
+  for (long long i = term_ptr[k] + lane; i < term_ptr[k + 1]; i += 32)
+    out += fmax(margin[i] - distance[i], 0.0) * coeff[i];
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1)
+    out += __shfl_down_sync(0xffffffffu, out, o);
+  if (lane == 0)
+    cost_term[k] = out;
+}
+__global__ void k_cost_traj_noalloc(int n_traj, int terms_per_traj, const double* cost_term, double* cost_traj)
+{
+  const int b = blockIdx.x * blockDim.x + threadIdx.x;
+  if (b >= n_traj)
+    return;
+  double out = 0;
+  for (int ti = 0; ti < terms_per_traj; ++ti)
+    out += cost_term[static_cast<size_t>(b) * terms_per_traj + ti];
+  cost_traj[b] = out;
+}
+
+// device address of g_noalloc_cost_term, resolved once per device with that device current (in host code the
+// array's name is only a stand-in for the symbol, not an address a kernel can use)
+constexpr int NOALLOC_MAX_DEVICES = 64;
+std::mutex g_noalloc_mutex;
+double* g_noalloc_ptr[NOALLOC_MAX_DEVICES] = {};
+}  // namespace
+
+extern "C" int tc_cost_noalloc(const int64_t* term_ptr, int32_t n_terms, int32_t terms_per_traj,
+                               const double* distance, const double* margin, const double* coeff,
+                               double* cost_per_traj, void* cuda_stream)
+{
+  static_assert(sizeof(long long) == sizeof(int64_t), "term_ptr layout");
+  if (!term_ptr || !cost_per_traj || n_terms <= 0 || terms_per_traj <= 0)
+    return fail(TC_ERR_INVALID, "tc_cost_noalloc: null argument or empty batch");
+  if (n_terms % terms_per_traj != 0)
+    return fail(TC_ERR_INVALID, "tc_cost_noalloc: n_terms is not a multiple of terms_per_traj");
+  if (n_terms > TC_NOALLOC_MAX_TERMS)
+    return fail(TC_ERR_OVERFLOW, "tc_cost_noalloc: n_terms = " + std::to_string(n_terms) + " exceeds the static scratch of " +
+                                     std::to_string(TC_NOALLOC_MAX_TERMS) +
+                                     " terms (TC_NOALLOC_MAX_TERMS); split the batch or use tc_result_cost");
+  int dev = -1;
+  TC_CUDA(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= NOALLOC_MAX_DEVICES)
+    return fail(TC_ERR_INVALID, "tc_cost_noalloc: device ordinal out of range");
+  double* scratch = nullptr;
+  {
+    std::lock_guard<std::mutex> lock(g_noalloc_mutex);
+    if (!g_noalloc_ptr[dev])
+    {
+      double* p = nullptr;
+      TC_CUDA(cudaGetSymbolAddress(reinterpret_cast<void**>(&p), g_noalloc_cost_term));
+      g_noalloc_ptr[dev] = p;
+    }
+    scratch = g_noalloc_ptr[dev];
+  }
+  cudaStream_t st = static_cast<cudaStream_t>(cuda_stream);
+  const int n_traj = n_terms / terms_per_traj;
+  const unsigned grid_term = static_cast<unsigned>((static_cast<long long>(n_terms) * 32 + 255) / 256);
+  k_cost_term_noalloc<<<grid_term, 256, 0, st>>>(reinterpret_cast<const long long*>(term_ptr), n_terms, distance, margin,
+                                                 coeff, scratch);
+  TC_CUDA(cudaGetLastError());
+  k_cost_traj_noalloc<<<(n_traj + 255) / 256, 256, 0, st>>>(n_traj, terms_per_traj, scratch, cost_per_traj);
+  TC_CUDA(cudaGetLastError());
+  return TC_OK;
+}
