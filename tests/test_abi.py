@@ -84,3 +84,18 @@ def test_product_tree_does_not_touch_the_oracle():
                 if re.search(r"pyoracle|liboracle|oracle/|import oracle|from oracle", txt):
                     hits.append(os.path.join(root, f))
     assert not hits, hits
+
+
+def test_noalloc_limit_matches_the_header_and_needs_no_device_to_reject():
+    """TC_NOALLOC_MAX_TERMS of the header = the constant of the Python mirror; the size and argument checks of
+    tc_cost_noalloc come before any CUDA call, so they answer without a GPU."""
+    m = re.search(r"#define\s+TC_NOALLOC_MAX_TERMS\s+(\d+)", open(HEADER).read())
+    assert m and int(m.group(1)) == helpers.capi.NOALLOC_MAX_TERMS
+    dll = lib()
+    dll.tc_last_error.restype = C.c_char_p
+    one = C.c_void_p(8)  # never dereferenced: the call is rejected first
+    args = lambda n, per: (one, C.c_int32(n), C.c_int32(per), one, one, one, one, C.c_void_p(0))
+    assert dll.tc_cost_noalloc(*args(helpers.capi.NOALLOC_MAX_TERMS + 1, 1)) == helpers.capi.TC_ERR_OVERFLOW
+    assert b"TC_NOALLOC_MAX_TERMS" in dll.tc_last_error()
+    assert dll.tc_cost_noalloc(*args(7, 2)) == helpers.capi.TC_ERR_INVALID
+    assert dll.tc_cost_noalloc(*args(0, 1)) == helpers.capi.TC_ERR_INVALID
