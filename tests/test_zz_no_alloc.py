@@ -20,7 +20,7 @@ def _batch(s, B, seed):
     return np.clip(q, lim[:, 0], lim[:, 1])
 
 
-def _noalloc_cost(cuda, sg, r, torch):
+def _noalloc_cost(cuda, sg, r, torch, stream=None):
     """per-trajectory cost of result r through tc_cost_noalloc; the test owns every device array"""
     cnt = r.counts()
     n_terms = cnt["n_terms"]
@@ -35,9 +35,12 @@ def _noalloc_cost(cuda, sg, r, torch):
     out = torch.full((r.B,), float("nan"), dtype=torch.float64, device=dev)
     torch.cuda.synchronize()
     status = cuda.cost_noalloc(term_ptr.data_ptr(), n_terms, n_terms // r.B, dist.data_ptr(), mar.data_ptr(),
-                               coe.data_ptr(), out.data_ptr())
+                               coe.data_ptr(), out.data_ptr(), stream=stream.cuda_stream if stream else None)
     cuda.check(status)
-    torch.cuda.synchronize()
+    if stream is not None:
+        stream.synchronize()  # the call only enqueues; the caller's stream orders it
+    else:
+        torch.cuda.synchronize()
     return out.cpu().numpy()
 
 
@@ -56,6 +59,19 @@ def test_noalloc_cost_matches_result_cost_twice(cuda):
         assert np.allclose(got, want, rtol=COST_TOL, atol=0.0), np.abs(got - want).max()
         seen += int(np.count_nonzero(want))
     assert seen > 0  # the batches do produce hinge cost
+
+
+def test_noalloc_on_a_caller_stream(cuda):
+    import torch
+    s = helpers.load_scene("arm_around_table")
+    sg = cuda.scene(s, 0.025, 20.0, 0.01)
+    r = cuda.eval(sg, _batch(s, 16, 3), capi.EVAL_LVS_CONTINUOUS, lvs=0.05)
+    _, want = r.cost()
+    side = torch.cuda.Stream()
+    for _ in range(2):  # back to back on one stream: ordered, so the shared scratch is safe
+        got = _noalloc_cost(cuda, sg, r, torch, stream=side)
+        assert np.allclose(got, want, rtol=COST_TOL, atol=0.0), np.abs(got - want).max()
+    assert np.count_nonzero(want) > 0
 
 
 def test_noalloc_rejects_sizes_beyond_the_static_scratch(cuda):
