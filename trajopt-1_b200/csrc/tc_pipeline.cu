@@ -506,7 +506,7 @@ __global__ void __launch_bounds__(1024) k_scan_sp(SceneView v, Work w)
 }
 
 #ifndef TC_FINALIZE_MINB
-#define TC_FINALIZE_MINB 4
+#define TC_FINALIZE_MINB 6  // measured on C4: 3: 5.47, 4: 5.40, 5: 5.27, 6: 5.21, 7: 5.22, 8: 5.50 ms for the tail (profiles/r1_minb_sweep.md)
 #endif
 // ---------------------------------------------------------------------------------------------
 // contact finalisation: ContactResult fields, cast bookkeeping, LVS merge, filters, sort key
