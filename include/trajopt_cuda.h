@@ -50,7 +50,7 @@
 extern "C" {
 #endif
 
-#define TC_ABI_VERSION 1
+#define TC_ABI_VERSION 2
 
 /* status codes */
 enum {
@@ -90,6 +90,16 @@ enum {
   TC_WANT_ROWS = 8       /* assemble the constraint rows inside tc_eval; without TC_WANT_GRADIENTS the per-link
                             gradient vectors are folded into the rows on the fly and never stored */
 };
+
+/* tesseract::collision::ContactTestType of the contact request the evaluators pass to contactTest
+ * (trajopt/src/problem_description.cpp:1669-1673; trajopt_common/include/trajopt_common/collision_types.h:113).
+ * ALL is 0 here so that a zero-initialised tc_eval_desc keeps the reference's default.
+ *   ALL      every contact of every shape pair
+ *   CLOSEST  per tested state (or sweep) and LINK pair only the contact with the smallest distance (first in
+ *            shape-pair order on ties), chosen BEFORE the evaluator's own filters, as the manager does
+ *   FIRST    per tested state (or sweep) one contact: the manager stops at the first one it finds; tesseract's order
+ *            is that of Bullet's broadphase, here it is the first in (link pair, shape pair) order */
+enum { TC_CONTACT_ALL = 0, TC_CONTACT_CLOSEST = 1, TC_CONTACT_FIRST = 2 };
 
 /* contact flags */
 enum { TC_FLAG_EPA = 1, TC_FLAG_DEGENERATE = 2, TC_FLAG_UNCONVERGED = 4 };
@@ -142,8 +152,9 @@ typedef struct tc_eval_desc {
   int32_t want;              /* TC_WANT_* mask */
   double lvs_length;         /* longest_valid_segment_length */
   const uint8_t* fixed_steps;/* [T] non-zero = timestep is fixed (host memory), or NULL */
-  int32_t q_on_device;       /* non-zero: q is a device pointer */
-  int32_t reserved;
+  int32_t q_on_device;       /* non-zero: q is a device pointer (it must stay valid until the result is no longer read:
+                                rows and the QP block are assembled from it on demand) */
+  int32_t contact_test_type; /* TC_CONTACT_* (0 = ALL) */
 } tc_eval_desc;
 
 /* One contact = the fields of tesseract::collision::ContactResult the path reads
@@ -192,6 +203,7 @@ typedef struct tc_counts {
   int64_t n_terms;       /* B x terms per trajectory                          */
   int64_t overflow;      /* non-zero if an arena overflowed                   */
   int64_t epa_iters;     /* sum of EPA expansion iterations                   */
+  int64_t support_compared; /* hull vertices actually compared (support look-up tables skip the rest) */
 } tc_counts;
 
 /* one row set of the fixed-size constraints (GradientResultsSet reduced to what the constraint reads) */
@@ -240,6 +252,26 @@ int tc_eval(tc_scene* scene, const tc_eval_desc* desc, const double* q, int32_t 
 int tc_eval_async(tc_scene* scene, const tc_eval_desc* desc, const double* q, int32_t B, int32_t T,
                   tc_result* out, void* cuda_stream);
 int tc_result_sync(tc_result* res);
+
+/* ---- seam B3: the contact manager itself.  What a tesseract_collision contact-manager plugin does between
+ * setCollisionObjectsTransform and contactTest (trajopt/src/collision_terms.cpp:616-625,665-667,887-889,1132-1134;
+ * factories named in trajopt_common/data/contact_manager_plugins.yaml:2-36), for n_states states at once and WITHOUT
+ * kinematics: the caller supplies link poses, not joint values.
+ *   link_pose0[n_states][n_active_links][12]  world poses of the scene's active links (the links the manager was told are
+ *                                             active: the first n_active_links links of the scene) in every state
+ *   link_pose1                                same shape: poses at the END of the sweep -> cast (continuous) manager,
+ *                                             every active shape is the convex hull of its two placements;
+ *                                             NULL -> discrete manager
+ * Static links keep the poses of the scene (tc_scene_create / tc_scene_set_link_poses).  Both arrays are host memory.
+ * The result is what tc_eval leaves for evaluator DISCRETE (link_pose1 == NULL) or CONTINUOUS with one sweep per state:
+ * contacts of state s carry traj = s, term = 0, sorted by (state, link pair, shape pair), distance <= pair margin +
+ * margin buffer (the manager's contact distance threshold), cc_time / cc_type filled for cast tests.
+ * tc_result_counts / _contacts / _contact_transforms / _term_ptr (one "term" per state) / _cost apply; gradients and
+ * rows need joint values and are refused.  No trajopt-side filter is applied (no fixed states, zero coefficients are
+ * still dropped as pairs the manager never reports); contact_test_type as in tc_eval_desc.
+ * A kinematics-free scene (one FIXED frame per active link) is enough for this entry point. */
+int tc_contact_test(tc_scene* scene, const double* link_pose0, const double* link_pose1, int32_t n_states,
+                    int32_t contact_test_type, int32_t precision, tc_result* out, void* cuda_stream);
 
 /* ---- result access (valid until the next tc_eval on the same result) ---- */
 int tc_result_counts(const tc_result* res, tc_counts* counts);
@@ -318,7 +350,10 @@ int tc_result_cost_device(const tc_result* res, const double** dev_ptr);
  * GPU that loads the library until exit); larger n_terms are rejected with TC_ERR_OVERFLOW.  The call enqueues two
  * kernels on cuda_stream (NULL = default stream) and returns without synchronising; it calls no cudaMalloc / cudaFree
  * or allocating library routine.  All calls share the array: calls that overlap on the GPU race — order them on one
- * stream or with events.  Nothing in the array has to be cleared between calls (every slot read is written first). */
+ * stream or with events.  Nothing in the array has to be cleared between calls (every slot read is written first).
+ * The call works on the CURRENT CUDA device (the arrays are the caller's) and does not need tc_init; tc_init resolves
+ * the scratch address of its device, any other device resolves it on its first call (one cudaGetSymbolAddress under a
+ * mutex): under graph capture make that first call, or tc_init, before the capture begins. */
 #define TC_NOALLOC_MAX_TERMS 65536
 int tc_cost_noalloc(const int64_t* term_ptr, int32_t n_terms, int32_t terms_per_traj, const double* distance,
                     const double* margin, const double* coeff, double* cost_per_traj, void* cuda_stream);

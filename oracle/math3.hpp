@@ -79,11 +79,51 @@ inline Pose operator*(const Pose& A, const Pose& B)
   return C;
 }
 
+// sin / cos of a joint angle.  The reference calls libm through Eigen::AngleAxisd (KDL / tesseract FK); libm's and
+// CUDA's results differ in the last bit for a fraction of the arguments, and GJK on a curved surface amplifies such
+// a difference to 1e-5 in the contact normal.  The checker and the checked therefore evaluate ONE operation sequence
+// (Cody-Waite reduction by pi/2 in three parts + the classic minimax polynomials on [-pi/4, pi/4], every operation
+// rounded on its own; built with -ffp-contract=off), restated here from the same published constants as
+// trajopt-1_b200/csrc/tc_math.cuh tc_sincos; absolute error <= 2e-16 for |x| <= 1e5, libm beyond.
+inline void sincosShared(double x, double& sn, double& cs)
+{
+  if (!(std::fabs(x) <= 1.0e5))
+  {
+    sn = std::sin(x);
+    cs = std::cos(x);
+    return;
+  }
+  const double fn = std::floor(x * 6.36619772367581382433e-01 + 0.5);
+  double r = x - fn * 1.57079632673412561417e+00;
+  r = r - fn * 6.07710050630396597660e-11;
+  r = r - fn * 2.02226624879595063154e-21;
+  const double z = r * r;
+  double ps = z * 1.58969099521155010221e-10;
+  ps = z * (-2.50507602534068634195e-08 + ps);
+  ps = z * (2.75573137070700676789e-06 + ps);
+  ps = z * (-1.98412698298579493134e-04 + ps);
+  ps = z * (8.33333333332248946124e-03 + ps);
+  ps = -1.66666666666666324348e-01 + ps;
+  const double s = r + (r * z) * ps;
+  double pc = z * -1.13596475577881948265e-11;
+  pc = z * (2.08757232129817482790e-09 + pc);
+  pc = z * (-2.75573143513906633035e-07 + pc);
+  pc = z * (2.48015872894767294178e-05 + pc);
+  pc = z * (-1.38888888888741095749e-03 + pc);
+  pc = 4.16666666666666019037e-02 + pc;
+  const double c = (1.0 - 0.5 * z) + (z * z) * pc;
+  const int q = static_cast<int>(static_cast<long long>(fn) & 3);
+  sn = (q == 0) ? s : ((q == 1) ? c : ((q == 2) ? -s : -c));
+  cs = (q == 0) ? c : ((q == 1) ? -s : ((q == 2) ? -c : s));
+}
+
 // Rodrigues rotation about a unit axis
 inline Pose axisAngle(V3 a, double q)
 {
   Pose T;
-  const double c = std::cos(q), s = std::sin(q), v = 1 - c;
+  double c, s;
+  sincosShared(q, s, c);
+  const double v = 1 - c;
   T.R[0][0] = c + a.x * a.x * v;
   T.R[0][1] = a.x * a.y * v - a.z * s;
   T.R[0][2] = a.x * a.z * v + a.y * s;

@@ -43,7 +43,13 @@ struct Shape
   double coreRadius() const { return (type == SPHERE || type == CAPSULE) ? radius : 0.0; }
 };
 
-// support point of the CORE of `s` in link-frame direction d (not normalised)
+// support point of the CORE of `s` in link-frame direction d (not normalised).
+// Tie band (SUPPORT_TIE): on the side of a capsule / cylinder the contact normal is perpendicular to the axis and on
+// the side of a cone it makes exactly the half-angle with it: the end-cap decision is a tie in exact arithmetic and a
+// coin flip on the last bit of d in floating point (Bullet's own support mappings have the same sign test).  A value
+// within 1e-12 |d| of the tie is taken as the tie and resolved one fixed way (+axis end; cone: base rim), so that two
+// implementations whose d differ in the last bits agree.  The support value loses at most 1e-12 |d| x length.
+constexpr double SUPPORT_TIE = 1e-12;
 inline V3 supportLocal(const Shape& s, V3 d, long* scanned = nullptr)
 {
   switch (s.type)
@@ -51,13 +57,18 @@ inline V3 supportLocal(const Shape& s, V3 d, long* scanned = nullptr)
     case SPHERE:
       return s.center;
     case CAPSULE:
-      return s.center + ((dot(d, s.axis) >= 0) ? s.half_len : -s.half_len) * s.axis;
+    {
+      const double al = dot(d, s.axis);
+      const double tie = SUPPORT_TIE * norm(d);
+      return s.center + ((al >= -tie) ? s.half_len : -s.half_len) * s.axis;
+    }
     case CYLINDER:
     {
       const double al = dot(d, s.axis);
+      const double tie = SUPPORT_TIE * norm(d);
       V3 rad = d - al * s.axis;
       const double rn = norm(rad);
-      V3 p = s.center + ((al >= 0) ? s.half_len : -s.half_len) * s.axis;
+      V3 p = s.center + ((al >= -tie) ? s.half_len : -s.half_len) * s.axis;
       if (rn > 1e-300)
         p += (s.radius / rn) * rad;
       return p;
@@ -66,11 +77,13 @@ inline V3 supportLocal(const Shape& s, V3 d, long* scanned = nullptr)
     {
       // apex at +half_len, base disc of `radius` at -half_len
       const double al = dot(d, s.axis);
+      const double dn = norm(d);
+      const double tie = SUPPORT_TIE * dn;
       V3 rad = d - al * s.axis;
       const double rn = norm(rad);
       const double h = 2 * s.half_len;
       const double sin_a = s.radius / std::sqrt(s.radius * s.radius + h * h);
-      if (al > norm(d) * sin_a)
+      if (al > dn * sin_a + tie)
         return s.center + s.half_len * s.axis;
       V3 p = s.center - s.half_len * s.axis;
       if (rn > 1e-300)

@@ -358,8 +358,12 @@ static void calculateContinuousData(Contact& col, const Shape& sh, const Pose& t
 
 // The contact manager: setCollisionObjectsTransform + contactTest (ContactTestType::ALL).
 // poses1 == nullptr -> discrete manager; otherwise cast manager (active links swept pose0 -> pose1).
+// `type`: tesseract::collision::ContactTestType as include/trajopt_cuda.h numbers it (TC_CONTACT_*): CLOSEST keeps,
+// per link pair, the result with the smallest distance (processResult replaces the stored one only when the new one is
+// strictly closer [upstream, recalled]); FIRST ends the whole test at the first result (cdata.done) — tesseract's
+// visiting order is Bullet's broadphase order, here the (link pair, shape pair) order of the scene.
 static void contactTest(const Scene& s, const std::vector<Pose>& poses0, const std::vector<Pose>* poses1,
-                        ContactResultMap& out, Stats& st)
+                        ContactResultMap& out, Stats& st, int type = TC_CONTACT_ALL)
 {
   const bool cast = poses1 != nullptr;
   auto worldAabb = [&](const Shape& sh, V3& lo, V3& hi) {
@@ -458,7 +462,16 @@ static void contactTest(const Scene& s, const std::vector<Pose>& poses0, const s
         if (PB.cast)
           calculateContinuousData(c, B, PB.pose0, PB.pose1, d.pb, -d.normal, 1);
       }
-      out[static_cast<int>(pi)].push_back(c);
+      std::vector<Contact>& dst = out[static_cast<int>(pi)];
+      if (type == TC_CONTACT_CLOSEST && !dst.empty())
+      {
+        if (c.c.distance < dst[0].c.distance)
+          dst[0] = c;
+      }
+      else
+        dst.push_back(c);
+      if (type == TC_CONTACT_FIRST)
+        return;
     }
   }
 }
@@ -512,6 +525,7 @@ struct TermEval
   long units{ 0 }, states{ 0 };
   FkState st0, st1;
   std::vector<Pose> poses0, poses1;
+  int type{ TC_CONTACT_ALL };
   explicit TermEval(const Scene& scene, double lvs_) : s(scene), lvs(lvs_)
   {
     poses0 = s.link_pose;
@@ -584,7 +598,7 @@ struct TermEval
   void single(const double* q, ContactResultMap& out, int state_base)
   {
     setPoses(q, st0, poses0);
-    contactTest(s, poses0, nullptr, out, stats);
+    contactTest(s, poses0, nullptr, out, stats, type);
     filter(out, false, false, true);
     for (auto& kv : out)
       for (Contact& c : kv.second)
@@ -593,7 +607,10 @@ struct TermEval
     states += 1;
   }
 
-  long subCount(const double* q0, const double* q1) const
+  // `longer` = dist > longest_valid_segment_length: the reference branches on THIS, not on cnt
+  // (collision_terms.cpp:1107, continuous_collision_evaluators.cpp:204); when dist barely exceeds the length,
+  // dist / length rounds to 1.0, cnt is 2 and the single sweep still goes through addInterpolatedCollisionResults
+  long subCount(const double* q0, const double* q1, bool* longer = nullptr) const
   {
     double d2 = 0;
     for (int j = 0; j < s.n_dof; ++j)
@@ -602,6 +619,8 @@ struct TermEval
     long cnt = 2;
     if (dist > lvs)
       cnt = static_cast<long>(std::ceil(dist / lvs)) + 1;
+    if (longer)
+      *longer = dist > lvs;
     return cnt;
   }
   void subState(const double* q0, const double* q1, long cnt, long i, std::vector<double>& q) const
@@ -624,7 +643,7 @@ struct TermEval
       subState(q0, q1, cnt, i, q);
       setPoses(q.data(), st0, poses0);
       ContactResultMap contacts;
-      contactTest(s, poses0, nullptr, contacts, stats);
+      contactTest(s, poses0, nullptr, contacts, stats, type);
       if (!contacts.empty())
         addInterpolated(out, contacts, i, last, dt, true, f0, f1, state_base + static_cast<int>(i));
     }
@@ -637,8 +656,9 @@ struct TermEval
   void cast(const double* q0, const double* q1, bool f0, bool f1, bool single_sweep, ContactResultMap& out,
             int state_base)
   {
-    const long cnt = subCount(q0, q1);
-    if (!single_sweep && cnt > 2)
+    bool longer = false;
+    const long cnt = subCount(q0, q1, &longer);
+    if (!single_sweep && longer)
     {
       const long last = cnt - 1;
       const double dt = 1.0 / static_cast<double>(last);
@@ -650,7 +670,7 @@ struct TermEval
         setPoses(qa.data(), st0, poses0);
         setPoses(qb.data(), st1, poses1);
         ContactResultMap contacts;
-        contactTest(s, poses0, &poses1, contacts, stats);
+        contactTest(s, poses0, &poses1, contacts, stats, type);
         if (!contacts.empty())
           addInterpolated(out, contacts, i, last, dt, false, f0, f1, state_base + static_cast<int>(i));
       }
@@ -661,7 +681,7 @@ struct TermEval
     {
       setPoses(q0, st0, poses0);
       setPoses(q1, st1, poses1);
-      contactTest(s, poses0, &poses1, out, stats);
+      contactTest(s, poses0, &poses1, out, stats, type);
       filter(out, f0, f1, false);
       for (auto& kv : out)
         for (Contact& c : kv.second)
@@ -844,6 +864,7 @@ static Result* evaluate(const Scene& s, const tc_eval_desc& d, const double* q, 
                                static_cast<std::size_t>(n);
     const double* q1 = q0 + n;
     TermEval ev(s, d.lvs_length);
+    ev.type = d.contact_test_type;
     ContactResultMap m;
     if (d.evaluator == TC_EVAL_DISCRETE)
       ev.single(q0, m, 0);
@@ -925,6 +946,7 @@ static Result* evaluate(const Scene& s, const tc_eval_desc& d, const double* q, 
     r->counts.n_narrowphase += st.narrow;
     r->counts.gjk_iters += st.gjk_iters;
     r->counts.support_verts += st.scanned;
+    r->counts.support_compared += st.scanned;  // the plain scan compares every vertex
     r->counts.n_epa += st.epa;
     r->counts.epa_iters += st.epa_iters;
     r->counts.n_unconverged += st.unconverged;
@@ -933,6 +955,71 @@ static Result* evaluate(const Scene& s, const tc_eval_desc& d, const double* q, 
   r->counts.n_contacts = static_cast<int64_t>(r->contacts.size());
   r->counts.n_rows = r->counts.n_contacts;
   r->counts.n_terms = n_terms;
+  return r.release();
+}
+
+// The contact manager driven directly (seam B3): poses in, contacts out, no kinematics and no evaluator filter beyond
+// the manager's own contact threshold.  pose0 / pose1: [n_states][n_active][12]; pose1 == nullptr -> discrete manager.
+static Result* contactTestStates(const Scene& s, const double* pose0, const double* pose1, int n_states, int type)
+{
+  auto r = std::make_unique<Result>();
+  r->scene = &s;
+  r->desc.evaluator = pose1 ? TC_EVAL_CONTINUOUS : TC_EVAL_DISCRETE;
+  r->desc.stack = TC_STACK_IFOPT;
+  r->desc.want = TC_WANT_CONTACTS | TC_WANT_COST;
+  r->desc.contact_test_type = type;
+  r->B = n_states;
+  r->T = pose1 ? 2 : 1;
+  r->terms_per_traj = 1;
+  r->term_t.push_back(0);
+  r->term_fixed.push_back({ false, false });
+  r->term_ptr.assign(static_cast<std::size_t>(n_states) + 1, 0);
+  std::vector<Pose> p0 = s.link_pose, p1 = s.link_pose;
+  const int spt = pose1 ? 2 : 1;
+  for (int k = 0; k < n_states; ++k)
+  {
+    for (int l = 0; l < s.n_active; ++l)
+    {
+      p0[static_cast<std::size_t>(l)] = Pose::from12(pose0 + (static_cast<std::size_t>(k) * s.n_active + l) * 12);
+      if (pose1)
+        p1[static_cast<std::size_t>(l)] = Pose::from12(pose1 + (static_cast<std::size_t>(k) * s.n_active + l) * 12);
+    }
+    ContactResultMap m;
+    Stats st;
+    contactTest(s, p0, pose1 ? &p1 : nullptr, m, st, type);
+    for (auto& kv : m)
+    {
+      if (s.pairs[static_cast<std::size_t>(kv.first)].zero_coeff)
+        continue;
+      for (Contact& c : kv.second)
+      {
+        c.c.traj = k;
+        c.c.term = 0;
+        c.c.substep = 0;
+        c.c.state = spt * k;
+        if (pose1)
+          for (int i = 0; i < 2; ++i)
+            if (s.isActive(c.c.link_ids[i]))
+              c.cc_transform[i] = p1[static_cast<std::size_t>(c.c.link_ids[i])];
+        r->contacts.push_back(c);
+      }
+    }
+    r->term_ptr[static_cast<std::size_t>(k) + 1] = static_cast<int64_t>(r->contacts.size());
+    r->counts.n_candidates += st.candidates;
+    r->counts.n_narrowphase += st.narrow;
+    r->counts.gjk_iters += st.gjk_iters;
+    r->counts.support_verts += st.scanned;
+    r->counts.support_compared += st.scanned;
+    r->counts.n_epa += st.epa;
+    r->counts.epa_iters += st.epa_iters;
+    r->counts.n_unconverged += st.unconverged;
+  }
+  r->counts.n_states = static_cast<int64_t>(spt) * n_states;
+  r->counts.n_units = n_states;
+  r->counts.n_dense = r->counts.n_units * static_cast<int64_t>(s.pairs.size());
+  r->counts.n_contacts = static_cast<int64_t>(r->contacts.size());
+  r->counts.n_rows = r->counts.n_contacts;
+  r->counts.n_terms = n_states;
   return r.release();
 }
 
@@ -1136,6 +1223,8 @@ int orc_scene_pairs(const void* scene, int32_t* l0, int32_t* l1, double* margin,
   return TC_OK;
 }
 
+void orc_sincos(double x, double* sn, double* cs) { orc::sincosShared(x, *sn, *cs); }
+
 int orc_fk(const void* scene, const double* q, double* link_poses /*[n_active][12]*/)
 {
   const Scene& s = *static_cast<const Scene*>(scene);
@@ -1223,6 +1312,17 @@ int orc_eval(void* scene, const tc_eval_desc* desc, const double* q, int32_t B, 
   *out = evaluate(*static_cast<Scene*>(scene), *desc, q, B, T, n_threads);
   ORC_CATCH
 }
+int orc_contact_test(void* scene, const double* pose0, const double* pose1, int32_t n_states, int32_t type, void** out)
+{
+  if (!scene || !pose0 || !out || n_states <= 0)
+  {
+    g_err = "bad argument";
+    return TC_ERR_INVALID;
+  }
+  *out = contactTestStates(*static_cast<Scene*>(scene), pose0, pose1, n_states, type);
+  return TC_OK;
+}
+
 void orc_result_destroy(void* res) { delete static_cast<Result*>(res); }
 
 int orc_result_counts(const void* res, tc_counts* c)

@@ -14,6 +14,8 @@ void orc_scene_destroy(void* scene);
 int orc_scene_num_pairs(const void* scene);
 int orc_scene_pairs(const void* scene, int32_t* l0, int32_t* l1, double* margin, double* coeff);
 int orc_fk(const void* scene, const double* q, double* link_poses);
+void orc_sincos(double x, double* sn, double* cs);
+int orc_contact_test(void* scene, const double* pose0, const double* pose1, int32_t n_states, int32_t type, void** out);
 int orc_jacobian(const void* scene, const double* q, int link, const double* ref_offset, double* J);
 int orc_shape_distance(const void* scene, int shape_a, const double* pose_a0, const double* pose_a1, int shape_b,
                        const double* pose_b0, const double* pose_b1, double threshold, int* contact, double* distance,

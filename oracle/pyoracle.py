@@ -31,12 +31,20 @@ class OracleLib(capi.Lib):
             build()
         super().__init__(LIB, "orc_")
 
+    def contact_test(self, scene, pose0, pose1=None, contact_type=capi.CONTACT_ALL):
+        pose0 = np.ascontiguousarray(pose0, dtype=np.float64)
+        p1 = np.ascontiguousarray(pose1, dtype=np.float64) if pose1 is not None else None
+        h = C.c_void_p()
+        self.check(self.dll.orc_contact_test(scene.handle, capi._p(pose0, _pd), capi._p(p1, _pd) if p1 is not None else _pd(),
+                                             C.c_int32(pose0.shape[0]), C.c_int32(contact_type), C.byref(h)))
+        return capi.Result(self, scene, h, pose0.shape[0], 2 if p1 is not None else 1)
+
     def eval(self, scene, q, evaluator, stack=capi.STACK_IFOPT, lvs=0.005, fixed=None, want=capi.WANT_ALL,
-             n_threads=1):
+             n_threads=1, contact_type=capi.CONTACT_ALL):
         q = np.ascontiguousarray(q, dtype=np.float64)
         B, T, n = q.shape
         assert n == scene.n_dof
-        d, keep = capi.make_eval_desc(evaluator, stack, lvs, fixed, want)
+        d, keep = capi.make_eval_desc(evaluator, stack, lvs, fixed, want, contact_type=contact_type)
         h = C.c_void_p()
         self.check(self.dll.orc_eval(scene.handle, C.byref(d), capi._p(q, _pd), C.c_int32(B), C.c_int32(T),
                                      C.byref(h), C.c_int(n_threads)))

@@ -335,3 +335,65 @@ def check_invariants(r, sg, q, evaluator, lvs, fixed, margin_buffer, stack=capi.
         assert (rows["col_idx"][rows["row_ptr"][:-1][nz]] >= first_col[nz]).all()
         assert (rows["col_idx"][rows["row_ptr"][1:][nz] - 1] < first_col[nz] + 2 * sg.n_dof).all()
     return c
+
+
+# ---- the stated band of the cc_type decision ----
+# calculateContinuousData decides TIME0 / TIME1 / BETWEEN by comparing the support values of the shape at its two end
+# poses against BULLET_SUPPORT_FUNC_TOLERANCE = 0.01, after GetAverageSupport has averaged the hull vertices within
+# BULLET_EPSILON = 1e-3 of the running maximum.  Both are discrete decisions on continuous quantities: a contact whose
+# quantity lies within CC_BAND of one of those thresholds may legitimately be classified differently by two
+# implementations whose arithmetic differs in the last bits.  Outside the band the classes must agree.
+CC_BAND = 1e-9
+
+
+def _avg_support_margin(verts, nl):
+    """GetAverageSupport scan (tc_contact.cuh averageSupport): returns (support, point, smallest distance of any of its
+    comparisons to the +-BULLET_EPSILON thresholds)"""
+    eps, mx, cnt, acc, closest = 1e-3, -1000.0, 0.0, np.zeros(3), np.inf
+    for p in verts:
+        sup = float(p @ nl)
+        closest = min(closest, abs(sup - (mx + eps)), abs(sup - (mx - eps)))
+        if sup > mx + eps:
+            cnt, acc, mx = 1.0, p.copy(), sup
+        elif sup < mx - eps:
+            pass
+        else:
+            cnt += 1.0
+            acc = acc + p
+    return mx, acc / cnt, closest
+
+
+def cc_type_outside_band(ro, rg, scene, band=CC_BAND):
+    """number of common contacts whose cc_type differs between the two results although every decision that leads to
+    the class is farther than `band` from its threshold (must be 0); also returns the number of mismatches"""
+    co, cg = ro.contacts(), rg.contacts()
+    _, a, b = np.intersect1d(packed_keys(co), packed_keys(cg), assume_unique=True, return_indices=True)
+    A, G = co[a], cg[b]
+    bad_rows = np.nonzero((A["cc_type"] != G["cc_type"]).any(axis=1))[0]
+    if len(bad_rows) == 0:
+        return 0, 0
+    xf = ro.contact_transforms()[a]
+    shape_pose = np.asarray(scene["shape_pose"], dtype=np.float64).reshape(-1, 3, 4)
+    outside = 0
+    for r in bad_rows:
+        c = A[r]
+        ok = False
+        for i in range(2):
+            if c["cc_type"][i] == G[r]["cc_type"][i]:
+                continue
+            sel = np.nonzero((scene["shape_link"] == c["link_ids"][i]) & (scene["shape_id"] == c["shape_id"][i]))[0]
+            if len(sel) != 1 or scene["shape_type"][sel[0]] != capi.SHAPE_HULL:
+                continue
+            k = sel[0]
+            v = np.asarray(scene["verts"], dtype=np.float64).reshape(-1, 3)
+            v = v[scene["shape_vert_offset"][k]:scene["shape_vert_offset"][k] + scene["shape_vert_count"][k]]
+            v = v @ shape_pose[k][:, :3].T + shape_pose[k][:, 3]
+            n = np.array(c["normal"]) * (1.0 if i == 0 else -1.0)
+            T0, T1 = xf[r, i, 0].reshape(3, 4), xf[r, i, 1].reshape(3, 4)
+            s0, p0, m0 = _avg_support_margin(v, T0[:, :3].T @ n)
+            s1, p1, m1 = _avg_support_margin(v, T1[:, :3].T @ n)
+            sup0, sup1 = float(n @ (T0[:, :3] @ p0 + T0[:, 3])), float(n @ (T1[:, :3] @ p1 + T1[:, 3]))
+            if min(m0, m1, abs(abs(sup0 - sup1) - 0.01)) <= band:
+                ok = True
+        outside += 0 if ok else 1
+    return outside, len(bad_rows)

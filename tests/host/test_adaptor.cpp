@@ -221,6 +221,36 @@ int main(int argc, char** argv)
       ev.calcCollisions(data, VectorXd{ -0.9, 0.01 }, 0);
       std::printf("NOSETS contacts %zu sets %zu\n", data.contact_results_map.count(), data.gradient_results_sets.size());
     }
+    // ---- DISCRETE batch with a fixed first timestep: tc_eval skips it, so timestep t is term t - 1 of the pass
+    {
+      SceneFile file(argv[2]);
+      auto scene = std::make_shared<Scene>(file.desc(0.025, 20.0, 0.01));
+      const std::size_t n = static_cast<std::size_t>(scene->nDof());
+      const std::vector<double>& traj = file.f64("seed_traj");
+      const int T = static_cast<int>(traj.size() / n);
+      TrajOptCollisionConfig cfg;
+      cfg.type = CollisionEvaluatorType::DISCRETE;
+      std::vector<uint8_t> fx(static_cast<std::size_t>(T), 0);
+      fx[0] = 1;
+      auto batch = std::make_shared<CollisionBatch>(scene, cfg, T, fx);
+      batch->update(traj.data());
+      int bad = 0;
+      std::size_t total = 0;
+      for (int t = 0; t < T; ++t)
+      {
+        const VectorXd q(traj.begin() + static_cast<long>(static_cast<std::size_t>(t) * n),
+                         traj.begin() + static_cast<long>(static_cast<std::size_t>(t + 1) * n));
+        CollisionCacheData alone, sliced;
+        SingleTimestepCollisionEvaluator ea(scene, cfg), eb(scene, cfg, batch, t);
+        ea.calcCollisions(alone, q, 3);
+        eb.calcCollisions(sliced, q, 3);
+        total += alone.contact_results_map.count();
+        if (!same(discreteRows(alone, 3, n, scene->marginBuffer()), discreteRows(sliced, 3, n, scene->marginBuffer())) ||
+            alone.contact_results_map.count() != sliced.contact_results_map.count())
+          ++bad;
+      }
+      std::printf("BATCH_DISCRETE_FIXED mismatches %d contacts %zu passes %ld\n", bad, total, batch->passes());
+    }
     // ---- arm_around_table seed trajectory: LVS_CONTINUOUS and LVS_DISCRETE per segment, standalone and batched
     {
       SceneFile file(argv[2]);
@@ -268,6 +298,38 @@ int main(int argc, char** argv)
           }
         }
         std::printf("BATCH_PASSES %d %ld\n", kind, batch->passes());
+        // fixed steps that make tc_eval skip terms: the first two timesteps fixed -> segment 0 has no term and segment
+        // t >= 1 is term t - 1 of the batched pass; every sliced segment must equal the standalone evaluator's, and
+        // the skipped one must fall back to a standalone pass (the evaluator itself still answers)
+        {
+          std::vector<uint8_t> fx(static_cast<std::size_t>(T), 0);
+          fx[0] = fx[1] = 1;
+          auto b2 = std::make_shared<CollisionBatch>(scene, cfg, T, fx);
+          b2->update(traj.data());
+          int bad = 0;
+          for (int t = 1; t + 1 < T; ++t)
+          {
+            const VectorXd q0(traj.begin() + static_cast<long>(t * n), traj.begin() + static_cast<long>((t + 1) * n));
+            const VectorXd q1(traj.begin() + static_cast<long>((t + 1) * n), traj.begin() + static_cast<long>((t + 2) * n));
+            const bool f0 = fx[static_cast<std::size_t>(t)] != 0, f1 = fx[static_cast<std::size_t>(t) + 1] != 0;
+            CollisionCacheData alone, sliced;
+            std::unique_ptr<ContinuousCollisionEvaluator> ea, eb;
+            if (kind)
+              ea.reset(new LVSDiscreteCollisionEvaluator(scene, cfg)), eb.reset(new LVSDiscreteCollisionEvaluator(scene, cfg, b2, t));
+            else
+              ea.reset(new LVSContinuousCollisionEvaluator(scene, cfg)), eb.reset(new LVSContinuousCollisionEvaluator(scene, cfg, b2, t));
+            ea->calcCollisionData(alone, q0, q1, f0, f1, max_num_cnt);
+            eb->calcCollisionData(sliced, q0, q1, f0, f1, max_num_cnt);
+            if (!same(continuousRows(alone, max_num_cnt, n, scene->marginBuffer(), f0, f1),
+                      continuousRows(sliced, max_num_cnt, n, scene->marginBuffer(), f0, f1)) ||
+                alone.contact_results_map.count() != sliced.contact_results_map.count())
+              ++bad;
+          }
+          CollisionCacheData none;
+          const bool skipped_refused = !b2->slice(none, 0, traj.data(), traj.data() + n, true, true, true, max_num_cnt);
+          std::printf("BATCH_SKIPPED_TERMS %d mismatches %d skipped_refused %d passes %ld\n", kind, bad, skipped_refused ? 1 : 0,
+                      b2->passes());
+        }
         // numerical-gradient constraint on segment (1, 2), both ends free, and the batched trajectory check
         {
           const VectorXd q1(traj.begin() + static_cast<long>(n), traj.begin() + static_cast<long>(2 * n));

@@ -6,7 +6,7 @@
 #include <string>
 #include <vector>
 
-#include "../../trajopt-1_b200/csrc/tc_scene.hpp"
+#include "../../trajopt-1_b200/csrc/tc_contact.cuh"
 
 using namespace tc;
 
@@ -56,7 +56,7 @@ int hc_support_lut_check(void* scene, const double* dirs, int n_dirs, long long*
     for (int k = 0; k < n_dirs; ++k)
     {
       const Vec3<double> d(dirs[3 * k], dirs[3 * k + 1], dirs[3 * k + 2]);
-      int sc = 0;
+      ScanCount sc = 0;
       const Vec3<double> a = full.support(d, sc), b = fast.support(d, sc);
       if (std::memcmp(&a, &b, sizeof(a)) != 0)
         ++*mismatches;
@@ -110,7 +110,7 @@ static int shapeDistance(const HostScene& s, int sa, const double* a0, const dou
   *used_epa = o.used_epa;
   *gjk_iters = o.gjk_iters;
   *epa_iters = o.epa_iters;
-  *scanned = o.scanned;
+  *scanned = static_cast<int>(o.scanned & 0xffffffffull);
   return TC_OK;
 }
 
@@ -127,4 +127,27 @@ int hc_shape_distance(const void* scene, int precision, int sa, const double* a0
   return shapeDistance<double>(s, sa, a0, a1, sb, b0, b1, threshold, max_verts, max_faces, status, distance, normal,
                                pa, pb, used_epa, gjk_iters, epa_iters, scanned);
 }
+
+// the device's FK chain (frameStepQ of tc_contact.cuh with the shared sin/cos of tc_math.cuh), frame by frame as k_fk
+// walks it: link_poses[n_active][12].  Must equal the oracle's FK bit for bit (tests/test_narrow_hostcheck.py).
+int hc_fk(const void* scene, const double* q, double* link_poses)
+{
+  const HostScene& s = *static_cast<const HostScene*>(scene);
+  const SceneView v = hostView(s);
+  std::vector<Pose<double>> frame(static_cast<size_t>(s.n_frames));
+  const Pose<double> base = Pose<double>::from12(v.base_pose);
+  for (int f = 0; f < s.n_frames; ++f)
+  {
+    const int p = s.frame_parent[static_cast<size_t>(f)];
+    double qf = 0;
+    if (s.frame_type[static_cast<size_t>(f)] != TC_JOINT_FIXED)
+      qf = q[s.frame_dof[static_cast<size_t>(f)]];
+    frame[static_cast<size_t>(f)] = frameStepQ(v, p < 0 ? base : frame[static_cast<size_t>(p)], f, qf);
+  }
+  for (int l = 0; l < s.n_active; ++l)
+    frame[static_cast<size_t>(s.link_frame[static_cast<size_t>(l)])].to12(link_poses + 12 * l);
+  return TC_OK;
+}
+
+void hc_sincos(double x, double* sn, double* cs) { tc_sincos(x, sn, cs); }
 }

@@ -202,3 +202,37 @@ def primitives_scene():
     s["verts"] = np.concatenate([box, 1.5 * box])
     s["acm"] = np.zeros((n_links, n_links), np.uint8)
     return s
+
+
+def arm_with_curved_obstacles_scene(seed=13):
+    """the PR2 arm of the fixture (REVOLUTE joints, hull links) among static cylinders and cones placed along its seed
+    path: curved cores met by shapes whose poses come from a sin/cos FK chain (primitives_scene has prismatic joints)"""
+    rng = np.random.default_rng(seed)
+    s = {k: np.array(v) for k, v in helpers.load_scene("arm_around_table").items()}
+    n_links0, n_new = len(s["link_frame"]), 6
+    centres = rng.uniform(np.array([0.35, -0.7, 0.55]), np.array([0.95, 0.1, 1.15]), (n_new, 3))
+    s["link_frame"] = np.concatenate([s["link_frame"], -np.ones(n_new, np.int32)])
+    s["link_names"] = np.concatenate([s["link_names"], np.array(["curved_%d" % i for i in range(n_new)])])
+    poses = []
+    for i in range(n_new):
+        a = rng.normal(size=3)
+        a /= np.linalg.norm(a)
+        th = rng.uniform(0.0, np.pi)
+        K = np.array([[0, -a[2], a[1]], [a[2], 0, -a[0]], [-a[1], a[0], 0]])
+        poses.append(_pose(np.eye(3) + np.sin(th) * K + (1 - np.cos(th)) * K @ K, centres[i]))
+        s["shape_type"] = np.append(s["shape_type"], np.int32(capi.SHAPE_CYLINDER if i % 2 == 0 else capi.SHAPE_CONE))
+        s["shape_link"] = np.append(s["shape_link"], np.int32(n_links0 + i))
+        s["shape_id"] = np.append(s["shape_id"], np.int32(0))
+        s["shape_params"] = np.concatenate([s["shape_params"], [[rng.uniform(0.04, 0.09), rng.uniform(0.06, 0.15), 0, 0]]])
+        s["shape_pose"] = np.concatenate([s["shape_pose"], IDENT[None]])
+        s["shape_vert_offset"] = np.append(s["shape_vert_offset"], np.int32(0))
+        s["shape_vert_count"] = np.append(s["shape_vert_count"], np.int32(0))
+    s["link_pose"] = np.concatenate([s["link_pose"], np.stack(poses)])
+    n = n_links0 + n_new
+    acm = np.ones((n, n), np.uint8)
+    acm[:n_links0, :n_links0] = s["acm"]
+    na = int(s["n_active_links"])
+    acm[:na, n_links0:] = 0
+    acm[n_links0:, :na] = 0
+    s["acm"] = acm
+    return s

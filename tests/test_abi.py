@@ -39,7 +39,7 @@ def test_every_declared_symbol_is_exported():
 
 def test_abi_version_and_record_sizes():
     dll = lib()
-    assert dll.tc_abi_version() == 1
+    assert dll.tc_abi_version() == 2
     capi = helpers.capi
     assert capi.CONTACT_DTYPE.itemsize == 200 and capi.GRADIENT_DTYPE.itemsize == 64 and capi.SET_DTYPE.itemsize == 112
 

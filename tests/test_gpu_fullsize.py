@@ -28,7 +28,9 @@ def test_c4_shard_against_oracle(cuda, oracle):
     ro = oracle.eval(so, q, capi.EVAL_LVS_CONTINUOUS, lvs=ms.LVS, fixed=ms.fixed_steps(), n_threads=oracle.num_threads())
     rep = helpers.compare_fast(ro, rg)
     assert rep["n_contacts"] > 100000, rep
-    assert rep["unmatched_outside_band"] == 0 and rep["cc_type_mismatch"] <= rep["n_contacts"] // 10000, rep
+    assert rep["unmatched_outside_band"] == 0, rep
+    # cc_type may differ only inside the stated band of its decision thresholds (helpers.CC_BAND)
+    assert helpers.cc_type_outside_band(ro, rg, s)[0] == 0, rep
     assert rep["max_dist_err"] <= 1e-6 and rep["max_normal_err"] <= 1e-5 and rep["max_cc_time_err"] <= 1e-5, rep
     assert rep["max_grad_rel_err"] <= 1e-5 and rep["rec_equal"], rep
     if rep["same_order"]:

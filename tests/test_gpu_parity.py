@@ -230,14 +230,26 @@ def test_primitive_shapes(cuda, oracle, evaluator):
     ro = oracle.eval(so, q, evaluator, lvs=0.05)
     rep = helpers.compare(ro, rg)
     assert rep["n_contacts"] > 50, rep
-    # Curved primitives have no closest VERTEX to lock on to: GJK stops on its 1e-10 m gap, which fixes the distance to
-    # 1e-10 but the direction of the closest vector only to ~sqrt(1e-10) = 1e-5, and the FMA-contracted device
-    # arithmetic takes a slightly different path to that stop than the oracle.  Distances keep the 1e-6 m bar;
-    # normals and the rows built from them are held to 1e-4 here.
-    assert rep["counts_equal"] and rep["unmatched_outside_band"] == 0, rep
-    assert rep["max_dist_err"] <= DIST_TOL, rep
-    # The swept evaluator scales a row by cc_time = l0 / (l0 + l1), a ratio of two witness-point distances that
-    # amplifies that directional noise on curved surfaces: its rows are held to 1e-2 (the gradients themselves to 1e-4).
-    row_tol = 1e-2 if evaluator == capi.EVAL_LVS_CONTINUOUS else 1e-4
-    assert rep["max_normal_err"] <= 1e-4 and rep["max_grad_rel_err"] <= 1e-4 and rep["max_row_rel_err"] <= row_tol, rep
-    assert rep["max_row_value_err"] <= 1e-6 and rep["cc_type_mismatch"] == 0, rep
+    # Cylinder and cone pairs run through the contraction-free kernels of tc_strict.cu (FK with the shared sin/cos,
+    # GJK/EPA operation for operation as the oracle), so the north_star tolerances hold for every shape type: 1e-6 m,
+    # normals / gradients / rows 1e-5 — the same `check` as every other scene.  (Round 1 needed 1e-4 / 1e-2 here.)
+    check(rep)
+    assert rep["cc_type_mismatch"] == 0, rep
+
+
+@pytest.mark.parametrize("evaluator", [capi.EVAL_LVS_DISCRETE, capi.EVAL_LVS_CONTINUOUS])
+def test_curved_obstacles_on_a_revolute_arm(cuda, oracle, evaluator):
+    """cylinders and cones against hull links whose poses come out of a revolute (sin/cos) FK chain: the contraction-free
+    FK + narrow phase (tc_strict.cu) keep the north_star tolerances there too"""
+    from tests import synthetic
+    s = synthetic.arm_with_curved_obstacles_scene()
+    sg, so = cuda.scene(s, 0.05, 20.0, 0.02), oracle.scene(s, 0.05, 20.0, 0.02)
+    q = helpers.pkg.multistart.make_batch(s, 300, 6, t_steps=6)
+    fixed = np.zeros(q.shape[1], np.uint8)
+    fixed[0] = fixed[-1] = 1
+    rg = cuda.eval(sg, q, evaluator, lvs=0.05, fixed=fixed)
+    ro = oracle.eval(so, q, evaluator, lvs=0.05, fixed=fixed, n_threads=8)
+    rep = helpers.compare(ro, rg)
+    curved = np.isin(ro.contacts()["link_ids"][:, 1], np.nonzero(np.char.startswith(s["link_names"].astype(str), "curved"))[0])
+    assert curved.sum() > 30, (rep, int(curved.sum()))
+    check(rep)

@@ -65,6 +65,12 @@ def test_adaptor_matches_known_answers_and_oracle(tmp_path, oracle):
     assert "BADCONFIG 1" in lines
     assert any(l.startswith("NOSETS contacts 1 sets 0") for l in lines)
     assert "BATCH_PASSES 0 1" in lines and "BATCH_PASSES 1 1" in lines  # one tc_eval served every segment
+    # fixed timesteps make tc_eval skip terms: slices must still be the right timestep / segment (one pass each)
+    assert "BATCH_SKIPPED_TERMS 0 mismatches 0 skipped_refused 1 passes 1" in lines, [l for l in lines if "SKIPPED" in l]
+    assert "BATCH_SKIPPED_TERMS 1 mismatches 0 skipped_refused 1 passes 1" in lines
+    bd = [l for l in lines if l.startswith("BATCH_DISCRETE_FIXED")]
+    assert len(bd) == 1 and bd[0].startswith("BATCH_DISCRETE_FIXED mismatches 0 contacts") and bd[0].endswith("passes 1"), bd
+    assert int(bd[0].split()[4]) > 0
     # arm_around_table seed trajectory against the oracle, segment by segment
     s = helpers.load_scene("arm_around_table")
     so = oracle.scene(s, 0.025, 20.0, 0.01)

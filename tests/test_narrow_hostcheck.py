@@ -143,3 +143,33 @@ def test_large_hull_without_table_matches_oracle(oracle, hostcheck):
             n_contact += 1
             assert ro["iters"] == rh["iters"] and abs(ro["distance"] - rh["distance"]) <= 1e-12, (it, ro, rh)
     assert n_contact > 30
+
+
+def test_shared_sincos_and_fk_are_bit_identical_and_accurate(oracle, hostcheck):
+    """The device FK (host-compiled), and the oracle's FK evaluate ONE sin/cos operation sequence: same bits out.
+    That is what lets the contraction-free GPU kernels (tc_strict.cu) start GJK on curved cores from the oracle's own
+    inputs.  Accuracy of the shared sin/cos against libm: <= 2.5e-16 absolute (it replaces libm's in both)."""
+    import ctypes as C
+    rng = np.random.default_rng(11)
+    xs = np.concatenate([rng.uniform(-7, 7, 20000), rng.uniform(-1e5, 1e5, 5000), [0.0, -0.0, np.pi / 2, np.pi, 1e5, 1e-300],
+                         np.arange(-8, 9) * (np.pi / 4)])
+    so, co, sh, ch = C.c_double(), C.c_double(), C.c_double(), C.c_double()
+    oracle.dll.orc_sincos.restype = None
+    hostcheck.dll.hc_sincos.restype = None
+    worst = 0.0
+    for x in xs:
+        oracle.dll.orc_sincos(C.c_double(x), C.byref(so), C.byref(co))
+        hostcheck.dll.hc_sincos(C.c_double(x), C.byref(sh), C.byref(ch))
+        assert so.value == sh.value and co.value == ch.value, x
+        worst = max(worst, abs(so.value - np.sin(x)), abs(co.value - np.cos(x)))
+    assert worst <= 2.5e-16, worst
+    s = helpers.load_scene("arm_around_table")
+    sco, sch = oracle.scene(s, 0.025, 20.0, 0.01), hostcheck.scene(s, 0.025, 20.0, 0.01)
+    lim = s["joint_limits"]
+    pd = C.POINTER(C.c_double)
+    for _ in range(200):
+        q = np.ascontiguousarray(rng.uniform(lim[:, 0], lim[:, 1]))
+        a = oracle.fk(sco, q)
+        b = np.zeros_like(a)
+        assert hostcheck.dll.hc_fk(sch.handle, q.ctypes.data_as(pd), b.ctypes.data_as(pd)) == 0
+        assert np.array_equal(a, b)

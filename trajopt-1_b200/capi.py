@@ -56,7 +56,7 @@ class SceneDesc(C.Structure):
 class EvalDesc(C.Structure):
     _fields_ = [
         ("evaluator", C.c_int32), ("stack", C.c_int32), ("precision", C.c_int32), ("want", C.c_int32),
-        ("lvs_length", C.c_double), ("fixed_steps", _pb), ("q_on_device", C.c_int32), ("reserved", C.c_int32),
+        ("lvs_length", C.c_double), ("fixed_steps", _pb), ("q_on_device", C.c_int32), ("contact_test_type", C.c_int32),
     ]
 
 
@@ -75,7 +75,7 @@ GRADIENT_DTYPE = np.dtype([
 assert GRADIENT_DTYPE.itemsize == 64
 
 COUNT_FIELDS = ["n_states", "n_units", "n_dense", "n_candidates", "n_narrowphase", "n_contacts", "n_rows", "nnz",
-                "gjk_iters", "support_verts", "n_epa", "n_unconverged", "n_terms", "overflow", "epa_iters"]
+                "gjk_iters", "support_verts", "n_epa", "n_unconverged", "n_terms", "overflow", "epa_iters", "support_compared"]
 
 SET_DTYPE = np.dtype([
     ("traj", "<i4"), ("term", "<i4"), ("pair", "<i4"), ("shape_key", "<i4", 2), ("n_results", "<i4"),
@@ -284,8 +284,11 @@ class Result:
             pass
 
 
+CONTACT_ALL, CONTACT_CLOSEST, CONTACT_FIRST = 0, 1, 2
+
+
 def make_eval_desc(evaluator, stack=STACK_IFOPT, lvs=0.005, fixed=None, want=WANT_ALL, precision=PRECISION_F64,
-                   q_on_device=False):
+                   q_on_device=False, contact_type=CONTACT_ALL):
     d = EvalDesc()
     d.evaluator, d.stack, d.precision, d.want = int(evaluator), int(stack), int(precision), int(want)
     d.lvs_length = float(lvs)
@@ -294,6 +297,7 @@ def make_eval_desc(evaluator, stack=STACK_IFOPT, lvs=0.005, fixed=None, want=WAN
         keep = np.ascontiguousarray(fixed, dtype=np.uint8)
         d.fixed_steps = _p(keep, _pb)
     d.q_on_device = 1 if q_on_device else 0
+    d.contact_test_type = int(contact_type)
     return d, keep
 
 
@@ -339,13 +343,30 @@ class CudaLib(Lib):
         self.check(self.dll.tc_result_create(scene.handle, C.byref(h)))
         return h
 
+    def contact_test(self, scene, pose0, pose1=None, contact_type=CONTACT_ALL, precision=PRECISION_F64, result=None):
+        """seam B3 (tc_contact_test): pose0 / pose1 numpy [n_states, n_active_links, 12] -> Result (one term per state)"""
+        pose0 = np.ascontiguousarray(pose0, dtype=np.float64)
+        n_states = pose0.shape[0]
+        assert pose0.shape[1:] == (scene.n_active, 12)
+        p1 = None
+        if pose1 is not None:
+            p1 = np.ascontiguousarray(pose1, dtype=np.float64)
+            assert p1.shape == pose0.shape
+        if result is None:
+            result = Result(self, scene, self.new_result(scene), n_states, 2 if p1 is not None else 1)
+        result.B, result.T = n_states, (2 if p1 is not None else 1)
+        self.check(self.dll.tc_contact_test(scene.handle, _p(pose0, _pd), _p(p1, _pd) if p1 is not None else _pd(),
+                                            C.c_int32(n_states), C.c_int32(contact_type), C.c_int32(precision),
+                                            result.handle, C.c_void_p(0)))
+        return result
+
     def eval(self, scene, q, evaluator, stack=STACK_IFOPT, lvs=0.005, fixed=None, want=WANT_ALL,
-             precision=PRECISION_F64, result=None, stream=None):
+             precision=PRECISION_F64, result=None, stream=None, contact_type=CONTACT_ALL):
         """q: numpy [B, T, n_dof] (host) -> Result"""
         q = np.ascontiguousarray(q, dtype=np.float64)
         B, T, n = q.shape
         assert n == scene.n_dof
-        d, keep = make_eval_desc(evaluator, stack, lvs, fixed, want, precision)
+        d, keep = make_eval_desc(evaluator, stack, lvs, fixed, want, precision, contact_type=contact_type)
         if result is None:
             result = Result(self, scene, self.new_result(scene), B, T)
         result.B, result.T = B, T

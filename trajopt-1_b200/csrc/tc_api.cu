@@ -36,6 +36,8 @@ int cudaFail(cudaError_t e, const char* what)
 
 std::mutex g_init_mutex;
 int g_device = -1;
+// tc_cost_noalloc's static scratch: its device address is resolved once per device (defined at the end of this file)
+int resolveNoallocScratch(int device, double** out);
 }  // namespace
 
 struct tc_scene
@@ -69,7 +71,8 @@ struct tc_result
   float stage_ms[10]{};
   int own_launches{ 0 }, lib_launches{ 0 };
   // arenas
-  DevBuf<double> q;
+  DevBuf<double> q, pose_in;
+  DevBuf<uint8_t> raw_valid;
   DevBuf<int32_t> term_t_d, term_cnt, term_states, term_units, state_base, unit_base, unit_term;
   DevBuf<uint8_t> term_fixed_d, term_interp;
   DevBuf<double> poses, aabb;
@@ -176,10 +179,12 @@ int reserve(DevBuf<T>& b, size_t n, const char* what)
 
 int enqueueRows(tc_result* r, bool fused);
 
+// pose0 / pose1 != nullptr: tc_contact_test — link poses come from the caller ([B][n_active][12] host arrays, pose1 only
+// for a cast test), there are no joint values (q == nullptr), B = number of states, T = 1 or 2
 int runEval(tc_scene* scene, const tc_eval_desc* desc, const double* q, int32_t B, int32_t T, tc_result* r,
-            cudaStream_t st)
+            cudaStream_t st, const double* pose0 = nullptr, const double* pose1 = nullptr)
 {
-  if (!scene || !desc || !q || !r)
+  if (!scene || !desc || (!q && !pose0) || !r)
     return fail(TC_ERR_INVALID, "null argument");
   if (r->scene != scene)
     return fail(TC_ERR_INVALID, "result object belongs to another scene");
@@ -189,6 +194,8 @@ int runEval(tc_scene* scene, const tc_eval_desc* desc, const double* q, int32_t 
     return fail(TC_ERR_INVALID, "invalid stack");
   if (desc->precision != TC_PRECISION_F64 && desc->precision != TC_PRECISION_F32)
     return fail(TC_ERR_INVALID, "invalid precision");
+  if (desc->contact_test_type < TC_CONTACT_ALL || desc->contact_test_type > TC_CONTACT_FIRST)
+    return fail(TC_ERR_INVALID, "invalid contact_test_type");
   if (B <= 0 || T <= 0)
     return fail(TC_ERR_INVALID, "empty batch");
   if (desc->evaluator != TC_EVAL_DISCRETE && T < 2)
@@ -251,6 +258,8 @@ int runEval(tc_scene* scene, const tc_eval_desc* desc, const double* q, int32_t 
   w.ep = ep;
   w.cast = (desc->evaluator == TC_EVAL_CONTINUOUS || desc->evaluator == TC_EVAL_LVS_CONTINUOUS) ? 1 : 0;
   w.single_sweep = (desc->evaluator == TC_EVAL_CONTINUOUS && desc->stack == TC_STACK_IFOPT) ? 1 : 0;
+  w.poses_given = pose0 ? 1 : 0;
+  w.contact_type = desc->contact_test_type;
   w.counters = r->d_counters;
   for (int i = 0; i < 10; ++i)
     r->stage_ms[i] = 0;
@@ -277,7 +286,17 @@ int runEval(tc_scene* scene, const tc_eval_desc* desc, const double* q, int32_t 
   // Host inputs reach the device through kernels that read mapped pinned memory, not through the copy
   // engines: a bulk result download of another tc_result may occupy an engine for milliseconds, and an
   // input copy queued behind it would stall this whole pass.
-  if (desc->q_on_device)
+  if (pose0)
+  {
+    const size_t np = static_cast<size_t>(B) * hs.n_active * 12;
+    TC_RESERVE(r->pose_in, 2 * np);
+    TC_CUDA(cudaMemcpyAsync(r->pose_in.p, pose0, np * sizeof(double), cudaMemcpyHostToDevice, st));
+    if (pose1)
+      TC_CUDA(cudaMemcpyAsync(r->pose_in.p + np, pose1, np * sizeof(double), cudaMemcpyHostToDevice, st));
+    w.pose_in = r->pose_in.p;
+    w.q = nullptr;
+  }
+  else if (desc->q_on_device)
     w.q = q;
   else
   {
@@ -338,7 +357,10 @@ int runEval(tc_scene* scene, const tc_eval_desc* desc, const double* q, int32_t 
   TC_RESERVE(r->sp_offset, hs.spairs.size() + 1);
   w.poses = r->poses.p, w.aabb = r->aabb.p, w.unit_term = r->unit_term.p;
   w.sp_count = r->sp_count.p, w.sp_cursor = r->sp_cursor.p, w.sp_offset = r->sp_offset.p;
-  TC_CUDA(launchFk(v, w, st));
+  if (pose0)
+    TC_CUDA(launchPoseIn(v, w, st));
+  else
+    TC_CUDA(launchFk(v, w, st));
   TC_CUDA(cudaEventRecord(r->ev[1], st));
   TC_CUDA(launchBroadCount(v, w, st));
   TC_TRY(readCounters(r));
@@ -358,6 +380,7 @@ int runEval(tc_scene* scene, const tc_eval_desc* desc, const double* q, int32_t 
     TC_CUDA(launchBroadFill(v, w, st));
     TC_CUDA(cudaEventRecord(r->ev[5], st));
     TC_CUDA(launchNarrow(v, w, desc->precision, st, r->ev[6]));
+    TC_CUDA(launchRouteCurved(v, w, st));  // cylinder / cone pairs: skipped by k_gjk, served by the deep kernel below
   }
   else
   {
@@ -390,6 +413,11 @@ int runEval(tc_scene* scene, const tc_eval_desc* desc, const double* q, int32_t 
   TC_RESERVE(r->idx_alt, w.n_raw);
   w.contacts_tmp = r->contacts_tmp.p;
   w.keys = r->keys.p, w.keys_alt = r->keys_alt.p, w.idx = r->idx.p, w.idx_alt = r->idx_alt.p;
+  if (w.contact_type != TC_CONTACT_ALL)
+  {
+    TC_RESERVE(r->raw_valid, w.n_raw);
+    w.raw_valid = r->raw_valid.p;
+  }
   if (w.n_raw > 0)
   {
     TC_CUDA(launchFinalize(v, w, st));
@@ -398,6 +426,13 @@ int runEval(tc_scene* scene, const tc_eval_desc* desc, const double* q, int32_t 
     TC_RESERVE(r->sort_temp, temp_bytes);
     TC_CUDA(sortContacts(w, r->sort_temp.p, temp_bytes, st));
     r->lib_launches += 1;  // cub::DeviceRadixSort (several kernels of the CUDA toolkit's library)
+    if (w.contact_type != TC_CONTACT_ALL)
+    {
+      // the manager's CLOSEST / FIRST choice over the sorted hits, then the final order
+      TC_CUDA(launchTypeFilter(v, w, r->raw_valid.p, st));
+      TC_CUDA(sortContacts(w, r->sort_temp.p, temp_bytes, st));
+      r->lib_launches += 1;
+    }
     TC_TRY(readCounters(r));
   }
   w.n_contacts = r->h_counters->n_valid;
@@ -406,6 +441,8 @@ int runEval(tc_scene* scene, const tc_eval_desc* desc, const double* q, int32_t 
   w.contacts = r->contacts.p, w.term_ptr = r->term_ptr.p;
   TC_CUDA(launchGather(v, w, st));
   // ---- K4 ----
+  if (pose0 && (desc->want & (TC_WANT_GRADIENTS | TC_WANT_ROWS)))
+    return fail(TC_ERR_INVALID, "gradients and rows need joint values");
   if (desc->want & TC_WANT_GRADIENTS)
   {
     TC_RESERVE(r->grad, static_cast<size_t>(w.n_contacts) * 4 * hs.n_dof);
@@ -456,6 +493,7 @@ int finishEval(tc_result* r)
   o.nnz = r->have_rows ? c.nnz : 0;
   o.gjk_iters = c.gjk_iters;
   o.support_verts = c.support_verts;
+  o.support_compared = c.support_compared;
   o.n_epa = c.n_epa;
   o.n_unconverged = c.n_unconverged;
   o.overflow = c.overflow;
@@ -592,6 +630,10 @@ int tc_init(int device_ordinal)
     return fail(TC_ERR_CUDA, std::string("device is not sm_100 (B200): ") + prop.name);
   TC_CUDA(cudaSetDevice(device_ordinal));
   g_device = device_ordinal;
+  // resolve tc_cost_noalloc's scratch address now, so that a later first call made under CUDA graph capture
+  // does not have to (cudaGetSymbolAddress may initialise the module, which is not capturable)
+  double* unused = nullptr;
+  TC_TRY(resolveNoallocScratch(device_ordinal, &unused));
   return TC_OK;
 }
 
@@ -651,6 +693,7 @@ int tc_scene_create(const tc_scene_desc* desc, tc_scene** out)
   UP(partner_ptr, h.partner_ptr);
   UP(partner_sp, h.partner_sp);
   UP(partner_word_ptr, h.partner_word_ptr);
+  UP(curved_sp, h.curved_sp);
 #undef UP
   if (st != TC_OK)
   {
@@ -749,6 +792,7 @@ void tc_result_destroy(tc_result* r)
   for (int i = 0; i < 7; ++i)
     if (r->ev[i])
       cudaEventDestroy(r->ev[i]);
+  r->pose_in.release(), r->raw_valid.release();
   r->q.release(), r->term_t_d.release(), r->term_cnt.release(), r->term_states.release(), r->term_units.release();
   r->state_base.release(), r->unit_base.release(), r->unit_term.release(), r->term_fixed_d.release();
   r->term_interp.release(), r->poses.release(), r->aabb.release(), r->bp_mask.release(), r->sp_count.release(), r->sp_offset.release();
@@ -777,6 +821,23 @@ int tc_result_sync(tc_result* res)
   if (!res)
     return fail(TC_ERR_INVALID, "null result");
   return finishEval(res);
+}
+
+int tc_contact_test(tc_scene* scene, const double* link_pose0, const double* link_pose1, int32_t n_states,
+                    int32_t contact_test_type, int32_t precision, tc_result* out, void* cuda_stream)
+{
+  if (!link_pose0)
+    return fail(TC_ERR_INVALID, "null argument");
+  tc_eval_desc d{};
+  d.evaluator = link_pose1 ? TC_EVAL_CONTINUOUS : TC_EVAL_DISCRETE;
+  d.stack = TC_STACK_IFOPT;  // CONTINUOUS = one sweep per state
+  d.precision = precision;
+  d.want = TC_WANT_CONTACTS | TC_WANT_COST;
+  d.lvs_length = 1.0;  // unused: one sweep per state
+  d.contact_test_type = contact_test_type;
+  TC_TRY(runEval(scene, &d, nullptr, n_states, link_pose1 ? 2 : 1, out, static_cast<cudaStream_t>(cuda_stream), link_pose0,
+                 link_pose1));
+  return finishEval(out);
 }
 
 int tc_eval(tc_scene* scene, const tc_eval_desc* desc, const double* q, int32_t B, int32_t T, tc_result* out,
@@ -1287,6 +1348,22 @@ __global__ void k_cost_traj_noalloc(int n_traj, int terms_per_traj, const double
 constexpr int NOALLOC_MAX_DEVICES = 64;
 std::mutex g_noalloc_mutex;
 double* g_noalloc_ptr[NOALLOC_MAX_DEVICES] = {};
+
+// `device` must be the current device
+int resolveNoallocScratch(int device, double** out)
+{
+  if (device < 0 || device >= NOALLOC_MAX_DEVICES)
+    return fail(TC_ERR_INVALID, "tc_cost_noalloc: device ordinal out of range");
+  std::lock_guard<std::mutex> lock(g_noalloc_mutex);
+  if (!g_noalloc_ptr[device])
+  {
+    double* p = nullptr;
+    TC_CUDA(cudaGetSymbolAddress(reinterpret_cast<void**>(&p), g_noalloc_cost_term));
+    g_noalloc_ptr[device] = p;
+  }
+  *out = g_noalloc_ptr[device];
+  return TC_OK;
+}
 }  // namespace
 
 extern "C" int tc_cost_noalloc(const int64_t* term_ptr, int32_t n_terms, int32_t terms_per_traj,
@@ -1294,7 +1371,7 @@ extern "C" int tc_cost_noalloc(const int64_t* term_ptr, int32_t n_terms, int32_t
                                double* cost_per_traj, void* cuda_stream)
 {
   static_assert(sizeof(long long) == sizeof(int64_t), "term_ptr layout");
-  if (!term_ptr || !cost_per_traj || n_terms <= 0 || terms_per_traj <= 0)
+  if (!term_ptr || !distance || !margin || !coeff || !cost_per_traj || n_terms <= 0 || terms_per_traj <= 0)
     return fail(TC_ERR_INVALID, "tc_cost_noalloc: null argument or empty batch");
   if (n_terms % terms_per_traj != 0)
     return fail(TC_ERR_INVALID, "tc_cost_noalloc: n_terms is not a multiple of terms_per_traj");
@@ -1302,21 +1379,12 @@ extern "C" int tc_cost_noalloc(const int64_t* term_ptr, int32_t n_terms, int32_t
     return fail(TC_ERR_OVERFLOW, "tc_cost_noalloc: n_terms = " + std::to_string(n_terms) + " exceeds the static scratch of " +
                                      std::to_string(TC_NOALLOC_MAX_TERMS) +
                                      " terms (TC_NOALLOC_MAX_TERMS); split the batch or use tc_result_cost");
+  // runs on the CURRENT device (the arrays are the caller's); the address of that device's copy of the scratch was
+  // resolved by tc_init for its device, and is resolved here on first use for any other
   int dev = -1;
   TC_CUDA(cudaGetDevice(&dev));
-  if (dev < 0 || dev >= NOALLOC_MAX_DEVICES)
-    return fail(TC_ERR_INVALID, "tc_cost_noalloc: device ordinal out of range");
   double* scratch = nullptr;
-  {
-    std::lock_guard<std::mutex> lock(g_noalloc_mutex);
-    if (!g_noalloc_ptr[dev])
-    {
-      double* p = nullptr;
-      TC_CUDA(cudaGetSymbolAddress(reinterpret_cast<void**>(&p), g_noalloc_cost_term));
-      g_noalloc_ptr[dev] = p;
-    }
-    scratch = g_noalloc_ptr[dev];
-  }
+  TC_TRY(resolveNoallocScratch(dev, &scratch));
   cudaStream_t st = static_cast<cudaStream_t>(cuda_stream);
   const int n_traj = n_terms / terms_per_traj;
   const unsigned grid_term = static_cast<unsigned>((static_cast<long long>(n_terms) * 32 + 255) / 256);

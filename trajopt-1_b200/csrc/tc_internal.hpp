@@ -54,6 +54,7 @@ struct Counters
   long long n_states, n_units, n_items, n_items_padded, n_raw, n_valid, n_deep;
   long long gjk_iters, support_verts, n_epa, epa_iters, n_unconverged, overflow, nnz;
   long long gjk_cursor, epa_cursor_g;  // work cursors of the warp-persistent narrow-phase kernels
+  long long support_compared;          // hull vertices actually compared by support queries (support_verts: all of the hull)
 };
 
 template <class T>
@@ -96,6 +97,9 @@ struct Work
   EvalParams ep;
   int cast;  // evaluator sweeps (CONTINUOUS / LVS_CONTINUOUS)
   int single_sweep;
+  int poses_given;  // tc_contact_test: link poses come from the caller (pose_in), there are no joint values
+  int contact_type; // TC_CONTACT_*
+  const double* pose_in;  // [2 (T0, T1)][n_terms][n_active][12] (device) when poses_given
   const double* q;
   const int32_t* term_t;       // [terms_per_traj]
   const uint8_t* term_fixed;   // [terms_per_traj][2]
@@ -114,6 +118,7 @@ struct Work
   EpaRec* epa_rec;
   unsigned long long *keys, *keys_alt;
   int32_t *idx, *idx_alt;
+  uint8_t* raw_valid;  // [n_raw] the evaluator's filters passed (contact_type != ALL: applied after the manager's choice)
   tc_contact *contacts_tmp, *contacts;
   long long* term_ptr;  // [n_terms+1]
   double* grad;
@@ -141,7 +146,9 @@ cudaError_t launchCopy32(void* dst, const void* src, size_t n_words, cudaStream_
 cudaError_t launchCopy64(void* dst, const void* src, size_t n_dwords, cudaStream_t st);
 cudaError_t launchSnapshot(const Counters* dev, Counters* mapped_host, cudaStream_t st);
 cudaError_t launchPlan(const SceneView& v, const Work& w, cudaStream_t st);
-cudaError_t launchFk(const SceneView& v, const Work& w, cudaStream_t st);
+cudaError_t launchFk(const SceneView& v, const Work& w, cudaStream_t st);  // tc_strict.cu
+cudaError_t launchPoseIn(const SceneView& v, const Work& w, cudaStream_t st);  // tc_strict.cu
+cudaError_t launchTypeFilter(const SceneView& v, const Work& w, const uint8_t* valid, cudaStream_t st);
 cudaError_t launchBroadCount(const SceneView& v, const Work& w, cudaStream_t st);
 cudaError_t launchBroadFill(const SceneView& v, const Work& w, cudaStream_t st);
 cudaError_t launchFinalize(const SceneView& v, const Work& w, cudaStream_t st);
@@ -162,6 +169,8 @@ cudaError_t launchSets(const SceneView& v, const Work& w, int max_num_cnt, tc_se
                        int32_t* set_run, double* values, double* coeffs, double* jac, cudaStream_t st);
 // ---- launchers (tc_narrow.cu) ----
 cudaError_t launchNarrow(const SceneView& v, const Work& w, int precision, cudaStream_t st, cudaEvent_t mid);
+// ---- launchers (tc_strict.cu: contraction-free kernels) ----
+cudaError_t launchRouteCurved(const SceneView& v, const Work& w, cudaStream_t st);
 cudaError_t launchNarrowDeep(const SceneView& v, const Work& w, int precision, long long n_deep, void* scratch,
                              size_t scratch_bytes_per_thread, int n_threads, cudaStream_t st);
 size_t deepScratchBytesPerThread(int precision);

@@ -81,6 +81,15 @@ TC_HD int lutCellF(float x, float y, float z)
   return ((2 * m + (mj < 0 ? 1 : 0)) * LUT_G + iv) * LUT_G + iu;
 }
 
+// Work counter of the support queries of one item: low half = vertices of the queried hulls (what the reference's
+// plain scan of every vertex touches: the ALGORITHMIC figure of SURVEY.md 8(d)), high half = vertices actually compared
+// (the look-up table leaves ~5 % of a hull) -> roofline.frac and roofline.frac_executed of bench.py
+typedef unsigned long long ScanCount;
+TC_HD void countScan(ScanCount& s, int full, int compared)
+{
+  s += static_cast<unsigned long long>(static_cast<unsigned>(full)) | (static_cast<unsigned long long>(static_cast<unsigned>(compared)) << 32);
+}
+
 template <class R>
 struct ShapeCore
 {
@@ -149,20 +158,41 @@ struct Tol<float>
   TC_HD static float centerTiny() { return 1e-12f; }
 };
 
-// support of a primitive core (not a hull) in link-frame direction d
+// support of a primitive core (not a hull) in link-frame direction d.
+// Tie band: on the SIDE of a capsule / cylinder the contact normal is perpendicular to the axis, and on the side of a
+// cone it makes exactly the half-angle with it, so in exact arithmetic the end-cap decision below is a tie, and in
+// floating point it is decided by the last bit of d (a coin flip that moves the support point by the whole length of
+// the shape; calculateContinuousData turns that into an O(1e-3) change of cc_time).  |al| within 1e-12 |d| of the tie
+// is therefore taken as the tie itself, resolved one fixed way (capsule / cylinder: the +axis end, cone: the base
+// rim).  The support value loses at most 1e-12 |d| x length, far below GJK's 1e-10 m stop.
+template <class R>
+TC_HD R supportTie();
+template <>
+TC_HD double supportTie<double>()
+{
+  return 1e-12;
+}
+template <>
+TC_HD float supportTie<float>()
+{
+  return 1e-5f;
+}
+
 template <class R>
 TC_HD Vec3<R> primitiveSupport(const ShapeCore<R>& s, Vec3<R> d)
 {
   if (s.type == SH_SPHERE)
     return s.center;
   const R al = dot(d, s.axis);
+  const R dn = norm(d);
+  const R tie = supportTie<R>() * dn;
   if (s.type == SH_CAPSULE)
-    return s.center + ((al >= 0) ? s.half_len : -s.half_len) * s.axis;
+    return s.center + ((al >= -tie) ? s.half_len : -s.half_len) * s.axis;
   const Vec3<R> rad = d - al * s.axis;
   const R rn = norm(rad);
   if (s.type == SH_CYLINDER)
   {
-    Vec3<R> p = s.center + ((al >= 0) ? s.half_len : -s.half_len) * s.axis;
+    Vec3<R> p = s.center + ((al >= -tie) ? s.half_len : -s.half_len) * s.axis;
     if (rn > Tol<R>::tiny())
       p = p + (s.radius / rn) * rad;
     return p;
@@ -170,7 +200,7 @@ TC_HD Vec3<R> primitiveSupport(const ShapeCore<R>& s, Vec3<R> d)
   // cone: apex at +half_len, base disc at -half_len
   const R h = 2 * s.half_len;
   const R sin_a = s.radius / tc_sqrt(s.radius * s.radius + h * h);
-  if (al > norm(d) * sin_a)
+  if (al > dn * sin_a + tie)
     return s.center + s.half_len * s.axis;
   Vec3<R> p = s.center - s.half_len * s.axis;
   if (rn > Tol<R>::tiny())
@@ -249,13 +279,13 @@ struct Placed
 
   // `scanned` counts the vertices of the hull per queried pose (the work of the plain scan the reference's
   // convex-hull support does), whether or not the look-up table let most of them be skipped
-  TC_HD Vec3<R> support(Vec3<R> d, int& scanned) const
+  TC_HD Vec3<R> support(Vec3<R> d, ScanCount& scanned) const
   {
     if (TC_UNLIKELY(sh.type != SH_HULL))
       return primitiveSupportPlaced(sh, p0, p1, cast, d);
     const Vec3<R> d0 = p0.rotT(d);
     const Vec3<R> d1 = cast ? p1.rotT(d) : d0;
-    int b0 = 0, b1 = 0;
+    int b0 = 0, b1 = 0, ncmp = 0;
     bool done = false;
     if (sh.lut)
     {
@@ -266,9 +296,10 @@ struct Placed
       if (c0 >= 0 && c1 >= 0)
       {
         R best = lowestReal<R>();
-        const int e0 = sh.lut[c0 + 1];
+        const int k0 = sh.lut[c0], e0 = sh.lut[c0 + 1];
+        ncmp = e0 - k0;
 #pragma unroll 1
-        for (int k = sh.lut[c0]; k < e0; ++k)
+        for (int k = k0; k < e0; ++k)
         {
           const int i = cand[k];
           const Vtx<R> q = sh.verts[i];
@@ -282,9 +313,10 @@ struct Placed
         if (cast)
         {
           best = lowestReal<R>();
-          const int e1 = sh.lut[c1 + 1];
+          const int k1 = sh.lut[c1], e1 = sh.lut[c1 + 1];
+          ncmp += e1 - k1;
 #pragma unroll 1
-          for (int k = sh.lut[c1]; k < e1; ++k)
+          for (int k = k1; k < e1; ++k)
           {
             const int i = cand[k];
             const Vtx<R> q = sh.verts[i];
@@ -304,15 +336,16 @@ struct Placed
       const int packed = hullScanFull(sh.verts, sh.nverts, d0, d1, cast);
       b0 = packed & 65535;
       b1 = packed >> 16;
+      ncmp = cast ? 2 * sh.nverts : sh.nverts;
     }
     const Vtx<R> q0 = sh.verts[b0];
     const Vec3<R> w0 = p0.apply(Vec3<R>(q0.x, q0.y, q0.z));
     if (!cast)
     {
-      scanned += sh.nverts;
+      countScan(scanned, sh.nverts, ncmp);
       return w0;
     }
-    scanned += 2 * sh.nverts;
+    countScan(scanned, 2 * sh.nverts, ncmp);
     const Vtx<R> q1 = sh.verts[b1];
     const Vec3<R> w1 = p1.apply(Vec3<R>(q1.x, q1.y, q1.z));
     return (dot(d, w0) > dot(d, w1)) ? w0 : w1;
@@ -523,7 +556,7 @@ TC_HD void putPoint(Simplex<R>& s, int k, Vec3<R> w, Vec3<R> a)
 }
 
 template <class R>
-TC_HD GjkOut<R> gjk(const Placed<R>& A, const Placed<R>& B, R threshold_core, Simplex<R>& S, int& scanned)
+TC_HD GjkOut<R> gjk(const Placed<R>& A, const Placed<R>& B, R threshold_core, Simplex<R>& S, ScanCount& scanned)
 {
   GjkOut<R> r;
   r.separated_beyond = false;
@@ -754,7 +787,7 @@ TC_HD void epaOffer(EpaState<R>& E, int f, R d)
 // returns 0: polytope ready, run trips; 1: finished already (flat Minkowski difference), r is final
 template <class R, bool MASK>
 TC_HDN int epaInit(const Placed<R>& A, const Placed<R>& B, const Simplex<R>& start, R scale, EpaStore<R>& st,
-                   EpaState<R>& E, EpaOut<R>& r, int& scanned)
+                   EpaState<R>& E, EpaOut<R>& r, ScanCount& scanned)
 {
   r.ok = true;
   r.converged = true;
@@ -903,7 +936,7 @@ TC_HD int lowestBit(unsigned long long x)
 // `erow` is all-zero on entry and on exit.
 template <class R>
 TC_HD int epaTripMasked(const Placed<R>& A, const Placed<R>& B, EpaStore<R>& st, EpaState<R>& E,
-                        unsigned long long* erow, int& scanned)
+                        unsigned long long* erow, ScanCount& scanned)
 {
   const R DEGENERATE = -lowestReal<R>();
   const Vec3<R> bn = st.fn[E.best];
@@ -1022,7 +1055,7 @@ TC_HD int epaTripMasked(const Placed<R>& A, const Placed<R>& B, EpaStore<R>& st,
 }
 
 template <class R, bool MASK>
-TC_HDN int epaTrip(const Placed<R>& A, const Placed<R>& B, EpaStore<R>& st, EpaState<R>& E, int& scanned)
+TC_HDN int epaTrip(const Placed<R>& A, const Placed<R>& B, EpaStore<R>& st, EpaState<R>& E, ScanCount& scanned)
 {
   const R DEGENERATE = -lowestReal<R>();
   const Vec3<R> bn = st.fn[E.best];
@@ -1183,7 +1216,7 @@ TC_HDN void epaFinish(const EpaStore<R>& st, const EpaState<R>& E, EpaOut<R>& r)
 
 template <class R, bool MASK>
 TC_HDN EpaOut<R> epa(const Placed<R>& A, const Placed<R>& B, const Simplex<R>& start, R scale, EpaStore<R>& st,
-                     int& scanned)
+                     ScanCount& scanned)
 {
   EpaOut<R> r;
   EpaState<R> E;
@@ -1240,7 +1273,8 @@ struct DistOut
   R distance;
   Vec3<R> normal, pa, pb;  // normal from A to B; world witness points on the surfaces
   bool used_epa, converged;
-  int gjk_iters, epa_iters, scanned;
+  int gjk_iters, epa_iters;
+  ScanCount scanned;
 };
 
 template <class R>

@@ -39,7 +39,13 @@ __global__ void k_plan(SceneView v, Work w)
   if (k >= w.ep.n_terms)
     return;
   int cnt = 1, states = 1, units = 1, interp = 0;
-  if (w.ep.evaluator != TC_EVAL_DISCRETE)
+  if (w.poses_given)
+  {
+    // tc_contact_test: one state (discrete manager) or one sweep T0 -> T1 (cast manager) per term
+    cnt = w.cast ? 2 : 1;
+    states = cnt;
+  }
+  else if (w.ep.evaluator != TC_EVAL_DISCRETE)
   {
     const int b = k / w.ep.terms_per_traj, ti = k % w.ep.terms_per_traj;
     const int n = v.n_dof;
@@ -69,8 +75,11 @@ __global__ void k_plan(SceneView v, Work w)
       states = units = cnt;
       interp = 1;
     }
-    else if (!w.single_sweep && cnt > 2)
+    else if (!w.single_sweep && dist > w.ep.lvs)
     {
+      // the reference branches on dist > length, not on cnt (collision_terms.cpp:1107,
+      // continuous_collision_evaluators.cpp:204): when dist / length rounds to 1.0, cnt is 2 and the one sweep still
+      // takes the interpolated path (cc_type / cc_time rewritten by addInterpolatedCollisionResults)
       states = cnt;
       units = cnt - 1;
       interp = 1;
@@ -152,167 +161,6 @@ __global__ void __launch_bounds__(1024) k_scan_terms(Work w)
     w.counters->n_units = carry_u;
     if (carry_s > 2000000000ll)
       w.counters->overflow = 3;
-  }
-}
-
-__global__ void k_unit_term(Work w)
-{
-  const int u = blockIdx.x * blockDim.x + threadIdx.x;
-  if (u < w.n_units)
-    w.unit_term[u] = lastLE(w.unit_base, w.ep.n_terms, u);
-}
-
-// ---------------------------------------------------------------------------------------------
-// K1: batched forward kinematics of every sub-state + world AABB of every active shape
-//   get_state_fn_ -> JointGroup::calcFwdKin (trajopt/src/collision_terms.cpp:401-417,656,880-885,1123-1124;
-//   discrete_collision_evaluators.cpp:57-73; continuous_collision_evaluators.cpp:65-81,285-301) and the
-//   sub-state interpolation LinSpaced(cnt, q0, q1) (collision_terms.cpp:846-848)
-// One thread per sub-state, frames visited in topological order.
-// ---------------------------------------------------------------------------------------------
-#ifndef TC_FK_MINB
-#define TC_FK_MINB 6
-#endif
-__global__ void __launch_bounds__(TPB, TC_FK_MINB) k_fk(SceneView v, Work w)
-{
-  // per-warp staging tile: 32 poses, rows padded to 13 doubles (bank spread)
-  __shared__ double tile[TPB / 32][32 * 13];
-  // the kinematic tables are the same for every thread: one copy per block in shared memory (small scenes; large
-  // ones keep reading them through L1)
-  constexpr int SF = 48, SL = 32;
-  __shared__ double s_origin[SF * 12], s_axis[SF * 3], s_box[SL * 6];
-  __shared__ int s_parent[SF], s_type[SF], s_dof[SF], s_flink[SF], s_lframe[SL], s_sframe[SL];
-  const bool staged = v.n_frames <= SF && v.n_active <= SL && v.n_active_shapes <= SL;
-  if (staged)
-  {
-    for (int e = threadIdx.x; e < v.n_frames * 12; e += blockDim.x)
-      s_origin[e] = v.frame_origin[e];
-    for (int e = threadIdx.x; e < v.n_frames * 3; e += blockDim.x)
-      s_axis[e] = v.frame_axis[e];
-    for (int e = threadIdx.x; e < v.n_frames; e += blockDim.x)
-    {
-      s_parent[e] = v.frame_parent[e], s_type[e] = v.frame_type[e], s_dof[e] = v.frame_dof[e];
-      s_flink[e] = v.frame_link[e];
-    }
-    for (int e = threadIdx.x; e < v.n_active; e += blockDim.x)
-      s_lframe[e] = v.link_frame[e];
-    for (int e = threadIdx.x; e < v.n_active_shapes; e += blockDim.x)
-    {
-      s_sframe[e] = v.active_shape_frame[e];
-      const ShapeD& sh = v.shapes[v.active_shapes[e]];
-      for (int r = 0; r < 3; ++r)
-        s_box[6 * e + r] = sh.aabb_c[r], s_box[6 * e + 3 + r] = sh.aabb_h[r];
-    }
-    __syncthreads();
-  }
-  SceneView t = v;  // table pointers redirected to the staged copies
-  if (staged)
-  {
-    t.frame_origin = s_origin, t.frame_axis = s_axis, t.frame_parent = s_parent, t.frame_type = s_type;
-    t.frame_dof = s_dof, t.frame_link = s_flink, t.link_frame = s_lframe, t.active_shape_frame = s_sframe;
-  }
-  const long long s_raw = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
-  const bool live = s_raw < w.n_states;
-  const long long s = live ? s_raw : w.n_states - 1;  // idle lanes shadow the last state and write nothing
-  const unsigned lane = threadIdx.x & 31;
-  const long long warp_s0 = s_raw - lane;
-  const int warp_n = static_cast<int>(min(32ll, w.n_states - warp_s0));  // live lanes of this warp (may be <= 0)
-  double* my_tile = tile[threadIdx.x >> 5];
-  const int k = lastLE(w.state_base, w.ep.n_terms, static_cast<int>(s));
-  const int i = static_cast<int>(s) - w.state_base[k];
-  const int b = k / w.ep.terms_per_traj, ti = k % w.ep.terms_per_traj;
-  const int n = v.n_dof;
-  const double* q0 = w.q + (static_cast<size_t>(b) * w.ep.T + w.term_t[ti]) * n;
-  const bool discrete = w.ep.evaluator == TC_EVAL_DISCRETE;
-  const int cnt = w.term_interp[k] ? w.term_cnt[k] : 2;
-  // Frames are visited in topological order with the previous frame's pose in registers; a branch reads
-  // its parent back from this thread's own record in the pose arena (no thread-local frame array).
-  const Pose<double> base = Pose<double>::from12(v.base_pose);
-  Pose<double> cur = base;
-  for (int f = 0; f < v.n_frames; ++f)
-  {
-    const int p = t.frame_parent[f];
-    Pose<double> parent;
-    if (p < 0)
-      parent = base;
-    else if (p == f - 1)
-      parent = cur;
-    else if (t.frame_link[p] >= 0)
-      parent = Pose<double>::from12(posePtr(w, t.frame_link[p], s));
-    else
-    {
-      // a branching frame that carries no collision link: rebuild it from the root (rare)
-      parent = base;
-      for (int a = v.path_ptr[p]; a < v.path_ptr[p + 1]; ++a)
-      {
-        const int g = v.path_frames[a];
-        double qa = 0;
-        if (t.frame_type[g] != TC_JOINT_FIXED)
-        {
-          const int j = t.frame_dof[g];
-          qa = discrete ? q0[j] : linspaced(cnt, q0[j], q0[n + j], i);
-        }
-        parent = frameStepQ(t, parent, g, qa);
-      }
-    }
-    double qf = 0;
-    if (t.frame_type[f] != TC_JOINT_FIXED)
-    {
-      const int j = t.frame_dof[f];
-      qf = discrete ? q0[j] : linspaced(cnt, q0[j], q0[n + j], i);
-    }
-    cur = frameStepQ(t, parent, f, qf);
-    // every active link riding on this frame: the warp's 32 records of one link are one contiguous run of
-    // the arena, written with coalesced stores after a transpose through shared memory
-    for (int l = 0; l < v.n_active; ++l)
-    {
-      if (t.link_frame[l] != f)
-        continue;
-      cur.to12(my_tile + lane * 13);
-      __syncwarp();
-      if (warp_n > 0)
-      {
-        double* dst = w.poses + (static_cast<size_t>(l) * static_cast<size_t>(w.n_states) + static_cast<size_t>(warp_s0)) * 12;
-        const int total = warp_n * 12;
-#pragma unroll
-        for (int j = 0; j < 12; ++j)
-        {
-          const int e = j * 32 + static_cast<int>(lane);
-          if (e < total)
-            dst[e] = my_tile[(e / 12) * 13 + (e % 12)];
-        }
-      }
-      __syncwarp();
-    }
-    if (!live)
-      continue;
-    for (int a = 0; a < v.n_active_shapes; ++a)
-    {
-      if (t.active_shape_frame[a] != f)
-        continue;
-      double bc[3], bh[3];
-      if (staged)
-      {
-#pragma unroll
-        for (int r = 0; r < 3; ++r)
-          bc[r] = s_box[6 * a + r], bh[r] = s_box[6 * a + 3 + r];
-      }
-      else
-      {
-        const ShapeD& sh = v.shapes[v.active_shapes[a]];
-#pragma unroll
-        for (int r = 0; r < 3; ++r)
-          bc[r] = sh.aabb_c[r], bh[r] = sh.aabb_h[r];
-      }
-      const Vec3<double> c = cur.apply(Vec3<double>(bc[0], bc[1], bc[2]));
-      double* dst = w.aabb + static_cast<size_t>(a) * 6 * w.n_states + s;
-#pragma unroll
-      for (int r = 0; r < 3; ++r)
-      {
-        const double e = fabs(cur.r[3 * r + 0]) * bh[0] + fabs(cur.r[3 * r + 1]) * bh[1] + fabs(cur.r[3 * r + 2]) * bh[2];
-        dst[static_cast<size_t>(r) * w.n_states] = c.get(r) - e;
-        dst[static_cast<size_t>(3 + r) * w.n_states] = c.get(r) + e;
-      }
-    }
   }
 }
 
@@ -559,13 +407,69 @@ __global__ void __launch_bounds__(TPB, TC_FINALIZE_MINB) k_finalize(SceneView v,
     valid = finalizeContact(v, w.ep, raw, ui, p0, p1, c, nullptr);
     w.contacts_tmp[i] = c;
     unsigned long long key = ~0ull;
-    if (valid)
+    if (w.contact_type != TC_CONTACT_ALL)
+    {
+      // CLOSEST / FIRST: the manager chooses among ALL its hits before the evaluator filters them, so every raw hit is
+      // sorted first (k_type_select then keeps the chosen ones that also pass the filters).  FIRST groups by tested
+      // unit, so its first key is unit-major: term | substep | pair | shape pair
+      w.raw_valid[i] = valid ? 1 : 0;
+      if (w.contact_type == TC_CONTACT_FIRST)
+        key = (static_cast<unsigned long long>(ui.term) << 36) | (static_cast<unsigned long long>(ui.substep) << 22) |
+              (static_cast<unsigned long long>(sp.pair) << 8) | static_cast<unsigned long long>(sp.k);
+      else
+        key = (static_cast<unsigned long long>(ui.term) << 36) | (static_cast<unsigned long long>(sp.pair) << 22) |
+              (static_cast<unsigned long long>(ui.substep) << 8) | static_cast<unsigned long long>(sp.k);
+      valid = false;  // counted by k_type_select
+    }
+    else if (valid)
       key = (static_cast<unsigned long long>(ui.term) << 36) | (static_cast<unsigned long long>(sp.pair) << 22) |
             (static_cast<unsigned long long>(ui.substep) << 8) | static_cast<unsigned long long>(sp.k);
     w.keys[i] = key;
     w.idx[i] = static_cast<int32_t>(i);
   }
   const unsigned m = __ballot_sync(0xffffffffu, valid);
+  if ((threadIdx.x & 31) == 0 && m)
+    atomicAdd(reinterpret_cast<unsigned long long*>(&w.counters->n_valid), static_cast<unsigned long long>(__popc(m)));
+}
+
+// ContactTestType CLOSEST / FIRST (tesseract_collision: the manager keeps one result per link pair / stops at its first
+// result; the evaluators pass the type through, trajopt/src/problem_description.cpp:1669-1673).  Input: every raw hit
+// sorted by the first key (keys_alt / idx_alt).  Output: keys / idx rewritten for the final sort — the standard key for
+// the chosen hit of every group if it also passed the evaluator's filters, all-ones otherwise.
+__global__ void __launch_bounds__(TPB) k_type_select(Work w, const uint8_t* valid)
+{
+  const long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+  bool keep = false;
+  if (i < w.n_raw)
+  {
+    const unsigned long long key = w.keys_alt[i];
+    unsigned long long out = ~0ull;
+    if (w.contact_type == TC_CONTACT_FIRST)
+    {
+      const bool leader = i == 0 || (w.keys_alt[i - 1] >> 22) != (key >> 22);
+      keep = leader && valid[w.idx_alt[i]];
+      // back to the standard layout term | pair | substep | shape pair
+      out = (key & ~((1ull << 36) - 1)) | (((key >> 8) & 0x3fffull) << 22) | (((key >> 22) & 0x3fffull) << 8) | (key & 0xffull);
+    }
+    else
+    {
+      // closest of the link pair in this unit: smallest distance, first in shape-pair order on ties
+      const unsigned long long g = key >> 8;
+      const double mine = w.contacts_tmp[w.idx_alt[i]].distance;
+      bool best = true;
+      for (long long j = i - 1; j >= 0 && (w.keys_alt[j] >> 8) == g; --j)
+        if (w.contacts_tmp[w.idx_alt[j]].distance <= mine)
+          best = false;
+      for (long long j = i + 1; j < w.n_raw && (w.keys_alt[j] >> 8) == g; ++j)
+        if (w.contacts_tmp[w.idx_alt[j]].distance < mine)
+          best = false;
+      keep = best && valid[w.idx_alt[i]];
+      out = key;
+    }
+    w.keys[i] = keep ? out : ~0ull;
+    w.idx[i] = w.idx_alt[i];
+  }
+  const unsigned m = __ballot_sync(0xffffffffu, keep);
   if ((threadIdx.x & 31) == 0 && m)
     atomicAdd(reinterpret_cast<unsigned long long*>(&w.counters->n_valid), static_cast<unsigned long long>(__popc(m)));
 }
@@ -1303,15 +1207,6 @@ cudaError_t launchPlan(const SceneView& v, const Work& w, cudaStream_t st)
   return cudaGetLastError();
 }
 
-cudaError_t launchFk(const SceneView& v, const Work& w, cudaStream_t st)
-{
-  ++launchCounter();
-  k_unit_term<<<gridFor(w.n_units, 256), 256, 0, st>>>(w);
-  ++launchCounter();
-  k_fk<<<gridFor(w.n_states, TPB), TPB, 0, st>>>(v, w);
-  return cudaGetLastError();
-}
-
 cudaError_t launchBroadCount(const SceneView& v, const Work& w, cudaStream_t st)
 {
   cudaError_t e = launchFill(w.sp_count, 0, v.n_spairs, st);
@@ -1345,6 +1240,17 @@ cudaError_t launchFinalize(const SceneView& v, const Work& w, cudaStream_t st)
   {
     ++launchCounter();
     k_finalize<<<gridFor(w.n_raw, TPB), TPB, 0, st>>>(v, w);
+  }
+  return cudaGetLastError();
+}
+
+cudaError_t launchTypeFilter(const SceneView& v, const Work& w, const uint8_t* valid, cudaStream_t st)
+{
+  (void)v;
+  if (w.n_raw > 0)
+  {
+    ++launchCounter();
+    k_type_select<<<gridFor(w.n_raw, TPB), TPB, 0, st>>>(w, valid);
   }
   return cudaGetLastError();
 }

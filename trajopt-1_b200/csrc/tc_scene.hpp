@@ -57,6 +57,7 @@ struct HostScene
   std::vector<ShapePairD> spairs;
   std::vector<int32_t> partner_ptr, partner_sp;  // per active shape: the shape pairs it leads
   std::vector<int32_t> partner_word_ptr;         // per active shape: first 32-bit word of its broadphase mask
+  std::vector<int32_t> curved_sp;                // shape pairs with a cylinder or cone (served by tc_strict.cu)
   double margin_buffer{ 0 };
   int max_hull_verts{ 0 };
   std::vector<uint8_t> lut;  // support look-up tables of the hulls (ShapeD::lut_off / lut_bytes)
@@ -85,6 +86,8 @@ struct SceneView
   const PairD* pairs;
   const ShapePairD* spairs;
   const int32_t *partner_ptr, *partner_sp, *partner_word_ptr;
+  const int32_t* curved_sp;
+  int n_curved_sp;
   double margin_buffer;
 };
 
@@ -110,6 +113,8 @@ inline SceneView hostView(const HostScene& s)
   v.pairs = s.pairs.data(), v.spairs = s.spairs.data();
   v.partner_ptr = s.partner_ptr.data(), v.partner_sp = s.partner_sp.data();
   v.partner_word_ptr = s.partner_word_ptr.data();
+  v.curved_sp = s.curved_sp.data();
+  v.n_curved_sp = static_cast<int>(s.curved_sp.size());
   v.margin_buffer = s.margin_buffer;
   return v;
 }
@@ -396,6 +401,8 @@ inline void buildHostScene(const tc_scene_desc& d, HostScene& s)
         {
           partners[static_cast<size_t>(s.shapes[static_cast<size_t>(sa)].active_index)].push_back(
               static_cast<int32_t>(s.spairs.size()));
+          if (s.shapes[static_cast<size_t>(sa)].type >= TC_SHAPE_CYLINDER || s.shapes[static_cast<size_t>(sb)].type >= TC_SHAPE_CYLINDER)
+            s.curved_sp.push_back(static_cast<int32_t>(s.spairs.size()));
           s.spairs.push_back(ShapePairD{ static_cast<int32_t>(s.pairs.size()), sa, sb, k++ });
         }
       p.sp_count = k;

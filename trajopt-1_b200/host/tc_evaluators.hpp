@@ -264,6 +264,23 @@ public:
   {
     if (static_cast<int>(fixed_.size()) != T_)
       throw std::runtime_error("CollisionBatch: fixed_steps must have one entry per timestep");
+    // tc_eval skips fixed timesteps (DISCRETE) and segments with both ends fixed (two-state evaluators) when it builds
+    // its term list (CollisionTermInfo::hatch, trajopt/src/problem_description.cpp:1735-1858): term k of the result is
+    // not timestep / segment k.  term_of_[t] = index into term_ptr, -1 = skipped.
+    const bool discrete = cfg_.type == CollisionEvaluatorType::DISCRETE;
+    term_of_.assign(static_cast<std::size_t>(T_), -1);
+    int k = 0;
+    for (int t = 0; t < T_; ++t)
+    {
+      const bool cur = fixed_[static_cast<std::size_t>(t)] != 0;
+      if (discrete)
+      {
+        if (!cur)
+          term_of_[static_cast<std::size_t>(t)] = k++;
+      }
+      else if (t + 1 < T_ && !(cur && fixed_[static_cast<std::size_t>(t) + 1] != 0))
+        term_of_[static_cast<std::size_t>(t)] = k++;
+    }
   }
   // x = the iterate's joint values, row-major [n_steps][n_dof].  Re-evaluates only when x changed.
   void update(const double* x)
@@ -278,7 +295,7 @@ public:
     ++passes_;
   }
   // term = timestep (discrete) or segment index (continuous).  Returns false when the joint values asked for are
-  // not the ones of the memoised iterate.
+  // not the ones of the memoised iterate, or when the batched pass holds no term for that timestep / segment (fixed).
   bool slice(CollisionCacheData& out, int term, const double* dof0, const double* dof1, bool continuous,
              bool vars0_fixed, bool vars1_fixed, std::size_t max_allowed)
   {
@@ -293,8 +310,13 @@ public:
     if (continuous && (vars0_fixed != (fixed_[static_cast<std::size_t>(term)] != 0) ||
                        vars1_fixed != (fixed_[static_cast<std::size_t>(term) + 1] != 0)))
       return false;
-    detail::fillCacheData(out, *eval_.scene(), host_, host_.term_ptr[static_cast<std::size_t>(term)],
-                          host_.term_ptr[static_cast<std::size_t>(term) + 1], continuous, vars0_fixed, vars1_fixed,
+    if (continuous == (cfg_.type == CollisionEvaluatorType::DISCRETE))
+      return false;  // a one-state evaluator on a two-state batch or the reverse
+    const int k = term_of_[static_cast<std::size_t>(term)];
+    if (k < 0 || static_cast<std::size_t>(k) + 1 >= host_.term_ptr.size())
+      return false;
+    detail::fillCacheData(out, *eval_.scene(), host_, host_.term_ptr[static_cast<std::size_t>(k)],
+                          host_.term_ptr[static_cast<std::size_t>(k) + 1], continuous, vars0_fixed, vars1_fixed,
                           max_allowed);
     return true;
   }
@@ -306,6 +328,7 @@ private:
   TrajOptCollisionConfig cfg_;
   int T_;
   std::vector<uint8_t> fixed_;
+  std::vector<int> term_of_;
   std::vector<double> x_;
   HostResult host_;
   bool valid_{ false };
@@ -399,6 +422,8 @@ public:
     const std::size_t nd = static_cast<std::size_t>(scene_->nDof());
     if (dof_vals0.size() != nd || dof_vals1.size() != nd)
       throw std::runtime_error("ContinuousCollisionEvaluator: dof_vals have the wrong size");
+    if (vars0_fixed && vars1_fixed)  // the reference's constraints refuse this case (continuous_collision_constraint.cpp:70,273)
+      throw std::runtime_error("ContinuousCollisionEvaluator: both ends cannot be fixed!");
     if (batch_ && batch_->slice(collision_data, segment_, dof_vals0.data(), dof_vals1.data(), true, vars0_fixed,
                                 vars1_fixed, max_allowed))
       return;
