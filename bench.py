@@ -64,7 +64,8 @@ class ClockSampler(threading.Thread):
 
 def cpu_baseline(scene, seconds=12.0, n_seeds=None):
     """oracle (CPU restatement of the reference's evaluators, one evaluator per term, terms spread over all host
-    threads like BasicTrustRegionSQPMultiThreaded) on a bounded sample of the same workload"""
+    threads like BasicTrustRegionSQPMultiThreaded) on a bounded sample of the same workload; also on ONE thread, so that
+    the port's own thread scaling is on the record (VERDICT r1 #12)"""
     from oracle import pyoracle
     capi = pyoracle.capi
     orc = pyoracle.OracleLib()
@@ -72,19 +73,25 @@ def cpu_baseline(scene, seconds=12.0, n_seeds=None):
     so = orc.scene(scene, MARGIN, COEFF, BUFFER)
     n = n_seeds or max(8, 2 * cores)
     q = make_batch(scene, 0, n)
-    best, dense, t_end = None, 0, time.time() + seconds
-    while True:
-        t0 = time.perf_counter()
-        r = orc.eval(so, q, capi.EVAL_LVS_CONTINUOUS, lvs=LVS, fixed=fixed_steps(), n_threads=cores)
-        r.rows()
-        dt = time.perf_counter() - t0
-        dense = r.counts()["n_dense"]
-        best = dt if best is None else min(best, dt)
-        if time.time() > t_end:
-            break
-    return {"value": dense / best, "unit": UNIT, "cores": cores, "kind": "port",
+
+    def best_of(threads, budget, qq):
+        best, dense, t_end = None, 0, time.time() + budget
+        while True:
+            t0 = time.perf_counter()
+            r = orc.eval(so, qq, capi.EVAL_LVS_CONTINUOUS, lvs=LVS, fixed=fixed_steps(), n_threads=threads)
+            r.rows()
+            dt = time.perf_counter() - t0
+            dense = r.counts()["n_dense"]
+            best = dt if best is None else min(best, dt)
+            if time.time() > t_end:
+                return best, dense
+    best, dense = best_of(cores, seconds, q)
+    b1, d1 = best_of(1, min(6.0, seconds), q[:4])
+    return {"value": dense / best, "unit": UNIT, "cores": cores, "kind": "port", "value_1thread": d1 / b1,
+            "thread_scaling": (dense / best) / (d1 / b1),
             "sample": f"{n} seeds of the C4 workload (seeds 4000..{4000 + n - 1}), linearisation pass incl. rows, "
-                      f"best wall time in {seconds:.0f} s, std::thread over terms"}, best, dense
+                      f"best wall time in {seconds:.0f} s, std::thread over terms; value_1thread: 4 of those seeds on "
+                      "one thread"}, best, dense
 
 
 def sqp_iteration_latency(cu, with_cpu):
@@ -111,17 +118,20 @@ def sqp_iteration_latency(cu, with_cpu):
         fixed = np.zeros(q.shape[1], np.uint8)
         fixed[0] = fixed[-1] = 1
         sg = cu.scene(sc, prm["margin"], prm["coeff"], prm["buffer"])
-        res = capi.Result(cu, sg, cu.new_result(sg), 1, q.shape[1])
+        # one result per kind of pass, as an SQP driver would hold them: each keeps seeing passes of ONE shape, so all
+        # but the first are sized speculatively (no read-back inside the pass)
+        res = (capi.Result(cu, sg, cu.new_result(sg), 1, q.shape[1]), capi.Result(cu, sg, cu.new_result(sg), 1, q.shape[1]))
 
         def one(lib, scene, result=None):
-            kw = dict(result=result) if result is not None else {}
+            kw = dict(result=result[0]) if result is not None else {}
+            kw2 = dict(result=result[1]) if result is not None else {}
             t0 = time.perf_counter()
             # the CPU port assembles its rows from stored gradients; the device folds them into the rows on the fly
             lin = capi.WANT_LINEARISE if result is not None else capi.WANT_ALL
             r = lib.eval(scene, q, capi.EVAL_LVS_CONTINUOUS, lvs=prm["lvs"], fixed=fixed, want=lin, **kw)
             r.rows()
             r2 = lib.eval(scene, q, capi.EVAL_LVS_CONTINUOUS, lvs=prm["lvs"], fixed=fixed,
-                          want=capi.WANT_COST | capi.WANT_CONTACTS, **kw)
+                          want=capi.WANT_COST | capi.WANT_CONTACTS, **kw2)
             r2.cost()
             return 1e3 * (time.perf_counter() - t0), r2.counts()["n_dense"]
         for _ in range(3):
@@ -132,6 +142,75 @@ def sqp_iteration_latency(cu, with_cpu):
             so = orc.scene(sc, prm["margin"], prm["coeff"], prm["buffer"])
             entry["cpu_port_1thread_ms"] = float(np.median([one(orc, so)[0] for _ in range(3)]))
         out[name] = entry
+    return out
+
+
+def other_configs(cu):
+    """The remaining SURVEY.md 8(d) lines, device-resident unless said otherwise (CUDA events around the passes, median of
+    5 after 3 warm-up passes; every pass after the first is speculative): C1 boxbot DISCRETE at B = 2^20 states (evals/s)
+    and B = 1 (us per pass, host buffers, wall clock), the LVS_DISCRETE term set of C4 (the "discrete" half of the
+    reference's discrete + cast costs), and one full SQP iteration of C2 with the host QP included (the in-repo ADMM
+    solver of tests/sqp.py standing in for OSQP, which is not installed here)."""
+    import torch
+    capi = pkg.capi
+    out = {}
+    box = ms_.load_scene("boxbot")
+    sb = cu.scene(box, 0.1, 1.0, 0.01)
+    rng = np.random.default_rng(1)
+
+    def timed(scene_h, q_np, evaluator, want, reps=5, **kw):
+        B, T = q_np.shape[0], q_np.shape[1]
+        qd = torch.from_numpy(q_np).cuda()
+        res = capi.Result(cu, scene_h, cu.new_result(scene_h), B, T)
+        st = torch.cuda.current_stream().cuda_stream
+        ts = []
+        for i in range(3 + reps):
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record()
+            cu.eval_device(scene_h, qd.data_ptr(), B, T, evaluator, res, stream=st, want=want, sync=False, **kw)
+            b.record()
+            cu.sync(res)
+            torch.cuda.synchronize()
+            if i >= 3:
+                ts.append(a.elapsed_time(b))
+        return float(np.median(ts)), res.counts()
+    q = rng.uniform(-2.2, 2.2, (1 << 20, 1, 2))
+    ms1, c1 = timed(sb, q, capi.EVAL_DISCRETE, capi.WANT_LINEARISE)
+    out["C1 boxbot DISCRETE B=2^20 (simple_collision_unit, 1 timestep per problem)"] = {
+        "ms_per_pass": ms1, "evals_per_s": c1["n_dense"] / (ms1 * 1e-3), "n_contacts": c1["n_contacts"]}
+    q1 = np.array([[[-0.9, 0.01]]])
+    r1 = capi.Result(cu, sb, cu.new_result(sb), 1, 1)
+    lat = []
+    for i in range(30):
+        t0 = time.perf_counter()
+        r = cu.eval(sb, q1, capi.EVAL_DISCRETE, want=capi.WANT_LINEARISE, result=r1)
+        r.rows()
+        lat.append(1e6 * (time.perf_counter() - t0))
+    out["C1 boxbot DISCRETE B=1"] = {"us_per_pass_host_buffers": float(np.median(lat[5:]))}
+    arm = ms_.load_scene("arm_around_table")
+    sa = cu.scene(arm, MARGIN, COEFF, BUFFER)
+    qa = make_batch(arm, 0, 4096)
+    ms2, c2 = timed(sa, qa, capi.EVAL_LVS_DISCRETE, capi.WANT_LINEARISE, lvs=LVS, fixed=fixed_steps())
+    out["C4 seeds, LVS_DISCRETE term set (discrete half of discrete + cast)"] = {
+        "ms_per_pass": ms2, "evals_per_s": c2["n_dense"] / (ms2 * 1e-3), "n_contacts": c2["n_contacts"]}
+    # one SQP iteration of C2 with the QP: linearisation pass + QP build and solve + one geometry pass at the trial point
+    from tests import sqp
+    prob = sqp.CollisionProblem(cu, arm, arm["seed_traj"], capi.EVAL_LVS_CONTINUOUS, MARGIN, COEFF, BUFFER, LVS)
+    x = prob.q0[1:-1].reshape(-1).copy()
+    prob.cost(x)
+    t_lin, t_qp, t_val = [], [], []
+    for _ in range(5):
+        t0 = time.perf_counter()
+        lin = prob.convexify(x)
+        t1 = time.perf_counter()
+        x_new, _, _ = prob.solve_model(x, lin, 0.1)
+        t2 = time.perf_counter()
+        prob.cost(x_new)
+        t3 = time.perf_counter()
+        t_lin.append(1e3 * (t1 - t0)), t_qp.append(1e3 * (t2 - t1)), t_val.append(1e3 * (t3 - t2))
+    out["C2 one SQP iteration with the host QP (in-repo ADMM, scipy; OSQP not installed)"] = {
+        "linearise_ms": float(np.median(t_lin)), "qp_ms": float(np.median(t_qp)), "value_pass_ms": float(np.median(t_val)),
+        "total_ms": float(np.median(t_lin) + np.median(t_qp) + np.median(t_val)), "rows": int(len(lin[1]))}
     return out
 
 
@@ -204,23 +283,18 @@ def run_ours(args, scene, rank, world, local_rank):
     pd = C.POINTER(C.c_double)
 
     def pick_best():
-        cu.check(cu.dll.tc_result_cost(res.handle, None, cost_traj.ctypes.data_as(pd)))
-        i = int(np.argmin(cost_traj))
-        if comm is None:
-            return float(cost_traj[i]), rank * B + i, 0
+        # arg-min over the per-trajectory costs on the device, record (cost, index, trajectory) exchanged with ONE
+        # all-gather on the evaluation's stream (a single rank just reads its record back): tc_result_allgather_best
         bc, bi, br = C.c_double(), C.c_int64(), C.c_int32()
-        cu.check(cu.dll.tc_allgather_best(C.c_double(cost_traj[i]), C.c_int64(rank * B + i), comm, C.c_int(world),
-                                          C.c_void_p(stream), C.byref(bc), C.byref(bi), C.byref(br)))
-        # the owner ships the winning trajectory to every rank (T x n_dof doubles)
-        win_traj[:] = q_host[i]
-        cu.check(cu.dll.tc_broadcast_trajectory(win_traj.ctypes.data_as(pd), C.c_size_t(win_traj.size), C.c_int(br.value),
-                                                comm, C.c_void_p(stream)))
+        cu.check(cu.dll.tc_result_allgather_best(res.handle, C.c_int64(rank * B), comm, C.c_int(world), C.byref(bc),
+                                                 C.byref(bi), C.byref(br), win_traj.ctypes.data_as(pd)))
         return bc.value, bi.value, br.value
 
     def step_device():
-        # want = cost + contacts + rows: the gradient vectors are folded into the CSR rows inside the pass
+        # want = cost + contacts + rows: the gradient vectors are folded into the CSR rows inside the pass.  The pass
+        # is only enqueued (speculative sizing after the first one); pick_best waits for it and for the all-gather
         cu.eval_device(sg, q_dev.data_ptr(), B, T_STEPS, capi.EVAL_LVS_CONTINUOUS, res, lvs=LVS, fixed=fixed,
-                       stream=stream, want=capi.WANT_LINEARISE)
+                       stream=stream, want=capi.WANT_LINEARISE, sync=False)
         return pick_best()
 
     def barrier():
@@ -237,10 +311,13 @@ def run_ours(args, scene, rank, world, local_rank):
     barrier()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     narrow_ms, launches, best = [], 0, None
+    rank_ms = []
     e0.record()
     for _ in range(args.steps):
         best = step_device()
-        narrow_ms.append(cu.stage_ms(res)[5])
+        st_ms = cu.stage_ms(res)
+        narrow_ms.append(st_ms[5])
+        rank_ms.append(st_ms[4])
         launches += cu.launches(res)[0]
     e1.record()
     barrier()
@@ -262,16 +339,21 @@ def run_ours(args, scene, rank, world, local_rank):
         csc_ms.append(a.elapsed_time(b))
 
     # ---- end to end through the C ABI with HOST buffers: H2D of q, D2H of rows + costs, every step.
-    # Sub-batches of 1024 seeds alternate between two streams so the D2H of one overlaps the kernels of the next
-    # (multistart.PipelinedEvaluator); each sub-batch is a plain tc_eval + tc_result_rows + tc_result_cost.
+    # tc_pipeline_eval_rows: sub-batches of --e2e-chunk seeds on a ring of --e2e-workers streams inside the library,
+    # compact rows (values + row value + link pair + term offsets) into pinned host arrays, one host thread.
     nd = sg.n_dof
-    pipe = ms_.PipelinedEvaluator(cu, sg, capi.EVAL_LVS_CONTINUOUS, LVS, fixed, nd, chunk=args.e2e_chunk,
-                                  n_workers=args.e2e_workers, concurrent=args.e2e_concurrent,
-                                  taper=bool(args.e2e_taper), compact=args.e2e_rows == "blocks")
+    tpt = T_STEPS - 1
+    pipe = capi.Pipeline(cu, sg, args.e2e_workers)
+    n_rows0, nnz0 = counts["n_contacts"], counts["nnz"]
+
+    def pinned(n, dt):
+        return torch.empty(int(n), dtype={np.int64: torch.int64, np.float64: torch.float64, np.int32: torch.int32}[dt]).pin_memory().numpy()
+    pipe.reserve(B, tpt, int(n_rows0 * 1.05) + 4096, int(nnz0 * 1.05) + 65536, alloc=pinned)
     q_np = q_pin.numpy()
 
     def step_e2e():
-        costs, n_rows, nnz_, _ = pipe.run(q_np)
+        n_rows, nnz_ = pipe.eval_rows(q_np, capi.EVAL_LVS_CONTINUOUS, LVS, fixed, args.e2e_chunk)
+        costs = pipe.out["cost"]
         i = int(np.argmin(costs))
         if comm is None:
             return (float(costs[i]), rank * B + i, 0), n_rows, nnz_
@@ -280,9 +362,10 @@ def run_ours(args, scene, rank, world, local_rank):
                                           C.c_void_p(stream), C.byref(bc), C.byref(bi), C.byref(br)))
         return (bc.value, bi.value, br.value), n_rows, nnz_
 
-    for _ in range(2):
+    for _ in range(3):
         best_e2e, nc, nnz = step_e2e()
     assert best_e2e[1] == best[1] or best_e2e[0] == best[0], (best_e2e, best)  # same winner as the resident path
+    assert nc == counts["n_contacts"] and nnz == counts["nnz"]
     barrier()
     t0 = time.perf_counter()
     for _ in range(args.steps):
@@ -290,15 +373,20 @@ def run_ours(args, scene, rank, world, local_rank):
     barrier()
     e2e_ms = 1e3 * (time.perf_counter() - t0) / args.steps
     pipe.close()
-    n_sub = -(-B // args.e2e_chunk) + (2 if args.e2e_taper else 0)
-    d2h = 8 * (nc + n_sub) + (8 * nnz + 8 * nc if args.e2e_rows == "blocks" else 12 * nnz) + 24 * nc + 8 * B
+    d2h = 8 * nnz + 12 * nc + 8 * B * tpt + 8 * B
     h2d = q_host.nbytes
 
-    t = torch.tensor([ms, e2e_ms], dtype=torch.float64, device="cuda")
+    t = torch.tensor([ms, e2e_ms, float(np.mean(rank_ms))], dtype=torch.float64, device="cuda")
+    tmin = torch.tensor([ms, e2e_ms, float(np.mean(rank_ms))], dtype=torch.float64, device="cuda")
     tot = torch.tensor([float(counts["n_dense"])], dtype=torch.float64, device="cuda")
     if dist is not None:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        dist.all_reduce(tmin, op=dist.ReduceOp.MIN)
         dist.all_reduce(tot, op=dist.ReduceOp.SUM)
+    # per-rank spread: step = pass + winner exchange (max over ranks is the reported time); pass_ms = the kernels of the
+    # pass alone.  step_max - pass_max is what the exchange and the waiting for the slowest rank cost
+    per_rank = {"step_ms_min": float(tmin[0]), "step_ms_max": float(t[0]), "pass_ms_min": float(tmin[2]),
+                "pass_ms_max": float(t[2]), "e2e_ms_min": float(tmin[1]), "e2e_ms_max": float(t[1])}
     ms, e2e_ms = float(t[0]), float(t[1])
     dense_total = float(tot[0])
     if rank == 0:
@@ -310,12 +398,17 @@ def run_ours(args, scene, rank, world, local_rank):
             peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
         except Exception:
             pass
-        traffic = None
-        try:
-            tr = json.load(open(os.path.join(ROOT, "profiles", "r1_traffic.json")))
-            traffic = sum(v["dram_bytes_per_launch"] for k, v in tr.items() if k.startswith(("k_gjk", "k_epa")))
-        except Exception:
-            pass
+        flops_exec = 5.0 * counts["support_compared"] + 280.0 * counts["gjk_iters"] + 400.0 * counts["epa_iters"]
+        traffic, traffic_src = None, None
+        for name in ("r2_traffic.json", "r1_traffic.json"):
+            try:
+                tr = json.load(open(os.path.join(ROOT, "profiles", name)))
+                traffic = sum(v["dram_bytes_per_launch"] for k, v in tr.items() if k.startswith(("k_gjk", "k_epa")))
+                traffic_src = f"ncu --set full capture committed as profiles/{name} (" + str(tr.get("_commit", "round 1 build")) + \
+                    "); not measured in this run"
+                break
+            except Exception:
+                pass
         base, _, _ = cpu_baseline(scene) if (world == 1 and not args.no_cpu_baseline) else ({"value": None, "unit": UNIT, "cores": 0,
                                                                             "kind": "port", "sample": "skipped"}, 0, 0)
         # HBM-bound rest of the pass (FK, broadphase, finalise, sort, gradients + rows, cost): algorithmic bytes of
@@ -326,6 +419,7 @@ def run_ours(args, scene, rank, world, local_rank):
                      counts["n_contacts"] * (176 + r_row))
         rest_ms = ms - nms
         latency = sqp_iteration_latency(cu, with_cpu=not args.no_cpu_baseline) if world == 1 else None
+        others = other_configs(cu) if world == 1 else None
         out = {
             "metric": METRIC, "value": dense_total / (ms * 1e-3), "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": max(3, args.warmup), "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
@@ -338,13 +432,19 @@ def run_ours(args, scene, rank, world, local_rank):
                              (counts["n_states"] * (14 * 96 + 14 * 48) / 1e9)},
             "e2e": {"value": dense_total / (e2e_ms * 1e-3), "unit": UNIT, "ms_per_step": e2e_ms,
                     "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
-                    "how": f"{args.e2e_workers} streams x sub-batches of {args.e2e_chunk} seeds ({args.e2e_concurrent} computing at a "
-                           f"time{', last one tapered' if args.e2e_taper else ''}), rows as {args.e2e_rows}, pinned host buffers, "
-                           "wall clock around the whole batch"},
+                    "how": f"tc_pipeline_eval_rows: sub-batches of {args.e2e_chunk} seeds (last one tapered) on a ring of "
+                           f"{args.e2e_workers} streams inside the library, one host thread, compact rows (values, row value, "
+                           "link pair, term offsets) into pinned host arrays, wall clock around the whole batch"},
+            "per_rank": per_rank,
             "gpu_launches": launches, "library_calls_per_step": cu.launches(res)[1],
             "roofline": {"bound": "fp64", "kernel": "narrow phase: k_gjk<double> + k_epa_wp<double> (2 launches)", "achieved": flops / (nms * 1e-3) / 1e12,
                          "peak": peak64, "unit": "TFLOP/s", "frac": flops / (nms * 1e-3) / 1e12 / peak64,
-                         "traffic": traffic, "peak_source": "DFMA loop measured in this run (tc_measure_fma_peak)",
+                         "frac_executed": flops_exec / (nms * 1e-3) / 1e12 / peak64,
+                         "frac_note": "frac counts 5 flop per vertex of every queried hull (the reference's plain scan, "
+                                      "SURVEY 8(d)); frac_executed counts the vertices the look-up tables left to compare",
+                         "executed_flops_per_launch": flops_exec,
+                         "traffic": traffic, "traffic_source": traffic_src,
+                         "peak_source": "DFMA loop measured in this run (tc_measure_fma_peak)",
                          "kernel_ms": nms, "algorithmic_flops_per_launch": flops,
                          "hbm_peak_gbs": peaks.get("hbm_gbs")},
             "roofline_hbm": {"bound": "hbm", "kernel": "everything but the narrow phase (FK, broadphase, finalise, sort, "
@@ -357,9 +457,10 @@ def run_ours(args, scene, rank, world, local_rank):
                        "all rows assembled on the device in CSC form (3 kernels), outside the timed step",
                        "nnz": int(counts["nnz"] + counts["n_contacts"])},
             "sqp_iteration_ms": latency,
+            "other_configs": others,
             "cpu_baseline": base,
             "counters": {k: counts[k] for k in ("n_dense", "n_units", "n_narrowphase", "n_contacts", "gjk_iters",
-                                                "epa_iters", "n_epa", "support_verts", "n_unconverged")},
+                                                "epa_iters", "n_epa", "support_verts", "support_compared", "n_unconverged")},
             "stage_ms": {"plan_fk": stage[0], "broadphase": stage[6], "narrow_kernels": stage[5], "gjk_kernel": stage[8],
                          "epa_kernel": stage[9], "deep_epa": stage[2],
                          "finalize_sort_rows": stage[3], "eval_total": stage[4]},
@@ -388,13 +489,7 @@ def main():
     ap.add_argument("--seeds", type=int, default=4096, help="trajectories per GPU")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--e2e-chunk", type=int, default=1024, help="seeds per sub-batch of the host-buffer (e2e) leg")
-    ap.add_argument("--e2e-workers", type=int, default=3, help="streams / host threads of the e2e leg")
-    ap.add_argument("--e2e-concurrent", type=int, default=2, help="sub-batches allowed to compute at the same time")
-    ap.add_argument("--e2e-rows", default="blocks", choices=["blocks", "csr"],
-                    help="form in which the rows reach the host: block form (tc_result_rows_blocks: first column of the "
-                         "T0 / T1 run per row) or full CSR with one column index per non-zero (tc_result_rows)")
-    ap.add_argument("--e2e-taper", type=int, default=1, help="cut the last sub-batch into 1/2 + 1/4 + 1/4 (its download "
-                    "is the part nothing overlaps)")
+    ap.add_argument("--e2e-workers", type=int, default=3, help="streams (ring slots) of the e2e leg")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))

@@ -95,8 +95,10 @@ enum {
  * (trajopt/src/problem_description.cpp:1669-1673; trajopt_common/include/trajopt_common/collision_types.h:113).
  * ALL is 0 here so that a zero-initialised tc_eval_desc keeps the reference's default.
  *   ALL      every contact of every shape pair
- *   CLOSEST  per tested state (or sweep) and LINK pair only the contact with the smallest distance (first in
- *            shape-pair order on ties), chosen BEFORE the evaluator's own filters, as the manager does
+ *   CLOSEST  per tested state (or sweep) and LINK pair only the contact with the smallest distance, chosen BEFORE the
+ *            evaluator's own filters, as the manager does; results within 1e-9 m of the smallest count as tied and
+ *            the first of them in shape-pair order is taken (sub-shapes of a compound link share faces, so exact
+ *            ties are common and the manager's strict "closer" would be decided by the last bit)
  *   FIRST    per tested state (or sweep) one contact: the manager stops at the first one it finds; tesseract's order
  *            is that of Bullet's broadphase, here it is the first in (link pair, shape pair) order */
 enum { TC_CONTACT_ALL = 0, TC_CONTACT_CLOSEST = 1, TC_CONTACT_FIRST = 2 };
@@ -247,11 +249,23 @@ void tc_result_destroy(tc_result* res);
  * before returning, so the accessors below can be called right away. */
 int tc_eval(tc_scene* scene, const tc_eval_desc* desc, const double* q, int32_t B, int32_t T,
             tc_result* out, void* cuda_stream);
-/* Asynchronous variant used by benchmarks: enqueues everything, returns without synchronising.
- * tc_result_sync() must be called before any accessor. */
+/* Asynchronous variant: enqueues the pass and returns; tc_result_sync() must be called before any accessor and before
+ * the next evaluation on the same result, and q (host or device) must stay valid until then.
+ * How far the call itself blocks depends on the pass (csrc/tc_api.cu runEval):
+ *   - the FIRST pass on a result, and any pass whose shape differs from the previous one (B, T, evaluator, options,
+ *     fixed steps), sizes its arenas from the device's counts stage by stage: five stream synchronisations inside
+ *     the call, possibly cudaMalloc;
+ *   - every later pass of the same shape is SPECULATIVE: arenas and grids come from the previous pass's counts plus
+ *     1/8 slack, the kernels read the actual counts on the device, and the call returns after ~30 launches without
+ *     touching the stream's progress.  If a count outgrows its capacity the device raises a flag, the remaining
+ *     kernels leave at once, and tc_result_sync() repeats the pass with exact sizes (tc_result_pass_info tells).
+ * The per-iteration call pattern this serves: trajopt_sco/src/optimizers.cpp:194-203. */
 int tc_eval_async(tc_scene* scene, const tc_eval_desc* desc, const double* q, int32_t B, int32_t T,
                   tc_result* out, void* cuda_stream);
 int tc_result_sync(tc_result* res);
+/* how the last pass ran: speculative = sized from the previous pass (no read-back inside the call), repeated = number of
+ * passes on this result that had to be repeated exactly because a count outgrew its predicted capacity */
+int tc_result_pass_info(const tc_result* res, int32_t* speculative, int32_t* repeated);
 
 /* ---- seam B3: the contact manager itself.  What a tesseract_collision contact-manager plugin does between
  * setCollisionObjectsTransform and contactTest (trajopt/src/collision_terms.cpp:616-625,665-667,887-889,1132-1134;
@@ -340,6 +354,31 @@ int tc_result_cost(const tc_result* res, double* cost_per_term, double* cost_per
 /* device pointer to cost_per_traj[B] (stays on the GPU for multi-start selection) */
 int tc_result_cost_device(const tc_result* res, const double** dev_ptr);
 
+/* ---- host-buffer pass over a large batch, pipelined inside the library.
+ * The consumer of the rows is the unchanged host QP build (trajopt_optimizers/trajopt_sqp/src/trajopt_qp_problem.cpp:
+ * 720-973 / trajopt_sco/src/osqp_interface.cpp:213-280), so a batched linearisation ends with hundreds of MB going
+ * device -> host.  tc_pipeline_eval_rows cuts the batch into sub-batches of `chunk` trajectories (the last one tapered
+ * 1/2 + 1/4 + 1/4: its download is the part nothing overlaps), evaluates them on a ring of streams with speculative
+ * passes (tc_eval_async) and starts the download of sub-batch j while j + 1 computes — one host thread, no
+ * allocation in steady state.  Rows arrive in COMPACT form, the fewest bytes that determine them:
+ *   term_ptr[B * terms_per_traj + 1]  first row of every (trajectory, term); terms_per_traj follows from T, the
+ *                                     evaluator and fixed_steps exactly as in tc_eval
+ *   val[nnz]                          row i = nb * n_dof values (T0 block, then T1 block; nb = free blocks of its term),
+ *                                     rows back to back in row order -> the offset of a row follows from term_ptr
+ *   row_value[n_rows], row_pair[n_rows]  as tc_result_rows' row_value and the index into tc_scene_pairs (margin and
+ *                                     coefficient of a row are those of its link pair: 4 bytes instead of 16)
+ *   cost_per_traj[B]
+ * (124 bytes per two-block row against 152 of tc_result_rows_blocks and 180 of tc_result_rows.)  All output arrays
+ * are host memory, pinned for the copies to be asynchronous; val_cap / row_cap are their capacities in elements
+ * (TC_ERR_OVERFLOW when a sub-batch would not fit).  q[B][T][n_dof] is host memory (pinned: read by a kernel through
+ * the mapping; pageable: staged by the runtime).  desc->want is ignored (cost + contacts + rows). */
+typedef struct tc_pipeline tc_pipeline;
+int tc_pipeline_create(tc_scene* scene, int32_t n_slots, tc_pipeline** out);
+void tc_pipeline_destroy(tc_pipeline* pipe);
+int tc_pipeline_eval_rows(tc_pipeline* pipe, const tc_eval_desc* desc, const double* q, int32_t B, int32_t T, int32_t chunk,
+                          int64_t* term_ptr, double* val, size_t val_cap, double* row_value, int32_t* row_pair,
+                          size_t row_cap, double* cost_per_traj, int64_t* n_rows, int64_t* nnz);
+
 /* ---- allocation-free entry point.  It has NO counterpart in the reference: it was added
  * for callers that cannot call cudaMalloc (CUDA graph capture, tight serving loops, harnesses that
  * forbid it).  Same arithmetic as tc_result_cost's per-trajectory output, over caller-owned DEVICE arrays:
@@ -371,6 +410,16 @@ int tc_allgather_best(double local_best_cost, int64_t local_best_idx, void* nccl
 /* the owner of the winning seed (best_rank) ships its trajectory traj[n_values] (host memory, T * n_dof doubles) to
  * every rank: one ncclBroadcast; on return every rank's buffer holds the root's values */
 int tc_broadcast_trajectory(double* traj, size_t n_values, int root_rank, void* nccl_comm, void* cuda_stream);
+
+/* The two calls above in one, fed from the device: the cheapest trajectory of `res` (arg-min over its per-trajectory
+ * costs, lowest index on ties; the evaluation must have run with TC_WANT_COST) is packed with its joint values on the
+ * device, all ranks exchange their records with ONE ncclAllGather ((2 + T * n_dof) * 8 bytes per rank) on the result's
+ * stream and pick the global winner (lowest rank on ties): no host-side cost array, no second collective, one stream
+ * synchronisation, no cudaMalloc.  index_offset = global index of this rank's first trajectory.  best_traj
+ * [T * n_dof] (host) receives the winner's joint values on every rank; may be NULL.  n_ranks == 1 (nccl_comm may be
+ * NULL) just reads this rank's winner back.  A pending tc_eval_async is waited for first. */
+int tc_result_allgather_best(tc_result* res, int64_t index_offset, void* nccl_comm, int n_ranks, double* best_cost,
+                             int64_t* best_idx, int32_t* best_rank, double* best_traj);
 
 /* ---- measurement helpers (bench only) ---- */
 /* register-resident DFMA / FFMA loop: returns achieved TFLOP/s (2 flop per FMA) */

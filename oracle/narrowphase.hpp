@@ -372,6 +372,7 @@ struct EpaResult
 
 constexpr double EPA_TOL = 1e-10;
 constexpr int EPA_MAX_ITERS = 255;
+constexpr int EPA_STALL_TRIPS = 6;
 
 inline EpaResult epa(const Placed& A, const Placed& B, const Simplex& start)
 {
@@ -528,6 +529,13 @@ inline EpaResult epa(const Placed& A, const Placed& B, const Simplex& start)
   addFace(0, 2, 3, true);
   addFace(1, 2, 3, true);
 
+  // On a curved core (cylinder, cone) the new vertices crowd on the surface, the faces turn into slivers whose plane
+  // distance carries ~1e-10 m of rounding, and a few items dither at the tolerance for a hundred trips.  Stall exit:
+  // EPA_STALL_TRIPS trips without narrowing the bracket between the closest face and the smallest support value by 10 %
+  // end the expansion on the current closest face.  Polytope pairs never take it (finite termination).
+  const bool stall_exit = A.shape->type >= CYLINDER || B.shape->type >= CYLINDER;
+  double ub_best = DBL_MAX, width_best = DBL_MAX;
+  int stall = 0;
   int best = -1;
   for (r.iters = 1; r.iters <= EPA_MAX_ITERS; ++r.iters)
   {
@@ -537,8 +545,24 @@ inline EpaResult epa(const Placed& A, const Placed& B, const Simplex& start)
         best = static_cast<int>(f);
     const Face bf = faces[static_cast<std::size_t>(best)];
     const Vtx x = sup(bf.n);
-    if (dot(bf.n, x.w) - bf.d <= EPA_TOL)
+    const double sv = dot(bf.n, x.w);
+    if (sv - bf.d <= EPA_TOL)
       break;
+    if (stall_exit)
+    {
+      // stall exit on curved cores (see EPA_STALL_TRIPS): the bracket [closest face, smallest support value] has not
+      // narrowed by 10 % for EPA_STALL_TRIPS trips -> the sliver faces are dithering at their rounding level
+      if (sv < ub_best)
+        ub_best = sv;
+      const double width = ub_best - bf.d;
+      if (width < 0.9 * width_best)
+      {
+        width_best = width;
+        stall = 0;
+      }
+      else if (++stall >= EPA_STALL_TRIPS)
+        break;
+    }
     if (r.iters == EPA_MAX_ITERS)
     {
       r.converged = false;

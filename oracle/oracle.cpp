@@ -360,8 +360,9 @@ static void calculateContinuousData(Contact& col, const Shape& sh, const Pose& t
 // poses1 == nullptr -> discrete manager; otherwise cast manager (active links swept pose0 -> pose1).
 // `type`: tesseract::collision::ContactTestType as include/trajopt_cuda.h numbers it (TC_CONTACT_*): CLOSEST keeps,
 // per link pair, the result with the smallest distance (processResult replaces the stored one only when the new one is
-// strictly closer [upstream, recalled]); FIRST ends the whole test at the first result (cdata.done) — tesseract's
+// strictly closer [upstream, recalled]; ties inside CLOSEST_TIE go to the first, see below); FIRST ends the whole test at the first result (cdata.done) — tesseract's
 // visiting order is Bullet's broadphase order, here the (link pair, shape pair) order of the scene.
+constexpr double CLOSEST_TIE = 1e-9;  // [m]
 static void contactTest(const Scene& s, const std::vector<Pose>& poses0, const std::vector<Pose>* poses1,
                         ContactResultMap& out, Stats& st, int type = TC_CONTACT_ALL)
 {
@@ -462,16 +463,29 @@ static void contactTest(const Scene& s, const std::vector<Pose>& poses0, const s
         if (PB.cast)
           calculateContinuousData(c, B, PB.pose0, PB.pose1, d.pb, -d.normal, 1);
       }
-      std::vector<Contact>& dst = out[static_cast<int>(pi)];
-      if (type == TC_CONTACT_CLOSEST && !dst.empty())
-      {
-        if (c.c.distance < dst[0].c.distance)
-          dst[0] = c;
-      }
-      else
-        dst.push_back(c);
+      out[static_cast<int>(pi)].push_back(c);
       if (type == TC_CONTACT_FIRST)
         return;
+    }
+    if (type == TC_CONTACT_CLOSEST)
+    {
+      // Sub-shapes of a compound link often share faces, so two shape pairs report the SAME distance and the strict
+      // "replace when closer" of the manager is decided by the last bit.  Stated rule: the first result, in shape-pair
+      // order, within CLOSEST_TIE of the smallest distance (identical to the manager's outside that band).
+      auto it = out.find(static_cast<int>(pi));
+      if (it != out.end() && it->second.size() > 1)
+      {
+        double dmin = it->second[0].c.distance;
+        for (const Contact& c : it->second)
+          dmin = std::min(dmin, c.c.distance);
+        for (const Contact& c : it->second)
+          if (c.c.distance <= dmin + CLOSEST_TIE)
+          {
+            const Contact keep = c;
+            it->second.assign(1, keep);
+            break;
+          }
+      }
     }
   }
 }

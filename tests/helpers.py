@@ -13,7 +13,7 @@ import tcb200  # noqa: E402
 
 pkg = tcb200.load()
 capi = pkg.capi
-SCENES = os.path.join(ROOT, "tests", "golden", "scenes")
+SCENES = os.path.join(ROOT, "trajopt-1_b200", "data", "scenes")
 _pd = C.POINTER(C.c_double)
 
 
@@ -92,7 +92,7 @@ def contact_keys(c):
                     c["shape_id"][:, 0].tolist(), c["shape_id"][:, 1].tolist()))
 
 
-def compare(ro, rg, band=1e-9, want_rows=True):
+def compare(ro, rg, band=1e-9, want_rows=True, scene=None):
     """Parity report oracle result `ro` vs CUDA result `rg` (same scene, same inputs).
 
     Contacts are matched by (traj, term, link pair, substep, shape ids).  Contacts whose oracle distance
@@ -134,6 +134,12 @@ def compare(ro, rg, band=1e-9, want_rows=True):
     xo, xg = ro.contact_transforms()[a], rg.contact_transforms()[b]
     rep["max_transform_err"] = float(np.abs(xo - xg).max())
     same_cc = ~(A["cc_type"] != G["cc_type"]).any(axis=1)
+    if scene is not None:
+        # contacts inside the stated band of the continuous-contact decisions may differ in cc_type / cc_time, and
+        # with them in everything scaled by cc_time; outside the band nothing may (cc_outside_band must be 0)
+        out, ins, keys_in = cc_band_check(ro, rg, scene)
+        rep["cc_outside_band"], rep["cc_inside_band"] = out, ins
+        same_cc &= ~np.isin(packed_keys(A), keys_in)
     if want_rows:
         reco, go = ro.gradients()
         recg, gg = rg.gradients()
@@ -149,8 +155,9 @@ def compare(ro, rg, band=1e-9, want_rows=True):
             assert len(vo) == len(vg)
             assert (rowo["col_idx"][rowo["row_ptr"][i]:rowo["row_ptr"][i + 1]] ==
                     rowg["col_idx"][rowg["row_ptr"][j]:rowg["row_ptr"][j + 1]]).all()
-            if len(vo) and not (A["cc_type"][np.where(a == i)[0][0]] != G["cc_type"][np.where(a == i)[0][0]]).any():
-                worst = max(worst, float(np.abs(vo - vg).max() / max(np.abs(vo).max(), 1e-12)))
+            if len(vo) and same_cc[np.where(a == i)[0][0]]:
+                # rows scaled by (1 - cc_time) ~ 1e-9 are numerically zero: floor the denominator well above rounding
+                worst = max(worst, float(np.abs(vo - vg).max() / max(np.abs(vo).max(), 1e-9)))
             worst_v = max(worst_v, abs(float(rowo["value"][i] - rowg["value"][j])))
         rep["max_row_rel_err"] = worst
         rep["max_row_value_err"] = worst_v
@@ -337,13 +344,16 @@ def check_invariants(r, sg, q, evaluator, lvs, fixed, margin_buffer, stack=capi.
     return c
 
 
-# ---- the stated band of the cc_type decision ----
-# calculateContinuousData decides TIME0 / TIME1 / BETWEEN by comparing the support values of the shape at its two end
-# poses against BULLET_SUPPORT_FUNC_TOLERANCE = 0.01, after GetAverageSupport has averaged the hull vertices within
-# BULLET_EPSILON = 1e-3 of the running maximum.  Both are discrete decisions on continuous quantities: a contact whose
-# quantity lies within CC_BAND of one of those thresholds may legitimately be classified differently by two
-# implementations whose arithmetic differs in the last bits.  Outside the band the classes must agree.
-CC_BAND = 1e-9
+# ---- the stated band of the continuous-contact decisions ----
+# calculateContinuousData is a chain of DISCRETE decisions on continuous quantities: GetAverageSupport averages the hull
+# vertices whose support value lies within BULLET_EPSILON = 1e-3 of the running maximum (a vertex is in or out), the
+# classes TIME0 / TIME1 / BETWEEN follow from comparing the two support values against BULLET_SUPPORT_FUNC_TOLERANCE =
+# 0.01, and cc_time switches to 0.5 below BULLET_LENGTH_TOLERANCE = 0.001.  Across any of those thresholds cc_type /
+# cc_time jump, so two implementations whose contact normals agree only to the stated 1e-5 can legitimately land on
+# different sides.  Stated band: a contact whose decisive quantity (a support value in metres, or the length sum) lies
+# within CC_BAND of its threshold may differ in cc_type / cc_time (and in the rows scaled by them); outside the band
+# they must agree.  CC_BAND = 1e-5 x 0.1 m: the normal tolerance times a typical vertex distance.
+CC_BAND = 1e-6
 
 
 def _avg_support_margin(verts, nl):
@@ -363,37 +373,49 @@ def _avg_support_margin(verts, nl):
     return mx, acc / cnt, closest
 
 
-def cc_type_outside_band(ro, rg, scene, band=CC_BAND):
-    """number of common contacts whose cc_type differs between the two results although every decision that leads to
-    the class is farther than `band` from its threshold (must be 0); also returns the number of mismatches"""
+def cc_decision_margin(c, xf, scene):
+    """smallest distance [m] of the continuous-contact decisions of contact record `c` (transforms xf[2][2][12]) to
+    their thresholds, over its swept hull links; inf when no decision is involved (cc_type NONE / primitives)"""
+    shape_pose = np.asarray(scene["shape_pose"], dtype=np.float64).reshape(-1, 3, 4)
+    allv = np.asarray(scene["verts"], dtype=np.float64).reshape(-1, 3)
+    margin = np.inf
+    for i in range(2):
+        if c["cc_type"][i] == capi.CC_NONE:
+            continue
+        sel = np.nonzero((scene["shape_link"] == c["link_ids"][i]) & (scene["shape_id"] == c["shape_id"][i]))[0]
+        if len(sel) != 1 or scene["shape_type"][sel[0]] != capi.SHAPE_HULL:
+            continue
+        k = sel[0]
+        v = allv[scene["shape_vert_offset"][k]:scene["shape_vert_offset"][k] + scene["shape_vert_count"][k]]
+        v = v @ shape_pose[k][:, :3].T + shape_pose[k][:, 3]
+        n = np.array(c["normal"]) * (1.0 if i == 0 else -1.0)
+        T0, T1 = xf[i, 0].reshape(3, 4), xf[i, 1].reshape(3, 4)
+        s0, p0, m0 = _avg_support_margin(v, T0[:, :3].T @ n)
+        s1, p1, m1 = _avg_support_margin(v, T1[:, :3].T @ n)
+        pw0, pw1 = T0[:, :3] @ p0 + T0[:, 3], T1[:, :3] @ p1 + T1[:, 3]
+        sup0, sup1 = float(n @ pw0), float(n @ pw1)
+        pt = np.array(c["nearest_points"][i])
+        lsum = np.linalg.norm(pt - pw0) + np.linalg.norm(pt - pw1)
+        margin = min(margin, m0, m1, abs(abs(sup0 - sup1) - 0.01), abs(lsum - 0.001))
+    return margin
+
+
+def cc_band_check(ro, rg, scene, band=CC_BAND, cc_time_tol=1e-6):
+    """Common contacts whose cc_type or cc_time differ between the two results: returns (number outside the stated
+    band — must be 0 —, number inside it, keys of the in-band ones)"""
     co, cg = ro.contacts(), rg.contacts()
     _, a, b = np.intersect1d(packed_keys(co), packed_keys(cg), assume_unique=True, return_indices=True)
     A, G = co[a], cg[b]
-    bad_rows = np.nonzero((A["cc_type"] != G["cc_type"]).any(axis=1))[0]
-    if len(bad_rows) == 0:
-        return 0, 0
+    differ = (A["cc_type"] != G["cc_type"]).any(axis=1) | (np.abs(A["cc_time"] - G["cc_time"]).max(axis=1) > cc_time_tol)
+    rows = np.nonzero(differ)[0]
+    if len(rows) == 0:
+        return 0, 0, np.zeros(0, np.int64)
     xf = ro.contact_transforms()[a]
-    shape_pose = np.asarray(scene["shape_pose"], dtype=np.float64).reshape(-1, 3, 4)
-    outside = 0
-    for r in bad_rows:
-        c = A[r]
-        ok = False
-        for i in range(2):
-            if c["cc_type"][i] == G[r]["cc_type"][i]:
-                continue
-            sel = np.nonzero((scene["shape_link"] == c["link_ids"][i]) & (scene["shape_id"] == c["shape_id"][i]))[0]
-            if len(sel) != 1 or scene["shape_type"][sel[0]] != capi.SHAPE_HULL:
-                continue
-            k = sel[0]
-            v = np.asarray(scene["verts"], dtype=np.float64).reshape(-1, 3)
-            v = v[scene["shape_vert_offset"][k]:scene["shape_vert_offset"][k] + scene["shape_vert_count"][k]]
-            v = v @ shape_pose[k][:, :3].T + shape_pose[k][:, 3]
-            n = np.array(c["normal"]) * (1.0 if i == 0 else -1.0)
-            T0, T1 = xf[r, i, 0].reshape(3, 4), xf[r, i, 1].reshape(3, 4)
-            s0, p0, m0 = _avg_support_margin(v, T0[:, :3].T @ n)
-            s1, p1, m1 = _avg_support_margin(v, T1[:, :3].T @ n)
-            sup0, sup1 = float(n @ (T0[:, :3] @ p0 + T0[:, 3])), float(n @ (T1[:, :3] @ p1 + T1[:, 3]))
-            if min(m0, m1, abs(abs(sup0 - sup1) - 0.01)) <= band:
-                ok = True
-        outside += 0 if ok else 1
-    return outside, len(bad_rows)
+    inside = [r for r in rows if cc_decision_margin(A[r], xf[r], scene) <= band]
+    return len(rows) - len(inside), len(inside), packed_keys(A[np.array(inside, dtype=np.int64)]) if inside else np.zeros(0, np.int64)
+
+
+def cc_type_outside_band(ro, rg, scene, band=CC_BAND):
+    """(mismatches of cc_type / cc_time outside the stated band — must be 0 —, mismatches inside it)"""
+    out, ins, _ = cc_band_check(ro, rg, scene, band)
+    return out, ins

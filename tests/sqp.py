@@ -134,7 +134,7 @@ class CollisionProblem:
 def optimize(prob, max_iter=50, trust_box=0.1, improve_ratio_threshold=0.25, min_trust_box=1e-4, min_approx_improve=1e-4,
              trust_shrink=0.1, trust_expand=1.5, log=None):
     """BasicTrustRegionSQP::optimize for a cost-only problem (no penalty iterations)"""
-    x = prob.q0[1:-1].reshape(-1).copy()
+    x = prob.x0() if hasattr(prob, "x0") else prob.q0[1:-1].reshape(-1).copy()
     old = prob.cost(x)
     status = "iteration limit"
     for it in range(max_iter):
@@ -164,3 +164,60 @@ def optimize(prob, max_iter=50, trust_box=0.1, improve_ratio_threshold=0.25, min
             status = "converged: trust region below minimum"
             break
     return prob.traj(x), old, status
+
+
+class SingleStateProblem:
+    """trajopt_common/data/config/simple_collision_test.json (trajopt/test/simple_collision_unit.cpp:62-124): ONE
+    timestep of spherebot, a joint-position cost towards `target`, a DISCRETE collision cost (dist_pen 0.3, coeff 1) and a
+    DISCRETE collision constraint (dist_pen 0.2, coeff 1).  BasicTrustRegionSQP turns the constraint into an l1 penalty
+    with merit coefficient mu (merit_error_coeff, 10 at the start: trajopt_sco/include/trajopt_sco/optimizers.hpp:92-125);
+    here mu is fixed, which is exact once it exceeds the multiplier.  Same interface as CollisionProblem."""
+
+    def __init__(self, lib, scene, q_init, target=(0.0, 0.0), mu=10.0, buffer=0.05):
+        self.lib, self.q0 = lib, np.array(q_init, dtype=np.float64).reshape(1, -1)
+        self.n = self.q0.shape[1]
+        self.target = np.asarray(target, dtype=np.float64)
+        self.terms = [(lib.scene(scene, 0.3, 1.0, buffer), 1.0), (lib.scene(scene, 0.2, 1.0, buffer), mu)]
+        lim = scene["joint_limits"]
+        self.lo, self.hi = lim[:, 0].copy(), lim[:, 1].copy()
+        self.passes = 0
+
+    def x0(self):
+        return self.q0.reshape(-1).copy()
+
+    def traj(self, x):
+        return x.reshape(1, self.n).copy()
+
+    def _eval(self, sc, x, want):
+        self.passes += 1
+        return self.lib.eval(sc, x.reshape(1, 1, self.n), capi.EVAL_DISCRETE, stack=capi.STACK_LEGACY, want=want)
+
+    def cost(self, x):
+        c = float(((x - self.target) ** 2).sum())
+        for sc, w in self.terms:
+            c += w * float(self._eval(sc, x, capi.WANT_COST | capi.WANT_CONTACTS).cost()[1][0])
+        return c
+
+    def convexify(self, x):
+        A, const, margin, coeff = [], [], [], []
+        for sc, w in self.terms:
+            rows = self._eval(sc, x, capi.WANT_ALL).rows()
+            m = len(rows["value"])
+            A.append(sp.csr_matrix((rows["val"], rows["col_idx"], rows["row_ptr"]), shape=(m, self.n)))
+            const.append(rows["value"]), margin.append(rows["margin"]), coeff.append(w * rows["coeff"])
+        return sp.vstack(A).tocsr(), np.concatenate(const), np.concatenate(margin), np.concatenate(coeff)
+
+    def solve_model(self, x, lin, box):
+        Ad, const, margin, coeff = lin
+        n, m = self.n, len(const)
+        P = sp.block_diag([2 * sp.identity(n), sp.csr_matrix((m, m))], format="csc")
+        qv = np.concatenate([-2 * self.target, np.ones(m)])
+        A = sp.vstack([sp.hstack([sp.diags(coeff) @ Ad, sp.identity(m)]),
+                       sp.hstack([sp.csr_matrix((m, n)), sp.identity(m)]),
+                       sp.hstack([sp.identity(n), sp.csr_matrix((n, m))])], format="csc")
+        l = np.concatenate([coeff * (margin - const), np.zeros(m), np.maximum(x - box, self.lo)])
+        u = np.concatenate([np.full(2 * m, np.inf), np.minimum(x + box, self.hi)])
+        z, iters = solve_qp(P, qv, A, l, u)
+        x_new = z[:n]
+        hinge = np.maximum(coeff * (margin - (const + Ad @ x_new)), 0.0)
+        return x_new, float(((x_new - self.target) ** 2).sum()) + float(hinge.sum()), iters

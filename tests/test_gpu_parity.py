@@ -253,3 +253,91 @@ def test_curved_obstacles_on_a_revolute_arm(cuda, oracle, evaluator):
     curved = np.isin(ro.contacts()["link_ids"][:, 1], np.nonzero(np.char.startswith(s["link_names"].astype(str), "curved"))[0])
     assert curved.sum() > 30, (rep, int(curved.sum()))
     check(rep)
+
+
+def test_speculative_pass_equals_exact_pass(cuda):
+    """A result's second pass of the same shape is sized from its first (no read-back inside the call).  Whatever the
+    new iterate does to the counts — more contacts than predicted (device flag, exact repeat inside tc_result_sync) or
+    fewer — contacts and rows are bit-identical to those of a fresh result evaluated exactly."""
+    s = helpers.load_scene("arm_around_table")
+    sg = cuda.scene(s, 0.025, 20.0, 0.01)
+    ms = helpers.pkg.multistart
+    calm = np.repeat(s["seed_traj"][None], 16, 0)              # the fixture path: few contacts
+    wild = ms.make_batch(s, 900, 16, t_steps=calm.shape[1])    # sigma 0.3 rad around it: many more
+    fixed = np.zeros(calm.shape[1], np.uint8)
+    fixed[0] = fixed[-1] = 1
+    res = capi.Result(cuda, sg, cuda.new_result(sg), 16, calm.shape[1])
+    seq = [calm, wild, wild, calm, calm]
+    want_spec = [False, True, True, True, True]
+    want_rep = [0, 1, 1, 1, 1]
+    for q, ws, wr in zip(seq, want_spec, want_rep):
+        r = cuda.eval(sg, q, capi.EVAL_LVS_CONTINUOUS, lvs=0.02, fixed=fixed, want=capi.WANT_LINEARISE, result=res)
+        spec, rep = cuda.pass_info(res)
+        assert rep == wr and (spec == ws or rep == wr), (spec, rep, ws, wr)
+        fresh = cuda.eval(sg, q, capi.EVAL_LVS_CONTINUOUS, lvs=0.02, fixed=fixed, want=capi.WANT_LINEARISE)
+        a, b = r.contacts(), fresh.contacts()
+        assert len(a) == len(b) and a.tobytes() == b.tobytes()
+        ra, rb = r.rows(), fresh.rows()
+        for k in ("row_ptr", "col_idx", "val", "value"):
+            assert np.array_equal(ra[k], rb[k]), k
+        ca, cb = r.counts(), fresh.counts()
+        assert all(ca[k] == cb[k] for k in ca if k != "overflow"), (ca, cb)
+    assert cuda.pass_info(res)[1] >= 1  # the wilder iterate outgrew the prediction at least once
+
+
+def test_eval_async_returns_before_the_stream_is_idle(cuda):
+    """tc_eval_async on a warmed-up result only enqueues: right after it returns the stream still has work"""
+    import torch
+    s = helpers.load_scene("arm_around_table")
+    sg = cuda.scene(s, 0.025, 20.0, 0.01)
+    ms = helpers.pkg.multistart
+    B = 1024
+    q = torch.from_numpy(ms.make_batch(s, 0, B)).cuda()
+    res = capi.Result(cuda, sg, cuda.new_result(sg), B, ms.T_STEPS)
+    stream = torch.cuda.Stream()
+    kw = dict(lvs=ms.LVS, fixed=ms.fixed_steps(), stream=stream.cuda_stream, want=capi.WANT_LINEARISE)
+    torch.cuda.synchronize()
+    cuda.eval_device(sg, q.data_ptr(), B, ms.T_STEPS, capi.EVAL_LVS_CONTINUOUS, res, **kw)  # exact pass, synchronised
+    busy = 0
+    for _ in range(3):
+        cuda.eval_device(sg, q.data_ptr(), B, ms.T_STEPS, capi.EVAL_LVS_CONTINUOUS, res, sync=False, **kw)
+        busy += 0 if stream.query() else 1
+        cuda.sync(res)
+        assert cuda.pass_info(res) == (True, 0)
+    assert busy == 3, busy
+    assert res.counts()["n_contacts"] > 100000
+
+
+@pytest.mark.parametrize("n_slots,chunk", [(3, 16), (1, 16), (2, 64)])
+def test_pipelined_host_pass_equals_one_pass(cuda, n_slots, chunk):
+    """tc_pipeline_eval_rows (sub-batches on a ring of streams, compact rows) delivers bit for bit the rows, costs
+    and term offsets of ONE tc_eval over the whole batch"""
+    s = helpers.load_scene("arm_around_table")
+    sg = cuda.scene(s, 0.025, 20.0, 0.01)
+    ms = helpers.pkg.multistart
+    B, T = 50, 6
+    q = ms.make_batch(s, 200, B, t_steps=T)
+    fixed = np.zeros(T, np.uint8)
+    fixed[0] = fixed[-1] = 1
+    ref = cuda.eval(sg, q, capi.EVAL_LVS_CONTINUOUS, lvs=0.02, fixed=fixed, want=capi.WANT_LINEARISE)
+    rows, co = ref.rows(), ref.contacts()
+    pipe = capi.Pipeline(cuda, sg, n_slots)
+    tpt = T - 1
+    pipe.reserve(B, tpt, len(co) + 10, len(rows["val"]) + 10)
+    for rep in range(3):  # the later rounds run speculatively on warmed-up slots
+        n_rows, nnz = pipe.eval_rows(q, capi.EVAL_LVS_CONTINUOUS, 0.02, fixed, chunk)
+        o = pipe.out
+        assert n_rows == len(co) and nnz == len(rows["val"])
+        assert np.array_equal(o["term_ptr"], ref.term_ptr())
+        assert np.array_equal(o["val"][:nnz], rows["val"]) and np.array_equal(o["value"][:n_rows], rows["value"])
+        assert np.array_equal(o["pair"][:n_rows], co["pair"])
+        assert np.array_equal(o["cost"], ref.cost()[1])
+        blocks = np.tile([1] + [2] * (tpt - 2) + [1], B)  # first / last segment have a fixed end
+        assert np.array_equal(capi.expand_compact_rows(o["term_ptr"], o["val"][:nnz], sg.n_dof, blocks), rows["row_ptr"])
+    _, _, margin, coeff = sg.pairs()
+    assert np.array_equal(margin[o["pair"][:n_rows]], rows["margin"]) and np.array_equal(coeff[o["pair"][:n_rows]], rows["coeff"])
+    pipe.close()
+    with pytest.raises(capi.TcError):
+        small = capi.Pipeline(cuda, sg, 2)
+        small.reserve(B, tpt, 5, 5)
+        small.eval_rows(q, capi.EVAL_LVS_CONTINUOUS, 0.02, fixed, chunk)

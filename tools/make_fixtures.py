@@ -1,5 +1,5 @@
 #!/usr/bin/env python3
-"""Generate scene fixtures under tests/golden/scenes/ from the reference's data files.
+"""Generate scene fixtures under trajopt-1_b200/data/scenes/ from the reference's data files.
 
 Run in the build container only (needs /root/reference).  The GPU box never sees
 /root/reference, so everything tests/bench need from it is frozen here as small .npz
@@ -33,7 +33,7 @@ import numpy as np
 from scipy.spatial import ConvexHull
 
 REF = "/root/reference/trajopt_common/data"
-OUT = os.path.join(os.path.dirname(os.path.abspath(__file__)), "..", "tests", "golden", "scenes")
+OUT = os.path.join(os.path.dirname(os.path.abspath(__file__)), "..", "trajopt-1_b200", "data", "scenes")
 
 JOINT_FIXED, JOINT_REVOLUTE, JOINT_PRISMATIC = 0, 1, 2
 SHAPE_SPHERE, SHAPE_HULL, SHAPE_CAPSULE, SHAPE_CYLINDER, SHAPE_CONE = 0, 1, 2, 3, 4

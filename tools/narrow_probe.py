@@ -36,5 +36,5 @@ for i in range(3 + reps):
         acc.append(cu.stage_ms(res))
 m = np.mean(np.array(acc), axis=0)
 c = res.counts()
-print("tag=%s gjk=%.3f epa=%.3f narrow=%.3f fk=%.3f broad=%.3f tail=%.3f total=%.3f wall=%.3f contacts=%d" % (
-    os.environ.get("TAG", ""), m[8], m[9], m[5], m[0], m[6], m[3], m[4], float(np.mean(wall)), c["n_contacts"]))
+print("tag=%s gjk=%.3f epa=%.3f narrow=%.3f fk=%.3f broad=%.3f deep=%.3f tail=%.3f total=%.3f wall=%.3f contacts=%d" % (
+    os.environ.get("TAG", ""), m[8], m[9], m[5], m[0], m[6], m[2], m[3], m[4], float(np.mean(wall)), c["n_contacts"]))

@@ -331,6 +331,60 @@ class Lib:
         return Scene(self, arrays, margin, coeff, margin_buffer, **kw)
 
 
+def expand_compact_rows(term_ptr, val, n_dof, blocks_per_term):
+    """row_ptr of compact rows (tc_pipeline_eval_rows): row i of term k holds blocks_per_term[k] * n_dof values;
+    blocks_per_term: [n_terms] (the same for every trajectory: tile the per-trajectory pattern)"""
+    rows_per_term = np.diff(term_ptr)
+    nnz_per_row = np.repeat(np.asarray(blocks_per_term, dtype=np.int64) * n_dof, rows_per_term)
+    row_ptr = np.zeros(len(nnz_per_row) + 1, np.int64)
+    np.cumsum(nnz_per_row, out=row_ptr[1:])
+    assert row_ptr[-1] == len(val)
+    return row_ptr
+
+
+class Pipeline:
+    """tc_pipeline: a batch cut into sub-batches on a ring of streams inside the library, rows downloaded in compact
+    form while the next sub-batch computes (one host thread).  Output arrays are allocated by the caller-supplied
+    `alloc(n, dtype)` (bench.py passes a pinned-memory allocator; numpy otherwise -> synchronous copies)."""
+
+    def __init__(self, lib, scene, n_slots=3):
+        self.lib, self.scene = lib, scene
+        self.handle = C.c_void_p()
+        lib.check(lib.dll.tc_pipeline_create(scene.handle, C.c_int32(n_slots), C.byref(self.handle)))
+        self.out = None
+
+    def close(self):
+        if self.handle:
+            self.lib.dll.tc_pipeline_destroy.restype = None
+            self.lib.dll.tc_pipeline_destroy(self.handle)
+            self.handle = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def reserve(self, B, terms_per_traj, row_cap, val_cap, alloc=None):
+        alloc = alloc or (lambda n, dt: np.zeros(n, dt))
+        self.out = dict(term_ptr=alloc(B * terms_per_traj + 1, np.int64), val=alloc(val_cap, np.float64),
+                        value=alloc(row_cap, np.float64), pair=alloc(row_cap, np.int32), cost=alloc(B, np.float64))
+
+    def eval_rows(self, q, evaluator, lvs, fixed, chunk, stack=STACK_IFOPT, precision=PRECISION_F64):
+        """q: numpy [B, T, n_dof] (host; pinned for asynchronous reads) -> (n_rows, nnz); arrays in self.out"""
+        B, T, n = q.shape
+        d, keep = make_eval_desc(evaluator, stack, lvs, fixed, WANT_LINEARISE, precision)
+        o = self.out
+        n_rows, nnz = C.c_int64(), C.c_int64()
+        _pl64 = C.POINTER(C.c_int64)
+        self.lib.check(self.lib.dll.tc_pipeline_eval_rows(
+            self.handle, C.byref(d), C.c_void_p(q.ctypes.data), C.c_int32(B), C.c_int32(T), C.c_int32(chunk),
+            C.c_void_p(o["term_ptr"].ctypes.data), C.c_void_p(o["val"].ctypes.data), C.c_size_t(len(o["val"])),
+            C.c_void_p(o["value"].ctypes.data), C.c_void_p(o["pair"].ctypes.data), C.c_size_t(len(o["value"])),
+            C.c_void_p(o["cost"].ctypes.data), C.byref(n_rows), C.byref(nnz)))
+        return n_rows.value, nnz.value
+
+
 class CudaLib(Lib):
     """libtrajopt_cuda.so"""
 
@@ -386,6 +440,12 @@ class CudaLib(Lib):
 
     def sync(self, result):
         self.check(self.dll.tc_result_sync(result.handle))
+
+    def pass_info(self, result):
+        """(speculative, repeated) of the last pass on `result` (tc_result_pass_info)"""
+        a, b = C.c_int32(), C.c_int32()
+        self.check(self.dll.tc_result_pass_info(result.handle, C.byref(a), C.byref(b)))
+        return bool(a.value), b.value
 
     def stage_ms(self, result):
         ms = (C.c_float * 10)()

@@ -40,6 +40,12 @@ int g_device = -1;
 int resolveNoallocScratch(int device, double** out);
 }  // namespace
 
+// counts of a finished pass, used as the capacities of the next one on the same result (speculative pass)
+struct PassSizes
+{
+  long long n_states{ 0 }, n_units{ 0 }, n_items_padded{ 0 }, n_raw{ 0 }, n_deep{ 0 };
+};
+
 struct tc_scene
 {
   HostScene host;
@@ -58,6 +64,14 @@ struct tc_result
   std::vector<uint8_t> term_fixed;
   bool pending{ false }, valid{ false };
   bool have_grad{ false }, have_cost{ false }, have_rows{ false };
+  // speculative sizing (runEval): counts of the last finished pass and what it takes to repeat the current one
+  PassSizes pred{};
+  unsigned long long pred_sig{ 0 }, pass_sig{ 0 };
+  bool pred_valid{ false }, speculative{ false }, deep_launched{ false };
+  int respeculated{ 0 };
+  std::vector<uint8_t> fixed_copy;
+  const double *arg_q{ nullptr }, *arg_pose0{ nullptr }, *arg_pose1{ nullptr };
+  int64_t pipe_row_base{ 0 };  // tc_pipeline_eval_rows: first global row of the sub-batch this result holds
   Work w{};
   Counters* h_counters{ nullptr };  // pinned + mapped: the device writes the snapshot itself
   Counters* h_counters_dev{ nullptr };  // device alias of h_counters
@@ -91,7 +105,7 @@ struct tc_result
   DevBuf<unsigned char> sort_temp, deep_scratch;
   DevBuf<double> cost_term, cost_traj;
   // rows
-  DevBuf<int32_t> col_idx, row_block;
+  DevBuf<int32_t> col_idx, row_block, row_pair;
   DevBuf<double> row_val, row_value, row_coeff, row_margin;
   // sets
   DevBuf<tc_set> sets;
@@ -147,8 +161,10 @@ int readCounters(tc_result* r)
   TC_CUDA(launchSnapshot(r->d_counters, r->h_counters_dev, r->stream));
   TC_CUDA(cudaStreamSynchronize(r->stream));
   trace(r, "counters read");
-  if (r->h_counters->overflow == 2)
+  if (r->h_counters->overflow == OVF_LVS_STATES)
     return fail(TC_ERR_OVERFLOW, "a segment needs more than 16384 LVS sub-states");
+  if (r->h_counters->overflow == OVF_SPECULATION)
+    return fail(TC_ERR_OVERFLOW, "a count outgrew the capacity predicted from the previous pass");  // finishEval repeats
   if (r->h_counters->overflow)
     return fail(TC_ERR_OVERFLOW, "an index arena exceeded 2^31 entries; split the batch");
   return TC_OK;
@@ -179,10 +195,42 @@ int reserve(DevBuf<T>& b, size_t n, const char* what)
 
 int enqueueRows(tc_result* r, bool fused);
 
+constexpr int DEEP_COUNT_GJK_FLAG = 1 << 30;  // tc_narrow_kernels.cuh DEEP_COUNT_GJK
+inline long long withSlack(long long n) { return n + n / 8 + 256; }
+
+// what makes two passes comparable in size: same batch shape, evaluator, options and fixed steps
+unsigned long long passSignature(const tc_eval_desc& d, int B, int T, bool poses)
+{
+  unsigned long long h = 1469598103934665603ull;
+  auto mix = [&h](unsigned long long x) {
+    h ^= x;
+    h *= 1099511628211ull;
+  };
+  mix(static_cast<unsigned>(B)), mix(static_cast<unsigned>(T)), mix(static_cast<unsigned>(d.evaluator));
+  mix(static_cast<unsigned>(d.stack)), mix(static_cast<unsigned>(d.precision)), mix(static_cast<unsigned>(d.want));
+  mix(static_cast<unsigned>(d.contact_test_type)), mix(poses ? 1 : 0);
+  unsigned long long lv;
+  std::memcpy(&lv, &d.lvs_length, sizeof(lv));
+  mix(lv);
+  if (d.fixed_steps)
+    for (int t = 0; t < T; ++t)
+      mix(d.fixed_steps[t] ? 2 : 3);
+  return h;
+}
+
 // pose0 / pose1 != nullptr: tc_contact_test — link poses come from the caller ([B][n_active][12] host arrays, pose1 only
-// for a cast test), there are no joint values (q == nullptr), B = number of states, T = 1 or 2
+// for a cast test), there are no joint values (q == nullptr), B = number of states, T = 1 or 2.
+//
+// Two ways through the pass:
+//   exact        every arena is sized from the device's own counts, read back stage by stage (five stream
+//                synchronisations); always used for the first pass of a result and whenever the pass signature changes
+//   speculative  arenas and launch grids are sized from the previous pass on this result plus 1/8 slack, the kernels take
+//                the actual counts from the device counters, nothing is read back until tc_result_sync: the call only
+//                enqueues.  A count that outgrows its capacity raises OVF_SPECULATION on the device, every later kernel
+//                leaves at once, and tc_result_sync repeats the pass exactly (counts between SQP iterations move by a
+//                few per cent, trajopt_sco/src/optimizers.cpp:194-203 evaluates the same problem at nearby iterates).
 int runEval(tc_scene* scene, const tc_eval_desc* desc, const double* q, int32_t B, int32_t T, tc_result* r,
-            cudaStream_t st, const double* pose0 = nullptr, const double* pose1 = nullptr)
+            cudaStream_t st, const double* pose0 = nullptr, const double* pose1 = nullptr, bool allow_speculative = true)
 {
   if (!scene || !desc || (!q && !pose0) || !r)
     return fail(TC_ERR_INVALID, "null argument");
@@ -203,6 +251,8 @@ int runEval(tc_scene* scene, const tc_eval_desc* desc, const double* q, int32_t 
   if (desc->evaluator != TC_EVAL_DISCRETE && !(desc->lvs_length > 0))
     return fail(TC_ERR_INVALID, "longest_valid_segment_length must be positive");
   TC_TRY(ensureDevice(scene->device));
+  if (r->pending)
+    cudaStreamSynchronize(r->stream);  // an evaluation that was never waited for: its arenas are about to be reused
   const HostScene& hs = scene->host;
   const SceneView& v = scene->dview;
   r->valid = false;
@@ -210,14 +260,20 @@ int runEval(tc_scene* scene, const tc_eval_desc* desc, const double* q, int32_t 
   r->have_grad = r->have_cost = r->have_rows = false;
   r->have_csc = false;
   r->stream = st;
+  // everything a repeat of this pass needs (speculation overflow)
+  if (desc->fixed_steps && desc->fixed_steps != r->fixed_copy.data())
+    r->fixed_copy.assign(desc->fixed_steps, desc->fixed_steps + T);
+  else if (!desc->fixed_steps)
+    r->fixed_copy.clear();
   r->desc = *desc;
-  r->desc.fixed_steps = nullptr;
+  r->desc.fixed_steps = r->fixed_copy.empty() ? nullptr : r->fixed_copy.data();
+  r->arg_q = q, r->arg_pose0 = pose0, r->arg_pose1 = pose1;
   // term list per trajectory: CollisionTermInfo::hatch (trajopt/src/problem_description.cpp:1735-1858)
   r->term_t.clear();
   r->term_fixed.clear();
   std::vector<uint8_t> fixed(static_cast<size_t>(T), 0);
-  if (desc->fixed_steps)
-    fixed.assign(desc->fixed_steps, desc->fixed_steps + T);
+  if (!r->fixed_copy.empty())
+    fixed = r->fixed_copy;
   if (desc->evaluator == TC_EVAL_DISCRETE)
   {
     for (int t = 0; t < T; ++t)
@@ -253,6 +309,13 @@ int runEval(tc_scene* scene, const tc_eval_desc* desc, const double* q, int32_t 
   ep.lvs = desc->lvs_length;
   std::memset(&r->counts, 0, sizeof(r->counts));
   r->counts.n_terms = n_terms;
+  static const bool no_spec = getenv("TC_NO_SPECULATION") != nullptr;  // diagnostics: every pass exact
+  const unsigned long long sig = passSignature(r->desc, B, T, pose0 != nullptr);
+  const bool spec = allow_speculative && !no_spec && r->pred_valid && r->pred_sig == sig && n_terms > 0;
+  r->pass_sig = sig;
+  r->speculative = spec;
+  r->deep_launched = false;
+  const PassSizes& pred = r->pred;
   Work& w = r->w;
   std::memset(&w, 0, sizeof(w));
   w.ep = ep;
@@ -260,12 +323,16 @@ int runEval(tc_scene* scene, const tc_eval_desc* desc, const double* q, int32_t 
   w.single_sweep = (desc->evaluator == TC_EVAL_CONTINUOUS && desc->stack == TC_STACK_IFOPT) ? 1 : 0;
   w.poses_given = pose0 ? 1 : 0;
   w.contact_type = desc->contact_test_type;
+  w.speculative = spec ? 1 : 0;
+  w.n_dof_q = hs.n_dof;
   w.counters = r->d_counters;
   for (int i = 0; i < 10; ++i)
     r->stage_ms[i] = 0;
   r->own_launches = r->lib_launches = 0;
   LaunchScope scope(r);
-  trace(r, "eval begin");
+  trace(r, spec ? "eval begin (speculative)" : "eval begin (exact)");
+  if (pose0 && (desc->want & (TC_WANT_GRADIENTS | TC_WANT_ROWS)))
+    return fail(TC_ERR_INVALID, "gradients and rows need joint values");
   // The first operation on the stream is a kernel, not the event record: when the stream's previous operation
   // was a device-to-host copy (a result download), an event record is queued on the copy engine, behind any bulk
   // download another tc_result has in flight there, and every kernel of this pass would wait for it.
@@ -342,10 +409,18 @@ int runEval(tc_scene* scene, const tc_eval_desc* desc, const double* q, int32_t 
   TC_RESERVE(r->unit_base, n_terms + 1);
   w.term_cnt = r->term_cnt.p, w.term_states = r->term_states.p, w.term_units = r->term_units.p;
   w.term_interp = r->term_interp.p, w.state_base = r->state_base.p, w.unit_base = r->unit_base.p;
+  if (spec)
+  {
+    w.n_states = withSlack(pred.n_states);
+    w.n_units = withSlack(pred.n_units);
+  }
   TC_CUDA(launchPlan(v, w, st));
-  TC_TRY(readCounters(r));
-  w.n_states = r->h_counters->n_states;
-  w.n_units = r->h_counters->n_units;
+  if (!spec)
+  {
+    TC_TRY(readCounters(r));
+    w.n_states = r->h_counters->n_states;
+    w.n_units = r->h_counters->n_units;
+  }
   // ---- K1 FK, K2 broadphase count ----
   TC_RESERVE(r->poses, static_cast<size_t>(w.n_states) * hs.n_active * 12);
   TC_RESERVE(r->aabb, static_cast<size_t>(w.n_states) * hs.n_active_shapes * 6);
@@ -362,10 +437,18 @@ int runEval(tc_scene* scene, const tc_eval_desc* desc, const double* q, int32_t 
   else
     TC_CUDA(launchFk(v, w, st));
   TC_CUDA(cudaEventRecord(r->ev[1], st));
+  if (spec)
+    w.n_items_padded = withSlack(pred.n_items_padded) / CHUNK * CHUNK;
   TC_CUDA(launchBroadCount(v, w, st));
-  TC_TRY(readCounters(r));
-  w.n_items_padded = r->h_counters->n_items_padded;
-  const long long n_items = r->h_counters->n_items;
+  long long n_items = 0;
+  if (!spec)
+  {
+    TC_TRY(readCounters(r));
+    w.n_items_padded = r->h_counters->n_items_padded;
+    n_items = r->h_counters->n_items;
+  }
+  else
+    n_items = w.n_items_padded;  // capacity of the raw-hit and deep lists
   // ---- K2 fill, K3 narrow phase ----
   TC_RESERVE(r->items, w.n_items_padded);
   TC_RESERVE(r->raw, n_items);
@@ -388,37 +471,71 @@ int runEval(tc_scene* scene, const tc_eval_desc* desc, const double* q, int32_t 
     TC_CUDA(cudaEventRecord(r->ev[6], st));
   }
   TC_CUDA(cudaEventRecord(r->ev[2], st));
-  TC_TRY(readCounters(r));
-  const long long n_deep = r->h_counters->n_deep;
+  long long n_deep = 0;
+  if (!spec)
   {
+    TC_TRY(readCounters(r));
+    n_deep = r->h_counters->n_deep;
     static const char* trace_deep = getenv("TC_TRACE_DEEP");  // tuning aid: how many items outgrew the fast polytope
     if (trace_deep)
+    {
       fprintf(stderr, "[tc] n_epa=%lld n_deep=%lld\n", r->h_counters->n_epa, n_deep);
+      // a path instead of "1": the (unit, shape pair) list and the units' T0 sub-states are written there (diagnostics)
+      if (trace_deep[0] == '/' && n_deep > 0)
+      {
+        std::vector<int32_t> di(static_cast<size_t>(2 * n_deep)), ut(static_cast<size_t>(w.n_units)), sb(static_cast<size_t>(n_terms) + 1),
+            ub(static_cast<size_t>(n_terms) + 1);
+        cudaMemcpy(di.data(), w.deep_items, di.size() * 4, cudaMemcpyDeviceToHost);
+        cudaMemcpy(ut.data(), w.unit_term, ut.size() * 4, cudaMemcpyDeviceToHost);
+        cudaMemcpy(sb.data(), w.state_base, sb.size() * 4, cudaMemcpyDeviceToHost);
+        cudaMemcpy(ub.data(), w.unit_base, ub.size() * 4, cudaMemcpyDeviceToHost);
+        std::vector<int32_t> cnt(static_cast<size_t>(n_terms));
+        cudaMemcpy(cnt.data(), w.term_cnt, cnt.size() * 4, cudaMemcpyDeviceToHost);
+        if (FILE* f = fopen(trace_deep, "w"))
+        {
+          for (long long i = 0; i < n_deep; ++i)
+          {
+            const int u = di[static_cast<size_t>(2 * i)], sp = di[static_cast<size_t>(2 * i + 1)];
+            const int k = ut[static_cast<size_t>(u)];
+            fprintf(f, "%d %d %d %d %d\n", u, sp & (DEEP_COUNT_GJK_FLAG - 1), k, u - ub[static_cast<size_t>(k)], cnt[static_cast<size_t>(k)]);
+          }
+          fclose(f);
+        }
+      }
+    }
   }
-  if (n_deep > 0)
+  else if (pred.n_deep > 0 || !hs.curved_sp.empty())
+    n_deep = -1;  // the kernel takes the count from the device
+  if (n_deep != 0)
   {
-    const int n_threads = 64 * static_cast<int>(std::min<long long>((n_deep + 63) / 64, 296));
+    // launch shape from the count (exact pass) or from the previous pass's count (speculative pass; the kernel strides
+    // over whatever the device count turns out to be)
+    const long long shape_n = n_deep < 0 ? std::max<long long>(withSlack(pred.n_deep), 256) : n_deep;
+    const int n_threads = 64 * static_cast<int>(std::min<long long>((shape_n + 63) / 64, 296));
     const size_t per = deepScratchBytesPerThread(desc->precision);
     TC_RESERVE(r->deep_scratch, per * n_threads);
     TC_CUDA(launchNarrowDeep(v, w, desc->precision, n_deep, r->deep_scratch.p, per, n_threads, st));
-    TC_TRY(readCounters(r));
+    r->deep_launched = true;
+    if (!spec)
+      TC_TRY(readCounters(r));
   }
   TC_CUDA(cudaEventRecord(r->ev[3], st));
-  w.n_raw = r->h_counters->n_raw;
   // ---- contact finalisation + sort ----
-  TC_RESERVE(r->contacts_tmp, w.n_raw);
-  TC_RESERVE(r->keys, w.n_raw);
-  TC_RESERVE(r->keys_alt, w.n_raw);
-  TC_RESERVE(r->idx, w.n_raw);
-  TC_RESERVE(r->idx_alt, w.n_raw);
+  w.n_sort = spec ? std::min(withSlack(pred.n_raw), n_items) : r->h_counters->n_raw;
+  w.n_raw = w.n_sort;
+  TC_RESERVE(r->contacts_tmp, w.n_sort);
+  TC_RESERVE(r->keys, w.n_sort);
+  TC_RESERVE(r->keys_alt, w.n_sort);
+  TC_RESERVE(r->idx, w.n_sort);
+  TC_RESERVE(r->idx_alt, w.n_sort);
   w.contacts_tmp = r->contacts_tmp.p;
   w.keys = r->keys.p, w.keys_alt = r->keys_alt.p, w.idx = r->idx.p, w.idx_alt = r->idx_alt.p;
   if (w.contact_type != TC_CONTACT_ALL)
   {
-    TC_RESERVE(r->raw_valid, w.n_raw);
+    TC_RESERVE(r->raw_valid, w.n_sort);
     w.raw_valid = r->raw_valid.p;
   }
-  if (w.n_raw > 0)
+  if (w.n_sort > 0)
   {
     TC_CUDA(launchFinalize(v, w, st));
     size_t temp_bytes = 0;
@@ -433,16 +550,18 @@ int runEval(tc_scene* scene, const tc_eval_desc* desc, const double* q, int32_t 
       TC_CUDA(sortContacts(w, r->sort_temp.p, temp_bytes, st));
       r->lib_launches += 1;
     }
-    TC_TRY(readCounters(r));
+    if (!spec)
+      TC_TRY(readCounters(r));
   }
-  w.n_contacts = r->h_counters->n_valid;
+  // grid bound of the kernels indexed by contact (they take the count itself from the device counters)
+  w.n_contacts = spec ? w.n_sort : r->h_counters->n_valid;
   TC_RESERVE(r->contacts, w.n_contacts);
   TC_RESERVE(r->term_ptr, n_terms + 1);
   w.contacts = r->contacts.p, w.term_ptr = r->term_ptr.p;
+  // rows wanted and no stored gradients: k_grad_rows runs in this pass and takes over the gather
+  w.gather_in_rows = ((desc->want & TC_WANT_ROWS) && !(desc->want & TC_WANT_GRADIENTS) && w.n_contacts > 0) ? 1 : 0;
   TC_CUDA(launchGather(v, w, st));
   // ---- K4 ----
-  if (pose0 && (desc->want & (TC_WANT_GRADIENTS | TC_WANT_ROWS)))
-    return fail(TC_ERR_INVALID, "gradients and rows need joint values");
   if (desc->want & TC_WANT_GRADIENTS)
   {
     TC_RESERVE(r->grad, static_cast<size_t>(w.n_contacts) * 4 * hs.n_dof);
@@ -470,10 +589,29 @@ int finishEval(tc_result* r)
 {
   if (!r->pending)
     return r->valid ? TC_OK : fail(TC_ERR_INVALID, "no evaluation to wait for");
-  LaunchScope scope(r);
   TC_TRY(ensureDevice(r->scene->device));
   if (r->ep.n_terms > 0)
-    TC_TRY(readCounters(r));
+  {
+    LaunchScope scope(r);
+    const int st = readCounters(r);
+    const bool respec = r->speculative && (r->h_counters->overflow == OVF_SPECULATION ||
+                                           (st == TC_OK && r->h_counters->n_deep > 0 && !r->deep_launched));
+    if (respec)
+    {
+      // a count outgrew the capacity taken from the previous pass: repeat with exact sizes
+      trace(r, "speculation overflow: exact repeat");
+      r->pred_valid = false;
+      r->pending = false;
+      const tc_eval_desc d = r->desc;
+      const int own = r->own_launches, lib = r->lib_launches;
+      TC_TRY(runEval(r->scene, &d, r->arg_q, r->ep.B, r->ep.T, r, r->stream, r->arg_pose0, r->arg_pose1, false));
+      r->own_launches += own, r->lib_launches += lib;
+      r->respeculated += 1;
+      return finishEval(r);
+    }
+    if (st != TC_OK)
+      return st;
+  }
   else
   {
     TC_CUDA(cudaStreamSynchronize(r->stream));
@@ -481,6 +619,18 @@ int finishEval(tc_result* r)
   }
   r->pending = false;
   const Counters& c = *r->h_counters;
+  // the accessors' kernels are launched with the actual counts; n_states / n_units / n_items_padded stay what they were
+  // during the pass: they are the strides of the arenas
+  r->w.n_raw = c.n_raw;
+  r->w.n_contacts = c.n_valid;
+  r->w.speculative = 0;
+  if (r->ep.n_terms > 0)
+  {
+    r->pred.n_states = c.n_states, r->pred.n_units = c.n_units, r->pred.n_items_padded = c.n_items_padded;
+    r->pred.n_raw = c.n_raw, r->pred.n_deep = c.n_deep;
+    r->pred_sig = r->pass_sig;
+    r->pred_valid = true;
+  }
   const HostScene& hs = r->scene->host;
   tc_counts& o = r->counts;
   o.n_states = c.n_states;
@@ -531,12 +681,14 @@ int enqueueRows(tc_result* r, bool fused)
   TC_RESERVE(r->term_row_base, r->ep.n_terms + 1);
   TC_RESERVE(r->col_idx, 2 * nc * hs.n_dof);
   TC_RESERVE(r->row_block, 2 * nc);
+  TC_RESERVE(r->row_pair, nc);
   TC_RESERVE(r->row_val, 2 * nc * hs.n_dof);
   TC_RESERVE(r->row_value, nc);
   TC_RESERVE(r->row_coeff, nc);
   TC_RESERVE(r->row_margin, nc);
   w.row_ptr = r->row_ptr.p;
   w.row_block = r->row_block.p;
+  w.row_pair = r->row_pair.p;
   TC_CUDA(launchRowBase(r->scene->dview, w, r->term_row_base.p, r->stream));
   if (fused)
     TC_CUDA(launchGradRows(r->scene->dview, w, r->term_row_base.p, r->col_idx.p, r->row_val.p, r->row_value.p,
@@ -800,7 +952,7 @@ void tc_result_destroy(tc_result* r)
   r->ghas.release(), r->raw.release(), r->keys.release(), r->keys_alt.release(), r->contacts_tmp.release();
   r->contacts.release(), r->xf.release(), r->grad.release(), r->term_ptr.release();
   r->row_ptr.release(), r->term_row_base.release(), r->grec.release(), r->sort_temp.release();
-  r->deep_scratch.release(), r->cost_term.release(), r->cost_traj.release(), r->col_idx.release(), r->row_block.release();
+  r->deep_scratch.release(), r->cost_term.release(), r->cost_traj.release(), r->col_idx.release(), r->row_block.release(), r->row_pair.release();
   r->csc_bt_base.release(), r->csc_col_ptr.release(), r->csc_row_idx.release(), r->csc_val.release();
   r->csc_upper.release(), r->csc_cost.release();
   r->row_val.release(), r->row_value.release(), r->row_coeff.release(), r->row_margin.release();
@@ -821,6 +973,17 @@ int tc_result_sync(tc_result* res)
   if (!res)
     return fail(TC_ERR_INVALID, "null result");
   return finishEval(res);
+}
+
+int tc_result_pass_info(const tc_result* res, int32_t* speculative, int32_t* repeated)
+{
+  if (!res)
+    return fail(TC_ERR_INVALID, "null result");
+  if (speculative)
+    *speculative = res->speculative ? 1 : 0;
+  if (repeated)
+    *repeated = res->respeculated;
+  return TC_OK;
 }
 
 int tc_contact_test(tc_scene* scene, const double* link_pose0, const double* link_pose1, int32_t n_states,
@@ -1228,6 +1391,271 @@ void tc_nccl_comm_destroy(void* comm)
     g_nccl.commDestroy(comm);
 }
 
+// ---------------------------------------------------------------------------------------------------------------
+// tc_pipeline: sub-batches on a ring of (result, stream) slots, one host thread
+// ---------------------------------------------------------------------------------------------------------------
+}  // extern "C" (reopened below)
+
+struct tc_pipeline
+{
+  tc_scene* scene{ nullptr };
+  int n_slots{ 0 };
+  // one ring of results per sub-batch size, so that every result keeps seeing passes of ONE shape and stays speculative
+  struct Ring
+  {
+    int B{ 0 };
+    std::vector<tc_result*> res;
+  };
+  std::vector<Ring> rings;
+  std::vector<cudaStream_t> streams;
+};
+
+namespace
+{
+struct SubBatch
+{
+  int first, count;
+};
+
+// chunks of `chunk` trajectories; the last one tapered into 1/2 + 1/4 + 1/4 (its download is what nothing overlaps)
+std::vector<SubBatch> cutBatch(int B, int chunk)
+{
+  std::vector<SubBatch> out;
+  int first = 0;
+  while (B - first > chunk)
+  {
+    out.push_back({ first, chunk });
+    first += chunk;
+  }
+  const int last = B - first;
+  if (last >= 8 && out.size() >= 1)
+  {
+    const int a = last / 2, b = last / 4;
+    out.push_back({ first, a });
+    out.push_back({ first + a, b });
+    out.push_back({ first + a + b, last - a - b });
+  }
+  else
+    out.push_back({ first, last });
+  return out;
+}
+
+tc_result* ringSlot(tc_pipeline* p, int B, int slot, int* status)
+{
+  *status = TC_OK;
+  for (auto& rg : p->rings)
+    if (rg.B == B)
+      return rg.res[static_cast<size_t>(slot)];
+  tc_pipeline::Ring rg;
+  rg.B = B;
+  for (int i = 0; i < p->n_slots; ++i)
+  {
+    tc_result* r = nullptr;
+    *status = tc_result_create(p->scene, &r);
+    if (*status != TC_OK)
+    {
+      for (tc_result* x : rg.res)
+        tc_result_destroy(x);
+      return nullptr;
+    }
+    rg.res.push_back(r);
+  }
+  p->rings.push_back(rg);
+  return p->rings.back().res[static_cast<size_t>(slot)];
+}
+}  // namespace
+
+extern "C" {
+
+int tc_pipeline_create(tc_scene* scene, int32_t n_slots, tc_pipeline** out)
+{
+  if (!scene || !out || n_slots < 1 || n_slots > 8)
+    return fail(TC_ERR_INVALID, "tc_pipeline_create: bad argument (1..8 slots)");
+  TC_TRY(ensureDevice(scene->device));
+  tc_pipeline* p = new (std::nothrow) tc_pipeline();
+  if (!p)
+    return fail(TC_ERR_INVALID, "out of memory");
+  p->scene = scene;
+  p->n_slots = n_slots;
+  for (int i = 0; i < n_slots; ++i)
+  {
+    cudaStream_t st = nullptr;
+    const cudaError_t e = cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking);
+    if (e != cudaSuccess)
+    {
+      tc_pipeline_destroy(p);
+      return cudaFail(e, "cudaStreamCreate");
+    }
+    p->streams.push_back(st);
+  }
+  *out = p;
+  return TC_OK;
+}
+
+void tc_pipeline_destroy(tc_pipeline* p)
+{
+  if (!p)
+    return;
+  cudaSetDevice(p->scene->device);
+  for (auto& rg : p->rings)
+    for (tc_result* r : rg.res)
+      tc_result_destroy(r);
+  for (cudaStream_t st : p->streams)
+    cudaStreamDestroy(st);
+  delete p;
+}
+
+int tc_pipeline_eval_rows(tc_pipeline* p, const tc_eval_desc* desc, const double* q, int32_t B, int32_t T, int32_t chunk,
+                          int64_t* term_ptr, double* val, size_t val_cap, double* row_value, int32_t* row_pair,
+                          size_t row_cap, double* cost_per_traj, int64_t* n_rows_out, int64_t* nnz_out)
+{
+  if (!p || !desc || !q || !term_ptr || !val || !row_value || !row_pair || !cost_per_traj || !n_rows_out || !nnz_out)
+    return fail(TC_ERR_INVALID, "tc_pipeline_eval_rows: null argument");
+  if (B <= 0 || T <= 0 || chunk <= 0)
+    return fail(TC_ERR_INVALID, "tc_pipeline_eval_rows: empty batch");
+  if (desc->q_on_device)
+    return fail(TC_ERR_INVALID, "tc_pipeline_eval_rows takes host joint values");
+  TC_TRY(ensureDevice(p->scene->device));
+  const int n_dof = p->scene->host.n_dof;
+  tc_eval_desc d = *desc;
+  d.want = TC_WANT_COST | TC_WANT_CONTACTS | TC_WANT_ROWS;
+  const std::vector<SubBatch> subs = cutBatch(B, chunk);
+  const int K = p->n_slots;
+  struct InFlight
+  {
+    tc_result* r{ nullptr };
+    SubBatch sb{};
+    bool evaluating{ false }, downloading{ false };
+  };
+  std::vector<InFlight> slot(static_cast<size_t>(K));
+  int64_t rows_done = 0, nnz_done = 0;
+  int tpt = -1;
+  // sub-batch j - 1 finished computing: size its download exactly and enqueue it behind its kernels
+  auto download = [&](InFlight& f) -> int {
+    TC_TRY(finishEval(f.r));
+    tc_result* r = f.r;
+    const int64_t nc = r->w.n_contacts, nz = r->h_counters->nnz;
+    if (static_cast<size_t>(rows_done + nc) > row_cap || static_cast<size_t>(nnz_done + nz) > val_cap)
+      return fail(TC_ERR_OVERFLOW, "tc_pipeline_eval_rows: the caller's row arrays are too small");
+    const size_t nt = static_cast<size_t>(f.sb.count) * static_cast<size_t>(tpt);
+    int64_t* tp = term_ptr + static_cast<size_t>(f.sb.first) * static_cast<size_t>(tpt);
+    // the sub-batch's term offsets are local; they are shifted by the rows before it once everything has landed (the
+    // closing entry of a sub-batch is the opening entry of the next, so only the nt opening entries are taken)
+    if (nt)
+      TC_CUDA(cudaMemcpyAsync(tp, r->w.term_ptr, nt * sizeof(int64_t), cudaMemcpyDeviceToHost, r->stream));
+    if (nz)
+      TC_CUDA(cudaMemcpyAsync(val + nnz_done, r->row_val.p, static_cast<size_t>(nz) * sizeof(double), cudaMemcpyDeviceToHost, r->stream));
+    if (nc)
+    {
+      TC_CUDA(cudaMemcpyAsync(row_value + rows_done, r->row_value.p, static_cast<size_t>(nc) * sizeof(double), cudaMemcpyDeviceToHost, r->stream));
+      TC_CUDA(cudaMemcpyAsync(row_pair + rows_done, r->row_pair.p, static_cast<size_t>(nc) * sizeof(int32_t), cudaMemcpyDeviceToHost, r->stream));
+    }
+    TC_CUDA(cudaMemcpyAsync(cost_per_traj + f.sb.first, r->cost_traj.p, static_cast<size_t>(f.sb.count) * sizeof(double),
+                            cudaMemcpyDeviceToHost, r->stream));
+    f.evaluating = false;
+    f.downloading = true;
+    // remember where this sub-batch's rows start: stored in the slot, applied after the final wait
+    r->pipe_row_base = rows_done;
+    rows_done += nc;
+    nnz_done += nz;
+    return TC_OK;
+  };
+  std::vector<std::pair<SubBatch, int64_t>> bases;  // (sub-batch, first row) for the final term_ptr shift
+  int pending_slot = -1;
+  auto finishSlot = [&](int s) -> int {
+    InFlight& g = slot[static_cast<size_t>(s)];
+    TC_TRY(download(g));
+    bases.push_back({ g.sb, g.r->pipe_row_base });
+    return TC_OK;
+  };
+  for (size_t j = 0; j < subs.size(); ++j)
+  {
+    const int s = static_cast<int>(j % static_cast<size_t>(K));
+    InFlight& f = slot[static_cast<size_t>(s)];
+    if (f.evaluating)
+    {
+      // a one-slot ring: the sub-batch still in the slot goes first (rows stay in sub-batch order)
+      TC_TRY(finishSlot(s));
+      pending_slot = -1;
+    }
+    if (f.downloading)
+    {
+      // the slot's previous sub-batch must have left the device before its arenas are reused
+      TC_CUDA(cudaStreamSynchronize(p->streams[static_cast<size_t>(s)]));
+      f.downloading = false;
+    }
+    int status = TC_OK;
+    f.r = ringSlot(p, subs[j].count, s, &status);
+    if (!f.r)
+      return status;
+    f.sb = subs[j];
+    TC_TRY(runEval(p->scene, &d, q + static_cast<size_t>(subs[j].first) * T * n_dof, subs[j].count, T, f.r,
+                   p->streams[static_cast<size_t>(s)]));
+    tpt = f.r->ep.terms_per_traj;
+    f.evaluating = true;
+    // the one before it (on another stream) finishes while this one is already queued
+    if (pending_slot >= 0)
+      TC_TRY(finishSlot(pending_slot));
+    pending_slot = s;
+  }
+  if (pending_slot >= 0)
+    TC_TRY(finishSlot(pending_slot));
+  for (int s = 0; s < K; ++s)
+    if (slot[static_cast<size_t>(s)].downloading)
+      TC_CUDA(cudaStreamSynchronize(p->streams[static_cast<size_t>(s)]));
+  // term offsets become global
+  for (const auto& b : bases)
+  {
+    const size_t nt = static_cast<size_t>(b.first.count) * static_cast<size_t>(tpt);
+    int64_t* tp = term_ptr + static_cast<size_t>(b.first.first) * static_cast<size_t>(tpt);
+    for (size_t k = 0; k < nt; ++k)
+      tp[k] += b.second;
+  }
+  term_ptr[static_cast<size_t>(B) * static_cast<size_t>(std::max(tpt, 0))] = rows_done;
+  *n_rows_out = rows_done;
+  *nnz_out = nnz_done;
+  return TC_OK;
+}
+
+// Device + pinned-host staging of the multi-start collectives, one per process, grown on demand and kept: the
+// collectives themselves never call cudaMalloc / cudaFree (each is a device-wide synchronisation).
+static int collectiveScratch(size_t dev_bytes, size_t host_bytes, unsigned char** dev, unsigned char** host)
+{
+  static std::mutex mu;
+  static unsigned char *d = nullptr, *h = nullptr;
+  static size_t dcap = 0, hcap = 0;
+  static int device = -1;
+  std::lock_guard<std::mutex> lock(mu);
+  if (device != g_device)
+  {
+    d = nullptr, dcap = 0;  // another device: its scratch is allocated afresh (the old one lives until exit)
+    device = g_device;
+  }
+  if (dev_bytes > dcap)
+  {
+    if (d)
+      cudaFree(d);
+    d = nullptr;
+    dcap = 0;
+    const size_t want = std::max<size_t>(dev_bytes * 2, 1 << 16);
+    TC_CUDA(cudaMalloc(reinterpret_cast<void**>(&d), want));
+    dcap = want;
+  }
+  if (host_bytes > hcap)
+  {
+    if (h)
+      cudaFreeHost(h);
+    h = nullptr;
+    hcap = 0;
+    const size_t want = std::max<size_t>(host_bytes * 2, 1 << 16);
+    TC_CUDA(cudaHostAlloc(reinterpret_cast<void**>(&h), want, cudaHostAllocDefault));
+    hcap = want;
+  }
+  *dev = d;
+  *host = h;
+  return TC_OK;
+}
+
 int tc_allgather_best(double local_best_cost, int64_t local_best_idx, void* nccl_comm, int n_ranks, void* cuda_stream,
                       double* best_cost, int64_t* best_idx, int32_t* best_rank)
 {
@@ -1243,29 +1671,24 @@ int tc_allgather_best(double local_best_cost, int64_t local_best_idx, void* nccl
     double cost;
     int64_t idx;
   };
-  Rec* d = nullptr;
-  TC_CUDA(cudaMalloc(reinterpret_cast<void**>(&d), sizeof(Rec) * (static_cast<size_t>(n_ranks) + 1)));
-  Rec mine{ local_best_cost, local_best_idx };
-  cudaError_t ce = cudaMemcpyAsync(d + n_ranks, &mine, sizeof(Rec), cudaMemcpyHostToDevice, st);
-  int ne = 0;
-  if (ce == cudaSuccess)
-    ne = g_nccl.allGather(d + n_ranks, d, sizeof(Rec), /* ncclChar */ 0, nccl_comm, st);
-  std::vector<Rec> all(static_cast<size_t>(n_ranks));
-  if (ce == cudaSuccess && ne == 0)
-    ce = cudaMemcpyAsync(all.data(), d, sizeof(Rec) * n_ranks, cudaMemcpyDeviceToHost, st);
-  if (ce == cudaSuccess && ne == 0)
-    ce = cudaStreamSynchronize(st);
-  cudaFree(d);
+  unsigned char *dv = nullptr, *hv = nullptr;
+  const size_t n = static_cast<size_t>(n_ranks);
+  TC_TRY(collectiveScratch(sizeof(Rec) * (n + 1), sizeof(Rec) * (n + 1), &dv, &hv));
+  Rec* d = reinterpret_cast<Rec*>(dv);
+  Rec* h = reinterpret_cast<Rec*>(hv);
+  h[n] = Rec{ local_best_cost, local_best_idx };
+  TC_CUDA(cudaMemcpyAsync(d + n, h + n, sizeof(Rec), cudaMemcpyHostToDevice, st));
+  const int ne = g_nccl.allGather(d + n, d, sizeof(Rec), /* ncclChar */ 0, nccl_comm, st);
   if (ne)
     return ncclFail(ne, "ncclAllGather");
-  if (ce != cudaSuccess)
-    return cudaFail(ce, "tc_allgather_best");
+  TC_CUDA(cudaMemcpyAsync(h, d, sizeof(Rec) * n, cudaMemcpyDeviceToHost, st));
+  TC_CUDA(cudaStreamSynchronize(st));
   int br = 0;
   for (int i = 1; i < n_ranks; ++i)
-    if (all[static_cast<size_t>(i)].cost < all[static_cast<size_t>(br)].cost)
+    if (h[i].cost < h[br].cost)
       br = i;
-  *best_cost = all[static_cast<size_t>(br)].cost;
-  *best_idx = all[static_cast<size_t>(br)].idx;
+  *best_cost = h[br].cost;
+  *best_idx = h[br].idx;
   *best_rank = br;
   return TC_OK;
 }
@@ -1280,22 +1703,70 @@ int tc_broadcast_trajectory(double* traj, size_t n_values, int root_rank, void* 
   TC_TRY(ensureDevice(g_device));
   cudaStream_t st = static_cast<cudaStream_t>(cuda_stream);
   const size_t bytes = n_values * sizeof(double);
-  double* d = nullptr;
-  TC_CUDA(cudaMalloc(reinterpret_cast<void**>(&d), bytes));
+  unsigned char *dv = nullptr, *hv = nullptr;
+  TC_TRY(collectiveScratch(bytes, bytes, &dv, &hv));
+  std::memcpy(hv, traj, bytes);
   // every rank uploads its buffer; only the root's content is read by the collective
-  cudaError_t ce = cudaMemcpyAsync(d, traj, bytes, cudaMemcpyHostToDevice, st);
-  int ne = 0;
-  if (ce == cudaSuccess)
-    ne = g_nccl.broadcast(d, d, bytes, /* ncclChar */ 0, root_rank, nccl_comm, st);
-  if (ce == cudaSuccess && ne == 0)
-    ce = cudaMemcpyAsync(traj, d, bytes, cudaMemcpyDeviceToHost, st);
-  if (ce == cudaSuccess && ne == 0)
-    ce = cudaStreamSynchronize(st);
-  cudaFree(d);
+  TC_CUDA(cudaMemcpyAsync(dv, hv, bytes, cudaMemcpyHostToDevice, st));
+  const int ne = g_nccl.broadcast(dv, dv, bytes, /* ncclChar */ 0, root_rank, nccl_comm, st);
   if (ne)
     return ncclFail(ne, "ncclBroadcast");
-  if (ce != cudaSuccess)
-    return cudaFail(ce, "tc_broadcast_trajectory");
+  TC_CUDA(cudaMemcpyAsync(hv, dv, bytes, cudaMemcpyDeviceToHost, st));
+  TC_CUDA(cudaStreamSynchronize(st));
+  std::memcpy(traj, hv, bytes);
+  return TC_OK;
+}
+
+int tc_result_allgather_best(tc_result* r, int64_t index_offset, void* nccl_comm, int n_ranks, double* best_cost,
+                             int64_t* best_idx, int32_t* best_rank, double* best_traj)
+{
+  if (!r || n_ranks <= 0 || !best_cost || !best_idx || !best_rank)
+    return fail(TC_ERR_INVALID, "bad argument");
+  if (n_ranks > 1 && !nccl_comm)
+    return fail(TC_ERR_INVALID, "a communicator is needed for more than one rank");
+  // the evaluation is finished first: a speculative pass may have to be repeated, and a repeat must not happen between
+  // ranks that have already entered the collective
+  if (r->pending)
+    TC_TRY(finishEval(r));
+  TC_TRY(needValid(r));
+  if (!r->have_cost || !r->w.q)
+    return fail(TC_ERR_INVALID, "the evaluation ran without TC_WANT_COST or without joint values");
+  if (n_ranks > 1)
+    TC_TRY(loadNccl());
+  const size_t nv = static_cast<size_t>(r->ep.T) * static_cast<size_t>(r->scene->host.n_dof);
+  const size_t rec = (2 + nv) * sizeof(double);  // cost, global index (as int64), trajectory
+  const size_t n = static_cast<size_t>(n_ranks);
+  unsigned char *dv = nullptr, *hv = nullptr;
+  TC_TRY(collectiveScratch(rec * (n + 1), rec * n, &dv, &hv));
+  cudaStream_t st = r->stream;
+  {
+    LaunchScope scope(r);
+    TC_CUDA(launchBestRecord(r->w, r->cost_traj.p, index_offset, reinterpret_cast<double*>(dv + rec * n), st));
+  }
+  if (n_ranks > 1)
+  {
+    const int ne = g_nccl.allGather(dv + rec * n, dv, rec, /* ncclChar */ 0, nccl_comm, st);
+    if (ne)
+      return ncclFail(ne, "ncclAllGather");
+    TC_CUDA(cudaMemcpyAsync(hv, dv, rec * n, cudaMemcpyDeviceToHost, st));
+  }
+  else
+    TC_CUDA(cudaMemcpyAsync(hv, dv + rec * n, rec, cudaMemcpyDeviceToHost, st));
+  TC_CUDA(cudaStreamSynchronize(st));
+  int br = 0;
+  auto costOf = [&](int i) {
+    double c;
+    std::memcpy(&c, hv + rec * static_cast<size_t>(i), sizeof(double));
+    return c;
+  };
+  for (int i = 1; i < n_ranks; ++i)
+    if (costOf(i) < costOf(br))
+      br = i;
+  *best_cost = costOf(br);
+  std::memcpy(best_idx, hv + rec * static_cast<size_t>(br) + sizeof(double), sizeof(int64_t));
+  *best_rank = br;
+  if (best_traj)
+    std::memcpy(best_traj, hv + rec * static_cast<size_t>(br) + 2 * sizeof(double), nv * sizeof(double));
   return TC_OK;
 }
 }  // extern "C"

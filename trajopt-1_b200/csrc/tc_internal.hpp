@@ -101,6 +101,7 @@ struct Work
   int contact_type; // TC_CONTACT_*
   const double* pose_in;  // [2 (T0, T1)][n_terms][n_active][12] (device) when poses_given
   const double* q;
+  int n_dof_q;                 // joints per timestep of q
   const int32_t* term_t;       // [terms_per_traj]
   const uint8_t* term_fixed;   // [terms_per_traj][2]
   int32_t *term_cnt, *term_states, *term_units, *state_base, *unit_base;
@@ -126,9 +127,29 @@ struct Work
   int32_t* ghas;
   long long* row_ptr;
   int32_t* row_block;    // [n_rows][2] first column of the T0 / T1 run of every row (-1 = block absent)
+  int32_t* row_pair;     // [n_rows] link pair of every row (margin and coefficient follow from it)
   Counters* counters;
-  long long n_states, n_units, n_items_padded, n_raw, n_contacts;
+  // LAYOUT STRIDES / CAPACITIES of the arenas, fixed on the host before the kernels run.  In an exact pass they equal the
+  // counts (read back stage by stage); in a speculative pass they are the previous pass's counts plus slack, and every
+  // kernel takes the actual counts from `counters` on the device and leaves at once when `counters->overflow` says
+  // a count outgrew its capacity (the host then repeats the pass exactly).
+  long long n_states, n_units, n_items_padded;
+  long long n_sort;      // entries the key sort covers (>= raw hits; the surplus carries all-ones keys)
+  // host-known counts for the kernels launched AFTER the pass has been synchronised (accessors)
+  long long n_raw, n_contacts;
   long long raw_cap, deep_cap;
+  int speculative;
+  int gather_in_rows;  // the fused gradient-row kernel performs the gather of the sorted contacts itself
+};
+
+// actual counts of the running pass, as the kernels see them
+__device__ __forceinline__ bool passOverflowed(const Work& w) { return w.counters->overflow != 0; }
+enum
+{
+  OVF_LVS_STATES = 2,   // a segment needs more than 16384 sub-states
+  OVF_INDEX_STATES = 3, // 32-bit index arenas
+  OVF_INDEX_ITEMS = 4,
+  OVF_SPECULATION = 5   // a count outgrew the capacity predicted from the previous pass: repeat exactly
 };
 
 // record of (link, state) in the pose arena; the next sub-state of the same link follows at +12
@@ -162,6 +183,8 @@ cudaError_t launchRows(const SceneView& v, const Work& w, long long* term_row_ba
 cudaError_t launchGradRows(const SceneView& v, const Work& w, long long* term_row_base, int32_t* col_idx, double* val,
                            double* row_value, double* row_coeff, double* row_margin, cudaStream_t st);
 cudaError_t launchCost(const SceneView& v, const Work& w, double* cost_term, double* cost_traj, cudaStream_t st);
+// record [cost, global index (int64 bits), trajectory T x n_dof] of the cheapest trajectory of the batch (first on ties)
+cudaError_t launchBestRecord(const Work& w, const double* cost_traj, long long index_offset, double* rec, cudaStream_t st);
 cudaError_t launchQpCsc(const SceneView& v, const Work& w, long long* bt_base, const double* val, const double* row_value,
                         const double* row_coeff, const double* row_margin, long long* col_ptr, int32_t* row_idx,
                         double* out, double* upper, double* slack_cost, cudaStream_t st);
@@ -171,6 +194,7 @@ cudaError_t launchSets(const SceneView& v, const Work& w, int max_num_cnt, tc_se
 cudaError_t launchNarrow(const SceneView& v, const Work& w, int precision, cudaStream_t st, cudaEvent_t mid);
 // ---- launchers (tc_strict.cu: contraction-free kernels) ----
 cudaError_t launchRouteCurved(const SceneView& v, const Work& w, cudaStream_t st);
+// n_deep < 0: the kernel takes the count from the device counters (speculative pass)
 cudaError_t launchNarrowDeep(const SceneView& v, const Work& w, int precision, long long n_deep, void* scratch,
                              size_t scratch_bytes_per_thread, int n_threads, cudaStream_t st);
 size_t deepScratchBytesPerThread(int precision);

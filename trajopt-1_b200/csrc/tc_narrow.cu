@@ -160,7 +160,9 @@ __global__ void __launch_bounds__(TC_GJK_NT, MINB * 128 / TC_GJK_NT) k_gjk(Scene
   __shared__ RunInfo s_run;
   __shared__ int s_next;
   Vtx<R>* sv = reinterpret_cast<Vtx<R>*>(smem_raw);
-  const int range_end = static_cast<int>(min(static_cast<long long>(blockIdx.x + 1) * run_items, static_cast<long long>(w.n_items_padded)));
+  if (passOverflowed(w))
+    return;
+  const int range_end = static_cast<int>(min(static_cast<long long>(blockIdx.x + 1) * run_items, w.counters->n_items_padded));
   if (threadIdx.x == 0)
     mbarInit(&bar, 1);
   long long st_gjk = 0, st_scan = 0, st_cmp = 0, st_unconv = 0;
@@ -293,7 +295,10 @@ __device__ __forceinline__ int bucketOf(const SceneView& v, const Work& w, int i
 template <class R, int MINB>
 __global__ void __launch_bounds__(128, MINB) k_epa_wp(SceneView v, Work w)
 {
+  if (passOverflowed(w))
+    return;
   const int lane = threadIdx.x & 31;
+  const long long n_items_padded = w.counters->n_items_padded;
   // thread-local polytope store; raw arrays so that nothing is zero-filled.  Hull vertices and support look-up tables
   // are read through L1 (the table keeps the reads to a handful per support call): nothing is staged in shared memory,
   // so the whole of L1 stays with the polytopes (measured on C4: 8.1 -> 7.0 ms against per-warp TMA staging)
@@ -320,7 +325,7 @@ __global__ void __launch_bounds__(128, MINB) k_epa_wp(SceneView v, Work w)
     if (lane == 0)
       group = static_cast<int>(atomicAdd(reinterpret_cast<unsigned long long*>(&w.counters->epa_cursor_g), 32ull));
     group = __shfl_sync(0xffffffffu, group, 0);
-    if (group >= w.n_items_padded)
+    if (group >= n_items_padded)
       break;
     if (sp < 0 || group >= bucket_end)
     {

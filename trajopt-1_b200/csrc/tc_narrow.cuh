@@ -691,7 +691,41 @@ struct EpaState
   unsigned long long alive;  // live-face mask (MASK mode)
   R bd, eps_len, vis_eps;
   Vec3<R> centroid;
+  // stall exit (curved cores, and every pair in FP32 mode): running minimum of the support values, the narrowest
+  // bracket [closest face, that minimum] seen so far and the trips since it last narrowed by 10 %
+  R ub_best, width_best;
+  int stall;
+  bool stall_exit;
 };
+
+// Stall exit.  EPA brackets the penetration depth between the closest face of the polytope (bd, never decreasing) and
+// the smallest support value found along a face normal (never increasing); it is done when the bracket closes to
+// epaTol.  On a polytope that happens after finitely many trips.  On a CURVED core (cylinder, cone) every new vertex
+// lies on the surface next to the previous ones, the faces become slivers whose plane distance carries ~1e-10 m of
+// rounding, and a few items then dither at the tolerance for a hundred trips without narrowing the bracket; in FP32 the
+// same happens on every shape at ~1e-6.  EPA_STALL_TRIPS trips without narrowing the bracket by 10 % therefore end the
+// expansion on the current closest face.  The CPU checker applies the same rule to curved cores (it has no FP32 mode);
+// hull / sphere / capsule pairs in FP64 never take this exit, there the gap test alone decides.
+enum
+{
+  EPA_STALL_TRIPS = 6
+};
+template <class R>
+TC_HD bool epaStalled(EpaState<R>& E, R support_value)
+{
+  if (!E.stall_exit)
+    return false;
+  if (support_value < E.ub_best)
+    E.ub_best = support_value;
+  const R width = E.ub_best - E.bd;
+  if (width < R(0.9) * E.width_best)
+  {
+    E.width_best = width;
+    E.stall = 0;
+    return false;
+  }
+  return ++E.stall >= EPA_STALL_TRIPS;
+}
 
 template <class R, bool MASK>
 TC_HD bool epaIsAlive(const EpaState<R>& E, const EpaStore<R>& st, int f)
@@ -896,6 +930,10 @@ TC_HDN int epaInit(const Placed<R>& A, const Placed<R>& B, const Simplex<R>& sta
   E.best = -1;
   E.bd = 0;
   E.iters = 1;
+  E.ub_best = -lowestReal<R>();
+  E.width_best = -lowestReal<R>();
+  E.stall = 0;
+  E.stall_exit = sizeof(R) == sizeof(float) || A.sh.type >= SH_CYLINDER || B.sh.type >= SH_CYLINDER;
   E.centroid = R(0.25) * (st.pw[0] + st.pw[1] + st.pw[2] + st.pw[3]);
   R d;
   int f = epaAddFace<R, MASK>(E, st, 0, 1, 2, true, d);
@@ -942,7 +980,8 @@ TC_HD int epaTripMasked(const Placed<R>& A, const Placed<R>& B, EpaStore<R>& st,
   const Vec3<R> bn = st.fn[E.best];
   const Vec3<R> xa = A.support(bn, scanned), xb = B.support(-bn, scanned);
   const Vec3<R> xw = xa - xb;
-  if (dot(bn, xw) - E.bd <= Tol<R>::epaTol())
+  const R sv = dot(bn, xw);
+  if (sv - E.bd <= Tol<R>::epaTol() || epaStalled(E, sv))
     return EPA_DONE;
   if (E.iters == EPA_MAX_ITERS)
     return EPA_UNCONVERGED;
@@ -1061,7 +1100,8 @@ TC_HDN int epaTrip(const Placed<R>& A, const Placed<R>& B, EpaStore<R>& st, EpaS
   const Vec3<R> bn = st.fn[E.best];
   const Vec3<R> xa = A.support(bn, scanned), xb = B.support(-bn, scanned);
   const Vec3<R> xw = xa - xb;
-  if (dot(bn, xw) - E.bd <= Tol<R>::epaTol())
+  const R sv = dot(bn, xw);
+  if (sv - E.bd <= Tol<R>::epaTol() || epaStalled(E, sv))
     return EPA_DONE;
   if (E.iters == EPA_MAX_ITERS)
     return EPA_UNCONVERGED;

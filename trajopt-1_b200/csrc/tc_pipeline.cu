@@ -160,7 +160,9 @@ __global__ void __launch_bounds__(1024) k_scan_terms(Work w)
     w.counters->n_states = carry_s;
     w.counters->n_units = carry_u;
     if (carry_s > 2000000000ll)
-      w.counters->overflow = 3;
+      w.counters->overflow = OVF_INDEX_STATES;
+    else if (w.speculative && (carry_s > w.n_states || carry_u > w.n_units) && w.counters->overflow == 0)
+      w.counters->overflow = OVF_SPECULATION;
   }
 }
 
@@ -192,58 +194,63 @@ __device__ __forceinline__ void loadBox(const Work& w, int a, long long s0, long
   }
 }
 
+// consecutive 128-unit chunks one block works through: the partner tile (and the two counter loads) are paid once per
+// block instead of once per chunk
+#ifndef TC_BROAD_CPB
+#define TC_BROAD_CPB 4
+#endif
 template <bool FILL>
 __global__ void __launch_bounds__(TPB) k_broad(SceneView v, Work w)
 {
-  const long long u = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (passOverflowed(w))
+    return;
+  const long long n_units = w.counters->n_units;
   const int a = blockIdx.y;
-  const bool inb = u < w.n_units;
   const unsigned lane = threadIdx.x & 31;
   const int p_begin = v.partner_ptr[a], p_end = v.partner_ptr[a + 1];
   uint32_t* mask = w.bp_mask + static_cast<size_t>(v.partner_word_ptr[a]) * static_cast<size_t>(w.n_units);
   if (FILL)
   {
     // replay the survivors the counting pass found: no AABB is read again
-    long long s0 = 0;
-    if (inb)
+    for (int c = 0; c < TC_BROAD_CPB; ++c)
     {
-      const int k = w.unit_term[u];
-      s0 = w.state_base[k] + (u - w.unit_base[k]);
-    }
-    uint32_t bits = 0;
-    for (int pi = p_begin; pi < p_end; ++pi)
-    {
-      const int j = (pi - p_begin) & 31;
-      if (j == 0)
-        bits = inb ? mask[static_cast<size_t>((pi - p_begin) >> 5) * static_cast<size_t>(w.n_units) + u] : 0u;
-      const bool overlap = (bits >> j) & 1u;
-      const unsigned m = __ballot_sync(0xffffffffu, overlap);
-      if (m == 0)
-        continue;
-      const int sp = v.partner_sp[pi];
-      const int leader = __ffs(m) - 1;
-      int base = 0;
-      if (lane == leader)
-        base = atomicAdd(&w.sp_cursor[sp], __popc(m));
-      base = __shfl_sync(0xffffffffu, base, leader);
-      if (overlap)
+      const long long u0 = (static_cast<long long>(blockIdx.x) * TC_BROAD_CPB + c) * blockDim.x;
+      if (u0 >= n_units)
+        break;
+      const long long u = u0 + threadIdx.x;
+      const bool inb = u < n_units;
+      long long s0 = 0;
+      if (inb)
       {
-        const int slot = w.sp_offset[sp] + base + __popc(m & ((1u << lane) - 1u));
-        w.items[slot] = static_cast<int32_t>(u);
-        w.item_state[slot] = static_cast<int32_t>(s0);
+        const int k = w.unit_term[u];
+        s0 = w.state_base[k] + (u - w.unit_base[k]);
+      }
+      uint32_t bits = 0;
+      for (int pi = p_begin; pi < p_end; ++pi)
+      {
+        const int j = (pi - p_begin) & 31;
+        if (j == 0)
+          bits = inb ? mask[static_cast<size_t>((pi - p_begin) >> 5) * static_cast<size_t>(w.n_units) + u] : 0u;
+        const bool overlap = (bits >> j) & 1u;
+        const unsigned m = __ballot_sync(0xffffffffu, overlap);
+        if (m == 0)
+          continue;
+        const int sp = v.partner_sp[pi];
+        const int leader = __ffs(m) - 1;
+        int base = 0;
+        if (lane == leader)
+          base = atomicAdd(&w.sp_cursor[sp], __popc(m));
+        base = __shfl_sync(0xffffffffu, base, leader);
+        if (overlap)
+        {
+          const int slot = w.sp_offset[sp] + base + __popc(m & ((1u << lane) - 1u));
+          w.items[slot] = static_cast<int32_t>(u);
+          w.item_state[slot] = static_cast<int32_t>(s0);
+        }
       }
     }
     return;
   }
-  long long s0 = 0, s1 = 0;
-  if (inb)
-  {
-    const int k = w.unit_term[u];
-    s0 = w.state_base[k] + (u - w.unit_base[k]);
-    s1 = w.cast ? s0 + 1 : s0;
-  }
-  double alo[3], ahi[3];
-  loadBox(w, a, s0, s1, alo, ahi);
   // the partner list is the same for the whole block: its records (threshold, partner box or partner shape) are
   // gathered once per tile into shared memory instead of being chased through four tables by every thread
   struct Partner
@@ -253,74 +260,95 @@ __global__ void __launch_bounds__(TPB) k_broad(SceneView v, Work w)
   };
   constexpr int TILE = 32;
   __shared__ Partner tile[TILE];
-  uint32_t bits = 0;
-  // box of the warp's 32 units (mostly consecutive sub-segments of one trajectory): a static partner that misses it
-  // misses every lane, and is dismissed with one warp-uniform test instead of 32 tests, a ballot and a branch
-  double wlo[3], whi[3];
-#pragma unroll
-  for (int r = 0; r < 3; ++r)
+  const bool single_tile = p_end - p_begin <= TILE;  // then the tile staged for the first chunk serves them all
+  for (int c = 0; c < TC_BROAD_CPB; ++c)
   {
-    wlo[r] = inb ? alo[r] : 1e300;
-    whi[r] = inb ? ahi[r] : -1e300;
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1)
-    {
-      wlo[r] = fmin(wlo[r], __shfl_xor_sync(0xffffffffu, wlo[r], o));
-      whi[r] = fmax(whi[r], __shfl_xor_sync(0xffffffffu, whi[r], o));
-    }
-  }
-  for (int t0 = p_begin; t0 < p_end; t0 += TILE)
-  {
-    const int tn = min(TILE, p_end - t0);
-    __syncthreads();
-    if (static_cast<int>(threadIdx.x) < tn)
-    {
-      Partner pr;
-      pr.sp = v.partner_sp[t0 + threadIdx.x];
-      const ShapePairD spd = v.spairs[pr.sp];
-      pr.thr = v.pairs[spd.pair].thr;
-      pr.bidx = v.shapes[spd.sb].active_index;
-#pragma unroll
-      for (int r = 0; r < 3; ++r)
-      {
-        pr.lo[r] = pr.bidx < 0 ? v.static_aabb[6 * spd.sb + r] : 0.0;
-        pr.hi[r] = pr.bidx < 0 ? v.static_aabb[6 * spd.sb + 3 + r] : 0.0;
-      }
-      tile[threadIdx.x] = pr;
-    }
-    __syncthreads();
-    for (int j = 0; j < tn; ++j)
-    {
-      const Partner& pr = tile[j];
-      double blo[3], bhi[3];
-      if (pr.bidx < 0)
-      {
-        bool miss = false;
-#pragma unroll
-        for (int r = 0; r < 3; ++r)
-          if (wlo[r] - pr.hi[r] > pr.thr || pr.lo[r] - whi[r] > pr.thr)
-            miss = true;
-        if (miss)
-          continue;
-#pragma unroll
-        for (int r = 0; r < 3; ++r)
-          blo[r] = pr.lo[r], bhi[r] = pr.hi[r];
-      }
-      else
-        loadBox(w, pr.bidx, s0, s1, blo, bhi);
-      bool overlap = inb;
-#pragma unroll
-      for (int r = 0; r < 3; ++r)
-        if (alo[r] - bhi[r] > pr.thr || blo[r] - ahi[r] > pr.thr)
-          overlap = false;
-      bits |= (overlap ? 1u : 0u) << j;
-      const unsigned m = __ballot_sync(0xffffffffu, overlap);
-      if (m && lane == static_cast<unsigned>(__ffs(m) - 1))
-        atomicAdd(&w.sp_count[pr.sp], __popc(m));
-    }
+    const long long u0 = (static_cast<long long>(blockIdx.x) * TC_BROAD_CPB + c) * blockDim.x;
+    if (u0 >= n_units)
+      break;
+    const long long u = u0 + threadIdx.x;
+    const bool inb = u < n_units;
+    long long s0 = 0, s1 = 0;
     if (inb)
-      mask[static_cast<size_t>((t0 - p_begin) >> 5) * static_cast<size_t>(w.n_units) + u] = bits;
-    bits = 0;
+    {
+      const int k = w.unit_term[u];
+      s0 = w.state_base[k] + (u - w.unit_base[k]);
+      s1 = w.cast ? s0 + 1 : s0;
+    }
+    double alo[3], ahi[3];
+    loadBox(w, a, s0, s1, alo, ahi);
+    uint32_t bits = 0;
+    // box of the warp's 32 units (mostly consecutive sub-segments of one trajectory): a static partner that misses it
+    // misses every lane, and is dismissed with one warp-uniform test instead of 32 tests, a ballot and a branch
+    double wlo[3], whi[3];
+#pragma unroll
+    for (int r = 0; r < 3; ++r)
+    {
+      wlo[r] = inb ? alo[r] : 1e300;
+      whi[r] = inb ? ahi[r] : -1e300;
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1)
+      {
+        wlo[r] = fmin(wlo[r], __shfl_xor_sync(0xffffffffu, wlo[r], o));
+        whi[r] = fmax(whi[r], __shfl_xor_sync(0xffffffffu, whi[r], o));
+      }
+    }
+    for (int t0 = p_begin; t0 < p_end; t0 += TILE)
+    {
+      const int tn = min(TILE, p_end - t0);
+      if (!(single_tile && c > 0))
+      {
+        __syncthreads();
+        if (static_cast<int>(threadIdx.x) < tn)
+        {
+          Partner pr;
+          pr.sp = v.partner_sp[t0 + threadIdx.x];
+          const ShapePairD spd = v.spairs[pr.sp];
+          pr.thr = v.pairs[spd.pair].thr;
+          pr.bidx = v.shapes[spd.sb].active_index;
+#pragma unroll
+          for (int r = 0; r < 3; ++r)
+          {
+            pr.lo[r] = pr.bidx < 0 ? v.static_aabb[6 * spd.sb + r] : 0.0;
+            pr.hi[r] = pr.bidx < 0 ? v.static_aabb[6 * spd.sb + 3 + r] : 0.0;
+          }
+          tile[threadIdx.x] = pr;
+        }
+        __syncthreads();
+      }
+      for (int j = 0; j < tn; ++j)
+      {
+        const Partner& pr = tile[j];
+        double blo[3], bhi[3];
+        if (pr.bidx < 0)
+        {
+          bool miss = false;
+#pragma unroll
+          for (int r = 0; r < 3; ++r)
+            if (wlo[r] - pr.hi[r] > pr.thr || pr.lo[r] - whi[r] > pr.thr)
+              miss = true;
+          if (miss)
+            continue;
+#pragma unroll
+          for (int r = 0; r < 3; ++r)
+            blo[r] = pr.lo[r], bhi[r] = pr.hi[r];
+        }
+        else
+          loadBox(w, pr.bidx, s0, s1, blo, bhi);
+        bool overlap = inb;
+#pragma unroll
+        for (int r = 0; r < 3; ++r)
+          if (alo[r] - bhi[r] > pr.thr || blo[r] - ahi[r] > pr.thr)
+            overlap = false;
+        bits |= (overlap ? 1u : 0u) << j;
+        const unsigned m = __ballot_sync(0xffffffffu, overlap);
+        if (m && lane == static_cast<unsigned>(__ffs(m) - 1))
+          atomicAdd(&w.sp_count[pr.sp], __popc(m));
+      }
+      if (inb)
+        mask[static_cast<size_t>((t0 - p_begin) >> 5) * static_cast<size_t>(w.n_units) + u] = bits;
+      bits = 0;
+    }
   }
 }
 
@@ -328,6 +356,8 @@ __global__ void __launch_bounds__(TPB) k_broad(SceneView v, Work w)
 __global__ void __launch_bounds__(1024) k_scan_sp(SceneView v, Work w)
 {
   __shared__ long long sm[33];
+  if (passOverflowed(w))
+    return;
   long long carry = 0, raw_total = 0;
   const int n = v.n_spairs;
   for (int base = 0; base < n; base += blockDim.x)
@@ -349,7 +379,9 @@ __global__ void __launch_bounds__(1024) k_scan_sp(SceneView v, Work w)
     w.counters->n_items_padded = carry;
     w.counters->n_items = raw_total;
     if (carry > 2000000000ll)
-      w.counters->overflow = 4;
+      w.counters->overflow = OVF_INDEX_ITEMS;
+    else if (w.speculative && carry > w.n_items_padded && w.counters->overflow == 0)
+      w.counters->overflow = OVF_SPECULATION;
   }
 }
 
@@ -378,9 +410,24 @@ __device__ __forceinline__ UnitInfo unitInfo(const Work& w, int u)
 
 __global__ void __launch_bounds__(TPB, TC_FINALIZE_MINB) k_finalize(SceneView v, Work w)
 {
+  if (passOverflowed(w))
+    return;
   const long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+  const long long n_raw = w.counters->n_raw;
+  if (n_raw > w.n_sort)
+  {
+    // more raw hits than the key sort was sized for (speculative pass): nothing may be written past the arenas
+    if (i == 0)
+      w.counters->overflow = OVF_SPECULATION;
+    return;
+  }
   bool valid = false;
-  if (i < w.n_raw)
+  if (i >= n_raw && i < w.n_sort)
+  {
+    w.keys[i] = ~0ull;  // surplus entries of the sort: sorted behind every contact
+    w.idx[i] = static_cast<int32_t>(i);
+  }
+  if (i < n_raw)
   {
     const RawContact raw = w.raw[i];
     const UnitInfo ui = unitInfo(w, raw.unit);
@@ -438,9 +485,17 @@ __global__ void __launch_bounds__(TPB, TC_FINALIZE_MINB) k_finalize(SceneView v,
 // the chosen hit of every group if it also passed the evaluator's filters, all-ones otherwise.
 __global__ void __launch_bounds__(TPB) k_type_select(Work w, const uint8_t* valid)
 {
+  if (passOverflowed(w))
+    return;
   const long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+  const long long n_raw = w.counters->n_raw;
   bool keep = false;
-  if (i < w.n_raw)
+  if (i >= n_raw && i < w.n_sort)
+  {
+    w.keys[i] = ~0ull;
+    w.idx[i] = w.idx_alt[i];
+  }
+  if (i < n_raw)
   {
     const unsigned long long key = w.keys_alt[i];
     unsigned long long out = ~0ull;
@@ -453,16 +508,19 @@ __global__ void __launch_bounds__(TPB) k_type_select(Work w, const uint8_t* vali
     }
     else
     {
-      // closest of the link pair in this unit: smallest distance, first in shape-pair order on ties
+      // closest of the link pair in this unit: the first result, in shape-pair order, within 1e-9 m of the smallest
+      // distance (sub-shapes of a compound link share faces: exact ties that the last bit would otherwise decide)
+      const double CLOSEST_TIE = 1e-9;
       const unsigned long long g = key >> 8;
       const double mine = w.contacts_tmp[w.idx_alt[i]].distance;
-      bool best = true;
+      double dmin = mine, dmin_before = 1e300;
       for (long long j = i - 1; j >= 0 && (w.keys_alt[j] >> 8) == g; --j)
-        if (w.contacts_tmp[w.idx_alt[j]].distance <= mine)
-          best = false;
-      for (long long j = i + 1; j < w.n_raw && (w.keys_alt[j] >> 8) == g; ++j)
-        if (w.contacts_tmp[w.idx_alt[j]].distance < mine)
-          best = false;
+        dmin_before = fmin(dmin_before, w.contacts_tmp[w.idx_alt[j]].distance);
+      dmin = fmin(dmin, dmin_before);
+      for (long long j = i + 1; j < n_raw && (w.keys_alt[j] >> 8) == g; ++j)
+        dmin = fmin(dmin, w.contacts_tmp[w.idx_alt[j]].distance);
+      // chosen = inside the band and nothing before it is
+      const bool best = mine <= dmin + CLOSEST_TIE && !(dmin_before <= dmin + CLOSEST_TIE);
       keep = best && valid[w.idx_alt[i]];
       out = key;
     }
@@ -497,18 +555,20 @@ __device__ __forceinline__ void contactTransforms(const SceneView& v, const Work
 __global__ void __launch_bounds__(TPB) k_transforms(SceneView v, Work w, double* xf)
 {
   const long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
-  if (i < w.n_contacts)
+  if (i < w.counters->n_valid)
     contactTransforms(v, w, w.contacts[i], xf + i * 48);
 }
 
 // sorted order -> final array, one thread per 8-byte word of tc_contact
 __global__ void __launch_bounds__(256) k_gather(Work w, const int32_t* idx)
 {
+  if (passOverflowed(w))
+    return;
   constexpr int WC = sizeof(tc_contact) / 8;
   const long long g = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
   const long long i = g / WC;
   const int word = static_cast<int>(g % WC);
-  if (i >= w.n_contacts)
+  if (i >= w.counters->n_valid)
     return;
   const long long src = idx[i];
   reinterpret_cast<double*>(w.contacts + i)[word] = reinterpret_cast<const double*>(w.contacts_tmp + src)[word];
@@ -516,11 +576,13 @@ __global__ void __launch_bounds__(256) k_gather(Work w, const int32_t* idx)
 
 __global__ void k_term_ptr(Work w, const unsigned long long* keys)
 {
+  if (passOverflowed(w))
+    return;
   const int k = blockIdx.x * blockDim.x + threadIdx.x;
   if (k > w.ep.n_terms)
     return;
   const unsigned long long target = static_cast<unsigned long long>(k) << 36;
-  long long lo = 0, hi = w.n_contacts;  // first index with key >= target
+  long long lo = 0, hi = w.counters->n_valid;  // first index with key >= target
   while (lo < hi)
   {
     const long long mid = (lo + hi) >> 1;
@@ -553,8 +615,10 @@ __device__ __forceinline__ int termOfContact(const Work& w, long long i)
 template <int NMAX>
 __global__ void __launch_bounds__(TPB) k_grad(SceneView v, Work w)
 {
+  if (passOverflowed(w))
+    return;
   const long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
-  if (i >= w.n_contacts)
+  if (i >= w.counters->n_valid)
     return;
   const tc_contact c = w.contacts[i];
   const int ti = termOfContact(w, i) % w.ep.terms_per_traj;
@@ -573,6 +637,8 @@ __global__ void __launch_bounds__(TPB) k_grad(SceneView v, Work w)
 // per-term row offsets: rows of a term all have n_dof * (#free blocks) entries
 __global__ void __launch_bounds__(1024) k_row_base(SceneView v, Work w, long long* term_row_base)
 {
+  if (passOverflowed(w))
+    return;
   __shared__ long long sm[33];
   long long carry = 0;
   const int n = w.ep.n_terms;
@@ -618,6 +684,7 @@ __device__ __forceinline__ void writeRow(const SceneView& v, const Work& w, long
   w.row_ptr[i] = nnz;
   w.row_block[2 * i] = f0 ? -1 : c.term * n;
   w.row_block[2 * i + 1] = (single || f1) ? -1 : (c.term + 1) * n;
+  w.row_pair[i] = c.pair;
   const PairD pr = v.pairs[c.pair];
   const double* q0 = w.q + (static_cast<size_t>(c.traj) * w.ep.T + c.term) * n;
   double constant = c.distance;
@@ -654,10 +721,12 @@ __device__ __forceinline__ void writeRow(const SceneView& v, const Work& w, long
 __global__ void __launch_bounds__(TPB) k_rows(SceneView v, Work w, const long long* term_row_base, int32_t* col_idx,
                                               double* val, double* row_value, double* row_coeff, double* row_margin)
 {
-  const long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
-  if (i > w.n_contacts)
+  if (passOverflowed(w))
     return;
-  if (i == w.n_contacts)
+  const long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (i > w.counters->n_valid)
+    return;
+  if (i == w.counters->n_valid)
   {
     w.row_ptr[i] = term_row_base[w.ep.n_terms];
     return;
@@ -671,20 +740,26 @@ __global__ void __launch_bounds__(TPB) k_rows(SceneView v, Work w, const long lo
 #ifndef TC_GRADROWS_MINB
 #define TC_GRADROWS_MINB 6
 #endif
-template <int NMAX>
+// GATHER: the kernel also is the gather of the sorted order — it takes its contact from the unsorted arena through the
+// sorted index and writes the final record itself, so k_gather's separate pass over 2 x 200 bytes per contact is saved
+template <int NMAX, bool GATHER>
 __global__ void __launch_bounds__(TPB, TC_GRADROWS_MINB) k_grad_rows(SceneView v, Work w, const long long* term_row_base, int32_t* col_idx,
                                                    double* val, double* row_value, double* row_coeff,
                                                    double* row_margin)
 {
-  const long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
-  if (i > w.n_contacts)
+  if (passOverflowed(w))
     return;
-  if (i == w.n_contacts)
+  const long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (i > w.counters->n_valid)
+    return;
+  if (i == w.counters->n_valid)
   {
     w.row_ptr[i] = term_row_base[w.ep.n_terms];
     return;
   }
-  const tc_contact c = w.contacts[i];
+  const tc_contact c = GATHER ? w.contacts_tmp[w.idx_alt[i]] : w.contacts[i];
+  if (GATHER)
+    w.contacts[i] = c;
   const int ti = termOfContact(w, i) % w.ep.terms_per_traj;
   const int n = v.n_dof;
   const double* q0 = w.q + (static_cast<size_t>(c.traj) * w.ep.T + c.term) * n;
@@ -775,7 +850,7 @@ __global__ void __launch_bounds__(256) k_csc_colptr(SceneView v, Work w, const l
     const long long c = (bt_base[e + 1] - bt_base[e]) / v.n_dof;
     col_ptr[g] = bt_base[e] + j * c;
   }
-  else if (g <= n_x + w.n_contacts)
+  else if (g <= n_x + w.counters->n_valid)
     col_ptr[g] = nnz_x + (g - n_x);  // slack columns hold one entry each; the last value closes the array
 }
 
@@ -785,7 +860,7 @@ __global__ void __launch_bounds__(TPB) k_csc_fill(SceneView v, Work w, const lon
                                                   double* upper, double* slack_cost)
 {
   const long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
-  if (i >= w.n_contacts)
+  if (i >= w.counters->n_valid)
     return;
   const int k = termOfContact(w, i);
   const int tpt = w.ep.terms_per_traj;
@@ -840,6 +915,8 @@ __global__ void __launch_bounds__(TPB) k_csc_fill(SceneView v, Work w, const lon
 // CollisionCost::value / CollisionConstraint::value (collision_terms.cpp:1287-1306,1367-1386)
 __global__ void __launch_bounds__(TPB) k_cost_term(SceneView v, Work w, double* cost_term)
 {
+  if (passOverflowed(w))
+    return;
   // one warp per term: lanes stride over the term's contacts, fixed-order tree reduction
   const int k = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const unsigned lane = threadIdx.x & 31;
@@ -866,6 +943,44 @@ __global__ void k_cost_traj(Work w, const double* cost_term, double* cost_traj)
   for (int ti = 0; ti < w.ep.terms_per_traj; ++ti)
     out += cost_term[static_cast<size_t>(b) * w.ep.terms_per_traj + ti];
   cost_traj[b] = out;
+}
+
+// multi-start winner of this rank, left on the device for the all-gather: one block, arg-min over the
+// per-trajectory costs with the lowest index winning ties, then the winner's joint values
+__global__ void __launch_bounds__(1024) k_best_record(Work w, const double* cost_traj, long long index_offset, double* rec, int n_dof)
+{
+  __shared__ double s_cost[1024];
+  __shared__ int s_idx[1024];
+  double best = 1.7976931348623157e308;
+  int bi = 0x7fffffff;
+  for (int b = threadIdx.x; b < w.ep.B; b += blockDim.x)
+  {
+    const double c = cost_traj[b];
+    if (c < best || (c == best && b < bi))
+      best = c, bi = b;
+  }
+  s_cost[threadIdx.x] = best, s_idx[threadIdx.x] = bi;
+  __syncthreads();
+  for (int o = blockDim.x / 2; o > 0; o >>= 1)
+  {
+    if (static_cast<int>(threadIdx.x) < o)
+    {
+      const double c = s_cost[threadIdx.x + o];
+      const int i = s_idx[threadIdx.x + o];
+      if (c < s_cost[threadIdx.x] || (c == s_cost[threadIdx.x] && i < s_idx[threadIdx.x]))
+        s_cost[threadIdx.x] = c, s_idx[threadIdx.x] = i;
+    }
+    __syncthreads();
+  }
+  const int win = s_idx[0];
+  if (threadIdx.x == 0)
+  {
+    rec[0] = s_cost[0];
+    reinterpret_cast<long long*>(rec)[1] = index_offset + win;
+  }
+  const int nv = w.ep.T * n_dof;
+  for (int e = threadIdx.x; e < nv; e += blockDim.x)
+    rec[2 + e] = w.q[static_cast<size_t>(win) * nv + e];
 }
 
 // GradientResultsSet grouping, ordering and the fixed-size constraint rows
@@ -1215,7 +1330,7 @@ cudaError_t launchBroadCount(const SceneView& v, const Work& w, cudaStream_t st)
   e = launchFill(w.sp_cursor, 0, v.n_spairs, st);
   if (e != cudaSuccess)
     return e;
-  const dim3 grid(gridFor(w.n_units, TPB), static_cast<unsigned>(v.n_active_shapes));
+  const dim3 grid(gridFor(w.n_units, TPB * TC_BROAD_CPB), static_cast<unsigned>(v.n_active_shapes));
   ++launchCounter();
   k_broad<false><<<grid, TPB, 0, st>>>(v, w);
   ++launchCounter();
@@ -1228,7 +1343,7 @@ cudaError_t launchBroadFill(const SceneView& v, const Work& w, cudaStream_t st)
   cudaError_t e = launchFill(w.items, 0xffffffffu, static_cast<size_t>(w.n_items_padded), st);
   if (e != cudaSuccess)
     return e;
-  const dim3 grid(gridFor(w.n_units, TPB), static_cast<unsigned>(v.n_active_shapes));
+  const dim3 grid(gridFor(w.n_units, TPB * TC_BROAD_CPB), static_cast<unsigned>(v.n_active_shapes));
   ++launchCounter();
   k_broad<true><<<grid, TPB, 0, st>>>(v, w);
   return cudaGetLastError();
@@ -1236,10 +1351,10 @@ cudaError_t launchBroadFill(const SceneView& v, const Work& w, cudaStream_t st)
 
 cudaError_t launchFinalize(const SceneView& v, const Work& w, cudaStream_t st)
 {
-  if (w.n_raw > 0)
+  if (w.n_sort > 0)
   {
     ++launchCounter();
-    k_finalize<<<gridFor(w.n_raw, TPB), TPB, 0, st>>>(v, w);
+    k_finalize<<<gridFor(w.n_sort, TPB), TPB, 0, st>>>(v, w);
   }
   return cudaGetLastError();
 }
@@ -1247,10 +1362,10 @@ cudaError_t launchFinalize(const SceneView& v, const Work& w, cudaStream_t st)
 cudaError_t launchTypeFilter(const SceneView& v, const Work& w, const uint8_t* valid, cudaStream_t st)
 {
   (void)v;
-  if (w.n_raw > 0)
+  if (w.n_sort > 0)
   {
     ++launchCounter();
-    k_type_select<<<gridFor(w.n_raw, TPB), TPB, 0, st>>>(w, valid);
+    k_type_select<<<gridFor(w.n_sort, TPB), TPB, 0, st>>>(w, valid);
   }
   return cudaGetLastError();
 }
@@ -1263,13 +1378,13 @@ cudaError_t sortContacts(const Work& w, void* temp, size_t& temp_bytes, cudaStre
   while (end_bit < 64 && (static_cast<long long>(w.ep.n_terms) >> (end_bit - 36)) != 0)
     ++end_bit;
   return cub::DeviceRadixSort::SortPairs(temp, temp_bytes, w.keys, w.keys_alt, w.idx, w.idx_alt,
-                                         static_cast<int>(w.n_raw), 0, end_bit, st);
+                                         static_cast<int>(w.n_sort), 0, end_bit, st);
 }
 
 cudaError_t launchGather(const SceneView& v, const Work& w, cudaStream_t st)
 {
   (void)v;
-  if (w.n_contacts > 0)
+  if (w.n_contacts > 0 && !w.gather_in_rows)
   {
     const long long words = w.n_contacts * (static_cast<long long>(sizeof(tc_contact)) / 8);
     ++launchCounter();
@@ -1323,12 +1438,18 @@ cudaError_t launchGradRows(const SceneView& v, const Work& w, long long* term_ro
                            double* row_value, double* row_coeff, double* row_margin, cudaStream_t st)
 {
   ++launchCounter();
-  if (v.n_dof <= 8)
-    k_grad_rows<8><<<gridFor(w.n_contacts + 1, TPB), TPB, 0, st>>>(v, w, term_row_base, col_idx, val, row_value,
-                                                                    row_coeff, row_margin);
+  const unsigned grid = gridFor(w.n_contacts + 1, TPB);
+  if (w.gather_in_rows)
+  {
+    if (v.n_dof <= 8)
+      k_grad_rows<8, true><<<grid, TPB, 0, st>>>(v, w, term_row_base, col_idx, val, row_value, row_coeff, row_margin);
+    else
+      k_grad_rows<64, true><<<grid, TPB, 0, st>>>(v, w, term_row_base, col_idx, val, row_value, row_coeff, row_margin);
+  }
+  else if (v.n_dof <= 8)
+    k_grad_rows<8, false><<<grid, TPB, 0, st>>>(v, w, term_row_base, col_idx, val, row_value, row_coeff, row_margin);
   else
-    k_grad_rows<64><<<gridFor(w.n_contacts + 1, TPB), TPB, 0, st>>>(v, w, term_row_base, col_idx, val, row_value,
-                                                                     row_coeff, row_margin);
+    k_grad_rows<64, false><<<grid, TPB, 0, st>>>(v, w, term_row_base, col_idx, val, row_value, row_coeff, row_margin);
   return cudaGetLastError();
 }
 
@@ -1338,6 +1459,14 @@ cudaError_t launchCost(const SceneView& v, const Work& w, double* cost_term, dou
   k_cost_term<<<gridFor(static_cast<long long>(w.ep.n_terms) * 32, TPB), TPB, 0, st>>>(v, w, cost_term);
   ++launchCounter();
   k_cost_traj<<<gridFor(w.ep.B, TPB), TPB, 0, st>>>(w, cost_term, cost_traj);
+  return cudaGetLastError();
+}
+
+cudaError_t launchBestRecord(const Work& w, const double* cost_traj, long long index_offset, double* rec, cudaStream_t st)
+{
+  ++launchCounter();
+  // n_dof is not in Work: the trajectory stride follows from the batch layout q[B][T][n_dof]
+  k_best_record<<<1, 1024, 0, st>>>(w, cost_traj, index_offset, rec, w.n_dof_q);
   return cudaGetLastError();
 }
 

@@ -53,8 +53,10 @@ __device__ __forceinline__ void writeShapeAabb(const Work& w, const Pose<double>
 
 __global__ void k_unit_term(Work w)
 {
+  if (passOverflowed(w))
+    return;
   const int u = blockIdx.x * blockDim.x + threadIdx.x;
-  if (u < w.n_units)
+  if (u < w.counters->n_units)
     w.unit_term[u] = lastLE(w.unit_base, w.ep.n_terms, u);
 }
 
@@ -70,6 +72,8 @@ __global__ void k_unit_term(Work w)
 #endif
 __global__ void __launch_bounds__(TPB, TC_FK_MINB) k_fk(SceneView v, Work w)
 {
+  if (passOverflowed(w) || static_cast<long long>(blockIdx.x) * blockDim.x >= w.counters->n_states)
+    return;  // uniform over the block
   // per-warp staging tile: 32 poses, rows padded to 13 doubles (bank spread)
   __shared__ double tile[TPB / 32][32 * 13];
   // the kinematic tables are the same for every thread: one copy per block in shared memory (small scenes; large
@@ -106,12 +110,13 @@ __global__ void __launch_bounds__(TPB, TC_FK_MINB) k_fk(SceneView v, Work w)
     t.frame_origin = s_origin, t.frame_axis = s_axis, t.frame_parent = s_parent, t.frame_type = s_type;
     t.frame_dof = s_dof, t.frame_link = s_flink, t.link_frame = s_lframe, t.active_shape_frame = s_sframe;
   }
+  const long long n_states = w.counters->n_states;  // actual count; w.n_states is the arenas' state stride (>= count)
   const long long s_raw = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
-  const bool live = s_raw < w.n_states;
-  const long long s = live ? s_raw : w.n_states - 1;  // idle lanes shadow the last state and write nothing
+  const bool live = s_raw < n_states;
+  const long long s = live ? s_raw : n_states - 1;  // idle lanes shadow the last state and write nothing
   const unsigned lane = threadIdx.x & 31;
   const long long warp_s0 = s_raw - lane;
-  const int warp_n = static_cast<int>(min(32ll, w.n_states - warp_s0));  // live lanes of this warp (may be <= 0)
+  const int warp_n = static_cast<int>(min(32ll, n_states - warp_s0));  // live lanes of this warp (may be <= 0)
   double* my_tile = tile[threadIdx.x >> 5];
   const int k = lastLE(w.state_base, w.ep.n_terms, static_cast<int>(s));
   const int i = static_cast<int>(s) - w.state_base[k];
@@ -209,7 +214,7 @@ __global__ void __launch_bounds__(TPB, TC_FK_MINB) k_fk(SceneView v, Work w)
 __global__ void __launch_bounds__(TPB) k_pose_in(SceneView v, Work w)
 {
   const long long s = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
-  if (s >= w.n_states)
+  if (passOverflowed(w) || s >= w.counters->n_states)
     return;
   const int spt = w.cast ? 2 : 1;
   const long long k = s / spt;
@@ -232,6 +237,8 @@ __global__ void __launch_bounds__(TPB) k_pose_in(SceneView v, Work w)
 // every item of the shape pairs with a curved core -> the deep list (k_gjk skips those buckets)
 __global__ void __launch_bounds__(256) k_route_curved(SceneView v, Work w)
 {
+  if (passOverflowed(w))
+    return;
   const int sp = v.curved_sp[blockIdx.y];
   const int off = w.sp_offset[sp], n = w.sp_count[sp];
   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
@@ -248,6 +255,10 @@ template <class R>
 __global__ void __launch_bounds__(64) k_narrow_deep(SceneView v, Work w, long long n_deep, unsigned char* scratch,
                                                     size_t bytes_per_thread)
 {
+  if (passOverflowed(w))
+    return;
+  if (n_deep < 0)
+    n_deep = w.counters->n_deep;  // speculative pass: the host has not read the count
   const int tid = blockIdx.x * blockDim.x + threadIdx.x;
   const int nthreads = gridDim.x * blockDim.x;
   unsigned char* mine = scratch + static_cast<size_t>(tid) * bytes_per_thread;
@@ -289,7 +300,34 @@ __global__ void __launch_bounds__(64) k_narrow_deep(SceneView v, Work w, long lo
       distanceGjk<R>(PA, PB, static_cast<R>(pr.thr), S, d);
       gjk_scanned = d.scanned;
       if (d.status == ND_NEED_EPA)
-        distanceEpa<R, false>(PA, static_cast<R>(A.brad), PB, static_cast<R>(B.brad), static_cast<R>(pr.thr), S, store, d);
+      {
+        bool done = false;
+        if (count_gjk)
+        {
+          // a curved-core item has not been through k_epa_wp: try the thread-local register-mask polytope first (same
+          // arithmetic and tie-breaks as the list form below, tests/test_narrow_hostcheck.py); the global slab, whose
+          // every face visit is an L2 round trip, is only for the few that outgrow it
+          R e_raw[(2 * EPA_FAST_VERTS + EPA_FAST_FACES) * 3 + EPA_FAST_FACES];
+          int e_int[2 * EPA_FAST_FACES];
+          unsigned long long e_row[EPA_FAST_VERTS];
+#pragma unroll 1
+          for (int i = 0; i < EPA_FAST_VERTS; ++i)
+            e_row[i] = 0;
+          Vec3<R>* e_pw = reinterpret_cast<Vec3<R>*>(e_raw);
+          EpaStore<R> fast{ e_pw, e_pw + EPA_FAST_VERTS, e_pw + 2 * EPA_FAST_VERTS,
+                            e_raw + (2 * EPA_FAST_VERTS + EPA_FAST_FACES) * 3, e_int, e_int + EPA_FAST_FACES,
+                            EPA_FAST_VERTS, EPA_FAST_FACES, e_row };
+          DistOut<R> df = d;
+          distanceEpa<R, true>(PA, static_cast<R>(A.brad), PB, static_cast<R>(B.brad), static_cast<R>(pr.thr), S, fast, df);
+          if (df.status != ND_EPA_OVERFLOW)
+          {
+            d = df;
+            done = true;
+          }
+        }
+        if (!done)
+          distanceEpa<R, false>(PA, static_cast<R>(A.brad), PB, static_cast<R>(B.brad), static_cast<R>(pr.thr), S, store, d);
+      }
     }
     storeHit<R>(w, d, u, sp, d.status == ND_CONTACT);
     // an item handed over by k_epa_wp had its GJK counted by k_gjk already; a curved-core item is counted here in full
@@ -338,7 +376,7 @@ size_t deepScratchBytesPerThread(int precision)
 cudaError_t launchNarrowDeep(const SceneView& v, const Work& w, int precision, long long n_deep, void* scratch,
                              size_t bytes_per_thread, int n_threads, cudaStream_t st)
 {
-  if (n_deep <= 0)
+  if (n_deep == 0)
     return cudaSuccess;
   const unsigned grid = static_cast<unsigned>(n_threads / 64);
   ++launchCounter();

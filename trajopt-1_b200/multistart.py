@@ -2,15 +2,17 @@
 seed generation, contiguous sharding of seeds over ranks, and winner selection.
 
 The path shards over independent trajectories only; there is no data-path collective.  The single exchange
-is the all-gather of every rank's (best cost, global seed index), followed by a broadcast of the winning
-trajectory from its owner: `tc_allgather_best` / `tc_broadcast_trajectory` (NCCL, inside libtrajopt_cuda.so) on GPUs; `allgather_best` below is the same reduction over any torch.distributed group and
-is what the world_size-2 gloo tests exercise on CPU."""
+is the all-gather of every rank's best (cost, global seed index, trajectory): `tc_result_allgather_best` (NCCL, inside
+libtrajopt_cuda.so, fed from the device) on GPUs; `allgather_best` / `broadcast_trajectory` below are the same
+reduction over any torch.distributed group and are what the world_size-2 gloo tests exercise on CPU.
+The host-buffer pass over a large batch (sub-batches on a ring of streams, compact rows) lives inside the library:
+`tc_pipeline_eval_rows` (capi.Pipeline)."""
 import os
 
 import numpy as np
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-SCENES = os.path.join(ROOT, "tests", "golden", "scenes")
+SCENES = os.path.join(os.path.dirname(os.path.abspath(__file__)), "data", "scenes")
 
 T_STEPS, LVS, MARGIN, COEFF, BUFFER, SIGMA = 10, 0.02, 0.025, 20.0, 0.01, 0.3
 
@@ -86,117 +88,3 @@ def broadcast_trajectory(traj, root, group=None):
     t = torch.from_numpy(np.ascontiguousarray(traj, dtype=np.float64).copy())
     dist.broadcast(t, src=root, group=group)
     return t.numpy()
-
-
-class PipelinedEvaluator:
-    """End-to-end multi-start pass with HOST buffers: the batch is cut into sub-batches that go round-robin to a
-    few worker threads, each with its own CUDA stream, tc_result and pinned output buffers.  While one worker's
-    rows travel device -> host, the other workers' kernels run, so the PCIe time of the rows (the bulk of the
-    bytes) hides behind the compute of the next sub-batch.  Every sub-batch is an ordinary
-    tc_eval + tc_result_rows + tc_result_cost through the C ABI; seeds are independent, so the host QP of a
-    sub-batch can start as soon as its rows have landed.
-
-    torch is used for pinned host memory and stream objects only."""
-
-    def __init__(self, cu, scene, evaluator, lvs, fixed, n_dof, chunk=1024, n_workers=2, rows_per_seed=1400,
-                 concurrent=1, taper=True, compact=True):
-        import queue
-        import threading
-        import torch
-        self.cu, self.scene, self.evaluator, self.lvs, self.fixed = cu, scene, evaluator, lvs, fixed
-        self.chunk, self.n_dof, self.taper, self.compact = chunk, n_dof, taper, compact
-        self.torch = torch
-        self.capi = cu.capi if hasattr(cu, "capi") else None
-        self.workers = []
-        self.jobs = [queue.Queue() for _ in range(n_workers)]
-        self.done = queue.Queue()
-        self.cap = int(chunk * rows_per_seed)
-        # at most `concurrent` sub-batches compute at a time; the slot is given up once the device -> host copies
-        # are enqueued, so a worker's copies run under other workers' kernels instead of all workers moving in
-        # lock step
-        self.compute = threading.Semaphore(concurrent)
-        for w in range(n_workers):
-            st = torch.cuda.Stream()
-            bufs = self._alloc(self.cap)
-            t = threading.Thread(target=self._work, args=(w, st, bufs), daemon=True)
-            t.start()
-            self.workers.append((t, st, bufs))
-
-    def _alloc(self, cap):
-        torch, nd = self.torch, self.n_dof
-        pin = lambda n, dt: torch.empty(n, dtype=dt).pin_memory().numpy()
-        return dict(cap=cap, row_ptr=pin(cap + 1, torch.int64), col=pin(2 * cap * nd, torch.int32),
-                    val=pin(2 * cap * nd, torch.float64), value=pin(cap, torch.float64), coeff=pin(cap, torch.float64),
-                    margin=pin(cap, torch.float64), cost=pin(self.chunk, torch.float64),
-                    first=pin(2 * cap, torch.int32))
-
-    def _work(self, w, stream, bufs):
-        import ctypes as C
-        from . import capi
-        cu = self.cu
-        torch = self.torch
-        res = None
-        pd, pi, pl = C.POINTER(C.c_double), C.POINTER(C.c_int32), C.POINTER(C.c_int64)
-        while True:
-            job = self.jobs[w].get()
-            if job is None:
-                return
-            idx, q = job
-            try:
-                if res is None:
-                    res = capi.Result(cu, self.scene, cu.new_result(self.scene), len(q), q.shape[1])
-                with self.compute:
-                    r = cu.eval(self.scene, q, self.evaluator, lvs=self.lvs, fixed=self.fixed, result=res,
-                                stream=stream.cuda_stream, want=capi.WANT_LINEARISE)
-                    n = r.counts()["n_contacts"]
-                    if n > bufs["cap"]:
-                        bufs.update(self._alloc(int(n * 1.25)))
-                    # the copies are enqueued before the next sub-batch may start (still under the lock) and
-                    # awaited after it has started
-                    # compact: the rows travel in block form (first column of the T0 / T1 run of every row instead
-                    # of one column index per non-zero, tc_result_rows_blocks_async) — the device -> host path is what
-                    # bounds this pass
-                    fn = cu.dll.tc_result_rows_blocks_async if self.compact else cu.dll.tc_result_rows_async
-                    cols = bufs["first"] if self.compact else bufs["col"]
-                    cu.check(fn(res.handle, bufs["row_ptr"].ctypes.data_as(pl), cols.ctypes.data_as(pi),
-                                bufs["val"].ctypes.data_as(pd), bufs["value"].ctypes.data_as(pd),
-                                bufs["coeff"].ctypes.data_as(pd), bufs["margin"].ctypes.data_as(pd)))
-                cu.check(cu.dll.tc_result_wait(res.handle))
-                cu.check(cu.dll.tc_result_cost(res.handle, None, bufs["cost"].ctypes.data_as(pd)))
-                c = r.counts()
-                self.done.put((idx, w, n, c["nnz"], c["n_dense"], bufs["cost"][:len(q)].copy(), None))
-            except Exception as e:  # surfaced by run()
-                self.done.put((idx, w, 0, 0, 0, None, e))
-
-    def run(self, q_pinned):
-        """q_pinned: numpy view of pinned host memory [B, T, n_dof].  Returns (costs[B], n_rows, nnz, n_dense);
-        the rows of sub-batch i are in worker (i % n_workers)'s pinned buffers when its entry arrives."""
-        B = len(q_pinned)
-        # sub-batch bounds: whole chunks, the last one cut in halves and quarters — the run ends with the download of
-        # the last sub-batch, which nothing overlaps, so that one is kept small
-        bounds, lo = [], 0
-        while lo < B:
-            hi = min(B, lo + self.chunk)
-            if hi == B and self.taper and hi - lo >= 4:
-                h, q = lo + (hi - lo) // 2, lo + 3 * (hi - lo) // 4
-                bounds += [(lo, h), (h, q), (q, hi)]
-            else:
-                bounds.append((lo, hi))
-            lo = hi
-        for i, (lo, hi) in enumerate(bounds):
-            self.jobs[i % len(self.jobs)].put((i, q_pinned[lo:hi]))
-        costs = np.zeros(B)
-        rows = nnz = dense = 0
-        for _ in range(len(bounds)):
-            idx, w, n, z, d, cost, err = self.done.get()
-            if err is not None:
-                raise err
-            costs[bounds[idx][0]: bounds[idx][0] + len(cost)] = cost
-            rows, nnz, dense = rows + n, nnz + z, dense + d
-        return costs, rows, nnz, dense
-
-    def close(self):
-        for q in self.jobs:
-            q.put(None)
-        for t, _, _ in self.workers:
-            t.join(timeout=10)
