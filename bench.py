@@ -409,7 +409,7 @@ def run_ours(args, scene, rank, world, local_rank):
                 break
             except Exception:
                 pass
-        base, _, _ = cpu_baseline(scene) if (world == 1 and not args.no_cpu_baseline) else ({"value": None, "unit": UNIT, "cores": 0,
+        base, _, _ = cpu_baseline(scene) if (world == 1 and not args.no_cpu_baseline and not args.skip_extras) else ({"value": None, "unit": UNIT, "cores": 0,
                                                                             "kind": "port", "sample": "skipped"}, 0, 0)
         # HBM-bound rest of the pass (FK, broadphase, finalise, sort, gradients + rows, cost): algorithmic bytes of
         # SURVEY.md 8(d) over the time of everything that is not the narrow phase
@@ -418,8 +418,9 @@ def run_ours(args, scene, rank, world, local_rank):
         hbm_bytes = (counts["n_states"] * (8 * nd + (96 + 96 + 48) * n_act) + 16 * counts["n_narrowphase"] +
                      counts["n_contacts"] * (176 + r_row))
         rest_ms = ms - nms
-        latency = sqp_iteration_latency(cu, with_cpu=not args.no_cpu_baseline) if world == 1 else None
-        others = other_configs(cu) if world == 1 else None
+        extras = world == 1 and not args.skip_extras
+        latency = sqp_iteration_latency(cu, with_cpu=not args.no_cpu_baseline) if extras else None
+        others = other_configs(cu) if extras else None
         out = {
             "metric": METRIC, "value": dense_total / (ms * 1e-3), "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": max(3, args.warmup), "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
@@ -488,6 +489,8 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--seeds", type=int, default=4096, help="trajectories per GPU")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--skip-extras", action="store_true", help="tuning runs: no CPU baseline, single-problem latencies or "
+                    "other configs (the default run reports them all)")
     ap.add_argument("--e2e-chunk", type=int, default=1024, help="seeds per sub-batch of the host-buffer (e2e) leg")
     ap.add_argument("--e2e-workers", type=int, default=3, help="streams (ring slots) of the e2e leg")
     args = ap.parse_args()

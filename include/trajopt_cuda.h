@@ -144,6 +144,15 @@ typedef struct tc_scene_desc {
   double default_margin;           /* CollisionMarginData default, WITHOUT the buffer */
   double default_coeff;
   double margin_buffer;            /* TrajOptCollisionConfig::collision_margin_buffer */
+  /* Dynamic environment (trajopt/src/collision_terms.cpp:399-411): links that move WITHOUT belonging to the planning
+   * group (another robot, a positioner, an attached object).  The reference then activates the contact manager on every
+   * active link of the environment, so such a link is tested against everything — the group's links, the static links
+   * and the other moving links — although it has no gradient for this group.  The n_env_active_links links that
+   * directly follow the group's links (indices n_active_links .. n_active_links + n_env_active_links - 1) are those
+   * links; their poses come from link_pose / tc_scene_set_link_poses.  0 = every non-group link is static and only
+   * pairs with a group link are candidates. */
+  int32_t n_env_active_links;
+  int32_t reserved;
 } tc_scene_desc;
 
 /* One batched evaluation: B trajectories x T timesteps, q[B][T][n_dof] row-major. */
@@ -231,7 +240,8 @@ void tc_scene_destroy(tc_scene* scene);
  * move between evaluations (another robot, a positioner, an attached object).  The reference reads their poses from
  * the environment state on every call; here the caller pushes them: link_pose[n_links][12], world poses; the entries
  * of the planning group's own links are ignored.  Takes effect for the next tc_eval; must not overlap an evaluation
- * that uses this scene.  Pairs of two non-group links stay untested (they carry no gradient for this group). */
+ * that uses this scene.  Pairs of two non-group links are candidates when at least one of them is among the scene's
+ * n_env_active_links (they carry no gradient for this group: constant rows, but they count in the cost). */
 int tc_scene_set_link_poses(tc_scene* scene, const double* link_pose);
 /* candidate link pairs (>= 1 active link, not ACM-disabled, sorted by (link0, link1)) */
 int tc_scene_num_pairs(const tc_scene* scene);

@@ -61,6 +61,7 @@ struct Scene
   std::vector<std::vector<int>> frame_dofs;  // dof-carrying ancestor frames (incl. self) of each frame
   Pose base;
   int n_links{ 0 }, n_active{ 0 };
+  int n_lead{ 0 };  // manager-active links: the group's + the environment's other moving links (dynamic environment)
   std::vector<int> link_frame;
   std::vector<Pose> link_pose;  // static world poses
   std::vector<Shape> shapes;
@@ -100,6 +101,9 @@ static Scene* buildScene(const tc_scene_desc& d)
   s->base = Pose::from12(d.base_pose);
   s->n_links = d.n_links;
   s->n_active = d.n_active_links;
+  if (d.n_env_active_links < 0 || d.n_active_links + d.n_env_active_links > d.n_links)
+    throw std::runtime_error("n_env_active_links out of range");
+  s->n_lead = d.n_active_links + d.n_env_active_links;
   s->link_frame.assign(d.link_frame, d.link_frame + d.n_links);
   for (int l = 0; l < d.n_links; ++l)
   {
@@ -189,7 +193,7 @@ static Scene* buildScene(const tc_scene_desc& d)
   for (int a = 0; a < d.n_links; ++a)
     for (int b = a + 1; b < d.n_links; ++b)
     {
-      if (!(s->isActive(a) || s->isActive(b)))
+      if (!(a < s->n_lead || b < s->n_lead))  // contactTest reports pairs with at least one manager-active link
         continue;
       if (d.acm && (d.acm[a * d.n_links + b] || d.acm[b * d.n_links + a]))
         continue;

@@ -236,3 +236,41 @@ def arm_with_curved_obstacles_scene(seed=13):
     acm[n_links0:, :na] = 0
     s["acm"] = acm
     return s
+
+
+def dynamic_env_scene(seed=17):
+    """arm_around_table plus two links that move WITHOUT belonging to the planning group (a cart and a tool on it;
+    trajopt/src/collision_terms.cpp:399-411 dynamic_environment): they directly follow the group's links
+    (n_env_active_links = 2), are checked against the arm, against the static scene and against EACH OTHER."""
+    s = {k: np.array(v) for k, v in helpers.load_scene("arm_around_table").items()}
+    na, nl0 = int(s["n_active_links"]), len(s["link_frame"])
+    ins = [("cart_link", np.array([[x, y, z] for x in (-0.15, 0.15) for y in (-0.2, 0.2) for z in (-0.1, 0.1)], dtype=np.float64),
+            _pose(t=(0.55, -0.45, 0.95))),
+           ("tool_link", np.array([[x, y, z] for x in (-0.05, 0.05) for y in (-0.05, 0.05) for z in (-0.12, 0.12)], dtype=np.float64),
+            _pose(t=(0.55, -0.45, 1.16)))]
+    k = len(ins)
+    remap = np.concatenate([np.arange(na), np.arange(na, nl0) + k])  # old link index -> new
+    s["link_names"] = np.concatenate([s["link_names"][:na], np.array([n for n, _, _ in ins]), s["link_names"][na:]])
+    s["link_frame"] = np.concatenate([s["link_frame"][:na], -np.ones(k, np.int32), s["link_frame"][na:]]).astype(np.int32)
+    lp = np.asarray(s["link_pose"], dtype=np.float64).reshape(nl0, 12)
+    s["link_pose"] = np.concatenate([lp[:na], np.stack([p for _, _, p in ins]), lp[na:]])
+    s["shape_link"] = remap[s["shape_link"]].astype(np.int32)
+    voff = len(s["verts"])
+    for i, (_, hv, _) in enumerate(ins):
+        s["shape_type"] = np.append(s["shape_type"], np.int32(1))
+        s["shape_link"] = np.append(s["shape_link"], np.int32(na + i))
+        s["shape_id"] = np.append(s["shape_id"], np.int32(0))
+        s["shape_params"] = np.concatenate([s["shape_params"], np.zeros((1, 4))])
+        s["shape_pose"] = np.concatenate([s["shape_pose"], IDENT[None]])
+        s["shape_vert_offset"] = np.append(s["shape_vert_offset"], np.int32(voff))
+        s["shape_vert_count"] = np.append(s["shape_vert_count"], np.int32(len(hv)))
+        s["verts"] = np.concatenate([s["verts"], hv])
+        voff += len(hv)
+    nl = nl0 + k
+    acm = np.zeros((nl, nl), np.uint8)
+    old = np.asarray(s["acm"])
+    acm[np.ix_(remap, remap)] = old
+    np.fill_diagonal(acm, 1)
+    s["acm"] = acm
+    s["n_env_active_links"] = np.int32(k)
+    return s

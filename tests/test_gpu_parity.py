@@ -341,3 +341,38 @@ def test_pipelined_host_pass_equals_one_pass(cuda, n_slots, chunk):
         small = capi.Pipeline(cuda, sg, 2)
         small.reserve(B, tpt, 5, 5)
         small.eval_rows(q, capi.EVAL_LVS_CONTINUOUS, 0.02, fixed, chunk)
+
+
+@pytest.mark.parametrize("evaluator", [capi.EVAL_DISCRETE, capi.EVAL_LVS_CONTINUOUS])
+def test_dynamic_environment_moving_links_outside_the_group(cuda, oracle, evaluator):
+    """collision_terms.cpp:399-411,828-836: with links that move outside the planning group the manager is active on
+    every moving link, so those links are tested against the arm, the static scene AND each other; pairs without a group
+    link have no gradient (constant rows) but count in the cost.  Then the links move (tc_scene_set_link_poses)."""
+    from tests import synthetic
+    s = synthetic.dynamic_env_scene()
+    sg, so = cuda.scene(s, 0.05, 20.0, 0.02), oracle.scene(s, 0.05, 20.0, 0.02)
+    assert sg.num_pairs() == so.num_pairs() > helpers.load_scene("arm_around_table")["acm"].shape[0]
+    q = helpers.pkg.multistart.make_batch(helpers.load_scene("arm_around_table"), 70, 4, t_steps=5)
+    fixed = np.zeros(q.shape[1], np.uint8)
+    fixed[0] = 1
+    na = int(s["n_active_links"])
+    for step in range(2):
+        rg = cuda.eval(sg, q, evaluator, lvs=0.05, fixed=fixed)
+        ro = oracle.eval(so, q, evaluator, lvs=0.05, fixed=fixed, n_threads=8)
+        rep = helpers.compare(ro, rg)
+        check(rep)
+        assert rep["same_order"] and rep["term_ptr_equal"]
+        c = rg.contacts()
+        env_env = (c["link_ids"][:, 0] >= na) & (c["link_ids"][:, 1] >= na)
+        env_arm = (c["link_ids"][:, 0] < na) & (c["link_ids"][:, 1] >= na) & (c["link_ids"][:, 1] < na + 2)
+        assert env_env.sum() > 0 and env_arm.sum() > 0, (int(env_env.sum()), int(env_arm.sum()))
+        rows = rg.rows()
+        for i in np.nonzero(env_env)[0][:20]:
+            assert not rows["val"][rows["row_ptr"][i]:rows["row_ptr"][i + 1]].any()  # no gradient for this group
+        # the cart rolls 4 cm: new scene poses on both sides
+        lp = np.array(s["link_pose"], dtype=np.float64).reshape(-1, 12).copy()
+        lp[na:na + 2, 3] += 0.04
+        s = dict(s)
+        s["link_pose"] = lp
+        sg.set_link_poses(lp)
+        so = oracle.scene(s, 0.05, 20.0, 0.02)

@@ -50,6 +50,7 @@ class SceneDesc(C.Structure):
         ("n_verts", C.c_int32), ("verts", _pd),
         ("acm", _pb), ("pair_margin", _pd), ("pair_coeff", _pd),
         ("default_margin", C.c_double), ("default_coeff", C.c_double), ("margin_buffer", C.c_double),
+        ("n_env_active_links", C.c_int32), ("reserved", C.c_int32),
     ]
 
 
@@ -140,6 +141,7 @@ class Scene:
             a["pair_coeff"] = np.ascontiguousarray(pair_coeff, dtype=np.float64)
             d.pair_coeff = _p(a["pair_coeff"], _pd)
         d.default_margin, d.default_coeff, d.margin_buffer = float(margin), float(coeff), float(margin_buffer)
+        d.n_env_active_links = int(arrays.get("n_env_active_links", 0))
         self.desc = d
         self.n_dof = d.n_dof
         self.n_links = d.n_links

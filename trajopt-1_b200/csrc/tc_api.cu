@@ -43,7 +43,7 @@ int resolveNoallocScratch(int device, double** out);
 // counts of a finished pass, used as the capacities of the next one on the same result (speculative pass)
 struct PassSizes
 {
-  long long n_states{ 0 }, n_units{ 0 }, n_items_padded{ 0 }, n_raw{ 0 }, n_deep{ 0 };
+  long long n_states{ 0 }, n_units{ 0 }, n_items_padded{ 0 }, n_raw{ 0 }, n_deep{ 0 }, n_curved{ 0 };
 };
 
 struct tc_scene
@@ -57,6 +57,7 @@ struct tc_scene
 struct tc_result
 {
   tc_scene* scene{ nullptr };
+  int device{ 0 };  // copied at creation: the destructor must not look at the scene, which may be gone by then
   cudaStream_t stream{ nullptr };
   tc_eval_desc desc{};
   EvalParams ep{};
@@ -91,7 +92,7 @@ struct tc_result
   DevBuf<uint8_t> term_fixed_d, term_interp;
   DevBuf<double> poses, aabb;
   DevBuf<uint32_t> bp_mask;
-  DevBuf<int32_t> sp_count, sp_offset, sp_cursor, items, deep_items, idx, idx_alt, ghas, epa_cursor, item_state;
+  DevBuf<int32_t> sp_count, sp_offset, sp_cursor, items, deep_items, curved_items, idx, idx_alt, ghas, epa_cursor, item_state;
   DevBuf<EpaRec> epa_rec;
   DevBuf<RawContact> raw;
   DevBuf<unsigned long long> keys, keys_alt;
@@ -102,7 +103,9 @@ struct tc_result
   DevBuf<double> csc_val, csc_upper, csc_cost;
   bool have_csc{ false };
   DevBuf<tc_gradient> grec;
-  DevBuf<unsigned char> sort_temp, deep_scratch;
+  DevBuf<unsigned char> sort_temp, deep_scratch, curved_scratch;
+  cudaStream_t side{ nullptr };  // speculative passes: the cold one-thread-per-item kernels run beside the main stream
+  cudaEvent_t ev_side[4]{};
   DevBuf<double> cost_term, cost_traj;
   // rows
   DevBuf<int32_t> col_idx, row_block, row_pair;
@@ -151,6 +154,9 @@ void trace(const tc_result* r, const char* what)
 int ensureDevice(int device)
 {
   TC_CUDA(cudaSetDevice(device));
+  // every launch of this library is checked right after it is issued, so anything still in the runtime's last-error
+  // slot here was left by other code of the process; it must not be blamed on our next launch
+  (void)cudaGetLastError();
   return TC_OK;
 }
 
@@ -458,12 +464,36 @@ int runEval(tc_scene* scene, const tc_eval_desc* desc, const double* q, int32_t 
   TC_RESERVE(r->epa_rec, w.n_items_padded);
   w.items = r->items.p, w.raw = r->raw.p, w.deep_items = r->deep_items.p;
   w.epa_cursor = r->epa_cursor.p, w.item_state = r->item_state.p, w.epa_rec = r->epa_rec.p;
+  TC_RESERVE(r->curved_items, hs.curved_sp.empty() ? 2 : 2 * n_items);
+  w.curved_items = r->curved_items.p;
+  // The two uses of the one-thread-per-item kernel of tc_strict.cu — the items of curved-core shape pairs and the few
+  // items whose polytope outgrew k_epa_wp's store — are a handful of warps running ~10^4 instructions that are in no
+  // cache when the launch comes: ~1 ms of instruction fetch for microseconds of arithmetic.  A speculative pass
+  // therefore runs them on the result's SIDE stream, the curved items next to k_gjk / k_epa_wp and the overflow
+  // re-runs next to the finalisation of the hits that already exist (k_finalize phases 1 and 2); an exact pass, which
+  // reads the counts back anyway, runs them in line.
+  const size_t deep_per = deepScratchBytesPerThread(TC_PRECISION_F64);  // the re-runs are FP64 in either mode
+  auto deepThreads = [](long long n) { return 64 * static_cast<int>(std::min<long long>((std::max<long long>(n, 1) + 63) / 64, 296)); };
+  const bool curved_scene = !hs.curved_sp.empty();
+  bool side_curved = false;
   if (w.n_items_padded > 0)
   {
     TC_CUDA(launchBroadFill(v, w, st));
     TC_CUDA(cudaEventRecord(r->ev[5], st));
+    if (curved_scene && spec)
+    {
+      const int nt = deepThreads(std::max<long long>(withSlack(pred.n_curved), 256));
+      TC_RESERVE(r->curved_scratch, deep_per * nt);
+      TC_CUDA(cudaEventRecord(r->ev_side[0], st));
+      TC_CUDA(cudaStreamWaitEvent(r->side, r->ev_side[0], 0));
+      TC_CUDA(launchRouteCurved(v, w, r->side));
+      TC_CUDA(launchNarrowDeep(v, w, desc->precision, 1, -1, r->curved_scratch.p, deep_per, nt, r->side));
+      TC_CUDA(cudaEventRecord(r->ev_side[1], r->side));
+      side_curved = true;
+    }
     TC_CUDA(launchNarrow(v, w, desc->precision, st, r->ev[6]));
-    TC_CUDA(launchRouteCurved(v, w, st));  // cylinder / cone pairs: skipped by k_gjk, served by the deep kernel below
+    if (curved_scene && !spec)
+      TC_CUDA(launchRouteCurved(v, w, st));
   }
   else
   {
@@ -471,53 +501,47 @@ int runEval(tc_scene* scene, const tc_eval_desc* desc, const double* q, int32_t 
     TC_CUDA(cudaEventRecord(r->ev[6], st));
   }
   TC_CUDA(cudaEventRecord(r->ev[2], st));
-  long long n_deep = 0;
+  bool split_finalize = false;
   if (!spec)
   {
     TC_TRY(readCounters(r));
-    n_deep = r->h_counters->n_deep;
+    const long long n_deep = r->h_counters->n_deep, n_curved = r->h_counters->n_curved;
     static const char* trace_deep = getenv("TC_TRACE_DEEP");  // tuning aid: how many items outgrew the fast polytope
     if (trace_deep)
+      fprintf(stderr, "[tc] n_epa=%lld n_deep=%lld n_curved=%lld\n", r->h_counters->n_epa, n_deep, n_curved);
+    if (n_curved > 0)
     {
-      fprintf(stderr, "[tc] n_epa=%lld n_deep=%lld\n", r->h_counters->n_epa, n_deep);
-      // a path instead of "1": the (unit, shape pair) list and the units' T0 sub-states are written there (diagnostics)
-      if (trace_deep[0] == '/' && n_deep > 0)
-      {
-        std::vector<int32_t> di(static_cast<size_t>(2 * n_deep)), ut(static_cast<size_t>(w.n_units)), sb(static_cast<size_t>(n_terms) + 1),
-            ub(static_cast<size_t>(n_terms) + 1);
-        cudaMemcpy(di.data(), w.deep_items, di.size() * 4, cudaMemcpyDeviceToHost);
-        cudaMemcpy(ut.data(), w.unit_term, ut.size() * 4, cudaMemcpyDeviceToHost);
-        cudaMemcpy(sb.data(), w.state_base, sb.size() * 4, cudaMemcpyDeviceToHost);
-        cudaMemcpy(ub.data(), w.unit_base, ub.size() * 4, cudaMemcpyDeviceToHost);
-        std::vector<int32_t> cnt(static_cast<size_t>(n_terms));
-        cudaMemcpy(cnt.data(), w.term_cnt, cnt.size() * 4, cudaMemcpyDeviceToHost);
-        if (FILE* f = fopen(trace_deep, "w"))
-        {
-          for (long long i = 0; i < n_deep; ++i)
-          {
-            const int u = di[static_cast<size_t>(2 * i)], sp = di[static_cast<size_t>(2 * i + 1)];
-            const int k = ut[static_cast<size_t>(u)];
-            fprintf(f, "%d %d %d %d %d\n", u, sp & (DEEP_COUNT_GJK_FLAG - 1), k, u - ub[static_cast<size_t>(k)], cnt[static_cast<size_t>(k)]);
-          }
-          fclose(f);
-        }
-      }
+      const int nt = deepThreads(n_curved);
+      TC_RESERVE(r->curved_scratch, deep_per * nt);
+      TC_CUDA(launchNarrowDeep(v, w, desc->precision, 1, n_curved, r->curved_scratch.p, deep_per, nt, st));
     }
-  }
-  else if (pred.n_deep > 0 || !hs.curved_sp.empty())
-    n_deep = -1;  // the kernel takes the count from the device
-  if (n_deep != 0)
-  {
-    // launch shape from the count (exact pass) or from the previous pass's count (speculative pass; the kernel strides
-    // over whatever the device count turns out to be)
-    const long long shape_n = n_deep < 0 ? std::max<long long>(withSlack(pred.n_deep), 256) : n_deep;
-    const int n_threads = 64 * static_cast<int>(std::min<long long>((shape_n + 63) / 64, 296));
-    const size_t per = deepScratchBytesPerThread(desc->precision);
-    TC_RESERVE(r->deep_scratch, per * n_threads);
-    TC_CUDA(launchNarrowDeep(v, w, desc->precision, n_deep, r->deep_scratch.p, per, n_threads, st));
+    if (n_deep > 0)
+    {
+      const int nt = deepThreads(n_deep);
+      TC_RESERVE(r->deep_scratch, deep_per * nt);
+      TC_CUDA(launchNarrowDeep(v, w, desc->precision, 0, n_deep, r->deep_scratch.p, deep_per, nt, st));
+    }
     r->deep_launched = true;
-    if (!spec)
+    if (n_curved > 0 || n_deep > 0)
       TC_TRY(readCounters(r));
+  }
+  else
+  {
+    if (side_curved)
+      TC_CUDA(cudaStreamWaitEvent(st, r->ev_side[1], 0));  // the curved items' hits are in before anything is finalised
+    // always: the re-run kernel leaves after one counter read when no polytope overflowed, and a pass never has to be
+    // repeated because the previous one happened to have none
+    r->deep_launched = true;
+    {
+      const int nt = deepThreads(std::max<long long>(withSlack(pred.n_deep), 256));
+      TC_RESERVE(r->deep_scratch, deep_per * nt);
+      TC_CUDA(launchSnapshotRaw(w, st));
+      TC_CUDA(cudaEventRecord(r->ev_side[2], st));
+      TC_CUDA(cudaStreamWaitEvent(r->side, r->ev_side[2], 0));
+      TC_CUDA(launchNarrowDeep(v, w, desc->precision, 0, -1, r->deep_scratch.p, deep_per, nt, r->side));
+      TC_CUDA(cudaEventRecord(r->ev_side[3], r->side));
+      split_finalize = true;
+    }
   }
   TC_CUDA(cudaEventRecord(r->ev[3], st));
   // ---- contact finalisation + sort ----
@@ -537,7 +561,14 @@ int runEval(tc_scene* scene, const tc_eval_desc* desc, const double* q, int32_t 
   }
   if (w.n_sort > 0)
   {
-    TC_CUDA(launchFinalize(v, w, st));
+    if (split_finalize)
+    {
+      TC_CUDA(launchFinalize(v, w, 1, st));
+      TC_CUDA(cudaStreamWaitEvent(st, r->ev_side[3], 0));
+      TC_CUDA(launchFinalize(v, w, 2, st));
+    }
+    else
+      TC_CUDA(launchFinalize(v, w, 0, st));
     size_t temp_bytes = 0;
     TC_CUDA(sortContacts(w, nullptr, temp_bytes, st));
     TC_RESERVE(r->sort_temp, temp_bytes);
@@ -553,6 +584,8 @@ int runEval(tc_scene* scene, const tc_eval_desc* desc, const double* q, int32_t 
     if (!spec)
       TC_TRY(readCounters(r));
   }
+  else if (split_finalize)
+    TC_CUDA(cudaStreamWaitEvent(st, r->ev_side[3], 0));
   // grid bound of the kernels indexed by contact (they take the count itself from the device counters)
   w.n_contacts = spec ? w.n_sort : r->h_counters->n_valid;
   TC_RESERVE(r->contacts, w.n_contacts);
@@ -589,7 +622,7 @@ int finishEval(tc_result* r)
 {
   if (!r->pending)
     return r->valid ? TC_OK : fail(TC_ERR_INVALID, "no evaluation to wait for");
-  TC_TRY(ensureDevice(r->scene->device));
+  TC_TRY(ensureDevice(r->device));
   if (r->ep.n_terms > 0)
   {
     LaunchScope scope(r);
@@ -627,7 +660,7 @@ int finishEval(tc_result* r)
   if (r->ep.n_terms > 0)
   {
     r->pred.n_states = c.n_states, r->pred.n_units = c.n_units, r->pred.n_items_padded = c.n_items_padded;
-    r->pred.n_raw = c.n_raw, r->pred.n_deep = c.n_deep;
+    r->pred.n_raw = c.n_raw, r->pred.n_deep = c.n_deep, r->pred.n_curved = c.n_curved;
     r->pred_sig = r->pass_sig;
     r->pred_valid = true;
   }
@@ -668,7 +701,7 @@ int needValid(const tc_result* r)
     return fail(TC_ERR_INVALID, "tc_result_sync() has not been called");
   if (!r->valid)
     return fail(TC_ERR_INVALID, "result holds no evaluation");
-  return ensureDevice(r->scene->device);
+  return ensureDevice(r->device);
 }
 
 // row assembly on the result's stream; `fused` = gradients recomputed inside the row kernel (no gradient arena)
@@ -880,6 +913,7 @@ void tc_scene_destroy(tc_scene* s)
   for (void* p : s->allocs)
     cudaFree(p);
   delete s;
+  (void)cudaGetLastError();  // failures above are ignored on purpose and must not surface at the next launch
 }
 
 int tc_scene_num_pairs(const tc_scene* s) { return s ? static_cast<int>(s->host.pairs.size()) : 0; }
@@ -911,6 +945,7 @@ int tc_result_create(tc_scene* scene, tc_result** out)
   if (!r)
     return fail(TC_ERR_INVALID, "out of memory");
   r->scene = scene;
+  r->device = scene->device;
   cudaError_t e = cudaHostAlloc(reinterpret_cast<void**>(&r->h_counters), sizeof(Counters), cudaHostAllocMapped);
   if (e == cudaSuccess)
     e = cudaHostGetDevicePointer(reinterpret_cast<void**>(&r->h_counters_dev), r->h_counters, 0);
@@ -918,6 +953,10 @@ int tc_result_create(tc_scene* scene, tc_result** out)
     e = cudaMalloc(reinterpret_cast<void**>(&r->d_counters), sizeof(Counters));
   for (int i = 0; i < 7 && e == cudaSuccess; ++i)
     e = cudaEventCreate(&r->ev[i]);
+  if (e == cudaSuccess)
+    e = cudaStreamCreateWithFlags(&r->side, cudaStreamNonBlocking);
+  for (int i = 0; i < 4 && e == cudaSuccess; ++i)
+    e = cudaEventCreateWithFlags(&r->ev_side[i], cudaEventDisableTiming);
   if (e != cudaSuccess)
   {
     tc_result_destroy(r);
@@ -931,7 +970,10 @@ void tc_result_destroy(tc_result* r)
 {
   if (!r)
     return;
-  cudaSetDevice(r->scene->device);
+  // Handles are destroyed in whatever order the host's garbage collector picks: nothing here may touch the scene.
+  // Failures of the calls below are deliberately ignored, and the runtime's last-error slot is cleared at the end so
+  // that they are not blamed on the next kernel launch of this thread.
+  cudaSetDevice(r->device);
   if (r->pending)
     cudaStreamSynchronize(r->stream);
   if (r->h_counters)
@@ -944,10 +986,19 @@ void tc_result_destroy(tc_result* r)
   for (int i = 0; i < 7; ++i)
     if (r->ev[i])
       cudaEventDestroy(r->ev[i]);
+  for (int i = 0; i < 4; ++i)
+    if (r->ev_side[i])
+      cudaEventDestroy(r->ev_side[i]);
+  if (r->side)
+  {
+    cudaStreamSynchronize(r->side);
+    cudaStreamDestroy(r->side);
+  }
   r->pose_in.release(), r->raw_valid.release();
   r->q.release(), r->term_t_d.release(), r->term_cnt.release(), r->term_states.release(), r->term_units.release();
   r->state_base.release(), r->unit_base.release(), r->unit_term.release(), r->term_fixed_d.release();
   r->term_interp.release(), r->poses.release(), r->aabb.release(), r->bp_mask.release(), r->sp_count.release(), r->sp_offset.release();
+  r->curved_items.release(), r->curved_scratch.release();
   r->sp_cursor.release(), r->items.release(), r->deep_items.release(), r->idx.release(), r->idx_alt.release();
   r->ghas.release(), r->raw.release(), r->keys.release(), r->keys_alt.release(), r->contacts_tmp.release();
   r->contacts.release(), r->xf.release(), r->grad.release(), r->term_ptr.release();
@@ -960,6 +1011,7 @@ void tc_result_destroy(tc_result* r)
   r->sets.release(), r->set_count.release(), r->set_run.release(), r->set_values.release();
   r->set_coeffs.release(), r->set_jac.release();
   delete r;
+  (void)cudaGetLastError();
 }
 
 int tc_eval_async(tc_scene* scene, const tc_eval_desc* desc, const double* q, int32_t B, int32_t T, tc_result* out,
@@ -1399,6 +1451,7 @@ void tc_nccl_comm_destroy(void* comm)
 struct tc_pipeline
 {
   tc_scene* scene{ nullptr };
+  int device{ 0 };
   int n_slots{ 0 };
   // one ring of results per sub-batch size, so that every result keeps seeing passes of ONE shape and stays speculative
   struct Ring
@@ -1476,6 +1529,7 @@ int tc_pipeline_create(tc_scene* scene, int32_t n_slots, tc_pipeline** out)
   if (!p)
     return fail(TC_ERR_INVALID, "out of memory");
   p->scene = scene;
+  p->device = scene->device;
   p->n_slots = n_slots;
   for (int i = 0; i < n_slots; ++i)
   {
@@ -1496,13 +1550,14 @@ void tc_pipeline_destroy(tc_pipeline* p)
 {
   if (!p)
     return;
-  cudaSetDevice(p->scene->device);
+  cudaSetDevice(p->device);
   for (auto& rg : p->rings)
     for (tc_result* r : rg.res)
       tc_result_destroy(r);
   for (cudaStream_t st : p->streams)
     cudaStreamDestroy(st);
   delete p;
+  (void)cudaGetLastError();
 }
 
 int tc_pipeline_eval_rows(tc_pipeline* p, const tc_eval_desc* desc, const double* q, int32_t B, int32_t T, int32_t chunk,

@@ -55,6 +55,8 @@ struct Counters
   long long gjk_iters, support_verts, n_epa, epa_iters, n_unconverged, overflow, nnz;
   long long gjk_cursor, epa_cursor_g;  // work cursors of the warp-persistent narrow-phase kernels
   long long support_compared;          // hull vertices actually compared by support queries (support_verts: all of the hull)
+  long long n_curved;                  // items of curved-core shape pairs routed to the contraction-free kernel
+  long long n_raw0;                    // raw hits present when the overflow re-runs start (they are finalised meanwhile)
 };
 
 template <class T>
@@ -113,7 +115,8 @@ struct Work
   int32_t *sp_count, *sp_offset, *sp_cursor;
   int32_t* items;
   RawContact* raw;
-  int32_t* deep_items;  // (unit, shape pair) of items whose EPA outgrew the thread-local polytope
+  int32_t* deep_items;   // (unit, shape pair) of items whose EPA outgrew the thread-local polytope
+  int32_t* curved_items; // (unit, shape pair | DEEP_COUNT_GJK) of every item of a curved-core shape pair
   int32_t* item_state;   // T0 sub-state of every item (parallel to items)
   int32_t* epa_cursor;   // GJK -> EPA hand-off: records packed per shape pair at the bucket offsets
   EpaRec* epa_rec;
@@ -172,7 +175,8 @@ cudaError_t launchPoseIn(const SceneView& v, const Work& w, cudaStream_t st);  /
 cudaError_t launchTypeFilter(const SceneView& v, const Work& w, const uint8_t* valid, cudaStream_t st);
 cudaError_t launchBroadCount(const SceneView& v, const Work& w, cudaStream_t st);
 cudaError_t launchBroadFill(const SceneView& v, const Work& w, cudaStream_t st);
-cudaError_t launchFinalize(const SceneView& v, const Work& w, cudaStream_t st);
+// phase 0: every raw hit; 1: the first n_raw0 of them; 2: the rest and the surplus entries of the sort
+cudaError_t launchFinalize(const SceneView& v, const Work& w, int phase, cudaStream_t st);
 cudaError_t sortContacts(const Work& w, void* temp, size_t& temp_bytes, cudaStream_t st);  // result in *_alt
 cudaError_t launchGather(const SceneView& v, const Work& w, cudaStream_t st);
 cudaError_t launchGradients(const SceneView& v, const Work& w, cudaStream_t st);
@@ -194,9 +198,12 @@ cudaError_t launchSets(const SceneView& v, const Work& w, int max_num_cnt, tc_se
 cudaError_t launchNarrow(const SceneView& v, const Work& w, int precision, cudaStream_t st, cudaEvent_t mid);
 // ---- launchers (tc_strict.cu: contraction-free kernels) ----
 cudaError_t launchRouteCurved(const SceneView& v, const Work& w, cudaStream_t st);
-// n_deep < 0: the kernel takes the count from the device counters (speculative pass)
-cudaError_t launchNarrowDeep(const SceneView& v, const Work& w, int precision, long long n_deep, void* scratch,
+// list: 0 = the EPA overflow list (deep_items, counter n_deep), 1 = the curved-core list (curved_items, n_curved).
+// n < 0: the kernel takes the count from the device counters (speculative pass)
+cudaError_t launchNarrowDeep(const SceneView& v, const Work& w, int precision, int list, long long n, void* scratch,
                              size_t scratch_bytes_per_thread, int n_threads, cudaStream_t st);
+// n_raw0 = n_raw (speculative pass: the raw hits that exist before the overflow re-runs can be finalised meanwhile)
+cudaError_t launchSnapshotRaw(const Work& w, cudaStream_t st);
 size_t deepScratchBytesPerThread(int precision);
 cudaError_t measureFmaPeak(int precision, double* tflops);
 }  // namespace tc

@@ -704,17 +704,20 @@ struct EpaState
 // lies on the surface next to the previous ones, the faces become slivers whose plane distance carries ~1e-10 m of
 // rounding, and a few items then dither at the tolerance for a hundred trips without narrowing the bracket; in FP32 the
 // same happens on every shape at ~1e-6.  EPA_STALL_TRIPS trips without narrowing the bracket by 10 % therefore end the
-// expansion on the current closest face.  The CPU checker applies the same rule to curved cores (it has no FP32 mode);
-// hull / sphere / capsule pairs in FP64 never take this exit, there the gap test alone decides.
+// expansion: in FP64 on the current closest face (the CPU checker applies the same rule to curved cores), in FP32 by
+// handing the item to the FP64 re-run kernel like one whose polytope overflowed — float EPA only ever reports results it
+// has closed to its tolerance.  Hull / sphere / capsule pairs in FP64 never take this exit: the gap test alone decides.
 enum
 {
-  EPA_STALL_TRIPS = 6
+  EPA_STALL_TRIPS = 6,       // FP64, curved cores
+  EPA_STALL_TRIPS_F32 = 16   // FP32, every pair: polytope pairs legitimately spend a few trips on coplanar faces
 };
 template <class R>
 TC_HD bool epaStalled(EpaState<R>& E, R support_value)
 {
   if (!E.stall_exit)
     return false;
+  const int patience = sizeof(R) == sizeof(float) ? EPA_STALL_TRIPS_F32 : EPA_STALL_TRIPS;
   if (support_value < E.ub_best)
     E.ub_best = support_value;
   const R width = E.ub_best - E.bd;
@@ -724,7 +727,7 @@ TC_HD bool epaStalled(EpaState<R>& E, R support_value)
     E.stall = 0;
     return false;
   }
-  return ++E.stall >= EPA_STALL_TRIPS;
+  return ++E.stall >= patience;
 }
 
 template <class R, bool MASK>
@@ -981,8 +984,10 @@ TC_HD int epaTripMasked(const Placed<R>& A, const Placed<R>& B, EpaStore<R>& st,
   const Vec3<R> xa = A.support(bn, scanned), xb = B.support(-bn, scanned);
   const Vec3<R> xw = xa - xb;
   const R sv = dot(bn, xw);
-  if (sv - E.bd <= Tol<R>::epaTol() || epaStalled(E, sv))
+  if (sv - E.bd <= Tol<R>::epaTol())
     return EPA_DONE;
+  if (epaStalled(E, sv))
+    return sizeof(R) == sizeof(float) ? EPA_OVERFLOW : EPA_DONE;  // FP32: the item is re-run in FP64 (deep list)
   if (E.iters == EPA_MAX_ITERS)
     return EPA_UNCONVERGED;
   if (E.np >= st.max_verts)
@@ -1101,8 +1106,10 @@ TC_HDN int epaTrip(const Placed<R>& A, const Placed<R>& B, EpaStore<R>& st, EpaS
   const Vec3<R> xa = A.support(bn, scanned), xb = B.support(-bn, scanned);
   const Vec3<R> xw = xa - xb;
   const R sv = dot(bn, xw);
-  if (sv - E.bd <= Tol<R>::epaTol() || epaStalled(E, sv))
+  if (sv - E.bd <= Tol<R>::epaTol())
     return EPA_DONE;
+  if (epaStalled(E, sv))
+    return sizeof(R) == sizeof(float) ? EPA_OVERFLOW : EPA_DONE;  // FP32: the item is re-run in FP64 (deep list)
   if (E.iters == EPA_MAX_ITERS)
     return EPA_UNCONVERGED;
   if (E.np >= st.max_verts)

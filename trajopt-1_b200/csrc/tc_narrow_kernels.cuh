@@ -38,11 +38,21 @@ __device__ __forceinline__ void placeItem(const SceneView& v, const Work& w, lon
                                           const Vtx<R>* vb, Placed<R>& PA, Placed<R>& PB, const void* la = nullptr,
                                           const void* lb = nullptr)
 {
-  const double* pa = posePtr(w, pr.a, s0);
   PA.sh = makeCore<R>(A, va, la);
-  PA.p0 = loadPose<R>(pa);
-  PA.cast = w.cast != 0;
-  PA.p1 = w.cast ? loadPose<R>(pa + 12) : PA.p0;
+  if (pr.a < v.n_active)
+  {
+    const double* pa = posePtr(w, pr.a, s0);
+    PA.p0 = loadPose<R>(pa);
+    PA.cast = w.cast != 0;
+    PA.p1 = w.cast ? loadPose<R>(pa + 12) : PA.p0;
+  }
+  else
+  {
+    // a moving link of the environment outside the planning group leads this pair: one pose for the whole pass
+    PA.p0 = loadPose<R>(v.link_pose + 12 * pr.a);
+    PA.cast = false;
+    PA.p1 = PA.p0;
+  }
   PB.sh = makeCore<R>(B, vb, lb);
   if (pr.b < v.n_active)
   {

@@ -408,12 +408,18 @@ __device__ __forceinline__ UnitInfo unitInfo(const Work& w, int u)
   return ui;
 }
 
-__global__ void __launch_bounds__(TPB, TC_FINALIZE_MINB) k_finalize(SceneView v, Work w)
+// phase 0: every raw hit.  Speculative pass: phase 1 = the hits that exist before the EPA-overflow re-runs start
+// (counters->n_raw0), finalised while those re-runs fetch their cold code on another stream; phase 2 = the hits they
+// added, and the surplus entries of the key sort
+__global__ void __launch_bounds__(TPB, TC_FINALIZE_MINB) k_finalize(SceneView v, Work w, int phase)
 {
   if (passOverflowed(w))
     return;
-  const long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
-  const long long n_raw = w.counters->n_raw;
+  const long long first = phase == 2 ? w.counters->n_raw0 : 0;
+  const long long i = first + static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+  const long long n_raw = phase == 1 ? w.counters->n_raw0 : w.counters->n_raw;
+  if (phase == 1 && i >= n_raw)
+    return;  // no surplus entries in this phase: warp-uniform apart from the last warp, whose ballot below it skips
   if (n_raw > w.n_sort)
   {
     // more raw hits than the key sort was sized for (speculative pass): nothing may be written past the arenas
@@ -474,9 +480,15 @@ __global__ void __launch_bounds__(TPB, TC_FINALIZE_MINB) k_finalize(SceneView v,
     w.keys[i] = key;
     w.idx[i] = static_cast<int32_t>(i);
   }
-  const unsigned m = __ballot_sync(0xffffffffu, valid);
-  if ((threadIdx.x & 31) == 0 && m)
+  const unsigned m = __ballot_sync(__activemask(), valid);
+  if (valid && (threadIdx.x & 31) == static_cast<unsigned>(__ffs(m) - 1))
     atomicAdd(reinterpret_cast<unsigned long long*>(&w.counters->n_valid), static_cast<unsigned long long>(__popc(m)));
+}
+
+__global__ void k_snapshot_raw(Work w)
+{
+  if (threadIdx.x == 0)
+    w.counters->n_raw0 = w.counters->n_raw;
 }
 
 // ContactTestType CLOSEST / FIRST (tesseract_collision: the manager keeps one result per link pair / stops at its first
@@ -1349,13 +1361,20 @@ cudaError_t launchBroadFill(const SceneView& v, const Work& w, cudaStream_t st)
   return cudaGetLastError();
 }
 
-cudaError_t launchFinalize(const SceneView& v, const Work& w, cudaStream_t st)
+cudaError_t launchFinalize(const SceneView& v, const Work& w, int phase, cudaStream_t st)
 {
   if (w.n_sort > 0)
   {
     ++launchCounter();
-    k_finalize<<<gridFor(w.n_sort, TPB), TPB, 0, st>>>(v, w);
+    k_finalize<<<gridFor(w.n_sort, TPB), TPB, 0, st>>>(v, w, phase);
   }
+  return cudaGetLastError();
+}
+
+cudaError_t launchSnapshotRaw(const Work& w, cudaStream_t st)
+{
+  ++launchCounter();
+  k_snapshot_raw<<<1, 32, 0, st>>>(w);
   return cudaGetLastError();
 }
 

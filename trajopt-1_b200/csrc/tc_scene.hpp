@@ -41,6 +41,7 @@ struct SceneError : std::runtime_error
 struct HostScene
 {
   int n_dof{ 0 }, n_frames{ 0 }, n_links{ 0 }, n_active{ 0 }, n_shapes{ 0 }, n_active_shapes{ 0 };
+  int n_lead{ 0 };  // links that may lead a candidate pair: the group's links + the environment's other moving links
   std::vector<int32_t> frame_parent, frame_type, frame_dof;
   std::vector<double> frame_axis, frame_origin;
   double base_pose[12];
@@ -206,7 +207,7 @@ inline void updateStaticPoses(HostScene& s, const double* link_pose)
     for (int k = 0; k < 12; ++k)
       s.link_pose[static_cast<size_t>(12 * l + k)] = link_pose[12 * l + k];
   for (int i = 0; i < s.n_shapes; ++i)
-    if (s.shapes[static_cast<size_t>(i)].active_index < 0)
+    if (s.shapes[static_cast<size_t>(i)].link >= s.n_active)
       staticShapeAabb(s, i);
 }
 
@@ -250,6 +251,9 @@ inline void buildHostScene(const tc_scene_desc& d, HostScene& s)
   }
   s.n_links = d.n_links;
   s.n_active = d.n_active_links;
+  if (d.n_env_active_links < 0 || d.n_active_links + d.n_env_active_links > d.n_links)
+    fail("n_env_active_links out of range");
+  s.n_lead = d.n_active_links + d.n_env_active_links;
   s.link_frame.assign(d.link_frame, d.link_frame + d.n_links);
   s.link_pose.assign(d.link_pose, d.link_pose + 12 * d.n_links);
   for (int l = 0; l < d.n_links; ++l)
@@ -353,13 +357,15 @@ inline void buildHostScene(const tc_scene_desc& d, HostScene& s)
       sh.aabb_h[k] = 0.5 * (hi[k] - lo[k]);
     }
     sh.active_index = -1;
-    if (sh.link < d.n_active_links)
+    if (sh.link < s.n_lead)
     {
+      // a shape that leads pairs in the broadphase owns a slot of the box arena; a moving link outside the group has no
+      // frame (-1): its box is the same in every state and is written from its current world pose
       sh.active_index = static_cast<int32_t>(s.active_shapes.size());
       s.active_shapes.push_back(i);
-      s.active_shape_frame.push_back(d.link_frame[sh.link]);
+      s.active_shape_frame.push_back(sh.link < d.n_active_links ? d.link_frame[sh.link] : -1);
     }
-    else
+    if (sh.link >= d.n_active_links)
     {
       const Pose<double> T = Pose<double>::from12(d.link_pose + 12 * sh.link);
       const Vec3<double> wc = T.apply(Vec3<double>(sh.aabb_c[0], sh.aabb_c[1], sh.aabb_c[2]));
@@ -379,8 +385,8 @@ inline void buildHostScene(const tc_scene_desc& d, HostScene& s)
   for (int a = 0; a < d.n_links; ++a)
     for (int b = a + 1; b < d.n_links; ++b)
     {
-      if (a >= d.n_active_links)
-        continue;  // active links come first, so link a of a candidate pair is always active
+      if (a >= s.n_lead)
+        continue;  // leading links come first, so link a of a candidate pair always is one
       if (d.acm && (d.acm[a * d.n_links + b] || d.acm[b * d.n_links + a]))
         continue;
       if (link_shapes[static_cast<size_t>(a)].empty() || link_shapes[static_cast<size_t>(b)].empty())

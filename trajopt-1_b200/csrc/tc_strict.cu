@@ -127,6 +127,16 @@ __global__ void __launch_bounds__(TPB, TC_FK_MINB) k_fk(SceneView v, Work w)
   const int cnt = w.term_interp[k] ? w.term_cnt[k] : 2;
   // Frames are visited in topological order with the previous frame's pose in registers; a branch reads
   // its parent back from this thread's own record in the pose arena (no thread-local frame array).
+  // moving links of the environment outside the planning group (dynamic environment): no frame, one pose for the whole
+  // pass; their shapes still lead pairs in the broadphase, so their (constant) box goes into every state's column
+  if (live)
+    for (int a = 0; a < v.n_active_shapes; ++a)
+    {
+      if (v.active_shape_frame[a] >= 0)
+        continue;
+      const ShapeD& sh = v.shapes[v.active_shapes[a]];
+      writeShapeAabb(w, Pose<double>::from12(v.link_pose + 12 * sh.link), sh.aabb_c, sh.aabb_h, a, s);
+    }
   const Pose<double> base = Pose<double>::from12(v.base_pose);
   Pose<double> cur = base;
   for (int f = 0; f < v.n_frames; ++f)
@@ -232,6 +242,12 @@ __global__ void __launch_bounds__(TPB) k_pose_in(SceneView v, Work w)
       writeShapeAabb(w, T, sh.aabb_c, sh.aabb_h, a, s);
     }
   }
+  for (int a = 0; a < v.n_active_shapes; ++a)
+  {
+    const ShapeD& sh = v.shapes[v.active_shapes[a]];
+    if (sh.link >= v.n_active)  // leading link without per-state poses: the scene's pose
+      writeShapeAabb(w, Pose<double>::from12(v.link_pose + 12 * sh.link), sh.aabb_c, sh.aabb_h, a, s);
+  }
 }
 
 // every item of the shape pairs with a curved core -> the deep list (k_gjk skips those buckets)
@@ -244,21 +260,22 @@ __global__ void __launch_bounds__(256) k_route_curved(SceneView v, Work w)
   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
   {
     const int u = w.items[off + i];
-    const unsigned long long d = atomicAdd(reinterpret_cast<unsigned long long*>(&w.counters->n_deep), 1ull);
-    w.deep_items[2 * d] = u;
-    w.deep_items[2 * d + 1] = sp | DEEP_COUNT_GJK;
+    const unsigned long long d = atomicAdd(reinterpret_cast<unsigned long long*>(&w.counters->n_curved), 1ull);
+    w.curved_items[2 * d] = u;
+    w.curved_items[2 * d + 1] = sp | DEEP_COUNT_GJK;
   }
 }
 
 // deep-expansion path: same arithmetic, polytope in global scratch, vertices read from global memory
 template <class R>
-__global__ void __launch_bounds__(64) k_narrow_deep(SceneView v, Work w, long long n_deep, unsigned char* scratch,
+__global__ void __launch_bounds__(64) k_narrow_deep(SceneView v, Work w, int list, long long n_deep, unsigned char* scratch,
                                                     size_t bytes_per_thread)
 {
+  const int32_t* items = list ? w.curved_items : w.deep_items;
   if (passOverflowed(w))
     return;
   if (n_deep < 0)
-    n_deep = w.counters->n_deep;  // speculative pass: the host has not read the count
+    n_deep = list ? w.counters->n_curved : w.counters->n_deep;  // speculative pass: the host has not read the count
   const int tid = blockIdx.x * blockDim.x + threadIdx.x;
   const int nthreads = gridDim.x * blockDim.x;
   unsigned char* mine = scratch + static_cast<size_t>(tid) * bytes_per_thread;
@@ -282,8 +299,8 @@ __global__ void __launch_bounds__(64) k_narrow_deep(SceneView v, Work w, long lo
     bool count_gjk = false;
     if (it < n_deep)
     {
-      u = w.deep_items[2 * it];
-      const int sp_raw = w.deep_items[2 * it + 1];
+      u = items[2 * it];
+      const int sp_raw = items[2 * it + 1];
       count_gjk = (sp_raw & DEEP_COUNT_GJK) != 0;
       sp = sp_raw & (DEEP_COUNT_GJK - 1);
       const ShapePairD spd = v.spairs[sp];
@@ -373,17 +390,16 @@ size_t deepScratchBytesPerThread(int precision)
   return (b + 15) / 16 * 16;
 }
 
-cudaError_t launchNarrowDeep(const SceneView& v, const Work& w, int precision, long long n_deep, void* scratch,
+cudaError_t launchNarrowDeep(const SceneView& v, const Work& w, int precision, int list, long long n_deep, void* scratch,
                              size_t bytes_per_thread, int n_threads, cudaStream_t st)
 {
   if (n_deep == 0)
     return cudaSuccess;
   const unsigned grid = static_cast<unsigned>(n_threads / 64);
   ++launchCounter();
-  if (precision == TC_PRECISION_F32)
-    k_narrow_deep<float><<<grid, 64, 0, st>>>(v, w, n_deep, static_cast<unsigned char*>(scratch), bytes_per_thread);
-  else
-    k_narrow_deep<double><<<grid, 64, 0, st>>>(v, w, n_deep, static_cast<unsigned char*>(scratch), bytes_per_thread);
+  // always FP64: in FP32 mode this kernel is where the items float EPA could not close get their answer
+  (void)precision;
+  k_narrow_deep<double><<<grid, 64, 0, st>>>(v, w, list, n_deep, static_cast<unsigned char*>(scratch), bytes_per_thread);
   return cudaGetLastError();
 }
 
