@@ -492,7 +492,7 @@ def main():
     ap.add_argument("--skip-extras", action="store_true", help="tuning runs: no CPU baseline, single-problem latencies or "
                     "other configs (the default run reports them all)")
     ap.add_argument("--e2e-chunk", type=int, default=1024, help="seeds per sub-batch of the host-buffer (e2e) leg")
-    ap.add_argument("--e2e-workers", type=int, default=3, help="streams (ring slots) of the e2e leg")
+    ap.add_argument("--e2e-workers", type=int, default=4, help="streams (ring slots) of the e2e leg")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))

@@ -98,3 +98,24 @@ def test_two_ranks_agree_with_one(oracle):
     # every rank holds the winner's trajectory after the broadcast
     want_traj = ms.make_batch(scene, want_idx, 1)[0]
     assert np.array_equal(got[0][3], want_traj) and np.array_equal(got[1][3], want_traj)
+
+
+@pytest.mark.gpu
+def test_result_allgather_best_single_rank_reads_the_device_winner(cuda):
+    """tc_result_allgather_best with one rank: arg-min over the per-trajectory costs and the winner's joint values come
+    back from the device record (lowest index on ties), no communicator needed"""
+    import ctypes as C
+    from tests import helpers
+    capi = helpers.capi
+    s = ms.load_scene()
+    sg = cuda.scene(s, ms.MARGIN, ms.COEFF, ms.BUFFER)
+    q = ms.make_batch(s, 11, 24)
+    r = cuda.eval(sg, q, capi.EVAL_LVS_CONTINUOUS, lvs=ms.LVS, fixed=ms.fixed_steps(), want=capi.WANT_COST | capi.WANT_CONTACTS)
+    _, costs = r.cost()
+    bc, bi, br = C.c_double(), C.c_int64(), C.c_int32()
+    traj = np.zeros(q.shape[1:])
+    cuda.check(cuda.dll.tc_result_allgather_best(r.handle, C.c_int64(1000), None, C.c_int(1), C.byref(bc), C.byref(bi), C.byref(br),
+                                                 traj.ctypes.data_as(C.POINTER(C.c_double))))
+    i = int(np.argmin(costs))
+    assert bc.value == costs[i] and bi.value == 1000 + i and br.value == 0
+    assert np.array_equal(traj, q[i])

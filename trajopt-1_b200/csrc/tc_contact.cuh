@@ -42,9 +42,23 @@ TC_HD double linspaced(int cnt, double lo, double hi, int i)
   return (i == size1) ? hi : (lo + static_cast<double>(i) * step);
 }
 
+// joint values behind an accessor, so that the chain walks below take a stored state (QArray) or a state between two
+// stored ones (QLerp) without a thread-local copy of it
+struct QArray
+{
+  const double* q;
+  TC_HD double operator()(int j) const { return q[j]; }
+};
+struct QLerp
+{
+  const double *q0, *q1;
+  double t;
+  TC_HD double operator()(int j) const { return q0[j] + (q1[j] - q0[j]) * t; }
+};
+
 // pose of frame f given its parent's pose; axis_w = world joint axis
-TC_HD Pose<double> frameStep(const SceneView& v, const Pose<double>& parent, int f, const double* q,
-                             Vec3<double>& axis_w)
+template <class QA>
+TC_HD Pose<double> frameStepA(const SceneView& v, const Pose<double>& parent, int f, const QA& q, Vec3<double>& axis_w)
 {
   const Pose<double> origin = Pose<double>::from12(v.frame_origin + 12 * f);
   Pose<double> T = compose(parent, origin);
@@ -52,10 +66,16 @@ TC_HD Pose<double> frameStep(const SceneView& v, const Pose<double>& parent, int
   axis_w = T.rot(ax);
   const int type = v.frame_type[f];
   if (type == TC_JOINT_REVOLUTE)
-    T = rotateAbout(T, ax, q[v.frame_dof[f]]);
+    T = rotateAbout(T, ax, q(v.frame_dof[f]));
   else if (type == TC_JOINT_PRISMATIC)
-    T.t = T.t + q[v.frame_dof[f]] * axis_w;
+    T.t = T.t + q(v.frame_dof[f]) * axis_w;
   return T;
+}
+
+TC_HD Pose<double> frameStep(const SceneView& v, const Pose<double>& parent, int f, const double* q,
+                             Vec3<double>& axis_w)
+{
+  return frameStepA(v, parent, f, QArray{ q }, axis_w);
 }
 
 // same with the joint value passed in (the FK kernel interpolates it on the fly)
@@ -73,63 +93,73 @@ TC_HD Pose<double> frameStepQ(const SceneView& v, const Pose<double>& parent, in
 }
 
 // world pose of frame lf at joint values q (walks the ancestor path)
-TC_HDN inline Pose<double> framePose(const SceneView& v, int lf, const double* q)
+template <class QA>
+TC_HDN inline Pose<double> framePoseA(const SceneView& v, int lf, const QA& q)
 {
   Pose<double> T = Pose<double>::from12(v.base_pose);
   for (int k = v.path_ptr[lf]; k < v.path_ptr[lf + 1]; ++k)
   {
     Vec3<double> z;
-    T = frameStep(v, T, v.path_frames[k], q, z);
+    T = frameStepA(v, T, v.path_frames[k], q, z);
   }
   return T;
 }
 
-// g[j] = tv . J_trans[:, j]  with the reference point = link origin + ref_offset (world frame)
-TC_HDN inline void pointGradient(const SceneView& v, int link, const double* q, Vec3<double> ref_offset,
-                                 Vec3<double> tv, double* g)
+TC_HDN inline Pose<double> framePose(const SceneView& v, int lf, const double* q)
 {
-  const int lf = v.link_frame[link];
-  for (int j = 0; j < v.n_dof; ++j)
-    g[j] = 0.0;
-  const Vec3<double> p = framePose(v, lf, q).t + ref_offset;
-  Pose<double> T = Pose<double>::from12(v.base_pose);
-  for (int k = v.path_ptr[lf]; k < v.path_ptr[lf + 1]; ++k)
-  {
-    const int f = v.path_frames[k];
-    Vec3<double> z;
-    T = frameStep(v, T, f, q, z);
-    const int type = v.frame_type[f];
-    if (type == TC_JOINT_FIXED)
-      continue;
-    const Vec3<double> col = (type == TC_JOINT_REVOLUTE) ? cross(z, p - T.t) : z;
-    g[v.frame_dof[f]] = col.x * tv.x + col.y * tv.y + col.z * tv.z;
-  }
+  return framePoseA(v, lf, QArray{ q });
 }
 
-// two reference points on the same link at the same joint values in one walk of the chain (the T0 and T1
-// blocks of trajopt_common::getGradient(q0, q1, ...), collision_utils.cpp:215-216)
-TC_HDN inline void pointGradient2(const SceneView& v, int link, const double* q, Vec3<double> ref0, Vec3<double> ref1,
-                                  Vec3<double> tv, double* g0, double* g1)
+// tv . J_trans[:, j] for every joint j on the path of `link`, for two reference points on the link (origin + ref0,
+// origin + ref1, world frame) at the same joint values in one walk of the chain: emit(j, g0, g1).  These are the T0 and
+// T1 blocks of trajopt_common::getGradient(q0, q1, ...) (collision_utils.cpp:215-216); joints off the path have zero
+// columns and are not emitted.
+// dot and cross product with every product and sum placed by hand (one fused multiply-add per term after the first):
+// the same bits from every instantiation of the walk below, whatever the compiler would have contracted around it
+TC_HD double placedDot(Vec3<double> a, Vec3<double> b) { return fma(a.z, b.z, fma(a.y, b.y, TC_MUL(a.x, b.x))); }
+TC_HD Vec3<double> placedCross(Vec3<double> a, Vec3<double> b)
+{
+  return Vec3<double>(fma(a.y, b.z, -TC_MUL(a.z, b.y)), fma(a.z, b.x, -TC_MUL(a.x, b.z)), fma(a.x, b.y, -TC_MUL(a.y, b.x)));
+}
+
+template <class QA, class EMIT>
+TC_HDN inline void pointGradientWalk(const SceneView& v, int link, const QA& q, Vec3<double> ref0, Vec3<double> ref1,
+                                     Vec3<double> tv, EMIT&& emit)
 {
   const int lf = v.link_frame[link];
-  for (int j = 0; j < v.n_dof; ++j)
-    g0[j] = g1[j] = 0.0;
-  const Vec3<double> pl = framePose(v, lf, q).t;
+  const Vec3<double> pl = framePoseA(v, lf, q).t;
   const Vec3<double> p0 = pl + ref0, p1 = pl + ref1;
   Pose<double> T = Pose<double>::from12(v.base_pose);
   for (int k = v.path_ptr[lf]; k < v.path_ptr[lf + 1]; ++k)
   {
     const int f = v.path_frames[k];
     Vec3<double> z;
-    T = frameStep(v, T, f, q, z);
+    T = frameStepA(v, T, f, q, z);
     const int type = v.frame_type[f];
     if (type == TC_JOINT_FIXED)
       continue;
-    const Vec3<double> c0 = (type == TC_JOINT_REVOLUTE) ? cross(z, p0 - T.t) : z;
-    const Vec3<double> c1 = (type == TC_JOINT_REVOLUTE) ? cross(z, p1 - T.t) : z;
-    g0[v.frame_dof[f]] = c0.x * tv.x + c0.y * tv.y + c0.z * tv.z;
-    g1[v.frame_dof[f]] = c1.x * tv.x + c1.y * tv.y + c1.z * tv.z;
+    const Vec3<double> c0 = (type == TC_JOINT_REVOLUTE) ? placedCross(z, p0 - T.t) : z;
+    const Vec3<double> c1 = (type == TC_JOINT_REVOLUTE) ? placedCross(z, p1 - T.t) : z;
+    emit(v.frame_dof[f], placedDot(c0, tv), placedDot(c1, tv));
   }
+}
+
+// g[j] = tv . J_trans[:, j]  with the reference point = link origin + ref_offset (world frame)
+TC_HDN inline void pointGradient(const SceneView& v, int link, const double* q, Vec3<double> ref_offset,
+                                 Vec3<double> tv, double* g)
+{
+  for (int j = 0; j < v.n_dof; ++j)
+    g[j] = 0.0;
+  pointGradientWalk(v, link, QArray{ q }, ref_offset, ref_offset, tv, [&](int j, double g0, double) { g[j] = g0; });
+}
+
+// two reference points on the same link at the same joint values
+TC_HDN inline void pointGradient2(const SceneView& v, int link, const double* q, Vec3<double> ref0, Vec3<double> ref1,
+                                  Vec3<double> tv, double* g0, double* g1)
+{
+  for (int j = 0; j < v.n_dof; ++j)
+    g0[j] = g1[j] = 0.0;
+  pointGradientWalk(v, link, QArray{ q }, ref0, ref1, tv, [&](int j, double a, double b) { g0[j] = a, g1[j] = b; });
 }
 
 // GetAverageSupport: mean of all hull vertices within BULLET_EPSILON of the running maximum
@@ -218,9 +248,9 @@ TC_HDN inline void averageSupportHull2(const SceneView& v, const ShapeD& sh, Vec
   pt1 = (1.0 / cnt1) * sum1;
 }
 
-// calculateContinuousData for link slot i of a cast contact
-TC_HDN inline void continuousData(const SceneView& v, tc_contact& c, const ShapeD& sh, const Pose<double>& tf0,
-                                  const Pose<double>& tf1, Vec3<double> pt_world, Vec3<double> normal_world, int i)
+// calculateContinuousData for one link of a cast contact
+TC_HDN inline void continuousData(const SceneView& v, const ShapeD& sh, const Pose<double>& tf0, const Pose<double>& tf1,
+                                  Vec3<double> pt_world, Vec3<double> normal_world, double& cc_time, int& cc_type)
 {
   const double SUPPORT_TOL = 0.01, LENGTH_TOL = 0.001;
   double s0, s1;
@@ -236,41 +266,41 @@ TC_HDN inline void continuousData(const SceneView& v, tc_contact& c, const Shape
   const double sup0 = dot(normal_world, pw0), sup1 = dot(normal_world, pw1);
   if (sup0 - sup1 > SUPPORT_TOL)
   {
-    c.cc_time[i] = 0;
-    c.cc_type[i] = TC_CC_TIME0;
+    cc_time = 0;
+    cc_type = TC_CC_TIME0;
   }
   else if (sup1 - sup0 > SUPPORT_TOL)
   {
-    c.cc_time[i] = 1;
-    c.cc_type[i] = TC_CC_TIME1;
+    cc_time = 1;
+    cc_type = TC_CC_TIME1;
   }
   else
   {
     const double l0c = norm(pt_world - pw0), l1c = norm(pt_world - pw1);
-    c.cc_type[i] = TC_CC_BETWEEN;
-    c.cc_time[i] = (l0c + l1c < LENGTH_TOL) ? 0.5 : l0c / (l0c + l1c);
+    cc_type = TC_CC_BETWEEN;
+    cc_time = (l0c + l1c < LENGTH_TOL) ? 0.5 : l0c / (l0c + l1c);
   }
 }
 
 // trajopt_common::removeInvalidContactResults predicate (true = drop)
-TC_HD bool invalidContact(const tc_contact& r, double margin, double buffer, bool f0, bool f1)
+TC_HD bool invalidContact(double distance, int cc_type0, int cc_type1, double margin, double buffer, bool f0, bool f1)
 {
-  if (r.distance > margin + buffer)
+  if (distance > margin + buffer)
     return true;
   if (!f0 && !f1)
     return false;
   if (f0)
   {
-    if (r.cc_type[0] != TC_CC_NONE && r.cc_type[0] != TC_CC_TIME0)
+    if (cc_type0 != TC_CC_NONE && cc_type0 != TC_CC_TIME0)
       return false;
-    if (r.cc_type[1] != TC_CC_NONE && r.cc_type[1] != TC_CC_TIME0)
+    if (cc_type1 != TC_CC_NONE && cc_type1 != TC_CC_TIME0)
       return false;
   }
   if (f1)
   {
-    if (r.cc_type[0] != TC_CC_NONE && r.cc_type[0] != TC_CC_TIME1)
+    if (cc_type0 != TC_CC_NONE && cc_type0 != TC_CC_TIME1)
       return false;
-    if (r.cc_type[1] != TC_CC_NONE && r.cc_type[1] != TC_CC_TIME1)
+    if (cc_type1 != TC_CC_NONE && cc_type1 != TC_CC_TIME1)
       return false;
   }
   return true;
@@ -288,90 +318,66 @@ struct UnitInfo
   bool f0, f1;   // vars0_fixed, vars1_fixed
 };
 
-// Builds the ContactResult of a raw hit.  xf (optional) = transform[0], cc_transform[0], transform[1],
-// cc_transform[1] (4 x 12 doubles).  pose0/pose1: link poses of both links at the unit's T0 / T1 state.
-// Returns false when the evaluators' filters drop the contact.
+// Builds the ContactResult of a raw hit in place (c may be the record in global memory: every field is written once,
+// nothing is read back).  pose0[i] / pose1[i]: 3x4 row-major pose of link i at the unit's T0 / T1 state (pose1 == pose0
+// for a link that does not move); they are loaded link by link, so that only one link's poses are live at a time.
+// transform[i] / cc_transform[i] of the result are not stored: they are pose0[i] and, for a cast or interpolated
+// contact, pose1[i] resp. pose0[i] (contactTransforms).  Returns false when the evaluators' filters drop the contact.
 TC_HDN inline bool finalizeContact(const SceneView& v, const EvalParams& ep, const RawContact& raw, const UnitInfo& u,
-                                   const Pose<double> pose0[2], const Pose<double> pose1[2], tc_contact& c, double* xf)
+                                   const double* const pose0[2], const double* const pose1[2], tc_contact& c)
 {
   const ShapePairD sp = v.spairs[raw.sp];
   const PairD pr = v.pairs[sp.pair];
-  const ShapeD& A = v.shapes[sp.sa];
-  const ShapeD& B = v.shapes[sp.sb];
   const bool cast = ep.evaluator == TC_EVAL_CONTINUOUS || ep.evaluator == TC_EVAL_LVS_CONTINUOUS;
   const Vec3<double> n(raw.normal[0], raw.normal[1], raw.normal[2]);
-  const Vec3<double> p[2] = { Vec3<double>(raw.pa[0], raw.pa[1], raw.pa[2]),
-                              Vec3<double>(raw.pb[0], raw.pb[1], raw.pb[2]) };
   c.distance = raw.distance;
   c.normal[0] = n.x, c.normal[1] = n.y, c.normal[2] = n.z;
-  Pose<double> cc_tf[2];
-  for (int i = 0; i < 2; ++i)
-  {
-    const Vec3<double> pl = pose0[i].applyInv(p[i]);
-    c.nearest_points[i][0] = p[i].x, c.nearest_points[i][1] = p[i].y, c.nearest_points[i][2] = p[i].z;
-    c.nearest_points_local[i][0] = pl.x, c.nearest_points_local[i][1] = pl.y, c.nearest_points_local[i][2] = pl.z;
-    c.cc_time[i] = -1;
-    c.cc_type[i] = TC_CC_NONE;
-    c.subshape_id[i] = -1;
-  }
   c.link_ids[0] = pr.a, c.link_ids[1] = pr.b;
-  c.shape_id[0] = A.shape_id, c.shape_id[1] = B.shape_id;
   c.traj = u.traj;
   c.term = u.t;
   c.substep = u.substep;
   c.pair = sp.pair;
   c.state = u.state0;
   c.flags = raw.flags;
-  const bool active[2] = { pr.a < v.n_active, pr.b < v.n_active };
-  if (cast)
+  int cc_type[2];
+#pragma unroll
+  for (int i = 0; i < 2; ++i)
   {
+    const ShapeD& sh = v.shapes[i ? sp.sb : sp.sa];
+    const Vec3<double> p = i ? Vec3<double>(raw.pb[0], raw.pb[1], raw.pb[2]) : Vec3<double>(raw.pa[0], raw.pa[1], raw.pa[2]);
+    const bool active = (i ? pr.b : pr.a) < v.n_active;
+    const Pose<double> tf0 = Pose<double>::from12(pose0[i]);
+    const Vec3<double> pl = tf0.applyInv(p);
+    c.nearest_points[i][0] = p.x, c.nearest_points[i][1] = p.y, c.nearest_points[i][2] = p.z;
+    c.nearest_points_local[i][0] = pl.x, c.nearest_points_local[i][1] = pl.y, c.nearest_points_local[i][2] = pl.z;
+    c.shape_id[i] = sh.shape_id;
+    c.subshape_id[i] = -1;
+    double time = -1;
+    int type = TC_CC_NONE;
     // the cast shape's normal points away from itself
-    if (active[0])
+    if (cast && active)
+      continuousData(v, sh, tf0, Pose<double>::from12(pose1[i]), p, i ? -n : n, time, type);
+    if (u.interp && active)
     {
-      continuousData(v, c, A, pose0[0], pose1[0], p[0], n, 0);
-      cc_tf[0] = pose1[0];
-    }
-    if (active[1])
-    {
-      continuousData(v, c, B, pose0[1], pose1[1], p[1], -n, 1);
-      cc_tf[1] = pose1[1];
-    }
-  }
-  if (u.interp)
-  {
-    const bool discrete = !cast;
-    const double dt = 1.0 / static_cast<double>(u.last);
-    const double i_dt = static_cast<double>(u.substep) * dt;
-    for (int j = 0; j < 2; ++j)
-    {
-      if (!active[j])
-        continue;
-      c.cc_time[j] = (c.cc_time[j] < 0) ? i_dt : i_dt + (c.cc_time[j] * dt);
-      if (u.substep == 0 && (c.cc_type[j] == TC_CC_TIME0 || c.cc_type[j] == TC_CC_NONE))
-        c.cc_type[j] = TC_CC_TIME0;
-      else if (u.substep == u.last && (c.cc_type[j] == TC_CC_TIME1 || c.cc_type[j] == TC_CC_NONE))
-        c.cc_type[j] = TC_CC_TIME1;
+      const double dt = 1.0 / static_cast<double>(u.last);
+      const double i_dt = static_cast<double>(u.substep) * dt;
+      time = (time < 0) ? i_dt : i_dt + (time * dt);
+      if (u.substep == 0 && (type == TC_CC_TIME0 || type == TC_CC_NONE))
+        type = TC_CC_TIME0;
+      else if (u.substep == u.last && (type == TC_CC_TIME1 || type == TC_CC_NONE))
+        type = TC_CC_TIME1;
       else
-        c.cc_type[j] = TC_CC_BETWEEN;
-      if (discrete)
-      {
-        cc_tf[0] = pose0[0];
-        cc_tf[1] = pose0[1];
-      }
+        type = TC_CC_BETWEEN;
     }
-  }
-  if (xf)
-  {
-    pose0[0].to12(xf + 0);
-    cc_tf[0].to12(xf + 12);
-    pose0[1].to12(xf + 24);
-    cc_tf[1].to12(xf + 36);
+    c.cc_time[i] = time;
+    c.cc_type[i] = type;
+    cc_type[i] = type;
   }
   if (pr.zero_coeff)
     return false;
   if (ep.evaluator == TC_EVAL_DISCRETE)
-    return !(c.distance > pr.margin + v.margin_buffer);
-  return !invalidContact(c, pr.margin, v.margin_buffer, u.f0, u.f1);
+    return !(raw.distance > pr.margin + v.margin_buffer);
+  return !invalidContact(raw.distance, cc_type[0], cc_type[1], pr.margin, v.margin_buffer, u.f0, u.f1);
 }
 
 // bits of GradOut::has: link l, block k (0 = gradients[], 1 = cc_gradients[]) -> bit 2*l + k

@@ -150,6 +150,33 @@ __device__ __forceinline__ const void* stagedLutB(const ShapeD& A, const ShapeD&
                      : nullptr;
 }
 
+// A pose parked in shared memory: element k (3x4 row-major, as in the pose arena) of this thread at base[k * STRIDE].
+// STRIDE = threads per CTA for a per-thread pose (lanes read consecutive 8-byte words: conflict-free), 1 for a pose
+// the whole CTA shares (a static partner: every lane reads the same word, a broadcast).  The loads are volatile so that
+// the compiler re-reads shared memory instead of carrying 12 doubles (24 registers) per pose through the GJK loop.
+template <class R, int STRIDE>
+struct SmemPose
+{
+  const R* base;
+  __device__ __forceinline__ R g(int k) const { return *reinterpret_cast<const volatile R*>(base + k * STRIDE); }
+  __device__ __forceinline__ Vec3<R> rot(Vec3<R> v) const
+  {
+    return Vec3<R>(g(0) * v.x + g(1) * v.y + g(2) * v.z, g(4) * v.x + g(5) * v.y + g(6) * v.z,
+                   g(8) * v.x + g(9) * v.y + g(10) * v.z);
+  }
+  __device__ __forceinline__ Vec3<R> rotT(Vec3<R> v) const
+  {
+    return Vec3<R>(g(0) * v.x + g(4) * v.y + g(8) * v.z, g(1) * v.x + g(5) * v.y + g(9) * v.z,
+                   g(2) * v.x + g(6) * v.y + g(10) * v.z);
+  }
+  __device__ __forceinline__ Vec3<R> apply(Vec3<R> v) const { return rot(v) + Vec3<R>(g(3), g(7), g(11)); }
+  __device__ __forceinline__ Vec3<R> applyInv(Vec3<R> p) const { return rotT(p - Vec3<R>(g(3), g(7), g(11))); }
+};
+
+#ifndef TC_GJK_SMEM_POSES
+#define TC_GJK_SMEM_POSES 1
+#endif
+
 // K3a: GJK for every bucketed item.  Separated pairs are finished here; touching / penetrating pairs hand
 // their simplex to the EPA stage through a per-shape-pair packed arena (SoA, 24 doubles per item).
 template <class R, int MINB>
@@ -160,6 +187,13 @@ __global__ void __launch_bounds__(TC_GJK_NT, MINB * 128 / TC_GJK_NT) k_gjk(Scene
   __shared__ RunInfo s_run;
   __shared__ int s_next;
   Vtx<R>* sv = reinterpret_cast<Vtx<R>*>(smem_raw);
+#if TC_GJK_SMEM_POSES
+  // behind the staged hulls and tables: the two poses of every thread's moving shape, [24][threads]; and the one pose
+  // of a static partner, shared by the CTA
+  __shared__ R s_bpose[12];
+  R* s_apose = reinterpret_cast<R*>(smem_raw + (static_cast<size_t>(2 * v.max_hull_verts) * sizeof(Vtx<R>) +
+                                                2 * static_cast<size_t>(v.max_lut_bytes) + 15) / 16 * 16);
+#endif
   if (passOverflowed(w))
     return;
   const int range_end = static_cast<int>(min(static_cast<long long>(blockIdx.x + 1) * run_items, w.counters->n_items_padded));
@@ -185,6 +219,14 @@ __global__ void __launch_bounds__(TC_GJK_NT, MINB * 128 / TC_GJK_NT) k_gjk(Scene
       item0 = run.q1;
       continue;
     }
+#if TC_GJK_SMEM_POSES
+    if (pr.b >= v.n_active)
+    {
+      if (threadIdx.x < 12)
+        s_bpose[threadIdx.x] = static_cast<R>(v.link_pose[12 * pr.b + threadIdx.x]);
+      __syncthreads();  // (the previous run's readers passed the barrier at the end of their run)
+    }
+#endif
     if (A.vert_cnt + B.vert_cnt > 0)
     {
       stageHulls<R>(v, A, B, sv, &bar, phase & 1);
@@ -206,6 +248,46 @@ __global__ void __launch_bounds__(TC_GJK_NT, MINB * 128 / TC_GJK_NT) k_gjk(Scene
       if (live)
       {
         u = w.items[slot];
+#if TC_GJK_SMEM_POSES
+        if (pr.b >= v.n_active && pr.a < v.n_active && A.type == SH_HULL && B.type == SH_HULL)
+        {
+          // the common case (group hull against a static hull): poses live in shared memory, not in registers
+          const double* pa = posePtr(w, pr.a, w.item_state[slot]);
+          R* mine = s_apose + threadIdx.x;
+          const int np = w.cast ? 24 : 12;
+#pragma unroll 4
+          for (int k = 0; k < np; ++k)
+            mine[k * TC_GJK_NT] = static_cast<R>(pa[k]);
+          Placed<R, SmemPose<R, TC_GJK_NT>> QA;
+          Placed<R, SmemPose<R, 1>> QB;
+          QA.sh = makeCore<R>(A, sv, stagedLutA<R>(A, B, sv));
+          QB.sh = makeCore<R>(B, sv + A.vert_cnt, stagedLutB<R>(A, B, sv));
+          QA.sh.type = SH_HULL;
+          QB.sh.type = SH_HULL;
+          QA.p0.base = mine;
+          QB.p0.base = s_bpose;
+          QB.p1.base = s_bpose;
+          QB.cast = false;
+          if (w.cast)
+          {
+            QA.p1.base = mine + 12 * TC_GJK_NT;
+            QA.cast = true;
+            distanceGjk<R>(QA, QB, thr, S, d);
+          }
+          else
+          {
+            QA.p1.base = mine;
+            QA.cast = false;
+            distanceGjk<R>(QA, QB, thr, S, d);
+          }
+          st_gjk += d.gjk_iters;
+          st_scan += static_cast<long long>(d.scanned & 0xffffffffull);
+          st_cmp += static_cast<long long>(d.scanned >> 32);
+          st_unconv += (d.status != ND_NEED_EPA && !d.converged) ? 1 : 0;
+        }
+        else
+        {
+#endif
         Placed<R> PA, PB;
         placeItem<R>(v, w, w.item_state[slot], spd, pr, A, B, sv, sv + A.vert_cnt, PA, PB, stagedLutA<R>(A, B, sv),
                      stagedLutB<R>(A, B, sv));
@@ -239,6 +321,9 @@ __global__ void __launch_bounds__(TC_GJK_NT, MINB * 128 / TC_GJK_NT) k_gjk(Scene
         st_scan += static_cast<long long>(d.scanned & 0xffffffffull);
         st_cmp += static_cast<long long>(d.scanned >> 32);
         st_unconv += (d.status != ND_NEED_EPA && !d.converged) ? 1 : 0;
+#if TC_GJK_SMEM_POSES
+        }
+#endif
       }
       storeHit<R>(w, d, u, sp, d.status == ND_CONTACT);
       const bool need = d.status == ND_NEED_EPA;
@@ -448,7 +533,7 @@ __global__ void k_fma_peak(R* out, int iters)
 
 // register budgets (resident CTAs of 128 threads per SM) of the two kernels; build-time tuning knobs
 #ifndef TC_GJK_MINB
-#define TC_GJK_MINB 3
+#define TC_GJK_MINB 4
 #endif
 #ifndef TC_EPA_MINB
 #define TC_EPA_MINB 4
@@ -459,7 +544,10 @@ static cudaError_t launchNarrowT(const SceneView& v, const Work& w, cudaStream_t
 {
   const int run_g = GJK_RUN_ITEMS;  // items per GJK CTA (hulls are staged once per run of one shape pair)
   const unsigned grid_g = static_cast<unsigned>((w.n_items_padded + run_g - 1) / run_g);
-  const size_t smem = static_cast<size_t>(2 * v.max_hull_verts) * sizeof(Vtx<R>) + 2 * static_cast<size_t>(v.max_lut_bytes) + 16;
+  size_t smem = static_cast<size_t>(2 * v.max_hull_verts) * sizeof(Vtx<R>) + 2 * static_cast<size_t>(v.max_lut_bytes) + 16;
+#if TC_GJK_SMEM_POSES
+  smem = (smem + 15) / 16 * 16 + static_cast<size_t>(24 * TC_GJK_NT) * sizeof(R);  // + the threads' two poses
+#endif
   cudaFuncSetAttribute(k_gjk<R, GB>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem));
   cudaError_t e = launchFill(w.epa_cursor, 0, v.n_spairs, st);
   if (e != cudaSuccess)

@@ -258,8 +258,8 @@ TC_NI int hullScanFull(const Vtx<R>* verts, int n, Vec3<R> d0, Vec3<R> d1, bool 
   return b0 | (b1 << 16);
 }
 
-template <class R>
-TC_NI Vec3<R> primitiveSupportPlaced(ShapeCore<R> sh, Pose<R> p0, Pose<R> p1, bool cast, Vec3<R> d)
+template <class R, class P>
+TC_NI Vec3<R> primitiveSupportPlaced(ShapeCore<R> sh, P p0, P p1, bool cast, Vec3<R> d)
 {
   const Vec3<R> w0 = p0.apply(primitiveSupport(sh, p0.rotT(d)));
   if (!cast)
@@ -270,11 +270,13 @@ TC_NI Vec3<R> primitiveSupportPlaced(ShapeCore<R> sh, Pose<R> p0, Pose<R> p1, bo
 
 // A shape placed in the world, optionally swept between two poses (convex hull of both placements):
 // support(d) = better of the supports at pose0 and pose1.
-template <class R>
+// P = how the two poses are held: Pose<R> (values, i.e. registers) or a view of poses parked in shared memory
+// (tc_narrow.cu SmemPose: three poses are 72 of a GJK thread's 168 registers)
+template <class R, class P = Pose<R>>
 struct Placed
 {
   ShapeCore<R> sh;
-  Pose<R> p0, p1;
+  P p0, p1;
   bool cast;
 
   // `scanned` counts the vertices of the hull per queried pose (the work of the plain scan the reference's
@@ -555,8 +557,8 @@ TC_HD void putPoint(Simplex<R>& s, int k, Vec3<R> w, Vec3<R> a)
     s.w[3] = w, s.a[3] = a;
 }
 
-template <class R>
-TC_HD GjkOut<R> gjk(const Placed<R>& A, const Placed<R>& B, R threshold_core, Simplex<R>& S, ScanCount& scanned)
+template <class R, class PLA, class PLB>
+TC_HD GjkOut<R> gjk(const PLA& A, const PLB& B, R threshold_core, Simplex<R>& S, ScanCount& scanned)
 {
   GjkOut<R> r;
   r.separated_beyond = false;
@@ -822,8 +824,8 @@ TC_HD void epaOffer(EpaState<R>& E, int f, R d)
 }
 
 // returns 0: polytope ready, run trips; 1: finished already (flat Minkowski difference), r is final
-template <class R, bool MASK>
-TC_HDN int epaInit(const Placed<R>& A, const Placed<R>& B, const Simplex<R>& start, R scale, EpaStore<R>& st,
+template <class R, bool MASK, class PLA, class PLB>
+TC_HDN int epaInit(const PLA& A, const PLB& B, const Simplex<R>& start, R scale, EpaStore<R>& st,
                    EpaState<R>& E, EpaOut<R>& r, ScanCount& scanned)
 {
   r.ok = true;
@@ -975,8 +977,8 @@ TC_HD int lowestBit(unsigned long long x)
 //      and cancels), 3. visible faces again, slot order: the edges still set are the horizon, in the order the
 //      list-based form produces them, 4. one new face per horizon edge.
 // `erow` is all-zero on entry and on exit.
-template <class R>
-TC_HD int epaTripMasked(const Placed<R>& A, const Placed<R>& B, EpaStore<R>& st, EpaState<R>& E,
+template <class R, class PLA, class PLB>
+TC_HD int epaTripMasked(const PLA& A, const PLB& B, EpaStore<R>& st, EpaState<R>& E,
                         unsigned long long* erow, ScanCount& scanned)
 {
   const R DEGENERATE = -lowestReal<R>();
@@ -1098,8 +1100,8 @@ TC_HD int epaTripMasked(const Placed<R>& A, const Placed<R>& B, EpaStore<R>& st,
   return EPA_CONTINUE;
 }
 
-template <class R, bool MASK>
-TC_HDN int epaTrip(const Placed<R>& A, const Placed<R>& B, EpaStore<R>& st, EpaState<R>& E, ScanCount& scanned)
+template <class R, bool MASK, class PLA, class PLB>
+TC_HDN int epaTrip(const PLA& A, const PLB& B, EpaStore<R>& st, EpaState<R>& E, ScanCount& scanned)
 {
   const R DEGENERATE = -lowestReal<R>();
   const Vec3<R> bn = st.fn[E.best];
@@ -1261,8 +1263,8 @@ TC_HDN void epaFinish(const EpaStore<R>& st, const EpaState<R>& E, EpaOut<R>& r)
   r.pb = r.pa - pw;
 }
 
-template <class R, bool MASK>
-TC_HDN EpaOut<R> epa(const Placed<R>& A, const Placed<R>& B, const Simplex<R>& start, R scale, EpaStore<R>& st,
+template <class R, bool MASK, class PLA, class PLB>
+TC_HDN EpaOut<R> epa(const PLA& A, const PLB& B, const Simplex<R>& start, R scale, EpaStore<R>& st,
                      ScanCount& scanned)
 {
   EpaOut<R> r;
@@ -1294,8 +1296,8 @@ TC_HDN EpaOut<R> epa(const Placed<R>& A, const Placed<R>& B, const Simplex<R>& s
 }
 
 // length scale of the Minkowski difference used by EPA's degeneracy thresholds
-template <class R>
-TC_HD R epaScale(const Placed<R>& A, R brad_a, const Placed<R>& B, R brad_b)
+template <class R, class PLA, class PLB>
+TC_HD R epaScale(const PLA& A, R brad_a, const PLB& B, R brad_b)
 {
   R s = 2 * (brad_a + brad_b);
   if (A.cast)
@@ -1336,8 +1338,8 @@ TC_HD void clearDist(DistOut<R>& out)
   out.scanned = 0;
 }
 
-template <class R>
-TC_HD void finishDist(const Placed<R>& A, const Placed<R>& B, R threshold, R d_core, Vec3<R> n, Vec3<R> pa, Vec3<R> pb,
+template <class R, class PLA, class PLB>
+TC_HD void finishDist(const PLA& A, const PLB& B, R threshold, R d_core, Vec3<R> n, Vec3<R> pa, Vec3<R> pb,
                       DistOut<R>& out)
 {
   const R ra = A.sh.coreRadius(), rb = B.sh.coreRadius();
@@ -1354,8 +1356,8 @@ TC_HD void finishDist(const Placed<R>& A, const Placed<R>& B, R threshold, R d_c
 }
 
 // stage 1: GJK.  ND_NONE / ND_CONTACT are final; ND_NEED_EPA leaves the simplex in S for stage 2
-template <class R>
-TC_HD void distanceGjk(const Placed<R>& A, const Placed<R>& B, R threshold, Simplex<R>& S, DistOut<R>& out)
+template <class R, class PLA, class PLB>
+TC_HD void distanceGjk(const PLA& A, const PLB& B, R threshold, Simplex<R>& S, DistOut<R>& out)
 {
   clearDist(out);
   const R ra = A.sh.coreRadius(), rb = B.sh.coreRadius();
@@ -1373,8 +1375,8 @@ TC_HD void distanceGjk(const Placed<R>& A, const Placed<R>& B, R threshold, Simp
 }
 
 // stage 2: EPA from the GJK simplex (out carries the stage-1 counters and convergence flag)
-template <class R, bool MASK>
-TC_HD void distanceEpa(const Placed<R>& A, R brad_a, const Placed<R>& B, R brad_b, R threshold, const Simplex<R>& S,
+template <class R, bool MASK, class PLA, class PLB>
+TC_HD void distanceEpa(const PLA& A, R brad_a, const PLB& B, R brad_b, R threshold, const Simplex<R>& S,
                        EpaStore<R>& store, DistOut<R>& out)
 {
   const EpaOut<R> e = epa<R, MASK>(A, B, S, epaScale(A, brad_a, B, brad_b), store, out.scanned);
@@ -1389,8 +1391,8 @@ TC_HD void distanceEpa(const Placed<R>& A, R brad_a, const Placed<R>& B, R brad_
   finishDist(A, B, threshold, -e.depth, e.normal, e.pa, e.pb, out);
 }
 
-template <class R, bool MASK>
-TC_HDN DistOut<R> signedDistance(const Placed<R>& A, R brad_a, const Placed<R>& B, R brad_b, R threshold,
+template <class R, bool MASK, class PLA, class PLB>
+TC_HDN DistOut<R> signedDistance(const PLA& A, R brad_a, const PLB& B, R brad_b, R threshold,
                                  EpaStore<R>& store)
 {
   DistOut<R> out;

@@ -439,26 +439,17 @@ __global__ void __launch_bounds__(TPB, TC_FINALIZE_MINB) k_finalize(SceneView v,
     const UnitInfo ui = unitInfo(w, raw.unit);
     const ShapePairD sp = v.spairs[raw.sp];
     const PairD pr = v.pairs[sp.pair];
-    Pose<double> p0[2], p1[2];
+    const double* p0[2];
+    const double* p1[2];
     const int links[2] = { pr.a, pr.b };
 #pragma unroll
     for (int j = 0; j < 2; ++j)
     {
-      if (links[j] < v.n_active)
-      {
-        const double* src = posePtr(w, links[j], ui.state0);
-        p0[j] = Pose<double>::from12(src);
-        p1[j] = w.cast ? Pose<double>::from12(src + 12) : p0[j];
-      }
-      else
-      {
-        p0[j] = Pose<double>::from12(v.link_pose + 12 * links[j]);
-        p1[j] = p0[j];
-      }
+      const bool active = links[j] < v.n_active;
+      p0[j] = active ? posePtr(w, links[j], ui.state0) : v.link_pose + 12 * links[j];
+      p1[j] = (active && w.cast) ? p0[j] + 12 : p0[j];
     }
-    tc_contact c;
-    valid = finalizeContact(v, w.ep, raw, ui, p0, p1, c, nullptr);
-    w.contacts_tmp[i] = c;
+    valid = finalizeContact(v, w.ep, raw, ui, p0, p1, w.contacts_tmp[i]);
     unsigned long long key = ~0ull;
     if (w.contact_type != TC_CONTACT_ALL)
     {
@@ -713,10 +704,10 @@ __device__ __forceinline__ void writeRow(const SceneView& v, const Work& w, long
 #pragma unroll
       for (int l = 0; l < 2; ++l)
         if (has & (1 << (2 * l + blk)))
-          s += (blk ? rec.scale1[l] : rec.scale0[l]) * g[(2 * l + blk) * n + j];
+          s = fma(blk ? rec.scale1[l] : rec.scale0[l], g[(2 * l + blk) * n + j], s);
       if (w.ep.stack == TC_STACK_LEGACY)
       {
-        constant -= s * qb[j];
+        constant = fma(-s, qb[j], constant);
         val[nnz] = s;
       }
       else
@@ -781,6 +772,161 @@ __global__ void __launch_bounds__(TPB, TC_GRADROWS_MINB) k_grad_rows(SceneView v
   GradOut out;
   contactGradient(v, w.ep, c, xf, q0, q1, w.term_fixed[2 * ti] != 0, w.term_fixed[2 * ti + 1] != 0, qt, g, out);
   writeRow(v, w, i, c, g, out.rec, out.has, term_row_base, col_idx, val, row_value, row_coeff, row_margin);
+}
+
+// The same rows for chains of up to NR joints with nothing in thread-local memory (the general kernel above keeps the
+// contact, its transforms and four gradient vectors on the stack: 1.1 kB per thread that the ncu capture of round 2
+// shows written back to DRAM, 5 GB per C4 pass).  The contact is read field by field where it lies, the joint values
+// come through an accessor, and the per-joint sums of writeRow live in two statically indexed register arrays.  The
+// arithmetic is contactGradient's and writeRow's, operation for operation (the on-demand path must give the same bits:
+// tests/test_gpu_parity.py::test_rows_folded_inside_the_pass_equal_rows_on_demand).
+template <int NR>
+struct RowSums
+{
+  double s0[NR], s1[NR];
+  __device__ __forceinline__ void add(int j, bool use0, double sc0, double g0, bool use1, double sc1, double g1)
+  {
+#pragma unroll
+    for (int jj = 0; jj < NR; ++jj)
+      if (jj == j)
+      {
+        if (use0)
+          s0[jj] = fma(sc0, g0, s0[jj]);
+        if (use1)
+          s1[jj] = fma(sc1, g1, s1[jj]);
+      }
+  }
+};
+
+__device__ __forceinline__ Vec3<double> rotBy(const double* p12, Vec3<double> x)
+{
+  return p12 ? Pose<double>::from12(p12).rot(x) : Pose<double>().rot(x);
+}
+
+template <int NR, bool GATHER>
+__global__ void __launch_bounds__(TPB, TC_GRADROWS_MINB) k_grad_rows_regs(SceneView v, Work w, const long long* term_row_base,
+                                                                         int32_t* col_idx, double* val, double* row_value,
+                                                                         double* row_coeff, double* row_margin)
+{
+  if (passOverflowed(w))
+    return;
+  const long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (i > w.counters->n_valid)
+    return;
+  if (i == w.counters->n_valid)
+  {
+    w.row_ptr[i] = term_row_base[w.ep.n_terms];
+    return;
+  }
+  const tc_contact* cp = GATHER ? w.contacts_tmp + w.idx_alt[i] : w.contacts + i;
+  if (GATHER)
+  {
+    constexpr int WC = sizeof(tc_contact) / 8;
+    const double* src = reinterpret_cast<const double*>(cp);
+    double* dst = reinterpret_cast<double*>(w.contacts + i);
+#pragma unroll
+    for (int k = 0; k < WC; ++k)
+      dst[k] = src[k];
+  }
+  const int k = termOfContact(w, i);
+  const int ti = k % w.ep.terms_per_traj;
+  const bool f0 = w.term_fixed[2 * ti] != 0, f1 = w.term_fixed[2 * ti + 1] != 0;
+  const bool single = w.ep.evaluator == TC_EVAL_DISCRETE;
+  const bool legacy = w.ep.stack == TC_STACK_LEGACY;
+  const bool lvs_discrete = w.ep.evaluator == TC_EVAL_LVS_DISCRETE;
+  const int n = v.n_dof;
+  const int term = cp->term, state = cp->state, pair = cp->pair;
+  const double distance = cp->distance;
+  const double* q0 = w.q + (static_cast<size_t>(cp->traj) * w.ep.T + term) * n;
+  const double* q1 = single ? q0 : q0 + n;
+  RowSums<NR> sum;
+#pragma unroll
+  for (int jj = 0; jj < NR; ++jj)
+    sum.s0[jj] = sum.s1[jj] = 0.0;
+  const Vec3<double> nrm(cp->normal[0], cp->normal[1], cp->normal[2]);
+#pragma unroll 1
+  for (int l = 0; l < 2; ++l)
+  {
+    const int link = cp->link_ids[l];
+    if (link >= v.n_active)
+      continue;
+    const int cct = cp->cc_type[l];
+    const double cc_time = cp->cc_time[l];
+    const bool cc = cct != TC_CC_NONE;
+    const Vec3<double> pl(cp->nearest_points_local[l][0], cp->nearest_points_local[l][1], cp->nearest_points_local[l][2]);
+    const Vec3<double> tv = (l == 0) ? -nrm : nrm;
+    const double* t0 = posePtr(w, link, state);                                        // transform[l]
+    const double* t1 = w.cast ? t0 + 12 : (lvs_discrete ? t0 : nullptr);               // cc_transform[l]
+    const double sc0 = cc ? (1 - cc_time) : 1.0, sc1 = cc ? cc_time : 1.0;
+    if (legacy || single)
+    {
+      // one GetGradient per free timestep block, each at that block's own joint values (linkGradient)
+      if (single || !f0)
+      {
+        const Vec3<double> ref = rotBy(t0, pl);
+        pointGradientWalk(v, link, QArray{ q0 }, ref, ref, tv,
+                          [&](int j, double g, double) { sum.add(j, true, sc0, g, false, 0.0, 0.0); });
+      }
+      if (legacy && !single && !f1)
+      {
+        const Vec3<double> ref = rotBy(cc ? t1 : t0, pl);
+        pointGradientWalk(v, link, QArray{ q1 }, ref, ref, tv,
+                          [&](int j, double g, double) { sum.add(j, false, 0.0, 0.0, true, sc1, g); });
+      }
+    }
+    else
+    {
+      // both blocks share the joint values: one chain walk, two reference points
+      const Vec3<double> ref0 = rotBy(t0, pl), ref1 = rotBy(cc ? t1 : t0, pl);
+      auto emit = [&](int j, double g0, double g1) { sum.add(j, true, sc0, g0, true, sc1, g1); };
+      if (cct == TC_CC_TIME0)
+        pointGradientWalk(v, link, QArray{ q0 }, ref0, ref1, tv, emit);
+      else if (cct == TC_CC_TIME1)
+        pointGradientWalk(v, link, QArray{ q1 }, ref0, ref1, tv, emit);
+      else
+        pointGradientWalk(v, link, QLerp{ q0, q1, cc_time }, ref0, ref1, tv, emit);
+    }
+  }
+  // writeRow
+  const bool b0 = !f0, b1 = !(single || f1);
+  const int nb = (b0 ? 1 : 0) + (b1 ? 1 : 0);
+  long long nnz = term_row_base[k] + (i - w.term_ptr[k]) * nb * n;
+  w.row_ptr[i] = nnz;
+  w.row_block[2 * i] = b0 ? term * n : -1;
+  w.row_block[2 * i + 1] = b1 ? (term + 1) * n : -1;
+  w.row_pair[i] = pair;
+  const PairD pr = v.pairs[pair];
+  double constant = distance;
+  if (b0)
+  {
+#pragma unroll
+    for (int jj = 0; jj < NR; ++jj)
+      if (jj < n)
+      {
+        const double s = sum.s0[jj];
+        if (legacy)
+          constant = fma(-s, q0[jj], constant);
+        val[nnz + jj] = legacy ? s : -1.0 * s;
+        col_idx[nnz + jj] = term * n + jj;
+      }
+    nnz += n;
+  }
+  if (b1)
+  {
+#pragma unroll
+    for (int jj = 0; jj < NR; ++jj)
+      if (jj < n)
+      {
+        const double s = sum.s1[jj];
+        if (legacy)
+          constant = fma(-s, q0[n + jj], constant);
+        val[nnz + jj] = legacy ? s : -1.0 * s;
+        col_idx[nnz + jj] = (term + 1) * n + jj;
+      }
+  }
+  row_value[i] = legacy ? constant : (pr.margin - distance);
+  row_coeff[i] = pr.coeff;
+  row_margin[i] = pr.margin;
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -1461,12 +1607,12 @@ cudaError_t launchGradRows(const SceneView& v, const Work& w, long long* term_ro
   if (w.gather_in_rows)
   {
     if (v.n_dof <= 8)
-      k_grad_rows<8, true><<<grid, TPB, 0, st>>>(v, w, term_row_base, col_idx, val, row_value, row_coeff, row_margin);
+      k_grad_rows_regs<8, true><<<grid, TPB, 0, st>>>(v, w, term_row_base, col_idx, val, row_value, row_coeff, row_margin);
     else
       k_grad_rows<64, true><<<grid, TPB, 0, st>>>(v, w, term_row_base, col_idx, val, row_value, row_coeff, row_margin);
   }
   else if (v.n_dof <= 8)
-    k_grad_rows<8, false><<<grid, TPB, 0, st>>>(v, w, term_row_base, col_idx, val, row_value, row_coeff, row_margin);
+    k_grad_rows_regs<8, false><<<grid, TPB, 0, st>>>(v, w, term_row_base, col_idx, val, row_value, row_coeff, row_margin);
   else
     k_grad_rows<64, false><<<grid, TPB, 0, st>>>(v, w, term_row_base, col_idx, val, row_value, row_coeff, row_margin);
   return cudaGetLastError();
