@@ -508,7 +508,12 @@ int runEval(tc_scene* scene, const tc_eval_desc* desc, const double* q, int32_t 
     const long long n_deep = r->h_counters->n_deep, n_curved = r->h_counters->n_curved;
     static const char* trace_deep = getenv("TC_TRACE_DEEP");  // tuning aid: how many items outgrew the fast polytope
     if (trace_deep)
-      fprintf(stderr, "[tc] n_epa=%lld n_deep=%lld n_curved=%lld\n", r->h_counters->n_epa, n_deep, n_curved);
+      fprintf(stderr, "[tc] n_epa=%lld n_deep=%lld n_curved=%lld epa_iters=%lld gjk_iters=%lld n_items=%lld group_max_epa=%lld group_max_gjk=%lld\n",
+              r->h_counters->n_epa, n_deep, n_curved, r->h_counters->epa_iters, r->h_counters->gjk_iters,
+              r->h_counters->n_items, r->h_counters->dbg[0], r->h_counters->dbg[1]);
+    if (trace_deep)
+      fprintf(stderr, "[tc] epa items with >= 11/15/19/23/27/31 trips: %lld %lld %lld %lld %lld %lld\n", r->h_counters->dbg[2],
+              r->h_counters->dbg[3], r->h_counters->dbg[4], r->h_counters->dbg[5], r->h_counters->dbg[6], r->h_counters->dbg[7]);
     if (n_curved > 0)
     {
       const int nt = deepThreads(n_curved);

@@ -57,6 +57,7 @@ struct Counters
   long long support_compared;          // hull vertices actually compared by support queries (support_verts: all of the hull)
   long long n_curved;                  // items of curved-core shape pairs routed to the contraction-free kernel
   long long n_raw0;                    // raw hits present when the overflow re-runs start (they are finalised meanwhile)
+  long long dbg[8];                    // TC_NARROW_HIST builds: 32 x (longest EPA / GJK run of every 32-item group), summed
 };
 
 template <class T>

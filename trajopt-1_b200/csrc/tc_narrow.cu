@@ -325,6 +325,15 @@ __global__ void __launch_bounds__(TC_GJK_NT, MINB * 128 / TC_GJK_NT) k_gjk(Scene
         }
 #endif
       }
+#ifdef TC_NARROW_HIST
+      {
+        int mx = live ? d.gjk_iters : 0;
+        for (int o = 16; o; o >>= 1)
+          mx = max(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+        if ((threadIdx.x & 31) == 0)
+          atomicAdd(reinterpret_cast<unsigned long long*>(&w.counters->dbg[1]), static_cast<unsigned long long>(32 * mx));
+      }
+#endif
       storeHit<R>(w, d, u, sp, d.status == ND_CONTACT);
       const bool need = d.status == ND_NEED_EPA;
       const unsigned m = __ballot_sync(0xffffffffu, need);
@@ -450,10 +459,10 @@ __global__ void __launch_bounds__(128, MINB) k_epa_wp(SceneView v, Work w)
         S.a[i] = Vec3<R>(static_cast<R>(rec.s[6 * i + 3]), static_cast<R>(rec.s[6 * i + 4]), static_cast<R>(rec.s[6 * i + 5]));
         S.lam[i] = 0;
       }
+      d.converged = (nflag & 8) == 0;
       Placed<R> PA, PB;
       placeItem<R>(v, w, rec.state, spd, pr, *A, *B, sceneVerts<R>(v) + A->vert_off, sceneVerts<R>(v) + B->vert_off, PA,
                    PB, A->lut_bytes ? v.lut + A->lut_off : nullptr, B->lut_bytes ? v.lut + B->lut_off : nullptr);
-      d.converged = (nflag & 8) == 0;
       if (pr.b >= v.n_active)
       {
         // static partner: a copy of the expansion in which the partner is known not to be swept (see k_gjk)
@@ -486,6 +495,22 @@ __global__ void __launch_bounds__(128, MINB) k_epa_wp(SceneView v, Work w)
         st_unconv += d.converged ? 0 : 1;
       }
     }
+#ifdef TC_NARROW_HIST
+    {
+      int mx = (slot < valid_end) ? d.epa_iters : 0;
+      for (int o = 16; o; o >>= 1)
+        mx = max(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+      if (lane == 0)
+        atomicAdd(reinterpret_cast<unsigned long long*>(&w.counters->dbg[0]), static_cast<unsigned long long>(32 * mx));
+      const int it = (slot < valid_end) ? d.epa_iters : 0;
+      for (int k = 0; k < 6; ++k)
+      {
+        const unsigned m = __ballot_sync(0xffffffffu, it >= 11 + 4 * k);
+        if (lane == 0 && m)
+          atomicAdd(reinterpret_cast<unsigned long long*>(&w.counters->dbg[2 + k]), static_cast<unsigned long long>(__popc(m)));
+      }
+    }
+#endif
     storeHit<R>(w, d, u, sp, d.status == ND_CONTACT);
     const bool deep = d.status == ND_EPA_OVERFLOW;
     const unsigned m = __ballot_sync(0xffffffffu, deep);
