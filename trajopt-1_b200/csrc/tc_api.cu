@@ -1579,7 +1579,27 @@ int tc_pipeline_eval_rows(tc_pipeline* p, const tc_eval_desc* desc, const double
   const int n_dof = p->scene->host.n_dof;
   tc_eval_desc d = *desc;
   d.want = TC_WANT_COST | TC_WANT_CONTACTS | TC_WANT_ROWS;
-  const std::vector<SubBatch> subs = cutBatch(B, chunk);
+  std::vector<SubBatch> subs = cutBatch(B, chunk);
+  if (const char* sched = getenv("TC_PIPELINE_SCHEDULE"))
+  {
+    // tuning aid: explicit sub-batch sizes "2304,1152,512,128" (must add up to B, else ignored)
+    std::vector<SubBatch> alt;
+    int first = 0;
+    for (const char* c = sched; *c;)
+    {
+      const int n = atoi(c);
+      if (n <= 0)
+        break;
+      alt.push_back({ first, n });
+      first += n;
+      while (*c && *c != ',')
+        ++c;
+      if (*c == ',')
+        ++c;
+    }
+    if (first == B)
+      subs = alt;
+  }
   const int K = p->n_slots;
   struct InFlight
   {
