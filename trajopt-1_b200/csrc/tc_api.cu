@@ -1043,6 +1043,25 @@ int tc_result_pass_info(const tc_result* res, int32_t* speculative, int32_t* rep
   return TC_OK;
 }
 
+#ifdef TC_NARROW_HIST
+// tuning builds only: headers (unit, state, nflag, gjk_iters | epa_iters << 16) of the hand-off records of the last
+// pass, the buckets' offsets and the number of valid records per bucket
+int tc_debug_epa_records(tc_result* r, int32_t* hdr, size_t cap, int32_t* sp_offset, int32_t* sp_valid, int32_t* n_sp)
+{
+  TC_TRY(ensureDevice(r->device));
+  cudaDeviceSynchronize();
+  const size_t n = static_cast<size_t>(r->w.n_items_padded);
+  if (n > cap)
+    return fail(TC_ERR_OVERFLOW, "cap");
+  TC_CUDA(cudaMemcpy2D(hdr, 16, r->epa_rec.p, sizeof(EpaRec), 16, n, cudaMemcpyDeviceToHost));
+  const int ns = r->scene->host.spairs.size();
+  TC_CUDA(cudaMemcpy(sp_offset, r->sp_offset.p, sizeof(int32_t) * ns, cudaMemcpyDeviceToHost));
+  TC_CUDA(cudaMemcpy(sp_valid, r->epa_cursor.p, sizeof(int32_t) * ns, cudaMemcpyDeviceToHost));
+  *n_sp = ns;
+  return TC_OK;
+}
+#endif
+
 int tc_contact_test(tc_scene* scene, const double* link_pose0, const double* link_pose1, int32_t n_states,
                     int32_t contact_test_type, int32_t precision, tc_result* out, void* cuda_stream)
 {

@@ -351,7 +351,11 @@ __global__ void __launch_bounds__(TC_GJK_NT, MINB * 128 / TC_GJK_NT) k_gjk(Scene
           rec.unit = u;
           rec.state = w.item_state[slot];
           rec.nflag = S.n | (d.converged ? 0 : 8);
+#ifdef TC_NARROW_HIST
+          rec.pad = d.gjk_iters;
+#else
           rec.pad = 0;
+#endif
 #pragma unroll
           for (int i = 0; i < 4; ++i)
           {
@@ -503,6 +507,8 @@ __global__ void __launch_bounds__(128, MINB) k_epa_wp(SceneView v, Work w)
       if (lane == 0)
         atomicAdd(reinterpret_cast<unsigned long long*>(&w.counters->dbg[0]), static_cast<unsigned long long>(32 * mx));
       const int it = (slot < valid_end) ? d.epa_iters : 0;
+      if (slot < valid_end)
+        w.epa_rec[slot].pad |= it << 16;
       for (int k = 0; k < 6; ++k)
       {
         const unsigned m = __ballot_sync(0xffffffffu, it >= 11 + 4 * k);
