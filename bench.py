@@ -352,7 +352,7 @@ def run_ours(args, scene, rank, world, local_rank):
     q_np = q_pin.numpy()
 
     def step_e2e():
-        n_rows, nnz_ = pipe.eval_rows(q_np, capi.EVAL_LVS_CONTINUOUS, LVS, fixed, args.e2e_chunk)
+        n_rows, nnz_ = pipe.eval_rows(q_np, capi.EVAL_LVS_CONTINUOUS, LVS, fixed, args.e2e_chunk, packed=not args.e2e_dense)
         costs = pipe.out["cost"]
         i = int(np.argmin(costs))
         if comm is None:
@@ -365,7 +365,8 @@ def run_ours(args, scene, rank, world, local_rank):
     for _ in range(3):
         best_e2e, nc, nnz = step_e2e()
     assert best_e2e[1] == best[1] or best_e2e[0] == best[0], (best_e2e, best)  # same winner as the resident path
-    assert nc == counts["n_contacts"] and nnz == counts["nnz"]
+    # packed rows leave out the joints that move neither link of a row (exact zeros, a third of the values)
+    assert nc == counts["n_contacts"] and (nnz == counts["nnz"] if args.e2e_dense else 0 < nnz < counts["nnz"])
     barrier()
     t0 = time.perf_counter()
     for _ in range(args.steps):
@@ -433,9 +434,12 @@ def run_ours(args, scene, rank, world, local_rank):
                              (counts["n_states"] * (14 * 96 + 14 * 48) / 1e9)},
             "e2e": {"value": dense_total / (e2e_ms * 1e-3), "unit": UNIT, "ms_per_step": e2e_ms,
                     "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
-                    "how": f"tc_pipeline_eval_rows: sub-batches of {args.e2e_chunk} seeds (last one tapered) on a ring of "
-                           f"{args.e2e_workers} streams inside the library, one host thread, compact rows (values, row value, "
-                           "link pair, term offsets) into pinned host arrays, wall clock around the whole batch"},
+                    "rows_form": "dense blocks" if args.e2e_dense else "packed (structural non-zeros only, lossless)",
+                    "row_values_per_step": int(nnz), "row_values_dense": int(counts["nnz"]),
+                    "how": f"tc_pipeline_eval_rows{'' if args.e2e_dense else '_packed'}: sub-batches of {args.e2e_chunk} seeds "
+                           f"(last one tapered) on a ring of {args.e2e_workers} streams inside the library, one host thread, "
+                           "compact rows (values, row value, link pair, term offsets) into pinned host arrays, wall clock "
+                           "around the whole batch"},
             "per_rank": per_rank,
             "gpu_launches": launches, "library_calls_per_step": cu.launches(res)[1],
             "roofline": {"bound": "fp64", "kernel": "narrow phase: k_gjk<double> + k_epa_wp<double> (2 launches)", "achieved": flops / (nms * 1e-3) / 1e12,
@@ -493,6 +497,8 @@ def main():
                     "other configs (the default run reports them all)")
     ap.add_argument("--e2e-chunk", type=int, default=1024, help="seeds per sub-batch of the host-buffer (e2e) leg")
     ap.add_argument("--e2e-workers", type=int, default=4, help="streams (ring slots) of the e2e leg")
+    ap.add_argument("--e2e-dense", action="store_true", help="e2e leg downloads dense row blocks (n_dof values per block) "
+                                                             "instead of the packed form")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))

@@ -388,6 +388,19 @@ void tc_pipeline_destroy(tc_pipeline* pipe);
 int tc_pipeline_eval_rows(tc_pipeline* pipe, const tc_eval_desc* desc, const double* q, int32_t B, int32_t T, int32_t chunk,
                           int64_t* term_ptr, double* val, size_t val_cap, double* row_value, int32_t* row_pair,
                           size_t row_cap, double* cost_per_traj, int64_t* n_rows, int64_t* nnz);
+/* The same pass with the rows in PACKED form: a block of a row holds only the joints that move one of the row's two
+ * links — ascending joint index, the set bits of tc_scene_pair_dof_mask(row_pair[i]) — instead of all n_dof.  The
+ * entries left out are the exact zeros the reference writes for joints outside both chains (getJacobian fills every
+ * column of a block, discrete_collision_constraint.cpp:266-277; continuous_collision_constraint.cpp:380-411), a third
+ * of the values on the arm_around_table batch, so nothing is lost; a QP builder that drops explicit zeros
+ * (trajopt_sco/src/solver_utils.cpp:111-144 prunes them) reads this form directly.  Row i starts where row i - 1
+ * ends: width(i) = popcount(mask(row_pair[i])) * nb(term of i); nnz counts the packed values. */
+int tc_pipeline_eval_rows_packed(tc_pipeline* pipe, const tc_eval_desc* desc, const double* q, int32_t B, int32_t T,
+                                 int32_t chunk, int64_t* term_ptr, double* val, size_t val_cap, double* row_value,
+                                 int32_t* row_pair, size_t row_cap, double* cost_per_traj, int64_t* n_rows, int64_t* nnz);
+/* bit j set: joint j is on the kinematic chain of one of the pair's two links (a link outside the planning group
+ * contributes nothing).  Scenes of up to 64 joints. */
+int tc_scene_pair_dof_mask(const tc_scene* scene, int32_t pair, uint64_t* mask);
 
 /* ---- allocation-free entry point.  It has NO counterpart in the reference: it was added
  * for callers that cannot call cudaMalloc (CUDA graph capture, tight serving loops, harnesses that

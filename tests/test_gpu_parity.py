@@ -343,6 +343,49 @@ def test_pipelined_host_pass_equals_one_pass(cuda, n_slots, chunk):
         small.eval_rows(q, capi.EVAL_LVS_CONTINUOUS, 0.02, fixed, chunk)
 
 
+@pytest.mark.parametrize("scene_name,evaluator,stack", [("arm_around_table", capi.EVAL_LVS_CONTINUOUS, capi.STACK_IFOPT),
+                                                        ("arm_around_table", capi.EVAL_LVS_CONTINUOUS, capi.STACK_LEGACY),
+                                                        ("arm_around_table", capi.EVAL_DISCRETE, capi.STACK_IFOPT),
+                                                        ("dual_arm", capi.EVAL_LVS_CONTINUOUS, capi.STACK_IFOPT)])
+def test_packed_rows_unpack_to_the_dense_rows(cuda, scene_name, evaluator, stack):
+    """tc_pipeline_eval_rows_packed leaves out exactly the joints that move neither link of a row: unpacked with
+    tc_scene_pair_dof_mask the values are those of ONE dense pass, every one of them, and what was left out is zero"""
+    ms = helpers.pkg.multistart
+    if scene_name == "dual_arm":
+        from tests import synthetic
+        s = synthetic.dual_arm_scene()  # 16 joints: the general row kernel
+        B, T = 6, 8
+        rng = np.random.default_rng(5)
+        q = s["traj"][::12][:T][None] + rng.normal(0, 0.05, (B, T, int(s["n_dof"])))
+    else:
+        s = helpers.load_scene(scene_name)
+        B, T = 40, 6
+        q = ms.make_batch(s, 300, B, t_steps=T)
+    sg = cuda.scene(s, 0.025, 20.0, 0.01)
+    fixed = np.zeros(T, np.uint8)
+    fixed[0] = 1
+    ref = cuda.eval(sg, q, evaluator, stack=stack, lvs=0.02, fixed=fixed, want=capi.WANT_LINEARISE)
+    rows, co = ref.rows(), ref.contacts()
+    assert len(co) > 0
+    single = evaluator == capi.EVAL_DISCRETE
+    tpt = (T - 1) if single else (T - 1)  # one fixed waypoint: T - 1 states, or T - 1 segments (the first with one block)
+    blocks_traj = [1] * tpt if single else [1] + [2] * (tpt - 1)
+    pipe = capi.Pipeline(cuda, sg, 3)
+    pipe.reserve(B, tpt, len(co) + 10, len(rows["val"]) + 10)
+    masks = pipe.pair_masks(len(sg.pairs()[0]))
+    for rep in range(3):
+        n_rows, nnz = pipe.eval_rows(q, evaluator, 0.02, fixed, 16, stack=stack, packed=True)
+        o = pipe.out
+        assert n_rows == len(co) and 0 < nnz < len(rows["val"])
+        assert np.array_equal(o["term_ptr"], ref.term_ptr()) and np.array_equal(o["pair"][:n_rows], co["pair"])
+        row_ptr, dense = capi.unpack_rows(o["term_ptr"], o["val"][:nnz], o["pair"][:n_rows], masks, sg.n_dof,
+                                          np.tile(blocks_traj, B))
+        assert np.array_equal(row_ptr, rows["row_ptr"])
+        assert np.array_equal(dense, rows["val"])  # -0.0 == 0.0: the entries left out are zeros of either sign
+        assert np.array_equal(o["value"][:n_rows], rows["value"]) and np.array_equal(o["cost"], ref.cost()[1])
+    pipe.close()
+
+
 @pytest.mark.parametrize("evaluator", [capi.EVAL_DISCRETE, capi.EVAL_LVS_CONTINUOUS])
 def test_dynamic_environment_moving_links_outside_the_group(cuda, oracle, evaluator):
     """collision_terms.cpp:399-411,828-836: with links that move outside the planning group the manager is active on

@@ -344,6 +344,26 @@ def expand_compact_rows(term_ptr, val, n_dof, blocks_per_term):
     return row_ptr
 
 
+def unpack_rows(term_ptr, val, pair, pair_masks, n_dof, blocks_per_term):
+    """packed rows (tc_pipeline_eval_rows_packed) -> (row_ptr, val) of the dense form tc_pipeline_eval_rows returns:
+    a block of row i holds the joints set in pair_masks[pair[i]] (tc_scene_pair_dof_mask), ascending"""
+    rows_per_term = np.diff(term_ptr)
+    nb = np.repeat(np.asarray(blocks_per_term, dtype=np.int64), rows_per_term)
+    bits = ((np.asarray(pair_masks, dtype=np.uint64)[pair][:, None] >> np.arange(n_dof, dtype=np.uint64)[None, :]) & 1).astype(bool)
+    width = bits.sum(axis=1) * nb
+    assert width.sum() == len(val)
+    row_ptr = np.zeros(len(nb) + 1, np.int64)
+    np.cumsum(nb * n_dof, out=row_ptr[1:])
+    dense = np.zeros(row_ptr[-1], np.float64)
+    # positions of the kept entries of every row, block after block
+    keep = np.concatenate([bits, bits], axis=1)  # [rows, 2 * n_dof]; a one-block row uses the first half only
+    keep[nb == 1, n_dof:] = False
+    keep[nb == 0, :] = False
+    cols = np.nonzero(keep)
+    dense[row_ptr[cols[0]] + cols[1]] = val
+    return row_ptr, dense
+
+
 class Pipeline:
     """tc_pipeline: a batch cut into sub-batches on a ring of streams inside the library, rows downloaded in compact
     form while the next sub-batch computes (one host thread).  Output arrays are allocated by the caller-supplied
@@ -372,14 +392,24 @@ class Pipeline:
         self.out = dict(term_ptr=alloc(B * terms_per_traj + 1, np.int64), val=alloc(val_cap, np.float64),
                         value=alloc(row_cap, np.float64), pair=alloc(row_cap, np.int32), cost=alloc(B, np.float64))
 
-    def eval_rows(self, q, evaluator, lvs, fixed, chunk, stack=STACK_IFOPT, precision=PRECISION_F64):
-        """q: numpy [B, T, n_dof] (host; pinned for asynchronous reads) -> (n_rows, nnz); arrays in self.out"""
+    def pair_masks(self, n_pairs):
+        """tc_scene_pair_dof_mask of every link pair"""
+        out = np.zeros(n_pairs, np.uint64)
+        m = C.c_uint64()
+        for p in range(n_pairs):
+            self.lib.check(self.lib.dll.tc_scene_pair_dof_mask(self.scene.handle, C.c_int32(p), C.byref(m)))
+            out[p] = m.value
+        return out
+
+    def eval_rows(self, q, evaluator, lvs, fixed, chunk, stack=STACK_IFOPT, precision=PRECISION_F64, packed=False):
+        """q: numpy [B, T, n_dof] (host; pinned for asynchronous reads) -> (n_rows, nnz); arrays in self.out.
+        packed: values of the joints that move a row's links only (unpack_rows restores the dense blocks)"""
         B, T, n = q.shape
         d, keep = make_eval_desc(evaluator, stack, lvs, fixed, WANT_LINEARISE, precision)
         o = self.out
         n_rows, nnz = C.c_int64(), C.c_int64()
-        _pl64 = C.POINTER(C.c_int64)
-        self.lib.check(self.lib.dll.tc_pipeline_eval_rows(
+        fn = self.lib.dll.tc_pipeline_eval_rows_packed if packed else self.lib.dll.tc_pipeline_eval_rows
+        self.lib.check(fn(
             self.handle, C.byref(d), C.c_void_p(q.ctypes.data), C.c_int32(B), C.c_int32(T), C.c_int32(chunk),
             C.c_void_p(o["term_ptr"].ctypes.data), C.c_void_p(o["val"].ctypes.data), C.c_size_t(len(o["val"])),
             C.c_void_p(o["value"].ctypes.data), C.c_void_p(o["pair"].ctypes.data), C.c_size_t(len(o["value"])),

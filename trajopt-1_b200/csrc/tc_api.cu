@@ -103,7 +103,9 @@ struct tc_result
   DevBuf<double> csc_val, csc_upper, csc_cost;
   bool have_csc{ false };
   DevBuf<tc_gradient> grec;
-  DevBuf<unsigned char> sort_temp, deep_scratch, curved_scratch;
+  DevBuf<unsigned char> sort_temp, deep_scratch, curved_scratch, scan_temp;
+  DevBuf<long long> row_width;
+  bool rows_packed{ false };  // set by tc_pipeline: rows in packed form (structural non-zeros only)
   cudaStream_t side{ nullptr };  // speculative passes: the cold one-thread-per-item kernels run beside the main stream
   cudaEvent_t ev_side[4]{};
   DevBuf<double> cost_term, cost_traj;
@@ -727,7 +729,21 @@ int enqueueRows(tc_result* r, bool fused)
   w.row_ptr = r->row_ptr.p;
   w.row_block = r->row_block.p;
   w.row_pair = r->row_pair.p;
-  TC_CUDA(launchRowBase(r->scene->dview, w, r->term_row_base.p, r->stream));
+  w.rows_packed = (r->rows_packed && fused) ? 1 : 0;
+  if (w.rows_packed)
+  {
+    if (hs.n_dof > 64)
+      return fail(TC_ERR_UNSUPPORTED, "packed rows: more than 64 joints");
+    TC_RESERVE(r->row_width, nc + 1);
+    w.row_width = r->row_width.p;
+    size_t temp_bytes = 0;
+    TC_CUDA(launchRowWidths(r->scene->dview, w, nullptr, temp_bytes, r->stream));
+    TC_RESERVE(r->scan_temp, temp_bytes);
+    TC_CUDA(launchRowWidths(r->scene->dview, w, r->scan_temp.p, temp_bytes, r->stream));
+    r->lib_launches += 1;  // cub::DeviceScan
+  }
+  else
+    TC_CUDA(launchRowBase(r->scene->dview, w, r->term_row_base.p, r->stream));
   if (fused)
     TC_CUDA(launchGradRows(r->scene->dview, w, r->term_row_base.p, r->col_idx.p, r->row_val.p, r->row_value.p,
                            r->row_coeff.p, r->row_margin.p, r->stream));
@@ -870,6 +886,7 @@ int tc_scene_create(const tc_scene_desc* desc, tc_scene** out)
   UP(path_frames, h.path_frames);
   UP(link_frame, h.link_frame);
   UP(frame_link, h.frame_link);
+  UP(link_dof_mask, h.link_dof_mask);
   UP(link_pose, h.link_pose);
   UP(shapes, h.shapes);
   UP(verts, h.verts);
@@ -1008,6 +1025,7 @@ void tc_result_destroy(tc_result* r)
   r->ghas.release(), r->raw.release(), r->keys.release(), r->keys_alt.release(), r->contacts_tmp.release();
   r->contacts.release(), r->xf.release(), r->grad.release(), r->term_ptr.release();
   r->row_ptr.release(), r->term_row_base.release(), r->grec.release(), r->sort_temp.release();
+  r->scan_temp.release(), r->row_width.release();
   r->deep_scratch.release(), r->cost_term.release(), r->cost_traj.release(), r->col_idx.release(), r->row_block.release(), r->row_pair.release();
   r->csc_bt_base.release(), r->csc_col_ptr.release(), r->csc_row_idx.release(), r->csc_val.release();
   r->csc_upper.release(), r->csc_cost.release();
@@ -1584,9 +1602,11 @@ void tc_pipeline_destroy(tc_pipeline* p)
   (void)cudaGetLastError();
 }
 
-int tc_pipeline_eval_rows(tc_pipeline* p, const tc_eval_desc* desc, const double* q, int32_t B, int32_t T, int32_t chunk,
-                          int64_t* term_ptr, double* val, size_t val_cap, double* row_value, int32_t* row_pair,
-                          size_t row_cap, double* cost_per_traj, int64_t* n_rows_out, int64_t* nnz_out)
+}  // extern "C"
+
+static int pipelineEvalRows(tc_pipeline* p, const tc_eval_desc* desc, const double* q, int32_t B, int32_t T, int32_t chunk,
+                            int64_t* term_ptr, double* val, size_t val_cap, double* row_value, int32_t* row_pair,
+                            size_t row_cap, double* cost_per_traj, int64_t* n_rows_out, int64_t* nnz_out, bool packed)
 {
   if (!p || !desc || !q || !term_ptr || !val || !row_value || !row_pair || !cost_per_traj || !n_rows_out || !nnz_out)
     return fail(TC_ERR_INVALID, "tc_pipeline_eval_rows: null argument");
@@ -1688,6 +1708,7 @@ int tc_pipeline_eval_rows(tc_pipeline* p, const tc_eval_desc* desc, const double
     if (!f.r)
       return status;
     f.sb = subs[j];
+    f.r->rows_packed = packed;
     TC_TRY(runEval(p->scene, &d, q + static_cast<size_t>(subs[j].first) * T * n_dof, subs[j].count, T, f.r,
                    p->streams[static_cast<size_t>(s)]));
     tpt = f.r->ep.terms_per_traj;
@@ -1713,6 +1734,38 @@ int tc_pipeline_eval_rows(tc_pipeline* p, const tc_eval_desc* desc, const double
   term_ptr[static_cast<size_t>(B) * static_cast<size_t>(std::max(tpt, 0))] = rows_done;
   *n_rows_out = rows_done;
   *nnz_out = nnz_done;
+  return TC_OK;
+}
+
+extern "C" {
+
+int tc_pipeline_eval_rows(tc_pipeline* p, const tc_eval_desc* desc, const double* q, int32_t B, int32_t T, int32_t chunk,
+                          int64_t* term_ptr, double* val, size_t val_cap, double* row_value, int32_t* row_pair,
+                          size_t row_cap, double* cost_per_traj, int64_t* n_rows_out, int64_t* nnz_out)
+{
+  return pipelineEvalRows(p, desc, q, B, T, chunk, term_ptr, val, val_cap, row_value, row_pair, row_cap, cost_per_traj,
+                          n_rows_out, nnz_out, false);
+}
+
+int tc_pipeline_eval_rows_packed(tc_pipeline* p, const tc_eval_desc* desc, const double* q, int32_t B, int32_t T,
+                                 int32_t chunk, int64_t* term_ptr, double* val, size_t val_cap, double* row_value,
+                                 int32_t* row_pair, size_t row_cap, double* cost_per_traj, int64_t* n_rows_out,
+                                 int64_t* nnz_out)
+{
+  return pipelineEvalRows(p, desc, q, B, T, chunk, term_ptr, val, val_cap, row_value, row_pair, row_cap, cost_per_traj,
+                          n_rows_out, nnz_out, true);
+}
+
+int tc_scene_pair_dof_mask(const tc_scene* scene, int32_t pair, uint64_t* mask)
+{
+  if (!scene || !mask)
+    return fail(TC_ERR_INVALID, "tc_scene_pair_dof_mask: null argument");
+  const HostScene& hs = scene->host;
+  if (pair < 0 || static_cast<size_t>(pair) >= hs.pairs.size())
+    return fail(TC_ERR_INVALID, "tc_scene_pair_dof_mask: pair out of range");
+  const PairD& pr = hs.pairs[static_cast<size_t>(pair)];
+  *mask = (pr.a < hs.n_active ? hs.link_dof_mask[static_cast<size_t>(pr.a)] : 0ull) |
+          (pr.b < hs.n_active ? hs.link_dof_mask[static_cast<size_t>(pr.b)] : 0ull);
   return TC_OK;
 }
 

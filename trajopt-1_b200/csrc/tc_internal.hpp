@@ -144,6 +144,9 @@ struct Work
   long long raw_cap, deep_cap;
   int speculative;
   int gather_in_rows;  // the fused gradient-row kernel performs the gather of the sorted contacts itself
+  int rows_packed;     // rows hold only their structural non-zeros (the joints that move either link); row_ptr is
+                       // then an exclusive scan of the row widths made before the row kernel runs
+  long long* row_width;
 };
 
 // actual counts of the running pass, as the kernels see them
@@ -183,6 +186,9 @@ cudaError_t launchGather(const SceneView& v, const Work& w, cudaStream_t st);
 cudaError_t launchGradients(const SceneView& v, const Work& w, cudaStream_t st);
 cudaError_t launchTransforms(const SceneView& v, const Work& w, double* xf, cudaStream_t st);
 cudaError_t launchRowBase(const SceneView& v, const Work& w, long long* term_row_base, cudaStream_t st);
+// packed rows: widths from the sorted keys, exclusive scan into w.row_ptr (n_contacts + 1 entries); temp == nullptr
+// only returns the scratch size
+cudaError_t launchRowWidths(const SceneView& v, const Work& w, void* temp, size_t& temp_bytes, cudaStream_t st);
 cudaError_t launchRows(const SceneView& v, const Work& w, long long* term_row_base, int32_t* col_idx, double* val,
                        double* row_value, double* row_coeff, double* row_margin, cudaStream_t st);
 cudaError_t launchGradRows(const SceneView& v, const Work& w, long long* term_row_base, int32_t* col_idx, double* val,

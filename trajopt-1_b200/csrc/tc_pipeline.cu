@@ -4,6 +4,7 @@
 //   K4 gradient rows / constraint rows / GradientResultsSets / cost.
 // Reference call sites are cited at each kernel.
 #include <cub/device/device_radix_sort.cuh>
+#include <cub/device/device_scan.cuh>
 
 #include "tc_internal.hpp"
 
@@ -669,6 +670,34 @@ __global__ void __launch_bounds__(1024) k_row_base(SceneView v, Work w, long lon
   }
 }
 
+// Packed rows (the compact transport form of tc_pipeline_eval_rows_packed).  A row's Jacobian block has a non-zero in
+// column j only if joint j moves one of the contact's two links: the reference writes all n_dof entries of a block,
+// zeros included (discrete_collision_constraint.cpp:266-277), a third of them on C4.  In packed form a block holds only
+// the joints of dofMask(link a) | dofMask(link b), ascending; the host re-expands with tc_scene_pair_dof_mask.
+__device__ __forceinline__ unsigned long long pairDofMask(const SceneView& v, int a, int b)
+{
+  return (a < v.n_active ? v.link_dof_mask[a] : 0ull) | (b < v.n_active ? v.link_dof_mask[b] : 0ull);
+}
+
+// widths of the packed rows, straight from the sorted keys (term | link pair | ...): no contact record is touched
+__global__ void __launch_bounds__(256) k_row_width(SceneView v, Work w, const unsigned long long* keys)
+{
+  const long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (i > w.n_contacts)
+    return;
+  long long width = 0;
+  if (!passOverflowed(w) && i < w.counters->n_valid)
+  {
+    const unsigned long long key = keys[i];
+    const int ti = static_cast<int>(key >> 36) % w.ep.terms_per_traj;
+    const PairD pr = v.pairs[(key >> 22) & 0x3fffull];
+    const bool single = w.ep.evaluator == TC_EVAL_DISCRETE;
+    const int nb = (w.term_fixed[2 * ti] ? 0 : 1) + ((single || w.term_fixed[2 * ti + 1]) ? 0 : 1);
+    width = static_cast<long long>(__popcll(pairDofMask(v, pr.a, pr.b))) * nb;
+  }
+  w.row_width[i] = width;
+}
+
 // DiscreteCollisionConstraintD / ContinuousCollisionConstraintD getValues + getJacobian
 // (discrete_collision_constraint.cpp:214-283, continuous_collision_constraint.cpp:311-417) and the legacy
 // CollisionsToDistanceExpressions / CalcDistExpressions* (collision_terms.cpp:341-386,463-554)
@@ -683,8 +712,10 @@ __device__ __forceinline__ void writeRow(const SceneView& v, const Work& w, long
   const bool single = w.ep.evaluator == TC_EVAL_DISCRETE;
   const int n = v.n_dof;
   const int nb = (f0 ? 0 : 1) + ((single || f1) ? 0 : 1);
-  long long nnz = term_row_base[k] + (i - w.term_ptr[k]) * nb * n;
-  w.row_ptr[i] = nnz;
+  const unsigned long long keep = w.rows_packed ? pairDofMask(v, c.link_ids[0], c.link_ids[1]) : ~0ull;
+  long long nnz = w.rows_packed ? w.row_ptr[i] : term_row_base[k] + (i - w.term_ptr[k]) * nb * n;
+  if (!w.rows_packed)
+    w.row_ptr[i] = nnz;
   w.row_block[2 * i] = f0 ? -1 : c.term * n;
   w.row_block[2 * i + 1] = (single || f1) ? -1 : (c.term + 1) * n;
   w.row_pair[i] = c.pair;
@@ -706,12 +737,10 @@ __device__ __forceinline__ void writeRow(const SceneView& v, const Work& w, long
         if (has & (1 << (2 * l + blk)))
           s = fma(blk ? rec.scale1[l] : rec.scale0[l], g[(2 * l + blk) * n + j], s);
       if (w.ep.stack == TC_STACK_LEGACY)
-      {
         constant = fma(-s, qb[j], constant);
-        val[nnz] = s;
-      }
-      else
-        val[nnz] = -1.0 * s;
+      if (j < 64 && !((keep >> j) & 1ull))
+        continue;  // packed rows: a joint that moves neither link (s is an exact zero)
+      val[nnz] = (w.ep.stack == TC_STACK_LEGACY) ? s : -1.0 * s;
       col_idx[nnz] = (c.term + blk) * n + j;
       ++nnz;
     }
@@ -757,7 +786,10 @@ __global__ void __launch_bounds__(TPB, TC_GRADROWS_MINB) k_grad_rows(SceneView v
     return;
   if (i == w.counters->n_valid)
   {
-    w.row_ptr[i] = term_row_base[w.ep.n_terms];
+    if (w.rows_packed)
+      w.counters->nnz = w.row_ptr[i];
+    else
+      w.row_ptr[i] = term_row_base[w.ep.n_terms];
     return;
   }
   const tc_contact c = GATHER ? w.contacts_tmp[w.idx_alt[i]] : w.contacts[i];
@@ -815,7 +847,10 @@ __global__ void __launch_bounds__(TPB, TC_GRADROWS_MINB) k_grad_rows_regs(SceneV
     return;
   if (i == w.counters->n_valid)
   {
-    w.row_ptr[i] = term_row_base[w.ep.n_terms];
+    if (w.rows_packed)
+      w.counters->nnz = w.row_ptr[i];
+    else
+      w.row_ptr[i] = term_row_base[w.ep.n_terms];
     return;
   }
   const tc_contact* cp = GATHER ? w.contacts_tmp + w.idx_alt[i] : w.contacts + i;
@@ -890,8 +925,11 @@ __global__ void __launch_bounds__(TPB, TC_GRADROWS_MINB) k_grad_rows_regs(SceneV
   // writeRow
   const bool b0 = !f0, b1 = !(single || f1);
   const int nb = (b0 ? 1 : 0) + (b1 ? 1 : 0);
-  long long nnz = term_row_base[k] + (i - w.term_ptr[k]) * nb * n;
-  w.row_ptr[i] = nnz;
+  const bool packed = w.rows_packed != 0;
+  const unsigned keep = packed ? static_cast<unsigned>(pairDofMask(v, cp->link_ids[0], cp->link_ids[1])) : ~0u;
+  long long nnz = packed ? w.row_ptr[i] : term_row_base[k] + (i - w.term_ptr[k]) * nb * n;
+  if (!packed)
+    w.row_ptr[i] = nnz;
   w.row_block[2 * i] = b0 ? term * n : -1;
   w.row_block[2 * i + 1] = b1 ? (term + 1) * n : -1;
   w.row_pair[i] = pair;
@@ -906,10 +944,16 @@ __global__ void __launch_bounds__(TPB, TC_GRADROWS_MINB) k_grad_rows_regs(SceneV
         const double s = sum.s0[jj];
         if (legacy)
           constant = fma(-s, q0[jj], constant);
-        val[nnz + jj] = legacy ? s : -1.0 * s;
-        col_idx[nnz + jj] = term * n + jj;
+        if ((keep >> jj) & 1u)
+        {
+          // dense rows: slot jj; packed rows: the joints kept below jj come first (col_idx is not part of that form)
+          const int at = packed ? __popc(keep & ((1u << jj) - 1u)) : jj;
+          val[nnz + at] = legacy ? s : -1.0 * s;
+          if (!packed)
+            col_idx[nnz + at] = term * n + jj;
+        }
       }
-    nnz += n;
+    nnz += packed ? __popc(keep) : n;
   }
   if (b1)
   {
@@ -920,8 +964,13 @@ __global__ void __launch_bounds__(TPB, TC_GRADROWS_MINB) k_grad_rows_regs(SceneV
         const double s = sum.s1[jj];
         if (legacy)
           constant = fma(-s, q0[n + jj], constant);
-        val[nnz + jj] = legacy ? s : -1.0 * s;
-        col_idx[nnz + jj] = (term + 1) * n + jj;
+        if ((keep >> jj) & 1u)
+        {
+          const int at = packed ? __popc(keep & ((1u << jj) - 1u)) : jj;
+          val[nnz + at] = legacy ? s : -1.0 * s;
+          if (!packed)
+            col_idx[nnz + at] = (term + 1) * n + jj;
+        }
       }
   }
   row_value[i] = legacy ? constant : (pr.margin - distance);
@@ -1590,6 +1639,16 @@ cudaError_t launchRows(const SceneView& v, const Work& w, long long* term_row_ba
   k_rows<<<gridFor(w.n_contacts + 1, TPB), TPB, 0, st>>>(v, w, term_row_base, col_idx, val, row_value, row_coeff,
                                                        row_margin);
   return cudaGetLastError();
+}
+
+cudaError_t launchRowWidths(const SceneView& v, const Work& w, void* temp, size_t& temp_bytes, cudaStream_t st)
+{
+  const int n = static_cast<int>(w.n_contacts + 1);
+  if (!temp)
+    return cub::DeviceScan::ExclusiveSum(nullptr, temp_bytes, w.row_width, w.row_ptr, n, st);
+  ++launchCounter();
+  k_row_width<<<gridFor(n, 256), 256, 0, st>>>(v, w, w.keys_alt);
+  return cub::DeviceScan::ExclusiveSum(temp, temp_bytes, w.row_width, w.row_ptr, n, st);
 }
 
 cudaError_t launchRowBase(const SceneView& v, const Work& w, long long* term_row_base, cudaStream_t st)

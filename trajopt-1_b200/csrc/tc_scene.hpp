@@ -48,6 +48,7 @@ struct HostScene
   std::vector<int32_t> path_ptr, path_frames;    // ancestor frames (root first, incl. self) of every frame
   std::vector<int32_t> link_frame;
   std::vector<int32_t> frame_link;               // first active link riding on a frame, -1 if none
+  std::vector<unsigned long long> link_dof_mask; // per link: bit j set if joint j moves the link (0 for static links)
   std::vector<double> link_pose;                 // [n_links][12] (static links)
   std::vector<ShapeD> shapes;
   std::vector<Vtx<double>> verts;                // link-frame hull vertices, 32 B each
@@ -77,6 +78,7 @@ struct SceneView
   const int32_t *path_ptr, *path_frames;
   const int32_t* link_frame;
   const int32_t* frame_link;
+  const unsigned long long* link_dof_mask;
   const double* link_pose;
   const ShapeD* shapes;
   const Vtx<double>* verts;
@@ -108,6 +110,7 @@ inline SceneView hostView(const HostScene& s)
   v.path_ptr = s.path_ptr.data(), v.path_frames = s.path_frames.data();
   v.link_frame = s.link_frame.data(), v.link_pose = s.link_pose.data();
   v.frame_link = s.frame_link.data();
+  v.link_dof_mask = s.link_dof_mask.data();
   v.shapes = s.shapes.data(), v.verts = s.verts.data(), v.verts_f32 = nullptr;
   v.active_shapes = s.active_shapes.data(), v.static_aabb = s.static_aabb.data();
   v.active_shape_frame = s.active_shape_frame.data();
@@ -262,6 +265,20 @@ inline void buildHostScene(const tc_scene_desc& d, HostScene& s)
       fail("active links must come first and carry a frame");
     if (d.link_frame[l] >= d.n_frames)
       fail("link frame out of range");
+  }
+  // joints that move a link = the movable frames on its chain path (the structural non-zeros of its Jacobian rows)
+  s.link_dof_mask.assign(static_cast<size_t>(d.n_links), 0ull);
+  for (int l = 0; l < d.n_links; ++l)
+  {
+    const int lf = d.link_frame[l];
+    if (lf < 0)
+      continue;
+    for (int k = s.path_ptr[lf]; k < s.path_ptr[lf + 1]; ++k)
+    {
+      const int f = s.path_frames[k];
+      if (s.frame_type[f] != TC_JOINT_FIXED && s.frame_dof[f] < 64)
+        s.link_dof_mask[static_cast<size_t>(l)] |= 1ull << s.frame_dof[f];
+    }
   }
   s.frame_link.assign(static_cast<size_t>(d.n_frames), -1);
   for (int l = d.n_active_links - 1; l >= 0; --l)
