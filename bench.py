@@ -193,6 +193,10 @@ def other_configs(cu):
     ms2, c2 = timed(sa, qa, capi.EVAL_LVS_DISCRETE, capi.WANT_LINEARISE, lvs=LVS, fixed=fixed_steps())
     out["C4 seeds, LVS_DISCRETE term set (discrete half of discrete + cast)"] = {
         "ms_per_pass": ms2, "evals_per_s": c2["n_dense"] / (ms2 * 1e-3), "n_contacts": c2["n_contacts"]}
+    ms3, c3 = timed(sa, qa, capi.EVAL_LVS_CONTINUOUS, capi.WANT_LINEARISE, lvs=LVS, fixed=fixed_steps(),
+                    precision=capi.PRECISION_F32)
+    out["C4 seeds, LVS_CONTINUOUS in FP32 (TC_PRECISION_F32; tolerance: tests/test_gpu_fullsize.py::test_fp32_mode_tolerance)"] = {
+        "ms_per_pass": ms3, "evals_per_s": c3["n_dense"] / (ms3 * 1e-3), "n_contacts": c3["n_contacts"]}
     # one SQP iteration of C2 with the QP: linearisation pass + QP build and solve + one geometry pass at the trial point
     from tests import sqp
     prob = sqp.CollisionProblem(cu, arm, arm["seed_traj"], capi.EVAL_LVS_CONTINUOUS, MARGIN, COEFF, BUFFER, LVS)

@@ -74,14 +74,18 @@ def _properties(cuda, B, min_contacts, lo):
 @gpu
 @pytest.mark.parametrize("evaluator", [capi.EVAL_LVS_DISCRETE, capi.EVAL_LVS_CONTINUOUS])
 def test_fp32_mode_tolerance(cuda, oracle, evaluator):
-    """FP32 narrow phase (TC_PRECISION_F32) against the FP64 oracle.  Stated (measured, round 1) tolerance of the
-    FP32 mode, which is NOT the parity mode:
-      * distances: median <= 1e-7 m, 99 % <= 1e-6 m, 99.9 % <= 1e-4 m, worst case <= 5e-3 m (a few float GJK runs
-        stop on a sliver simplex one step early);
-      * gradient rows: 99 % within 1e-3 relative;
+    """FP32 narrow phase (TC_PRECISION_F32) against the FP64 oracle.  Stated tolerance of the FP32 mode, which is NOT
+    the parity mode (measured in round 2 on 128 seeds: 2e-8 / 8e-8 / 6e-7 / 3e-5 m; gradients 1e-7 / 3e-5 at the
+    median / 99 %; cost 8e-7):
+      * distances: median <= 1e-7 m, 99 % <= 1e-6 m, 99.9 % <= 1e-5 m, worst case <= 1e-4 m.  The worst case is bounded
+        by construction: a float GJK run may only report a result whose last gap test was below 5e-5 m, a float EPA
+        only one whose bracket closed to 2e-6 m; every other item (1-3 % of them) is re-run in FP64 by the kernel that
+        also takes polytope overflows (tc_narrow.cuh: gjk `certified`, epaStalled);
+      * gradient rows: 99 % within 1e-4 relative (the rest are normals of near-touching pairs, whose direction float
+        resolves to ~1e-3);
       * contact sets: at most 2e-4 of the oracle's contacts missing or extra outside a 1e-4 m band around
-        margin+buffer (deep penetrations whose float EPA does not close);
-      * trajectory cost within 1e-2 relative."""
+        margin+buffer;
+      * trajectory cost within 1e-5 relative."""
     s, sg = _scene(cuda)
     _, so = _scene(oracle)
     q = ms.make_batch(s, 100, 32)
@@ -93,10 +97,10 @@ def test_fp32_mode_tolerance(cuda, oracle, evaluator):
     _, a, b = np.intersect1d(helpers.packed_keys(co), helpers.packed_keys(cg), assume_unique=True, return_indices=True)
     de = np.abs(co["distance"][a] - cg["distance"][b])
     p50, p99, p999, worst = np.percentile(de, [50, 99, 99.9, 100])
-    assert p50 <= 1e-7 and p99 <= 1e-6 and p999 <= 1e-4 and worst <= 5e-3, (p50, p99, p999, worst)
+    assert p50 <= 1e-7 and p99 <= 1e-6 and p999 <= 1e-5 and worst <= 1e-4, (p50, p99, p999, worst)
     _, go = ro.gradients()
     _, gg = rg.gradients()
     go, gg = go[a].reshape(len(a), -1), gg[b].reshape(len(b), -1)
     rel = np.abs(go - gg).max(axis=1) / np.maximum(np.abs(go).max(axis=1), 1e-12)
-    assert np.percentile(rel, 99) <= 1e-3, np.percentile(rel, [50, 99, 99.9, 100])
-    assert rep["max_cost_rel_err"] <= 1e-2, rep
+    assert np.percentile(rel, 99) <= 1e-4, np.percentile(rel, [50, 99, 99.9, 100])
+    assert rep["max_cost_rel_err"] <= 1e-5, rep

@@ -335,6 +335,28 @@ __global__ void __launch_bounds__(TC_GJK_NT, MINB * 128 / TC_GJK_NT) k_gjk(Scene
       }
 #endif
       storeHit<R>(w, d, u, sp, d.status == ND_CONTACT);
+      if (sizeof(R) == sizeof(float))
+      {
+        // float GJK that ended without an error bound (tc_narrow.cuh, gjk): re-run in FP64 with the overflow list
+        const bool redo = d.status == ND_EPA_OVERFLOW;
+        const unsigned mr = __ballot_sync(0xffffffffu, redo);
+        if (mr)
+        {
+          const unsigned lane = threadIdx.x & 31;
+          const int leader = __ffs(mr) - 1;
+          unsigned long long dbase = 0;
+          if (lane == static_cast<unsigned>(leader))
+            dbase = atomicAdd(reinterpret_cast<unsigned long long*>(&w.counters->n_deep),
+                              static_cast<unsigned long long>(__popc(mr)));
+          dbase = __shfl_sync(0xffffffffu, dbase, leader);
+          if (redo)
+          {
+            const unsigned long long ds = dbase + __popc(mr & ((1u << lane) - 1u));
+            w.deep_items[2 * ds] = u;
+            w.deep_items[2 * ds + 1] = sp;
+          }
+        }
+      }
       const bool need = d.status == ND_NEED_EPA;
       const unsigned m = __ballot_sync(0xffffffffu, need);
       if (m)

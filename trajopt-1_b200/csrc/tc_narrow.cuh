@@ -538,6 +538,7 @@ template <class R>
 struct GjkOut
 {
   bool separated_beyond, intersect, converged;
+  bool certified;  // the loop ended on a test that bounds the error (gap, separation, enclosure); see gjk()
   R dist;
   Vec3<R> pa, pb;
   int iters;
@@ -564,6 +565,7 @@ TC_HD GjkOut<R> gjk(const PLA& A, const PLB& B, R threshold_core, Simplex<R>& S,
   r.separated_beyond = false;
   r.intersect = false;
   r.converged = true;
+  r.certified = true;
   r.dist = 0;
   Vec3<R> v = A.center() - B.center();
   if (norm2(v) < Tol<R>::centerTiny())
@@ -608,8 +610,16 @@ TC_HD GjkOut<R> gjk(const PLA& A, const PLB& B, R threshold_core, Simplex<R>& S,
       dup = true;
     if (S.n > 2 && norm2(w - S.w[2]) <= dupt)
       dup = true;
+    // The two exits below (support point seen before; no progress within rounding) end GJK on the closest point found
+    // so far WITHOUT a bound on its error.  In FP64 they fire within ~1e-10 m of the gap test; in FP32 a sliver simplex
+    // can trigger them centimetres early, so a float run that leaves through them with a gap above 5e-5 m is not
+    // reported: the item is re-run in FP64 (distanceGjk)
+    const bool open_gap = sizeof(R) == sizeof(float) && vv - vw > R(5e-5) * tc_sqrt(vv);
     if (dup)
+    {
+      r.certified = !open_gap;
       break;
+    }
     putPoint(S, S.n, w, a);  // slots >= n are free: S itself is untouched until the commit below
     R lam[4];
     int mask;
@@ -623,12 +633,15 @@ TC_HD GjkOut<R> gjk(const PLA& A, const PLB& B, R threshold_core, Simplex<R>& S,
     }
     const R vvn = norm2(vn);
     if (vvn >= vv)
+    {
+      r.certified = !open_gap;
       break;  // no progress within rounding: S already holds the closest point
+    }
     compactSimplex(S, lam, mask);
     v = vn;
     vv = vvn;
     if (r.iters == GJK_MAX_ITERS)
-      r.converged = false;
+      r.converged = false, r.certified = false;
   }
   if (!r.intersect)
   {
@@ -1034,8 +1047,8 @@ TC_HD int epaTripMasked(const PLA& A, const PLB& B, EpaStore<R>& st, EpaState<R>
       }
     }
   }
-  if (vis == 0)
-    return EPA_DONE;  // numerically x is not outside any face although the gap test said so: accept the face
+  if (vis == 0)  // numerically x is not outside any face although the gap test said so: accept the face (FP32: re-run)
+    return sizeof(R) == sizeof(float) ? EPA_OVERFLOW : EPA_DONE;
   for (unsigned long long m = vis; m; m &= m - 1)
   {
     const int fv = st.fv[lowestBit(m)];
@@ -1077,7 +1090,7 @@ TC_HD int epaTripMasked(const PLA& A, const PLB& B, EpaStore<R>& st, EpaState<R>
   if (overflow)
     return EPA_OVERFLOW;
   if (ne == 0)
-    return EPA_DONE;
+    return sizeof(R) == sizeof(float) ? EPA_OVERFLOW : EPA_DONE;
   E.alive &= ~vis;
   const int xi = E.np;
   st.pw[xi] = xw;
@@ -1369,6 +1382,11 @@ TC_HD void distanceGjk(const PLA& A, const PLB& B, R threshold, Simplex<R>& S, D
   if (g.intersect)
   {
     out.status = ND_NEED_EPA;
+    return;
+  }
+  if (sizeof(R) == sizeof(float) && !g.certified)
+  {
+    out.status = ND_EPA_OVERFLOW;  // float run without an error bound: the FP64 re-run kernel takes the item
     return;
   }
   finishDist(A, B, threshold, g.dist, (R(1) / g.dist) * (g.pb - g.pa), g.pa, g.pb, out);
