@@ -74,6 +74,48 @@ def test_noalloc_on_a_caller_stream(cuda):
     assert np.count_nonzero(want) > 0
 
 
+def test_noalloc_inside_a_cuda_graph(cuda):
+    """the use the entry point exists for: captured into a CUDA graph (no allocation, no synchronisation, the scratch
+    address resolved by tc_init beforehand) and replayed on new inputs written into the same device arrays"""
+    import torch
+    s = helpers.load_scene("arm_around_table")
+    sg = cuda.scene(s, 0.025, 20.0, 0.01)
+    fixed = np.zeros(s["seed_traj"].shape[0], np.uint8)
+    fixed[0] = fixed[-1] = 1
+    B = 12
+    runs = [cuda.eval(sg, _batch(s, B, seed), capi.EVAL_LVS_CONTINUOUS, lvs=0.05, fixed=fixed,
+                      result=None) for seed in (21, 22)]
+    _, _, margin, coeff = sg.pairs()
+    dev = torch.device("cuda:0")
+    n_terms = runs[0].counts()["n_terms"]
+    cap = max(len(r.contacts()) for r in runs)
+    term_ptr = torch.zeros(n_terms + 1, dtype=torch.int64, device=dev)
+    dist, mar, coe = (torch.zeros(cap, dtype=torch.float64, device=dev) for _ in range(3))
+    out = torch.zeros(B, dtype=torch.float64, device=dev)
+
+    def load(r):
+        c = r.contacts()
+        term_ptr.copy_(torch.from_numpy(r.term_ptr()))
+        dist[:len(c)].copy_(torch.from_numpy(np.ascontiguousarray(c["distance"])))
+        mar[:len(c)].copy_(torch.from_numpy(np.ascontiguousarray(margin[c["pair"]])))
+        coe[:len(c)].copy_(torch.from_numpy(np.ascontiguousarray(coeff[c["pair"]])))
+
+    load(runs[0])
+    torch.cuda.synchronize()
+    g = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(g):
+        cuda.check(cuda.cost_noalloc(term_ptr.data_ptr(), n_terms, n_terms // B, dist.data_ptr(), mar.data_ptr(),
+                                     coe.data_ptr(), out.data_ptr(), stream=torch.cuda.current_stream().cuda_stream))
+    for r in (runs[0], runs[1], runs[0]):
+        load(r)
+        out.fill_(float("nan"))
+        g.replay()
+        torch.cuda.synchronize()
+        _, want = r.cost()
+        assert np.allclose(out.cpu().numpy(), want, rtol=COST_TOL, atol=0.0)
+    assert np.count_nonzero(runs[1].cost()[1]) > 0
+
+
 def test_noalloc_rejects_sizes_beyond_the_static_scratch(cuda):
     import torch
     dev = torch.device("cuda:0")

@@ -1,6 +1,6 @@
 #!/usr/bin/env python3
-"""Prints the stage times of one C4 linearisation pass (tuning probe; env TC_LIB_PATH / TC_GJK_RUN / TC_EPA_RUN /
-TC_NARROW_VARIANT select the build and the launch shape)."""
+"""Prints the stage times of one C4 linearisation pass (tuning probe).  usage: narrow_probe.py [seeds] [reps]; env
+TC_LIB_PATH selects a build of tools/build_variant.sh, TC_PROBE_PREC=f32 / TC_PROBE_EVAL=discrete the mode, TAG a label."""
 import os
 import sys
 

@@ -35,12 +35,9 @@ namespace tc
 #ifndef TC_GJK_RUN
 #define TC_GJK_RUN 512
 #endif
-#ifndef TC_EPA_RUN
-#define TC_EPA_RUN 1024
-#endif
 constexpr int CHUNK = TC_CHUNK;  // bucket padding unit = threads per narrow-phase CTA
-// items one narrow-phase CTA works through (hulls are staged once per run of one shape pair)
-constexpr int GJK_RUN_ITEMS = TC_GJK_RUN, EPA_RUN_ITEMS = TC_EPA_RUN;
+// items one GJK CTA works through (hulls are staged once per run of one shape pair)
+constexpr int GJK_RUN_ITEMS = TC_GJK_RUN;
 constexpr int MAX_FRAMES = 64;
 #ifndef TC_EPA_VERTS
 #define TC_EPA_VERTS 34
