@@ -1680,7 +1680,11 @@ static int pipelineEvalRows(tc_pipeline* p, const tc_eval_desc* desc, const doub
     return TC_OK;
   };
   std::vector<std::pair<SubBatch, int64_t>> bases;  // (sub-batch, first row) for the final term_ptr shift
-  int pending_slot = -1;
+  std::vector<int> pending;  // slots whose pass is enqueued and not yet finished, oldest first
+  static const int depth = [] {
+    const char* e = getenv("TC_PIPELINE_DEPTH");  // tuning aid: passes enqueued beyond the one being waited for
+    return e ? std::max(1, atoi(e)) : 1;
+  }();
   auto finishSlot = [&](int s) -> int {
     InFlight& g = slot[static_cast<size_t>(s)];
     TC_TRY(download(g));
@@ -1691,11 +1695,12 @@ static int pipelineEvalRows(tc_pipeline* p, const tc_eval_desc* desc, const doub
   {
     const int s = static_cast<int>(j % static_cast<size_t>(K));
     InFlight& f = slot[static_cast<size_t>(s)];
-    if (f.evaluating)
+    while (f.evaluating)
     {
-      // a one-slot ring: the sub-batch still in the slot goes first (rows stay in sub-batch order)
-      TC_TRY(finishSlot(s));
-      pending_slot = -1;
+      // the ring came round to a slot whose sub-batch is still computing: finish the oldest ones first (rows stay in
+      // sub-batch order)
+      TC_TRY(finishSlot(pending.front()));
+      pending.erase(pending.begin());
     }
     if (f.downloading)
     {
@@ -1713,13 +1718,16 @@ static int pipelineEvalRows(tc_pipeline* p, const tc_eval_desc* desc, const doub
                    p->streams[static_cast<size_t>(s)]));
     tpt = f.r->ep.terms_per_traj;
     f.evaluating = true;
-    // the one before it (on another stream) finishes while this one is already queued
-    if (pending_slot >= 0)
-      TC_TRY(finishSlot(pending_slot));
-    pending_slot = s;
+    // the ones before it (on other streams) finish while this one is already queued
+    pending.push_back(s);
+    while (static_cast<int>(pending.size()) > depth)
+    {
+      TC_TRY(finishSlot(pending.front()));
+      pending.erase(pending.begin());
+    }
   }
-  if (pending_slot >= 0)
-    TC_TRY(finishSlot(pending_slot));
+  for (int s : pending)
+    TC_TRY(finishSlot(s));
   for (int s = 0; s < K; ++s)
     if (slot[static_cast<size_t>(s)].downloading)
       TC_CUDA(cudaStreamSynchronize(p->streams[static_cast<size_t>(s)]));
