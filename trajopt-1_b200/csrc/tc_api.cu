@@ -513,6 +513,15 @@ int runEval(tc_scene* scene, const tc_eval_desc* desc, const double* q, int32_t 
       fprintf(stderr, "[tc] n_epa=%lld n_deep=%lld n_curved=%lld epa_iters=%lld gjk_iters=%lld n_items=%lld group_max_epa=%lld group_max_gjk=%lld\n",
               r->h_counters->n_epa, n_deep, n_curved, r->h_counters->epa_iters, r->h_counters->gjk_iters,
               r->h_counters->n_items, r->h_counters->dbg[0], r->h_counters->dbg[1]);
+#ifdef TC_NARROW_HIST
+    if (trace_deep)
+    {
+      unsigned long long sd[4];
+      cudaDeviceSynchronize();
+      narrowScanDebug(sd);
+      fprintf(stderr, "[tc] epa plane scan: faces tested %llu, skippable by |x| < d %llu, visible %llu\n", sd[0], sd[1], sd[2]);
+    }
+#endif
     if (trace_deep)
       fprintf(stderr, "[tc] epa items with >= 11/15/19/23/27/31 trips: %lld %lld %lld %lld %lld %lld\n", r->h_counters->dbg[2],
               r->h_counters->dbg[3], r->h_counters->dbg[4], r->h_counters->dbg[5], r->h_counters->dbg[6], r->h_counters->dbg[7]);

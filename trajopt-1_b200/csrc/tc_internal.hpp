@@ -178,6 +178,9 @@ cudaError_t launchBroadCount(const SceneView& v, const Work& w, cudaStream_t st)
 cudaError_t launchBroadFill(const SceneView& v, const Work& w, cudaStream_t st);
 // phase 0: every raw hit; 1: the first n_raw0 of them; 2: the rest and the surplus entries of the sort
 cudaError_t launchFinalize(const SceneView& v, const Work& w, int phase, cudaStream_t st);
+#ifdef TC_NARROW_HIST
+void narrowScanDebug(unsigned long long out[4]);  // tuning builds: counters of the EPA plane scan since the last call
+#endif
 cudaError_t sortContacts(const Work& w, void* temp, size_t& temp_bytes, cudaStream_t st);  // result in *_alt
 cudaError_t launchGather(const SceneView& v, const Work& w, cudaStream_t st);
 cudaError_t launchGradients(const SceneView& v, const Work& w, cudaStream_t st);

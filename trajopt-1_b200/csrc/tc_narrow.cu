@@ -584,6 +584,15 @@ __global__ void k_fma_peak(R* out, int iters)
 }
 }  // namespace
 
+#ifdef TC_NARROW_HIST
+void narrowScanDebug(unsigned long long out[4])
+{
+  cudaMemcpyFromSymbol(out, g_scan_dbg, 4 * sizeof(unsigned long long));
+  const unsigned long long zero[4] = { 0, 0, 0, 0 };
+  cudaMemcpyToSymbol(g_scan_dbg, zero, sizeof(zero));
+}
+#endif
+
 // register budgets (resident CTAs of 128 threads per SM) of the two kernels; build-time tuning knobs
 #ifndef TC_GJK_MINB
 #define TC_GJK_MINB 4

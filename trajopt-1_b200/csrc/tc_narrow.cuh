@@ -990,6 +990,10 @@ TC_HD int lowestBit(unsigned long long x)
 //      and cancels), 3. visible faces again, slot order: the edges still set are the horizon, in the order the
 //      list-based form produces them, 4. one new face per horizon edge.
 // `erow` is all-zero on entry and on exit.
+#if defined(TC_NARROW_HIST) && defined(__CUDACC__)
+static __device__ unsigned long long g_scan_dbg[4];  // faces scanned, faces a norm bound would have skipped, faces visible
+#endif
+
 template <class R, class PLA, class PLB>
 TC_HD int epaTripMasked(const PLA& A, const PLB& B, EpaStore<R>& st, EpaState<R>& E,
                         unsigned long long* erow, ScanCount& scanned)
@@ -1035,6 +1039,16 @@ TC_HD int epaTripMasked(const PLA& A, const PLB& B, EpaStore<R>& st, EpaState<R>
     for (int k = 0; k < 4; ++k)
     {
       const bool visible = (fd[k] != DEGENERATE) && (dot(fn[k], xw) - fd[k] > E.vis_eps);
+#if defined(TC_NARROW_HIST) && defined(__CUDA_ARCH__)
+      if (ok[k])
+      {
+        atomicAdd(&g_scan_dbg[0], 1ull);
+        if (fd[k] > 0 && norm2(xw) < fd[k] * fd[k] * (R(1) - R(1e-12)))
+          atomicAdd(&g_scan_dbg[1], 1ull);
+        if (visible)
+          atomicAdd(&g_scan_dbg[2], 1ull);
+      }
+#endif
       if (ok[k])
       {
         if (visible)
