@@ -56,6 +56,24 @@ struct QLerp
   TC_HD double operator()(int j) const { return q0[j] + (q1[j] - q0[j]) * t; }
 };
 
+// the joint values getGradient(dofvals0, dofvals1, ...) evaluates a link at: the first state for a contact at TIME0, the
+// second for TIME1, the interpolated state otherwise (collision_utils.cpp:176-221) — one accessor, so that a warp whose
+// contacts are of different kinds still runs ONE copy of the chain walk
+struct QByKind
+{
+  const double *q0, *q1;
+  double t;
+  int kind;  // TC_CC_TIME0 / TC_CC_TIME1 / anything else = interpolate
+  TC_HD double operator()(int j) const
+  {
+    if (kind == TC_CC_TIME0)
+      return q0[j];
+    if (kind == TC_CC_TIME1)
+      return q1[j];
+    return q0[j] + (q1[j] - q0[j]) * t;
+  }
+};
+
 // pose of frame f given its parent's pose; axis_w = world joint axis
 template <class QA>
 TC_HD Pose<double> frameStepA(const SceneView& v, const Pose<double>& parent, int f, const QA& q, Vec3<double>& axis_w)

@@ -913,13 +913,8 @@ __global__ void __launch_bounds__(TPB, TC_GRADROWS_MINB) k_grad_rows_regs(SceneV
     {
       // both blocks share the joint values: one chain walk, two reference points
       const Vec3<double> ref0 = rotBy(t0, pl), ref1 = rotBy(cc ? t1 : t0, pl);
-      auto emit = [&](int j, double g0, double g1) { sum.add(j, true, sc0, g0, true, sc1, g1); };
-      if (cct == TC_CC_TIME0)
-        pointGradientWalk(v, link, QArray{ q0 }, ref0, ref1, tv, emit);
-      else if (cct == TC_CC_TIME1)
-        pointGradientWalk(v, link, QArray{ q1 }, ref0, ref1, tv, emit);
-      else
-        pointGradientWalk(v, link, QLerp{ q0, q1, cc_time }, ref0, ref1, tv, emit);
+      pointGradientWalk(v, link, QByKind{ q0, q1, cc_time, cct }, ref0, ref1, tv,
+                        [&](int j, double g0, double g1) { sum.add(j, true, sc0, g0, true, sc1, g1); });
     }
   }
   // writeRow
